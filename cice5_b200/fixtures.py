@@ -1,0 +1,475 @@
+"""Deterministic synthetic grids, ice state and forcing for the EVP path.
+
+Everything here is host-side numpy.  Arrays are ONE global block with a width-1 ghost ring,
+shape ``(ny+2, nx+2)`` C-contiguous, i.e. exactly the Fortran ``(nx_block, ny_block)`` layout
+(``a[j-1, i-1]`` is Fortran ``a(i,j)``).  A slab for rank ``r`` of ``N`` is the column slice
+``[:, r*nxl : r*nxl + nxl + 2]`` (see :func:`slab`), which is what the reference's block
+decomposition hands each task for an x-slab (``ice_blocks.F90:205-311``).
+
+Grid metrics follow the reference's construction so that the ghost cells hold what the
+reference's ``init_grid2`` leaves in them:
+  * ``primary_grid_lengths_HTN/HTE``  (``source/ice_grid.F90:1408-1545``)
+  * ``scatter_global`` ghost rules    (``serial/ice_gather_scatter.F90:486-719``)
+  * ``init_grid2``                     (``source/ice_grid.F90:338-406``)
+  * ``makemask``                       (``source/ice_grid.F90:1555-1617``)
+  * ``ice_HaloUpdate`` semantics       (``serial/ice_boundary.F90:630-896``; MPI ring pre-fill)
+This module never imports the oracle.
+"""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass, field
+
+import numpy as np
+
+_DATA = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data")
+
+# drivers/cice/ice_constants.F90:21-38 (AusCOM: radius 6.371e6, runtime dragio)
+RHOS, RHOI, RHOW = 330.0, 917.0, 1026.0
+DRAGIO = 0.00536
+GRAVIT = 9.80616
+OMEGA = 7.292e-5
+PUNY = 1.0e-11
+RADIUS = 6.371e6
+PSTAR, CSTAR = 2.75e4, 20.0  # ice_mechred.F90:80-82
+
+CENTER, NECORNER, NFACE, EFACE = 0, 1, 2, 3
+SCALAR, VECTOR = 0, 1
+
+
+@dataclass
+class Domain:
+    nx: int
+    ny: int
+    ew_cyclic: bool = True
+    ns_tripole: bool = False      # ns_boundary_type == 'tripole' (u-fold)
+    ns_open: bool = True          # 'open' (grid ghosts mirror) vs 'closed' (ghosts 0); halos fill either way
+    grid_tripole: bool = False    # grid_type == 'tripole'
+    name: str = ""
+
+
+# --------------------------------------------------------------------------------------
+# ghost filling
+# --------------------------------------------------------------------------------------
+def _wrap_cols(dom: Domain, a: np.ndarray, fill: float) -> None:
+    """E-W ghosts of the physical rows."""
+    if dom.ew_cyclic:
+        a[1:-1, 0] = a[1:-1, -2]
+        a[1:-1, -1] = a[1:-1, 1]
+    else:
+        a[1:-1, 0] = fill
+        a[1:-1, -1] = fill
+
+
+def halo_update(dom: Domain, a: np.ndarray, loc: int = CENTER, kind: int = SCALAR,
+                fill: float = 0.0) -> np.ndarray:
+    """``ice_HaloUpdate`` on a global-with-ghost array, in place (MPI pre-fill semantics).
+
+    Only ``center`` and ``NEcorner`` locations are supported (all that ``evp`` uses)."""
+    nx, ny = dom.nx, dom.ny
+    assert a.shape == (ny + 2, nx + 2)
+    a[0, :] = fill
+    a[-1, :] = fill
+    a[:, 0] = fill
+    a[:, -1] = fill
+    _wrap_cols(dom, a, fill)
+    if dom.ns_tripole:
+        isign = 1.0 if kind == SCALAR else -1.0
+        buf1 = a[ny - 1, 1:nx + 1].copy()   # global row ny-1
+        buf2 = a[ny, 1:nx + 1].copy()       # global row ny
+        ig = np.arange(0, nx + 2)           # global column of local column i (1-based i = index+1)
+        ig[0] = nx
+        ig[-1] = 1
+        if loc == CENTER:
+            isrc = nx - ig + 1
+            isrc[isrc == 0] = nx
+            isrc[isrc > nx] -= nx
+            a[ny + 1, :] = isign * buf2[isrc - 1]
+        elif loc == NECORNER:
+            for i in range(1, nx // 2):     # i = 1 .. nx/2 - 1
+                m = nx - i
+                x1, x2 = buf2[i - 1], buf2[m - 1]
+                xavg = 0.5 * (x1 + isign * x2)
+                buf2[i - 1] = xavg
+                buf2[m - 1] = isign * xavg
+            isrc = nx - ig
+            isrc[isrc == 0] = nx
+            isrc[isrc > nx] -= nx
+            a[ny, :] = isign * buf2[isrc - 1]
+            a[ny + 1, :] = isign * buf1[isrc - 1]
+        else:
+            raise ValueError("halo_update: unsupported field location")
+    return a
+
+
+def scatter_global(dom: Domain, g: np.ndarray, loc: int, kind: int = SCALAR) -> np.ndarray:
+    """``scatter_global`` of a physical (ny, nx) array to one block with ghosts."""
+    nx, ny = dom.nx, dom.ny
+    a = np.zeros((ny + 2, nx + 2), dtype=g.dtype)
+    a[1:-1, 1:-1] = g
+    if dom.ew_cyclic:
+        a[1:-1, 0] = g[:, -1]
+        a[1:-1, -1] = g[:, 0]
+    ig = np.arange(0, nx + 2)
+    ig[0] = nx
+    ig[-1] = 1
+    cols = slice(None) if dom.ew_cyclic else slice(1, nx + 1)
+    if dom.ns_tripole or dom.ns_open:
+        a[0, cols] = a[1, cols]             # j_glob = 1 (ice_blocks.F90:213-218)
+    if dom.ns_tripole:
+        isign = 1 if kind == SCALAR else -1
+        xoff, yoff = {CENTER: (1, 1), NECORNER: (0, 0), EFACE: (0, 1), NFACE: (1, 0)}[loc]
+        jsrc = ny + yoff - 1                # serial/ice_gather_scatter.F90:652-655
+        isrc = nx + xoff - ig
+        isrc[isrc < 1] += nx
+        isrc[isrc > nx] -= nx
+        row = isign * g[jsrc - 1, isrc - 1]
+        if dom.ew_cyclic:
+            a[ny + 1, :] = row
+        else:
+            a[ny + 1, 1:nx + 1] = row[1:nx + 1]
+    elif dom.ns_open:
+        a[ny + 1, cols] = a[ny, cols]       # j_glob = ny (ice_blocks.F90:238-240)
+    return a
+
+
+# --------------------------------------------------------------------------------------
+# grid
+# --------------------------------------------------------------------------------------
+@dataclass
+class Grid:
+    dom: Domain
+    f: dict = field(default_factory=dict)   # name -> (ny+2, nx+2) array
+    ulat: np.ndarray | None = None           # physical (ny, nx) radians (U points)
+    tlat: np.ndarray | None = None
+    tlon: np.ndarray | None = None
+
+
+def build_grid(dom: Domain, HTN: np.ndarray, HTE: np.ndarray, ULAT: np.ndarray,
+               kmt: np.ndarray) -> Grid:
+    """Metrics and masks from global HTN/HTE (metres), ULAT (radians), kmt, as the reference does."""
+    nx, ny = dom.nx, dom.ny
+    assert HTN.shape == (ny, nx) and HTE.shape == (ny, nx)
+    # primary_grid_lengths_HTN (ice_grid.F90:1439-1462)
+    dxu = 0.5 * (HTN + np.roll(HTN, -1, axis=1))
+    dxt = np.empty_like(HTN)
+    dxt[1:, :] = 0.5 * (HTN[1:, :] + HTN[:-1, :])
+    dxt[0, :] = 2.0 * HTN[1, :] - HTN[2, :]
+    # primary_grid_lengths_HTE (ice_grid.F90:1509-1537)
+    dyu = np.empty_like(HTE)
+    dyu[:-1, :] = 0.5 * (HTE[:-1, :] + HTE[1:, :])
+    dyu[-1, :] = 2.0 * HTE[-2, :] - HTE[-3, :]
+    dyt = 0.5 * (HTE + np.roll(HTE, 1, axis=1))
+
+    f = {}
+    htn = scatter_global(dom, HTN, NFACE)
+    hte = scatter_global(dom, HTE, EFACE)
+    f["dxu"] = scatter_global(dom, dxu, NECORNER)
+    f["dyu"] = scatter_global(dom, dyu, NECORNER)
+    f["dxt"] = scatter_global(dom, dxt, CENTER)
+    f["dyt"] = scatter_global(dom, dyt, CENTER)
+    f["HTN"], f["HTE"] = htn, hte
+
+    z = lambda: np.zeros((ny + 2, nx + 2))
+    tarea, uarea, tarear, uarear, tinyarea, dxhy, dyhx = (z() for _ in range(7))
+    P = (slice(1, ny + 1), slice(1, nx + 1))
+    tarea[P] = f["dxt"][P] * f["dyt"][P]                      # ice_grid.F90:341-342
+    uarea[P] = f["dxu"][P] * f["dyu"][P]
+    with np.errstate(divide="ignore"):
+        tarear[P] = np.where(tarea[P] > 0.0, 1.0 / tarea[P], 0.0)
+        uarear[P] = np.where(uarea[P] > 0.0, 1.0 / uarea[P], 0.0)
+    tinyarea[P] = PUNY * tarea[P]
+    dxhy[P] = 0.5 * (hte[1:ny + 1, 1:nx + 1] - hte[1:ny + 1, 0:nx])     # :356
+    dyhx[P] = 0.5 * (htn[1:ny + 1, 1:nx + 1] - htn[0:ny, 1:nx + 1])     # :357
+    cyp, cxp, cym, cxm = (z() for _ in range(4))
+    Q = (slice(1, ny + 2), slice(1, nx + 2))                  # ilo..ihi+1, jlo..jhi+1 (:361-369)
+    cyp[Q] = 1.5 * hte[1:ny + 2, 1:nx + 2] - 0.5 * hte[1:ny + 2, 0:nx + 1]
+    cxp[Q] = 1.5 * htn[1:ny + 2, 1:nx + 2] - 0.5 * htn[0:ny + 1, 1:nx + 2]
+    cym[Q] = -(1.5 * hte[1:ny + 2, 0:nx + 1] - 0.5 * hte[1:ny + 2, 1:nx + 2])
+    cxm[Q] = -(1.5 * htn[0:ny + 1, 1:nx + 2] - 0.5 * htn[1:ny + 2, 1:nx + 2])
+    # ghost cell updates, fillValue = c1 (:385-405)
+    halo_update(dom, tarea, CENTER, SCALAR, 1.0)
+    halo_update(dom, uarea, NECORNER, SCALAR, 1.0)
+    halo_update(dom, tarear, CENTER, SCALAR, 1.0)
+    halo_update(dom, uarear, NECORNER, SCALAR, 1.0)
+    halo_update(dom, tinyarea, CENTER, SCALAR, 1.0)
+    halo_update(dom, dxhy, CENTER, VECTOR, 1.0)
+    halo_update(dom, dyhx, CENTER, VECTOR, 1.0)
+    f.update(tarea=tarea, uarea=uarea, tarear=tarear, uarear=uarear, tinyarea=tinyarea,
+             dxhy=dxhy, dyhx=dyhx, cyp=cyp, cxp=cxp, cym=cym, cxm=cxm)
+
+    # fcor_blk = 2*omega*sin(ULAT) (ice_dyn_shared.F90:150); only physical U points are read
+    ul = scatter_global(dom, ULAT, NECORNER)
+    f["fcor"] = 2.0 * OMEGA * np.sin(ul)
+
+    # makemask (ice_grid.F90:1555-1617)
+    hm = z()
+    hm[P] = (kmt >= 1).astype("f8")
+    halo_update(dom, hm, CENTER, SCALAR, 0.0)
+    uvm = z()
+    uvm[P] = np.minimum(np.minimum(hm[1:ny + 1, 1:nx + 1], hm[1:ny + 1, 2:nx + 2]),
+                        np.minimum(hm[2:ny + 2, 1:nx + 1], hm[2:ny + 2, 2:nx + 2]))
+    halo_update(dom, uvm, NECORNER, SCALAR, 0.0)
+    f["tmask"] = (hm > 0.5).astype(np.int32)
+    f["umask"] = (uvm > 0.5).astype(np.int32)
+    return Grid(dom=dom, f=f, ulat=ULAT)
+
+
+def _continents(nx: int, ny: int, tlat_deg: np.ndarray) -> np.ndarray:
+    """Three rectangular land masses covering ~30 % of the columns for |lat| < 60 deg."""
+    land = np.zeros((ny, nx), dtype=bool)
+    spans = [(0.05, 0.15), (0.40, 0.50), (0.72, 0.82)]
+    band = np.abs(tlat_deg) < 60.0
+    for a, b in spans:
+        i0, i1 = int(round(a * nx)), int(round(b * nx))
+        land[:, i0:i1] |= band[:, None]
+    return land
+
+
+def synthetic_tripole(nx: int, ny: int, name: str = "") -> Grid:
+    """Synthetic tripole (u-fold) grid, E-W cyclic ('Metrics', 'Masks').
+
+    Latitude runs from -78 to +89.5 deg for Coriolis and the ice caps; the zonal metric uses
+    cos(min(|lat|, 65 deg)) so that cells do not collapse towards the (synthetic) pole, as on a
+    real tripole grid whose northern cap is roughly isotropic.  The i-perturbations are built
+    explicitly symmetric under the fold maps (E face: i -> nx-i, N face: i -> nx+1-i).
+    """
+    dom = Domain(nx, ny, ew_cyclic=True, ns_tripole=True, ns_open=False, grid_tripole=True,
+                 name=name or f"tripole_{nx}x{ny}")
+    dphi = np.deg2rad(89.5 - (-78.0)) / ny
+    dlam = 2.0 * np.pi / nx
+    j = np.arange(1, ny + 1, dtype="f8")
+    i = np.arange(1, nx + 1, dtype="f8")
+    ulat = np.deg2rad(-78.0) + dphi * j                  # U point = NE corner of T cell
+    tlat = ulat - 0.5 * dphi
+    nlat_eff = np.minimum(np.abs(ulat), np.deg2rad(65.0))   # N face latitude (= ulat)
+    ie = np.minimum(i, nx - i)                           # E-face symmetric index (i=nx -> 0)
+    inn = np.minimum(i, nx + 1 - i) - 0.5                # N-face symmetric index
+    HTE = np.broadcast_to(RADIUS * dphi * (1.0 + 0.1 * np.cos(2.0 * np.pi * ie / nx)), (ny, nx)).copy()
+    HTN = (RADIUS * np.cos(nlat_eff) * dlam)[:, None] * (1.0 + 0.1 * np.cos(2.0 * np.pi * inn / nx))[None, :]
+    ULAT = np.broadcast_to(ulat[:, None], (ny, nx)).copy()
+    tlat_deg = np.rad2deg(tlat)
+    land = _continents(nx, ny, tlat_deg)
+    land[:2, :] = True                                   # rows j <= 2
+    # the two singular points of the fold (U points ig = nx/2 and ig = nx on the top row) are land:
+    # make the T cells around them land so that umask is false there
+    for ic in (nx // 2, nx):
+        cols = [(ic - 1) % nx, ic % nx]                  # T columns ic, ic+1 (0-based ic-1, ic)
+        land[ny - 2:, cols] = True
+    # symmetrise the land mask across the fold for the top rows (T cell i <-> nx+1-i)
+    top = land[ny - 3:, :]
+    land[ny - 3:, :] = top | top[:, ::-1]
+    kmt = np.where(land, 0, 1).astype(np.int32)
+    g = build_grid(dom, HTN, HTE, ULAT, kmt)
+    g.tlat = np.broadcast_to(tlat[:, None], (ny, nx)).copy()
+    g.tlon = np.broadcast_to(((i - 0.5) * dlam)[None, :], (ny, nx)).copy()
+    return g
+
+
+def synthetic_displaced(nx: int, ny: int, kmt: np.ndarray | None = None, name: str = "") -> Grid:
+    """Synthetic lat-lon-like grid with gx1/gx3 boundary types: E-W cyclic, N-S open."""
+    dom = Domain(nx, ny, ew_cyclic=True, ns_tripole=False, ns_open=True, grid_tripole=False,
+                 name=name or f"displaced_{nx}x{ny}")
+    dphi = np.deg2rad(88.0 - (-79.0)) / ny
+    dlam = 2.0 * np.pi / nx
+    j = np.arange(1, ny + 1, dtype="f8")
+    i = np.arange(1, nx + 1, dtype="f8")
+    ulat = np.deg2rad(-79.0) + dphi * j
+    tlat = ulat - 0.5 * dphi
+    nlat_eff = np.minimum(np.abs(ulat), np.deg2rad(70.0))
+    HTE = np.broadcast_to(RADIUS * dphi * (1.0 + 0.1 * np.cos(2.0 * np.pi * i / nx)), (ny, nx)).copy()
+    HTN = (RADIUS * np.cos(nlat_eff) * dlam)[:, None] * (1.0 + 0.1 * np.cos(2.0 * np.pi * (i - 0.5) / nx))[None, :]
+    ULAT = np.broadcast_to(ulat[:, None], (ny, nx)).copy()
+    if kmt is None:
+        land = _continents(nx, ny, np.rad2deg(tlat))
+        land[:2, :] = True
+        land[-2:, :] = True
+        kmt = np.where(land, 0, 1).astype(np.int32)
+    g = build_grid(dom, HTN, HTE, ULAT, kmt)
+    g.tlat = np.broadcast_to(tlat[:, None], (ny, nx)).copy()
+    g.tlon = np.broadcast_to(((i - 0.5) * dlam)[None, :], (ny, nx)).copy()
+    return g
+
+
+def gx3_grid() -> Grid:
+    """The reference's real gx3 grid (100 x 116, displaced pole, E-W cyclic, N-S open;
+    ``input_templates/gx3/ice_in:43-62``), lengths converted cm -> m as ``ice_grid.F90:1436``."""
+    z = np.load(os.path.join(_DATA, "gx3_grid.npz"))
+    cm_to_m = 0.01
+    dom = Domain(100, 116, ew_cyclic=True, ns_tripole=False, ns_open=True, grid_tripole=False, name="gx3")
+    g = build_grid(dom, z["HTN_cm"] * cm_to_m, z["HTE_cm"] * cm_to_m, z["ULAT"], z["kmt"])
+    ulat = z["ULAT"]
+    g.tlat = ulat.copy()      # T/U latitude difference is irrelevant for the synthetic ice state
+    g.tlon = np.broadcast_to((np.arange(100) + 0.5)[None, :] * (2 * np.pi / 100), (116, 100)).copy()
+    return g
+
+
+def gx1_grid() -> Grid:
+    """gx1 320 x 384: the reference's real kmt; the grid file is a missing blob so metrics are synthetic."""
+    kmt = np.load(os.path.join(_DATA, "gx1_kmt.npz"))["kmt"]
+    return synthetic_displaced(320, 384, kmt=kmt, name="gx1")
+
+
+GRIDS = {
+    "gx3": gx3_grid,
+    "gx1": gx1_grid,
+    "tp1": lambda: synthetic_tripole(360, 300, "tp1"),         # ACCESS-OM 1 deg
+    "tp025": lambda: synthetic_tripole(1440, 1080, "tp025"),   # ACCESS-OM 0.25 deg
+    "tp01": lambda: synthetic_tripole(3600, 2700, "tp01"),     # AusCOM 0.1 deg
+}
+
+# dt per grid: the model time steps these resolutions are run with (1 h for the coarse grids,
+# shorter for the eddy-rich ones); ndte = 120 everywhere (BASELINE.json configs).
+GRID_DT = {"gx3": 3600.0, "gx1": 3600.0, "tp1": 3600.0, "tp025": 1800.0, "tp01": 600.0}
+
+
+def make_grid(name: str) -> Grid:
+    return GRIDS[name]()
+
+
+# --------------------------------------------------------------------------------------
+# ice state and forcing
+# --------------------------------------------------------------------------------------
+IN_FIELDS = ("aice", "vice", "vsno", "aice_init", "strairxT", "strairyT", "uocn", "vocn",
+             "ss_tltx", "ss_tlty", "Cw", "strength")
+STRESS_FIELDS = tuple(f"stress{k}_{c}" for k in ("p", "m", "12") for c in (1, 2, 3, 4))
+INOUT_FIELDS = ("uvel", "vvel") + STRESS_FIELDS + ("fm",)
+OUT_FIELDS = ("strairx", "strairy", "strtltx", "strtlty", "strocnx", "strocny", "strintx",
+              "strinty", "strocnxT", "strocnyT", "divu", "shear", "rdg_conv", "rdg_shear",
+              "prs_sig", "uvel_init", "vvel_init", "tmass", "strength_out")
+GRID_FIELDS = ("dxt", "dyt", "dxhy", "dyhx", "cxp", "cyp", "cxm", "cym", "tarea", "uarea",
+               "tarear", "uarear", "tinyarea", "fcor")
+
+
+def _with_ghosts(dom: Domain, phys: np.ndarray, loc=CENTER, kind=SCALAR) -> np.ndarray:
+    a = np.zeros((dom.ny + 2, dom.nx + 2))
+    a[1:-1, 1:-1] = phys
+    return halo_update(dom, a, loc, kind, 0.0)
+
+
+def ice_state(grid: Grid, scenario: str = "full") -> dict:
+    """aice, vice, vsno, aice_init (ghosts current, as evp assumes: ice_dyn_evp.F90:158-169)
+    and the Hibler strength (ice_mechred.F90:2263) on all physical cells."""
+    dom = grid.dom
+    tm = grid.f["tmask"][1:-1, 1:-1] > 0
+    lam, phi = grid.tlon, grid.tlat
+    if scenario == "full":
+        aice = np.where(tm, 0.95, 0.0)
+        vice = np.where(tm, 0.95 * (2.0 + np.sin(2.0 * lam) * np.cos(3.0 * phi)), 0.0)
+    elif scenario == "caps":
+        absdeg = np.abs(np.rad2deg(phi))
+        ramp = np.clip((absdeg - 55.0) / 15.0, 0.0, 1.0)
+        aice = np.where(tm, 0.98 * ramp, 0.0)
+        h = 1.0 + 2.0 * np.clip((absdeg - 55.0) / 35.0, 0.0, 1.0)
+        vice = aice * h
+    else:
+        raise ValueError(scenario)
+    vsno = 0.2 * aice
+    strength = PSTAR * vice * np.exp(-CSTAR * (1.0 - aice))
+    s = {
+        "aice": _with_ghosts(dom, aice), "vice": _with_ghosts(dom, vice),
+        "vsno": _with_ghosts(dom, vsno), "strength": _with_ghosts(dom, strength),
+    }
+    s["aice_init"] = s["aice"].copy()
+    return s
+
+
+def forcing(grid: Grid, state: dict, step: int = 0, steps_per_cycle: int = 240) -> dict:
+    """Wind stress on T cells (translating cyclone), ocean gyre on U points, zero tilt,
+    constant ocean drag (SURVEY.md section 8d 'Forcing')."""
+    dom = grid.dom
+    nx, ny = dom.nx, dom.ny
+    aice = state["aice"][1:-1, 1:-1]
+    x = (np.arange(nx) + 0.5) / nx
+    y = (np.arange(ny) + 0.5) / ny
+    X, Y = np.meshgrid(x, y)
+    xc = (0.3 + step / float(steps_per_cycle)) % 1.0
+    U = np.zeros((ny, nx))
+    V = np.zeros((ny, nx))
+    for yc, sgn in ((0.88, 1.0), (0.10, -1.0)):         # one cyclone per polar cap
+        dx = X - xc
+        dx = dx - np.round(dx)                            # periodic in x
+        dy = Y - yc
+        r = np.sqrt(dx * dx + dy * dy) + 1e-12
+        amp = 15.0 * np.exp(-r / 0.12) * np.minimum(r / 0.02, 1.0)
+        U += sgn * amp * (-dy / r)
+        V += sgn * amp * (dx / r)
+    U += 3.0 * np.cos(2.0 * np.pi * Y)                    # weak background zonal wind
+    spd = np.sqrt(U * U + V * V)
+    rhoa, cd = 1.3, 1.3e-3
+    sx = aice * rhoa * cd * spd * U
+    sy = aice * rhoa * cd * spd * V
+    uo = 0.1 * np.sin(2.0 * np.pi * X) * np.cos(np.pi * (Y - 0.5))
+    vo = 0.05 * np.cos(2.0 * np.pi * X) * np.sin(2.0 * np.pi * Y)
+    um = grid.f["umask"][1:-1, 1:-1] > 0
+    uo = np.where(um, uo, 0.0)
+    vo = np.where(um, vo, 0.0)
+    z = np.zeros((ny + 2, nx + 2))
+    return {
+        "strairxT": _with_ghosts(dom, sx, CENTER, VECTOR),
+        "strairyT": _with_ghosts(dom, sy, CENTER, VECTOR),
+        "uocn": _with_ghosts(dom, uo, NECORNER, VECTOR),
+        "vocn": _with_ghosts(dom, vo, NECORNER, VECTOR),
+        "ss_tltx": z.copy(), "ss_tlty": z.copy(),
+        "Cw": np.full((ny + 2, nx + 2), DRAGIO),
+    }
+
+
+def initial_dynamic_state(dom: Domain) -> dict:
+    """init_evp: zero velocity, stresses, iceumask = .false. (ice_dyn_shared.F90:133-172)."""
+    z = lambda: np.zeros((dom.ny + 2, dom.nx + 2))
+    s = {k: z() for k in INOUT_FIELDS}
+    s["iceumask"] = np.zeros((dom.ny + 2, dom.nx + 2), dtype=np.int32)
+    return s
+
+
+def zeroed_outputs(dom: Domain) -> dict:
+    """Outputs as init_history_dyn leaves them before each call (ice_flux.F90:639-673)."""
+    z = lambda: np.zeros((dom.ny + 2, dom.nx + 2))
+    o = {k: z() for k in OUT_FIELDS}
+    o["icetmask"] = np.zeros((dom.ny + 2, dom.nx + 2), dtype=np.int32)
+    return o
+
+
+@dataclass
+class Case:
+    """Everything one evp(dt) call needs, as global-with-ghost arrays."""
+    grid: Grid
+    dt: float
+    ndte: int
+    inp: dict
+    io: dict
+    out: dict
+    scenario: str = "full"
+
+    @property
+    def dom(self) -> Domain:
+        return self.grid.dom
+
+
+def make_case(grid_name: str | Grid, scenario: str = "full", ndte: int = 120,
+              dt: float | None = None, step: int = 0) -> Case:
+    grid = make_grid(grid_name) if isinstance(grid_name, str) else grid_name
+    if dt is None:
+        dt = GRID_DT.get(grid.dom.name, 3600.0)
+    st = ice_state(grid, scenario)
+    inp = dict(st)
+    inp.update(forcing(grid, st, step))
+    return Case(grid=grid, dt=dt, ndte=ndte, inp=inp, io=initial_dynamic_state(grid.dom),
+                out=zeroed_outputs(grid.dom), scenario=scenario)
+
+
+def slab(a: np.ndarray, rank: int, nranks: int) -> np.ndarray:
+    """Column slice (with ghosts) of a global-with-ghost array owned by x-slab `rank`."""
+    nx = a.shape[1] - 2
+    assert nx % nranks == 0
+    nxl = nx // nranks
+    return np.ascontiguousarray(a[:, rank * nxl: rank * nxl + nxl + 2])
+
+
+def unslab(parts: list) -> np.ndarray:
+    """Inverse of :func:`slab`: physical columns from the owner, outer ghosts from the end slabs."""
+    n = len(parts)
+    cols = [p[:, (0 if r == 0 else 1):(p.shape[1] if r == n - 1 else p.shape[1] - 1)]
+            for r, p in enumerate(parts)]
+    return np.ascontiguousarray(np.concatenate(cols, axis=1))

@@ -1,0 +1,111 @@
+/*
+ * evp_oracle.h -- CPU restatement of CICE5's EVP momentum solver (TEST INFRASTRUCTURE).
+ *
+ * This is the parity oracle for the B200 kernels: a plain-C restatement of
+ * `subroutine evp(dt)` and its helpers, written from the reference Fortran
+ * (citations are path:line relative to the reference checkout):
+ *   source/ice_dyn_evp.F90:68-510     evp driver
+ *   source/ice_dyn_evp.F90:520-849    stress
+ *   source/ice_dyn_shared.F90:185-259 set_evp_parameters
+ *   source/ice_dyn_shared.F90:270-365 evp_prep1
+ *   source/ice_dyn_shared.F90:377-614 evp_prep2
+ *   source/ice_dyn_shared.F90:623-748 stepu
+ *   source/ice_dyn_shared.F90:757-844 evp_finish
+ *   source/ice_grid.F90:1799-1958     t2ugrid_vector, to_ugrid, u2tgrid_vector, to_tgrid
+ *   serial/ice_boundary.F90:630-896   ice_HaloUpdate2DR8 (tripole u-fold included)
+ *   serial/ice_boundary.F90:3269-3443 ice_HaloUpdate_stress
+ *   mpi/ice_boundary.F90:2625-2632    ghost-ring pre-fill of the MPI build
+ *
+ * PARITY UNPINNED: the reference ships no tests, golden logs or fixtures for this
+ * path and cannot be compiled in this image (no Fortran compiler), so this
+ * restatement is pinned only by reading the source, by its own invariants
+ * (decomposition independence, seam symmetry, free drift) and by an independent
+ * numpy restatement (oracle/evp_numpy.py).
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl
+ * reference legs may load this code.  The product path never does.
+ *
+ * Array convention: every field is ONE global block with a width-1 ghost ring,
+ * Fortran order (i fastest), dimensions (nx_global+2) x (ny_global+2), i.e.
+ * element (i,j), 1-based, lives at [(j-1)*(nx_global+2) + (i-1)].  Internally
+ * the domain is cut into `nslabs` x-slabs (one reference "block" each) so that
+ * the block/halo structure of the reference is exercised; results are merged
+ * back into the global-with-ghost arrays.
+ */
+#ifndef EVP_ORACLE_H
+#define EVP_ORACLE_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct {
+    int nx_global, ny_global; /* physical cells                                  */
+    int nslabs;               /* number of x-slabs (blocks); divides nx_global   */
+    int ndte;                 /* subcycles (ice_dyn_shared.F90:33)                */
+    int ew_cyclic;            /* ew_boundary_type=='cyclic' (else ghosts = fill)  */
+    int ns_tripole;           /* ns_boundary_type=='tripole' (else ghosts = fill) */
+    int grid_tripole;         /* grid_type=='tripole' (ice_dyn_evp.F90:416)       */
+    int tilt_mode;            /* 0: strtlt from geostrophic current (uncoupled, or
+                                    AusCOM with .not.use_ocnslope);
+                                 1: -gravit*umass*ss_tlt (#ifdef coupled)          */
+    int strength_masked;      /* 1: strength kept only on icetmask==1 cells, 0 elsewhere
+                                    (kstrength=1 list semantics, ice_mechred.F90:2175);
+                                 0: used as given on all physical cells (kstrength=0,
+                                    ice_mechred.F90:2259-2263)                         */
+    int nthreads;             /* OpenMP threads for the ij loops (0 = default)    */
+    double dt_init;           /* dt handed to init_evp -> set_evp_parameters      */
+    double cosw, sinw;        /* ocean turning angle                              */
+    double rhow, rhoi, rhos, gravit;
+    double a_min, m_min;      /* ice_dyn_shared.F90:60-61                         */
+} evp_oracle_cfg;
+
+/* grid arrays, ghosts valid as the reference's init_grid2 leaves them */
+typedef struct {
+    const double *dxt, *dyt, *dxhy, *dyhx, *cxp, *cyp, *cxm, *cym;
+    const double *tarea, *uarea, *tarear, *uarear, *tinyarea, *fcor;
+    const int *tmask, *umask; /* 0/1 */
+} evp_oracle_grid;
+
+typedef struct {
+    /* in (per call) */
+    const double *aice, *vice, *vsno, *aice_init;
+    const double *strairxT, *strairyT, *uocn, *vocn, *ss_tltx, *ss_tlty, *Cw;
+    const double *strength_in; /* host ice_strength result on T cells (>= icetmask cells) */
+    /* inout */
+    double *uvel, *vvel;
+    double *stressp[4], *stressm[4], *stress12[4];
+    int *iceumask;
+    double *fm;
+    /* out */
+    double *strairx, *strairy, *strtltx, *strtlty, *strocnx, *strocny, *strintx, *strinty;
+    double *strocnxT, *strocnyT, *divu, *shear, *rdg_conv, *rdg_shear, *prs_sig;
+    double *uvel_init, *vvel_init, *tmass, *strength;
+    int *icetmask;             /* diagnostic: mask after its halo update */
+} evp_oracle_state;
+
+typedef struct {
+    double loop_seconds;       /* wall time of the ksub loop only              */
+    double total_seconds;      /* wall time of the whole evp call              */
+    long long active_t_cells;  /* sum over blocks of icellt                    */
+    long long active_u_cells;  /* sum over blocks of icellu                    */
+} evp_oracle_stats;
+
+/* One call of evp(dt).  Returns 0 on success. */
+int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
+                   evp_oracle_state *s, double dt, evp_oracle_stats *stats);
+
+/* Stand-alone halo updates on a global-with-ghost array (for fixtures & tests).
+ * loc: 0 = center, 1 = NEcorner.  kind: 0 = scalar, 1 = vector.               */
+int evp_oracle_halo_r8(const evp_oracle_cfg *cfg, double *a, int loc, int kind, double fill);
+int evp_oracle_halo_i4(const evp_oracle_cfg *cfg, int *a, int loc, int kind, int fill);
+
+/* principal_stress, ice_dyn_shared.F90:853-893 (diagnostic, n elements) */
+void evp_oracle_principal_stress(long long n, const double *stressp_1, const double *stressm_1,
+                                 const double *stress12_1, const double *prs_sig,
+                                 double *sig1, double *sig2);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,139 @@
+"""ctypes wrapper around oracle/_build/libevp_oracle.so (TEST INFRASTRUCTURE ONLY).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module (see oracle/evp_oracle.h).  PARITY UNPINNED: no reference golden vectors
+exist for this path and the Fortran reference cannot be compiled in this image.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "_build", "libevp_oracle.so")
+
+_DP = C.POINTER(C.c_double)
+_IP = C.POINTER(C.c_int)
+
+
+class Cfg(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("nx_global", "ny_global", "nslabs", "ndte", "ew_cyclic",
+                                       "ns_tripole", "grid_tripole", "tilt_mode",
+                                       "strength_masked", "nthreads")] + \
+               [(n, C.c_double) for n in ("dt_init", "cosw", "sinw", "rhow", "rhoi", "rhos",
+                                          "gravit", "a_min", "m_min")]
+
+
+_GRID_R8 = ("dxt", "dyt", "dxhy", "dyhx", "cxp", "cyp", "cxm", "cym", "tarea", "uarea",
+            "tarear", "uarear", "tinyarea", "fcor")
+
+
+class GridS(C.Structure):
+    _fields_ = [(n, _DP) for n in _GRID_R8] + [("tmask", _IP), ("umask", _IP)]
+
+
+_STATE_IN = ("aice", "vice", "vsno", "aice_init", "strairxT", "strairyT", "uocn", "vocn",
+             "ss_tltx", "ss_tlty", "Cw", "strength_in")
+_STATE_OUT = ("strairx", "strairy", "strtltx", "strtlty", "strocnx", "strocny", "strintx",
+              "strinty", "strocnxT", "strocnyT", "divu", "shear", "rdg_conv", "rdg_shear",
+              "prs_sig", "uvel_init", "vvel_init", "tmass", "strength")
+
+
+class StateS(C.Structure):
+    _fields_ = [(n, _DP) for n in _STATE_IN] + [("uvel", _DP), ("vvel", _DP),
+               ("stressp", _DP * 4), ("stressm", _DP * 4), ("stress12", _DP * 4),
+               ("iceumask", _IP), ("fm", _DP)] + [(n, _DP) for n in _STATE_OUT] + \
+               [("icetmask", _IP)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("loop_seconds", C.c_double), ("total_seconds", C.c_double),
+                ("active_t_cells", C.c_longlong), ("active_u_cells", C.c_longlong)]
+
+
+def build(force: bool = False) -> str:
+    if force or not os.path.exists(_SO) or \
+            os.path.getmtime(_SO) < os.path.getmtime(os.path.join(_HERE, "evp_oracle.c")):
+        subprocess.run(["make", "-C", _HERE] + (["-B"] if force else []), check=True,
+                       stdout=subprocess.DEVNULL)
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(build())
+        _lib.evp_oracle_run.restype = C.c_int
+        _lib.evp_oracle_halo_r8.restype = C.c_int
+        _lib.evp_oracle_halo_i4.restype = C.c_int
+    return _lib
+
+
+def _dp(a):
+    assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(_DP)
+
+
+def _ip(a):
+    assert a.dtype == np.int32 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(_IP)
+
+
+def make_cfg(dom, ndte, dt_init, nslabs=1, nthreads=0, cosw=1.0, sinw=0.0, tilt_mode=0,
+             strength_masked=0) -> Cfg:
+    from cice5_b200 import fixtures as fx
+    return Cfg(nx_global=dom.nx, ny_global=dom.ny, nslabs=nslabs, ndte=ndte,
+               ew_cyclic=int(dom.ew_cyclic), ns_tripole=int(dom.ns_tripole),
+               grid_tripole=int(dom.grid_tripole), tilt_mode=tilt_mode,
+               strength_masked=strength_masked, nthreads=nthreads, dt_init=dt_init,
+               cosw=cosw, sinw=sinw, rhow=fx.RHOW, rhoi=fx.RHOI, rhos=fx.RHOS,
+               gravit=fx.GRAVIT, a_min=1.0e-3, m_min=1.0e-2)
+
+
+def run_case(case, nslabs=1, nthreads=0, dt_init=None, **cfg_kw):
+    """One evp(dt) call on a fixtures.Case; updates case.io / case.out in place.
+
+    Returns the Stats structure."""
+    dom = case.dom
+    cfg = make_cfg(dom, case.ndte, case.dt if dt_init is None else dt_init, nslabs, nthreads,
+                   **cfg_kw)
+    gf = case.grid.f
+    g = GridS(**{n: _dp(gf[n]) for n in _GRID_R8}, tmask=_ip(gf["tmask"]), umask=_ip(gf["umask"]))
+    inp, io, out = case.inp, case.io, case.out
+    s = StateS()
+    for n in _STATE_IN:
+        setattr(s, n, _dp(inp["strength" if n == "strength_in" else n]))
+    s.uvel, s.vvel, s.fm = _dp(io["uvel"]), _dp(io["vvel"]), _dp(io["fm"])
+    for c in range(4):
+        s.stressp[c] = _dp(io[f"stressp_{c + 1}"])
+        s.stressm[c] = _dp(io[f"stressm_{c + 1}"])
+        s.stress12[c] = _dp(io[f"stress12_{c + 1}"])
+    s.iceumask = _ip(io["iceumask"])
+    for n in _STATE_OUT:
+        setattr(s, n, _dp(out["strength_out" if n == "strength" else n]))
+    s.icetmask = _ip(out["icetmask"])
+    st = Stats()
+    rc = lib().evp_oracle_run(C.byref(cfg), C.byref(g), C.byref(s), C.c_double(case.dt), C.byref(st))
+    if rc != 0:
+        raise RuntimeError(f"evp_oracle_run failed with status {rc}")
+    return st
+
+
+def halo_r8(dom, a, loc, kind, fill=0.0, nslabs=1):
+    cfg = make_cfg(dom, 1, 1.0, nslabs)
+    rc = lib().evp_oracle_halo_r8(C.byref(cfg), _dp(a), loc, kind, C.c_double(fill))
+    assert rc == 0
+    return a
+
+
+def principal_stress(sp1, sm1, s121, prs):
+    sig1, sig2 = np.empty_like(sp1), np.empty_like(sp1)
+    lib().evp_oracle_principal_stress(C.c_longlong(sp1.size), _dp(sp1), _dp(sm1), _dp(s121),
+                                      _dp(prs), _dp(sig1), _dp(sig2))
+    return sig1, sig2
