@@ -1,0 +1,309 @@
+// evp_prep.cuh -- once-per-call kernels around the subcycle loop and the generic width-1 halo.
+//
+// Reference semantics (path:line in the reference checkout):
+//   evp_prep1   source/ice_dyn_shared.F90:270-365      to_ugrid  source/ice_grid.F90:1834-1876
+//   evp_prep2   source/ice_dyn_shared.F90:377-614      to_tgrid  source/ice_grid.F90:1921-1958
+//   evp_finish  source/ice_dyn_shared.F90:757-844
+//   ice_HaloUpdate          serial/ice_boundary.F90:630-896 (+ MPI ring pre-fill mpi/..:2625-2632)
+//   ice_HaloUpdate_stress   serial/ice_boundary.F90:3269-3443
+// None of these is performance critical (a dozen field sweeps against 120 x 49 in the loop).
+#pragma once
+#include "evp_kernels.cuh"
+
+namespace evp {
+
+struct Geom {
+    int nxl, ny, ld, nx_global, lo, nranks, rank;
+    int tripole, ew_cyclic;
+    int inbox_ld;
+};
+
+__device__ __forceinline__ int glob_col(const Geom &g, int c)
+{
+    int ig = g.lo + c;
+    if (ig < 1) ig += g.nx_global;
+    if (ig > g.nx_global) ig -= g.nx_global;
+    return ig;
+}
+
+// ---- generic halo, step 1: my physical edge values go to whoever holds them as ghosts -------
+// E-W: column 1 -> east ghost of the west neighbour, column nxl -> west ghost of the east
+// neighbour (rows 1..ny).  Tripole: rows ny-1, ny of every physical column go to the inbox of
+// the rank(s) whose columns fold onto it.  ioff = 0 for center fields (source nx+1-ig),
+// 1 for NEcorner fields (source nx-ig) (serial/ice_boundary.F90:803-812,874-877).
+struct PushArgs {
+    Geom g;
+    const double *plane;
+    double *planeW, *planeE;          // same plane on the neighbours (self if cyclic on 1 GPU)
+    double *inbox[kMaxRanks];
+    int ioff;
+    int inbox_row0;                   // first of the two inbox rows to use
+};
+
+__global__ void halo_push_kernel(const __grid_constant__ PushArgs a)
+{
+    const Geom &g = a.g;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < g.ny) {
+        const int r = t + 1;
+        if (a.planeW) a.planeW[(size_t)r * g.ld + g.nxl + 1] = a.plane[(size_t)r * g.ld + 1];
+        if (a.planeE) a.planeE[(size_t)r * g.ld] = a.plane[(size_t)r * g.ld + g.nxl];
+    } else if (g.tripole && t < g.ny + g.nxl) {
+        const int c = t - g.ny + 1;
+        const int ig = g.lo + c;
+        int X = g.nx_global + 1 - a.ioff - ig;
+        if (X == 0) X = g.nx_global;
+        const int tr = (X - 1) / g.nxl, ct = X - tr * g.nxl;
+#pragma unroll
+        for (int rs = 0; rs < 2; ++rs) {
+            const double v = a.plane[(size_t)(g.ny - 1 + rs) * g.ld + c];
+            const size_t row = (size_t)(a.inbox_row0 + rs) * g.inbox_ld;
+            a.inbox[tr][row + ct] = v;
+            if (ct == 1) a.inbox[(tr + g.nranks - 1) % g.nranks][row + g.nxl + 1] = v;
+            if (ct == g.nxl) a.inbox[(tr + 1) % g.nranks][row] = v;
+        }
+    }
+}
+
+// ---- generic halo, step 2: ring pre-fill + tripole fold out of the inbox -----------------------
+// loc 0 = center (ghost row only), 1 = NEcorner (top physical row averaged + ghost row).
+// sgn = +1 scalar, -1 vector.
+__global__ void halo_apply_kernel(double *plane, Geom g, const double *inbox, int inbox_row0,
+                                  int loc, double sgn, double fill, int west_closed, int east_closed)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int nxb = g.nxl + 2;
+    if (t < nxb) {
+        const int c = t;
+        plane[c] = fill;                                           // south ghost row
+        if (g.tripole) {
+            const double *in_below = inbox + (size_t)inbox_row0 * g.inbox_ld;
+            const double *in_top = in_below + g.inbox_ld;
+            if (loc == 0)
+                plane[(size_t)(g.ny + 1) * g.ld + c] = sgn * in_top[c];
+            else
+                fold_necorner_column(plane, g.ld, g.ny, c, glob_col(g, c), g.nx_global, in_below,
+                                     in_top, sgn);
+        } else {
+            plane[(size_t)(g.ny + 1) * g.ld + c] = fill;           // open / closed north
+        }
+    } else if (t < nxb + g.ny) {
+        const int r = t - nxb + 1;
+        if (west_closed) plane[(size_t)r * g.ld] = fill;
+        if (east_closed) plane[(size_t)r * g.ld + g.nxl + 1] = fill;
+    }
+}
+
+// ice_HaloUpdate_stress: ghost row of a1 <- mirrored top physical row of a2 (center, +1);
+// the closed south row (and closed E-W ghosts) get 0 (:3351-3353).  Inbox row = inbox_row0+1.
+__global__ void halo_stress_apply_kernel(double *a1, Geom g, const double *inbox, int inbox_row0,
+                                         int west_closed, int east_closed)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int nxb = g.nxl + 2;
+    if (t < nxb) {
+        a1[t] = 0.0;
+        if (g.tripole) a1[(size_t)(g.ny + 1) * g.ld + t] = inbox[(size_t)(inbox_row0 + 1) * g.inbox_ld + t];
+    } else if (t < nxb + g.ny + 2) {
+        const int r = t - nxb;
+        if (west_closed) a1[(size_t)r * g.ld] = 0.0;
+        if (east_closed) a1[(size_t)r * g.ld + g.nxl + 1] = 0.0;
+    }
+}
+
+// ---- evp_prep1 -------------------------------------------------------------------------------
+struct Prep1Args {
+    Geom g;
+    double rhoi, rhos, a_min, m_min;
+    const double *aice, *vice, *vsno, *strairxT, *strairyT;
+    const int *tmask;
+    double *tmass, *work1, *work2, *icetmask;   // work1/2 <- strairxT/yT (for t2ugrid_vector)
+};
+
+__device__ __forceinline__ bool tmphm_at(const Prep1Args &a, size_t q)
+{
+    if (!a.tmask[q]) return false;
+    const double tm = a.rhoi * a.vice[q] + a.rhos * a.vsno[q];
+    return (a.aice[q] > a.a_min) && (tm > a.m_min);
+}
+
+__global__ void prep1_kernel(const __grid_constant__ Prep1Args a)
+{
+    const Geom &g = a.g;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+    if (c > g.nxl + 1) return;
+    const size_t q = (size_t)r * g.ld + c;
+    a.tmass[q] = a.tmask[q] ? (a.rhoi * a.vice[q] + a.rhos * a.vsno[q]) : 0.0;
+    a.work1[q] = a.strairxT[q];
+    a.work2[q] = a.strairyT[q];
+    double m = 0.0;
+    if (c >= 1 && c <= g.nxl && r >= 1 && r <= g.ny) {
+        bool any = false;
+#pragma unroll
+        for (int dr = -1; dr <= 1; ++dr)
+#pragma unroll
+            for (int dc = -1; dc <= 1; ++dc) any |= tmphm_at(a, q + (ptrdiff_t)dr * g.ld + dc);
+        if (any && a.tmask[q]) m = 1.0;
+    }
+    a.icetmask[q] = m;
+}
+
+// ---- to_ugrid x4 -----------------------------------------------------------------------------
+struct ToUArgs {
+    Geom g;
+    const double *tarea, *uarea;
+    const double *in[4];
+    double *out[4];
+};
+
+__global__ void to_ugrid4_kernel(const __grid_constant__ ToUArgs a)
+{
+    const Geom &g = a.g;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+    if (c > g.nxl + 1) return;
+    const size_t q = (size_t)r * g.ld + c;
+    const bool phys = c >= 1 && c <= g.nxl && r >= 1 && r <= g.ny;
+#pragma unroll
+    for (int f = 0; f < 4; ++f) {
+        double w = 0.0;
+        if (phys) {
+            const double *x = a.in[f];
+            w = 0.25 * (x[q] * a.tarea[q] + x[q + 1] * a.tarea[q + 1] + x[q + g.ld] * a.tarea[q + g.ld] +
+                        x[q + g.ld + 1] * a.tarea[q + g.ld + 1]) / a.uarea[q];
+        }
+        a.out[f][q] = w;
+    }
+}
+
+// ---- evp_prep2 (+ ice_strength masking, + the loop's active-cell mask) --------------------------
+struct Prep2Args {
+    Geom g;
+    double dt, a_min, m_min, cosw, sinw, gravit;
+    int tilt_mode, strength_masked;
+    const double *aiu, *umass, *fcor, *uocn, *vocn, *strairx, *strairy, *ss_tltx, *ss_tlty;
+    const double *icetmask, *strength_in;
+    const int *umask;
+    int *iceumask;
+    double *fm, *strtltx, *strtlty, *strocnx, *strocny, *strintx, *strinty;
+    double *umassdti, *waterx, *watery, *forcex, *forcey, *strength;
+    double *sA[12], *sB[12];                    // both ping-pong copies of the stresses
+    double *uA, *vA, *uvel_init, *vvel_init;
+    unsigned char *mask;
+    int ldm;
+    unsigned long long *counts;                 // [0] active T cells, [1] active U cells
+};
+
+__global__ void prep2_kernel(const __grid_constant__ Prep2Args a)
+{
+    const Geom &g = a.g;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+    if (c > g.nxl + 1) return;
+    const size_t q = (size_t)r * g.ld + c;
+    const bool tice = a.icetmask[q] == 1.0;
+    double waterx = 0.0, watery = 0.0, forcex = 0.0, forcey = 0.0, umassdti = 0.0;   // :486-490
+    if (!tice) {                                                                       // :505-517
+#pragma unroll
+        for (int s = 0; s < 12; ++s) { a.sA[s][q] = 0.0; a.sB[s][q] = 0.0; }
+    } else {
+#pragma unroll
+        for (int s = 0; s < 12; ++s) a.sB[s][q] = a.sA[s][q];   // cells the loop never stores
+    }
+    unsigned m = 0;
+    if (tice && c >= 1 && r >= 1) m |= 1u;                                           // :528-537
+    const bool phys = c >= 1 && c <= g.nxl && r >= 1 && r <= g.ny;
+    double st = 0.0;
+    if (phys) {
+        const bool old = a.iceumask[q] != 0;
+        const bool ice = a.umask[q] && (a.aiu[q] > a.a_min) && (a.umass[q] > a.m_min);  // :551
+        a.iceumask[q] = ice ? 1 : 0;
+        double u = a.uA[q], v = a.vA[q];
+        if (ice) {
+            m |= 2u;
+            if (!old) { u = a.uocn[q]; v = a.vocn[q]; }                                // :560-563
+            umassdti = a.umass[q] / a.dt;                                              // :587
+            const double fm = a.fcor[q] * a.umass[q];
+            const double sg = copysign(1.0, fm);
+            a.fm[q] = fm;
+            waterx = a.uocn[q] * a.cosw - a.vocn[q] * a.sinw * sg;
+            watery = a.vocn[q] * a.cosw + a.uocn[q] * a.sinw * sg;
+            double tx, ty;
+            if (a.tilt_mode == 0) { tx = -fm * a.vocn[q]; ty = fm * a.uocn[q]; }
+            else { tx = -a.gravit * a.umass[q] * a.ss_tltx[q]; ty = -a.gravit * a.umass[q] * a.ss_tlty[q]; }
+            a.strtltx[q] = tx; a.strtlty[q] = ty;
+            forcex = a.strairx[q] + tx;
+            forcey = a.strairy[q] + ty;
+        } else {
+            u = 0.0; v = 0.0;                                                          // :566-571
+            a.strintx[q] = 0.0; a.strinty[q] = 0.0; a.strocnx[q] = 0.0; a.strocny[q] = 0.0;
+        }
+        a.uA[q] = u; a.vA[q] = v;
+        a.uvel_init[q] = u; a.vvel_init[q] = v;                                       // :574-575
+        st = (!a.strength_masked || tice) ? a.strength_in[q] : 0.0;
+    }
+    a.strength[q] = st;
+    a.waterx[q] = waterx; a.watery[q] = watery; a.forcex[q] = forcex; a.forcey[q] = forcey;
+    a.umassdti[q] = umassdti;
+    a.mask[(size_t)r * a.ldm + c] = (unsigned char)m;
+    // active-cell counts (metric denominator); one atomic per warp
+    const unsigned bt = __ballot_sync(__activemask(), m & 1u), bu = __ballot_sync(__activemask(), m & 2u);
+    if ((threadIdx.x & 31) == 0) {
+        if (bt) atomicAdd(&a.counts[0], (unsigned long long)__popc(bt));
+        if (bu) atomicAdd(&a.counts[1], (unsigned long long)__popc(bu));
+    }
+}
+
+// the T mask bit of the ghost cells depends on icetmask AFTER its halo update, which prep2 sees;
+// but strength's ghost values come from its own halo: nothing else to do here.
+
+// ---- evp_finish ------------------------------------------------------------------------------
+struct FinishArgs {
+    Geom g;
+    double rhow, cosw, sinw;
+    const double *u, *v, *uocn, *vocn, *aiu, *fm, *Cw;
+    const int *iceumask;
+    double *strocnx, *strocny, *work1, *work2;      // work1/2 <- strocnxT/yT on the U grid
+};
+
+__global__ void finish_kernel(const __grid_constant__ FinishArgs a)
+{
+    const Geom &g = a.g;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+    if (c > g.nxl + 1) return;
+    const size_t q = (size_t)r * g.ld + c;
+    double tx = 0.0, ty = 0.0;                                                         // :806-811
+    if (c >= 1 && c <= g.nxl && r >= 1 && r <= g.ny && a.iceumask[q]) {
+        const double du = a.uocn[q] - a.u[q], dv = a.vocn[q] - a.v[q];
+        double vrel = a.rhow * a.Cw[q] * sqrt(du * du + dv * dv);                      // :818
+        vrel = vrel * a.aiu[q];                                                        // :827
+        const double sg = copysign(1.0, a.fm[q]);
+        const double sx = vrel * (du * a.cosw - dv * a.sinw * sg);
+        const double sy = vrel * (dv * a.cosw + du * a.sinw * sg);
+        a.strocnx[q] = sx; a.strocny[q] = sy;
+        tx = sx / a.aiu[q]; ty = sy / a.aiu[q];                                        // :840-841
+    }
+    a.work1[q] = tx; a.work2[q] = ty;
+}
+
+// to_tgrid x2: out = 0 outside the physical cells (evp_finish zero-fill, :806-811)
+__global__ void to_tgrid2_kernel(Geom g, const double *tarea, const double *uarea, const double *in0,
+                                 const double *in1, double *out0, double *out1)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+    if (c > g.nxl + 1) return;
+    const size_t q = (size_t)r * g.ld + c;
+    double w0 = 0.0, w1 = 0.0;
+    if (c >= 1 && c <= g.nxl && r >= 1 && r <= g.ny) {
+        const size_t w = q - 1, s = q - g.ld, sw = q - g.ld - 1;
+        w0 = 0.25 * (in0[q] * uarea[q] + in0[w] * uarea[w] + in0[s] * uarea[s] + in0[sw] * uarea[sw]) / tarea[q];
+        w1 = 0.25 * (in1[q] * uarea[q] + in1[w] * uarea[w] + in1[s] * uarea[s] + in1[sw] * uarea[sw]) / tarea[q];
+    }
+    out0[q] = w0; out1[q] = w1;
+}
+
+__global__ void double_to_int_kernel(const double *in, int *out, size_t n)
+{
+    const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q < n) out[q] = (int)in[q];
+}
+
+}  // namespace evp

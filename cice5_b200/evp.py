@@ -1,0 +1,247 @@
+"""Host-side mirror of the reference interface for the EVP path, over the C ABI (ctypes).
+
+The reference's entry point is ``call evp(dt)`` in ``module ice_dyn_evp``
+(``source/ice_dyn_evp.F90:68``) operating on module arrays; :class:`EvpGpu` holds the same
+arrays by their reference names (``uvel``, ``stressp_1`` ...) and :meth:`EvpGpu.evp` is that
+call.  Everything numeric happens in ``lib/libevp_b200.so`` (CUDA, sm_100a); if the library or a
+GPU is missing this module raises -- there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+_DP = C.POINTER(C.c_double)
+_IP = C.POINTER(C.c_int)
+
+
+class EvpError(RuntimeError):
+    pass
+
+
+class Config(C.Structure):
+    _fields_ = [(n, C.c_int) for n in (
+        "nx_global", "ny_global", "nx_block", "ny_block", "rank", "nranks", "device", "ndte",
+        "kdyn", "revised_evp", "ew_boundary", "ns_boundary", "grid_tripole", "tilt_mode",
+        "strength_masked", "use_cuda_graph")] + [(n, C.c_double) for n in (
+        "dt_init", "cosw", "sinw", "rhow", "rhoi", "rhos", "gravit", "a_min", "m_min")]
+
+
+GRID_R8 = ("dxt", "dyt", "dxhy", "dyhx", "cxp", "cyp", "cxm", "cym", "tarea", "uarea", "tarear",
+           "uarear", "tinyarea", "fcor")
+IN_R8 = ("aice", "vice", "vsno", "aice_init", "strairxT", "strairyT", "uocn", "vocn", "ss_tltx",
+         "ss_tlty", "Cdn_ocn", "strength")
+OUT_R8 = ("strairx", "strairy", "strtltx", "strtlty", "strocnx", "strocny", "strintx", "strinty",
+          "strocnxT", "strocnyT", "divu", "shear", "rdg_conv", "rdg_shear", "prs_sig",
+          "uvel_init", "vvel_init", "tmass", "strength")
+
+
+class GridS(C.Structure):
+    _fields_ = [(n, _DP) for n in GRID_R8] + [("tmask", _IP), ("umask", _IP)]
+
+
+class InS(C.Structure):
+    _fields_ = [(n, _DP) for n in IN_R8]
+
+
+class InOutS(C.Structure):
+    _fields_ = [("uvel", _DP), ("vvel", _DP), ("stressp", _DP * 4), ("stressm", _DP * 4),
+                ("stress12", _DP * 4), ("iceumask", _IP), ("fm", _DP)]
+
+
+class OutS(C.Structure):
+    _fields_ = [(n, _DP) for n in OUT_R8] + [("icetmask", _IP)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("prep_ms", C.c_double), ("loop_ms", C.c_double), ("finish_ms", C.c_double),
+                ("total_ms", C.c_double), ("active_t_cells", C.c_longlong),
+                ("active_u_cells", C.c_longlong), ("kernel_launches", C.c_longlong),
+                ("loop_kernel_launches", C.c_longlong)]
+
+
+EXPORTS = ("evp_gpu_init", "evp_gpu_set_grid", "evp_gpu_run", "evp_gpu_upload", "evp_gpu_compute",
+           "evp_gpu_download", "evp_gpu_get_stats", "evp_gpu_synchronize", "evp_gpu_peer_blob_size",
+           "evp_gpu_get_peer_blob", "evp_gpu_set_peers", "evp_gpu_finalize", "evp_gpu_strerror",
+           "evp_gpu_last_cuda_error", "evp_gpu_device_count")
+
+_libs: dict = {}
+
+
+def load_library(strict: bool = False):
+    """dlopen the in-tree CUDA library (building it if nvcc is here and it is stale)."""
+    if strict in _libs:
+        return _libs[strict]
+    path = _build.lib_path(strict)
+    try:
+        _build.build()
+    except Exception:
+        if not os.path.exists(path):
+            raise
+    if not os.path.exists(path):
+        raise EvpError(f"CUDA extension {path} is missing: build it with `python -m cice5_b200.build`")
+    lib = C.CDLL(path)
+    lib.evp_gpu_strerror.restype = C.c_char_p
+    lib.evp_gpu_last_cuda_error.restype = C.c_char_p
+    for n in EXPORTS:
+        getattr(lib, n)
+    _libs[strict] = lib
+    return lib
+
+
+def _dp(a):
+    if a is None:
+        return None
+    if a.dtype != np.float64 or not a.flags["C_CONTIGUOUS"]:
+        raise EvpError("arrays must be C-contiguous float64 with shape (ny_block, nx_block)")
+    return a.ctypes.data_as(_DP)
+
+
+def _ip(a):
+    if a is None:
+        return None
+    if a.dtype != np.int32 or not a.flags["C_CONTIGUOUS"]:
+        raise EvpError("mask arrays must be C-contiguous int32")
+    return a.ctypes.data_as(_IP)
+
+
+class EvpGpu:
+    """One task's EVP solver on one GPU (one block, x-slab ``rank`` of ``nranks``)."""
+
+    def __init__(self, nx_global, ny_global, ndte, dt_init, *, rank=0, nranks=1, device=0,
+                 ew_cyclic=True, ns_boundary="open", grid_tripole=False, tilt_mode=0,
+                 strength_masked=0, cosw=1.0, sinw=0.0, rhow=1026.0, rhoi=917.0, rhos=330.0,
+                 gravit=9.80616, a_min=1.0e-3, m_min=1.0e-2, kdyn=1, revised_evp=False,
+                 use_cuda_graph=False, strict=False):
+        self.lib = load_library(strict)
+        ns = {"open": 0, "closed": 1, "tripole": 2}[ns_boundary]
+        if nx_global % nranks:
+            raise EvpError("nranks must divide nx_global")
+        self.nxl = nx_global // nranks
+        self.shape = (ny_global + 2, self.nxl + 2)
+        self.cfg = Config(nx_global=nx_global, ny_global=ny_global, nx_block=self.nxl + 2,
+                          ny_block=ny_global + 2, rank=rank, nranks=nranks, device=device,
+                          ndte=ndte, kdyn=kdyn, revised_evp=int(revised_evp),
+                          ew_boundary=int(ew_cyclic), ns_boundary=ns,
+                          grid_tripole=int(grid_tripole), tilt_mode=tilt_mode,
+                          strength_masked=strength_masked, use_cuda_graph=int(use_cuda_graph),
+                          dt_init=dt_init, cosw=cosw, sinw=sinw, rhow=rhow, rhoi=rhoi, rhos=rhos,
+                          gravit=gravit, a_min=a_min, m_min=m_min)
+        self._h = C.c_void_p()
+        self._check(self.lib.evp_gpu_init(C.byref(self.cfg), C.byref(self._h)))
+        self._keep = []
+
+    # -- error behaviour of the reference: abort_ice(message); here: raise with the same text
+    def _check(self, rc):
+        if rc != 0:
+            msg = self.lib.evp_gpu_strerror(rc).decode()
+            if rc == 3:
+                msg += " [" + self.lib.evp_gpu_last_cuda_error().decode() + "]"
+            raise EvpError(msg)
+
+    @classmethod
+    def for_domain(cls, dom, ndte, dt_init, **kw):
+        ns = "tripole" if dom.ns_tripole else ("open" if dom.ns_open else "closed")
+        return cls(dom.nx, dom.ny, ndte, dt_init, ew_cyclic=dom.ew_cyclic, ns_boundary=ns,
+                   grid_tripole=dom.grid_tripole, **kw)
+
+    def set_grid(self, f: dict):
+        for n in GRID_R8 + ("tmask", "umask"):
+            if f[n].shape != self.shape:
+                raise EvpError(f"grid array {n} has shape {f[n].shape}, expected {self.shape}")
+        g = GridS(**{n: _dp(f[n]) for n in GRID_R8}, tmask=_ip(f["tmask"]), umask=_ip(f["umask"]))
+        self._check(self.lib.evp_gpu_set_grid(self._h, C.byref(g)))
+
+    @staticmethod
+    def _in_struct(inp):
+        s = InS()
+        for n in IN_R8:
+            key = "Cw" if n == "Cdn_ocn" and "Cdn_ocn" not in inp else n
+            setattr(s, n, _dp(inp[key]))
+        return s
+
+    @staticmethod
+    def _io_struct(io):
+        s = InOutS()
+        s.uvel, s.vvel, s.fm = _dp(io["uvel"]), _dp(io["vvel"]), _dp(io["fm"])
+        for c in range(4):
+            s.stressp[c] = _dp(io[f"stressp_{c + 1}"])
+            s.stressm[c] = _dp(io[f"stressm_{c + 1}"])
+            s.stress12[c] = _dp(io[f"stress12_{c + 1}"])
+        s.iceumask = _ip(io["iceumask"])
+        return s
+
+    @staticmethod
+    def _out_struct(out):
+        s = OutS()
+        for n in OUT_R8:
+            key = "strength_out" if n == "strength" else n
+            if out.get(key) is not None:
+                setattr(s, n, _dp(out[key]))
+        if out.get("icetmask") is not None:
+            s.icetmask = _ip(out["icetmask"])
+        return s
+
+    def evp(self, dt, inp, io, out):
+        """``call evp(dt)``: host arrays in, host arrays out (H2D + device solve + D2H)."""
+        i, s, o = self._in_struct(inp), self._io_struct(io), self._out_struct(out)
+        self._check(self.lib.evp_gpu_run(self._h, C.c_double(dt), C.byref(i), C.byref(s), C.byref(o)))
+
+    def upload(self, inp, io):
+        i, s = self._in_struct(inp), self._io_struct(io)
+        self._check(self.lib.evp_gpu_upload(self._h, C.byref(i), C.byref(s)))
+
+    def compute(self, dt):
+        self._check(self.lib.evp_gpu_compute(self._h, C.c_double(dt)))
+
+    def download(self, io, out):
+        s, o = self._io_struct(io), self._out_struct(out)
+        self._check(self.lib.evp_gpu_download(self._h, C.byref(s), C.byref(o)))
+
+    def stats(self) -> Stats:
+        st = Stats()
+        self._check(self.lib.evp_gpu_get_stats(self._h, C.byref(st)))
+        return st
+
+    def synchronize(self):
+        self._check(self.lib.evp_gpu_synchronize(self._h))
+
+    def peer_blob(self) -> bytes:
+        n = self.lib.evp_gpu_peer_blob_size()
+        buf = C.create_string_buffer(n)
+        self._check(self.lib.evp_gpu_get_peer_blob(self._h, buf))
+        return buf.raw
+
+    def set_peers(self, blobs: list):
+        raw = b"".join(blobs)
+        self._check(self.lib.evp_gpu_set_peers(self._h, raw))
+
+    def close(self):
+        if self._h:
+            self.lib.evp_gpu_finalize(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def device_count() -> int:
+    return load_library().evp_gpu_device_count()
+
+
+def run_case(case, strict=False, **kw):
+    """One evp(dt) call on a fixtures.Case through the C ABI (single GPU). Returns Stats."""
+    e = EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=strict, **kw)
+    try:
+        e.set_grid(case.grid.f)
+        e.evp(case.dt, case.inp, case.io, case.out)
+        return e.stats()
+    finally:
+        e.close()

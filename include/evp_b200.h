@@ -1,0 +1,133 @@
+/*
+ * evp_b200.h -- C ABI of the B200-native EVP momentum solver (drop-in for CICE5 `evp(dt)`).
+ *
+ * The reference has no FFI or plugin API for this path: the boundary is the Fortran module
+ * procedure `ice_dyn_evp::evp(dt)` (source/ice_dyn_evp.F90:47,68), called from
+ * `step_dynamics` (source/ice_step_mod.F90:1119), which exchanges all of its data through
+ * `use`-associated module arrays (source/ice_dyn_evp.F90:70-92).  The entry points below are
+ * what a replacement `module ice_dyn_evp` binds with `iso_c_binding`
+ * (cice5_b200/fortran/ice_dyn_evp_gpu.F90).
+ *
+ * Array convention (identical to the reference): every field is the calling task's block,
+ * Fortran order, `real(dbl_kind)` / `integer(int_kind)`, dimensions (nx_block, ny_block)
+ * with a width-1 ghost ring (nghost = 1, source/ice_blocks.F90:42-47); one block per task
+ * (max_blocks = 1).  Logical masks are passed as int32 0/1.  Pointers are borrowed for the
+ * duration of the call; the handle owns all device memory.  Every function returns 0 on
+ * success and a non-zero status otherwise (text via evp_gpu_strerror; the Fortran shim hands
+ * it to abort_ice, mpi/ice_exit.F90).  One handle per task, one task per GPU; calls are not
+ * re-entrant (neither is the reference's caller).
+ */
+#ifndef EVP_B200_H
+#define EVP_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct evp_handle evp_handle_t;
+
+enum {
+    EVP_OK = 0,
+    EVP_ERR_ARG = 1,          /* null pointer / inconsistent sizes                      */
+    EVP_ERR_UNSUPPORTED = 2,  /* kdyn != 1, revised_evp, unsupported boundary type      */
+    EVP_ERR_CUDA = 3,         /* a CUDA runtime call failed (see evp_gpu_last_cuda_error) */
+    EVP_ERR_STATE = 4,        /* call order violated (e.g. run before set_grid)         */
+    EVP_ERR_NO_DEVICE = 5,    /* no usable CUDA device: there is NO CPU fallback        */
+    EVP_ERR_PEER = 6          /* multi-GPU peer mapping failed                          */
+};
+
+enum { EVP_EW_CLOSED = 0, EVP_EW_CYCLIC = 1 };
+enum { EVP_NS_OPEN = 0, EVP_NS_CLOSED = 1, EVP_NS_TRIPOLE = 2 };
+
+/* Frozen at init (namelist + CPP switches of the reference build). */
+typedef struct {
+    int nx_global, ny_global;   /* ice_domain_size.F90:24-25                                  */
+    int nx_block, ny_block;     /* block incl. ghosts: nx_global/nranks + 2, ny_global + 2     */
+    int rank, nranks;           /* x-slab index / count (slenderX1-style decomposition)        */
+    int device;                 /* CUDA device ordinal for this task                           */
+    int ndte;                   /* dynamics_nml ndte (ice_dyn_shared.F90:33)                   */
+    int kdyn;                   /* must be 1 (EVP)                                             */
+    int revised_evp;            /* must be 0 (classic EVP, ice_dyn_shared.F90:239-242)          */
+    int ew_boundary;            /* EVP_EW_*   (ice_domain.F90 ew_boundary_type)                 */
+    int ns_boundary;            /* EVP_NS_*   (ns_boundary_type; tripole = u-fold)              */
+    int grid_tripole;           /* grid_type == 'tripole' (ice_dyn_evp.F90:416)                 */
+    int tilt_mode;              /* 0: strtlt = -+fm*ocn (uncoupled / AusCOM .not.use_ocnslope,
+                                      ice_dyn_shared.F90:598-599,605-608);
+                                   1: -gravit*umass*ss_tlt (#ifdef coupled, :601-602)           */
+    int strength_masked;        /* 1: keep strength only where icetmask==1 (kstrength=1 list
+                                      semantics); 0: as given on physical cells (kstrength=0)   */
+    int use_cuda_graph;         /* capture the ndte loop in a CUDA graph                        */
+    double dt_init;             /* dt given to init_evp -> set_evp_parameters (:185-259)        */
+    double cosw, sinw;          /* ocean turning angle (namelist under AusCOM)                  */
+    double rhow, rhoi, rhos, gravit;
+    double a_min, m_min;        /* ice_dyn_shared.F90:60-61                                     */
+} evp_config_t;
+
+/* Grid arrays (source/ice_grid.F90:48-77,112-115; fcor_blk ice_dyn_shared.F90:83-84),
+ * copied to the device once. */
+typedef struct {
+    const double *dxt, *dyt, *dxhy, *dyhx, *cxp, *cyp, *cxm, *cym;
+    const double *tarea, *uarea, *tarear, *uarear, *tinyarea, *fcor;
+    const int *tmask, *umask;
+} evp_grid_t;
+
+/* Per-call inputs (ice_state.F90:54-56,155; ice_flux.F90:37-48; ice_atmo.F90:40). */
+typedef struct {
+    const double *aice, *vice, *vsno, *aice_init;
+    const double *strairxT, *strairyT, *uocn, *vocn, *ss_tltx, *ss_tlty;
+    const double *Cdn_ocn;
+    const double *strength;     /* host ice_strength result on the block's physical T cells */
+} evp_in_t;
+
+/* Persistent dynamic state, read and written (ice_state.F90:143-144; ice_flux.F90:95-107). */
+typedef struct {
+    double *uvel, *vvel;
+    double *stressp[4], *stressm[4], *stress12[4];   /* _1.._4 */
+    int *iceumask;
+    double *fm;
+} evp_inout_t;
+
+/* Outputs; any pointer may be NULL to skip its download. */
+typedef struct {
+    double *strairx, *strairy, *strtltx, *strtlty, *strocnx, *strocny, *strintx, *strinty;
+    double *strocnxT, *strocnyT, *divu, *shear, *rdg_conv, *rdg_shear, *prs_sig;
+    double *uvel_init, *vvel_init, *tmass, *strength;
+    int *icetmask;
+} evp_out_t;
+
+typedef struct {
+    double prep_ms, loop_ms, finish_ms, total_ms;   /* device times of the last evp_gpu_compute */
+    long long active_t_cells, active_u_cells;       /* icellt / icellu of this block            */
+    long long kernel_launches;                      /* kernels launched by the last compute     */
+    long long loop_kernel_launches;                 /* ... of which inside the ndte loop        */
+} evp_stats_t;
+
+int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **h);
+int evp_gpu_set_grid(evp_handle_t *h, const evp_grid_t *g);
+
+/* == one call of evp(dt): upload + compute + download */
+int evp_gpu_run(evp_handle_t *h, double dt, const evp_in_t *in, evp_inout_t *io, evp_out_t *out);
+
+/* The same in three stages (device-resident benchmarking; "next" row: resident state). */
+int evp_gpu_upload(evp_handle_t *h, const evp_in_t *in, const evp_inout_t *io);
+int evp_gpu_compute(evp_handle_t *h, double dt);
+int evp_gpu_download(evp_handle_t *h, evp_inout_t *io, evp_out_t *out);
+
+int evp_gpu_get_stats(evp_handle_t *h, evp_stats_t *st);
+int evp_gpu_synchronize(evp_handle_t *h);
+
+/* Multi-GPU (one task per GPU): every task exports a blob, the host gathers the blobs of all
+ * tasks in rank order (MPI_Allgather in the shim) and hands them back. */
+int evp_gpu_peer_blob_size(void);
+int evp_gpu_get_peer_blob(evp_handle_t *h, void *blob);
+int evp_gpu_set_peers(evp_handle_t *h, const void *blobs_all_ranks);
+
+int evp_gpu_finalize(evp_handle_t *h);
+const char *evp_gpu_strerror(int status);
+const char *evp_gpu_last_cuda_error(void);
+int evp_gpu_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
