@@ -507,25 +507,29 @@ int evp_gpu_compute(evp_handle_t *h, double dt)
         a.strintx = h->plane(O_STRINTX); a.strinty = h->plane(O_STRINTY);
         a.umassdti = h->plane(W_UMASSDTI); a.waterx = h->plane(W_WATERX); a.watery = h->plane(W_WATERY);
         a.forcex = h->plane(W_FORCEX); a.forcey = h->plane(W_FORCEY); a.strength = h->plane(W_STRENGTH);
-        for (int q = 0; q < 12; ++q) { a.sA[q] = h->plane(S_STRA + q); a.sB[q] = h->plane(S_STRB + q); }
-        a.uA = h->plane(S_UA); a.vA = h->plane(S_VA);
+        const int cur = h->parity;
+        for (int q = 0; q < 12; ++q) {
+            a.sA[q] = h->plane((cur ? S_STRB : S_STRA) + q);
+            a.sB[q] = h->plane((cur ? S_STRA : S_STRB) + q);
+        }
+        a.uA = h->plane(cur ? S_UB : S_UA); a.vA = h->plane(cur ? S_VB : S_VA);
         a.uvel_init = h->plane(O_UVELINIT); a.vvel_init = h->plane(O_VVELINIT);
         a.mask = h->mask(); a.ldm = h->ldm; a.counts = h->counts();
         prep2_kernel<<<grid2d(h), 128, 0, s>>>(a);
         ++L.n;
     }
     TRY(do_halo(L, W_STRENGTH, 0, +1.0, 0.0));                 // :311
-    TRY(do_halo(L, S_UA, 1, -1.0, 0.0));                       // :314 (fld2)
-    TRY(do_halo(L, S_VA, 1, -1.0, 0.0));
-    // the B copies must carry the same ghost ring where the loop never writes (south row, closed
-    // E-W edges, open north row): start them as a copy of A
-    CK(cudaMemcpyAsync(h->plane(S_UB), h->plane(S_UA), pb * 2, cudaMemcpyDeviceToDevice, s));
+    TRY(do_halo(L, h->parity ? S_UB : S_UA, 1, -1.0, 0.0));    // :314 (fld2)
+    TRY(do_halo(L, h->parity ? S_VB : S_VA, 1, -1.0, 0.0));
+    // the other copy must carry the same ghost ring where the loop never writes (south row,
+    // closed E-W edges, open north row): start it as a copy of the current one
+    CK(cudaMemcpyAsync(h->plane(h->parity ? S_UA : S_UB), h->plane(h->parity ? S_UB : S_UA), pb * 2,
+                       cudaMemcpyDeviceToDevice, s));
     CK(cudaGetLastError());
 
     // ---- subcycling (:336-410) ----
     CK(cudaEventRecord(h->ev[1], s));
     const long long n_before_loop = L.n;
-    h->parity = 0;
     for (int ksub = 1; ksub <= cfg.ndte; ++ksub) {
         TRY(launch_subcycle(L, h->parity, ksub == cfg.ndte));
         h->parity ^= 1;

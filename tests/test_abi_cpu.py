@@ -1,0 +1,73 @@
+"""The C-ABI library loads and exports every symbol include/evp_b200.h declares; without a GPU
+it must fail loudly (no CPU fallback).  No compute calls here."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+from cice5_b200 import build, evp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_functions():
+    txt = open(os.path.join(ROOT, "include", "evp_b200.h")).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(evp_gpu_\w+)\s*\(", txt)))
+
+
+@pytest.mark.parametrize("strict", [False, True])
+def test_library_exports_every_declared_symbol(strict):
+    names = _declared_functions()
+    assert len(names) >= 15
+    lib = evp.load_library(strict)
+    for n in names:
+        assert hasattr(lib, n), n
+    assert set(names) == set(evp.EXPORTS)
+
+
+def test_strerror_and_status_codes():
+    lib = evp.load_library()
+    assert lib.evp_gpu_strerror(0) == b"ok"
+    for rc in range(1, 7):
+        assert lib.evp_gpu_strerror(rc).startswith(b"evp_gpu:")
+
+
+def test_config_struct_matches_header():
+    txt = open(os.path.join(ROOT, "include", "evp_b200.h")).read()
+    body = re.search(r"typedef struct \{(.*?)\} evp_config_t;", txt, flags=re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    fields = []
+    for decl in body.split(";"):
+        decl = decl.strip()
+        if not decl:
+            continue
+        typ, rest = decl.split(None, 1)
+        fields += [(n.strip(), typ) for n in rest.split(",")]
+    got = [(n, "int" if t is C.c_int else "double") for n, t in evp.Config._fields_]
+    assert got == fields
+
+
+def test_no_gpu_means_loud_failure(have_gpu):
+    if have_gpu:
+        pytest.skip("a GPU is present")
+    with pytest.raises(evp.EvpError, match="no usable CUDA device|no CPU fallback"):
+        evp.EvpGpu(100, 116, 120, 3600.0)
+
+
+def test_argument_validation_precedes_device_probe():
+    with pytest.raises(evp.EvpError, match="unsupported"):
+        evp.EvpGpu(100, 116, 120, 3600.0, kdyn=2)
+    with pytest.raises(evp.EvpError, match="unsupported"):
+        evp.EvpGpu(100, 116, 120, 3600.0, revised_evp=True)
+    with pytest.raises(evp.EvpError):
+        evp.EvpGpu(100, 116, 120, 3600.0, nranks=3)      # 3 does not divide 100
+
+
+def test_product_path_never_imports_oracle():
+    import sys
+    for mod in ("cice5_b200.evp", "cice5_b200.fixtures", "cice5_b200.build"):
+        src = open(sys.modules[mod].__file__ if mod in sys.modules else
+                   os.path.join(ROOT, *mod.split(".")) + ".py").read()
+        assert "import oracle" not in src and "from oracle" not in src

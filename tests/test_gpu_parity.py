@@ -1,0 +1,129 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle -- the tests proper.
+
+Bar (BASELINE.json north_star): uvel/vvel and the 12 stresses after a full evp call (ndte=120)
+within 1e-10 relative; the `-fmad=false` build of the same kernels must be BITWISE equal to the
+oracle (both then evaluate the same IEEE operations in the same order)."""
+import numpy as np
+import pytest
+
+from cice5_b200 import evp, fixtures as fx
+from tests.util import STATE, REL_TOL, clone_case, compare_cases, phys
+
+pytestmark = pytest.mark.gpu
+
+OUT_CHECK = ("strairx", "strairy", "strtltx", "strtlty", "strocnx", "strocny", "strintx",
+             "strinty", "strocnxT", "strocnyT", "divu", "shear", "rdg_conv", "rdg_shear",
+             "prs_sig", "uvel_init", "vvel_init", "tmass", "strength_out", "icetmask")
+
+
+def _oracle(case, **kw):
+    from oracle import oracle as orc
+    ref = clone_case(case)
+    orc.run_case(ref, **kw)
+    return ref
+
+
+def _small_tripole(nx, ny):
+    return fx.synthetic_tripole(nx, ny, f"tp_{nx}x{ny}")
+
+
+@pytest.mark.parametrize("grid,scenario", [("gx3", "full"), ("gx3", "caps"), ("gx1", "full"),
+                                           ("tp1", "full"), ("tp1", "caps")])
+def test_one_call_bitwise_strict(grid, scenario):
+    case = fx.make_case(grid, scenario, ndte=120)
+    ref = _oracle(case)
+    got = clone_case(case)
+    st = evp.run_case(got, strict=True)
+    assert st.active_t_cells > 0 and st.loop_kernel_launches >= 120
+    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+    assert np.array_equal(phys(got.io["iceumask"]), phys(ref.io["iceumask"]))
+
+
+@pytest.mark.parametrize("grid,scenario", [("gx3", "full"), ("gx1", "full"), ("tp1", "full"),
+                                           ("tp1", "caps")])
+def test_one_call_fast_build_1e10(grid, scenario):
+    case = fx.make_case(grid, scenario, ndte=120)
+    ref = _oracle(case)
+    got = clone_case(case)
+    evp.run_case(got, strict=False)
+    rep = compare_cases(got, ref, fields_io=STATE, fields_out=OUT_CHECK[:-1], tol=REL_TOL)
+    assert max(v[0] for v in rep.values()) <= REL_TOL
+
+
+@pytest.mark.parametrize("nx,ny", [(62, 40), (64, 33), (30, 9), (94, 65), (200, 70)])
+def test_ragged_tripole_sizes_bitwise(nx, ny):
+    """Strip (31 columns) and row-chunk edges at awkward sizes, with the fold."""
+    case = fx.make_case(_small_tripole(nx, ny), "full", ndte=12, dt=3600.0)
+    ref = _oracle(case)
+    got = clone_case(case)
+    evp.run_case(got, strict=True)
+    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+
+
+def test_multi_call_state_carry_bitwise():
+    """Six consecutive calls with moving forcing; stresses, velocity and iceumask carried."""
+    grid = fx.make_grid("tp1")
+    case = fx.make_case(grid, "caps", ndte=120)
+    ref = clone_case(case)
+    got = clone_case(case)
+    from oracle import oracle as orc
+    e = evp.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True)
+    try:
+        e.set_grid(grid.f)
+        for step in range(6):
+            f = fx.forcing(grid, case.inp, step)
+            for c in (ref, got):
+                c.inp.update({k: v.copy() for k, v in f.items()})
+                c.out = fx.zeroed_outputs(case.dom)
+            orc.run_case(ref)
+            e.evp(case.dt, got.inp, got.io, got.out)
+            compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+    finally:
+        e.close()
+
+
+def test_odd_ndte_and_resident_recompute():
+    """ndte odd leaves the state in the second ping-pong copy; a second device-resident
+    compute() must continue from it (== two oracle calls)."""
+    grid = _small_tripole(94, 65)
+    case = fx.make_case(grid, "full", ndte=7, dt=3600.0)
+    ref = clone_case(case)
+    from oracle import oracle as orc
+    orc.run_case(ref)
+    ref.out = fx.zeroed_outputs(case.dom)
+    orc.run_case(ref)
+    got = clone_case(case)
+    e = evp.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True)
+    try:
+        e.set_grid(grid.f)
+        e.upload(got.inp, got.io)
+        e.compute(case.dt)
+        e.compute(case.dt)
+        e.download(got.io, got.out)
+    finally:
+        e.close()
+    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+
+
+def test_tilt_and_turning_angle_options():
+    """coupled tilt (ss_tlt) and a non-zero ocean turning angle (AusCOM cosw/sinw namelist)."""
+    grid = fx.make_grid("gx3")
+    case = fx.make_case(grid, "full", ndte=30)
+    rng = np.random.default_rng(7)
+    case.inp["ss_tltx"] = fx._with_ghosts(case.dom, 1e-6 * rng.standard_normal((case.dom.ny, case.dom.nx)))
+    case.inp["ss_tlty"] = fx._with_ghosts(case.dom, 1e-6 * rng.standard_normal((case.dom.ny, case.dom.nx)))
+    kw = dict(cosw=np.cos(np.deg2rad(25.0)), sinw=np.sin(np.deg2rad(25.0)), tilt_mode=1,
+              strength_masked=1)
+    ref = _oracle(case, **kw)
+    got = clone_case(case)
+    evp.run_case(got, strict=True, **kw)
+    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+
+
+def test_rejects_unsupported_configs():
+    with pytest.raises(evp.EvpError):
+        evp.EvpGpu(100, 116, 120, 3600.0, kdyn=2)
+    with pytest.raises(evp.EvpError):
+        evp.EvpGpu(100, 116, 120, 3600.0, revised_evp=True)
+    with pytest.raises(evp.EvpError):
+        evp.EvpGpu(100, 116, 120, 3600.0, device=99)
