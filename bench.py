@@ -44,6 +44,8 @@ def parse():
     ap.add_argument("--ndte", type=int, default=120)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch the ndte loop kernel by kernel")
+    ap.add_argument("--fma", action="store_true", help="use the FMA-contracted comparison build")
     ap.add_argument("--cpu-ndte", type=int, default=24, help="subcycles of the CPU sample")
     return ap.parse_args()
 
@@ -208,7 +210,8 @@ def main():
     gridf = {k: sl(grid.f[k]) for k in evp.GRID_R8 + ("tmask", "umask")}
     inp, io, out = pin(case.inp), pin(case.io), pin(case.out)
 
-    e = evp.EvpGpu.for_domain(dom, args.ndte, dt, rank=rank, nranks=N, device=local_rank)
+    e = evp.EvpGpu.for_domain(dom, args.ndte, dt, rank=rank, nranks=N, device=local_rank,
+                              strict=not args.fma, use_cuda_graph=not args.no_graph)
     e.set_grid(gridf)
     if N > 1:
         blob = e.peer_blob()

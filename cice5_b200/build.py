@@ -1,8 +1,8 @@
 """nvcc driver: builds the in-tree C-ABI libraries for sm_100a.
 
-  lib/libevp_b200.so         product build (-O3, FMA contraction on)
-  lib/libevp_b200_strict.so  same sources with -fmad=false: IEEE evaluation without contraction,
-                             used by the parity tests to demand BITWISE equality with the oracle
+  lib/libevp_b200_strict.so  PRODUCT build: -O3 -fmad=false, IEEE evaluation without contraction,
+                             bitwise equal to the oracle (and to itself across decompositions)
+  lib/libevp_b200.so         same sources with FMA contraction on (comparison only)
 """
 from __future__ import annotations
 

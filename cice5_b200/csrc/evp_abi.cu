@@ -4,10 +4,13 @@
 #include "../../include/evp_b200.h"
 
 #include <cuda_runtime.h>
+#include <unistd.h>
 
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <new>
 #include <vector>
 
@@ -52,11 +55,17 @@ enum Plane {
     NPLANES
 };
 
-constexpr int kInboxRows = 4;
-
 struct PeerBlob {                 // exchanged between the tasks of one node
     cudaIpcMemHandle_t arena;
-    int rank, device, pid_tag;
+    int rank, device;
+    long long pid;                // same pid => same process: use the raw pointer, no IPC
+    unsigned long long arena_ptr;
+};
+
+struct Launcher;
+struct Op {                       // one step of the evp(dt) program of a handle
+    bool sync;                    // true: cross-rank barrier (signal + wait), no fn
+    std::function<int(Launcher &)> fn;
 };
 
 }  // namespace
@@ -64,6 +73,7 @@ struct PeerBlob {                 // exchanged between the tasks of one node
 struct evp_handle {
     evp_config_t cfg;
     Geom g;
+    InboxGeom ib;
     Consts k;
     int nxb, nyb, ld, ldm;
     size_t plane_elems;           // doubles per plane (ld * nyb)
@@ -75,9 +85,11 @@ struct evp_handle {
     bool peer_opened[kMaxRanks] = {false};
     bool grid_set = false, uploaded = false, peers_set = false;
     int parity = 0;               // which ping-pong copy holds the current state (0 = A)
-    cudaStream_t stream = nullptr;
+    int halo_seq = 0;             // halo operations issued in this compute (inbox buffer = seq & 1)
+    cudaStream_t stream = nullptr, own_stream = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-    cudaGraphExec_t loop_graph = nullptr;
+    cudaGraphExec_t loop_graph[2] = {nullptr, nullptr};   // per starting ping-pong parity
+    int h_error = 0;
     evp_stats_t stats;
     unsigned long long h_counts[2];
 
@@ -86,11 +98,17 @@ struct evp_handle {
         char *base = (rank < 0 || rank == cfg.rank) ? arena : peer_arena[rank];
         return reinterpret_cast<double *>(base + off_planes) + (size_t)p * plane_elems;
     }
-    double *inbox(int rank = -1) const
+    double *inbox(int buf, int rank = -1) const
     {
         char *base = (rank < 0 || rank == cfg.rank) ? arena : peer_arena[rank];
-        return reinterpret_cast<double *>(base + off_inbox);
+        return reinterpret_cast<double *>(base + off_inbox) + (size_t)buf * inbox_doubles(ib);
     }
+    unsigned long long *flags(int rank = -1) const   // [0..kMaxRanks) slots, [kMaxRanks] epoch
+    {
+        char *base = (rank < 0 || rank == cfg.rank) ? arena : peer_arena[rank];
+        return reinterpret_cast<unsigned long long *>(base + off_flags);
+    }
+    int *dev_error() const { return reinterpret_cast<int *>(arena + off_flags + 1024); }
     int *iplane(int p) const   // 0 tmask, 1 umask, 2 iceumask, 3 icetmask(int)
     {
         return reinterpret_cast<int *>(arena + off_int) + (size_t)p * plane_elems;
@@ -197,10 +215,12 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
     g.lo = cfg->rank * g.nxl; g.nranks = cfg->nranks; g.rank = cfg->rank;
     g.tripole = cfg->ns_boundary == EVP_NS_TRIPOLE; g.ew_cyclic = cfg->ew_boundary == EVP_EW_CYCLIC;
     g.inbox_ld = (int)align_up((size_t)h->nxb, 16);
+    h->ib.inbox_ld = g.inbox_ld;
+    h->ib.col_ld = (int)align_up((size_t)h->nyb, 16);
 
     size_t off = 0;
     h->off_planes = off; off = align_up(off + (size_t)NPLANES * h->plane_elems * sizeof(double), 256);
-    h->off_inbox = off;  off = align_up(off + (size_t)kInboxRows * g.inbox_ld * sizeof(double), 256);
+    h->off_inbox = off;  off = align_up(off + 2 * inbox_doubles(h->ib) * sizeof(double), 256);
     h->off_flags = off;  off = align_up(off + 4096, 256);
     h->off_int = off;    off = align_up(off + 4 * h->plane_elems * sizeof(int), 256);
     h->off_mask = off;   off = align_up(off + (size_t)h->ldm * h->nyb, 256);
@@ -213,7 +233,8 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
         return EVP_ERR_CUDA;
     }
     CK(cudaMemset(h->arena, 0, h->arena_bytes));
-    CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+    h->stream = h->own_stream;
     for (auto &ev : h->ev) CK(cudaEventCreate(&ev));
     memset(&h->stats, 0, sizeof(h->stats));
     h->peer_arena[cfg->rank] = h->arena;
@@ -227,11 +248,11 @@ int evp_gpu_finalize(evp_handle_t *h)
     if (!h) return EVP_ERR_ARG;
     cudaSetDevice(h->cfg.device);
     cudaDeviceSynchronize();
-    if (h->loop_graph) cudaGraphExecDestroy(h->loop_graph);
+    for (auto &gr : h->loop_graph) if (gr) cudaGraphExecDestroy(gr);
     for (int r = 0; r < kMaxRanks; ++r)
         if (h->peer_opened[r]) cudaIpcCloseMemHandle(h->peer_arena[r]);
     for (auto &ev : h->ev) if (ev) cudaEventDestroy(ev);
-    if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->own_stream) cudaStreamDestroy(h->own_stream);
     if (h->arena) cudaFree(h->arena);
     delete h;
     return EVP_OK;
@@ -348,56 +369,106 @@ struct Launcher {
     cudaStream_t s() const { return h->stream; }
 };
 
-// ice_HaloUpdate of one device plane: push my edges / top rows, then pre-fill + fold.
-int do_halo(Launcher &L, int plane, int loc, double sgn, double fill)
+void fill_sync_args(const evp_handle *h, SyncArgs &a)
 {
-    evp_handle *h = L.h;
-    const Geom &g = h->g;
-    PushArgs pa;
-    pa.g = g;
-    pa.plane = h->plane(plane);
-    pa.planeW = h->west_closed() ? nullptr : h->plane(plane, h->west());
-    pa.planeE = h->east_closed() ? nullptr : h->plane(plane, h->east());
-    for (int r = 0; r < kMaxRanks; ++r) pa.inbox[r] = r < g.nranks ? h->inbox(r) : nullptr;
-    pa.ioff = loc;              // center: source nx+1-ig, NEcorner: nx-ig
-    pa.inbox_row0 = 0;
-    const int nt = g.ny + (g.tripole ? g.nxl : 0);
-    halo_push_kernel<<<(nt + 255) / 256, 256, 0, L.s()>>>(pa);
+    memset(&a, 0, sizeof(a));
+    a.rank = h->cfg.rank; a.nranks = h->cfg.nranks;
+    a.epoch = h->flags() + kMaxRanks;
+    for (int r = 0; r < h->cfg.nranks; ++r) a.flags[r] = h->flags(r);
+    a.error = h->dev_error();
+    a.timeout_ns = 10ull * 1000ull * 1000ull * 1000ull;
+}
+
+int launch_signal(Launcher &L)
+{
+    SyncArgs a;
+    fill_sync_args(L.h, a);
+    halo_signal_kernel<<<1, 32, 0, L.s()>>>(a);
     ++L.n;
-    const int na = g.nxl + 2 + g.ny;
-    halo_apply_kernel<<<(na + 255) / 256, 256, 0, L.s()>>>(h->plane(plane), g, h->inbox(), 0, loc, sgn, fill,
-                                                        h->west_closed(), h->east_closed());
+    return EVP_OK;
+}
+int launch_wait(Launcher &L)
+{
+    SyncArgs a;
+    fill_sync_args(L.h, a);
+    halo_wait_kernel<<<1, 32, 0, L.s()>>>(a);
     ++L.n;
-    CK(cudaGetLastError());
     return EVP_OK;
 }
 
-// ice_HaloUpdate_stress(a1, a2): needs a2's top physical row mirrored with center offsets.
-int do_halo_stress(Launcher &L, int a1, int a2)
-{
-    evp_handle *h = L.h;
-    const Geom &g = h->g;
-    if (g.tripole) {
-        PushArgs pa;
-        pa.g = g;
-        pa.plane = h->plane(a2);
-        pa.planeW = nullptr; pa.planeE = nullptr;     // no ordinary neighbour copies (:3346-3353)
-        for (int r = 0; r < kMaxRanks; ++r) pa.inbox[r] = r < g.nranks ? h->inbox(r) : nullptr;
-        pa.ioff = 0;
-        pa.inbox_row0 = 0;
-        const int nt = g.ny + g.nxl;
-        halo_push_kernel<<<(nt + 255) / 256, 256, 0, L.s()>>>(pa);
-        ++L.n;
+// ---- program builder: the evp(dt) driver (source/ice_dyn_evp.F90:68-510) as a list of steps ----
+struct Builder {
+    evp_handle *h;
+    std::vector<Op> &prog;
+    int seq = 0;                               // halo operations so far -> inbox buffer
+    void op(std::function<int(Launcher &)> f) { prog.push_back(Op{false, std::move(f)}); }
+    void sync() { if (h->cfg.nranks > 1) prog.push_back(Op{true, nullptr}); }
+
+    // ice_HaloUpdate of one device plane: push edges / top rows into the inboxes, sync, apply
+    void halo(int plane, int loc, double sgn, double fill)
+    {
+        evp_handle *hh = h;
+        const int buf = (seq++) & 1;
+        op([hh, plane, loc, buf](Launcher &L) {
+            const Geom &g = hh->g;
+            PushArgs pa;
+            memset(&pa, 0, sizeof(pa));
+            pa.g = g; pa.ib = hh->ib; pa.plane = hh->plane(plane);
+            for (int r = 0; r < g.nranks; ++r) pa.inbox[r] = hh->inbox(buf, r);
+            pa.west = hh->west_closed() ? -1 : hh->west();
+            pa.east = hh->east_closed() ? -1 : hh->east();
+            pa.ioff = loc; pa.ew = 1;
+            const int nt = g.ny + (g.tripole ? g.nxl : 0);
+            halo_push_kernel<<<(nt + 255) / 256, 256, 0, L.s()>>>(pa);
+            ++L.n;
+            return EVP_OK;
+        });
+        sync();
+        op([hh, plane, loc, sgn, fill, buf](Launcher &L) {
+            const Geom &g = hh->g;
+            const int na = g.nxl + 2 + g.ny;
+            halo_apply_kernel<<<(na + 255) / 256, 256, 0, L.s()>>>(hh->plane(plane), g, hh->ib, hh->inbox(buf), loc,
+                                                                sgn, fill, hh->west_closed(), hh->east_closed());
+            ++L.n;
+            CK(cudaGetLastError());
+            return EVP_OK;
+        });
     }
-    const int na = g.nxl + 2 + g.ny + 2;
-    halo_stress_apply_kernel<<<(na + 255) / 256, 256, 0, L.s()>>>(h->plane(a1), g, h->inbox(), 0,
-                                                               h->west_closed(), h->east_closed());
-    ++L.n;
-    CK(cudaGetLastError());
-    return EVP_OK;
-}
 
-void fill_loop_args(const evp_handle *h, int from_parity, LoopArgs &a)
+    // ice_HaloUpdate_stress(a1, a2): a2's top physical row mirrored with center offsets
+    void halo_stress(int a1, int a2)
+    {
+        evp_handle *hh = h;
+        const int buf = (seq++) & 1;
+        if (hh->g.tripole) {
+            op([hh, a2, buf](Launcher &L) {
+                const Geom &g = hh->g;
+                PushArgs pa;
+                memset(&pa, 0, sizeof(pa));
+                pa.g = g; pa.ib = hh->ib; pa.plane = hh->plane(a2);
+                for (int r = 0; r < g.nranks; ++r) pa.inbox[r] = hh->inbox(buf, r);
+                pa.west = -1; pa.east = -1;            // no ordinary neighbour copies (:3346-3353)
+                pa.ioff = 0; pa.ew = 0;
+                const int nt = g.ny + g.nxl;
+                halo_push_kernel<<<(nt + 255) / 256, 256, 0, L.s()>>>(pa);
+                ++L.n;
+                return EVP_OK;
+            });
+            sync();
+        }
+        op([hh, a1, buf](Launcher &L) {
+            const Geom &g = hh->g;
+            const int na = g.nxl + 2 + g.ny + 2;
+            halo_stress_apply_kernel<<<(na + 255) / 256, 256, 0, L.s()>>>(hh->plane(a1), g, hh->ib, hh->inbox(buf),
+                                                                       hh->west_closed(), hh->east_closed());
+            ++L.n;
+            CK(cudaGetLastError());
+            return EVP_OK;
+        });
+    }
+};
+
+void fill_loop_args(const evp_handle *h, int from_parity, int inbox_buf, LoopArgs &a)
 {
     const Geom &g = h->g;
     memset(&a, 0, sizeof(a));
@@ -421,28 +492,236 @@ void fill_loop_args(const evp_handle *h, int from_parity, LoopArgs &a)
     a.divu = h->plane(O_DIVU); a.shear = h->plane(O_SHEAR); a.rdg_conv = h->plane(O_RDGCONV);
     a.rdg_shear = h->plane(O_RDGSHEAR); a.prs_sig = h->plane(O_PRSSIG);
     a.strintx = h->plane(O_STRINTX); a.strinty = h->plane(O_STRINTY);
+    // E-W ghosts of the NEW velocity planes are written in place (self, or peer memory over
+    // NVLink): the ping-pong separates these stores from every read of the same plane by one sync
     if (!h->west_closed()) { a.uW = h->plane(U1, h->west()); a.vW = h->plane(V1, h->west()); }
     if (!h->east_closed()) { a.uE = h->plane(U1, h->east()); a.vE = h->plane(V1, h->east()); }
-    for (int r = 0; r < g.nranks; ++r) a.inbox[r] = h->inbox(r);
+    for (int r = 0; r < g.nranks; ++r) a.inbox[r] = h->inbox(inbox_buf, r);
     a.k = h->k;
 }
 
-// one subcycle: stress + stepu + halo pushes fused; then the tripole fold of the new u, v
-int launch_subcycle(Launcher &L, int from_parity, bool last)
+// one subcycle: stress + stepu + halo pushes fused; [sync]; then the tripole fold of the new u, v
+void add_subcycle(Builder &B, int from_parity, bool last)
+{
+    evp_handle *h = B.h;
+    const int buf = (B.seq++) & 1;
+    B.op([h, from_parity, last, buf](Launcher &L) {
+        const Geom &g = h->g;
+        LoopArgs a;
+        fill_loop_args(h, from_parity, buf, a);
+        const int strips = (g.nxl + kUColsPerWarp - 1) / kUColsPerWarp;
+        dim3 grid((strips + kWarpsPerBlock - 1) / kWarpsPerBlock, (g.ny + a.rows_per_chunk - 1) / a.rows_per_chunk);
+        if (last) evp_subcycle_kernel<true><<<grid, kWarpsPerBlock * 32, 0, L.s()>>>(a);
+        else evp_subcycle_kernel<false><<<grid, kWarpsPerBlock * 32, 0, L.s()>>>(a);
+        ++L.n;
+        return EVP_OK;
+    });
+    B.sync();
+    if (h->g.tripole) {
+        B.op([h, from_parity, buf](Launcher &L) {
+            const Geom &g = h->g;
+            double *u1 = h->plane(from_parity ? S_UA : S_UB), *v1 = h->plane(from_parity ? S_VA : S_VB);
+            fold_uv_kernel<<<(g.nxl + 2 + 127) / 128, 128, 0, L.s()>>>(u1, v1, g.ld, g.nxl, g.ny, g.nx_global, g.lo,
+                                                                     h->inbox(buf), g.inbox_ld);
+            ++L.n;
+            return EVP_OK;
+        });
+    }
+}
+
+struct Program {
+    std::vector<Op> ops;
+    size_t loop_begin = 0, loop_end = 0;       // [begin, end) = the ndte subcycles
+    int end_parity = 0;
+};
+
+void build_program(evp_handle *h, double dt, Program &P)
+{
+    const evp_config_t &cfg = h->cfg;
+    Builder B{h, P.ops};
+    const size_t pb = h->plane_elems * sizeof(double);
+    const int cur = h->parity;
+    const int Ucur = cur ? S_UB : S_UA, Vcur = cur ? S_VB : S_VA, Uoth = cur ? S_UA : S_UB;
+
+    B.sync();      // every rank has left its previous call: inbox buffers and planes are free
+    B.op([h, pb](Launcher &L) {
+        cudaStream_t s = L.s();
+        CK(cudaEventRecord(h->ev[0], s));
+        // init_history_dyn contract (ice_flux.F90:639-673) + evp's own zeroing (ice_dyn_evp.F90:174-182)
+        CK(cudaMemsetAsync(h->plane(O_STRAIRX), 0, pb * 17, s));   // all output planes
+        CK(cudaMemsetAsync(h->plane(S_FM), 0, pb, s));
+        CK(cudaMemsetAsync(h->counts(), 0, 16, s));
+        // evp_prep1 (:194)
+        Prep1Args a;
+        a.g = h->g; a.rhoi = h->cfg.rhoi; a.rhos = h->cfg.rhos; a.a_min = h->cfg.a_min; a.m_min = h->cfg.m_min;
+        a.aice = h->plane(I_AICE); a.vice = h->plane(I_VICE); a.vsno = h->plane(I_VSNO);
+        a.strairxT = h->plane(I_STRAIRXT); a.strairyT = h->plane(I_STRAIRYT); a.tmask = h->iplane(0);
+        a.tmass = h->plane(W_TMASS); a.work1 = h->plane(W_1); a.work2 = h->plane(W_2);
+        a.icetmask = h->plane(W_ICETMASK);
+        prep1_kernel<<<grid2d(h), 128, 0, s>>>(a);
+        ++L.n;
+        return EVP_OK;
+    });
+    B.halo(W_ICETMASK, 0, +1.0, 0.0);                          // :210
+    B.halo(W_1, 0, -1.0, 0.0);                                 // t2ugrid_vector (ice_grid.F90:1817)
+    B.halo(W_2, 0, -1.0, 0.0);
+    B.op([h, dt, cur](Launcher &L) {
+        cudaStream_t s = L.s();
+        const evp_config_t &cfg = h->cfg;
+        {   // to_ugrid: umass, aiu, strairx, strairy (:218-241)
+            ToUArgs a;
+            a.g = h->g; a.tarea = h->plane(G_TAREA); a.uarea = h->plane(G_UAREA);
+            a.in[0] = h->plane(W_TMASS); a.out[0] = h->plane(W_UMASS);
+            a.in[1] = h->plane(I_AICE_INIT); a.out[1] = h->plane(W_AIU);
+            a.in[2] = h->plane(W_1); a.out[2] = h->plane(O_STRAIRX);
+            a.in[3] = h->plane(W_2); a.out[3] = h->plane(O_STRAIRY);
+            to_ugrid4_kernel<<<grid2d(h), 128, 0, s>>>(a);
+            ++L.n;
+        }
+        {   // evp_prep2 + ice_strength masking (:260-301)
+            Prep2Args a;
+            a.g = h->g; a.dt = dt; a.a_min = cfg.a_min; a.m_min = cfg.m_min; a.cosw = cfg.cosw; a.sinw = cfg.sinw;
+            a.gravit = cfg.gravit; a.tilt_mode = cfg.tilt_mode; a.strength_masked = cfg.strength_masked;
+            a.aiu = h->plane(W_AIU); a.umass = h->plane(W_UMASS); a.fcor = h->plane(G_FCOR);
+            a.uocn = h->plane(I_UOCN); a.vocn = h->plane(I_VOCN); a.strairx = h->plane(O_STRAIRX);
+            a.strairy = h->plane(O_STRAIRY); a.ss_tltx = h->plane(I_SSTLTX); a.ss_tlty = h->plane(I_SSTLTY);
+            a.icetmask = h->plane(W_ICETMASK); a.strength_in = h->plane(I_STRENGTH);
+            a.umask = h->iplane(1); a.iceumask = h->iplane(2);
+            a.fm = h->plane(S_FM); a.strtltx = h->plane(O_STRTLTX); a.strtlty = h->plane(O_STRTLTY);
+            a.strocnx = h->plane(O_STROCNX); a.strocny = h->plane(O_STROCNY);
+            a.strintx = h->plane(O_STRINTX); a.strinty = h->plane(O_STRINTY);
+            a.umassdti = h->plane(W_UMASSDTI); a.waterx = h->plane(W_WATERX); a.watery = h->plane(W_WATERY);
+            a.forcex = h->plane(W_FORCEX); a.forcey = h->plane(W_FORCEY); a.strength = h->plane(W_STRENGTH);
+            for (int q = 0; q < 12; ++q) {
+                a.sA[q] = h->plane((cur ? S_STRB : S_STRA) + q);
+                a.sB[q] = h->plane((cur ? S_STRA : S_STRB) + q);
+            }
+            a.uA = h->plane(cur ? S_UB : S_UA); a.vA = h->plane(cur ? S_VB : S_VA);
+            a.uvel_init = h->plane(O_UVELINIT); a.vvel_init = h->plane(O_VVELINIT);
+            a.mask = h->mask(); a.ldm = h->ldm; a.counts = h->counts();
+            prep2_kernel<<<grid2d(h), 128, 0, s>>>(a);
+            ++L.n;
+        }
+        CK(cudaGetLastError());
+        return EVP_OK;
+    });
+    B.halo(W_STRENGTH, 0, +1.0, 0.0);                          // :311
+    B.halo(Ucur, 1, -1.0, 0.0);                                // :314 (fld2)
+    B.halo(Vcur, 1, -1.0, 0.0);
+    B.op([h, pb, Ucur, Uoth](Launcher &L) {
+        // the other ping-pong copy must carry the same ghost ring where the loop never writes
+        // (south row, closed E-W edges, open north row): start it as a copy of the current one
+        CK(cudaMemcpyAsync(h->plane(Uoth), h->plane(Ucur), pb * 2, cudaMemcpyDeviceToDevice, L.s()));
+        return EVP_OK;
+    });
+    B.sync();      // neighbours' in-loop ghost stores into that copy must come after this memcpy
+    B.op([h](Launcher &L) { CK(cudaEventRecord(h->ev[1], L.s())); return EVP_OK; });
+
+    // ---- subcycling (:336-410) ----
+    P.loop_begin = P.ops.size();
+    int par = cur;
+    for (int ksub = 1; ksub <= cfg.ndte; ++ksub) {
+        add_subcycle(B, par, ksub == cfg.ndte);
+        par ^= 1;
+    }
+    P.loop_end = P.ops.size();
+    P.end_parity = par;
+    B.op([h](Launcher &L) { CK(cudaEventRecord(h->ev[2], L.s())); return EVP_OK; });
+
+    // ---- tripole stress symmetrisation (:416-481) ----
+    if (cfg.grid_tripole) {
+        const int S = par ? S_STRB : S_STRA;
+        for (int f = 0; f < 3; ++f) {
+            const int b = S + 4 * f;
+            B.halo_stress(b + 0, b + 2); B.halo_stress(b + 2, b + 0);
+            B.halo_stress(b + 1, b + 3); B.halo_stress(b + 3, b + 1);
+        }
+    }
+    B.op([h, par](Launcher &L) {   // evp_finish (:490)
+        FinishArgs a;
+        a.g = h->g; a.rhow = h->cfg.rhow; a.cosw = h->cfg.cosw; a.sinw = h->cfg.sinw;
+        a.u = h->plane(par ? S_UB : S_UA); a.v = h->plane(par ? S_VB : S_VA);
+        a.uocn = h->plane(I_UOCN); a.vocn = h->plane(I_VOCN); a.aiu = h->plane(W_AIU); a.fm = h->plane(S_FM);
+        a.Cw = h->plane(I_CW); a.iceumask = h->iplane(2);
+        a.strocnx = h->plane(O_STROCNX); a.strocny = h->plane(O_STROCNY);
+        a.work1 = h->plane(W_1); a.work2 = h->plane(W_2);
+        finish_kernel<<<grid2d(h), 128, 0, L.s()>>>(a);
+        ++L.n;
+        return EVP_OK;
+    });
+    B.halo(W_1, 1, -1.0, 0.0);                                 // u2tgrid_vector (:505-506)
+    B.halo(W_2, 1, -1.0, 0.0);
+    B.op([h](Launcher &L) {
+        cudaStream_t s = L.s();
+        to_tgrid2_kernel<<<grid2d(h), 128, 0, s>>>(h->g, h->plane(G_TAREA), h->plane(G_UAREA), h->plane(W_1),
+                                                  h->plane(W_2), h->plane(O_STROCNXT), h->plane(O_STROCNYT));
+        ++L.n;
+        double_to_int_kernel<<<(unsigned)((h->plane_elems + 255) / 256), 256, 0, s>>>(h->plane(W_ICETMASK),
+                                                                                      h->iplane(3), h->plane_elems);
+        ++L.n;
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(h->ev[3], s));
+        CK(cudaMemcpyAsync(h->h_counts, h->counts(), 16, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(&h->h_error, h->dev_error(), sizeof(int), cudaMemcpyDeviceToHost, s));
+        return EVP_OK;
+    });
+}
+
+int exec_range(Launcher &L, const Program &P, size_t b, size_t e)
+{
+    for (size_t i = b; i < e; ++i) {
+        const Op &op = P.ops[i];
+        if (op.sync) { TRY(launch_signal(L)); TRY(launch_wait(L)); }
+        else TRY(op.fn(L));
+    }
+    return EVP_OK;
+}
+
+// the ndte loop: straight launches, or one CUDA graph per starting parity, captured on first use
+int exec_loop(Launcher &L, const Program &P, long long &n_loop)
 {
     evp_handle *h = L.h;
-    const Geom &g = h->g;
-    LoopArgs a;
-    fill_loop_args(h, from_parity, a);
-    const int strips = (g.nxl + kUColsPerWarp - 1) / kUColsPerWarp;
-    dim3 grid((strips + kWarpsPerBlock - 1) / kWarpsPerBlock, (g.ny + a.rows_per_chunk - 1) / a.rows_per_chunk);
-    if (last) evp_subcycle_kernel<true><<<grid, kWarpsPerBlock * 32, 0, L.s()>>>(a);
-    else evp_subcycle_kernel<false><<<grid, kWarpsPerBlock * 32, 0, L.s()>>>(a);
-    ++L.n;
-    if (g.tripole) {
-        fold_uv_kernel<<<(g.nxl + 2 + 127) / 128, 128, 0, L.s()>>>(a.u1, a.v1, g.ld, g.nxl, g.ny, g.nx_global,
-                                                                 g.lo, h->inbox(), g.inbox_ld);
-        ++L.n;
+    const long long n0 = L.n;
+    if (!h->cfg.use_cuda_graph) {
+        TRY(exec_range(L, P, P.loop_begin, P.loop_end));
+        n_loop = L.n - n0;
+        return EVP_OK;
+    }
+    cudaGraphExec_t &ge = h->loop_graph[h->parity];
+    if (!ge) {
+        cudaGraph_t graph = nullptr;
+        CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+        int rc = exec_range(L, P, P.loop_begin, P.loop_end);
+        cudaError_t e = cudaStreamEndCapture(h->stream, &graph);
+        if (rc != EVP_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+        CK(e);
+        CK(cudaGraphInstantiate(&ge, graph, 0));
+        CK(cudaGraphDestroy(graph));
+        h->stats.loop_kernel_launches = L.n - n0;
+    } else {
+        L.n += h->stats.loop_kernel_launches;
+    }
+    CK(cudaGraphLaunch(ge, h->stream));
+    n_loop = h->stats.loop_kernel_launches;
+    return EVP_OK;
+}
+
+int finish_compute(evp_handle *h, const Program &P, long long n_total, long long n_loop)
+{
+    CK(cudaStreamSynchronize(h->stream));
+    h->parity = P.end_parity;
+    float ms;
+    CK(cudaEventElapsedTime(&ms, h->ev[0], h->ev[1])); h->stats.prep_ms = ms;
+    CK(cudaEventElapsedTime(&ms, h->ev[1], h->ev[2])); h->stats.loop_ms = ms;
+    CK(cudaEventElapsedTime(&ms, h->ev[2], h->ev[3])); h->stats.finish_ms = ms;
+    CK(cudaEventElapsedTime(&ms, h->ev[0], h->ev[3])); h->stats.total_ms = ms;
+    h->stats.active_t_cells = (long long)h->h_counts[0];
+    h->stats.active_u_cells = (long long)h->h_counts[1];
+    h->stats.kernel_launches = n_total;
+    h->stats.loop_kernel_launches = n_loop;
+    if (h->h_error) {
+        snprintf(g_cuda_err, sizeof(g_cuda_err), "halo wait timed out: a peer rank did not arrive");
+        return EVP_ERR_PEER;
     }
     return EVP_OK;
 }
@@ -456,131 +735,58 @@ int evp_gpu_compute(evp_handle_t *h, double dt)
     if (!h) return EVP_ERR_ARG;
     if (!h->grid_set || !h->uploaded || !h->peers_set) return EVP_ERR_STATE;
     if (!(dt > 0.0)) return EVP_ERR_ARG;
-    if (h->cfg.nranks > 1) return EVP_ERR_UNSUPPORTED;   // multi-GPU sync arrives with evp_multi
     CK(cudaSetDevice(h->cfg.device));
-    const Geom &g = h->g;
-    const evp_config_t &cfg = h->cfg;
+    Program P;
+    build_program(h, dt, P);
     Launcher L{h};
-    cudaStream_t s = h->stream;
-    const size_t pb = h->plane_elems * sizeof(double);
-
-    CK(cudaEventRecord(h->ev[0], s));
-    // init_history_dyn contract (ice_flux.F90:639-673) + evp's own zeroing (ice_dyn_evp.F90:174-182)
-    CK(cudaMemsetAsync(h->plane(O_STRAIRX), 0, pb * 17, s));   // all output planes
-    CK(cudaMemsetAsync(h->plane(S_FM), 0, pb, s));
-    CK(cudaMemsetAsync(h->counts(), 0, 16, s));
-
-    {   // evp_prep1 (:194)
-        Prep1Args a;
-        a.g = g; a.rhoi = cfg.rhoi; a.rhos = cfg.rhos; a.a_min = cfg.a_min; a.m_min = cfg.m_min;
-        a.aice = h->plane(I_AICE); a.vice = h->plane(I_VICE); a.vsno = h->plane(I_VSNO);
-        a.strairxT = h->plane(I_STRAIRXT); a.strairyT = h->plane(I_STRAIRYT); a.tmask = h->iplane(0);
-        a.tmass = h->plane(W_TMASS); a.work1 = h->plane(W_1); a.work2 = h->plane(W_2);
-        a.icetmask = h->plane(W_ICETMASK);
-        prep1_kernel<<<grid2d(h), 128, 0, s>>>(a);
-        ++L.n;
-    }
-    TRY(do_halo(L, W_ICETMASK, 0, +1.0, 0.0));                 // :210
-    TRY(do_halo(L, W_1, 0, -1.0, 0.0));                        // t2ugrid_vector (ice_grid.F90:1817)
-    TRY(do_halo(L, W_2, 0, -1.0, 0.0));
-    {   // to_ugrid: umass, aiu, strairx, strairy (:218-241)
-        ToUArgs a;
-        a.g = g; a.tarea = h->plane(G_TAREA); a.uarea = h->plane(G_UAREA);
-        a.in[0] = h->plane(W_TMASS); a.out[0] = h->plane(W_UMASS);
-        a.in[1] = h->plane(I_AICE_INIT); a.out[1] = h->plane(W_AIU);
-        a.in[2] = h->plane(W_1); a.out[2] = h->plane(O_STRAIRX);
-        a.in[3] = h->plane(W_2); a.out[3] = h->plane(O_STRAIRY);
-        to_ugrid4_kernel<<<grid2d(h), 128, 0, s>>>(a);
-        ++L.n;
-    }
-    {   // evp_prep2 + ice_strength masking (:260-301)
-        Prep2Args a;
-        a.g = g; a.dt = dt; a.a_min = cfg.a_min; a.m_min = cfg.m_min; a.cosw = cfg.cosw; a.sinw = cfg.sinw;
-        a.gravit = cfg.gravit; a.tilt_mode = cfg.tilt_mode; a.strength_masked = cfg.strength_masked;
-        a.aiu = h->plane(W_AIU); a.umass = h->plane(W_UMASS); a.fcor = h->plane(G_FCOR);
-        a.uocn = h->plane(I_UOCN); a.vocn = h->plane(I_VOCN); a.strairx = h->plane(O_STRAIRX);
-        a.strairy = h->plane(O_STRAIRY); a.ss_tltx = h->plane(I_SSTLTX); a.ss_tlty = h->plane(I_SSTLTY);
-        a.icetmask = h->plane(W_ICETMASK); a.strength_in = h->plane(I_STRENGTH);
-        a.umask = h->iplane(1); a.iceumask = h->iplane(2);
-        a.fm = h->plane(S_FM); a.strtltx = h->plane(O_STRTLTX); a.strtlty = h->plane(O_STRTLTY);
-        a.strocnx = h->plane(O_STROCNX); a.strocny = h->plane(O_STROCNY);
-        a.strintx = h->plane(O_STRINTX); a.strinty = h->plane(O_STRINTY);
-        a.umassdti = h->plane(W_UMASSDTI); a.waterx = h->plane(W_WATERX); a.watery = h->plane(W_WATERY);
-        a.forcex = h->plane(W_FORCEX); a.forcey = h->plane(W_FORCEY); a.strength = h->plane(W_STRENGTH);
-        const int cur = h->parity;
-        for (int q = 0; q < 12; ++q) {
-            a.sA[q] = h->plane((cur ? S_STRB : S_STRA) + q);
-            a.sB[q] = h->plane((cur ? S_STRA : S_STRB) + q);
-        }
-        a.uA = h->plane(cur ? S_UB : S_UA); a.vA = h->plane(cur ? S_VB : S_VA);
-        a.uvel_init = h->plane(O_UVELINIT); a.vvel_init = h->plane(O_VVELINIT);
-        a.mask = h->mask(); a.ldm = h->ldm; a.counts = h->counts();
-        prep2_kernel<<<grid2d(h), 128, 0, s>>>(a);
-        ++L.n;
-    }
-    TRY(do_halo(L, W_STRENGTH, 0, +1.0, 0.0));                 // :311
-    TRY(do_halo(L, h->parity ? S_UB : S_UA, 1, -1.0, 0.0));    // :314 (fld2)
-    TRY(do_halo(L, h->parity ? S_VB : S_VA, 1, -1.0, 0.0));
-    // the other copy must carry the same ghost ring where the loop never writes (south row,
-    // closed E-W edges, open north row): start it as a copy of the current one
-    CK(cudaMemcpyAsync(h->plane(h->parity ? S_UA : S_UB), h->plane(h->parity ? S_UB : S_UA), pb * 2,
-                       cudaMemcpyDeviceToDevice, s));
+    long long n_loop = 0;
+    TRY(exec_range(L, P, 0, P.loop_begin));
+    TRY(exec_loop(L, P, n_loop));
+    TRY(exec_range(L, P, P.loop_end, P.ops.size()));
     CK(cudaGetLastError());
+    return finish_compute(h, P, L.n, n_loop);
+}
 
-    // ---- subcycling (:336-410) ----
-    CK(cudaEventRecord(h->ev[1], s));
-    const long long n_before_loop = L.n;
-    for (int ksub = 1; ksub <= cfg.ndte; ++ksub) {
-        TRY(launch_subcycle(L, h->parity, ksub == cfg.ndte));
-        h->parity ^= 1;
+// Several ranks driven by ONE host thread on ONE stream (all handles on the same device, or
+// tests with fewer GPUs than ranks): the steps of all ranks are interleaved phase by phase, so
+// every signal is enqueued before any wait of the same barrier and no kernel ever spins.
+int evp_gpu_compute_group(evp_handle_t **hs, int n, double dt)
+{
+    if (!hs || n < 1 || n > kMaxRanks) return EVP_ERR_ARG;
+    for (int r = 0; r < n; ++r) {
+        if (!hs[r] || hs[r]->cfg.nranks != n || hs[r]->cfg.rank != r) return EVP_ERR_ARG;
+        if (!hs[r]->grid_set || !hs[r]->uploaded || !hs[r]->peers_set) return EVP_ERR_STATE;
+        if (hs[r]->cfg.device != hs[0]->cfg.device) return EVP_ERR_UNSUPPORTED;
     }
-    CK(cudaGetLastError());
-    const long long n_loop = L.n - n_before_loop;
-    CK(cudaEventRecord(h->ev[2], s));
-
-    // ---- tripole stress symmetrisation (:416-481) ----
-    if (cfg.grid_tripole) {
-        const int S = h->parity ? S_STRB : S_STRA;
-        for (int f = 0; f < 3; ++f) {
-            const int b = S + 4 * f;
-            TRY(do_halo_stress(L, b + 0, b + 2)); TRY(do_halo_stress(L, b + 2, b + 0));
-            TRY(do_halo_stress(L, b + 1, b + 3)); TRY(do_halo_stress(L, b + 3, b + 1));
+    if (!(dt > 0.0)) return EVP_ERR_ARG;
+    CK(cudaSetDevice(hs[0]->cfg.device));
+    std::vector<Program> P(n);
+    std::vector<Launcher> L;
+    for (int r = 0; r < n; ++r) {
+        CK(cudaStreamSynchronize(hs[r]->stream));
+        hs[r]->stream = hs[0]->own_stream;             // one shared stream
+        build_program(hs[r], dt, P[r]);
+        L.push_back(Launcher{hs[r]});
+        if (P[r].ops.size() != P[0].ops.size()) return EVP_ERR_STATE;
+    }
+    int rc = EVP_OK;
+    long long n_before = 0, n_after = 0;
+    for (size_t i = 0; i < P[0].ops.size() && rc == EVP_OK; ++i) {
+        if (i == P[0].loop_begin) n_before = L[0].n;
+        if (i == P[0].loop_end) n_after = L[0].n;
+        if (P[0].ops[i].sync) {
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = launch_signal(L[r]);
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = launch_wait(L[r]);
+        } else {
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = P[r].ops[i].fn(L[r]);
         }
     }
-    {   // evp_finish (:490) + u2tgrid_vector (:505-506)
-        FinishArgs a;
-        a.g = g; a.rhow = cfg.rhow; a.cosw = cfg.cosw; a.sinw = cfg.sinw;
-        a.u = h->plane(h->parity ? S_UB : S_UA); a.v = h->plane(h->parity ? S_VB : S_VA);
-        a.uocn = h->plane(I_UOCN); a.vocn = h->plane(I_VOCN); a.aiu = h->plane(W_AIU); a.fm = h->plane(S_FM);
-        a.Cw = h->plane(I_CW); a.iceumask = h->iplane(2);
-        a.strocnx = h->plane(O_STROCNX); a.strocny = h->plane(O_STROCNY);
-        a.work1 = h->plane(W_1); a.work2 = h->plane(W_2);
-        finish_kernel<<<grid2d(h), 128, 0, s>>>(a);
-        ++L.n;
+    for (int r = 0; r < n; ++r) {
+        int rc2 = (rc == EVP_OK) ? finish_compute(hs[r], P[r], L[r].n, n_after - n_before) : rc;
+        hs[r]->stream = hs[r]->own_stream;
+        if (rc2 != EVP_OK) rc = rc2;
     }
-    TRY(do_halo(L, W_1, 1, -1.0, 0.0));
-    TRY(do_halo(L, W_2, 1, -1.0, 0.0));
-    to_tgrid2_kernel<<<grid2d(h), 128, 0, s>>>(g, h->plane(G_TAREA), h->plane(G_UAREA), h->plane(W_1),
-                                              h->plane(W_2), h->plane(O_STROCNXT), h->plane(O_STROCNYT));
-    ++L.n;
-    double_to_int_kernel<<<(unsigned)((h->plane_elems + 255) / 256), 256, 0, s>>>(h->plane(W_ICETMASK), h->iplane(3),
-                                                                                  h->plane_elems);
-    ++L.n;
-    CK(cudaGetLastError());
-    CK(cudaEventRecord(h->ev[3], s));
-    CK(cudaMemcpyAsync(h->h_counts, h->counts(), 16, cudaMemcpyDeviceToHost, s));
-    CK(cudaStreamSynchronize(s));
-
-    float ms;
-    CK(cudaEventElapsedTime(&ms, h->ev[0], h->ev[1])); h->stats.prep_ms = ms;
-    CK(cudaEventElapsedTime(&ms, h->ev[1], h->ev[2])); h->stats.loop_ms = ms;
-    CK(cudaEventElapsedTime(&ms, h->ev[2], h->ev[3])); h->stats.finish_ms = ms;
-    CK(cudaEventElapsedTime(&ms, h->ev[0], h->ev[3])); h->stats.total_ms = ms;
-    h->stats.active_t_cells = (long long)h->h_counts[0];
-    h->stats.active_u_cells = (long long)h->h_counts[1];
-    h->stats.kernel_launches = L.n;
-    h->stats.loop_kernel_launches = n_loop;
-    return EVP_OK;
+    return rc;
 }
 
 int evp_gpu_run(evp_handle_t *h, double dt, const evp_in_t *in, evp_inout_t *io, evp_out_t *out)
@@ -601,7 +807,8 @@ int evp_gpu_get_peer_blob(evp_handle_t *h, void *blob)
     PeerBlob b;
     memset(&b, 0, sizeof(b));
     CK(cudaIpcGetMemHandle(&b.arena, h->arena));
-    b.rank = h->cfg.rank; b.device = h->cfg.device; b.pid_tag = 0;
+    b.rank = h->cfg.rank; b.device = h->cfg.device; b.pid = (long long)getpid();
+    b.arena_ptr = (unsigned long long)(uintptr_t)h->arena;
     memcpy(blob, &b, sizeof(b));
     return EVP_OK;
 }
@@ -615,6 +822,19 @@ int evp_gpu_set_peers(evp_handle_t *h, const void *blobs)
         if (r == h->cfg.rank) continue;
         if (b[r].rank != r) return EVP_ERR_PEER;
         void *p = nullptr;
+        if (b[r].pid == (long long)getpid()) {          // same process: plain pointer (+ peer access)
+            if (b[r].device != h->cfg.device) {
+                cudaError_t e2 = cudaDeviceEnablePeerAccess(b[r].device, 0);
+                if (e2 != cudaSuccess && e2 != cudaErrorPeerAccessAlreadyEnabled) {
+                    snprintf(g_cuda_err, sizeof(g_cuda_err), "cudaDeviceEnablePeerAccess(%d): %s", b[r].device,
+                             cudaGetErrorString(e2));
+                    return EVP_ERR_PEER;
+                }
+                cudaGetLastError();
+            }
+            h->peer_arena[r] = reinterpret_cast<char *>((uintptr_t)b[r].arena_ptr);
+            continue;
+        }
         cudaError_t e = cudaIpcOpenMemHandle(&p, b[r].arena, cudaIpcMemLazyEnablePeerAccess);
         if (e != cudaSuccess) {
             snprintf(g_cuda_err, sizeof(g_cuda_err), "cudaIpcOpenMemHandle(rank %d): %s", r, cudaGetErrorString(e));

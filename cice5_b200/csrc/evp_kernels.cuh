@@ -306,31 +306,32 @@ evp_subcycle_kernel(const __grid_constant__ LoopArgs a)
     }
 }
 
-// Tripole u-fold of an NEcorner field pair/plane from the inbox (serial/ice_boundary.F90:809-824,
-// 861-890): top physical row r = ny is replaced by the (anti)symmetrised average, ghost row
-// r = ny+1 by the mirrored row ny-1.  One thread per local column, ghosts included.
-// inbox rows: [0] = row ny-1 of the fold source column, [1] = row ny.
+// Tripole u-fold of one column of an NEcorner field (serial/ice_boundary.F90:809-824, 861-890):
+// the top physical row r = ny is replaced by the (anti)symmetrised average, the ghost row
+// r = ny+1 by the mirrored row ny-1.  own = this column's row-ny value before the fold,
+// src_top / src_below = rows ny / ny-1 of the fold source column (global column nx - ig).
 __device__ __forceinline__ void fold_necorner_column(double *plane, int ld, int ny, int c, int ig,
-                                                     int nx, const double *in_below,
-                                                     const double *in_top, double sgn)
+                                                     int nx, double own, double src_below,
+                                                     double src_top, double sgn)
 {
     const int m = (nx - ig == 0) ? nx : nx - ig;
     const int half = nx / 2;
-    const double own = plane[(size_t)ny * ld + c];
-    const double src = in_top[c];
     double x;
     if (ig >= 1 && ig <= half - 1) {
-        x = 0.5 * (own + sgn * src);                   // xavg; copy-out gives sgn*(sgn*xavg)
+        x = 0.5 * (own + sgn * src_top);               // xavg; copy-out gives sgn*(sgn*xavg)
         x = sgn * (sgn * x);
     } else if (m >= 1 && m <= half - 1) {
-        x = sgn * (0.5 * (src + sgn * own));           // sgn * xavg of the pair (m, ig)
+        x = sgn * (0.5 * (src_top + sgn * own));       // sgn * xavg of the pair (m, ig)
     } else {
-        x = sgn * src;                                 // self-mirrored / unpaired points
+        x = sgn * src_top;                             // self-mirrored / unpaired points
     }
     plane[(size_t)ny * ld + c] = x;
-    plane[(size_t)(ny + 1) * ld + c] = sgn * in_below[c];
+    plane[(size_t)(ny + 1) * ld + c] = sgn * src_below;
 }
 
+// Fold of the freshly stepped (u, v): one thread per local column, ghost columns included (their
+// row-ny value was pushed into the plane by the E-W neighbour's subcycle kernel).
+// inbox rows: [0] u row ny-1, [1] u row ny, [2] v row ny-1, [3] v row ny of the fold source.
 __global__ void fold_uv_kernel(double *u, double *v, int ld, int nxl, int ny, int nx, int lo,
                                const double *inbox, int inbox_ld)
 {
@@ -339,8 +340,9 @@ __global__ void fold_uv_kernel(double *u, double *v, int ld, int nxl, int ny, in
     int ig = lo + c;
     if (ig < 1) ig += nx;
     if (ig > nx) ig -= nx;
-    fold_necorner_column(u, ld, ny, c, ig, nx, inbox + 0 * inbox_ld, inbox + 1 * inbox_ld, -1.0);
-    fold_necorner_column(v, ld, ny, c, ig, nx, inbox + 2 * inbox_ld, inbox + 3 * inbox_ld, -1.0);
+    fold_necorner_column(u, ld, ny, c, ig, nx, u[(size_t)ny * ld + c], inbox[c], inbox[inbox_ld + c], -1.0);
+    fold_necorner_column(v, ld, ny, c, ig, nx, v[(size_t)ny * ld + c], inbox[2 * inbox_ld + c],
+                         inbox[3 * inbox_ld + c], -1.0);
 }
 
 }  // namespace evp

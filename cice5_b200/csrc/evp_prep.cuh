@@ -26,18 +26,41 @@ __device__ __forceinline__ int glob_col(const Geom &g, int c)
     return ig;
 }
 
+// ---- inbox: all cross-rank halo traffic lands here (never directly in a peer's planes, so a
+// producer kernel that sweeps whole planes cannot race with a neighbour that runs ahead).
+// Two buffers, alternated per halo operation: a writer of operation n+2 has passed the sync of
+// operation n+1, i.e. the owner has finished reading buffer (n & 1).
+//   rows[4][inbox_ld]  : [field a: row ny-1 | row ny][field b: row ny-1 | row ny] of the fold source
+//   cols[4][col_ld]    : [a: west ghost | a: east ghost | b: west ghost | b: east ghost], index = row
+struct InboxGeom {
+    int inbox_ld, col_ld;
+};
+__host__ __device__ __forceinline__ size_t inbox_doubles(const InboxGeom &ib)
+{
+    return (size_t)4 * ib.inbox_ld + (size_t)4 * ib.col_ld;
+}
+__device__ __forceinline__ double *inbox_row(double *base, const InboxGeom &ib, int row)
+{
+    return base + (size_t)row * ib.inbox_ld;
+}
+__device__ __forceinline__ double *inbox_col(double *base, const InboxGeom &ib, int col)
+{
+    return base + (size_t)4 * ib.inbox_ld + (size_t)col * ib.col_ld;
+}
+
 // ---- generic halo, step 1: my physical edge values go to whoever holds them as ghosts -------
-// E-W: column 1 -> east ghost of the west neighbour, column nxl -> west ghost of the east
-// neighbour (rows 1..ny).  Tripole: rows ny-1, ny of every physical column go to the inbox of
-// the rank(s) whose columns fold onto it.  ioff = 0 for center fields (source nx+1-ig),
-// 1 for NEcorner fields (source nx-ig) (serial/ice_boundary.F90:803-812,874-877).
+// E-W: column 1 -> east-ghost inbox column of the west neighbour, column nxl -> west-ghost inbox
+// column of the east neighbour (rows 1..ny).  Tripole: rows ny-1, ny of every physical column go
+// to the inbox rows of the rank(s) whose columns fold onto it.  ioff = 0 for center fields
+// (source nx+1-ig), 1 for NEcorner fields (source nx-ig) (serial/ice_boundary.F90:803-812,874-877).
 struct PushArgs {
     Geom g;
+    InboxGeom ib;
     const double *plane;
-    double *planeW, *planeE;          // same plane on the neighbours (self if cyclic on 1 GPU)
-    double *inbox[kMaxRanks];
+    double *inbox[kMaxRanks];         // buffer of this operation on every rank (peer pointers)
+    int west, east;                   // neighbour ranks, -1 on a closed edge
     int ioff;
-    int inbox_row0;                   // first of the two inbox rows to use
+    int ew;                           // 0: skip the E-W columns (ice_HaloUpdate_stress)
 };
 
 __global__ void halo_push_kernel(const __grid_constant__ PushArgs a)
@@ -45,9 +68,10 @@ __global__ void halo_push_kernel(const __grid_constant__ PushArgs a)
     const Geom &g = a.g;
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t < g.ny) {
+        if (!a.ew) return;
         const int r = t + 1;
-        if (a.planeW) a.planeW[(size_t)r * g.ld + g.nxl + 1] = a.plane[(size_t)r * g.ld + 1];
-        if (a.planeE) a.planeE[(size_t)r * g.ld] = a.plane[(size_t)r * g.ld + g.nxl];
+        if (a.west >= 0) inbox_col(a.inbox[a.west], a.ib, 1)[r] = a.plane[(size_t)r * g.ld + 1];
+        if (a.east >= 0) inbox_col(a.inbox[a.east], a.ib, 0)[r] = a.plane[(size_t)r * g.ld + g.nxl];
     } else if (g.tripole && t < g.ny + g.nxl) {
         const int c = t - g.ny + 1;
         const int ig = g.lo + c;
@@ -57,19 +81,18 @@ __global__ void halo_push_kernel(const __grid_constant__ PushArgs a)
 #pragma unroll
         for (int rs = 0; rs < 2; ++rs) {
             const double v = a.plane[(size_t)(g.ny - 1 + rs) * g.ld + c];
-            const size_t row = (size_t)(a.inbox_row0 + rs) * g.inbox_ld;
-            a.inbox[tr][row + ct] = v;
-            if (ct == 1) a.inbox[(tr + g.nranks - 1) % g.nranks][row + g.nxl + 1] = v;
-            if (ct == g.nxl) a.inbox[(tr + 1) % g.nranks][row] = v;
+            inbox_row(a.inbox[tr], a.ib, rs)[ct] = v;
+            if (ct == 1) inbox_row(a.inbox[(tr + g.nranks - 1) % g.nranks], a.ib, rs)[g.nxl + 1] = v;
+            if (ct == g.nxl) inbox_row(a.inbox[(tr + 1) % g.nranks], a.ib, rs)[0] = v;
         }
     }
 }
 
-// ---- generic halo, step 2: ring pre-fill + tripole fold out of the inbox -----------------------
+// ---- generic halo, step 2: ring pre-fill, E-W ghosts and tripole fold out of my inbox -----------
 // loc 0 = center (ghost row only), 1 = NEcorner (top physical row averaged + ghost row).
 // sgn = +1 scalar, -1 vector.
-__global__ void halo_apply_kernel(double *plane, Geom g, const double *inbox, int inbox_row0,
-                                  int loc, double sgn, double fill, int west_closed, int east_closed)
+__global__ void halo_apply_kernel(double *plane, Geom g, InboxGeom ib, double *inbox, int loc,
+                                  double sgn, double fill, int west_closed, int east_closed)
 {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int nxb = g.nxl + 2;
@@ -77,38 +100,90 @@ __global__ void halo_apply_kernel(double *plane, Geom g, const double *inbox, in
         const int c = t;
         plane[c] = fill;                                           // south ghost row
         if (g.tripole) {
-            const double *in_below = inbox + (size_t)inbox_row0 * g.inbox_ld;
-            const double *in_top = in_below + g.inbox_ld;
-            if (loc == 0)
+            const double *in_below = inbox_row(inbox, ib, 0);
+            const double *in_top = inbox_row(inbox, ib, 1);
+            if (loc == 0) {
                 plane[(size_t)(g.ny + 1) * g.ld + c] = sgn * in_top[c];
-            else
-                fold_necorner_column(plane, g.ld, g.ny, c, glob_col(g, c), g.nx_global, in_below,
-                                     in_top, sgn);
+            } else {
+                double own;                                        // row ny before the fold
+                if (c == 0) own = west_closed ? fill : inbox_col(inbox, ib, 0)[g.ny];
+                else if (c == g.nxl + 1) own = east_closed ? fill : inbox_col(inbox, ib, 1)[g.ny];
+                else own = plane[(size_t)g.ny * g.ld + c];
+                fold_necorner_column(plane, g.ld, g.ny, c, glob_col(g, c), g.nx_global, own,
+                                     in_below[c], in_top[c], sgn);
+            }
         } else {
             plane[(size_t)(g.ny + 1) * g.ld + c] = fill;           // open / closed north
         }
     } else if (t < nxb + g.ny) {
         const int r = t - nxb + 1;
-        if (west_closed) plane[(size_t)r * g.ld] = fill;
-        if (east_closed) plane[(size_t)r * g.ld + g.nxl + 1] = fill;
+        if (g.tripole && loc == 1 && r == g.ny) return;            // written by the fold above
+        plane[(size_t)r * g.ld] = west_closed ? fill : inbox_col(inbox, ib, 0)[r];
+        plane[(size_t)r * g.ld + g.nxl + 1] = east_closed ? fill : inbox_col(inbox, ib, 1)[r];
     }
 }
 
 // ice_HaloUpdate_stress: ghost row of a1 <- mirrored top physical row of a2 (center, +1);
-// the closed south row (and closed E-W ghosts) get 0 (:3351-3353).  Inbox row = inbox_row0+1.
-__global__ void halo_stress_apply_kernel(double *a1, Geom g, const double *inbox, int inbox_row0,
+// the closed south row (and closed E-W ghosts) get 0 (:3351-3353).
+__global__ void halo_stress_apply_kernel(double *a1, Geom g, InboxGeom ib, double *inbox,
                                          int west_closed, int east_closed)
 {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int nxb = g.nxl + 2;
     if (t < nxb) {
         a1[t] = 0.0;
-        if (g.tripole) a1[(size_t)(g.ny + 1) * g.ld + t] = inbox[(size_t)(inbox_row0 + 1) * g.inbox_ld + t];
+        if (g.tripole) a1[(size_t)(g.ny + 1) * g.ld + t] = inbox_row(inbox, ib, 1)[t];
     } else if (t < nxb + g.ny + 2) {
         const int r = t - nxb;
         if (west_closed) a1[(size_t)r * g.ld] = 0.0;
         if (east_closed) a1[(size_t)r * g.ld + g.nxl + 1] = 0.0;
     }
+}
+
+// ---- cross-rank synchronisation (one rank per GPU; flags live in every rank's arena) ------------
+// signal: bump my epoch and store it into slot [my rank] of every peer's flag array.
+// wait:   spin until every peer's slot in MY flag array has reached my epoch.
+// Every rank executes the same sequence of halo operations, so epochs advance in lock step.
+struct SyncArgs {
+    int rank, nranks;
+    unsigned long long *epoch;                    // mine
+    unsigned long long *flags[kMaxRanks];         // flag arrays of all ranks (peer pointers)
+    int *error;                                   // mine; set on time-out
+    unsigned long long timeout_ns;
+};
+
+__global__ void halo_signal_kernel(const __grid_constant__ SyncArgs a)
+{
+    __shared__ unsigned long long e;
+    if (threadIdx.x == 0) { e = *a.epoch + 1; *a.epoch = e; }
+    __syncthreads();
+    __threadfence_system();
+    const int r = threadIdx.x;
+    if (r < a.nranks && r != a.rank) {
+        unsigned long long *p = a.flags[r] + a.rank;
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(e) : "memory");
+    }
+}
+
+__global__ void halo_wait_kernel(const __grid_constant__ SyncArgs a)
+{
+    const int r = threadIdx.x;
+    if (r < a.nranks && r != a.rank) {
+        const unsigned long long e = *(volatile unsigned long long *)a.epoch;
+        const unsigned long long *p = a.flags[a.rank] + r;
+        unsigned long long t0, t1, v;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+            if (v >= e) break;
+            if (*(volatile int *)a.error) break;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > a.timeout_ns) { *(volatile int *)a.error = 1; break; }
+            __nanosleep(200);
+        }
+    }
+    __syncthreads();
+    __threadfence_system();
 }
 
 // ---- evp_prep1 -------------------------------------------------------------------------------

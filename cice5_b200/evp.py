@@ -65,15 +65,20 @@ class Stats(C.Structure):
 
 
 EXPORTS = ("evp_gpu_init", "evp_gpu_set_grid", "evp_gpu_run", "evp_gpu_upload", "evp_gpu_compute",
-           "evp_gpu_download", "evp_gpu_get_stats", "evp_gpu_synchronize", "evp_gpu_peer_blob_size",
+           "evp_gpu_download", "evp_gpu_compute_group", "evp_gpu_get_stats", "evp_gpu_synchronize", "evp_gpu_peer_blob_size",
            "evp_gpu_get_peer_blob", "evp_gpu_set_peers", "evp_gpu_finalize", "evp_gpu_strerror",
            "evp_gpu_last_cuda_error", "evp_gpu_device_count")
 
 _libs: dict = {}
 
 
-def load_library(strict: bool = False):
-    """dlopen the in-tree CUDA library (building it if nvcc is here and it is stale)."""
+def load_library(strict: bool = True):
+    """dlopen the in-tree CUDA library (building it if nvcc is here and it is stale).
+
+    strict=True (the product default) is the build without FMA contraction: it evaluates the
+    reference's IEEE operations one by one and is bitwise equal to the CPU oracle.  strict=False
+    is the same source with contraction on, kept for comparison only (EVP at ndte=120 amplifies
+    round-off on some grids, so a contracted build cannot promise 1e-10 there)."""
     if strict in _libs:
         return _libs[strict]
     path = _build.lib_path(strict)
@@ -116,7 +121,7 @@ class EvpGpu:
                  ew_cyclic=True, ns_boundary="open", grid_tripole=False, tilt_mode=0,
                  strength_masked=0, cosw=1.0, sinw=0.0, rhow=1026.0, rhoi=917.0, rhos=330.0,
                  gravit=9.80616, a_min=1.0e-3, m_min=1.0e-2, kdyn=1, revised_evp=False,
-                 use_cuda_graph=False, strict=False):
+                 use_cuda_graph=False, strict=True):
         self.lib = load_library(strict)
         ns = {"open": 0, "closed": 1, "tripole": 2}[ns_boundary]
         if nx_global % nranks:
@@ -232,11 +237,17 @@ class EvpGpu:
             pass
 
 
+def compute_group(solvers: list, dt: float):
+    """evp_gpu_compute_group: all ranks of one decomposition driven from this thread."""
+    arr = (C.c_void_p * len(solvers))(*[e._h for e in solvers])
+    solvers[0]._check(solvers[0].lib.evp_gpu_compute_group(arr, len(solvers), C.c_double(dt)))
+
+
 def device_count() -> int:
     return load_library().evp_gpu_device_count()
 
 
-def run_case(case, strict=False, **kw):
+def run_case(case, strict=True, **kw):
     """One evp(dt) call on a fixtures.Case through the C ABI (single GPU). Returns Stats."""
     e = EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=strict, **kw)
     try:
@@ -245,3 +256,46 @@ def run_case(case, strict=False, **kw):
         return e.stats()
     finally:
         e.close()
+
+
+class EvpGroup:
+    """All x-slabs of one decomposition driven from one process (one device): the host-side mirror
+    of `nranks` tasks each calling evp(dt) on its own block.  Global-with-ghost arrays in and out."""
+
+    def __init__(self, dom, ndte, dt_init, nranks, device=0, **kw):
+        from . import fixtures as fx
+        self._fx = fx
+        self.n = nranks
+        self.ranks = [EvpGpu.for_domain(dom, ndte, dt_init, rank=r, nranks=nranks, device=device, **kw)
+                      for r in range(nranks)]
+        blobs = [e.peer_blob() for e in self.ranks]
+        for e in self.ranks:
+            e.set_peers(blobs)
+
+    def _slabs(self, d, r):
+        return {k: self._fx.slab(v, r, self.n) for k, v in d.items() if v is not None}
+
+    def set_grid(self, f):
+        names = GRID_R8 + ("tmask", "umask")
+        for r, e in enumerate(self.ranks):
+            e.set_grid(self._slabs({k: f[k] for k in names}, r))
+
+    def evp(self, dt, inp, io, out):
+        parts = []
+        for r, e in enumerate(self.ranks):
+            si, sio, so = self._slabs(inp, r), self._slabs(io, r), self._slabs(out, r)
+            parts.append((sio, so))
+            e.upload(si, sio)
+        compute_group(self.ranks, dt)
+        for e, (sio, so) in zip(self.ranks, parts):
+            e.download(sio, so)
+        for k in io:
+            io[k][...] = self._fx.unslab([p[0][k] for p in parts])
+        for k in out:
+            if out[k] is not None:
+                out[k][...] = self._fx.unslab([p[1][k] for p in parts])
+        return [e.stats() for e in self.ranks]
+
+    def close(self):
+        for e in self.ranks:
+            e.close()

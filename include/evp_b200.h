@@ -113,6 +113,10 @@ int evp_gpu_upload(evp_handle_t *h, const evp_in_t *in, const evp_inout_t *io);
 int evp_gpu_compute(evp_handle_t *h, double dt);
 int evp_gpu_download(evp_handle_t *h, evp_inout_t *io, evp_out_t *out);
 
+/* Several ranks driven by one host thread (handles of ranks 0..n-1 on ONE device, e.g. tests with
+ * fewer GPUs than ranks): steps are interleaved on one stream so that no kernel ever waits. */
+int evp_gpu_compute_group(evp_handle_t **handles, int n, double dt);
+
 int evp_gpu_get_stats(evp_handle_t *h, evp_stats_t *st);
 int evp_gpu_synchronize(evp_handle_t *h);
 

@@ -1,0 +1,53 @@
+"""x-slab decomposition (one block per rank, NVLink-style inbox halos) on ONE device: all ranks are
+driven through evp_gpu_compute_group, which interleaves their steps on one stream.  Results must
+be BITWISE equal to the single-block oracle (the reference guarantees decomposition independence,
+cicedoc.tex:4601-4603)."""
+import numpy as np
+import pytest
+
+from cice5_b200 import evp, fixtures as fx
+from tests.util import clone_case, compare_cases
+from tests.test_gpu_parity import OUT_CHECK, _oracle, _small_tripole
+
+pytestmark = pytest.mark.gpu
+
+
+def _run_group(case, nranks, calls=1, **kw):
+    got = clone_case(case)
+    g = evp.EvpGroup(case.dom, case.ndte, case.dt, nranks, strict=True, **kw)
+    try:
+        g.set_grid(case.grid.f)
+        for _ in range(calls):
+            got.out = fx.zeroed_outputs(case.dom)
+            st = g.evp(case.dt, got.inp, got.io, got.out)
+    finally:
+        g.close()
+    return got, st
+
+
+@pytest.mark.parametrize("nx,ny,nranks", [(96, 40, 2), (96, 40, 4), (96, 40, 8), (124, 33, 4)])
+def test_small_tripole_group_bitwise(nx, ny, nranks):
+    case = fx.make_case(_small_tripole(nx, ny), "full", ndte=12, dt=3600.0)
+    ref = _oracle(case)
+    got, _ = _run_group(case, nranks)
+    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+
+
+@pytest.mark.parametrize("grid,nranks", [("gx3", 2), ("gx3", 5), ("tp1", 2), ("tp1", 8)])
+def test_named_grids_group_bitwise(grid, nranks):
+    case = fx.make_case(grid, "caps", ndte=120)
+    ref = _oracle(case)
+    got, st = _run_group(case, nranks)
+    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+    assert sum(s.active_u_cells for s in st) == int(ref.io["iceumask"][1:-1, 1:-1].sum())
+
+
+def test_group_two_calls_odd_ndte():
+    case = fx.make_case(_small_tripole(96, 40), "full", ndte=5, dt=3600.0)
+    ref = clone_case(case)
+    from oracle import oracle as orc
+    for _ in range(2):
+        ref.out = fx.zeroed_outputs(case.dom)
+        orc.run_case(ref)
+    got, _ = _run_group(case, 4, calls=2)
+    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
