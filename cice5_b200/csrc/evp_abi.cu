@@ -473,7 +473,13 @@ void fill_loop_args(const evp_handle *h, int from_parity, int inbox_buf, LoopArg
     const Geom &g = h->g;
     memset(&a, 0, sizeof(a));
     a.nxl = g.nxl; a.ny = g.ny; a.ld = g.ld; a.ldm = h->ldm;
-    a.rows_per_chunk = 32;
+    {   // rows marched by one warp: long chunks amortise the redundant north row on big grids,
+        // short chunks give the small (L2-resident, latency-bound) grids enough warps
+        const long long strips = (g.nxl + kUColsPerWarp - 1) / kUColsPerWarp;
+        const long long want_warps = 148LL * 16 * 2;
+        long long rpc = (strips * g.ny + want_warps - 1) / want_warps;
+        a.rows_per_chunk = (int)(rpc < 2 ? 2 : (rpc > 32 ? 32 : rpc));
+    }
     a.nx_global = g.nx_global; a.lo = g.lo; a.nranks = g.nranks; a.rank = g.rank; a.tripole = g.tripole;
     a.inbox_ld = g.inbox_ld;
     a.mask = h->mask();
