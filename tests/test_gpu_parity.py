@@ -172,3 +172,17 @@ def test_cuda_graph_loop_bitwise(ndte):
     finally:
         e.close()
     compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+
+
+@pytest.mark.parametrize("name,grid", [("gx3_full", "gx3"), ("tp62x40_full", None)])
+def test_against_committed_golden_vectors(name, grid):
+    """CUDA path vs tests/golden/*.npz (oracle outputs committed with their generating script)."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", f"{name}_ndte120_oracle.npz"))
+    g = fx.make_grid(grid) if grid else _small_tripole(62, 40)
+    got = fx.make_case(g, "full", ndte=120, dt=3600.0)
+    evp.run_case(got, strict=True)
+    for k in z.files:
+        grp, f = k.split("_", 1)
+        a = getattr(got, grp if grp == "io" else "out")[f]
+        assert np.array_equal(phys(a), phys(z[k])), k

@@ -1,0 +1,140 @@
+"""The CPU oracle against (a) an independent numpy restatement written from the Fortran, (b) the
+invariants the reference guarantees, (c) its own committed golden vectors.  PARITY UNPINNED: the
+reference ships no golden vectors for this path."""
+import os
+
+import numpy as np
+import pytest
+
+from cice5_b200 import fixtures as fx
+from oracle import oracle as orc, evp_numpy
+from tests.util import clone_case, compare_cases, phys
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _run(case, **kw):
+    c = clone_case(case)
+    orc.run_case(c, **kw)
+    return c
+
+
+@pytest.mark.parametrize("grid,scen,kw", [
+    ("gx3", "full", {}),
+    ("gx3", "caps", dict(cosw=0.9, sinw=float(np.sqrt(1 - 0.81)), tilt_mode=1, strength_masked=1)),
+    ("tp", "full", {}), ("tp", "caps", dict(strength_masked=1))])
+def test_c_oracle_equals_numpy_restatement_bitwise(grid, scen, kw):
+    g = fx.synthetic_tripole(62, 40) if grid == "tp" else fx.make_grid(grid)
+    case = fx.make_case(g, scen, ndte=15, dt=3600.0)
+    a = _run(case, **kw)
+    b = clone_case(case)
+    nt, nu = evp_numpy.evp(b, **kw)
+    compare_cases(b, a, bitwise=True)
+    assert nu == int(phys(a.io["iceumask"]).sum())
+
+
+@pytest.mark.parametrize("grid,slabs", [("gx3", (2, 4, 5)), ("tp", (2, 4, 8))])
+def test_decomposition_independence_bitwise(grid, slabs):
+    """cicedoc.tex:4601-4603: results do not depend on the block decomposition."""
+    g = fx.synthetic_tripole(96, 40) if grid == "tp" else fx.make_grid(grid)
+    case = fx.make_case(g, "full", ndte=30, dt=3600.0)
+    ref = _run(case, nslabs=1)
+    for n in slabs:
+        compare_cases(_run(case, nslabs=n), ref, bitwise=True)
+
+
+def test_tripole_seam_antisymmetry():
+    """After evp the top U row is antisymmetric under i -> nx - i."""
+    g = fx.synthetic_tripole(96, 40)
+    c = _run(fx.make_case(g, "full", ndte=60, dt=3600.0))
+    nx, ny = g.dom.nx, g.dom.ny
+    for f in ("uvel", "vvel"):
+        top = c.io[f][ny, 1:nx + 1]                    # ig = 1..nx
+        i = np.arange(1, nx // 2)
+        assert np.array_equal(top[i - 1], -top[nx - i - 1])
+        assert np.abs(top).max() > 0.0
+        # ghost row = minus the mirrored row ny-1
+        ghost, below = c.io[f][ny + 1, 1:nx + 1], c.io[f][ny - 1, 1:nx + 1]
+        ig = np.arange(1, nx)
+        assert np.array_equal(ghost[ig - 1], -below[nx - ig - 1])
+
+
+def test_zero_forcing_zero_state_stays_at_rest():
+    case = fx.make_case("gx3", "full", ndte=20)
+    for k in ("strairxT", "strairyT", "uocn", "vocn"):
+        case.inp[k][...] = 0.0
+    c = _run(case)
+    for k in ("uvel", "vvel") + fx.STRESS_FIELDS:
+        assert np.abs(phys(c.io[k])).max() == 0.0
+
+
+def test_free_drift_matches_closed_form_solve():
+    """strength = 0 => no internal stress; each subcycle is the pointwise 2x2 solve of stepu
+    (ice_dyn_shared.F90:708-737) -- iterated here in numpy from the oracle's own prep outputs."""
+    case = fx.make_case("gx3", "full", ndte=25)
+    case.inp["strength"][...] = 0.0
+    c = _run(case)
+    ice = c.io["iceumask"] > 0
+    P = (slice(1, -1), slice(1, -1))
+    g, inp = case.grid.f, case.inp
+    tmass = c.out["tmass"]
+    umass = evp_numpy.to_ugrid(tmass, g["tarea"], g["uarea"])
+    aiu = evp_numpy.to_ugrid(inp["aice_init"], g["tarea"], g["uarea"])
+    fm = c.io["fm"]
+    forcex = c.out["strairx"] + c.out["strtltx"]
+    forcey = c.out["strairy"] + c.out["strtlty"]
+    u, v = c.out["uvel_init"].copy(), c.out["vvel_init"].copy()
+    brlx = evp_numpy.evp_parameters(case.dt, case.ndte)[2]
+    for _ in range(case.ndte):
+        vrel = aiu * fx.RHOW * inp["Cw"] * np.sqrt((inp["uocn"] - u) * (inp["uocn"] - u) + (inp["vocn"] - v) * (inp["vocn"] - v))
+        cca = brlx * (umass / case.dt) + vrel * 1.0
+        ccb = fm + np.copysign(1.0, fm) * vrel * 0.0
+        cc1 = 0.0 + forcex + vrel * inp["uocn"] + (umass / case.dt) * (brlx * u)
+        cc2 = 0.0 + forcey + vrel * inp["vocn"] + (umass / case.dt) * (brlx * v)
+        ab2 = cca * cca + ccb * ccb
+        with np.errstate(divide="ignore", invalid="ignore"):
+            un, vn = (cca * cc1 + ccb * cc2) / ab2, (cca * cc2 - ccb * cc1) / ab2
+        u, v = np.where(ice, un, u), np.where(ice, vn, v)
+    assert np.allclose(u[P], c.io["uvel"][P], rtol=1e-12, atol=1e-15)
+    assert np.allclose(v[P], c.io["vvel"][P], rtol=1e-12, atol=1e-15)
+    assert np.abs(phys(c.io["stressp_1"])).max() == 0.0
+
+
+@pytest.mark.parametrize("tripole", [True, False])
+@pytest.mark.parametrize("loc,kind", [(0, 0), (0, 1), (1, 0), (1, 1)])
+def test_halo_update_c_vs_numpy(tripole, loc, kind):
+    """ice_HaloUpdate (center / NEcorner x scalar / vector), C oracle with 1..4 blocks against the
+    numpy implementation in fixtures.halo_update."""
+    g = fx.synthetic_tripole(48, 20) if tripole else fx.synthetic_displaced(48, 20)
+    rng = np.random.default_rng(3)
+    a = rng.standard_normal((22, 50))
+    ref = fx.halo_update(g.dom, a.copy(), loc, kind, 0.0)
+    for n in (1, 2, 3, 4):
+        got = orc.halo_r8(g.dom, a.copy(), loc, kind, 0.0, nslabs=n)
+        assert np.array_equal(got, ref), n
+
+
+def test_principal_stress_diagnostic():
+    rng = np.random.default_rng(0)
+    sp, sm, s12 = (rng.standard_normal(100) for _ in range(3))
+    prs = np.abs(rng.standard_normal(100)); prs[:5] = 0.0
+    s1, s2 = orc.principal_stress(sp, sm, s12, prs)
+    assert np.all(s1[:5] == 1e30) and np.all(s2[:5] == 1e30)
+    r = np.sqrt(sm * sm + 4.0 * (s12 * s12))
+    assert np.array_equal(s1[5:], ((0.5 * (sp + r)) / prs)[5:])
+
+
+@pytest.mark.parametrize("name,grid", [("gx3_full", "gx3"), ("tp62x40_full", None)])
+def test_oracle_reproduces_committed_golden_vectors(name, grid):
+    z = np.load(os.path.join(GOLD, f"{name}_ndte120_oracle.npz"))
+    g = fx.make_grid(grid) if grid else fx.synthetic_tripole(62, 40)
+    c = _run(fx.make_case(g, "full", ndte=120, dt=3600.0), nslabs=2)
+    for k in z.files:
+        grp, f = k.split("_", 1)
+        assert np.array_equal(getattr(c, grp if grp == "io" else "out")[f], z[k]), k
+
+
+def test_umax_sanity():
+    """check_umax (ice_diagnostics.F90:340-364): |u| stays below umax_stab = 1 m/s."""
+    c = _run(fx.make_case("gx3", "full", ndte=120))
+    assert np.hypot(c.io["uvel"], c.io["vvel"]).max() < 1.0
