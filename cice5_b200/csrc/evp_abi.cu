@@ -16,6 +16,7 @@
 
 #include "evp_kernels.cuh"
 #include "evp_prep.cuh"
+#include "evp_subcycle_tma.cuh"
 
 using namespace evp;
 
@@ -35,25 +36,25 @@ thread_local char g_cuda_err[512] = "";
 
 // ---- plane directory ----------------------------------------------------------------------
 enum Plane {
-    // grid (evp_grid_t order)
-    G_DXT, G_DYT, G_DXHY, G_DYHX, G_CXP, G_CYP, G_CXM, G_CYM, G_TAREA, G_UAREA, G_TAREAR, G_UAREAR,
-    G_TINYAREA, G_FCOR,
-    // per-call inputs (evp_in_t order)
-    I_AICE, I_VICE, I_VSNO, I_AICE_INIT, I_STRAIRXT, I_STRAIRYT, I_UOCN, I_VOCN, I_SSTLTX, I_SSTLTY,
-    I_CW, I_STRENGTH,
-    // dynamic state, ping-pong A / B
-    S_UA, S_VA, S_UB, S_VB,
-    S_STRA, S_STRA_END = S_STRA + 11,
-    S_STRB, S_STRB_END = S_STRB + 11,
-    S_FM,
+    // T-cell coefficients of the subcycle kernel: contiguous, one TMA box of depth 10 (11 with
+    // tarear on the last subcycle)
+    G_DXT, G_DYT, G_DXHY, G_DYHX, G_CXP, G_CYP, G_CXM, G_CYM, G_TINYAREA, W_STRENGTH, G_TAREAR,
+    // U-cell coefficients of the subcycle kernel: contiguous, one TMA box of depth 11
+    W_AIU, I_CW, I_UOCN, I_VOCN, W_WATERX, W_WATERY, W_FORCEX, W_FORCEY, W_UMASSDTI, S_FM, G_UAREAR,
+    // dynamic state, ping-pong copies A / B: u, v, stressp_1..4, stressm_1..4, stress12_1..4
+    S_UA, S_VA, S_STRA, S_STRA_END = S_STRA + 11,
+    S_UB, S_VB, S_STRB, S_STRB_END = S_STRB + 11,
+    // remaining grid planes and per-call inputs
+    G_TAREA, G_UAREA, G_FCOR,
+    I_AICE, I_VICE, I_VSNO, I_AICE_INIT, I_STRAIRXT, I_STRAIRYT, I_SSTLTX, I_SSTLTY, I_STRENGTH,
     // evp locals (ice_dyn_evp.F90:120-137)
-    W_TMASS, W_UMASS, W_AIU, W_UMASSDTI, W_WATERX, W_WATERY, W_FORCEX, W_FORCEY, W_STRENGTH,
-    W_ICETMASK, W_1, W_2,
-    // outputs (evp_out_t order, first 17)
+    W_TMASS, W_UMASS, W_ICETMASK, W_1, W_2,
+    // outputs (evp_out_t order, first 17; contiguous: zeroed with one memset)
     O_STRAIRX, O_STRAIRY, O_STRTLTX, O_STRTLTY, O_STROCNX, O_STROCNY, O_STRINTX, O_STRINTY,
     O_STROCNXT, O_STROCNYT, O_DIVU, O_SHEAR, O_RDGCONV, O_RDGSHEAR, O_PRSSIG, O_UVELINIT, O_VVELINIT,
     NPLANES
 };
+constexpr int kTGroup = G_DXT, kUGroup = W_AIU;
 
 struct PeerBlob {                 // exchanged between the tasks of one node
     cudaIpcMemHandle_t arena;
@@ -90,6 +91,9 @@ struct evp_handle {
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaGraphExec_t loop_graph[2] = {nullptr, nullptr};   // per starting ping-pong parity
     int h_error = 0;
+    bool use_tma = false;         // subcycle kernel v2 (TMA ring) instead of v1 (register sweep)
+    int sm_count = 148;
+    CUtensorMap mapS, mapT10, mapT11, mapU, mapM;
     evp_stats_t stats;
     unsigned long long h_counts[2];
 
@@ -145,6 +149,54 @@ void set_evp_parameters(const evp_config_t &c, Consts &k)
     k.brlx = c.dt_init * dtei;
     k.denom1 = c1 / (c1 + k.arlx1i);
     k.cosw = c.cosw; k.sinw = c.sinw; k.rhow = c.rhow;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// Tensor maps of the subcycle kernel v2: ONE 3-D tensor (column, row, plane) over the whole plane
+// arena, boxes of 128 columns x 1 row x depth planes; a 2-D byte tensor for the activity mask.
+int make_tensor_maps(evp_handle *h)
+{
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || !fn || qres != cudaDriverEntryPointSuccess) {
+        snprintf(g_cuda_err, sizeof(g_cuda_err), "cuTensorMapEncodeTiled is not available from this driver");
+        return EVP_ERR_CUDA;
+    }
+    EncodeTiledFn enc = reinterpret_cast<EncodeTiledFn>(fn);
+    const cuuint64_t dims[3] = {(cuuint64_t)h->ld, (cuuint64_t)h->nyb, (cuuint64_t)NPLANES};
+    const cuuint64_t strides[2] = {(cuuint64_t)h->ld * 8, (cuuint64_t)h->plane_elems * 8};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    struct { CUtensorMap *m; int depth; } maps[4] = {{&h->mapS, kStateDepth}, {&h->mapT10, kTDepth - 1},
+                                                     {&h->mapT11, kTDepth}, {&h->mapU, kUDepth}};
+    for (auto &mm : maps) {
+        const cuuint32_t box[3] = {(cuuint32_t)kTmaBoxW, 1, (cuuint32_t)mm.depth};
+        CUresult r = enc(mm.m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, h->plane(0), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) {
+            snprintf(g_cuda_err, sizeof(g_cuda_err), "cuTensorMapEncodeTiled(depth %d) failed: %d", mm.depth, (int)r);
+            return EVP_ERR_CUDA;
+        }
+    }
+    const cuuint64_t mdims[2] = {(cuuint64_t)h->ldm, (cuuint64_t)h->nyb};
+    const cuuint64_t mstr[1] = {(cuuint64_t)h->ldm};
+    const cuuint32_t mbox[2] = {(cuuint32_t)kMaskBoxW, 1};
+    CUresult r = enc(&h->mapM, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, h->mask(), mdims, mstr, mbox, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        snprintf(g_cuda_err, sizeof(g_cuda_err), "cuTensorMapEncodeTiled(mask) failed: %d", (int)r);
+        return EVP_ERR_CUDA;
+    }
+    CK(cudaFuncSetAttribute(evp_subcycle_tma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            kTmaStages * kStageBytes));
+    CK(cudaFuncSetAttribute(evp_subcycle_tma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            kTmaStages * kStageBytes));
+    return EVP_OK;
 }
 
 dim3 grid2d(const evp_handle *h, int bx = 128) { return dim3((h->nxb + bx - 1) / bx, h->nyb, 1); }
@@ -208,7 +260,8 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
     h->cfg = *cfg;
     set_evp_parameters(*cfg, h->k);
     h->nxb = cfg->nx_block; h->nyb = cfg->ny_block;
-    h->ld = h->nxb; h->ldm = h->nxb;
+    h->ld = (int)align_up((size_t)h->nxb, 16);   // rows start on 128-byte boundaries (TMA, sectors)
+    h->ldm = h->ld;
     h->plane_elems = (size_t)h->ld * h->nyb;
     Geom &g = h->g;
     g.nxl = h->nxb - 2; g.ny = h->nyb - 2; g.ld = h->ld; g.nx_global = cfg->nx_global;
@@ -237,6 +290,14 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
     h->stream = h->own_stream;
     for (auto &ev : h->ev) CK(cudaEventCreate(&ev));
     memset(&h->stats, 0, sizeof(h->stats));
+    {
+        const char *kv = getenv("EVP_B200_KERNEL");          // "tma" (default) | "sweep"
+        h->use_tma = !(kv && strcmp(kv, "sweep") == 0);
+        cudaDeviceProp prop;
+        CK(cudaGetDeviceProperties(&prop, cfg->device));
+        h->sm_count = prop.multiProcessorCount;
+        if (h->use_tma) { int rc = make_tensor_maps(h); if (rc != EVP_OK) { evp_gpu_finalize(h); return rc; } }
+    }
     h->peer_arena[cfg->rank] = h->arena;
     h->peers_set = cfg->nranks == 1;
     *out = h;
@@ -269,13 +330,29 @@ int evp_gpu_synchronize(evp_handle_t *h)
 static int h2d(evp_handle *h, int p, const double *src)
 {
     if (!src) return EVP_ERR_ARG;
-    CK(cudaMemcpyAsync(h->plane(p), src, h->plane_elems * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpy2DAsync(h->plane(p), (size_t)h->ld * sizeof(double), src, (size_t)h->nxb * sizeof(double),
+                         (size_t)h->nxb * sizeof(double), h->nyb, cudaMemcpyHostToDevice, h->stream));
+    return EVP_OK;
+}
+static int h2d_i(evp_handle *h, int p, const int *src)
+{
+    if (!src) return EVP_ERR_ARG;
+    CK(cudaMemcpy2DAsync(h->iplane(p), (size_t)h->ld * sizeof(int), src, (size_t)h->nxb * sizeof(int),
+                         (size_t)h->nxb * sizeof(int), h->nyb, cudaMemcpyHostToDevice, h->stream));
+    return EVP_OK;
+}
+static int d2h_i(evp_handle *h, int p, int *dst)
+{
+    if (!dst) return EVP_OK;
+    CK(cudaMemcpy2DAsync(dst, (size_t)h->nxb * sizeof(int), h->iplane(p), (size_t)h->ld * sizeof(int),
+                         (size_t)h->nxb * sizeof(int), h->nyb, cudaMemcpyDeviceToHost, h->stream));
     return EVP_OK;
 }
 static int d2h(evp_handle *h, int p, double *dst)
 {
     if (!dst) return EVP_OK;
-    CK(cudaMemcpyAsync(dst, h->plane(p), h->plane_elems * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpy2DAsync(dst, (size_t)h->nxb * sizeof(double), h->plane(p), (size_t)h->ld * sizeof(double),
+                         (size_t)h->nxb * sizeof(double), h->nyb, cudaMemcpyDeviceToHost, h->stream));
     return EVP_OK;
 }
 #define TRY(x) do { int rc_ = (x); if (rc_ != EVP_OK) return rc_; } while (0)
@@ -286,10 +363,11 @@ int evp_gpu_set_grid(evp_handle_t *h, const evp_grid_t *gr)
     CK(cudaSetDevice(h->cfg.device));
     const double *src[14] = {gr->dxt, gr->dyt, gr->dxhy, gr->dyhx, gr->cxp, gr->cyp, gr->cxm, gr->cym,
                              gr->tarea, gr->uarea, gr->tarear, gr->uarear, gr->tinyarea, gr->fcor};
-    for (int p = 0; p < 14; ++p) TRY(h2d(h, G_DXT + p, src[p]));
-    if (!gr->tmask || !gr->umask) return EVP_ERR_ARG;
-    CK(cudaMemcpyAsync(h->iplane(0), gr->tmask, h->plane_elems * sizeof(int), cudaMemcpyHostToDevice, h->stream));
-    CK(cudaMemcpyAsync(h->iplane(1), gr->umask, h->plane_elems * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    const int dstp[14] = {G_DXT, G_DYT, G_DXHY, G_DYHX, G_CXP, G_CYP, G_CXM, G_CYM,
+                          G_TAREA, G_UAREA, G_TAREAR, G_UAREAR, G_TINYAREA, G_FCOR};
+    for (int p = 0; p < 14; ++p) TRY(h2d(h, dstp[p], src[p]));
+    TRY(h2d_i(h, 0, gr->tmask));
+    TRY(h2d_i(h, 1, gr->umask));
     CK(cudaStreamSynchronize(h->stream));
     h->grid_set = true;
     return EVP_OK;
@@ -302,7 +380,9 @@ int evp_gpu_upload(evp_handle_t *h, const evp_in_t *in, const evp_inout_t *io)
     CK(cudaSetDevice(h->cfg.device));
     const double *src[12] = {in->aice, in->vice, in->vsno, in->aice_init, in->strairxT, in->strairyT,
                              in->uocn, in->vocn, in->ss_tltx, in->ss_tlty, in->Cdn_ocn, in->strength};
-    for (int p = 0; p < 12; ++p) TRY(h2d(h, I_AICE + p, src[p]));
+    const int dstp[12] = {I_AICE, I_VICE, I_VSNO, I_AICE_INIT, I_STRAIRXT, I_STRAIRYT,
+                          I_UOCN, I_VOCN, I_SSTLTX, I_SSTLTY, I_CW, I_STRENGTH};
+    for (int p = 0; p < 12; ++p) TRY(h2d(h, dstp[p], src[p]));
     // dynamic state always lands in copy A
     TRY(h2d(h, S_UA, io->uvel));
     TRY(h2d(h, S_VA, io->vvel));
@@ -311,8 +391,7 @@ int evp_gpu_upload(evp_handle_t *h, const evp_in_t *in, const evp_inout_t *io)
         TRY(h2d(h, S_STRA + 4 + c, io->stressm[c]));
         TRY(h2d(h, S_STRA + 8 + c, io->stress12[c]));
     }
-    if (!io->iceumask) return EVP_ERR_ARG;
-    CK(cudaMemcpyAsync(h->iplane(2), io->iceumask, h->plane_elems * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    TRY(h2d_i(h, 2, io->iceumask));
     h->parity = 0;
     h->uploaded = true;
     return EVP_OK;
@@ -334,8 +413,7 @@ int evp_gpu_download(evp_handle_t *h, evp_inout_t *io, evp_out_t *out)
             TRY(d2h(h, S + 8 + c, io->stress12[c]));
         }
         TRY(d2h(h, S_FM, io->fm));
-        if (io->iceumask)
-            CK(cudaMemcpyAsync(io->iceumask, h->iplane(2), h->plane_elems * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        TRY(d2h_i(h, 2, io->iceumask));
     }
     if (out) {
         double *dst[17] = {out->strairx, out->strairy, out->strtltx, out->strtlty, out->strocnx, out->strocny,
@@ -344,8 +422,7 @@ int evp_gpu_download(evp_handle_t *h, evp_inout_t *io, evp_out_t *out)
         for (int p = 0; p < 17; ++p) TRY(d2h(h, O_STRAIRX + p, dst[p]));
         TRY(d2h(h, W_TMASS, out->tmass));
         TRY(d2h(h, W_STRENGTH, out->strength));
-        if (out->icetmask)
-            CK(cudaMemcpyAsync(out->icetmask, h->iplane(3), h->plane_elems * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        TRY(d2h_i(h, 3, out->icetmask));
     }
     CK(cudaStreamSynchronize(h->stream));
     return EVP_OK;
@@ -515,6 +592,36 @@ void add_subcycle(Builder &B, int from_parity, bool last)
         const Geom &g = h->g;
         LoopArgs a;
         fill_loop_args(h, from_parity, buf, a);
+        if (h->use_tma) {
+            // v2: persistent CTAs (2 per SM) fed by a TMA ring; work item = (strip of 124 U columns,
+            // chunk of rows).  Chunk height: fewest rounds x (rows + pipeline fill) over the CTAs.
+            TmaArgs t;
+            t.a = a;
+            t.plane_state = from_parity ? S_UB : S_UA;
+            t.plane_t = kTGroup; t.plane_u = kUGroup;
+            t.strips = (g.nxl + kTmaUCols - 1) / kTmaUCols;
+            const int slots = 2 * h->sm_count;
+            int best = 4; double best_cost = 1e300;
+            for (int rpc = 4; rpc <= 64; ++rpc) {
+                const long long items = (long long)t.strips * ((g.ny + rpc - 1) / rpc);
+                const long long G = items < slots ? items : slots;
+                const double cost = (double)((items + G - 1) / G) * (rpc + 1.5);
+                if (cost < best_cost) { best_cost = cost; best = rpc; }
+            }
+            t.a.rows_per_chunk = best;
+            t.chunks = (g.ny + best - 1) / best;
+            t.items = t.strips * t.chunks;
+            const int grid = t.items < slots ? t.items : slots;
+            const size_t smem = (size_t)kTmaStages * kStageBytes;
+            if (last)
+                evp_subcycle_tma_kernel<true><<<grid, (kTmaConsumers + 1) * 32, smem, L.s()>>>(h->mapS, h->mapT11, h->mapU,
+                                                                                             h->mapM, t);
+            else
+                evp_subcycle_tma_kernel<false><<<grid, (kTmaConsumers + 1) * 32, smem, L.s()>>>(h->mapS, h->mapT10, h->mapU,
+                                                                                              h->mapM, t);
+            ++L.n;
+            return EVP_OK;
+        }
         const int strips = (g.nxl + kUColsPerWarp - 1) / kUColsPerWarp;
         dim3 grid((strips + kWarpsPerBlock - 1) / kWarpsPerBlock, (g.ny + a.rows_per_chunk - 1) / a.rows_per_chunk);
         if (last) evp_subcycle_kernel<true><<<grid, kWarpsPerBlock * 32, 0, L.s()>>>(a);

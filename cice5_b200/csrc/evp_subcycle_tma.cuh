@@ -1,0 +1,258 @@
+// evp_subcycle_tma.cuh -- fused subcycle kernel v2: persistent, warp-specialised, TMA-fed.
+//
+// Same arithmetic and the same warp-sweep as evp_subcycle_kernel (evp_kernels.cuh; reference
+// stress source/ice_dyn_evp.F90:618-847 and stepu source/ice_dyn_shared.F90:700-746), but the 36
+// input planes of a row are no longer loaded into registers by the computing warps.  A producer
+// warp streams them into a shared-memory ring with TMA (cp.async.bulk.tensor over ONE 3-D tensor
+// map of the whole plane arena: box = 128 columns x 1 row x k consecutive planes), completion is
+// signalled through mbarriers, and the consumer warps only see ~30-cycle shared-memory reads.
+// Bytes in flight per SM are set by the ring depth, not by how many warps fit at 128 registers.
+//
+// CTA = 4 consumer warps (31 U columns each -> 124 U columns, box column 0 = the west ghost of
+// the strip) + 1 producer warp.  Persistent: CTA b takes work items b, b + grid, ... ; an item is
+// (strip, row chunk).  Stage j of an item holds: state planes (u, v, 12 stresses) of row j,
+// T coefficients + activity mask of row j, U coefficients of row j-1.
+#pragma once
+#include <cuda.h>
+
+#include "evp_kernels.cuh"
+
+namespace evp {
+
+constexpr int kTmaConsumers = 4;
+constexpr int kTmaBoxW = 128;                                // doubles per box row
+constexpr int kTmaUCols = kTmaConsumers * kUColsPerWarp;     // 124
+constexpr int kTmaStages = 3;
+constexpr int kStateDepth = 14, kTDepth = 11, kUDepth = 11;
+constexpr int kMaskBoxW = kTmaBoxW + 16;     // the byte mask is fetched from a 16-byte aligned column (TMA
+                                             // needs 16-byte aligned box starts), up to 12 bytes early
+constexpr int kStageBytes = (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8 + 256;        // + mask row
+static_assert(kStageBytes % 128 == 0, "TMA destinations must stay 128-byte aligned");
+
+struct TmaArgs {
+    LoopArgs a;                  // geometry, constants, output / push pointers (inputs unused)
+    int plane_state;             // first plane of the OLD state copy
+    int plane_t, plane_u;        // first plane of the T / U coefficient groups
+    int strips, chunks, items;
+};
+
+__device__ __forceinline__ unsigned smem_u32(const void *p)
+{
+    return (unsigned)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(unsigned long long *b, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *b, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *b)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *b, unsigned parity)
+{
+    unsigned done;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(smem_u32(b)), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, unsigned long long *bar, int x,
+                                            int y, int z)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y), "r"(z)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, unsigned long long *bar, int x, int y)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y)
+        : "memory");
+}
+
+template <bool LAST>
+__global__ void __launch_bounds__((kTmaConsumers + 1) * 32, 2)
+evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_constant__ CUtensorMap mapT,
+                        const __grid_constant__ CUtensorMap mapU, const __grid_constant__ CUtensorMap mapM,
+                        const __grid_constant__ TmaArgs p)
+{
+    extern __shared__ __align__(1024) unsigned char ring[];
+    __shared__ unsigned long long full_bar[kTmaStages], empty_bar[kTmaStages];
+    const LoopArgs &a = p.a;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    constexpr int kTUsed = LAST ? kTDepth : kTDepth - 1;       // tarear only on the last subcycle
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < kTmaStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], kTmaConsumers); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+
+    int stage = 0;
+    unsigned phase = 0;
+
+    if (warp == kTmaConsumers) {
+        // ------------------------------ producer ------------------------------
+        if (lane == 0) {
+            for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
+                const int strip = item % p.strips, chunk = item / p.strips;
+                const int x0 = strip * kTmaUCols;                       // box column 0 = U column c0 - 1
+                const int r0 = 1 + chunk * a.rows_per_chunk;
+                const int rend = min(r0 + a.rows_per_chunk, a.ny + 1);
+                for (int j = r0 - 1; j <= rend; ++j) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1u);
+                    unsigned char *sb = ring + (size_t)stage * kStageBytes;
+                    unsigned bytes = kStateDepth * kTmaBoxW * 8;
+                    if (j >= r0) bytes += kTUsed * kTmaBoxW * 8 + kMaskBoxW;
+                    if (j > r0) bytes += kUDepth * kTmaBoxW * 8;
+                    mbar_expect_tx(&full_bar[stage], bytes);
+                    tma_load_3d(sb, &mapS, &full_bar[stage], x0, j, p.plane_state);
+                    if (j >= r0) {
+                        tma_load_3d(sb + kStateDepth * kTmaBoxW * 8, &mapT, &full_bar[stage], x0, j, p.plane_t);
+                        tma_load_2d(sb + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8, &mapM, &full_bar[stage],
+                                    x0 & ~15, j);
+                    }
+                    if (j > r0)
+                        tma_load_3d(sb + (kStateDepth + kTDepth) * kTmaBoxW * 8, &mapU, &full_bar[stage], x0, j - 1,
+                                    p.plane_u);
+                    if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
+                }
+            }
+        }
+        return;
+    }
+
+    // ------------------------------ consumers ------------------------------
+    const Consts &k = a.k;
+    const int ld = a.ld;
+    const int bi = 1 + warp * kUColsPerWarp + lane;                     // my column inside the box
+    for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
+        const int strip = item % p.strips, chunk = item / p.strips;
+        const int c = 1 + strip * kTmaUCols + warp * kUColsPerWarp + lane;   // T column (U column if lane < 31)
+        const bool warp_on = (c - lane) <= a.nxl;                       // warp-uniform
+        const int mshift = (strip * kTmaUCols) & 15;                    // mask box starts this many bytes early
+        const int r0 = 1 + chunk * a.rows_per_chunk;
+        const int rend = min(r0 + a.rows_per_chunk, a.ny + 1);
+        const bool tcol = c <= a.nxl + 1;
+        const bool ucol = lane < kUColsPerWarp && c <= a.nxl;
+        const bool tstore_col = tcol && (lane < kUColsPerWarp || c == a.nxl + 1);
+
+        // row r0-1: velocities only
+        double u_s, v_s, uw_s, vw_s;
+        {
+            mbar_wait(&full_bar[stage], phase);
+            const double *st = reinterpret_cast<const double *>(ring + (size_t)stage * kStageBytes);
+            u_s = st[bi]; v_s = st[kTmaBoxW + bi]; uw_s = st[bi - 1]; vw_s = st[kTmaBoxW + bi - 1];
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[stage]);
+            if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
+        }
+        double s1p = 0.0, s5p = 0.0, n2p = 0.0, n7p = 0.0;
+        unsigned mprev = 0;
+
+        for (int r = r0; r <= rend; ++r) {
+            mbar_wait(&full_bar[stage], phase);
+            const double *st = reinterpret_cast<const double *>(ring + (size_t)stage * kStageBytes);
+            const double *tc = st + kStateDepth * kTmaBoxW;
+            const double *uc = tc + kTDepth * kTmaBoxW;
+            const unsigned char *mk = reinterpret_cast<const unsigned char *>(uc + kUDepth * kTmaBoxW);
+            const double u_c = st[bi], v_c = st[kTmaBoxW + bi];
+            const double uw_c = st[bi - 1], vw_c = st[kTmaBoxW + bi - 1];
+            const unsigned m = (warp_on && tcol) ? mk[bi + mshift] : 0u;
+            const bool tact = (m & 1u) != 0;
+            const bool uact = warp_on && ucol && (mprev & 2u) && r > r0;
+            const bool any_t = __ballot_sync(0xffffffffu, tact) != 0u;
+            const bool any_u = __ballot_sync(0xffffffffu, uact) != 0u;
+            double s[12], tco[kTDepth], uco[kUDepth];
+            if (any_t) {
+#pragma unroll
+                for (int q = 0; q < 12; ++q) s[q] = st[(2 + q) * kTmaBoxW + bi];
+#pragma unroll
+                for (int q = 0; q < kTUsed; ++q) tco[q] = tc[q * kTmaBoxW + bi];
+            }
+            if (any_u) {
+#pragma unroll
+                for (int q = 0; q < kUDepth; ++q) uco[q] = uc[q * kTmaBoxW + bi];
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[stage]);              // slot free: everything is in registers
+            if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
+
+            const size_t idx = (size_t)r * ld + c;
+            double str[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+            if (tact) {
+                double divu, shear, rdg_conv, rdg_shear, prs_sig;
+                // tco: dxt dyt dxhy dyhx cxp cyp cxm cym tinyarea strength [tarear]
+                stress_cell<LAST>(k, u_c, uw_c, u_s, uw_s, v_c, vw_c, v_s, vw_s, tco[0], tco[1], tco[2], tco[3],
+                                  tco[4], tco[5], tco[6], tco[7], tco[8], tco[9], LAST ? tco[kTDepth - 1] : 0.0, s,
+                                  str, divu, shear, rdg_conv, rdg_shear, prs_sig);
+                if (tstore_col && (r < rend || r == a.ny + 1)) {
+#pragma unroll
+                    for (int q = 0; q < 12; ++q) a.s1[q][idx] = s[q];
+                    if (LAST) {
+                        a.divu[idx] = divu; a.shear[idx] = shear; a.rdg_conv[idx] = rdg_conv;
+                        a.rdg_shear[idx] = rdg_shear; a.prs_sig[idx] = prs_sig;
+                    }
+                }
+            }
+            const double e2 = shfl_down1(str[1]), e4 = shfl_down1(str[3]);
+            const double e7 = shfl_down1(str[6]), e8 = shfl_down1(str[7]);
+
+            if (r > r0 && warp_on) {                                    // stepu on U row r-1 (:700-746)
+                const size_t iu = idx - ld;
+                double unew = u_s, vnew = v_s;
+                if (uact) {
+                    // uco: aiu Cw uocn vocn waterx watery forcex forcey umassdti fm uarear
+                    const double uold = u_s, vold = v_s;
+                    const double du = uco[2] - uold, dv = uco[3] - vold;
+                    const double vrel = uco[0] * k.rhow * uco[1] * sqrt(du * du + dv * dv);
+                    const double taux = vrel * uco[4], tauy = vrel * uco[5];
+                    const double umdt = uco[8], fm = uco[9];
+                    const double cca = (k.brlx + k.revp) * umdt + vrel * k.cosw;
+                    const double ccb = fm + copysign(1.0, fm) * vrel * k.sinw;
+                    const double ab2 = cca * cca + ccb * ccb;
+                    const double uar = uco[10];
+                    const double strintx = uar * (s1p + n2p + str[2] + e4);
+                    const double strinty = uar * (s5p + str[5] + n7p + e8);
+                    const double cc1 = strintx + uco[6] + taux + umdt * (k.brlx * uold);
+                    const double cc2 = strinty + uco[7] + tauy + umdt * (k.brlx * vold);
+                    unew = (cca * cc1 + ccb * cc2) / ab2;
+                    vnew = (cca * cc2 - ccb * cc1) / ab2;
+                    if (LAST) { a.strintx[iu] = strintx; a.strinty[iu] = strinty; }
+                }
+                if (ucol) {
+                    a.u1[iu] = unew; a.v1[iu] = vnew;
+                    if (c == 1 && a.uW) {
+                        const size_t ig = (size_t)(r - 1) * ld + a.nxl + 1;
+                        a.uW[ig] = unew; a.vW[ig] = vnew;
+                    }
+                    if (c == a.nxl && a.uE) {
+                        const size_t ig = (size_t)(r - 1) * ld;
+                        a.uE[ig] = unew; a.vE[ig] = vnew;
+                    }
+                    if (a.tripole && r - 1 >= a.ny - 1) tripole_push(a, c, (r - 1) - (a.ny - 1), unew, vnew);
+                }
+            }
+            s1p = str[0]; s5p = str[4]; n2p = e2; n7p = e7;
+            u_s = u_c; v_s = v_c; uw_s = uw_c; vw_s = vw_c; mprev = m;
+        }
+    }
+}
+
+}  // namespace evp

@@ -29,3 +29,11 @@ def pytest_collection_modifyitems(config, items):
 @pytest.fixture(scope="session")
 def have_gpu():
     return _have_gpu()
+
+
+@pytest.fixture(params=["tma", "sweep"])
+def subcycle_kernel(request, monkeypatch):
+    """Run a test once per subcycle-kernel variant (v2 TMA ring = product default, v1 register
+    sweep); the library reads EVP_B200_KERNEL when a handle is created."""
+    monkeypatch.setenv("EVP_B200_KERNEL", request.param)
+    return request.param

@@ -9,7 +9,7 @@ from cice5_b200 import evp, fixtures as fx
 from tests.util import clone_case, compare_cases
 from tests.test_gpu_parity import OUT_CHECK, _oracle, _small_tripole
 
-pytestmark = pytest.mark.gpu
+pytestmark = [pytest.mark.gpu, pytest.mark.usefixtures("subcycle_kernel")]
 
 
 def _run_group(case, nranks, calls=1, **kw):

@@ -9,7 +9,7 @@ import pytest
 from cice5_b200 import evp, fixtures as fx
 from tests.util import STATE, REL_TOL, clone_case, compare_cases, phys
 
-pytestmark = pytest.mark.gpu
+pytestmark = [pytest.mark.gpu, pytest.mark.usefixtures("subcycle_kernel")]
 
 OUT_CHECK = ("strairx", "strairy", "strtltx", "strtlty", "strocnx", "strocny", "strintx",
              "strinty", "strocnxT", "strocnyT", "divu", "shear", "rdg_conv", "rdg_shear",
