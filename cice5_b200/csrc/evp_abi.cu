@@ -81,7 +81,8 @@ struct evp_handle {
     // one arena, identical layout on every rank, so a peer's plane is peer_base + offset
     char *arena = nullptr;
     size_t arena_bytes = 0;
-    size_t off_planes = 0, off_inbox = 0, off_flags = 0, off_int = 0, off_mask = 0, off_counts = 0;
+    size_t off_planes = 0, off_inbox = 0, off_flags = 0, off_int = 0, off_mask = 0, off_counts = 0, off_tflags = 0;
+    int tflags_ld = 0, tstrips = 0;
     char *peer_arena[kMaxRanks] = {nullptr};
     bool peer_opened[kMaxRanks] = {false};
     bool grid_set = false, uploaded = false, peers_set = false;
@@ -118,6 +119,7 @@ struct evp_handle {
         return reinterpret_cast<int *>(arena + off_int) + (size_t)p * plane_elems;
     }
     unsigned char *mask() const { return reinterpret_cast<unsigned char *>(arena + off_mask); }
+    unsigned char *tflags() const { return reinterpret_cast<unsigned char *>(arena + off_tflags); }
     unsigned long long *counts() const
     {
         return reinterpret_cast<unsigned long long *>(arena + off_counts);
@@ -278,6 +280,9 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
     h->off_int = off;    off = align_up(off + 4 * h->plane_elems * sizeof(int), 256);
     h->off_mask = off;   off = align_up(off + (size_t)h->ldm * h->nyb, 256);
     h->off_counts = off; off = align_up(off + 64, 256);
+    h->tstrips = (g.nxl + kTmaUCols - 1) / kTmaUCols;
+    h->tflags_ld = (int)align_up((size_t)h->nyb + 4, 16);
+    h->off_tflags = off; off = align_up(off + (size_t)h->tstrips * h->tflags_ld, 256);
     h->arena_bytes = off;
     cudaError_t e = cudaMalloc(&h->arena, h->arena_bytes);
     if (e != cudaSuccess) {
@@ -599,7 +604,8 @@ void add_subcycle(Builder &B, int from_parity, bool last)
             t.a = a;
             t.plane_state = from_parity ? S_UB : S_UA;
             t.plane_t = kTGroup; t.plane_u = kUGroup;
-            t.strips = (g.nxl + kTmaUCols - 1) / kTmaUCols;
+            t.strips = h->tstrips;
+            t.tile_flags = h->tflags(); t.flags_ld = h->tflags_ld;
             const int slots = 2 * h->sm_count;
             int best = 4; double best_cost = 1e300;
             for (int rpc = 4; rpc <= 64; ++rpc) {
@@ -713,6 +719,12 @@ void build_program(evp_handle *h, double dt, Program &P)
             a.uvel_init = h->plane(O_UVELINIT); a.vvel_init = h->plane(O_VVELINIT);
             a.mask = h->mask(); a.ldm = h->ldm; a.counts = h->counts();
             prep2_kernel<<<grid2d(h), 128, 0, s>>>(a);
+            ++L.n;
+        }
+        if (h->use_tma) {   // per-strip row activity for the TMA producer
+            dim3 grid(h->tstrips, (h->g.ny + 4 + 3) / 4);
+            tile_flags_kernel<<<grid, 128, 0, s>>>(h->mask(), h->ldm, h->g.nxl, h->g.ny, h->tstrips, h->tflags(),
+                                                  h->tflags_ld);
             ++L.n;
         }
         CK(cudaGetLastError());

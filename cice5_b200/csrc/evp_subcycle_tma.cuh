@@ -34,6 +34,8 @@ struct TmaArgs {
     int plane_state;             // first plane of the OLD state copy
     int plane_t, plane_u;        // first plane of the T / U coefficient groups
     int strips, chunks, items;
+    const unsigned char *tile_flags;   // [strip][ny + 4]: bit0 any active T cell, bit1 any active U cell
+    int flags_ld;
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void *p)
@@ -115,20 +117,30 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                 const int x0 = strip * kTmaUCols;                       // box column 0 = U column c0 - 1
                 const int r0 = 1 + chunk * a.rows_per_chunk;
                 const int rend = min(r0 + a.rows_per_chunk, a.ny + 1);
+                const unsigned char *fl = p.tile_flags + (size_t)strip * p.flags_ld;
                 for (int j = r0 - 1; j <= rend; ++j) {
+                    // what this row segment needs: T data if it has an active T cell; U data of the
+                    // row below if that row has an active U cell; the state (u, v, stresses) if this
+                    // row or the next one has an active T cell or this row an active U cell.  The top
+                    // rows are never skipped: their velocities feed the tripole inboxes every subcycle.
+                    const bool top = j >= a.ny - 2;
+                    const unsigned f0 = fl[j], f1 = fl[j + 1], fm1 = j > 0 ? fl[j - 1] : 0u;
+                    const bool needT = j >= r0 && ((f0 & 1u) || top);
+                    const bool needU = j > r0 && ((fm1 & 2u) || top);
+                    const bool needS = ((f0 | f1) & 1u) || (f0 & 2u) || top;
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
                     unsigned char *sb = ring + (size_t)stage * kStageBytes;
-                    unsigned bytes = kStateDepth * kTmaBoxW * 8;
-                    if (j >= r0) bytes += kTUsed * kTmaBoxW * 8 + kMaskBoxW;
-                    if (j > r0) bytes += kUDepth * kTmaBoxW * 8;
+                    unsigned char *mk = sb + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8;
+                    *reinterpret_cast<volatile unsigned *>(mk + 192) = needS ? 1u : 0u;
+                    unsigned bytes = kMaskBoxW;
+                    if (needS) bytes += kStateDepth * kTmaBoxW * 8;
+                    if (needT) bytes += kTUsed * kTmaBoxW * 8;
+                    if (needU) bytes += kUDepth * kTmaBoxW * 8;
                     mbar_expect_tx(&full_bar[stage], bytes);
-                    tma_load_3d(sb, &mapS, &full_bar[stage], x0, j, p.plane_state);
-                    if (j >= r0) {
-                        tma_load_3d(sb + kStateDepth * kTmaBoxW * 8, &mapT, &full_bar[stage], x0, j, p.plane_t);
-                        tma_load_2d(sb + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8, &mapM, &full_bar[stage],
-                                    x0 & ~15, j);
-                    }
-                    if (j > r0)
+                    tma_load_2d(mk, &mapM, &full_bar[stage], x0 & ~15, j);
+                    if (needS) tma_load_3d(sb, &mapS, &full_bar[stage], x0, j, p.plane_state);
+                    if (needT) tma_load_3d(sb + kStateDepth * kTmaBoxW * 8, &mapT, &full_bar[stage], x0, j, p.plane_t);
+                    if (needU)
                         tma_load_3d(sb + (kStateDepth + kTDepth) * kTmaBoxW * 8, &mapU, &full_bar[stage], x0, j - 1,
                                     p.plane_u);
                     if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
@@ -155,9 +167,12 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
 
         // row r0-1: velocities only
         double u_s, v_s, uw_s, vw_s;
+        bool loaded_s;                                                  // state of the row below was fetched
         {
             mbar_wait(&full_bar[stage], phase);
             const double *st = reinterpret_cast<const double *>(ring + (size_t)stage * kStageBytes);
+            loaded_s = *reinterpret_cast<const unsigned *>(
+                           ring + (size_t)stage * kStageBytes + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8 + 192) != 0u;
             u_s = st[bi]; v_s = st[kTmaBoxW + bi]; uw_s = st[bi - 1]; vw_s = st[kTmaBoxW + bi - 1];
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty_bar[stage]);
@@ -172,6 +187,7 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             const double *tc = st + kStateDepth * kTmaBoxW;
             const double *uc = tc + kTDepth * kTmaBoxW;
             const unsigned char *mk = reinterpret_cast<const unsigned char *>(uc + kUDepth * kTmaBoxW);
+            const bool loaded_c = *reinterpret_cast<const unsigned *>(mk + 192) != 0u;
             const double u_c = st[bi], v_c = st[kTmaBoxW + bi];
             const double uw_c = st[bi - 1], vw_c = st[kTmaBoxW + bi - 1];
             const unsigned m = (warp_on && tcol) ? mk[bi + mshift] : 0u;
@@ -214,7 +230,7 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             const double e2 = shfl_down1(str[1]), e4 = shfl_down1(str[3]);
             const double e7 = shfl_down1(str[6]), e8 = shfl_down1(str[7]);
 
-            if (r > r0 && warp_on) {                                    // stepu on U row r-1 (:700-746)
+            if (r > r0 && warp_on && loaded_s) {                        // stepu on U row r-1 (:700-746)
                 const size_t iu = idx - ld;
                 double unew = u_s, vnew = v_s;
                 if (uact) {
@@ -250,9 +266,32 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                 }
             }
             s1p = str[0]; s5p = str[4]; n2p = e2; n7p = e7;
-            u_s = u_c; v_s = v_c; uw_s = uw_c; vw_s = vw_c; mprev = m;
+            u_s = u_c; v_s = v_c; uw_s = uw_c; vw_s = vw_c; mprev = m; loaded_s = loaded_c;
         }
     }
+}
+
+// Row activity of every strip, once per evp call (the masks are fixed for the call): lets the
+// producer skip the TMA boxes of row segments without ice (land, open ocean).
+__global__ void tile_flags_kernel(const unsigned char *mask, int ldm, int nxl, int ny, int strips,
+                                  unsigned char *flags, int flags_ld)
+{
+    const int strip = blockIdx.x, r = blockIdx.y * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (r > ny + 3) return;
+    unsigned f = 0;
+    if (r >= 1 && r <= ny + 1) {
+        const int c0 = 1 + strip * kTmaUCols;
+        for (int q = lane; q <= kTmaUCols; q += 32) {          // T columns c0 .. c0+124
+            const int c = c0 + q;
+            if (c <= nxl + 1) {
+                const unsigned m = mask[(size_t)r * ldm + c];
+                f |= (m & 1u);
+                if (q < kTmaUCols && c <= nxl) f |= (m & 2u);
+            }
+        }
+    }
+    f = __reduce_or_sync(0xffffffffu, f);
+    if (lane == 0) flags[(size_t)strip * flags_ld + r] = (unsigned char)f;
 }
 
 }  // namespace evp
