@@ -606,7 +606,7 @@ void add_subcycle(Builder &B, int from_parity, bool last)
             t.plane_t = kTGroup; t.plane_u = kUGroup;
             t.strips = h->tstrips;
             t.tile_flags = h->tflags(); t.flags_ld = h->tflags_ld;
-            const int slots = 2 * h->sm_count;
+            const int slots = kTmaBlocksPerSM * h->sm_count;
             int best = 4; double best_cost = 1e300;
             for (int rpc = 4; rpc <= 64; ++rpc) {
                 const long long items = (long long)t.strips * ((g.ny + rpc - 1) / rpc);

@@ -19,14 +19,33 @@
 
 namespace evp {
 
-constexpr int kTmaConsumers = 4;
-constexpr int kTmaBoxW = 128;                                // doubles per box row
+#ifndef EVP_TMA_WARPS
+#define EVP_TMA_WARPS 4
+#endif
+constexpr int kTmaConsumers = EVP_TMA_WARPS;                 // 4 (128-column boxes) or 8 (256-column boxes)
+constexpr int kTmaBoxW = 32 * kTmaConsumers;                 // doubles per box row
+static_assert(kTmaBoxW <= 256, "TMA box dimensions are limited to 256 elements");
 constexpr int kTmaUCols = kTmaConsumers * kUColsPerWarp;     // 124
-constexpr int kTmaStages = 3;
+#ifndef EVP_TMA_STAGES
+#define EVP_TMA_STAGES 3
+#endif
+#ifndef EVP_TMA_BLOCKS
+#define EVP_TMA_BLOCKS 2
+#endif
+#ifndef EVP_TMA_LATE
+#define EVP_TMA_LATE 1
+#endif
+// EVP_TMA_LATE = 1: the U coefficients are read from the stage just before stepu and the stage is
+// released after the row is finished (fewer live registers, stage held longer).
+constexpr bool kLateRelease = EVP_TMA_LATE != 0;
+constexpr int kTmaStages = EVP_TMA_STAGES;
+constexpr int kTmaBlocksPerSM = EVP_TMA_BLOCKS;
 constexpr int kStateDepth = 14, kTDepth = 11, kUDepth = 11;
-constexpr int kMaskBoxW = kTmaBoxW + 16;     // the byte mask is fetched from a 16-byte aligned column (TMA
+constexpr int kMaskBoxW = 128 + 16;          // per mask box; kTmaBoxW / 128 boxes per row
+constexpr int kMaskBoxes = kTmaBoxW / 128;
+constexpr int kMaskFlagOff = 256 * (kMaskBoxes - 1) + kMaskBoxW + 48;     // stage word after the mask bytes (16-byte aligned)     // the byte mask is fetched from a 16-byte aligned column (TMA
                                              // needs 16-byte aligned box starts), up to 12 bytes early
-constexpr int kStageBytes = (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8 + 256;        // + mask row
+constexpr int kStageBytes = (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8 + 256 * kMaskBoxes;   // + mask row
 static_assert(kStageBytes % 128 == 0, "TMA destinations must stay 128-byte aligned");
 
 struct TmaArgs {
@@ -87,7 +106,7 @@ __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, u
 }
 
 template <bool LAST>
-__global__ void __launch_bounds__((kTmaConsumers + 1) * 32, 2)
+__global__ void __launch_bounds__((kTmaConsumers + 1) * 32, kTmaBlocksPerSM)
 evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_constant__ CUtensorMap mapT,
                         const __grid_constant__ CUtensorMap mapU, const __grid_constant__ CUtensorMap mapM,
                         const __grid_constant__ TmaArgs p)
@@ -131,13 +150,15 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
                     unsigned char *sb = ring + (size_t)stage * kStageBytes;
                     unsigned char *mk = sb + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8;
-                    *reinterpret_cast<volatile unsigned *>(mk + 192) = needS ? 1u : 0u;
-                    unsigned bytes = kMaskBoxW;
+                    *reinterpret_cast<volatile unsigned *>(mk + kMaskFlagOff) = needS ? 1u : 0u;
+                    unsigned bytes = kMaskBoxW * kMaskBoxes;
                     if (needS) bytes += kStateDepth * kTmaBoxW * 8;
                     if (needT) bytes += kTUsed * kTmaBoxW * 8;
                     if (needU) bytes += kUDepth * kTmaBoxW * 8;
                     mbar_expect_tx(&full_bar[stage], bytes);
-                    tma_load_2d(mk, &mapM, &full_bar[stage], x0 & ~15, j);
+#pragma unroll
+                    for (int mb = 0; mb < kMaskBoxes; ++mb)
+                        tma_load_2d(mk + mb * 256, &mapM, &full_bar[stage], (x0 & ~15) + mb * 128, j);
                     if (needS) tma_load_3d(sb, &mapS, &full_bar[stage], x0, j, p.plane_state);
                     if (needT) tma_load_3d(sb + kStateDepth * kTmaBoxW * 8, &mapT, &full_bar[stage], x0, j, p.plane_t);
                     if (needU)
@@ -172,7 +193,7 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             mbar_wait(&full_bar[stage], phase);
             const double *st = reinterpret_cast<const double *>(ring + (size_t)stage * kStageBytes);
             loaded_s = *reinterpret_cast<const unsigned *>(
-                           ring + (size_t)stage * kStageBytes + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8 + 192) != 0u;
+                           ring + (size_t)stage * kStageBytes + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8 + kMaskFlagOff) != 0u;
             u_s = st[bi]; v_s = st[kTmaBoxW + bi]; uw_s = st[bi - 1]; vw_s = st[kTmaBoxW + bi - 1];
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty_bar[stage]);
@@ -187,10 +208,12 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             const double *tc = st + kStateDepth * kTmaBoxW;
             const double *uc = tc + kTDepth * kTmaBoxW;
             const unsigned char *mk = reinterpret_cast<const unsigned char *>(uc + kUDepth * kTmaBoxW);
-            const bool loaded_c = *reinterpret_cast<const unsigned *>(mk + 192) != 0u;
+            const bool loaded_c = *reinterpret_cast<const unsigned *>(mk + kMaskFlagOff) != 0u;
             const double u_c = st[bi], v_c = st[kTmaBoxW + bi];
             const double uw_c = st[bi - 1], vw_c = st[kTmaBoxW + bi - 1];
-            const unsigned m = (warp_on && tcol) ? mk[bi + mshift] : 0u;
+            const int mpos = bi + mshift;                               // mask box b covers bytes [128 b, 128 b + 144)
+            const int mbox = min(mpos >> 7, kMaskBoxes - 1);            // and sits 256 b bytes into the mask area
+            const unsigned m = (warp_on && tcol) ? mk[mbox * 256 + (mpos - mbox * 128)] : 0u;
             const bool tact = (m & 1u) != 0;
             const bool uact = warp_on && ucol && (mprev & 2u) && r > r0;
             const bool any_t = __ballot_sync(0xffffffffu, tact) != 0u;
@@ -202,22 +225,28 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
 #pragma unroll
                 for (int q = 0; q < kTUsed; ++q) tco[q] = tc[q * kTmaBoxW + bi];
             }
-            if (any_u) {
+            if (!kLateRelease) {
+                if (any_u) {
 #pragma unroll
-                for (int q = 0; q < kUDepth; ++q) uco[q] = uc[q * kTmaBoxW + bi];
+                    for (int q = 0; q < kUDepth; ++q) uco[q] = uc[q * kTmaBoxW + bi];
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty_bar[stage]);          // slot free: everything is in registers
+                if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&empty_bar[stage]);              // slot free: everything is in registers
-            if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
 
             const size_t idx = (size_t)r * ld + c;
             double str[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
             if (tact) {
                 double divu, shear, rdg_conv, rdg_shear, prs_sig;
                 // tco: dxt dyt dxhy dyhx cxp cyp cxm cym tinyarea strength [tarear]
+#ifdef EVP_TMA_NOCOMPUTE   /* timing experiment only: data path without the arithmetic */
+                for (int q = 0; q < 8; ++q) str[q] = s[q] + tco[q] + u_c + uw_c + v_c + vw_c; divu = shear = rdg_conv = rdg_shear = prs_sig = 0.0;
+#else
                 stress_cell<LAST>(k, u_c, uw_c, u_s, uw_s, v_c, vw_c, v_s, vw_s, tco[0], tco[1], tco[2], tco[3],
                                   tco[4], tco[5], tco[6], tco[7], tco[8], tco[9], LAST ? tco[kTDepth - 1] : 0.0, s,
                                   str, divu, shear, rdg_conv, rdg_shear, prs_sig);
+#endif
                 if (tstore_col && (r < rend || r == a.ny + 1)) {
 #pragma unroll
                     for (int q = 0; q < 12; ++q) a.s1[q][idx] = s[q];
@@ -234,10 +263,18 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                 const size_t iu = idx - ld;
                 double unew = u_s, vnew = v_s;
                 if (uact) {
+                    if (kLateRelease) {
+#pragma unroll
+                        for (int q = 0; q < kUDepth; ++q) uco[q] = uc[q * kTmaBoxW + bi];
+                    }
                     // uco: aiu Cw uocn vocn waterx watery forcex forcey umassdti fm uarear
                     const double uold = u_s, vold = v_s;
                     const double du = uco[2] - uold, dv = uco[3] - vold;
+#ifdef EVP_TMA_NOCOMPUTE
+                    const double vrel = uco[0] + uco[1] + du + dv;
+#else
                     const double vrel = uco[0] * k.rhow * uco[1] * sqrt(du * du + dv * dv);
+#endif
                     const double taux = vrel * uco[4], tauy = vrel * uco[5];
                     const double umdt = uco[8], fm = uco[9];
                     const double cca = (k.brlx + k.revp) * umdt + vrel * k.cosw;
@@ -248,8 +285,12 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     const double strinty = uar * (s5p + str[5] + n7p + e8);
                     const double cc1 = strintx + uco[6] + taux + umdt * (k.brlx * uold);
                     const double cc2 = strinty + uco[7] + tauy + umdt * (k.brlx * vold);
+#ifdef EVP_TMA_NOCOMPUTE
+                    unew = cca + cc1 + ab2; vnew = ccb + cc2;
+#else
                     unew = (cca * cc1 + ccb * cc2) / ab2;
                     vnew = (cca * cc2 - ccb * cc1) / ab2;
+#endif
                     if (LAST) { a.strintx[iu] = strintx; a.strinty[iu] = strinty; }
                 }
                 if (ucol) {
@@ -264,6 +305,11 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     }
                     if (a.tripole && r - 1 >= a.ny - 1) tripole_push(a, c, (r - 1) - (a.ny - 1), unew, vnew);
                 }
+            }
+            if (kLateRelease) {
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty_bar[stage]);          // row done: slot free
+                if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
             }
             s1p = str[0]; s5p = str[4]; n2p = e2; n7p = e7;
             u_s = u_c; v_s = v_c; uw_s = uw_c; vw_s = vw_c; mprev = m; loaded_s = loaded_c;

@@ -81,7 +81,7 @@ def load_library(strict: bool = True):
     round-off on some grids, so a contracted build cannot promise 1e-10 there)."""
     if strict in _libs:
         return _libs[strict]
-    path = _build.lib_path(strict)
+    path = os.environ.get("EVP_B200_LIB") or _build.lib_path(strict)   # override: kernel-tuning experiments
     try:
         _build.build()
     except Exception:
