@@ -40,7 +40,8 @@ enum Plane {
     // tarear on the last subcycle)
     G_DXT, G_DYT, G_DXHY, G_DYHX, G_CXP, G_CYP, G_CXM, G_CYM, G_TINYAREA, W_STRENGTH, G_TAREAR,
     // U-cell coefficients of the subcycle kernel: contiguous, one TMA box of depth 11
-    W_AIU, I_CW, I_UOCN, I_VOCN, W_WATERX, W_WATERY, W_FORCEX, W_FORCEY, W_UMASSDTI, S_FM, G_UAREAR,
+    // (waterx, watery last: when cosw = 1, sinw = 0 they equal uocn, vocn and the box stops before them)
+    W_AIU, I_CW, I_UOCN, I_VOCN, W_FORCEX, W_FORCEY, W_UMASSDTI, S_FM, G_UAREAR, W_WATERX, W_WATERY,
     // dynamic state, ping-pong copies A / B: u, v, stressp_1..4, stressm_1..4, stress12_1..4
     S_UA, S_VA, S_STRA, S_STRA_END = S_STRA + 11,
     S_UB, S_VB, S_STRB, S_STRB_END = S_STRB + 11,
@@ -94,7 +95,7 @@ struct evp_handle {
     int h_error = 0;
     bool use_tma = false;         // subcycle kernel v2 (TMA ring) instead of v1 (register sweep)
     int sm_count = 148;
-    CUtensorMap mapS, mapT10, mapT11, mapU, mapM;
+    CUtensorMap mapS, mapT10, mapT11, mapU, mapU9, mapM;
     evp_stats_t stats;
     unsigned long long h_counts[2];
 
@@ -153,6 +154,11 @@ void set_evp_parameters(const evp_config_t &c, Consts &k)
     k.cosw = c.cosw; k.sinw = c.sinw; k.rhow = c.rhow;
 }
 
+// L2 promotion of the plane boxes: box rows start on 32-byte sectors but not on 128/256-byte lines,
+// so any promotion fetches bytes of the neighbouring strips (measured: +20 % DRAM reads with 256 B)
+#ifndef EVP_TMA_L2PROMO
+#define EVP_TMA_L2PROMO CU_TENSOR_MAP_L2_PROMOTION_NONE
+#endif
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -172,12 +178,13 @@ int make_tensor_maps(evp_handle *h)
     const cuuint64_t dims[3] = {(cuuint64_t)h->ld, (cuuint64_t)h->nyb, (cuuint64_t)NPLANES};
     const cuuint64_t strides[2] = {(cuuint64_t)h->ld * 8, (cuuint64_t)h->plane_elems * 8};
     const cuuint32_t estr[3] = {1, 1, 1};
-    struct { CUtensorMap *m; int depth; } maps[4] = {{&h->mapS, kStateDepth}, {&h->mapT10, kTDepth - 1},
-                                                     {&h->mapT11, kTDepth}, {&h->mapU, kUDepth}};
+    struct { CUtensorMap *m; int depth; } maps[5] = {{&h->mapS, kStateDepth}, {&h->mapT10, kTDepth - 1},
+                                                     {&h->mapT11, kTDepth}, {&h->mapU, kUDepth},
+                                                     {&h->mapU9, kUDepth - 2}};
     for (auto &mm : maps) {
         const cuuint32_t box[3] = {(cuuint32_t)kTmaBoxW, 1, (cuuint32_t)mm.depth};
         CUresult r = enc(mm.m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, h->plane(0), dims, strides, box, estr,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, (CUtensorMapL2promotion)EVP_TMA_L2PROMO,
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) {
             snprintf(g_cuda_err, sizeof(g_cuda_err), "cuTensorMapEncodeTiled(depth %d) failed: %d", mm.depth, (int)r);
@@ -604,6 +611,10 @@ void add_subcycle(Builder &B, int from_parity, bool last)
             t.a = a;
             t.plane_state = from_parity ? S_UB : S_UA;
             t.plane_t = kTGroup; t.plane_u = kUGroup;
+            // waterx = uocn*cosw - vocn*sinw*sign(fm) is uocn itself (up to the sign of zero) when the
+            // turning angle is zero: skip those two planes (ice_dyn_shared.F90:590-591)
+            t.water_is_ocn = (h->cfg.cosw == 1.0 && h->cfg.sinw == 0.0) ? 1 : 0;
+            const CUtensorMap &mapU = t.water_is_ocn ? h->mapU9 : h->mapU;
             t.strips = h->tstrips;
             t.tile_flags = h->tflags(); t.flags_ld = h->tflags_ld;
             const int slots = kTmaBlocksPerSM * h->sm_count;
@@ -620,10 +631,10 @@ void add_subcycle(Builder &B, int from_parity, bool last)
             const int grid = t.items < slots ? t.items : slots;
             const size_t smem = (size_t)kTmaStages * kStageBytes;
             if (last)
-                evp_subcycle_tma_kernel<true><<<grid, (kTmaConsumers + 1) * 32, smem, L.s()>>>(h->mapS, h->mapT11, h->mapU,
+                evp_subcycle_tma_kernel<true><<<grid, (kTmaConsumers + 1) * 32, smem, L.s()>>>(h->mapS, h->mapT11, mapU,
                                                                                              h->mapM, t);
             else
-                evp_subcycle_tma_kernel<false><<<grid, (kTmaConsumers + 1) * 32, smem, L.s()>>>(h->mapS, h->mapT10, h->mapU,
+                evp_subcycle_tma_kernel<false><<<grid, (kTmaConsumers + 1) * 32, smem, L.s()>>>(h->mapS, h->mapT10, mapU,
                                                                                               h->mapM, t);
             ++L.n;
             return EVP_OK;

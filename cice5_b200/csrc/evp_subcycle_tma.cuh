@@ -55,6 +55,7 @@ struct TmaArgs {
     int strips, chunks, items;
     const unsigned char *tile_flags;   // [strip][ny + 4]: bit0 any active T cell, bit1 any active U cell
     int flags_ld;
+    int water_is_ocn;            // cosw == 1 && sinw == 0: waterx/watery are not fetched (== uocn/vocn)
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void *p)
@@ -154,7 +155,7 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     unsigned bytes = kMaskBoxW * kMaskBoxes;
                     if (needS) bytes += kStateDepth * kTmaBoxW * 8;
                     if (needT) bytes += kTUsed * kTmaBoxW * 8;
-                    if (needU) bytes += kUDepth * kTmaBoxW * 8;
+                    if (needU) bytes += (p.water_is_ocn ? kUDepth - 2 : kUDepth) * kTmaBoxW * 8;
                     mbar_expect_tx(&full_bar[stage], bytes);
 #pragma unroll
                     for (int mb = 0; mb < kMaskBoxes; ++mb)
@@ -228,7 +229,9 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             if (!kLateRelease) {
                 if (any_u) {
 #pragma unroll
-                    for (int q = 0; q < kUDepth; ++q) uco[q] = uc[q * kTmaBoxW + bi];
+                    for (int q = 0; q < kUDepth - 2; ++q) uco[q] = uc[q * kTmaBoxW + bi];
+                    uco[9] = p.water_is_ocn ? uco[2] : uc[9 * kTmaBoxW + bi];
+                    uco[10] = p.water_is_ocn ? uco[3] : uc[10 * kTmaBoxW + bi];
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&empty_bar[stage]);          // slot free: everything is in registers
@@ -265,9 +268,11 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                 if (uact) {
                     if (kLateRelease) {
 #pragma unroll
-                        for (int q = 0; q < kUDepth; ++q) uco[q] = uc[q * kTmaBoxW + bi];
+                        for (int q = 0; q < kUDepth - 2; ++q) uco[q] = uc[q * kTmaBoxW + bi];
+                        uco[9] = p.water_is_ocn ? uco[2] : uc[9 * kTmaBoxW + bi];
+                        uco[10] = p.water_is_ocn ? uco[3] : uc[10 * kTmaBoxW + bi];
                     }
-                    // uco: aiu Cw uocn vocn waterx watery forcex forcey umassdti fm uarear
+                    // uco: aiu Cw uocn vocn forcex forcey umassdti fm uarear waterx watery
                     const double uold = u_s, vold = v_s;
                     const double du = uco[2] - uold, dv = uco[3] - vold;
 #ifdef EVP_TMA_NOCOMPUTE
@@ -275,16 +280,16 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
 #else
                     const double vrel = uco[0] * k.rhow * uco[1] * sqrt(du * du + dv * dv);
 #endif
-                    const double taux = vrel * uco[4], tauy = vrel * uco[5];
-                    const double umdt = uco[8], fm = uco[9];
+                    const double taux = vrel * uco[9], tauy = vrel * uco[10];
+                    const double umdt = uco[6], fm = uco[7];
                     const double cca = (k.brlx + k.revp) * umdt + vrel * k.cosw;
                     const double ccb = fm + copysign(1.0, fm) * vrel * k.sinw;
                     const double ab2 = cca * cca + ccb * ccb;
-                    const double uar = uco[10];
+                    const double uar = uco[8];
                     const double strintx = uar * (s1p + n2p + str[2] + e4);
                     const double strinty = uar * (s5p + str[5] + n7p + e8);
-                    const double cc1 = strintx + uco[6] + taux + umdt * (k.brlx * uold);
-                    const double cc2 = strinty + uco[7] + tauy + umdt * (k.brlx * vold);
+                    const double cc1 = strintx + uco[4] + taux + umdt * (k.brlx * uold);
+                    const double cc2 = strinty + uco[5] + tauy + umdt * (k.brlx * vold);
 #ifdef EVP_TMA_NOCOMPUTE
                     unew = cca + cc1 + ab2; vnew = ccb + cc2;
 #else
