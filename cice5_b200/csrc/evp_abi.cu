@@ -84,6 +84,8 @@ struct evp_handle {
     size_t arena_bytes = 0;
     size_t off_planes = 0, off_inbox = 0, off_flags = 0, off_int = 0, off_mask = 0, off_counts = 0, off_tflags = 0;
     int tflags_ld = 0, tstrips = 0;
+    int t_rpc = 0, t_chunks = 0, t_items = 0;    // TMA kernel work items: (strip, chunk of t_rpc rows)
+    size_t off_queue = 0;                        // int queue[ndte], int item_count, int item_list[t_items]
     char *peer_arena[kMaxRanks] = {nullptr};
     bool peer_opened[kMaxRanks] = {false};
     bool grid_set = false, uploaded = false, peers_set = false;
@@ -121,6 +123,9 @@ struct evp_handle {
     }
     unsigned char *mask() const { return reinterpret_cast<unsigned char *>(arena + off_mask); }
     unsigned char *tflags() const { return reinterpret_cast<unsigned char *>(arena + off_tflags); }
+    int *queue(int ksub) const { return reinterpret_cast<int *>(arena + off_queue) + ksub; }
+    int *item_count() const { return reinterpret_cast<int *>(arena + off_queue) + cfg.ndte; }
+    int *item_list() const { return reinterpret_cast<int *>(arena + off_queue) + cfg.ndte + 1; }
     unsigned long long *counts() const
     {
         return reinterpret_cast<unsigned long long *>(arena + off_counts);
@@ -290,6 +295,20 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
     h->tstrips = (g.nxl + kTmaUCols - 1) / kTmaUCols;
     h->tflags_ld = (int)align_up((size_t)h->nyb + 4, 16);
     h->off_tflags = off; off = align_up(off + (size_t)h->tstrips * h->tflags_ld, 256);
+    {   // work items of the TMA kernel: enough of them (about 8 per resident CTA) that the dynamic
+        // queue evens out land / open-ocean items, tall enough that the redundant first row of an
+        // item (velocities of row r0-1) stays a few per cent; small grids: one item per CTA
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device);
+        const long long slots = (long long)kTmaBlocksPerSM * sms;
+        long long rpc = ((long long)h->tstrips * g.ny + 8 * slots - 1) / (8 * slots);
+        if (const char *ev = getenv("EVP_B200_RPC")) rpc = atoi(ev);      // tuning experiments
+        rpc = rpc < 4 ? 4 : (rpc > 48 ? 48 : rpc);
+        h->t_rpc = (int)rpc;
+        h->t_chunks = (g.ny + h->t_rpc - 1) / h->t_rpc;
+        h->t_items = h->tstrips * h->t_chunks;
+    }
+    h->off_queue = off;  off = align_up(off + ((size_t)cfg->ndte + 1 + h->t_items) * sizeof(int), 256);
     h->arena_bytes = off;
     cudaError_t e = cudaMalloc(&h->arena, h->arena_bytes);
     if (e != cudaSuccess) {
@@ -596,11 +615,11 @@ void fill_loop_args(const evp_handle *h, int from_parity, int inbox_buf, LoopArg
 }
 
 // one subcycle: stress + stepu + halo pushes fused; [sync]; then the tripole fold of the new u, v
-void add_subcycle(Builder &B, int from_parity, bool last)
+void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
 {
     evp_handle *h = B.h;
     const int buf = (B.seq++) & 1;
-    B.op([h, from_parity, last, buf](Launcher &L) {
+    B.op([h, from_parity, last, buf, ksub](Launcher &L) {
         const Geom &g = h->g;
         LoopArgs a;
         fill_loop_args(h, from_parity, buf, a);
@@ -618,16 +637,10 @@ void add_subcycle(Builder &B, int from_parity, bool last)
             t.strips = h->tstrips;
             t.tile_flags = h->tflags(); t.flags_ld = h->tflags_ld;
             const int slots = kTmaBlocksPerSM * h->sm_count;
-            int best = 4; double best_cost = 1e300;
-            for (int rpc = 4; rpc <= 64; ++rpc) {
-                const long long items = (long long)t.strips * ((g.ny + rpc - 1) / rpc);
-                const long long G = items < slots ? items : slots;
-                const double cost = (double)((items + G - 1) / G) * (rpc + 1.5);
-                if (cost < best_cost) { best_cost = cost; best = rpc; }
-            }
-            t.a.rows_per_chunk = best;
-            t.chunks = (g.ny + best - 1) / best;
-            t.items = t.strips * t.chunks;
+            t.a.rows_per_chunk = h->t_rpc;
+            t.chunks = h->t_chunks;
+            t.items = h->t_items;
+            t.queue = h->queue(ksub - 1); t.item_list = h->item_list(); t.item_count = h->item_count();
             const int grid = t.items < slots ? t.items : slots;
             const size_t smem = (size_t)kTmaStages * kStageBytes;
             if (last)
@@ -736,7 +749,10 @@ void build_program(evp_handle *h, double dt, Program &P)
             dim3 grid(h->tstrips, (h->g.ny + 4 + 3) / 4);
             tile_flags_kernel<<<grid, 128, 0, s>>>(h->mask(), h->ldm, h->g.nxl, h->g.ny, h->tstrips, h->tflags(),
                                                   h->tflags_ld);
-            ++L.n;
+            item_list_kernel<<<1, 1024, 0, s>>>(h->tflags(), h->tflags_ld, h->tstrips, h->t_chunks, h->t_rpc, h->g.ny,
+                                                h->g.tripole ? 1 : 0, h->item_list(), h->item_count(), h->queue(0),
+                                                h->cfg.ndte);
+            L.n += 2;
         }
         CK(cudaGetLastError());
         return EVP_OK;
@@ -757,7 +773,7 @@ void build_program(evp_handle *h, double dt, Program &P)
     P.loop_begin = P.ops.size();
     int par = cur;
     for (int ksub = 1; ksub <= cfg.ndte; ++ksub) {
-        add_subcycle(B, par, ksub == cfg.ndte);
+        add_subcycle(B, par, ksub == cfg.ndte, ksub);
         par ^= 1;
     }
     P.loop_end = P.ops.size();

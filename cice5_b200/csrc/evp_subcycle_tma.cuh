@@ -53,6 +53,11 @@ struct TmaArgs {
     int plane_state;             // first plane of the OLD state copy
     int plane_t, plane_u;        // first plane of the T / U coefficient groups
     int strips, chunks, items;
+    // dynamic work queue: CTAs draw positions with atomicAdd(queue, 1); position q maps to the item
+    // item_list[q] (the items of this call that hold ice, built by item_list_kernel) for
+    // q < *item_count.  One counter per subcycle launch, zeroed once per evp call.
+    int *queue;
+    const int *item_list, *item_count;
     const unsigned char *tile_flags;   // [strip][ny + 4]: bit0 any active T cell, bit1 any active U cell
     int flags_ld;
     int water_is_ocn;            // cosw == 1 && sinw == 0: waterx/watery are not fetched (== uocn/vocn)
@@ -132,7 +137,17 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
     if (warp == kTmaConsumers) {
         // ------------------------------ producer ------------------------------
         if (lane == 0) {
-            for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
+            const int nitems = *p.item_count;
+            for (;;) {
+                const int q = atomicAdd(p.queue, 1);
+                if (q >= nitems) {                                      // queue drained: tell the consumers
+                    mbar_wait(&empty_bar[stage], phase ^ 1u);
+                    unsigned char *mk = ring + (size_t)stage * kStageBytes + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8;
+                    *reinterpret_cast<volatile int *>(mk + kMaskFlagOff + 4) = -1;
+                    mbar_arrive(&full_bar[stage]);
+                    break;
+                }
+                const int item = p.item_list[q];
                 const int strip = item % p.strips, chunk = item / p.strips;
                 const int x0 = strip * kTmaUCols;                       // box column 0 = U column c0 - 1
                 const int r0 = 1 + chunk * a.rows_per_chunk;
@@ -152,6 +167,7 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     unsigned char *sb = ring + (size_t)stage * kStageBytes;
                     unsigned char *mk = sb + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8;
                     *reinterpret_cast<volatile unsigned *>(mk + kMaskFlagOff) = needS ? 1u : 0u;
+                    *reinterpret_cast<volatile int *>(mk + kMaskFlagOff + 4) = item;
                     unsigned bytes = kMaskBoxW * kMaskBoxes;
                     if (needS) bytes += kStateDepth * kTmaBoxW * 8;
                     if (needT) bytes += kTUsed * kTmaBoxW * 8;
@@ -176,7 +192,11 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
     const Consts &k = a.k;
     const int ld = a.ld;
     const int bi = 1 + warp * kUColsPerWarp + lane;                     // my column inside the box
-    for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
+    for (;;) {
+        mbar_wait(&full_bar[stage], phase);                             // first stage of the next item
+        const int item = *reinterpret_cast<const int *>(
+            ring + (size_t)stage * kStageBytes + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8 + kMaskFlagOff + 4);
+        if (item < 0) break;
         const int strip = item % p.strips, chunk = item / p.strips;
         const int c = 1 + strip * kTmaUCols + warp * kUColsPerWarp + lane;   // T column (U column if lane < 31)
         const bool warp_on = (c - lane) <= a.nxl;                       // warp-uniform
@@ -191,7 +211,6 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
         double u_s, v_s, uw_s, vw_s;
         bool loaded_s;                                                  // state of the row below was fetched
         {
-            mbar_wait(&full_bar[stage], phase);
             const double *st = reinterpret_cast<const double *>(ring + (size_t)stage * kStageBytes);
             loaded_s = *reinterpret_cast<const unsigned *>(
                            ring + (size_t)stage * kStageBytes + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8 + kMaskFlagOff) != 0u;
@@ -343,6 +362,44 @@ __global__ void tile_flags_kernel(const unsigned char *mask, int ldm, int nxl, i
     }
     f = __reduce_or_sync(0xffffffffu, f);
     if (lane == 0) flags[(size_t)strip * flags_ld + r] = (unsigned char)f;
+}
+
+// The work list of the call: the (strip, row chunk) items that hold ice, in item order (one block,
+// ordered compaction so the list is reproducible).  An item without any active row segment writes
+// nothing (the ping-pong copies agree where the loop never writes), so it is dropped -- except the
+// chunks that reach the top rows of a tripole grid, whose velocities feed the fold every subcycle.
+__global__ void item_list_kernel(const unsigned char *flags, int flags_ld, int strips, int chunks, int rpc, int ny,
+                                 int tripole, int *list, int *count, int *queues, int nqueues)
+{
+    __shared__ int wsum[32];
+    __shared__ int base;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    if (threadIdx.x == 0) base = 0;
+    for (int q = threadIdx.x; q < nqueues; q += blockDim.x) queues[q] = 0;
+    __syncthreads();
+    const int items = strips * chunks;
+    for (int i0 = 0; i0 < items; i0 += blockDim.x) {
+        const int item = i0 + threadIdx.x;
+        bool keep = false;
+        if (item < items) {
+            const int strip = item % strips, chunk = item / strips;
+            const int r0 = 1 + chunk * rpc, rend = min(r0 + rpc, ny + 1);
+            const unsigned char *fl = flags + (size_t)strip * flags_ld;
+            unsigned f = 0;
+            for (int j = r0 - 1; j <= rend + 1; ++j) f |= fl[j];
+            keep = f != 0u || (tripole && rend >= ny - 2);
+        }
+        const unsigned b = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) wsum[warp] = __popc(b);
+        __syncthreads();
+        int off = base;
+        for (int w = 0; w < warp; ++w) off += wsum[w];
+        if (keep) list[off + __popc(b & ((1u << lane) - 1u))] = item;
+        __syncthreads();
+        if (threadIdx.x == 0) { int t = 0; for (int w = 0; w < nw; ++w) t += wsum[w]; base += t; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *count = base;
 }
 
 }  // namespace evp
