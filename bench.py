@@ -46,6 +46,8 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch the ndte loop kernel by kernel")
     ap.add_argument("--fma", action="store_true", help="use the FMA-contracted comparison build")
+    ap.add_argument("--no-compact-metrics", action="store_true",
+                    help="do not pass HTE/HTN: fetch all 8 metric planes + tinyarea every subcycle")
     ap.add_argument("--cpu-ndte", type=int, default=24, help="subcycles of the CPU sample")
     return ap.parse_args()
 
@@ -207,11 +209,12 @@ def main():
             o[k] = a
         return o
 
-    gridf = {k: sl(grid.f[k]) for k in evp.GRID_R8 + ("tmask", "umask")}
+    gridf = {k: sl(grid.f[k]) for k in evp.GRID_R8 + ("tmask", "umask", "HTE", "HTN")}
     inp, io, out = pin(case.inp), pin(case.io), pin(case.out)
 
     e = evp.EvpGpu.for_domain(dom, args.ndte, dt, rank=rank, nranks=N, device=local_rank,
-                              strict=not args.fma, use_cuda_graph=not args.no_graph)
+                              strict=not args.fma, use_cuda_graph=not args.no_graph,
+                              compact_metrics=not args.no_compact_metrics)
     e.set_grid(gridf)
     if N > 1:
         blob = e.peer_blob()

@@ -36,12 +36,16 @@ thread_local char g_cuda_err[512] = "";
 
 // ---- plane directory ----------------------------------------------------------------------
 enum Plane {
-    // T-cell coefficients of the subcycle kernel: contiguous, one TMA box of depth 10 (11 with
-    // tarear on the last subcycle)
-    G_DXT, G_DYT, G_DXHY, G_DYHX, G_CXP, G_CYP, G_CXM, G_CYM, G_TINYAREA, W_STRENGTH, G_TAREAR,
-    // U-cell coefficients of the subcycle kernel: contiguous, one TMA box of depth 11
+    // T-cell coefficients of the subcycle kernel (TMA boxes over consecutive planes):
+    //   compact rows: HTE, HTN, strength [, tinyarea]  (depth 3 / 4 from G_HTE) -- the 8 metric
+    //                 terms (and tinyarea) are recomputed from HTE / HTN where set_grid verified
+    //                 that this reproduces the host's arrays bit for bit
+    //   full rows   : strength, tinyarea, dxt .. cym   (depth 10 from W_STRENGTH)
+    //   tarear alone on the last subcycle, HTN alone where the next row needs its southern HTN
+    G_HTE, G_HTN, W_STRENGTH, G_TINYAREA, G_DXT, G_DYT, G_DXHY, G_DYHX, G_CXP, G_CYP, G_CXM, G_CYM, G_TAREAR,
+    // U-cell coefficients of the subcycle kernel: contiguous, one TMA box of depth 10
     // (waterx, watery last: when cosw = 1, sinw = 0 they equal uocn, vocn and the box stops before them)
-    W_AIU, I_CW, I_UOCN, I_VOCN, W_FORCEX, W_FORCEY, W_UMASSDTI, S_FM, G_UAREAR, W_WATERX, W_WATERY,
+    W_VRELC, I_UOCN, I_VOCN, W_FORCEX, W_FORCEY, W_UMASSDTI, S_FM, G_UAREAR, W_WATERX, W_WATERY,
     // dynamic state, ping-pong copies A / B: u, v, stressp_1..4, stressm_1..4, stress12_1..4
     S_UA, S_VA, S_STRA, S_STRA_END = S_STRA + 11,
     S_UB, S_VB, S_STRB, S_STRB_END = S_STRB + 11,
@@ -49,13 +53,13 @@ enum Plane {
     G_TAREA, G_UAREA, G_FCOR,
     I_AICE, I_VICE, I_VSNO, I_AICE_INIT, I_STRAIRXT, I_STRAIRYT, I_SSTLTX, I_SSTLTY, I_STRENGTH,
     // evp locals (ice_dyn_evp.F90:120-137)
-    W_TMASS, W_UMASS, W_ICETMASK, W_1, W_2,
+    W_TMASS, W_UMASS, W_ICETMASK, W_1, W_2, W_AIU, I_CW,
     // outputs (evp_out_t order, first 17; contiguous: zeroed with one memset)
     O_STRAIRX, O_STRAIRY, O_STRTLTX, O_STRTLTY, O_STROCNX, O_STROCNY, O_STRINTX, O_STRINTY,
     O_STROCNXT, O_STROCNYT, O_DIVU, O_SHEAR, O_RDGCONV, O_RDGSHEAR, O_PRSSIG, O_UVELINIT, O_VVELINIT,
     NPLANES
 };
-constexpr int kTGroup = G_DXT, kUGroup = W_AIU;
+constexpr int kTGroup = G_HTE, kUGroup = W_VRELC;
 
 struct PeerBlob {                 // exchanged between the tasks of one node
     cudaIpcMemHandle_t arena;
@@ -85,6 +89,7 @@ struct evp_handle {
     size_t off_planes = 0, off_inbox = 0, off_flags = 0, off_int = 0, off_mask = 0, off_counts = 0, off_tflags = 0;
     int tflags_ld = 0, tstrips = 0;
     int t_rpc = 0, t_chunks = 0, t_items = 0;    // TMA kernel work items: (strip, chunk of t_rpc rows)
+    size_t off_gflags = 0;                       // per strip row: bit2 metrics, bit3 tinyarea reproducible from HTE/HTN
     size_t off_queue = 0;                        // int queue[ndte], int item_count, int item_list[t_items]
     char *peer_arena[kMaxRanks] = {nullptr};
     bool peer_opened[kMaxRanks] = {false};
@@ -97,7 +102,8 @@ struct evp_handle {
     int h_error = 0;
     bool use_tma = false;         // subcycle kernel v2 (TMA ring) instead of v1 (register sweep)
     int sm_count = 148;
-    CUtensorMap mapS, mapT10, mapT11, mapU, mapU9, mapM;
+    CUtensorMap mapS, mapT1, mapT3, mapT4, mapT10, mapU, mapU8, mapM;
+    bool have_ht = false;         // HTE / HTN were given: compact metric rows are possible
     evp_stats_t stats;
     unsigned long long h_counts[2];
 
@@ -123,6 +129,7 @@ struct evp_handle {
     }
     unsigned char *mask() const { return reinterpret_cast<unsigned char *>(arena + off_mask); }
     unsigned char *tflags() const { return reinterpret_cast<unsigned char *>(arena + off_tflags); }
+    unsigned char *gflags() const { return reinterpret_cast<unsigned char *>(arena + off_gflags); }
     int *queue(int ksub) const { return reinterpret_cast<int *>(arena + off_queue) + ksub; }
     int *item_count() const { return reinterpret_cast<int *>(arena + off_queue) + cfg.ndte; }
     int *item_list() const { return reinterpret_cast<int *>(arena + off_queue) + cfg.ndte + 1; }
@@ -183,9 +190,9 @@ int make_tensor_maps(evp_handle *h)
     const cuuint64_t dims[3] = {(cuuint64_t)h->ld, (cuuint64_t)h->nyb, (cuuint64_t)NPLANES};
     const cuuint64_t strides[2] = {(cuuint64_t)h->ld * 8, (cuuint64_t)h->plane_elems * 8};
     const cuuint32_t estr[3] = {1, 1, 1};
-    struct { CUtensorMap *m; int depth; } maps[5] = {{&h->mapS, kStateDepth}, {&h->mapT10, kTDepth - 1},
-                                                     {&h->mapT11, kTDepth}, {&h->mapU, kUDepth},
-                                                     {&h->mapU9, kUDepth - 2}};
+    struct { CUtensorMap *m; int depth; } maps[7] = {{&h->mapS, kStateDepth}, {&h->mapT1, 1}, {&h->mapT3, 3},
+                                                     {&h->mapT4, 4}, {&h->mapT10, 10}, {&h->mapU, kUDepth},
+                                                     {&h->mapU8, kUDepth - 2}};
     for (auto &mm : maps) {
         const cuuint32_t box[3] = {(cuuint32_t)kTmaBoxW, 1, (cuuint32_t)mm.depth};
         CUresult r = enc(mm.m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, h->plane(0), dims, strides, box, estr,
@@ -295,6 +302,7 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
     h->tstrips = (g.nxl + kTmaUCols - 1) / kTmaUCols;
     h->tflags_ld = (int)align_up((size_t)h->nyb + 4, 16);
     h->off_tflags = off; off = align_up(off + (size_t)h->tstrips * h->tflags_ld, 256);
+    h->off_gflags = off; off = align_up(off + (size_t)h->tstrips * h->tflags_ld, 256);
     {   // work items of the TMA kernel: enough of them (about 8 per resident CTA) that the dynamic
         // queue evens out land / open-ocean items, tall enough that the redundant first row of an
         // item (velocities of row r0-1) stays a few per cent; small grids: one item per CTA
@@ -397,6 +405,27 @@ int evp_gpu_set_grid(evp_handle_t *h, const evp_grid_t *gr)
     const int dstp[14] = {G_DXT, G_DYT, G_DXHY, G_DYHX, G_CXP, G_CYP, G_CXM, G_CYM,
                           G_TAREA, G_UAREA, G_TAREAR, G_UAREAR, G_TINYAREA, G_FCOR};
     for (int p = 0; p < 14; ++p) TRY(h2d(h, dstp[p], src[p]));
+    h->have_ht = gr->HTE && gr->HTN;
+    CK(cudaMemsetAsync(h->gflags(), 0, (size_t)h->tstrips * h->tflags_ld, h->stream));
+    if (h->have_ht) {
+        // compact metric rows: where the 8 metric terms (and tinyarea) of a row segment are
+        // reproduced bit for bit from HTE / HTN (ice_grid.F90:341-367,1456,1536), the subcycle
+        // kernel fetches 2 planes instead of 8 (9) and recomputes; every other segment (the
+        // extrapolated row j = 1, halo-filled ghost rows, AusCOM's file tarea ...) keeps the planes
+        TRY(h2d(h, G_HTE, gr->HTE));
+        TRY(h2d(h, G_HTN, gr->HTN));
+        if (h->use_tma) {
+            MetricCheckArgs m;
+            m.hte = h->plane(G_HTE); m.htn = h->plane(G_HTN);
+            const int mp[8] = {G_DXT, G_DYT, G_DXHY, G_DYHX, G_CXP, G_CYP, G_CXM, G_CYM};
+            for (int q = 0; q < 8; ++q) m.met[q] = h->plane(mp[q]);
+            m.tinyarea = h->plane(G_TINYAREA);
+            m.ld = h->ld; m.nxl = h->g.nxl; m.ny = h->g.ny; m.flags = h->gflags(); m.flags_ld = h->tflags_ld;
+            dim3 grid(h->tstrips, (h->g.ny + 4 + 3) / 4);
+            metric_flags_kernel<<<grid, 128, 0, h->stream>>>(m);
+            CK(cudaGetLastError());
+        }
+    }
     TRY(h2d_i(h, 0, gr->tmask));
     TRY(h2d_i(h, 1, gr->umask));
     CK(cudaStreamSynchronize(h->stream));
@@ -630,10 +659,11 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
             t.a = a;
             t.plane_state = from_parity ? S_UB : S_UA;
             t.plane_t = kTGroup; t.plane_u = kUGroup;
+            t.puny = 1.0e-11;
             // waterx = uocn*cosw - vocn*sinw*sign(fm) is uocn itself (up to the sign of zero) when the
             // turning angle is zero: skip those two planes (ice_dyn_shared.F90:590-591)
             t.water_is_ocn = (h->cfg.cosw == 1.0 && h->cfg.sinw == 0.0) ? 1 : 0;
-            const CUtensorMap &mapU = t.water_is_ocn ? h->mapU9 : h->mapU;
+            const CUtensorMap &mapU = t.water_is_ocn ? h->mapU8 : h->mapU;
             t.strips = h->tstrips;
             t.tile_flags = h->tflags(); t.flags_ld = h->tflags_ld;
             const int slots = kTmaBlocksPerSM * h->sm_count;
@@ -644,11 +674,11 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
             const int grid = t.items < slots ? t.items : slots;
             const size_t smem = (size_t)kTmaStages * kStageBytes;
             if (last)
-                evp_subcycle_tma_kernel<true><<<grid, (kTmaConsumers + 1) * 32, smem, L.s()>>>(h->mapS, h->mapT11, mapU,
-                                                                                             h->mapM, t);
+                evp_subcycle_tma_kernel<true><<<grid, (kTmaConsumers + 1) * 32, smem, L.s()>>>(
+                    h->mapS, h->mapT1, h->mapT3, h->mapT4, h->mapT10, mapU, h->mapM, t);
             else
-                evp_subcycle_tma_kernel<false><<<grid, (kTmaConsumers + 1) * 32, smem, L.s()>>>(h->mapS, h->mapT10, mapU,
-                                                                                              h->mapM, t);
+                evp_subcycle_tma_kernel<false><<<grid, (kTmaConsumers + 1) * 32, smem, L.s()>>>(
+                    h->mapS, h->mapT1, h->mapT3, h->mapT4, h->mapT10, mapU, h->mapM, t);
             ++L.n;
             return EVP_OK;
         }
@@ -729,6 +759,7 @@ void build_program(evp_handle *h, double dt, Program &P)
             a.uocn = h->plane(I_UOCN); a.vocn = h->plane(I_VOCN); a.strairx = h->plane(O_STRAIRX);
             a.strairy = h->plane(O_STRAIRY); a.ss_tltx = h->plane(I_SSTLTX); a.ss_tlty = h->plane(I_SSTLTY);
             a.icetmask = h->plane(W_ICETMASK); a.strength_in = h->plane(I_STRENGTH);
+            a.rhow = cfg.rhow; a.Cw = h->plane(I_CW); a.vrelc = h->plane(W_VRELC);
             a.umask = h->iplane(1); a.iceumask = h->iplane(2);
             a.fm = h->plane(S_FM); a.strtltx = h->plane(O_STRTLTX); a.strtlty = h->plane(O_STRTLTY);
             a.strocnx = h->plane(O_STROCNX); a.strocny = h->plane(O_STROCNY);
@@ -748,7 +779,7 @@ void build_program(evp_handle *h, double dt, Program &P)
         if (h->use_tma) {   // per-strip row activity for the TMA producer
             dim3 grid(h->tstrips, (h->g.ny + 4 + 3) / 4);
             tile_flags_kernel<<<grid, 128, 0, s>>>(h->mask(), h->ldm, h->g.nxl, h->g.ny, h->tstrips, h->tflags(),
-                                                  h->tflags_ld);
+                                                  h->tflags_ld, h->gflags());
             item_list_kernel<<<1, 1024, 0, s>>>(h->tflags(), h->tflags_ld, h->tstrips, h->t_chunks, h->t_rpc, h->g.ny,
                                                 h->g.tripole ? 1 : 0, h->item_list(), h->item_count(), h->queue(0),
                                                 h->cfg.ndte);

@@ -253,8 +253,10 @@ __global__ void to_ugrid4_kernel(const __grid_constant__ ToUArgs a)
 // ---- evp_prep2 (+ ice_strength masking, + the loop's active-cell mask) --------------------------
 struct Prep2Args {
     Geom g;
-    double dt, a_min, m_min, cosw, sinw, gravit;
+    double dt, a_min, m_min, cosw, sinw, gravit, rhow;
     int tilt_mode, strength_masked;
+    const double *Cw;
+    double *vrelc;                              // aiu*rhow*Cw: the constant factor of stepu's vrel
     const double *aiu, *umass, *fcor, *uocn, *vocn, *strairx, *strairy, *ss_tltx, *ss_tlty;
     const double *icetmask, *strength_in;
     const int *umask;
@@ -318,6 +320,9 @@ __global__ void prep2_kernel(const __grid_constant__ Prep2Args a)
     a.strength[q] = st;
     a.waterx[q] = waterx; a.watery[q] = watery; a.forcex[q] = forcex; a.forcey[q] = forcey;
     a.umassdti[q] = umassdti;
+    // stepu evaluates vrel = aiu*rhow*Cw*sqrt(...) left to right (ice_dyn_shared.F90:708-709): the
+    // first two products do not change inside the loop -> one plane instead of two
+    a.vrelc[q] = a.aiu[q] * a.rhow * a.Cw[q];
     a.mask[(size_t)r * a.ldm + c] = (unsigned char)m;
     // active-cell counts (metric denominator); one atomic per warp
     const unsigned bt = __ballot_sync(__activemask(), m & 1u), bu = __ballot_sync(__activemask(), m & 2u);

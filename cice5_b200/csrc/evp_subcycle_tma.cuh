@@ -27,10 +27,10 @@ constexpr int kTmaBoxW = 32 * kTmaConsumers;                 // doubles per box 
 static_assert(kTmaBoxW <= 256, "TMA box dimensions are limited to 256 elements");
 constexpr int kTmaUCols = kTmaConsumers * kUColsPerWarp;     // 124
 #ifndef EVP_TMA_STAGES
-#define EVP_TMA_STAGES 3
+#define EVP_TMA_STAGES 2
 #endif
 #ifndef EVP_TMA_BLOCKS
-#define EVP_TMA_BLOCKS 2
+#define EVP_TMA_BLOCKS 3
 #endif
 #ifndef EVP_TMA_LATE
 #define EVP_TMA_LATE 1
@@ -40,7 +40,13 @@ constexpr int kTmaUCols = kTmaConsumers * kUColsPerWarp;     // 124
 constexpr bool kLateRelease = EVP_TMA_LATE != 0;
 constexpr int kTmaStages = EVP_TMA_STAGES;
 constexpr int kTmaBlocksPerSM = EVP_TMA_BLOCKS;
-constexpr int kStateDepth = 14, kTDepth = 11, kUDepth = 11;
+constexpr int kStateDepth = 14, kTDepth = 12, kUDepth = 10;
+// T slots of a stage (each kTmaBoxW doubles).  Compact row: 0 HTE, 1 HTN, 2 strength, 3 tinyarea;
+// full row: 0 strength, 1 tinyarea, 2..9 dxt dyt dxhy dyhx cxp cyp cxm cym; both: 10 tarear (last
+// subcycle), 11 HTN of this row when only the next row needs it (its southern HTN).
+constexpr int kSlotTarear = 10, kSlotHtnExtra = 11;
+// stage word bits written by the producer
+constexpr unsigned kMetaState = 1u, kMetaCompact = 2u, kMetaTinyFromMetrics = 4u, kMetaHtnExtra = 8u, kMetaT = 16u;
 constexpr int kMaskBoxW = 128 + 16;          // per mask box; kTmaBoxW / 128 boxes per row
 constexpr int kMaskBoxes = kTmaBoxW / 128;
 constexpr int kMaskFlagOff = 256 * (kMaskBoxes - 1) + kMaskBoxW + 48;     // stage word after the mask bytes (16-byte aligned)     // the byte mask is fetched from a 16-byte aligned column (TMA
@@ -61,6 +67,7 @@ struct TmaArgs {
     const unsigned char *tile_flags;   // [strip][ny + 4]: bit0 any active T cell, bit1 any active U cell
     int flags_ld;
     int water_is_ocn;            // cosw == 1 && sinw == 0: waterx/watery are not fetched (== uocn/vocn)
+    double puny;                 // tinyarea = puny*tarea (ice_grid.F90:354)
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void *p)
@@ -111,17 +118,31 @@ __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, u
         : "memory");
 }
 
+// dxt dyt dxhy dyhx cxp cyp cxm cym from HTE(i,j), HTE(i-1,j), HTN(i,j), HTN(i,j-1) exactly as the
+// reference builds them (ice_grid.F90:356-357,361-366,1456,1536)
+__device__ __forceinline__ void metric_terms(double hte, double hte_w, double htn, double htn_s, double *m)
+{
+    m[0] = __dmul_rn(0.5, __dadd_rn(htn, htn_s));                               // dxt
+    m[1] = __dmul_rn(0.5, __dadd_rn(hte, hte_w));                               // dyt
+    m[2] = __dmul_rn(0.5, __dsub_rn(hte, hte_w));                               // dxhy
+    m[3] = __dmul_rn(0.5, __dsub_rn(htn, htn_s));                               // dyhx
+    m[4] = __dsub_rn(__dmul_rn(1.5, htn), __dmul_rn(0.5, htn_s));               // cxp
+    m[5] = __dsub_rn(__dmul_rn(1.5, hte), __dmul_rn(0.5, hte_w));               // cyp
+    m[6] = -__dsub_rn(__dmul_rn(1.5, htn_s), __dmul_rn(0.5, htn));              // cxm
+    m[7] = -__dsub_rn(__dmul_rn(1.5, hte_w), __dmul_rn(0.5, hte));              // cym
+}
+
 template <bool LAST>
 __global__ void __launch_bounds__((kTmaConsumers + 1) * 32, kTmaBlocksPerSM)
-evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_constant__ CUtensorMap mapT,
-                        const __grid_constant__ CUtensorMap mapU, const __grid_constant__ CUtensorMap mapM,
-                        const __grid_constant__ TmaArgs p)
+evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_constant__ CUtensorMap mapT1,
+                        const __grid_constant__ CUtensorMap mapT3, const __grid_constant__ CUtensorMap mapT4,
+                        const __grid_constant__ CUtensorMap mapT10, const __grid_constant__ CUtensorMap mapU,
+                        const __grid_constant__ CUtensorMap mapM, const __grid_constant__ TmaArgs p)
 {
     extern __shared__ __align__(1024) unsigned char ring[];
     __shared__ unsigned long long full_bar[kTmaStages], empty_bar[kTmaStages];
     const LoopArgs &a = p.a;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    constexpr int kTUsed = LAST ? kTDepth : kTDepth - 1;       // tarear only on the last subcycle
 
     if (threadIdx.x == 0) {
 #pragma unroll
@@ -163,21 +184,38 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     const bool needT = j >= r0 && ((f0 & 1u) || top);
                     const bool needU = j > r0 && ((fm1 & 2u) || top);
                     const bool needS = ((f0 | f1) & 1u) || (f0 & 2u) || top;
+                    const bool cmp = (f0 & 4u) != 0u, tinym = (f0 & 8u) != 0u;
+                    // the next row, if compact, recomputes its metrics from HTN of this row too
+                    const bool nextT = j + 1 <= rend && ((f1 & 1u) || j + 1 >= a.ny - 2) && (f1 & 4u);
+                    const bool htn_extra = nextT && !(needT && cmp);
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
                     unsigned char *sb = ring + (size_t)stage * kStageBytes;
+                    unsigned char *tb = sb + kStateDepth * kTmaBoxW * 8;
                     unsigned char *mk = sb + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8;
-                    *reinterpret_cast<volatile unsigned *>(mk + kMaskFlagOff) = needS ? 1u : 0u;
+                    *reinterpret_cast<volatile unsigned *>(mk + kMaskFlagOff) =
+                        (needS ? kMetaState : 0u) | (cmp ? kMetaCompact : 0u) | (tinym ? kMetaTinyFromMetrics : 0u) |
+                        (htn_extra ? kMetaHtnExtra : 0u) | (needT ? kMetaT : 0u);
                     *reinterpret_cast<volatile int *>(mk + kMaskFlagOff + 4) = item;
+                    const int tdepth = cmp ? (tinym ? 3 : 4) : 10;
                     unsigned bytes = kMaskBoxW * kMaskBoxes;
                     if (needS) bytes += kStateDepth * kTmaBoxW * 8;
-                    if (needT) bytes += kTUsed * kTmaBoxW * 8;
+                    if (needT) bytes += (tdepth + (LAST ? 1 : 0)) * kTmaBoxW * 8;
+                    if (htn_extra) bytes += kTmaBoxW * 8;
                     if (needU) bytes += (p.water_is_ocn ? kUDepth - 2 : kUDepth) * kTmaBoxW * 8;
                     mbar_expect_tx(&full_bar[stage], bytes);
 #pragma unroll
                     for (int mb = 0; mb < kMaskBoxes; ++mb)
                         tma_load_2d(mk + mb * 256, &mapM, &full_bar[stage], (x0 & ~15) + mb * 128, j);
                     if (needS) tma_load_3d(sb, &mapS, &full_bar[stage], x0, j, p.plane_state);
-                    if (needT) tma_load_3d(sb + kStateDepth * kTmaBoxW * 8, &mapT, &full_bar[stage], x0, j, p.plane_t);
+                    if (needT) {
+                        if (!cmp) tma_load_3d(tb, &mapT10, &full_bar[stage], x0, j, p.plane_t + 2);
+                        else if (tinym) tma_load_3d(tb, &mapT3, &full_bar[stage], x0, j, p.plane_t);
+                        else tma_load_3d(tb, &mapT4, &full_bar[stage], x0, j, p.plane_t);
+                        if (LAST)
+                            tma_load_3d(tb + kSlotTarear * kTmaBoxW * 8, &mapT1, &full_bar[stage], x0, j, p.plane_t + 12);
+                    }
+                    if (htn_extra)
+                        tma_load_3d(tb + kSlotHtnExtra * kTmaBoxW * 8, &mapT1, &full_bar[stage], x0, j, p.plane_t + 1);
                     if (needU)
                         tma_load_3d(sb + (kStateDepth + kTDepth) * kTmaBoxW * 8, &mapU, &full_bar[stage], x0, j - 1,
                                     p.plane_u);
@@ -209,11 +247,14 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
 
         // row r0-1: velocities only
         double u_s, v_s, uw_s, vw_s;
+        double htn_s = 0.0;                                             // HTN of the row below (compact rows)
         bool loaded_s;                                                  // state of the row below was fetched
         {
             const double *st = reinterpret_cast<const double *>(ring + (size_t)stage * kStageBytes);
-            loaded_s = *reinterpret_cast<const unsigned *>(
-                           ring + (size_t)stage * kStageBytes + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8 + kMaskFlagOff) != 0u;
+            const unsigned meta = *reinterpret_cast<const unsigned *>(
+                ring + (size_t)stage * kStageBytes + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8 + kMaskFlagOff);
+            loaded_s = (meta & kMetaState) != 0u;
+            if (meta & kMetaHtnExtra) htn_s = st[(kStateDepth + kSlotHtnExtra) * kTmaBoxW + bi];
             u_s = st[bi]; v_s = st[kTmaBoxW + bi]; uw_s = st[bi - 1]; vw_s = st[kTmaBoxW + bi - 1];
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty_bar[stage]);
@@ -228,7 +269,8 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             const double *tc = st + kStateDepth * kTmaBoxW;
             const double *uc = tc + kTDepth * kTmaBoxW;
             const unsigned char *mk = reinterpret_cast<const unsigned char *>(uc + kUDepth * kTmaBoxW);
-            const bool loaded_c = *reinterpret_cast<const unsigned *>(mk + kMaskFlagOff) != 0u;
+            const unsigned meta = *reinterpret_cast<const unsigned *>(mk + kMaskFlagOff);
+            const bool loaded_c = (meta & kMetaState) != 0u;
             const double u_c = st[bi], v_c = st[kTmaBoxW + bi];
             const double uw_c = st[bi - 1], vw_c = st[kTmaBoxW + bi - 1];
             const int mpos = bi + mshift;                               // mask box b covers bytes [128 b, 128 b + 144)
@@ -238,19 +280,37 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             const bool uact = warp_on && ucol && (mprev & 2u) && r > r0;
             const bool any_t = __ballot_sync(0xffffffffu, tact) != 0u;
             const bool any_u = __ballot_sync(0xffffffffu, uact) != 0u;
-            double s[12], tco[kTDepth], uco[kUDepth];
+            double s[12], tco[11], uco[kUDepth];
+            // tco: dxt dyt dxhy dyhx cxp cyp cxm cym tinyarea strength tarear
             if (any_t) {
 #pragma unroll
                 for (int q = 0; q < 12; ++q) s[q] = st[(2 + q) * kTmaBoxW + bi];
+                if (meta & kMetaCompact) {
+                    // metric terms from HTE (this cell and its western neighbour) and HTN (this
+                    // row and the row below), the reference's own formulas (ice_grid.F90:354-367,
+                    // 1456,1536); set_grid checked that they reproduce the host arrays bit for bit
+                    // on this row segment.  Explicit _rn intrinsics: never contracted.
+                    const double hte = tc[bi], hte_w = tc[bi - 1], htn = tc[kTmaBoxW + bi];
+                    metric_terms(hte, hte_w, htn, htn_s, tco);
+                    tco[9] = tc[2 * kTmaBoxW + bi];
+                    tco[8] = (meta & kMetaTinyFromMetrics) ? __dmul_rn(p.puny, __dmul_rn(tco[0], tco[1]))
+                                                           : tc[3 * kTmaBoxW + bi];
+                } else {
+                    tco[9] = tc[bi]; tco[8] = tc[kTmaBoxW + bi];
 #pragma unroll
-                for (int q = 0; q < kTUsed; ++q) tco[q] = tc[q * kTmaBoxW + bi];
+                    for (int q = 0; q < 8; ++q) tco[q] = tc[(2 + q) * kTmaBoxW + bi];
+                }
+                if (LAST) tco[10] = tc[kSlotTarear * kTmaBoxW + bi];
             }
+            // southern HTN of the next row
+            if ((meta & (kMetaCompact | kMetaT)) == (kMetaCompact | kMetaT)) htn_s = tc[kTmaBoxW + bi];
+            else if (meta & kMetaHtnExtra) htn_s = tc[kSlotHtnExtra * kTmaBoxW + bi];
             if (!kLateRelease) {
                 if (any_u) {
 #pragma unroll
                     for (int q = 0; q < kUDepth - 2; ++q) uco[q] = uc[q * kTmaBoxW + bi];
+                    uco[8] = p.water_is_ocn ? uco[1] : uc[8 * kTmaBoxW + bi];
                     uco[9] = p.water_is_ocn ? uco[2] : uc[9 * kTmaBoxW + bi];
-                    uco[10] = p.water_is_ocn ? uco[3] : uc[10 * kTmaBoxW + bi];
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&empty_bar[stage]);          // slot free: everything is in registers
@@ -261,12 +321,11 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             double str[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
             if (tact) {
                 double divu, shear, rdg_conv, rdg_shear, prs_sig;
-                // tco: dxt dyt dxhy dyhx cxp cyp cxm cym tinyarea strength [tarear]
 #ifdef EVP_TMA_NOCOMPUTE   /* timing experiment only: data path without the arithmetic */
                 for (int q = 0; q < 8; ++q) str[q] = s[q] + tco[q] + u_c + uw_c + v_c + vw_c; divu = shear = rdg_conv = rdg_shear = prs_sig = 0.0;
 #else
                 stress_cell<LAST>(k, u_c, uw_c, u_s, uw_s, v_c, vw_c, v_s, vw_s, tco[0], tco[1], tco[2], tco[3],
-                                  tco[4], tco[5], tco[6], tco[7], tco[8], tco[9], LAST ? tco[kTDepth - 1] : 0.0, s,
+                                  tco[4], tco[5], tco[6], tco[7], tco[8], tco[9], LAST ? tco[10] : 0.0, s,
                                   str, divu, shear, rdg_conv, rdg_shear, prs_sig);
 #endif
                 if (tstore_col && (r < rend || r == a.ny + 1)) {
@@ -288,27 +347,27 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     if (kLateRelease) {
 #pragma unroll
                         for (int q = 0; q < kUDepth - 2; ++q) uco[q] = uc[q * kTmaBoxW + bi];
+                        uco[8] = p.water_is_ocn ? uco[1] : uc[8 * kTmaBoxW + bi];
                         uco[9] = p.water_is_ocn ? uco[2] : uc[9 * kTmaBoxW + bi];
-                        uco[10] = p.water_is_ocn ? uco[3] : uc[10 * kTmaBoxW + bi];
                     }
-                    // uco: aiu Cw uocn vocn forcex forcey umassdti fm uarear waterx watery
+                    // uco: aiu*rhow*Cw uocn vocn forcex forcey umassdti fm uarear waterx watery
                     const double uold = u_s, vold = v_s;
-                    const double du = uco[2] - uold, dv = uco[3] - vold;
+                    const double du = uco[1] - uold, dv = uco[2] - vold;
 #ifdef EVP_TMA_NOCOMPUTE
-                    const double vrel = uco[0] + uco[1] + du + dv;
+                    const double vrel = uco[0] + du + dv;
 #else
-                    const double vrel = uco[0] * k.rhow * uco[1] * sqrt(du * du + dv * dv);
+                    const double vrel = uco[0] * sqrt(du * du + dv * dv);
 #endif
-                    const double taux = vrel * uco[9], tauy = vrel * uco[10];
-                    const double umdt = uco[6], fm = uco[7];
+                    const double taux = vrel * uco[8], tauy = vrel * uco[9];
+                    const double umdt = uco[5], fm = uco[6];
                     const double cca = (k.brlx + k.revp) * umdt + vrel * k.cosw;
                     const double ccb = fm + copysign(1.0, fm) * vrel * k.sinw;
                     const double ab2 = cca * cca + ccb * ccb;
-                    const double uar = uco[8];
+                    const double uar = uco[7];
                     const double strintx = uar * (s1p + n2p + str[2] + e4);
                     const double strinty = uar * (s5p + str[5] + n7p + e8);
-                    const double cc1 = strintx + uco[4] + taux + umdt * (k.brlx * uold);
-                    const double cc2 = strinty + uco[5] + tauy + umdt * (k.brlx * vold);
+                    const double cc1 = strintx + uco[3] + taux + umdt * (k.brlx * uold);
+                    const double cc2 = strinty + uco[4] + tauy + umdt * (k.brlx * vold);
 #ifdef EVP_TMA_NOCOMPUTE
                     unew = cca + cc1 + ab2; vnew = ccb + cc2;
 #else
@@ -344,7 +403,7 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
 // Row activity of every strip, once per evp call (the masks are fixed for the call): lets the
 // producer skip the TMA boxes of row segments without ice (land, open ocean).
 __global__ void tile_flags_kernel(const unsigned char *mask, int ldm, int nxl, int ny, int strips,
-                                  unsigned char *flags, int flags_ld)
+                                  unsigned char *flags, int flags_ld, const unsigned char *gflags)
 {
     const int strip = blockIdx.x, r = blockIdx.y * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (r > ny + 3) return;
@@ -361,7 +420,44 @@ __global__ void tile_flags_kernel(const unsigned char *mask, int ldm, int nxl, i
         }
     }
     f = __reduce_or_sync(0xffffffffu, f);
-    if (lane == 0) flags[(size_t)strip * flags_ld + r] = (unsigned char)f;
+    if (lane == 0)
+        flags[(size_t)strip * flags_ld + r] = (unsigned char)(f | (gflags[(size_t)strip * flags_ld + r] & 12u));
+}
+
+// Once per set_grid: which row segments of which strips can use compact metric rows.  bit2: the 8
+// metric terms of every T cell of the segment equal metric_terms(HTE, HTN) bit for bit; bit3: so
+// does tinyarea = puny*(dxt*dyt).  All cells are checked, ocean or not.
+struct MetricCheckArgs {
+    const double *hte, *htn, *met[8], *tinyarea;
+    int ld, nxl, ny;
+    unsigned char *flags;
+    int flags_ld;
+};
+__global__ void metric_flags_kernel(const __grid_constant__ MetricCheckArgs a)
+{
+    const int strip = blockIdx.x, r = blockIdx.y * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (r > a.ny + 3) return;
+    unsigned bad = 0;                                          // bit0: a metric differs, bit1: tinyarea differs
+    if (r >= 1 && r <= a.ny + 1) {
+        const int c0 = 1 + strip * kTmaUCols;
+        for (int q = lane; q <= kTmaUCols; q += 32) {
+            const int c = c0 + q;
+            if (c > a.nxl + 1) continue;
+            const size_t i = (size_t)r * a.ld + c;
+            double m[8];
+            metric_terms(a.hte[i], a.hte[i - 1], a.htn[i], a.htn[i - a.ld], m);
+#pragma unroll
+            for (int t = 0; t < 8; ++t)
+                if (__double_as_longlong(m[t]) != __double_as_longlong(a.met[t][i])) bad |= 1u;
+            const double tiny = __dmul_rn(1.0e-11, __dmul_rn(m[0], m[1]));
+            if (__double_as_longlong(tiny) != __double_as_longlong(a.tinyarea[i])) bad |= 2u;
+        }
+    } else {
+        bad = 3u;
+    }
+    bad = __reduce_or_sync(0xffffffffu, bad);
+    if (lane == 0)
+        a.flags[(size_t)strip * a.flags_ld + r] = (unsigned char)((bad & 1u) ? 0u : ((bad & 2u) ? 4u : 12u));
 }
 
 // The work list of the call: the (strip, row chunk) items that hold ice, in item order (one block,
@@ -386,7 +482,7 @@ __global__ void item_list_kernel(const unsigned char *flags, int flags_ld, int s
             const int r0 = 1 + chunk * rpc, rend = min(r0 + rpc, ny + 1);
             const unsigned char *fl = flags + (size_t)strip * flags_ld;
             unsigned f = 0;
-            for (int j = r0 - 1; j <= rend + 1; ++j) f |= fl[j];
+            for (int j = r0 - 1; j <= rend + 1; ++j) f |= fl[j] & 3u;    // activity bits only
             keep = f != 0u || (tripole && rend >= ny - 2);
         }
         const unsigned b = __ballot_sync(0xffffffffu, keep);

@@ -41,7 +41,7 @@ OUT_R8 = ("strairx", "strairy", "strtltx", "strtlty", "strocnx", "strocny", "str
 
 
 class GridS(C.Structure):
-    _fields_ = [(n, _DP) for n in GRID_R8] + [("tmask", _IP), ("umask", _IP)]
+    _fields_ = [(n, _DP) for n in GRID_R8] + [("tmask", _IP), ("umask", _IP), ("HTE", _DP), ("HTN", _DP)]
 
 
 class InS(C.Structure):
@@ -121,8 +121,9 @@ class EvpGpu:
                  ew_cyclic=True, ns_boundary="open", grid_tripole=False, tilt_mode=0,
                  strength_masked=0, cosw=1.0, sinw=0.0, rhow=1026.0, rhoi=917.0, rhos=330.0,
                  gravit=9.80616, a_min=1.0e-3, m_min=1.0e-2, kdyn=1, revised_evp=False,
-                 use_cuda_graph=False, strict=True):
+                 use_cuda_graph=False, strict=True, compact_metrics=True):
         self.lib = load_library(strict)
+        self.compact_metrics = compact_metrics      # pass HTE / HTN to set_grid when the grid has them
         ns = {"open": 0, "closed": 1, "tripole": 2}[ns_boundary]
         if nx_global % nranks:
             raise EvpError("nranks must divide nx_global")
@@ -159,6 +160,8 @@ class EvpGpu:
             if f[n].shape != self.shape:
                 raise EvpError(f"grid array {n} has shape {f[n].shape}, expected {self.shape}")
         g = GridS(**{n: _dp(f[n]) for n in GRID_R8}, tmask=_ip(f["tmask"]), umask=_ip(f["umask"]))
+        if f.get("HTE") is not None and f.get("HTN") is not None and self.compact_metrics:
+            g.HTE, g.HTN = _dp(f["HTE"]), _dp(f["HTN"])     # optional: compact metric rows
         self._check(self.lib.evp_gpu_set_grid(self._h, C.byref(g)))
 
     @staticmethod
@@ -276,7 +279,7 @@ class EvpGroup:
         return {k: self._fx.slab(v, r, self.n) for k, v in d.items() if v is not None}
 
     def set_grid(self, f):
-        names = GRID_R8 + ("tmask", "umask")
+        names = GRID_R8 + ("tmask", "umask") + tuple(k for k in ("HTE", "HTN") if f.get(k) is not None)
         for r, e in enumerate(self.ranks):
             e.set_grid(self._slabs({k: f[k] for k in names}, r))
 

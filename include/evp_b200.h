@@ -69,6 +69,10 @@ typedef struct {
     const double *dxt, *dyt, *dxhy, *dyhx, *cxp, *cyp, *cxm, *cym;
     const double *tarea, *uarea, *tarear, *uarear, *tinyarea, *fcor;
     const int *tmask, *umask;
+    /* optional (NULL = not given): HTE, HTN (ice_grid.F90:51-52).  Where the metric terms above
+     * are reproduced bit for bit from them (verified cell by cell at set_grid), the subcycle
+     * kernel fetches HTE / HTN instead of the 8 (9) derived planes; results are identical. */
+    const double *HTE, *HTN;
 } evp_grid_t;
 
 /* Per-call inputs (ice_state.F90:54-56,155; ice_flux.F90:37-48; ice_atmo.F90:40). */

@@ -36,7 +36,7 @@ def main():
     sl = lambda d: {k: fx.slab(v, rank, world) for k, v in d.items()}
     e = evp.EvpGpu.for_domain(dom, args.ndte, case.dt, rank=rank, nranks=world, device=local,
                               strict=True, use_cuda_graph=bool(args.graph))
-    e.set_grid(sl({k: grid.f[k] for k in evp.GRID_R8 + ("tmask", "umask")}))
+    e.set_grid(sl({k: grid.f[k] for k in evp.GRID_R8 + ("tmask", "umask", "HTE", "HTN")}))
     blobs = [None] * world
     dist.all_gather_object(blobs, e.peer_blob())
     e.set_peers(blobs)

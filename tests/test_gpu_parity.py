@@ -202,3 +202,34 @@ def test_ten_day_run_gx3_bitwise(subcycle_kernel):
     assert rep["oracle_umax_final"] > 1e-3          # the ice is really moving
     for n in STATE:
         assert rep["fields"]["strict"][n]["max_inf"] == 0.0
+
+
+@pytest.mark.parametrize("grid,scenario", [("gx3", "full"), ("tp1", "caps")])
+def test_full_metric_planes_path_bitwise(grid, scenario):
+    """Without HTE / HTN (evp_grid_t.HTE = NULL) every row uses the 10-plane T box: same bits."""
+    case = fx.make_case(grid, scenario, ndte=120)
+    ref = _oracle(case)
+    got = clone_case(case)
+    evp.run_case(got, strict=True, compact_metrics=False)
+    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+
+
+def test_inconsistent_hte_falls_back_to_planes():
+    """HTE / HTN that do NOT reproduce the metric arrays (here: perturbed in the last bit on a band of
+    rows) must be detected at set_grid and those row segments must keep using the planes."""
+    grid = fx.make_grid("tp1")
+    case = fx.make_case(grid, "full", ndte=30)
+    ref = _oracle(case)
+    got = clone_case(case)
+    f = dict(grid.f)
+    f["HTE"] = grid.f["HTE"].copy()
+    f["HTN"] = grid.f["HTN"].copy()
+    f["HTE"][100:180, :] = np.nextafter(f["HTE"][100:180, :], np.inf)
+    f["HTN"][150:220, 50:90] *= 1.0000001
+    e = evp.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True)
+    try:
+        e.set_grid(f)
+        e.evp(case.dt, got.inp, got.io, got.out)
+    finally:
+        e.close()
+    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
