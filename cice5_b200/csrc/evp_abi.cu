@@ -90,7 +90,7 @@ struct evp_handle {
     int tflags_ld = 0, tstrips = 0;
     int t_rpc = 0, t_chunks = 0, t_items = 0;    // TMA kernel work items: (strip, chunk of t_rpc rows)
     size_t off_gflags = 0;                       // per strip row: bit2 metrics, bit3 tinyarea reproducible from HTE/HTN
-    size_t off_queue = 0;                        // int queue[ndte], int item_count, int item_list[t_items]
+    size_t off_queue = 0;                        // int queue[ndte], done[ndte], item_count, item_list[t_items]
     char *peer_arena[kMaxRanks] = {nullptr};
     bool peer_opened[kMaxRanks] = {false};
     bool grid_set = false, uploaded = false, peers_set = false;
@@ -131,8 +131,9 @@ struct evp_handle {
     unsigned char *tflags() const { return reinterpret_cast<unsigned char *>(arena + off_tflags); }
     unsigned char *gflags() const { return reinterpret_cast<unsigned char *>(arena + off_gflags); }
     int *queue(int ksub) const { return reinterpret_cast<int *>(arena + off_queue) + ksub; }
-    int *item_count() const { return reinterpret_cast<int *>(arena + off_queue) + cfg.ndte; }
-    int *item_list() const { return reinterpret_cast<int *>(arena + off_queue) + cfg.ndte + 1; }
+    int *done(int ksub) const { return reinterpret_cast<int *>(arena + off_queue) + cfg.ndte + ksub; }
+    int *item_count() const { return reinterpret_cast<int *>(arena + off_queue) + 2 * cfg.ndte; }
+    int *item_list() const { return reinterpret_cast<int *>(arena + off_queue) + 2 * cfg.ndte + 1; }
     unsigned long long *counts() const
     {
         return reinterpret_cast<unsigned long long *>(arena + off_counts);
@@ -316,7 +317,7 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
         h->t_chunks = (g.ny + h->t_rpc - 1) / h->t_rpc;
         h->t_items = h->tstrips * h->t_chunks;
     }
-    h->off_queue = off;  off = align_up(off + ((size_t)cfg->ndte + 1 + h->t_items) * sizeof(int), 256);
+    h->off_queue = off;  off = align_up(off + (2 * (size_t)cfg->ndte + 1 + h->t_items) * sizeof(int), 256);
     h->arena_bytes = off;
     cudaError_t e = cudaMalloc(&h->arena, h->arena_bytes);
     if (e != cudaSuccess) {
@@ -648,7 +649,11 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
 {
     evp_handle *h = B.h;
     const int buf = (B.seq++) & 1;
-    B.op([h, from_parity, last, buf, ksub](Launcher &L) {
+    // N > 1 on a tripole grid with the TMA kernel: the cross-rank barrier between the subcycle
+    // kernel and the fold is fused into both -- the last CTA to finish signals the peers, the fold
+    // kernel waits for theirs -- 2 launches per subcycle instead of 4
+    const bool fused_sync = h->cfg.nranks > 1 && h->use_tma && h->g.tripole;
+    B.op([h, from_parity, last, buf, ksub, fused_sync](Launcher &L) {
         const Geom &g = h->g;
         LoopArgs a;
         fill_loop_args(h, from_parity, buf, a);
@@ -671,6 +676,9 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
             t.chunks = h->t_chunks;
             t.items = h->t_items;
             t.queue = h->queue(ksub - 1); t.item_list = h->item_list(); t.item_count = h->item_count();
+            t.fused_signal = fused_sync ? 1 : 0;
+            t.done = h->done(ksub - 1);
+            fill_sync_args(h, t.sync);
             const int grid = t.items < slots ? t.items : slots;
             const size_t smem = (size_t)kTmaStages * kStageBytes;
             if (last)
@@ -689,13 +697,15 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
         ++L.n;
         return EVP_OK;
     });
-    B.sync();
+    if (!fused_sync) B.sync();
     if (h->g.tripole) {
-        B.op([h, from_parity, buf](Launcher &L) {
+        B.op([h, from_parity, buf, fused_sync](Launcher &L) {
             const Geom &g = h->g;
             double *u1 = h->plane(from_parity ? S_UA : S_UB), *v1 = h->plane(from_parity ? S_VA : S_VB);
+            SyncArgs sa;
+            fill_sync_args(h, sa);
             fold_uv_kernel<<<(g.nxl + 2 + 127) / 128, 128, 0, L.s()>>>(u1, v1, g.ld, g.nxl, g.ny, g.nx_global, g.lo,
-                                                                     h->inbox(buf), g.inbox_ld);
+                                                                     h->inbox(buf), g.inbox_ld, sa, fused_sync ? 1 : 0);
             ++L.n;
             return EVP_OK;
         });
@@ -782,7 +792,7 @@ void build_program(evp_handle *h, double dt, Program &P)
                                                   h->tflags_ld, h->gflags());
             item_list_kernel<<<1, 1024, 0, s>>>(h->tflags(), h->tflags_ld, h->tstrips, h->t_chunks, h->t_rpc, h->g.ny,
                                                 h->g.tripole ? 1 : 0, h->item_list(), h->item_count(), h->queue(0),
-                                                h->cfg.ndte);
+                                                2 * h->cfg.ndte);
             L.n += 2;
         }
         CK(cudaGetLastError());

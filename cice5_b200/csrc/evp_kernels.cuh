@@ -329,12 +329,64 @@ __device__ __forceinline__ void fold_necorner_column(double *plane, int ld, int 
     plane[(size_t)(ny + 1) * ld + c] = sgn * src_below;
 }
 
+// ---- cross-rank synchronisation (one rank per GPU; flags live in every rank's arena) ------------
+// signal: bump my epoch and store it into slot [my rank] of every peer's flag array.
+// wait:   spin until every peer's slot in MY flag array has reached my epoch.
+// Every rank executes the same sequence of halo operations, so epochs advance in lock step.
+struct SyncArgs {
+    int rank, nranks;
+    unsigned long long *epoch;                    // mine
+    unsigned long long *flags[kMaxRanks];         // flag arrays of all ranks (peer pointers)
+    int *error;                                   // mine; set on time-out
+    unsigned long long timeout_ns;
+};
+
+// one thread: everything this rank stored before (made visible to it by fences / barriers) is
+// released to the peers together with the new epoch
+__device__ __forceinline__ void peer_signal(const SyncArgs &a)
+{
+    const unsigned long long e = *(volatile unsigned long long *)a.epoch + 1;
+    *(volatile unsigned long long *)a.epoch = e;
+    __threadfence_system();
+    for (int r = 0; r < a.nranks; ++r)
+        if (r != a.rank) {
+            unsigned long long *p = a.flags[r] + a.rank;
+            asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(e) : "memory");
+        }
+}
+
+// thread r < nranks waits for peer r; callers follow with __syncthreads + __threadfence_system
+__device__ __forceinline__ void peer_wait(const SyncArgs &a, int r)
+{
+    if (r < a.nranks && r != a.rank) {
+        const unsigned long long e = *(volatile unsigned long long *)a.epoch;
+        const unsigned long long *p = a.flags[a.rank] + r;
+        unsigned long long t0, t1, v;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+            if (v >= e) break;
+            if (*(volatile int *)a.error) break;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > a.timeout_ns) { *(volatile int *)a.error = 1; break; }
+            __nanosleep(100);
+        }
+    }
+}
+
 // Fold of the freshly stepped (u, v): one thread per local column, ghost columns included (their
 // row-ny value was pushed into the plane by the E-W neighbour's subcycle kernel).
 // inbox rows: [0] u row ny-1, [1] u row ny, [2] v row ny-1, [3] v row ny of the fold source.
+// do_wait: first wait until every peer has signalled the end of its subcycle kernel (the barrier
+// that otherwise is the separate halo_wait_kernel).
 __global__ void fold_uv_kernel(double *u, double *v, int ld, int nxl, int ny, int nx, int lo,
-                               const double *inbox, int inbox_ld)
+                               const double *inbox, int inbox_ld, const __grid_constant__ SyncArgs sa, int do_wait)
 {
+    if (do_wait) {
+        peer_wait(sa, threadIdx.x);
+        __syncthreads();
+        __threadfence_system();
+    }
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c > nxl + 1) return;
     int ig = lo + c;

@@ -140,48 +140,15 @@ __global__ void halo_stress_apply_kernel(double *a1, Geom g, InboxGeom ib, doubl
     }
 }
 
-// ---- cross-rank synchronisation (one rank per GPU; flags live in every rank's arena) ------------
-// signal: bump my epoch and store it into slot [my rank] of every peer's flag array.
-// wait:   spin until every peer's slot in MY flag array has reached my epoch.
-// Every rank executes the same sequence of halo operations, so epochs advance in lock step.
-struct SyncArgs {
-    int rank, nranks;
-    unsigned long long *epoch;                    // mine
-    unsigned long long *flags[kMaxRanks];         // flag arrays of all ranks (peer pointers)
-    int *error;                                   // mine; set on time-out
-    unsigned long long timeout_ns;
-};
-
+// ---- cross-rank synchronisation: SyncArgs, peer_signal, peer_wait live in evp_kernels.cuh ---------
 __global__ void halo_signal_kernel(const __grid_constant__ SyncArgs a)
 {
-    __shared__ unsigned long long e;
-    if (threadIdx.x == 0) { e = *a.epoch + 1; *a.epoch = e; }
-    __syncthreads();
-    __threadfence_system();
-    const int r = threadIdx.x;
-    if (r < a.nranks && r != a.rank) {
-        unsigned long long *p = a.flags[r] + a.rank;
-        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(e) : "memory");
-    }
+    if (threadIdx.x == 0) peer_signal(a);
 }
 
 __global__ void halo_wait_kernel(const __grid_constant__ SyncArgs a)
 {
-    const int r = threadIdx.x;
-    if (r < a.nranks && r != a.rank) {
-        const unsigned long long e = *(volatile unsigned long long *)a.epoch;
-        const unsigned long long *p = a.flags[a.rank] + r;
-        unsigned long long t0, t1, v;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-        for (;;) {
-            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-            if (v >= e) break;
-            if (*(volatile int *)a.error) break;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-            if (t1 - t0 > a.timeout_ns) { *(volatile int *)a.error = 1; break; }
-            __nanosleep(200);
-        }
-    }
+    peer_wait(a, threadIdx.x);
     __syncthreads();
     __threadfence_system();
 }

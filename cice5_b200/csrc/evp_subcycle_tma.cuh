@@ -68,6 +68,11 @@ struct TmaArgs {
     int flags_ld;
     int water_is_ocn;            // cosw == 1 && sinw == 0: waterx/watery are not fetched (== uocn/vocn)
     double puny;                 // tinyarea = puny*tarea (ice_grid.F90:354)
+    // fused cross-rank signal: every CTA counts itself in `done` when its stores are out; the last
+    // one bumps the epoch and releases it to the peers (what halo_signal_kernel does otherwise)
+    int fused_signal;
+    int *done;
+    SyncArgs sync;
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void *p)
@@ -396,6 +401,17 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             }
             s1p = str[0]; s5p = str[4]; n2p = e2; n7p = e7;
             u_s = u_c; v_s = v_c; uw_s = uw_c; vw_s = vw_c; mprev = m; loaded_s = loaded_c;
+        }
+    }
+    if (p.fused_signal) {
+        __threadfence_system();                                         // my stores (peer ghosts, inboxes) are out
+        asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
+        if (threadIdx.x == 0) {
+            __threadfence_system();
+            if (atomicAdd(p.done, 1) == (int)gridDim.x - 1) {
+                __threadfence_system();
+                peer_signal(p.sync);
+            }
         }
     }
 }
