@@ -242,6 +242,16 @@ def main():
     wall_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.stop() if rank == 0 else None
     st = e.stats()
+    if os.environ.get("EVP_B200_TRACE"):
+        # per-subcycle timeline of the last call (device globaltimer): where the time between two
+        # subcycle kernels goes at N > 1
+        tr = e.trace().astype(np.int64)
+        k = tr[:-1]
+        med = lambda x: float(np.median(x)) / 1e3
+        print(f"[trace rank {rank}] us (median over subcycles; signal..wait only at N > 1): kernel {med(k[:, 1] - k[:, 0]):.1f}  "
+              f"signal {med(k[:, 2] - k[:, 1]):.1f}  to-fold {med(k[:, 3] - k[:, 2]):.1f}  "
+              f"wait {med(k[:, 4] - k[:, 3]):.1f}  fold+next-launch {med(tr[1:, 0] - k[:, 4]):.1f}  "
+              f"period {med(tr[1:, 0] - k[:, 0]):.1f}", file=sys.stderr, flush=True)
     act_t, act_u = st.active_t_cells, st.active_u_cells
     loop_launches = st.loop_kernel_launches
 

@@ -89,6 +89,8 @@ struct evp_handle {
     size_t off_planes = 0, off_inbox = 0, off_flags = 0, off_int = 0, off_mask = 0, off_counts = 0, off_tflags = 0;
     int tflags_ld = 0, tstrips = 0;
     int t_rpc = 0, t_chunks = 0, t_items = 0;    // TMA kernel work items: (strip, chunk of t_rpc rows)
+    size_t off_trace = 0;                        // u64 trace[ndte][8] (EVP_B200_TRACE=1)
+    bool trace_on = false;
     size_t off_gflags = 0;                       // per strip row: bit2 metrics, bit3 tinyarea reproducible from HTE/HTN
     size_t off_queue = 0;                        // int queue[ndte], done[ndte], item_count, item_list[t_items]
     char *peer_arena[kMaxRanks] = {nullptr};
@@ -131,6 +133,10 @@ struct evp_handle {
     unsigned char *tflags() const { return reinterpret_cast<unsigned char *>(arena + off_tflags); }
     unsigned char *gflags() const { return reinterpret_cast<unsigned char *>(arena + off_gflags); }
     int *queue(int ksub) const { return reinterpret_cast<int *>(arena + off_queue) + ksub; }
+    unsigned long long *trace(int ksub) const
+    {
+        return trace_on ? reinterpret_cast<unsigned long long *>(arena + off_trace) + 8 * (size_t)ksub : nullptr;
+    }
     int *done(int ksub) const { return reinterpret_cast<int *>(arena + off_queue) + cfg.ndte + ksub; }
     int *item_count() const { return reinterpret_cast<int *>(arena + off_queue) + 2 * cfg.ndte; }
     int *item_list() const { return reinterpret_cast<int *>(arena + off_queue) + 2 * cfg.ndte + 1; }
@@ -310,13 +316,26 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
         int sms = 148;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device);
         const long long slots = (long long)kTmaBlocksPerSM * sms;
-        long long rpc = ((long long)h->tstrips * g.ny + 8 * slots - 1) / (8 * slots);
+        // rows per item: makespan of uniform items over the CTA slots = rounds x (rows + the
+        // redundant first row); among the heights within 3 % of the best take the smallest (more,
+        // smaller items even out land / open ocean through the dynamic queue)
+        double best = 1e300;
+        double cost[49];
+        for (int r = 4; r <= 48; ++r) {
+            const long long items = (long long)h->tstrips * ((g.ny + r - 1) / r);
+            cost[r] = (double)((items + slots - 1) / slots) * (r + 1.0);
+            if (cost[r] < best) best = cost[r];
+        }
+        long long rpc = 48;
+        for (int r = 4; r <= 48; ++r) if (cost[r] <= 1.03 * best) { rpc = r; break; }
         if (const char *ev = getenv("EVP_B200_RPC")) rpc = atoi(ev);      // tuning experiments
-        rpc = rpc < 4 ? 4 : (rpc > 48 ? 48 : rpc);
+        rpc = rpc < 2 ? 2 : (rpc > 64 ? 64 : rpc);
         h->t_rpc = (int)rpc;
         h->t_chunks = (g.ny + h->t_rpc - 1) / h->t_rpc;
         h->t_items = h->tstrips * h->t_chunks;
     }
+    h->trace_on = getenv("EVP_B200_TRACE") != nullptr;
+    h->off_trace = off;  off = align_up(off + (size_t)cfg->ndte * 8 * sizeof(unsigned long long), 256);
     h->off_queue = off;  off = align_up(off + (2 * (size_t)cfg->ndte + 1 + h->t_items) * sizeof(int), 256);
     h->arena_bytes = off;
     cudaError_t e = cudaMalloc(&h->arena, h->arena_bytes);
@@ -679,6 +698,7 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
             t.fused_signal = fused_sync ? 1 : 0;
             t.done = h->done(ksub - 1);
             fill_sync_args(h, t.sync);
+            t.trace = h->trace(ksub - 1);
             const int grid = t.items < slots ? t.items : slots;
             const size_t smem = (size_t)kTmaStages * kStageBytes;
             if (last)
@@ -699,13 +719,14 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
     });
     if (!fused_sync) B.sync();
     if (h->g.tripole) {
-        B.op([h, from_parity, buf, fused_sync](Launcher &L) {
+        B.op([h, from_parity, buf, fused_sync, ksub](Launcher &L) {
             const Geom &g = h->g;
             double *u1 = h->plane(from_parity ? S_UA : S_UB), *v1 = h->plane(from_parity ? S_VA : S_VB);
             SyncArgs sa;
             fill_sync_args(h, sa);
             fold_uv_kernel<<<(g.nxl + 2 + 127) / 128, 128, 0, L.s()>>>(u1, v1, g.ld, g.nxl, g.ny, g.nx_global, g.lo,
-                                                                     h->inbox(buf), g.inbox_ld, sa, fused_sync ? 1 : 0);
+                                                                     h->inbox(buf), g.inbox_ld, sa, fused_sync ? 1 : 0,
+                                                                     h->trace(ksub - 1));
             ++L.n;
             return EVP_OK;
         });
@@ -988,6 +1009,17 @@ int evp_gpu_run(evp_handle_t *h, double dt, const evp_in_t *in, evp_inout_t *io,
     TRY(evp_gpu_upload(h, in, io));
     TRY(evp_gpu_compute(h, dt));
     TRY(evp_gpu_download(h, io, out));
+    return EVP_OK;
+}
+
+int evp_gpu_get_trace(evp_handle_t *h, unsigned long long *buf, int n)
+{
+    if (!h || !buf) return EVP_ERR_ARG;
+    if (!h->trace_on) return EVP_ERR_STATE;
+    const int have = h->cfg.ndte * 8;
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaMemcpy(buf, h->arena + h->off_trace, sizeof(unsigned long long) * (size_t)(n < have ? n : have),
+                  cudaMemcpyDeviceToHost));
     return EVP_OK;
 }
 

@@ -341,18 +341,28 @@ struct SyncArgs {
     unsigned long long timeout_ns;
 };
 
-// one thread: everything this rank stored before (made visible to it by fences / barriers) is
-// released to the peers together with the new epoch
-__device__ __forceinline__ void peer_signal(const SyncArgs &a)
+// one warp: everything this rank stored before (made visible to lane 0 by fences / barriers) is
+// released to the peers together with the new epoch; lane r stores to peer r, in parallel
+__device__ __forceinline__ void peer_signal_warp(const SyncArgs &a, int lane)
 {
-    const unsigned long long e = *(volatile unsigned long long *)a.epoch + 1;
-    *(volatile unsigned long long *)a.epoch = e;
-    __threadfence_system();
-    for (int r = 0; r < a.nranks; ++r)
-        if (r != a.rank) {
-            unsigned long long *p = a.flags[r] + a.rank;
-            asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(e) : "memory");
-        }
+    unsigned long long e = 0;
+    if (lane == 0) {
+        e = *(volatile unsigned long long *)a.epoch + 1;
+        *(volatile unsigned long long *)a.epoch = e;
+        __threadfence_system();
+    }
+    e = __shfl_sync(0xffffffffu, e, 0);
+    if (lane < a.nranks && lane != a.rank) {
+        unsigned long long *p = a.flags[lane] + a.rank;
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(e) : "memory");
+    }
+}
+
+__device__ __forceinline__ unsigned long long global_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
 }
 
 // thread r < nranks waits for peer r; callers follow with __syncthreads + __threadfence_system
@@ -380,12 +390,15 @@ __device__ __forceinline__ void peer_wait(const SyncArgs &a, int r)
 // do_wait: first wait until every peer has signalled the end of its subcycle kernel (the barrier
 // that otherwise is the separate halo_wait_kernel).
 __global__ void fold_uv_kernel(double *u, double *v, int ld, int nxl, int ny, int nx, int lo,
-                               const double *inbox, int inbox_ld, const __grid_constant__ SyncArgs sa, int do_wait)
+                               const double *inbox, int inbox_ld, const __grid_constant__ SyncArgs sa, int do_wait,
+                               unsigned long long *trace)
 {
     if (do_wait) {
+        if (trace && blockIdx.x == 0 && threadIdx.x == 0) trace[3] = global_ns();
         peer_wait(sa, threadIdx.x);
         __syncthreads();
         __threadfence_system();
+        if (trace && blockIdx.x == 0 && threadIdx.x == 0) trace[4] = global_ns();
     }
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c > nxl + 1) return;

@@ -143,7 +143,7 @@ __global__ void halo_stress_apply_kernel(double *a1, Geom g, InboxGeom ib, doubl
 // ---- cross-rank synchronisation: SyncArgs, peer_signal, peer_wait live in evp_kernels.cuh ---------
 __global__ void halo_signal_kernel(const __grid_constant__ SyncArgs a)
 {
-    if (threadIdx.x == 0) peer_signal(a);
+    if (threadIdx.x < 32) peer_signal_warp(a, threadIdx.x);
 }
 
 __global__ void halo_wait_kernel(const __grid_constant__ SyncArgs a)

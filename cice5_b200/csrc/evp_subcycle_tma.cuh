@@ -73,6 +73,9 @@ struct TmaArgs {
     int fused_signal;
     int *done;
     SyncArgs sync;
+    // timing trace of this launch (EVP_B200_TRACE=1), globaltimer ns: [0] first CTA start, [1] last
+    // CTA done, [2] peers signalled; the fold kernel adds [3] wait begin, [4] wait end
+    unsigned long long *trace;
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void *p)
@@ -235,6 +238,8 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
     const Consts &k = a.k;
     const int ld = a.ld;
     const int bi = 1 + warp * kUColsPerWarp + lane;                     // my column inside the box
+    bool did_remote = false;                                            // stored into (possibly) peer memory
+    if (p.trace && blockIdx.x == 0 && threadIdx.x == 0) p.trace[0] = global_ns();
     for (;;) {
         mbar_wait(&full_bar[stage], phase);                             // first stage of the next item
         const int item = *reinterpret_cast<const int *>(
@@ -385,13 +390,16 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     a.u1[iu] = unew; a.v1[iu] = vnew;
                     if (c == 1 && a.uW) {
                         const size_t ig = (size_t)(r - 1) * ld + a.nxl + 1;
-                        a.uW[ig] = unew; a.vW[ig] = vnew;
+                        a.uW[ig] = unew; a.vW[ig] = vnew; did_remote = true;
                     }
                     if (c == a.nxl && a.uE) {
                         const size_t ig = (size_t)(r - 1) * ld;
-                        a.uE[ig] = unew; a.vE[ig] = vnew;
+                        a.uE[ig] = unew; a.vE[ig] = vnew; did_remote = true;
                     }
-                    if (a.tripole && r - 1 >= a.ny - 1) tripole_push(a, c, (r - 1) - (a.ny - 1), unew, vnew);
+                    if (a.tripole && r - 1 >= a.ny - 1) {
+                        tripole_push(a, c, (r - 1) - (a.ny - 1), unew, vnew);
+                        did_remote = true;
+                    }
                 }
             }
             if (kLateRelease) {
@@ -403,14 +411,24 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             u_s = u_c; v_s = v_c; uw_s = uw_c; vw_s = vw_c; mprev = m; loaded_s = loaded_c;
         }
     }
-    if (p.fused_signal) {
-        __threadfence_system();                                         // my stores (peer ghosts, inboxes) are out
+    if (p.fused_signal || p.trace) {
+        // only stores into peer memory (E-W ghosts, tripole inboxes) must be out before the signal
+        if (did_remote) __threadfence_system();
         asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
-        if (threadIdx.x == 0) {
-            __threadfence_system();
-            if (atomicAdd(p.done, 1) == (int)gridDim.x - 1) {
+        if (warp == 0) {
+            int last = 0;
+            if (lane == 0) {
                 __threadfence_system();
-                peer_signal(p.sync);
+                last = atomicAdd(p.done, 1) == (int)gridDim.x - 1;
+                if (last) {
+                    __threadfence_system();
+                    if (p.trace) p.trace[1] = global_ns();
+                }
+            }
+            last = __shfl_sync(0xffffffffu, last, 0);
+            if (last && p.fused_signal) {
+                peer_signal_warp(p.sync, lane);
+                if (p.trace && lane == 0) { __threadfence_system(); p.trace[2] = global_ns(); }
             }
         }
     }

@@ -67,7 +67,7 @@ class Stats(C.Structure):
 EXPORTS = ("evp_gpu_init", "evp_gpu_set_grid", "evp_gpu_run", "evp_gpu_upload", "evp_gpu_compute",
            "evp_gpu_download", "evp_gpu_compute_group", "evp_gpu_get_stats", "evp_gpu_synchronize", "evp_gpu_peer_blob_size",
            "evp_gpu_get_peer_blob", "evp_gpu_set_peers", "evp_gpu_finalize", "evp_gpu_strerror",
-           "evp_gpu_last_cuda_error", "evp_gpu_device_count")
+           "evp_gpu_last_cuda_error", "evp_gpu_device_count", "evp_gpu_get_trace")
 
 _libs: dict = {}
 
@@ -214,6 +214,13 @@ class EvpGpu:
         st = Stats()
         self._check(self.lib.evp_gpu_get_stats(self._h, C.byref(st)))
         return st
+
+    def trace(self):
+        """(ndte, 8) uint64 device timestamps of the last compute (needs EVP_B200_TRACE=1)."""
+        buf = np.zeros((self.cfg.ndte, 8), dtype=np.uint64)
+        self._check(self.lib.evp_gpu_get_trace(self._h, buf.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                               C.c_int(buf.size)))
+        return buf
 
     def synchronize(self):
         self._check(self.lib.evp_gpu_synchronize(self._h))

@@ -126,6 +126,11 @@ int evp_gpu_synchronize(evp_handle_t *h);
 
 /* Multi-GPU (one task per GPU): every task exports a blob, the host gathers the blobs of all
  * tasks in rank order (MPI_Allgather in the shim) and hands them back. */
+/* Diagnostics (library started with EVP_B200_TRACE=1): per subcycle 8 x u64 device timestamps in
+ * ns: [0] subcycle kernel start, [1] its last CTA done, [2] peers signalled, [3] fold wait begin,
+ * [4] fold wait end.  No reference counterpart (the reference's timers are ice_timers.F90). */
+int evp_gpu_get_trace(evp_handle_t *h, unsigned long long *buf, int n_u64);
+
 int evp_gpu_peer_blob_size(void);
 int evp_gpu_get_peer_blob(evp_handle_t *h, void *blob);
 int evp_gpu_set_peers(evp_handle_t *h, const void *blobs_all_ranks);
