@@ -104,7 +104,7 @@ struct evp_handle {
     int h_error = 0;
     bool use_tma = false;         // subcycle kernel v2 (TMA ring) instead of v1 (register sweep)
     int sm_count = 148;
-    CUtensorMap mapS, mapT1, mapT3, mapT4, mapT10, mapU, mapU8, mapM;
+    CUtensorMap mapS, mapS2, mapT1, mapT3, mapT4, mapT10, mapU, mapU8, mapM;
     bool have_ht = false;         // HTE / HTN were given: compact metric rows are possible
     evp_stats_t stats;
     unsigned long long h_counts[2];
@@ -197,7 +197,7 @@ int make_tensor_maps(evp_handle *h)
     const cuuint64_t dims[3] = {(cuuint64_t)h->ld, (cuuint64_t)h->nyb, (cuuint64_t)NPLANES};
     const cuuint64_t strides[2] = {(cuuint64_t)h->ld * 8, (cuuint64_t)h->plane_elems * 8};
     const cuuint32_t estr[3] = {1, 1, 1};
-    struct { CUtensorMap *m; int depth; } maps[7] = {{&h->mapS, kStateDepth}, {&h->mapT1, 1}, {&h->mapT3, 3},
+    struct { CUtensorMap *m; int depth; } maps[8] = {{&h->mapS, kStateDepth}, {&h->mapS2, 2}, {&h->mapT1, 1}, {&h->mapT3, 3},
                                                      {&h->mapT4, 4}, {&h->mapT10, 10}, {&h->mapU, kUDepth},
                                                      {&h->mapU8, kUDepth - 2}};
     for (auto &mm : maps) {
@@ -316,18 +316,12 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
         int sms = 148;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device);
         const long long slots = (long long)kTmaBlocksPerSM * sms;
-        // rows per item: makespan of uniform items over the CTA slots = rounds x (rows + the
-        // redundant first row); among the heights within 3 % of the best take the smallest (more,
-        // smaller items even out land / open ocean through the dynamic queue)
-        double best = 1e300;
-        double cost[49];
-        for (int r = 4; r <= 48; ++r) {
-            const long long items = (long long)h->tstrips * ((g.ny + r - 1) / r);
-            cost[r] = (double)((items + slots - 1) / slots) * (r + 1.0);
-            if (cost[r] < best) best = cost[r];
-        }
-        long long rpc = 48;
-        for (int r = 4; r <= 48; ++r) if (cost[r] <= 1.03 * best) { rpc = r; break; }
+        // rows per item: about 4 items per resident CTA (drawn heaviest first from the dynamic
+        // queue, so land / open-ocean items even out), at most 32 rows (a grid that is mostly
+        // ice-free keeps enough items: caps scenario, 48 rows: -17 %); the cost of an item beyond
+        // its rows is one extra stage with the velocities of row r0-1
+        long long rpc = ((long long)h->tstrips * g.ny + 4 * slots - 1) / (4 * slots);
+        rpc = rpc < 4 ? 4 : (rpc > 32 ? 32 : rpc);
         if (const char *ev = getenv("EVP_B200_RPC")) rpc = atoi(ev);      // tuning experiments
         rpc = rpc < 2 ? 2 : (rpc > 64 ? 64 : rpc);
         h->t_rpc = (int)rpc;
@@ -703,10 +697,10 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
             const size_t smem = (size_t)kTmaStages * kStageBytes;
             if (last)
                 evp_subcycle_tma_kernel<true><<<grid, (kTmaConsumers + 1) * 32, smem, L.s()>>>(
-                    h->mapS, h->mapT1, h->mapT3, h->mapT4, h->mapT10, mapU, h->mapM, t);
+                    h->mapS, h->mapS2, h->mapT1, h->mapT3, h->mapT4, h->mapT10, mapU, h->mapM, t);
             else
                 evp_subcycle_tma_kernel<false><<<grid, (kTmaConsumers + 1) * 32, smem, L.s()>>>(
-                    h->mapS, h->mapT1, h->mapT3, h->mapT4, h->mapT10, mapU, h->mapM, t);
+                    h->mapS, h->mapS2, h->mapT1, h->mapT3, h->mapT4, h->mapT10, mapU, h->mapM, t);
             ++L.n;
             return EVP_OK;
         }

@@ -142,7 +142,8 @@ __device__ __forceinline__ void metric_terms(double hte, double hte_w, double ht
 
 template <bool LAST>
 __global__ void __launch_bounds__((kTmaConsumers + 1) * 32, kTmaBlocksPerSM)
-evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_constant__ CUtensorMap mapT1,
+evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_constant__ CUtensorMap mapS2,
+                        const __grid_constant__ CUtensorMap mapT1,
                         const __grid_constant__ CUtensorMap mapT3, const __grid_constant__ CUtensorMap mapT4,
                         const __grid_constant__ CUtensorMap mapT10, const __grid_constant__ CUtensorMap mapU,
                         const __grid_constant__ CUtensorMap mapM, const __grid_constant__ TmaArgs p)
@@ -206,7 +207,8 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     *reinterpret_cast<volatile int *>(mk + kMaskFlagOff + 4) = item;
                     const int tdepth = cmp ? (tinym ? 3 : 4) : 10;
                     unsigned bytes = kMaskBoxW * kMaskBoxes;
-                    if (needS) bytes += kStateDepth * kTmaBoxW * 8;
+                    const bool uv_only = j == r0 - 1;                    // first row of an item: velocities only
+                    if (needS) bytes += (uv_only ? 2 : kStateDepth) * kTmaBoxW * 8;
                     if (needT) bytes += (tdepth + (LAST ? 1 : 0)) * kTmaBoxW * 8;
                     if (htn_extra) bytes += kTmaBoxW * 8;
                     if (needU) bytes += (p.water_is_ocn ? kUDepth - 2 : kUDepth) * kTmaBoxW * 8;
@@ -214,7 +216,7 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
 #pragma unroll
                     for (int mb = 0; mb < kMaskBoxes; ++mb)
                         tma_load_2d(mk + mb * 256, &mapM, &full_bar[stage], (x0 & ~15) + mb * 128, j);
-                    if (needS) tma_load_3d(sb, &mapS, &full_bar[stage], x0, j, p.plane_state);
+                    if (needS) tma_load_3d(sb, uv_only ? &mapS2 : &mapS, &full_bar[stage], x0, j, p.plane_state);
                     if (needT) {
                         if (!cmp) tma_load_3d(tb, &mapT10, &full_bar[stage], x0, j, p.plane_t + 2);
                         else if (tinym) tma_load_3d(tb, &mapT3, &full_bar[stage], x0, j, p.plane_t);
@@ -494,42 +496,41 @@ __global__ void metric_flags_kernel(const __grid_constant__ MetricCheckArgs a)
         a.flags[(size_t)strip * a.flags_ld + r] = (unsigned char)((bad & 1u) ? 0u : ((bad & 2u) ? 4u : 12u));
 }
 
-// The work list of the call: the (strip, row chunk) items that hold ice, in item order (one block,
-// ordered compaction so the list is reproducible).  An item without any active row segment writes
-// nothing (the ping-pong copies agree where the loop never writes), so it is dropped -- except the
-// chunks that reach the top rows of a tripole grid, whose velocities feed the fold every subcycle.
+// The work list of the call: the (strip, row chunk) items that hold ice, heaviest first (most rows
+// with ice: longest-processing-time order, so the dynamic queue ends evenly even with 2-3 items
+// per CTA).  An item without any active row segment writes nothing (the ping-pong copies agree
+// where the loop never writes), so it is dropped -- except the chunks that reach the top rows of a
+// tripole grid, whose velocities feed the fold every subcycle.  The order inside one weight class
+// is not deterministic; results do not depend on the order of the items.
 __global__ void item_list_kernel(const unsigned char *flags, int flags_ld, int strips, int chunks, int rpc, int ny,
                                  int tripole, int *list, int *count, int *queues, int nqueues)
 {
-    __shared__ int wsum[32];
-    __shared__ int base;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    if (threadIdx.x == 0) base = 0;
+    constexpr int kBins = 80;                       // weight = active rows of the item, 0 .. rpc + 2 <= 66
+    __shared__ int hist[kBins], cursor[kBins];
     for (int q = threadIdx.x; q < nqueues; q += blockDim.x) queues[q] = 0;
+    for (int q = threadIdx.x; q < kBins; q += blockDim.x) hist[q] = 0;
     __syncthreads();
     const int items = strips * chunks;
-    for (int i0 = 0; i0 < items; i0 += blockDim.x) {
-        const int item = i0 + threadIdx.x;
-        bool keep = false;
-        if (item < items) {
+    for (int pass = 0; pass < 2; ++pass) {
+        for (int item = threadIdx.x; item < items; item += blockDim.x) {
             const int strip = item % strips, chunk = item / strips;
             const int r0 = 1 + chunk * rpc, rend = min(r0 + rpc, ny + 1);
             const unsigned char *fl = flags + (size_t)strip * flags_ld;
-            unsigned f = 0;
-            for (int j = r0 - 1; j <= rend + 1; ++j) f |= fl[j] & 3u;    // activity bits only
-            keep = f != 0u || (tripole && rend >= ny - 2);
+            int w = 0;
+            for (int j = r0 - 1; j <= rend + 1; ++j) w += (fl[j] & 3u) != 0u;    // activity bits only
+            if (w == 0 && tripole && rend >= ny - 2) w = 1;
+            if (w == 0) continue;
+            if (pass == 0) atomicAdd(&hist[w], 1);
+            else list[atomicAdd(&cursor[w], 1)] = item;
         }
-        const unsigned b = __ballot_sync(0xffffffffu, keep);
-        if (lane == 0) wsum[warp] = __popc(b);
         __syncthreads();
-        int off = base;
-        for (int w = 0; w < warp; ++w) off += wsum[w];
-        if (keep) list[off + __popc(b & ((1u << lane) - 1u))] = item;
-        __syncthreads();
-        if (threadIdx.x == 0) { int t = 0; for (int w = 0; w < nw; ++w) t += wsum[w]; base += t; }
+        if (pass == 0 && threadIdx.x == 0) {
+            int off = 0;
+            for (int w = kBins - 1; w >= 1; --w) { cursor[w] = off; off += hist[w]; }
+            *count = off;
+        }
         __syncthreads();
     }
-    if (threadIdx.x == 0) *count = base;
 }
 
 }  // namespace evp
