@@ -48,6 +48,8 @@ def parse():
     ap.add_argument("--fma", action="store_true", help="use the FMA-contracted comparison build")
     ap.add_argument("--no-compact-metrics", action="store_true",
                     help="do not pass HTE/HTN: fetch all 8 metric planes + tinyarea every subcycle")
+    ap.add_argument("--equal-slabs", action="store_true",
+                    help="N > 1: nx/N columns per GPU instead of slabs balanced by ocean cells")
     ap.add_argument("--cpu-ndte", type=int, default=24, help="subcycles of the CPU sample")
     return ap.parse_args()
 
@@ -196,8 +198,14 @@ def main():
     case = fx.make_case(grid, args.scenario, ndte=args.ndte, dt=dt)
     N = world
 
+    # x-slab boundaries: balanced by ocean T cells per column (static, from the land mask -- the
+    # reference balances its block distribution the same way), or equal widths
+    starts = None
+    if N > 1 and not args.equal_slabs:
+        starts = fx.balanced_slab_starts((grid.f["tmask"][1:-1, 1:-1] > 0).sum(axis=0), N)
+
     def sl(a):
-        return fx.slab(a, rank, N) if N > 1 else a
+        return fx.slab(a, rank, N, starts) if N > 1 else a
 
     keep = []
 
@@ -214,7 +222,7 @@ def main():
 
     e = evp.EvpGpu.for_domain(dom, args.ndte, dt, rank=rank, nranks=N, device=local_rank,
                               strict=not args.fma, use_cuda_graph=not args.no_graph,
-                              compact_metrics=not args.no_compact_metrics)
+                              compact_metrics=not args.no_compact_metrics, slab_start=starts)
     e.set_grid(gridf)
     if N > 1:
         blob = e.peer_blob()
@@ -312,7 +320,8 @@ def main():
                "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                "config": {"workload": f"{args.grid} {dom.nx}x{dom.ny} tripole (AusCOM 0.1 deg shape), "
                                       f"scenario {args.scenario}, ndte={args.ndte}, dt={dt}",
-                          "decomposition": f"{N} x-slab(s) of {dom.nx // N} columns",
+                          "decomposition": (f"{N} x-slab(s) of {dom.nx // N} columns" if starts is None else
+                                            f"{N} x-slabs balanced by ocean cells, first columns {starts}"),
                           "active_t_cells": act_phys, "grid_cells": dom.nx * dom.ny,
                           "l2": "working set per subcycle (~3 GB) exceeds the 126 MB L2; no flush needed"},
                "loop_ms_per_step": loop_ms / args.steps, "wall_ms_per_step": wall_ms / args.steps,

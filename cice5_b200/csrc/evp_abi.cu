@@ -92,7 +92,7 @@ struct evp_handle {
     size_t off_trace = 0;                        // u64 trace[ndte][8] (EVP_B200_TRACE=1)
     bool trace_on = false;
     size_t off_gflags = 0;                       // per strip row: bit2 metrics, bit3 tinyarea reproducible from HTE/HTN
-    size_t off_queue = 0;                        // int queue[ndte], done[ndte], item_count, item_list[t_items]
+    size_t off_queue = 0;                        // int queue[ndte], done[ndte], done_bnd[ndte], item_count[2], item_list[t_items]
     char *peer_arena[kMaxRanks] = {nullptr};
     bool peer_opened[kMaxRanks] = {false};
     bool grid_set = false, uploaded = false, peers_set = false;
@@ -138,8 +138,9 @@ struct evp_handle {
         return trace_on ? reinterpret_cast<unsigned long long *>(arena + off_trace) + 8 * (size_t)ksub : nullptr;
     }
     int *done(int ksub) const { return reinterpret_cast<int *>(arena + off_queue) + cfg.ndte + ksub; }
-    int *item_count() const { return reinterpret_cast<int *>(arena + off_queue) + 2 * cfg.ndte; }
-    int *item_list() const { return reinterpret_cast<int *>(arena + off_queue) + 2 * cfg.ndte + 1; }
+    int *done_bnd(int ksub) const { return reinterpret_cast<int *>(arena + off_queue) + 2 * cfg.ndte + ksub; }
+    int *item_count() const { return reinterpret_cast<int *>(arena + off_queue) + 3 * cfg.ndte; }   // [2]
+    int *item_list() const { return reinterpret_cast<int *>(arena + off_queue) + 3 * cfg.ndte + 2; }
     unsigned long long *counts() const
     {
         return reinterpret_cast<unsigned long long *>(arena + off_counts);
@@ -241,7 +242,7 @@ const char *evp_gpu_strerror(int status)
         case EVP_ERR_ARG: return "evp_gpu: invalid argument (null pointer or inconsistent block sizes)";
         case EVP_ERR_UNSUPPORTED:
             return "evp_gpu: unsupported configuration (needs kdyn=1, revised_evp=.false., "
-                   "tripole only with cyclic E-W, nranks <= 8 dividing nx_global)";
+                   "tripole only with cyclic E-W, nranks <= 8, slabs >= 2 columns)";
         case EVP_ERR_CUDA: return "evp_gpu: CUDA runtime error (see evp_gpu_last_cuda_error)";
         case EVP_ERR_STATE: return "evp_gpu: call order violated (init -> set_grid -> [set_peers] -> run)";
         case EVP_ERR_NO_DEVICE: return "evp_gpu: no usable CUDA device; this library has no CPU fallback";
@@ -267,10 +268,28 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
     if (cfg->nranks < 1 || cfg->nranks > kMaxRanks || cfg->rank < 0 || cfg->rank >= cfg->nranks)
         return EVP_ERR_UNSUPPORTED;
     if (cfg->nx_global < 2 || cfg->ny_global < 3 || cfg->ndte < 1 || !(cfg->dt_init > 0.0)) return EVP_ERR_ARG;
-    if (cfg->nx_global % cfg->nranks) return EVP_ERR_UNSUPPORTED;
-    if (cfg->nx_block != cfg->nx_global / cfg->nranks + 2 || cfg->ny_block != cfg->ny_global + 2)
+    // x-slabs: equal widths (slab_start all zero; nranks must divide nx_global) or the caller's
+    // own boundaries (e.g. balanced by ocean cells), slab_start[r] = first global column of rank r,
+    // 0-based, slab_start[0] = 0
+    int start[kMaxRanks + 1];
+    bool given = false;
+    for (int r = 1; r < cfg->nranks; ++r) given = given || cfg->slab_start[r] != 0;
+    if (given) {
+        for (int r = 0; r < cfg->nranks; ++r) start[r] = cfg->slab_start[r];
+        if (start[0] != 0) return EVP_ERR_ARG;
+    } else {
+        if (cfg->nx_global % cfg->nranks) return EVP_ERR_UNSUPPORTED;
+        for (int r = 0; r < cfg->nranks; ++r) start[r] = r * (cfg->nx_global / cfg->nranks);
+    }
+    start[cfg->nranks] = cfg->nx_global;
+    int maxw = 0;
+    for (int r = 0; r < cfg->nranks; ++r) {
+        const int w = start[r + 1] - start[r];
+        if (w < 2) return EVP_ERR_UNSUPPORTED;
+        if (w > maxw) maxw = w;
+    }
+    if (cfg->nx_block != start[cfg->rank + 1] - start[cfg->rank] + 2 || cfg->ny_block != cfg->ny_global + 2)
         return EVP_ERR_ARG;
-    if (cfg->nx_global / cfg->nranks < 2) return EVP_ERR_UNSUPPORTED;
     if (cfg->ns_boundary == EVP_NS_TRIPOLE && cfg->ew_boundary != EVP_EW_CYCLIC) return EVP_ERR_UNSUPPORTED;
     if (cfg->ns_boundary < 0 || cfg->ns_boundary > 2 || cfg->ew_boundary < 0 || cfg->ew_boundary > 1)
         return EVP_ERR_UNSUPPORTED;
@@ -288,14 +307,17 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
     h->cfg = *cfg;
     set_evp_parameters(*cfg, h->k);
     h->nxb = cfg->nx_block; h->nyb = cfg->ny_block;
-    h->ld = (int)align_up((size_t)h->nxb, 16);   // rows start on 128-byte boundaries (TMA, sectors)
+    // rows start on 128-byte boundaries (TMA, sectors); the pitch is that of the widest slab so that
+    // every rank's arena has the same layout (peer plane = peer base + the same offset)
+    h->ld = (int)align_up((size_t)maxw + 2, 16);
     h->ldm = h->ld;
     h->plane_elems = (size_t)h->ld * h->nyb;
     Geom &g = h->g;
     g.nxl = h->nxb - 2; g.ny = h->nyb - 2; g.ld = h->ld; g.nx_global = cfg->nx_global;
-    g.lo = cfg->rank * g.nxl; g.nranks = cfg->nranks; g.rank = cfg->rank;
+    g.lo = start[cfg->rank]; g.nranks = cfg->nranks; g.rank = cfg->rank;
+    for (int r = 0; r <= kMaxRanks; ++r) g.start[r] = r <= cfg->nranks ? start[r] : cfg->nx_global;
     g.tripole = cfg->ns_boundary == EVP_NS_TRIPOLE; g.ew_cyclic = cfg->ew_boundary == EVP_EW_CYCLIC;
-    g.inbox_ld = (int)align_up((size_t)h->nxb, 16);
+    g.inbox_ld = h->ld;
     h->ib.inbox_ld = g.inbox_ld;
     h->ib.col_ld = (int)align_up((size_t)h->nyb, 16);
 
@@ -330,7 +352,7 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
     }
     h->trace_on = getenv("EVP_B200_TRACE") != nullptr;
     h->off_trace = off;  off = align_up(off + (size_t)cfg->ndte * 8 * sizeof(unsigned long long), 256);
-    h->off_queue = off;  off = align_up(off + (2 * (size_t)cfg->ndte + 1 + h->t_items) * sizeof(int), 256);
+    h->off_queue = off;  off = align_up(off + (3 * (size_t)cfg->ndte + 2 + h->t_items) * sizeof(int), 256);
     h->arena_bytes = off;
     cudaError_t e = cudaMalloc(&h->arena, h->arena_bytes);
     if (e != cudaSuccess) {
@@ -632,6 +654,8 @@ void fill_loop_args(const evp_handle *h, int from_parity, int inbox_buf, LoopArg
         a.rows_per_chunk = (int)(rpc < 2 ? 2 : (rpc > 32 ? 32 : rpc));
     }
     a.nx_global = g.nx_global; a.lo = g.lo; a.nranks = g.nranks; a.rank = g.rank; a.tripole = g.tripole;
+    for (int r = 0; r <= kMaxRanks; ++r) a.start[r] = g.start[r];
+    a.nxl_west = g.start[h->west() + 1] - g.start[h->west()];
     a.inbox_ld = g.inbox_ld;
     a.mask = h->mask();
     const int U0 = from_parity ? S_UB : S_UA, V0 = from_parity ? S_VB : S_VA;
@@ -690,7 +714,7 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
             t.items = h->t_items;
             t.queue = h->queue(ksub - 1); t.item_list = h->item_list(); t.item_count = h->item_count();
             t.fused_signal = fused_sync ? 1 : 0;
-            t.done = h->done(ksub - 1);
+            t.done = h->done(ksub - 1); t.done_bnd = h->done_bnd(ksub - 1);
             fill_sync_args(h, t.sync);
             t.trace = h->trace(ksub - 1);
             const int grid = t.items < slots ? t.items : slots;
@@ -806,8 +830,8 @@ void build_program(evp_handle *h, double dt, Program &P)
             tile_flags_kernel<<<grid, 128, 0, s>>>(h->mask(), h->ldm, h->g.nxl, h->g.ny, h->tstrips, h->tflags(),
                                                   h->tflags_ld, h->gflags());
             item_list_kernel<<<1, 1024, 0, s>>>(h->tflags(), h->tflags_ld, h->tstrips, h->t_chunks, h->t_rpc, h->g.ny,
-                                                h->g.tripole ? 1 : 0, h->item_list(), h->item_count(), h->queue(0),
-                                                2 * h->cfg.ndte);
+                                                h->g.tripole ? 1 : 0, h->west_closed() ? 0 : 1, h->east_closed() ? 0 : 1,
+                                                h->item_list(), h->item_count(), h->queue(0), 3 * h->cfg.ndte);
             L.n += 2;
         }
         CK(cudaGetLastError());

@@ -35,6 +35,8 @@ struct LoopArgs {
     int rows_per_chunk;
     int nx_global, lo;             // global columns; lo = global index of local column c=0
     int nranks, rank, tripole;
+    int start[kMaxRanks + 1];      // x-slabs: rank t owns global columns start[t]+1 .. start[t+1]
+    int nxl_west;                  // physical columns of the west neighbour (its east ghost = nxl_west + 1)
     int inbox_ld;                  // pitch of one inbox row (doubles)
     const unsigned char *mask;     // bit0: T cell active (icetmask==1), bit1: U cell active (iceumask)
     const double *u0, *v0;
@@ -51,6 +53,15 @@ struct LoopArgs {
     double *inbox[kMaxRanks];
     Consts k;
 };
+
+// owner rank t, its local column ct (1-based) and its width wt for global column X (1-based)
+__device__ __forceinline__ void slab_owner(const int *start, int nranks, int X, int &t, int &ct, int &wt)
+{
+    t = 0;
+    while (t + 1 < nranks && X > start[t + 1]) ++t;
+    ct = X - start[t];
+    wt = start[t + 1] - start[t];
+}
 
 __device__ __forceinline__ double shfl_up1(double x)
 {
@@ -185,17 +196,18 @@ __device__ __forceinline__ void tripole_push(const LoopArgs &a, int c, int rowse
     const int ig = a.lo + c;                  // global column, 1-based
     int X = a.nx_global - ig;                 // the column whose fold source is ig
     if (X == 0) X = a.nx_global;
-    const int t = (X - 1) / a.nxl;
-    const int ct = X - t * a.nxl;             // local column on rank t (1..nxl)
+    int t, ct, wt;                            // owner, local column on rank t (1..wt)
+    slab_owner(a.start, a.nranks, X, t, ct, wt);
     const size_t urow = (size_t)(0 + rowsel) * a.inbox_ld, vrow = (size_t)(2 + rowsel) * a.inbox_ld;
     a.inbox[t][urow + ct] = u;
     a.inbox[t][vrow + ct] = v;
     if (ct == 1) {                            // also the east ghost of rank t-1
         const int t2 = (t + a.nranks - 1) % a.nranks;
-        a.inbox[t2][urow + a.nxl + 1] = u;
-        a.inbox[t2][vrow + a.nxl + 1] = v;
+        const int w2 = a.start[t2 + 1] - a.start[t2];
+        a.inbox[t2][urow + w2 + 1] = u;
+        a.inbox[t2][vrow + w2 + 1] = v;
     }
-    if (ct == a.nxl) {                        // also the west ghost of rank t+1
+    if (ct == wt) {                           // also the west ghost of rank t+1
         const int t2 = (t + 1) % a.nranks;
         a.inbox[t2][urow] = u;
         a.inbox[t2][vrow] = v;
@@ -291,7 +303,7 @@ evp_subcycle_kernel(const __grid_constant__ LoopArgs a)
                 a.u1[iu] = unew; a.v1[iu] = vnew;
                 // width-1 halo, E-W part: my edge columns are the neighbours' ghosts
                 if (c == 1 && a.uW) {
-                    const size_t ig = (size_t)(r - 1) * ld + a.nxl + 1;
+                    const size_t ig = (size_t)(r - 1) * ld + a.nxl_west + 1;
                     a.uW[ig] = unew; a.vW[ig] = vnew;
                 }
                 if (c == a.nxl && a.uE) {

@@ -16,6 +16,7 @@ struct Geom {
     int nxl, ny, ld, nx_global, lo, nranks, rank;
     int tripole, ew_cyclic;
     int inbox_ld;
+    int start[kMaxRanks + 1];      // x-slabs: rank t owns global columns start[t]+1 .. start[t+1]
 };
 
 __device__ __forceinline__ int glob_col(const Geom &g, int c)
@@ -77,13 +78,17 @@ __global__ void halo_push_kernel(const __grid_constant__ PushArgs a)
         const int ig = g.lo + c;
         int X = g.nx_global + 1 - a.ioff - ig;
         if (X == 0) X = g.nx_global;
-        const int tr = (X - 1) / g.nxl, ct = X - tr * g.nxl;
+        int tr, ct, wt;
+        slab_owner(g.start, g.nranks, X, tr, ct, wt);
 #pragma unroll
         for (int rs = 0; rs < 2; ++rs) {
             const double v = a.plane[(size_t)(g.ny - 1 + rs) * g.ld + c];
             inbox_row(a.inbox[tr], a.ib, rs)[ct] = v;
-            if (ct == 1) inbox_row(a.inbox[(tr + g.nranks - 1) % g.nranks], a.ib, rs)[g.nxl + 1] = v;
-            if (ct == g.nxl) inbox_row(a.inbox[(tr + 1) % g.nranks], a.ib, rs)[0] = v;
+            if (ct == 1) {
+                const int t2 = (tr + g.nranks - 1) % g.nranks;
+                inbox_row(a.inbox[t2], a.ib, rs)[g.start[t2 + 1] - g.start[t2] + 1] = v;
+            }
+            if (ct == wt) inbox_row(a.inbox[(tr + 1) % g.nranks], a.ib, rs)[0] = v;
         }
     }
 }

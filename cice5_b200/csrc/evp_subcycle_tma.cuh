@@ -45,6 +45,7 @@ constexpr int kStateDepth = 14, kTDepth = 12, kUDepth = 10;
 // full row: 0 strength, 1 tinyarea, 2..9 dxt dyt dxhy dyhx cxp cyp cxm cym; both: 10 tarear (last
 // subcycle), 11 HTN of this row when only the next row needs it (its southern HTN).
 constexpr int kSlotTarear = 10, kSlotHtnExtra = 11;
+constexpr int kItemBoundary = 0x40000000;    // tag of a work item that stores into peer memory
 // stage word bits written by the producer
 constexpr unsigned kMetaState = 1u, kMetaCompact = 2u, kMetaTinyFromMetrics = 4u, kMetaHtnExtra = 8u, kMetaT = 16u;
 constexpr int kMaskBoxW = 128 + 16;          // per mask box; kTmaBoxW / 128 boxes per row
@@ -71,7 +72,7 @@ struct TmaArgs {
     // fused cross-rank signal: every CTA counts itself in `done` when its stores are out; the last
     // one bumps the epoch and releases it to the peers (what halo_signal_kernel does otherwise)
     int fused_signal;
-    int *done;
+    int *done, *done_bnd;        // finished CTAs / finished boundary items of this launch
     SyncArgs sync;
     // timing trace of this launch (EVP_B200_TRACE=1), globaltimer ns: [0] first CTA start, [1] last
     // CTA done, [2] peers signalled; the fold kernel adds [3] wait begin, [4] wait end
@@ -167,7 +168,7 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
     if (warp == kTmaConsumers) {
         // ------------------------------ producer ------------------------------
         if (lane == 0) {
-            const int nitems = *p.item_count;
+            const int nitems = p.item_count[0], nbnd = p.item_count[1];
             for (;;) {
                 const int q = atomicAdd(p.queue, 1);
                 if (q >= nitems) {                                      // queue drained: tell the consumers
@@ -178,6 +179,7 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     break;
                 }
                 const int item = p.item_list[q];
+                const int item_tag = item | (q < nbnd ? kItemBoundary : 0);
                 const int strip = item % p.strips, chunk = item / p.strips;
                 const int x0 = strip * kTmaUCols;                       // box column 0 = U column c0 - 1
                 const int r0 = 1 + chunk * a.rows_per_chunk;
@@ -204,7 +206,7 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     *reinterpret_cast<volatile unsigned *>(mk + kMaskFlagOff) =
                         (needS ? kMetaState : 0u) | (cmp ? kMetaCompact : 0u) | (tinym ? kMetaTinyFromMetrics : 0u) |
                         (htn_extra ? kMetaHtnExtra : 0u) | (needT ? kMetaT : 0u);
-                    *reinterpret_cast<volatile int *>(mk + kMaskFlagOff + 4) = item;
+                    *reinterpret_cast<volatile int *>(mk + kMaskFlagOff + 4) = item_tag;
                     const int tdepth = cmp ? (tinym ? 3 : 4) : 10;
                     unsigned bytes = kMaskBoxW * kMaskBoxes;
                     const bool uv_only = j == r0 - 1;                    // first row of an item: velocities only
@@ -244,9 +246,10 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
     if (p.trace && blockIdx.x == 0 && threadIdx.x == 0) p.trace[0] = global_ns();
     for (;;) {
         mbar_wait(&full_bar[stage], phase);                             // first stage of the next item
-        const int item = *reinterpret_cast<const int *>(
+        const int item_tag = *reinterpret_cast<const int *>(
             ring + (size_t)stage * kStageBytes + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8 + kMaskFlagOff + 4);
-        if (item < 0) break;
+        if (item_tag < 0) break;
+        const int item = item_tag & ~kItemBoundary;
         const int strip = item % p.strips, chunk = item / p.strips;
         const int c = 1 + strip * kTmaUCols + warp * kUColsPerWarp + lane;   // T column (U column if lane < 31)
         const bool warp_on = (c - lane) <= a.nxl;                       // warp-uniform
@@ -391,7 +394,7 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                 if (ucol) {
                     a.u1[iu] = unew; a.v1[iu] = vnew;
                     if (c == 1 && a.uW) {
-                        const size_t ig = (size_t)(r - 1) * ld + a.nxl + 1;
+                        const size_t ig = (size_t)(r - 1) * ld + a.nxl_west + 1;
                         a.uW[ig] = unew; a.vW[ig] = vnew; did_remote = true;
                     }
                     if (c == a.nxl && a.uE) {
@@ -412,6 +415,25 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             s1p = str[0]; s5p = str[4]; n2p = e2; n7p = e7;
             u_s = u_c; v_s = v_c; uw_s = uw_c; vw_s = vw_c; mprev = m; loaded_s = loaded_c;
         }
+        if (p.fused_signal && (item_tag & kItemBoundary)) {
+            // a boundary item is complete: count it; whoever completes the last one signals the
+            // peers -- the interior items of every rank are computed while the signals travel
+            if (did_remote) { __threadfence_system(); did_remote = false; }
+            asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
+            if (warp == 0) {
+                int fire = 0;
+                if (lane == 0) {
+                    __threadfence_system();
+                    fire = atomicAdd(p.done_bnd, 1) == p.item_count[1] - 1;
+                    if (fire) __threadfence_system();
+                }
+                fire = __shfl_sync(0xffffffffu, fire, 0);
+                if (fire) {
+                    peer_signal_warp(p.sync, lane);
+                    if (p.trace && lane == 0) p.trace[2] = global_ns();
+                }
+            }
+        }
     }
     if (p.fused_signal || p.trace) {
         // only stores into peer memory (E-W ghosts, tripole inboxes) must be out before the signal
@@ -428,9 +450,9 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                 }
             }
             last = __shfl_sync(0xffffffffu, last, 0);
-            if (last && p.fused_signal) {
+            if (last && p.fused_signal && p.item_count[1] == 0) {       // no boundary item held ice
                 peer_signal_warp(p.sync, lane);
-                if (p.trace && lane == 0) { __threadfence_system(); p.trace[2] = global_ns(); }
+                if (p.trace && lane == 0) p.trace[2] = global_ns();
             }
         }
     }
@@ -503,9 +525,13 @@ __global__ void metric_flags_kernel(const __grid_constant__ MetricCheckArgs a)
 // tripole grid, whose velocities feed the fold every subcycle.  The order inside one weight class
 // is not deterministic; results do not depend on the order of the items.
 __global__ void item_list_kernel(const unsigned char *flags, int flags_ld, int strips, int chunks, int rpc, int ny,
-                                 int tripole, int *list, int *count, int *queues, int nqueues)
+                                 int tripole, int bnd_west, int bnd_east, int *list, int *count, int *queues,
+                                 int nqueues)
 {
-    constexpr int kBins = 80;                       // weight = active rows of the item, 0 .. rpc + 2 <= 66
+    // weight = active rows of the item, 0 .. rpc + 2 <= 66; boundary items (they store into peer
+    // memory: E-W ghost columns, tripole inboxes) come first, so that the peers can be signalled
+    // while the interior items are still being computed: count[1] = number of boundary items
+    constexpr int kW = 80, kBins = 2 * kW;
     __shared__ int hist[kBins], cursor[kBins];
     for (int q = threadIdx.x; q < nqueues; q += blockDim.x) queues[q] = 0;
     for (int q = threadIdx.x; q < kBins; q += blockDim.x) hist[q] = 0;
@@ -520,14 +546,19 @@ __global__ void item_list_kernel(const unsigned char *flags, int flags_ld, int s
             for (int j = r0 - 1; j <= rend + 1; ++j) w += (fl[j] & 3u) != 0u;    // activity bits only
             if (w == 0 && tripole && rend >= ny - 2) w = 1;
             if (w == 0) continue;
-            if (pass == 0) atomicAdd(&hist[w], 1);
-            else list[atomicAdd(&cursor[w], 1)] = item;
+            const bool bnd = (strip == 0 && bnd_west) || (strip == strips - 1 && bnd_east) || (tripole && rend >= ny - 2);
+            const int key = w + (bnd ? kW : 0);
+            if (pass == 0) atomicAdd(&hist[key], 1);
+            else list[atomicAdd(&cursor[key], 1)] = item;
         }
         __syncthreads();
         if (pass == 0 && threadIdx.x == 0) {
             int off = 0;
-            for (int w = kBins - 1; w >= 1; --w) { cursor[w] = off; off += hist[w]; }
-            *count = off;
+            for (int key = kBins - 1; key >= 1; --key) {
+                if (key == kW - 1) count[1] = off;              // everything before: boundary items
+                cursor[key] = off; off += hist[key];
+            }
+            count[0] = off;
         }
         __syncthreads();
     }

@@ -28,7 +28,8 @@ class Config(C.Structure):
         "nx_global", "ny_global", "nx_block", "ny_block", "rank", "nranks", "device", "ndte",
         "kdyn", "revised_evp", "ew_boundary", "ns_boundary", "grid_tripole", "tilt_mode",
         "strength_masked", "use_cuda_graph")] + [(n, C.c_double) for n in (
-        "dt_init", "cosw", "sinw", "rhow", "rhoi", "rhos", "gravit", "a_min", "m_min")]
+        "dt_init", "cosw", "sinw", "rhow", "rhoi", "rhos", "gravit", "a_min", "m_min")] + [
+        ("slab_start", C.c_int * 9)]
 
 
 GRID_R8 = ("dxt", "dyt", "dxhy", "dyhx", "cxp", "cyp", "cxm", "cym", "tarea", "uarea", "tarear",
@@ -121,13 +122,19 @@ class EvpGpu:
                  ew_cyclic=True, ns_boundary="open", grid_tripole=False, tilt_mode=0,
                  strength_masked=0, cosw=1.0, sinw=0.0, rhow=1026.0, rhoi=917.0, rhos=330.0,
                  gravit=9.80616, a_min=1.0e-3, m_min=1.0e-2, kdyn=1, revised_evp=False,
-                 use_cuda_graph=False, strict=True, compact_metrics=True):
+                 use_cuda_graph=False, strict=True, compact_metrics=True, slab_start=None):
         self.lib = load_library(strict)
         self.compact_metrics = compact_metrics      # pass HTE / HTN to set_grid when the grid has them
         ns = {"open": 0, "closed": 1, "tripole": 2}[ns_boundary]
-        if nx_global % nranks:
-            raise EvpError("nranks must divide nx_global")
-        self.nxl = nx_global // nranks
+        if slab_start is None:
+            if nx_global % nranks:
+                raise EvpError("nranks must divide nx_global (or pass slab_start)")
+            slab_start = [r * (nx_global // nranks) for r in range(nranks)]
+        slab_start = [int(x) for x in slab_start]
+        if len(slab_start) != nranks or slab_start[0] != 0:
+            raise EvpError("slab_start needs one 0-based first column per rank, starting at 0")
+        self.slab_start = slab_start
+        self.nxl = (slab_start + [nx_global])[rank + 1] - slab_start[rank]
         self.shape = (ny_global + 2, self.nxl + 2)
         self.cfg = Config(nx_global=nx_global, ny_global=ny_global, nx_block=self.nxl + 2,
                           ny_block=ny_global + 2, rank=rank, nranks=nranks, device=device,
@@ -137,6 +144,8 @@ class EvpGpu:
                           strength_masked=strength_masked, use_cuda_graph=int(use_cuda_graph),
                           dt_init=dt_init, cosw=cosw, sinw=sinw, rhow=rhow, rhoi=rhoi, rhos=rhos,
                           gravit=gravit, a_min=a_min, m_min=m_min)
+        for r, x in enumerate(slab_start):
+            self.cfg.slab_start[r] = x
         self._h = C.c_void_p()
         self._check(self.lib.evp_gpu_init(C.byref(self.cfg), C.byref(self._h)))
         self._keep = []
@@ -272,18 +281,20 @@ class EvpGroup:
     """All x-slabs of one decomposition driven from one process (one device): the host-side mirror
     of `nranks` tasks each calling evp(dt) on its own block.  Global-with-ghost arrays in and out."""
 
-    def __init__(self, dom, ndte, dt_init, nranks, device=0, **kw):
+    def __init__(self, dom, ndte, dt_init, nranks, device=0, slab_start=None, **kw):
         from . import fixtures as fx
         self._fx = fx
         self.n = nranks
-        self.ranks = [EvpGpu.for_domain(dom, ndte, dt_init, rank=r, nranks=nranks, device=device, **kw)
+        self.starts = slab_start            # None = equal slabs
+        self.ranks = [EvpGpu.for_domain(dom, ndte, dt_init, rank=r, nranks=nranks, device=device,
+                                        slab_start=slab_start, **kw)
                       for r in range(nranks)]
         blobs = [e.peer_blob() for e in self.ranks]
         for e in self.ranks:
             e.set_peers(blobs)
 
     def _slabs(self, d, r):
-        return {k: self._fx.slab(v, r, self.n) for k, v in d.items() if v is not None}
+        return {k: self._fx.slab(v, r, self.n, self.starts) for k, v in d.items() if v is not None}
 
     def set_grid(self, f):
         names = GRID_R8 + ("tmask", "umask") + tuple(k for k in ("HTE", "HTN") if f.get(k) is not None)

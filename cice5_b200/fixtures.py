@@ -459,12 +459,36 @@ def make_case(grid_name: str | Grid, scenario: str = "full", ndte: int = 120,
                 out=zeroed_outputs(grid.dom), scenario=scenario)
 
 
-def slab(a: np.ndarray, rank: int, nranks: int) -> np.ndarray:
+def slab_bounds(nx: int, nranks: int, starts=None) -> list:
+    """[first physical column (0-based) of rank 0, ..., of rank n-1, nx]."""
+    if starts is None:
+        assert nx % nranks == 0
+        return [r * (nx // nranks) for r in range(nranks)] + [nx]
+    assert len(starts) == nranks and starts[0] == 0
+    return [int(x) for x in starts] + [nx]
+
+
+def slab(a: np.ndarray, rank: int, nranks: int, starts=None) -> np.ndarray:
     """Column slice (with ghosts) of a global-with-ghost array owned by x-slab `rank`."""
-    nx = a.shape[1] - 2
-    assert nx % nranks == 0
-    nxl = nx // nranks
-    return np.ascontiguousarray(a[:, rank * nxl: rank * nxl + nxl + 2])
+    b = slab_bounds(a.shape[1] - 2, nranks, starts)
+    return np.ascontiguousarray(a[:, b[rank]: b[rank + 1] + 2])
+
+
+def balanced_slab_starts(weight_per_column: np.ndarray, nranks: int, min_width: int = 2) -> list:
+    """x-slab boundaries that even out the work per rank (what the reference's ice_distribution
+    does with its land-mask work estimate, source/ice_distribution.F90 create_distrb_*): greedy cut of
+    the cumulative column weight (e.g. ocean T cells per column) into nranks equal shares."""
+    w = np.asarray(weight_per_column, dtype="f8") + 1e-9
+    nx = w.size
+    cum = np.concatenate([[0.0], np.cumsum(w)])
+    starts = [0]
+    for r in range(1, nranks):
+        target = cum[-1] * r / nranks
+        c = int(np.searchsorted(cum, target))
+        c = max(c, starts[-1] + min_width)
+        c = min(c, nx - (nranks - r) * min_width)
+        starts.append(c)
+    return starts
 
 
 def unslab(parts: list) -> np.ndarray:

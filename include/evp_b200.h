@@ -61,6 +61,10 @@ typedef struct {
     double cosw, sinw;          /* ocean turning angle (namelist under AusCOM)                  */
     double rhow, rhoi, rhos, gravit;
     double a_min, m_min;        /* ice_dyn_shared.F90:60-61                                     */
+    int slab_start[9];          /* first global column (0-based) of every rank's x-slab; all zero =
+                                   equal slabs of nx_global/nranks columns.  Unequal slabs are the
+                                   load balancing the reference does in ice_distribution
+                                   (create_distrb_*, work per block from the land mask)            */
 } evp_config_t;
 
 /* Grid arrays (source/ice_grid.F90:48-77,112-115; fcor_blk ice_dyn_shared.F90:83-84),

@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--ndte", type=int, default=120)
     ap.add_argument("--calls", type=int, default=2)
     ap.add_argument("--graph", type=int, default=1)
+    ap.add_argument("--balanced", type=int, default=1, help="slabs balanced by ocean cells")
     args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
@@ -33,9 +34,12 @@ def main():
     grid = fx.make_grid(args.grid)
     case = fx.make_case(grid, args.scenario, ndte=args.ndte)
     dom = case.dom
-    sl = lambda d: {k: fx.slab(v, rank, world) for k, v in d.items()}
+    starts = None
+    if args.balanced:
+        starts = fx.balanced_slab_starts((grid.f["tmask"][1:-1, 1:-1] > 0).sum(axis=0), world)
+    sl = lambda d: {k: fx.slab(v, rank, world, starts) for k, v in d.items()}
     e = evp.EvpGpu.for_domain(dom, args.ndte, case.dt, rank=rank, nranks=world, device=local,
-                              strict=True, use_cuda_graph=bool(args.graph))
+                              strict=True, use_cuda_graph=bool(args.graph), slab_start=starts)
     e.set_grid(sl({k: grid.f[k] for k in evp.GRID_R8 + ("tmask", "umask", "HTE", "HTN")}))
     blobs = [None] * world
     dist.all_gather_object(blobs, e.peer_blob())

@@ -45,7 +45,14 @@ def test_config_struct_matches_header():
             continue
         typ, rest = decl.split(None, 1)
         fields += [(n.strip(), typ) for n in rest.split(",")]
-    got = [(n, "int" if t is C.c_int else "double") for n, t in evp.Config._fields_]
+
+    def cname(n, t):
+        if t is C.c_int:
+            return (n, "int")
+        if t is C.c_double:
+            return (n, "double")
+        return (f"{n}[{t._length_}]", "int")            # int array member
+    got = [cname(n, t) for n, t in evp.Config._fields_]
     assert got == fields
 
 

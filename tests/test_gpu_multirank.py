@@ -51,3 +51,23 @@ def test_group_two_calls_odd_ndte():
         orc.run_case(ref)
     got, _ = _run_group(case, 4, calls=2)
     compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+
+
+@pytest.mark.parametrize("grid,starts", [
+    ((96, 40), [0, 10, 50, 53]),                 # very uneven, a 3-column slab
+    ((124, 33), [0, 2, 4, 70, 72, 100]),         # 2-column slabs next to wide ones
+    ("tp1", None),                               # balanced by ocean cells, 8 ranks
+])
+def test_unequal_slabs_group_bitwise(grid, starts):
+    """Slabs of different widths (evp_config_t.slab_start: load balancing by ocean cells, as the
+    reference's ice_distribution does): same bits as the single block."""
+    g = _small_tripole(*grid) if isinstance(grid, tuple) else fx.make_grid(grid)
+    case = fx.make_case(g, "full", ndte=12 if isinstance(grid, tuple) else 40, dt=3600.0)
+    if starts is None:
+        w = (g.f["tmask"][1:-1, 1:-1] > 0).sum(axis=0)
+        starts = fx.balanced_slab_starts(w, 8)
+        assert len(set(np.diff(starts + [g.dom.nx]))) > 1          # really unequal
+    ref = _oracle(case)
+    got, st = _run_group(case, len(starts), slab_start=starts)
+    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+    assert sum(s.active_u_cells for s in st) == int(ref.io["iceumask"][1:-1, 1:-1].sum())
