@@ -141,6 +141,29 @@ __device__ __forceinline__ void metric_terms(double hte, double hte_w, double ht
     m[7] = -__dsub_rn(__dmul_rn(1.5, hte_w), __dmul_rn(0.5, hte));              // cym
 }
 
+// Consumer warps of one CTA: `n` more boundary items are complete (all their stores into peer
+// memory issued).  Fence once, count; the CTA that completes the count releases the epoch.
+__device__ __noinline__ void boundary_done(const TmaArgs &p, int *bnd_count, int warp, int lane)
+{
+    __threadfence_system();                          // my stores into peer memory are out
+    asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
+    if (warp == 0) {
+        int fire = 0;
+        if (lane == 0) {
+            const int n = *bnd_count;                // written by this thread only
+            *bnd_count = 0;
+            __threadfence_system();
+            fire = atomicAdd(p.done_bnd, n) + n == p.item_count[1];
+            if (fire) __threadfence_system();
+        }
+        fire = __shfl_sync(0xffffffffu, fire, 0);
+        if (fire) {
+            peer_signal_warp(p.sync, lane);
+            if (p.trace && lane == 0) p.trace[2] = global_ns();
+        }
+    }
+}
+
 template <bool LAST>
 __global__ void __launch_bounds__((kTmaConsumers + 1) * 32, kTmaBlocksPerSM)
 evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_constant__ CUtensorMap mapS2,
@@ -151,10 +174,12 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
 {
     extern __shared__ __align__(1024) unsigned char ring[];
     __shared__ unsigned long long full_bar[kTmaStages], empty_bar[kTmaStages];
+    __shared__ int bnd_count;                        // boundary items taken by this CTA (thread 0 only)
     const LoopArgs &a = p.a;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
+        bnd_count = 0;
 #pragma unroll
         for (int s = 0; s < kTmaStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], kTmaConsumers); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -242,14 +267,25 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
     const Consts &k = a.k;
     const int ld = a.ld;
     const int bi = 1 + warp * kUColsPerWarp + lane;                     // my column inside the box
-    bool did_remote = false;                                            // stored into (possibly) peer memory
+    bool in_bnd = false;                                                // boundary items taken, not yet counted
     if (p.trace && blockIdx.x == 0 && threadIdx.x == 0) p.trace[0] = global_ns();
     for (;;) {
         mbar_wait(&full_bar[stage], phase);                             // first stage of the next item
         const int item_tag = *reinterpret_cast<const int *>(
             ring + (size_t)stage * kStageBytes + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8 + kMaskFlagOff + 4);
+        if (in_bnd && (item_tag < 0 || !(item_tag & kItemBoundary))) {
+            // this CTA has left the boundary items (they come first in the queue): count them;
+            // whoever completes the count signals the peers, and the interior items of every rank
+            // are computed while the signals travel
+            if (p.fused_signal) boundary_done(p, &bnd_count, warp, lane);
+            in_bnd = false;
+        }
         if (item_tag < 0) break;
         const int item = item_tag & ~kItemBoundary;
+        if (item_tag & kItemBoundary) {
+            in_bnd = true;
+            if (threadIdx.x == 0) ++bnd_count;
+        }
         const int strip = item % p.strips, chunk = item / p.strips;
         const int c = 1 + strip * kTmaUCols + warp * kUColsPerWarp + lane;   // T column (U column if lane < 31)
         const bool warp_on = (c - lane) <= a.nxl;                       // warp-uniform
@@ -395,15 +431,15 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     a.u1[iu] = unew; a.v1[iu] = vnew;
                     if (c == 1 && a.uW) {
                         const size_t ig = (size_t)(r - 1) * ld + a.nxl_west + 1;
-                        a.uW[ig] = unew; a.vW[ig] = vnew; did_remote = true;
+                        a.uW[ig] = unew; a.vW[ig] = vnew;
                     }
                     if (c == a.nxl && a.uE) {
                         const size_t ig = (size_t)(r - 1) * ld;
-                        a.uE[ig] = unew; a.vE[ig] = vnew; did_remote = true;
+                        a.uE[ig] = unew; a.vE[ig] = vnew;
                     }
                     if (a.tripole && r - 1 >= a.ny - 1) {
                         tripole_push(a, c, (r - 1) - (a.ny - 1), unew, vnew);
-                        did_remote = true;
+                       
                     }
                 }
             }
@@ -415,29 +451,9 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             s1p = str[0]; s5p = str[4]; n2p = e2; n7p = e7;
             u_s = u_c; v_s = v_c; uw_s = uw_c; vw_s = vw_c; mprev = m; loaded_s = loaded_c;
         }
-        if (p.fused_signal && (item_tag & kItemBoundary)) {
-            // a boundary item is complete: count it; whoever completes the last one signals the
-            // peers -- the interior items of every rank are computed while the signals travel
-            if (did_remote) { __threadfence_system(); did_remote = false; }
-            asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
-            if (warp == 0) {
-                int fire = 0;
-                if (lane == 0) {
-                    __threadfence_system();
-                    fire = atomicAdd(p.done_bnd, 1) == p.item_count[1] - 1;
-                    if (fire) __threadfence_system();
-                }
-                fire = __shfl_sync(0xffffffffu, fire, 0);
-                if (fire) {
-                    peer_signal_warp(p.sync, lane);
-                    if (p.trace && lane == 0) p.trace[2] = global_ns();
-                }
-            }
-        }
     }
     if (p.fused_signal || p.trace) {
-        // only stores into peer memory (E-W ghosts, tripole inboxes) must be out before the signal
-        if (did_remote) __threadfence_system();
+        __threadfence_system();
         asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
         if (warp == 0) {
             int last = 0;
