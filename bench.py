@@ -202,7 +202,7 @@ def main():
     # reference balances its block distribution the same way), or equal widths
     starts = None
     if N > 1 and not args.equal_slabs:
-        starts = fx.balanced_slab_starts((grid.f["tmask"][1:-1, 1:-1] > 0).sum(axis=0), N)
+        starts = fx.balanced_slab_starts(grid.f["tmask"][1:-1, 1:-1] > 0, N)
 
     def sl(a):
         return fx.slab(a, rank, N, starts) if N > 1 else a

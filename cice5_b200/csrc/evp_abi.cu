@@ -829,7 +829,7 @@ void build_program(evp_handle *h, double dt, Program &P)
             dim3 grid(h->tstrips, (h->g.ny + 4 + 3) / 4);
             tile_flags_kernel<<<grid, 128, 0, s>>>(h->mask(), h->ldm, h->g.nxl, h->g.ny, h->tstrips, h->tflags(),
                                                   h->tflags_ld, h->gflags());
-            item_list_kernel<<<1, 1024, 0, s>>>(h->tflags(), h->tflags_ld, h->tstrips, h->t_chunks, h->t_rpc, h->g.ny,
+            item_list_kernel<<<1, kSortThreads, 0, s>>>(h->tflags(), h->tflags_ld, h->tstrips, h->t_chunks, h->t_rpc, h->g.ny,
                                                 h->g.tripole ? 1 : 0, h->west_closed() ? 0 : 1, h->east_closed() ? 0 : 1,
                                                 h->item_list(), h->item_count(), h->queue(0), 3 * h->cfg.ndte);
             L.n += 2;

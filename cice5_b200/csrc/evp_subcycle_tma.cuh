@@ -45,6 +45,7 @@ constexpr int kStateDepth = 14, kTDepth = 12, kUDepth = 10;
 // full row: 0 strength, 1 tinyarea, 2..9 dxt dyt dxhy dyhx cxp cyp cxm cym; both: 10 tarear (last
 // subcycle), 11 HTN of this row when only the next row needs it (its southern HTN).
 constexpr int kSlotTarear = 10, kSlotHtnExtra = 11;
+constexpr int kSortThreads = 64;
 constexpr int kItemBoundary = 0x40000000;    // tag of a work item that stores into peer memory
 // stage word bits written by the producer
 constexpr unsigned kMetaState = 1u, kMetaCompact = 2u, kMetaTinyFromMetrics = 4u, kMetaHtnExtra = 8u, kMetaT = 16u;
@@ -544,17 +545,23 @@ __global__ void item_list_kernel(const unsigned char *flags, int flags_ld, int s
                                  int tripole, int bnd_west, int bnd_east, int *list, int *count, int *queues,
                                  int nqueues)
 {
-    // weight = active rows of the item, 0 .. rpc + 2 <= 66; boundary items (they store into peer
-    // memory: E-W ghost columns, tripole inboxes) come first, so that the peers can be signalled
-    // while the interior items are still being computed: count[1] = number of boundary items
+    // Stable counting sort, one block of kSortThreads threads, thread t owns a contiguous range of
+    // items.  key = weight (rows of the item with ice, 0 .. rpc + 3 <= 67) + kW for boundary items
+    // (they store into peer memory: E-W ghost columns, tripole inboxes): boundary items first, so
+    // that the peers can be signalled while the interior items are still being computed, heaviest
+    // first inside each class; equal keys keep the item order (neighbouring items run at the same
+    // time and the list is the same on every call).  count[0] = items kept, count[1] = boundary.
     constexpr int kW = 80, kBins = 2 * kW;
-    __shared__ int hist[kBins], cursor[kBins];
-    for (int q = threadIdx.x; q < nqueues; q += blockDim.x) queues[q] = 0;
-    for (int q = threadIdx.x; q < kBins; q += blockDim.x) hist[q] = 0;
-    __syncthreads();
+    __shared__ int hist[kSortThreads][kBins];
+    __shared__ int binbase[kBins];
+    const int t = threadIdx.x;
+    for (int q = t; q < nqueues; q += blockDim.x) queues[q] = 0;
+    for (int q = 0; q < kBins; ++q) hist[t][q] = 0;
     const int items = strips * chunks;
+    const int per = (items + kSortThreads - 1) / kSortThreads;
+    const int i0 = min(t * per, items), i1 = min(i0 + per, items);
     for (int pass = 0; pass < 2; ++pass) {
-        for (int item = threadIdx.x; item < items; item += blockDim.x) {
+        for (int item = i0; item < i1; ++item) {
             const int strip = item % strips, chunk = item / strips;
             const int r0 = 1 + chunk * rpc, rend = min(r0 + rpc, ny + 1);
             const unsigned char *fl = flags + (size_t)strip * flags_ld;
@@ -563,20 +570,27 @@ __global__ void item_list_kernel(const unsigned char *flags, int flags_ld, int s
             if (w == 0 && tripole && rend >= ny - 2) w = 1;
             if (w == 0) continue;
             const bool bnd = (strip == 0 && bnd_west) || (strip == strips - 1 && bnd_east) || (tripole && rend >= ny - 2);
-            const int key = w + (bnd ? kW : 0);
-            if (pass == 0) atomicAdd(&hist[key], 1);
-            else list[atomicAdd(&cursor[key], 1)] = item;
+            const int key = min(w, kW - 1) + (bnd ? kW : 0);
+            if (pass == 0) ++hist[t][key];
+            else list[binbase[key] + hist[t][key]++] = item;
         }
         __syncthreads();
-        if (pass == 0 && threadIdx.x == 0) {
-            int off = 0;
-            for (int key = kBins - 1; key >= 1; --key) {
-                if (key == kW - 1) count[1] = off;              // everything before: boundary items
-                cursor[key] = off; off += hist[key];
+        if (pass == 0) {
+            if (t == 0) {
+                int off = 0;
+                for (int key = kBins - 1; key >= 1; --key) {
+                    if (key == kW - 1) count[1] = off;          // everything before: boundary items
+                    binbase[key] = off;
+                    for (int q = 0; q < kSortThreads; ++q) {    // exclusive scan over the threads
+                        const int n = hist[q][key];
+                        hist[q][key] = off - binbase[key];
+                        off += n;
+                    }
+                }
+                count[0] = off;
             }
-            count[0] = off;
+            __syncthreads();
         }
-        __syncthreads();
     }
 }
 

@@ -474,21 +474,47 @@ def slab(a: np.ndarray, rank: int, nranks: int, starts=None) -> np.ndarray:
     return np.ascontiguousarray(a[:, b[rank]: b[rank + 1] + 2])
 
 
-def balanced_slab_starts(weight_per_column: np.ndarray, nranks: int, min_width: int = 2) -> list:
+STRIP_COLUMNS = 124      # U columns per work strip of the subcycle kernel (4 warps x 31 columns)
+
+
+def balanced_slab_starts(ocean: np.ndarray, nranks: int, strip: int = STRIP_COLUMNS) -> list:
     """x-slab boundaries that even out the work per rank (what the reference's ice_distribution
-    does with its land-mask work estimate, source/ice_distribution.F90 create_distrb_*): greedy cut of
-    the cumulative column weight (e.g. ocean T cells per column) into nranks equal shares."""
-    w = np.asarray(weight_per_column, dtype="f8") + 1e-9
-    nx = w.size
-    cum = np.concatenate([[0.0], np.cumsum(w)])
-    starts = [0]
-    for r in range(1, nranks):
-        target = cum[-1] * r / nranks
-        c = int(np.searchsorted(cum, target))
-        c = max(c, starts[-1] + min_width)
-        c = min(c, nx - (nranks - r) * min_width)
-        starts.append(c)
-    return starts
+    does with its land-mask work estimate, source/ice_distribution.F90 create_distrb_*).
+
+    ocean: (ny, nx) bool, physical T cells.  The subcycle kernel works in strips of `strip` columns
+    and a strip row costs the same whether 1 or 124 of its cells hold ice, so the unit of work is
+    the (strip, row) segment with at least one ocean cell and slab boundaries sit on strip
+    boundaries: the strips are cut into `nranks` contiguous groups with the smallest possible
+    maximum work (exact, dynamic programme).  Grids narrower than nranks strips fall back to
+    cutting the cumulative ocean-cell count."""
+    ocean = np.asarray(ocean) > 0
+    ny, nx = ocean.shape
+    nstrips = -(-nx // strip)
+    if nstrips < nranks:
+        cum = np.concatenate([[0.0], np.cumsum(ocean.sum(axis=0) + 1e-9)])
+        starts = [0]
+        for r in range(1, nranks):
+            c = int(np.searchsorted(cum, cum[-1] * r / nranks))
+            c = min(max(c, starts[-1] + 2), nx - (nranks - r) * 2)
+            starts.append(c)
+        return starts
+    w = np.array([ocean[:, k * strip:(k + 1) * strip].any(axis=1).sum() + 1e-3 for k in range(nstrips)])
+    pre = np.concatenate([[0.0], np.cumsum(w)])
+    INF = float("inf")
+    best = [[INF] * (nstrips + 1) for _ in range(nranks + 1)]
+    cut = [[0] * (nstrips + 1) for _ in range(nranks + 1)]
+    best[0][0] = 0.0
+    for r in range(1, nranks + 1):
+        for e in range(r, nstrips + 1):
+            for b in range(r - 1, e):
+                v = max(best[r - 1][b], pre[e] - pre[b])
+                if v < best[r][e]:
+                    best[r][e], cut[r][e] = v, b
+    bounds, e = [], nstrips
+    for r in range(nranks, 0, -1):
+        e = cut[r][e]
+        bounds.append(e)
+    return [b * strip for b in reversed(bounds)]
 
 
 def unslab(parts: list) -> np.ndarray:

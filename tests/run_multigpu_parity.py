@@ -36,7 +36,7 @@ def main():
     dom = case.dom
     starts = None
     if args.balanced:
-        starts = fx.balanced_slab_starts((grid.f["tmask"][1:-1, 1:-1] > 0).sum(axis=0), world)
+        starts = fx.balanced_slab_starts(grid.f["tmask"][1:-1, 1:-1] > 0, world)
     sl = lambda d: {k: fx.slab(v, rank, world, starts) for k, v in d.items()}
     e = evp.EvpGpu.for_domain(dom, args.ndte, case.dt, rank=rank, nranks=world, device=local,
                               strict=True, use_cuda_graph=bool(args.graph), slab_start=starts)
