@@ -31,6 +31,10 @@ import numpy as np
 
 ALG_BYTES = 392.0          # per active cell-subcycle (49 doubles), SURVEY.md section 8d
 L2_BYTES = 126e6
+# dram__bytes_read.sum + dram__bytes_write.sum of one evp_subcycle_tma_kernel<false> launch on the
+# default workload (tp01 full, 1 GPU), from the ncu pass in profiles/r01_launches_tp01_final.md;
+# only quoted for exactly that workload
+NCU_TRAFFIC = {("tp01", "full", 1, True): 1.7716e9 + 0.8417e9}
 
 
 def parse():
@@ -311,7 +315,16 @@ def main():
         sub_ms = loop_ms / (args.steps * args.ndte)
         ach = ALG_BYTES * (act_phys / N) / (sub_ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "peak_source": peak_src, "kernel": "evp_subcycle_kernel",
+                "traffic": NCU_TRAFFIC.get((args.grid, args.scenario, N, not args.no_compact_metrics)),
+                "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum per launch, "
+                                  "profiles/r01_launches_tp01_final.md (null for other workloads)",
+                "peak_source": peak_src,
+                "kernel": "evp_subcycle_tma_kernel<false> (fused stress + stepu + E-W halo, TMA ring)"
+                          if os.environ.get("EVP_B200_KERNEL", "tma") != "sweep" else "evp_subcycle_kernel<false>",
+                "note": "achieved = 392 algorithmic B x active cells of one launch / (ndte-loop CUDA-event time / "
+                        "ndte); the loop also holds the small tripole fold kernel of every subcycle.  The kernel "
+                        "really moves fewer bytes than the algorithmic 392 B/cell (compact metric rows, merged "
+                        "coefficient planes): see traffic",
                 "alg_bytes_per_cell_subcycle": ALG_BYTES, "avg_launch_ms": sub_ms,
                 "active_cells_per_launch": act_phys / N}
         res = {"metric": "EVP cell-subcycles/s", "value": value, "unit": "cell-subcycles/s",

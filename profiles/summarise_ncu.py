@@ -32,21 +32,31 @@ def rows_of(path):
 
 
 def launches(path):
+    """Per-kernel launches, time share, average duration and (when the pass collected them) DRAM
+    bytes read / written per launch."""
     rows = rows_of(path)
     hdr = rows[0]
-    ik, iv, im = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Metric Name")
+    ik, iv, im, iu = (hdr.index(k) for k in ("Kernel Name", "Metric Value", "Metric Name", "Metric Unit"))
+    scale = {"ns": 1.0, "us": 1e3, "ms": 1e6, "byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     agg = OrderedDict()
     for r in rows[1:]:
-        if r[im] != "gpu__time_duration.sum":
-            continue
-        a = agg.setdefault(r[ik], [0, 0.0])
-        a[0] += 1
-        a[1] += float(r[iv].replace(",", ""))
-    tot = sum(v[1] for v in agg.values())
-    print("| kernel | launches | total (ns) | share | avg (ns) |\n|---|---:|---:|---:|---:|")
-    for k, (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
-        print(f"| `{k}` | {n} | {t:.0f} | {100 * t / tot:.2f} % | {t / n:.1f} |")
-    print(f"| **all** | {sum(v[0] for v in agg.values())} | {tot:.0f} | 100 % | |")
+        a = agg.setdefault(r[ik], {"n": 0, "t": 0.0, "rd": 0.0, "wr": 0.0})
+        v = float(r[iv].replace(",", "")) * scale.get(r[iu], 1.0)
+        if r[im] == "gpu__time_duration.sum":
+            a["n"] += 1
+            a["t"] += v
+        elif r[im] == "dram__bytes_read.sum":
+            a["rd"] += v
+        elif r[im] == "dram__bytes_write.sum":
+            a["wr"] += v
+    tot = sum(a["t"] for a in agg.values())
+    print("| kernel | launches | total (ns) | share | avg (ns) | DRAM read / launch (MB) | DRAM write / launch (MB) |")
+    print("|---|---:|---:|---:|---:|---:|---:|")
+    for k, a in sorted(agg.items(), key=lambda kv: -kv[1]["t"]):
+        n = a["n"]
+        print(f"| `{k}` | {n} | {a['t']:.0f} | {100 * a['t'] / tot:.2f} % | {a['t'] / n:.1f} | "
+              f"{a['rd'] / n / 1e6:.1f} | {a['wr'] / n / 1e6:.1f} |")
+    print(f"| **all** | {sum(a['n'] for a in agg.values())} | {tot:.0f} | 100 % | | | |")
 
 
 def full(path, pattern=".*"):
