@@ -30,12 +30,14 @@
          integer(c_int) :: ndte, kdyn, revised_evp, ew_boundary, ns_boundary, grid_tripole
          integer(c_int) :: tilt_mode, strength_masked, use_cuda_graph
          real(c_double) :: dt_init, cosw, sinw, rhow, rhoi, rhos, gravit, a_min, m_min
+         integer(c_int) :: slab_start(9)     ! all zero: equal x-slabs (CICE blocks have one size)
       end type
 
       type, bind(C) :: evp_grid_t
          type(c_ptr) :: dxt, dyt, dxhy, dyhx, cxp, cyp, cxm, cym
          type(c_ptr) :: tarea, uarea, tarear, uarear, tinyarea, fcor
          type(c_ptr) :: tmask, umask
+         type(c_ptr) :: HTE, HTN             ! optional (c_null_ptr): compact metric rows
       end type
 
       type, bind(C) :: evp_in_t
@@ -132,7 +134,7 @@
       use ice_domain_size, only: nx_global, ny_global
       use ice_exit, only: abort_ice
       use ice_grid, only: tmask, umask, dxt, dyt, dxhy, dyhx, cxp, cyp, cxm, cym, &
-          tarea, uarea, tarear, uarear, tinyarea, grid_type
+          tarea, uarea, tarear, uarear, tinyarea, grid_type, HTE, HTN
       include 'mpif.h'
       real (kind=dbl_kind), intent(in) :: dt
       type(evp_config_t) :: cfg
@@ -172,6 +174,7 @@
       cfg%cosw = cosw;  cfg%sinw = sinw
       cfg%rhow = rhow;  cfg%rhoi = rhoi;  cfg%rhos = rhos;  cfg%gravit = gravit
       cfg%a_min = a_min;  cfg%m_min = m_min
+      cfg%slab_start = 0            ! blocks of one size: task r owns columns r*block_size_x+1 ...
       call check(evp_gpu_init(cfg, handle), 'init')
 
       allocate(tmask_i(nx_block,ny_block), umask_i(nx_block,ny_block), &
@@ -185,6 +188,9 @@
       g%tarear = c_loc(tarear(1,1,1)); g%uarear = c_loc(uarear(1,1,1))
       g%tinyarea = c_loc(tinyarea(1,1,1)); g%fcor = c_loc(fcor_blk(1,1,1))
       g%tmask = c_loc(tmask_i(1,1));   g%umask = c_loc(umask_i(1,1))
+      ! HTE, HTN (ice_grid.F90:51-52): where the library verifies, cell by cell, that the metric
+      ! arrays above follow from them bit for bit it fetches these two instead of nine planes
+      g%HTE = c_loc(HTE(1,1,1));       g%HTN = c_loc(HTN(1,1,1))
       call check(evp_gpu_set_grid(handle, g), 'set_grid')
 
       if (ntasks > 1) then          ! exchange the peer-memory handles of all tasks of the node
