@@ -155,9 +155,9 @@ namespace {
 
 size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-// set_evp_parameters, source/ice_dyn_shared.F90:209-257 (classic branch); constants
+// set_evp_parameters, source/ice_dyn_shared.F90:209-257; constants
 // drivers/cice/ice_constants.F90:142-148 are computed, not literals.
-void set_evp_parameters(const evp_config_t &c, Consts &k)
+void set_evp_parameters(const evp_config_t &c, Consts &k, double xmin = 1.0)
 {
     const double c1 = 1.0, c2 = 2.0, p5 = 0.5, eyc = 0.36;
     k.p166 = c1 / 6.0; k.p333 = c1 / 3.0; k.p111 = c1 / 9.0;
@@ -167,9 +167,17 @@ void set_evp_parameters(const evp_config_t &c, Consts &k)
     k.ecci = 0.25;
     const double tdamp2 = c2 * eyc * c.dt_init;
     const double dte2T = dte / tdamp2;
-    k.revp = 0.0;
-    k.arlx1i = dte2T;
-    k.brlx = c.dt_init * dtei;
+    if (c.revised_evp) {            // Bouillon et al. 2013 (:225-233); xmin = min(dxt, dyt) over tmask
+        const double Se = 0.86, xi = 5.5e-3;
+        const double gamma = 0.25 * 1.e11 * c.dt_init;
+        k.revp = c1;
+        k.arlx1i = c2 * xi / Se;
+        k.brlx = c2 * Se * xi * gamma / (xmin * xmin);
+    } else {
+        k.revp = 0.0;
+        k.arlx1i = dte2T;
+        k.brlx = c.dt_init * dtei;
+    }
     k.denom1 = c1 / (c1 + k.arlx1i);
     k.cosw = c.cosw; k.sinw = c.sinw; k.rhow = c.rhow;
 }
@@ -221,9 +229,13 @@ int make_tensor_maps(evp_handle *h)
         snprintf(g_cuda_err, sizeof(g_cuda_err), "cuTensorMapEncodeTiled(mask) failed: %d", (int)r);
         return EVP_ERR_CUDA;
     }
-    CK(cudaFuncSetAttribute(evp_subcycle_tma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    CK(cudaFuncSetAttribute(evp_subcycle_tma_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                             kTmaStages * kStageBytes));
-    CK(cudaFuncSetAttribute(evp_subcycle_tma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    CK(cudaFuncSetAttribute(evp_subcycle_tma_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            kTmaStages * kStageBytes));
+    CK(cudaFuncSetAttribute(evp_subcycle_tma_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            kTmaStages * kStageBytes));
+    CK(cudaFuncSetAttribute(evp_subcycle_tma_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                             kTmaStages * kStageBytes));
     return EVP_OK;
 }
@@ -241,7 +253,7 @@ const char *evp_gpu_strerror(int status)
         case EVP_OK: return "ok";
         case EVP_ERR_ARG: return "evp_gpu: invalid argument (null pointer or inconsistent block sizes)";
         case EVP_ERR_UNSUPPORTED:
-            return "evp_gpu: unsupported configuration (needs kdyn=1, revised_evp=.false., "
+            return "evp_gpu: unsupported configuration (needs kdyn=1 (EVP), "
                    "tripole only with cyclic E-W, nranks <= 8, slabs >= 2 columns)";
         case EVP_ERR_CUDA: return "evp_gpu: CUDA runtime error (see evp_gpu_last_cuda_error)";
         case EVP_ERR_STATE: return "evp_gpu: call order violated (init -> set_grid -> [set_peers] -> run)";
@@ -264,7 +276,8 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
 {
     if (!cfg || !out) return EVP_ERR_ARG;
     *out = nullptr;
-    if (cfg->kdyn != 1 || cfg->revised_evp != 0) return EVP_ERR_UNSUPPORTED;
+    if (cfg->kdyn != 1 || cfg->revised_evp < 0 || cfg->revised_evp > 1) return EVP_ERR_UNSUPPORTED;
+    if (cfg->revised_evp && cfg->nranks > 1 && !(cfg->xmin > 0.0)) return EVP_ERR_ARG;   // needs the GLOBAL xmin
     if (cfg->nranks < 1 || cfg->nranks > kMaxRanks || cfg->rank < 0 || cfg->rank >= cfg->nranks)
         return EVP_ERR_UNSUPPORTED;
     if (cfg->nx_global < 2 || cfg->ny_global < 3 || cfg->ndte < 1 || !(cfg->dt_init > 0.0)) return EVP_ERR_ARG;
@@ -441,6 +454,23 @@ int evp_gpu_set_grid(evp_handle_t *h, const evp_grid_t *gr)
     const int dstp[14] = {G_DXT, G_DYT, G_DXHY, G_DYHX, G_CXP, G_CYP, G_CXM, G_CYM,
                           G_TAREA, G_UAREA, G_TAREAR, G_UAREAR, G_TINYAREA, G_FCOR};
     for (int p = 0; p < 14; ++p) TRY(h2d(h, dstp[p], src[p]));
+    if (h->cfg.revised_evp) {
+        // xmin = min(global_minval(dxt, tmask), global_minval(dyt, tmask)) (ice_dyn_shared.F90:220-223):
+        // given by the host when the domain is split over tasks, else taken from this block
+        double xmin = h->cfg.xmin;
+        if (!(xmin > 0.0)) {
+            xmin = 1.0e300;
+            for (int j = 1; j <= h->g.ny; ++j)
+                for (int i = 1; i <= h->g.nxl; ++i) {
+                    const size_t q = (size_t)j * h->nxb + i;
+                    if (gr->tmask[q]) {
+                        if (gr->dxt[q] < xmin) xmin = gr->dxt[q];
+                        if (gr->dyt[q] < xmin) xmin = gr->dyt[q];
+                    }
+                }
+        }
+        set_evp_parameters(h->cfg, h->k, xmin);
+    }
     h->have_ht = gr->HTE && gr->HTN;
     CK(cudaMemsetAsync(h->gflags(), 0, (size_t)h->tstrips * h->tflags_ld, h->stream));
     if (h->have_ht) {
@@ -673,6 +703,7 @@ void fill_loop_args(const evp_handle *h, int from_parity, int inbox_buf, LoopArg
     a.divu = h->plane(O_DIVU); a.shear = h->plane(O_SHEAR); a.rdg_conv = h->plane(O_RDGCONV);
     a.rdg_shear = h->plane(O_RDGSHEAR); a.prs_sig = h->plane(O_PRSSIG);
     a.strintx = h->plane(O_STRINTX); a.strinty = h->plane(O_STRINTY);
+    a.uvel_init = h->plane(O_UVELINIT); a.vvel_init = h->plane(O_VVELINIT);
     // E-W ghosts of the NEW velocity planes are written in place (self, or peer memory over
     // NVLink): the ping-pong separates these stores from every read of the same plane by one sync
     if (!h->west_closed()) { a.uW = h->plane(U1, h->west()); a.vW = h->plane(V1, h->west()); }
@@ -719,19 +750,18 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
             t.trace = h->trace(ksub - 1);
             const int grid = t.items < slots ? t.items : slots;
             const size_t smem = (size_t)kTmaStages * kStageBytes;
-            if (last)
-                evp_subcycle_tma_kernel<true><<<grid, (kTmaConsumers + 1) * 32, smem, L.s()>>>(
-                    h->mapS, h->mapS2, h->mapT1, h->mapT3, h->mapT4, h->mapT10, mapU, h->mapM, t);
-            else
-                evp_subcycle_tma_kernel<false><<<grid, (kTmaConsumers + 1) * 32, smem, L.s()>>>(
-                    h->mapS, h->mapS2, h->mapT1, h->mapT3, h->mapT4, h->mapT10, mapU, h->mapM, t);
+            auto kern = h->cfg.revised_evp ? (last ? evp_subcycle_tma_kernel<true, true> : evp_subcycle_tma_kernel<false, true>)
+                                           : (last ? evp_subcycle_tma_kernel<true, false> : evp_subcycle_tma_kernel<false, false>);
+            kern<<<grid, (kTmaConsumers + 1) * 32, smem, L.s()>>>(h->mapS, h->mapS2, h->mapT1, h->mapT3, h->mapT4,
+                                                                   h->mapT10, mapU, h->mapM, t);
             ++L.n;
             return EVP_OK;
         }
         const int strips = (g.nxl + kUColsPerWarp - 1) / kUColsPerWarp;
         dim3 grid((strips + kWarpsPerBlock - 1) / kWarpsPerBlock, (g.ny + a.rows_per_chunk - 1) / a.rows_per_chunk);
-        if (last) evp_subcycle_kernel<true><<<grid, kWarpsPerBlock * 32, 0, L.s()>>>(a);
-        else evp_subcycle_kernel<false><<<grid, kWarpsPerBlock * 32, 0, L.s()>>>(a);
+        auto kern1 = h->cfg.revised_evp ? (last ? evp_subcycle_kernel<true, true> : evp_subcycle_kernel<false, true>)
+                                        : (last ? evp_subcycle_kernel<true, false> : evp_subcycle_kernel<false, false>);
+        kern1<<<grid, kWarpsPerBlock * 32, 0, L.s()>>>(a);
         ++L.n;
         return EVP_OK;
     });
@@ -809,6 +839,7 @@ void build_program(evp_handle *h, double dt, Program &P)
             a.strairy = h->plane(O_STRAIRY); a.ss_tltx = h->plane(I_SSTLTX); a.ss_tlty = h->plane(I_SSTLTY);
             a.icetmask = h->plane(W_ICETMASK); a.strength_in = h->plane(I_STRENGTH);
             a.rhow = cfg.rhow; a.Cw = h->plane(I_CW); a.vrelc = h->plane(W_VRELC);
+            a.revised = cfg.revised_evp;
             a.umask = h->iplane(1); a.iceumask = h->iplane(2);
             a.fm = h->plane(S_FM); a.strtltx = h->plane(O_STRTLTX); a.strtlty = h->plane(O_STRTLTY);
             a.strocnx = h->plane(O_STROCNX); a.strocny = h->plane(O_STROCNY);

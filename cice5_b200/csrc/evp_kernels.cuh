@@ -46,6 +46,7 @@ struct LoopArgs {
     const double *dxt, *dyt, *dxhy, *dyhx, *cxp, *cyp, *cxm, *cym, *tinyarea, *strength, *tarear;
     const double *aiu, *Cw, *uocn, *vocn, *waterx, *watery, *forcex, *forcey, *umassdti, *fm, *uarear;
     double *divu, *shear, *rdg_conv, *rdg_shear, *prs_sig, *strintx, *strinty;
+    const double *uvel_init, *vvel_init;   // read by stepu only under revised EVP (revp = 1)
     // E-W ghost pushes: new-velocity planes of the west / east neighbour (self when cyclic on
     // one GPU, peer memory over NVLink otherwise, null on a closed edge)
     double *uW, *vW, *uE, *vE;
@@ -214,7 +215,7 @@ __device__ __forceinline__ void tripole_push(const LoopArgs &a, int c, int rowse
     }
 }
 
-template <bool LAST>
+template <bool LAST, bool REVISED = false>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 evp_subcycle_kernel(const __grid_constant__ LoopArgs a)
 {
@@ -292,8 +293,10 @@ evp_subcycle_kernel(const __grid_constant__ LoopArgs a)
                     const double strintx = uar * (s1p + n2p + str[2] + e4);
                     const double strinty = uar * (s5p + str[5] + n7p + e8);
                     // revp = 0 for classic EVP, so revp*uvel_init vanishes (:731-734)
-                    const double cc1 = strintx + a.forcex[iu] + taux + umdt * (k.brlx * uold);
-                    const double cc2 = strinty + a.forcey[iu] + tauy + umdt * (k.brlx * vold);
+                    const double cc1 = strintx + a.forcex[iu] + taux +
+                                       umdt * (REVISED ? k.brlx * uold + k.revp * a.uvel_init[iu] : k.brlx * uold);
+                    const double cc2 = strinty + a.forcey[iu] + tauy +
+                                       umdt * (REVISED ? k.brlx * vold + k.revp * a.vvel_init[iu] : k.brlx * vold);
                     unew = (cca * cc1 + ccb * cc2) / ab2;
                     vnew = (cca * cc2 - ccb * cc1) / ab2;
                     if (LAST) { a.strintx[iu] = strintx; a.strinty[iu] = strinty; }

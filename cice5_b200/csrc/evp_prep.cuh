@@ -227,6 +227,7 @@ struct Prep2Args {
     Geom g;
     double dt, a_min, m_min, cosw, sinw, gravit, rhow;
     int tilt_mode, strength_masked;
+    int revised;                                // revised EVP: all stresses restart from zero (:492-504)
     const double *Cw;
     double *vrelc;                              // aiu*rhow*Cw: the constant factor of stepu's vrel
     const double *aiu, *umass, *fcor, *uocn, *vocn, *strairx, *strairy, *ss_tltx, *ss_tlty;
@@ -250,7 +251,7 @@ __global__ void prep2_kernel(const __grid_constant__ Prep2Args a)
     const size_t q = (size_t)r * g.ld + c;
     const bool tice = a.icetmask[q] == 1.0;
     double waterx = 0.0, watery = 0.0, forcex = 0.0, forcey = 0.0, umassdti = 0.0;   // :486-490
-    if (!tice) {                                                                       // :505-517
+    if (!tice || a.revised) {                                                          // :492-517
 #pragma unroll
         for (int s = 0; s < 12; ++s) { a.sA[s][q] = 0.0; a.sB[s][q] = 0.0; }
     } else {

@@ -165,7 +165,7 @@ __device__ __noinline__ void boundary_done(const TmaArgs &p, int *bnd_count, int
     }
 }
 
-template <bool LAST>
+template <bool LAST, bool REVISED = false>
 __global__ void __launch_bounds__((kTmaConsumers + 1) * 32, kTmaBlocksPerSM)
 evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_constant__ CUtensorMap mapS2,
                         const __grid_constant__ CUtensorMap mapT1,
@@ -418,8 +418,12 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     const double uar = uco[7];
                     const double strintx = uar * (s1p + n2p + str[2] + e4);
                     const double strinty = uar * (s5p + str[5] + n7p + e8);
-                    const double cc1 = strintx + uco[3] + taux + umdt * (k.brlx * uold);
-                    const double cc2 = strinty + uco[4] + tauy + umdt * (k.brlx * vold);
+                    // revised EVP (revp = 1) also needs uvel_init (:731-734): two direct global loads,
+                    // only in the REVISED instantiation
+                    const double cc1 = strintx + uco[3] + taux +
+                                       umdt * (REVISED ? k.brlx * uold + k.revp * a.uvel_init[iu] : k.brlx * uold);
+                    const double cc2 = strinty + uco[4] + tauy +
+                                       umdt * (REVISED ? k.brlx * vold + k.revp * a.vvel_init[iu] : k.brlx * vold);
 #ifdef EVP_TMA_NOCOMPUTE
                     unew = cca + cc1 + ab2; vnew = ccb + cc2;
 #else

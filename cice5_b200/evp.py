@@ -28,7 +28,7 @@ class Config(C.Structure):
         "nx_global", "ny_global", "nx_block", "ny_block", "rank", "nranks", "device", "ndte",
         "kdyn", "revised_evp", "ew_boundary", "ns_boundary", "grid_tripole", "tilt_mode",
         "strength_masked", "use_cuda_graph")] + [(n, C.c_double) for n in (
-        "dt_init", "cosw", "sinw", "rhow", "rhoi", "rhos", "gravit", "a_min", "m_min")] + [
+        "dt_init", "cosw", "sinw", "rhow", "rhoi", "rhos", "gravit", "a_min", "m_min", "xmin")] + [
         ("slab_start", C.c_int * 9)]
 
 
@@ -122,7 +122,7 @@ class EvpGpu:
                  ew_cyclic=True, ns_boundary="open", grid_tripole=False, tilt_mode=0,
                  strength_masked=0, cosw=1.0, sinw=0.0, rhow=1026.0, rhoi=917.0, rhos=330.0,
                  gravit=9.80616, a_min=1.0e-3, m_min=1.0e-2, kdyn=1, revised_evp=False,
-                 use_cuda_graph=False, strict=True, compact_metrics=True, slab_start=None):
+                 use_cuda_graph=False, strict=True, compact_metrics=True, slab_start=None, xmin=0.0):
         self.lib = load_library(strict)
         self.compact_metrics = compact_metrics      # pass HTE / HTN to set_grid when the grid has them
         ns = {"open": 0, "closed": 1, "tripole": 2}[ns_boundary]
@@ -143,7 +143,7 @@ class EvpGpu:
                           grid_tripole=int(grid_tripole), tilt_mode=tilt_mode,
                           strength_masked=strength_masked, use_cuda_graph=int(use_cuda_graph),
                           dt_init=dt_init, cosw=cosw, sinw=sinw, rhow=rhow, rhoi=rhoi, rhos=rhos,
-                          gravit=gravit, a_min=a_min, m_min=m_min)
+                          gravit=gravit, a_min=a_min, m_min=m_min, xmin=xmin)
         for r, x in enumerate(slab_start):
             self.cfg.slab_start[r] = x
         self._h = C.c_void_p()

@@ -30,6 +30,7 @@
          integer(c_int) :: ndte, kdyn, revised_evp, ew_boundary, ns_boundary, grid_tripole
          integer(c_int) :: tilt_mode, strength_masked, use_cuda_graph
          real(c_double) :: dt_init, cosw, sinw, rhow, rhoi, rhos, gravit, a_min, m_min
+         real(c_double) :: xmin              ! revised EVP: global min(dxt, dyt) over tmask cells
          integer(c_int) :: slab_start(9)     ! all zero: equal x-slabs (CICE blocks have one size)
       end type
 
@@ -130,7 +131,8 @@
       use ice_blocks, only: nx_block, ny_block
       use ice_communicate, only: my_task, MPI_COMM_ICE, get_num_procs
       use ice_constants, only: rhow, rhoi, rhos, gravit
-      use ice_domain, only: nblocks, ew_boundary_type, ns_boundary_type
+      use ice_domain, only: nblocks, ew_boundary_type, ns_boundary_type, distrb_info
+      use ice_global_reductions, only: global_minval
       use ice_domain_size, only: nx_global, ny_global
       use ice_exit, only: abort_ice
       use ice_grid, only: tmask, umask, dxt, dyt, dxhy, dyhx, cxp, cyp, cxm, cym, &
@@ -174,6 +176,8 @@
       cfg%cosw = cosw;  cfg%sinw = sinw
       cfg%rhow = rhow;  cfg%rhoi = rhoi;  cfg%rhos = rhos;  cfg%gravit = gravit
       cfg%a_min = a_min;  cfg%m_min = m_min
+      ! xmin exactly as set_evp_parameters computes it (ice_dyn_shared.F90:220-223)
+      cfg%xmin = min(global_minval(dxt, distrb_info, tmask), global_minval(dyt, distrb_info, tmask))
       cfg%slab_start = 0            ! blocks of one size: task r owns columns r*block_size_x+1 ...
       call check(evp_gpu_init(cfg, handle), 'init')
 

@@ -29,7 +29,7 @@ typedef struct evp_handle evp_handle_t;
 enum {
     EVP_OK = 0,
     EVP_ERR_ARG = 1,          /* null pointer / inconsistent sizes                      */
-    EVP_ERR_UNSUPPORTED = 2,  /* kdyn != 1, revised_evp, unsupported boundary type      */
+    EVP_ERR_UNSUPPORTED = 2,  /* kdyn != 1, unsupported boundary type / decomposition   */
     EVP_ERR_CUDA = 3,         /* a CUDA runtime call failed (see evp_gpu_last_cuda_error) */
     EVP_ERR_STATE = 4,        /* call order violated (e.g. run before set_grid)         */
     EVP_ERR_NO_DEVICE = 5,    /* no usable CUDA device: there is NO CPU fallback        */
@@ -47,7 +47,8 @@ typedef struct {
     int device;                 /* CUDA device ordinal for this task                           */
     int ndte;                   /* dynamics_nml ndte (ice_dyn_shared.F90:33)                   */
     int kdyn;                   /* must be 1 (EVP)                                             */
-    int revised_evp;            /* must be 0 (classic EVP, ice_dyn_shared.F90:239-242)          */
+    int revised_evp;            /* 0: classic EVP (ice_dyn_shared.F90:239-242); 1: revised EVP
+                                   (Bouillon et al. 2013, :230-233,492-504,715,732-734)         */
     int ew_boundary;            /* EVP_EW_*   (ice_domain.F90 ew_boundary_type)                 */
     int ns_boundary;            /* EVP_NS_*   (ns_boundary_type; tripole = u-fold)              */
     int grid_tripole;           /* grid_type == 'tripole' (ice_dyn_evp.F90:416)                 */
@@ -61,6 +62,9 @@ typedef struct {
     double cosw, sinw;          /* ocean turning angle (namelist under AusCOM)                  */
     double rhow, rhoi, rhos, gravit;
     double a_min, m_min;        /* ice_dyn_shared.F90:60-61                                     */
+    double xmin;                /* revised EVP only: min(dxt, dyt) over ALL tmask cells of the
+                                   global domain (ice_dyn_shared.F90:220-223); 0 = take it from this
+                                   task's block (only valid when nranks == 1)                    */
     int slab_start[9];          /* first global column (0-based) of every rank's x-slab; all zero =
                                    equal slabs of nx_global/nranks columns.  Unequal slabs are the
                                    load balancing the reference does in ice_distribution

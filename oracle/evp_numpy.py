@@ -21,15 +21,21 @@ def _sh(a, di, dj):
     return a[1 + dj:1 + dj + ny, 1 + di:1 + di + nx]
 
 
-def evp_parameters(dt, ndte):
-    """set_evp_parameters, classic branch (ice_dyn_shared.F90:209-257)."""
+def evp_parameters(dt, ndte, revised_evp=False, xmin=None):
+    """set_evp_parameters (ice_dyn_shared.F90:209-257); xmin = min(dxt, dyt) over tmask cells."""
     dte = dt / float(ndte)
     dtei = 1.0 / dte
     ecci = 0.25
     tdamp2 = 2.0 * 0.36 * dt
     dte2T = dte / tdamp2
-    arlx1i = dte2T
-    brlx = dt * dtei
+    if revised_evp:                        # Bouillon et al. 2013 (:225-233)
+        Se, xi = 0.86, 5.5e-3
+        gamma = 0.25 * 1.0e11 * dt
+        arlx1i = 2.0 * xi / Se
+        brlx = 2.0 * Se * xi * gamma / (xmin * xmin)
+    else:
+        arlx1i = dte2T
+        brlx = dt * dtei
     denom1 = 1.0 / (1.0 + arlx1i)
     return ecci, arlx1i, brlx, denom1
 
@@ -158,12 +164,15 @@ def stress(k, ksub, ndte, tact, u, v, g, strength, S, out):
     return full
 
 
-def evp(case, cosw=1.0, sinw=0.0, tilt_mode=0, strength_masked=0, dt_init=None):
+def evp(case, cosw=1.0, sinw=0.0, tilt_mode=0, strength_masked=0, dt_init=None, revised_evp=False):
     """One call of evp(dt) on a fixtures.Case (single block); updates case.io / case.out in place."""
     dom, g, inp, io, out = case.dom, case.grid.f, case.inp, case.io, case.out
     dt, ndte = case.dt, case.ndte
-    k = evp_parameters(case.dt if dt_init is None else dt_init, ndte)
+    tm = g["tmask"][1:-1, 1:-1] > 0
+    xmin = min(g["dxt"][1:-1, 1:-1][tm].min(), g["dyt"][1:-1, 1:-1][tm].min())
+    k = evp_parameters(case.dt if dt_init is None else dt_init, ndte, revised_evp, xmin)
     brlx = k[2]
+    revp = 1.0 if revised_evp else 0.0
     rhoi, rhos, rhow, gravit = fx.RHOI, fx.RHOS, fx.RHOW, fx.GRAVIT
     a_min, m_min = 1.0e-3, 1.0e-2
     P = (slice(1, -1), slice(1, -1))
@@ -193,7 +202,10 @@ def evp(case, cosw=1.0, sinw=0.0, tilt_mode=0, strength_masked=0, dt_init=None):
     strairy = to_ugrid(w, g["tarea"], g["uarea"])
     # evp_prep2 (ice_dyn_shared.F90:484-612)
     for n in fx.STRESS_FIELDS:
-        S[n][icetmask == 0] = 0.0
+        if revised_evp:
+            S[n][...] = 0.0                                                       # :492-504
+        else:
+            S[n][icetmask == 0] = 0.0
     tact = icetmask == 1
     tact[0, :] = False; tact[:, 0] = False
     old = io["iceumask"] > 0
@@ -242,14 +254,14 @@ def evp(case, cosw=1.0, sinw=0.0, tilt_mode=0, strength_masked=0, dt_init=None):
         uold, vold = u.copy(), v.copy()
         vrel = aiu * rhow * Cw * np.sqrt((uo - uold) * (uo - uold) + (vo - vold) * (vo - vold))
         taux, tauy = vrel * waterx, vrel * watery
-        cca = (brlx + 0.0) * umassdti + vrel * cosw
+        cca = (brlx + revp) * umassdti + vrel * cosw
         ccb = fm + np.copysign(1.0, fm) * vrel * sinw
         ab2 = cca * cca + ccb * ccb
         sx, sy = np.zeros(u.shape), np.zeros(u.shape)
         sx[P] = uarear[P] * (_sh(s[0], 0, 0) + _sh(s[1], 1, 0) + _sh(s[2], 0, 1) + _sh(s[3], 1, 1))
         sy[P] = uarear[P] * (_sh(s[4], 0, 0) + _sh(s[5], 0, 1) + _sh(s[6], 1, 0) + _sh(s[7], 1, 1))
-        cc1 = sx + forcex + taux + umassdti * (brlx * uold + 0.0 * out["uvel_init"])
-        cc2 = sy + forcey + tauy + umassdti * (brlx * vold + 0.0 * out["vvel_init"])
+        cc1 = sx + forcex + taux + umassdti * (brlx * uold + revp * out["uvel_init"])
+        cc2 = sy + forcey + tauy + umassdti * (brlx * vold + revp * out["vvel_init"])
         with np.errstate(divide="ignore", invalid="ignore"):
             un = (cca * cc1 + ccb * cc2) / ab2
             vn = (cca * cc2 - ccb * cc1) / ab2

@@ -27,7 +27,9 @@ typedef struct {
     double dte, dtei, ecci, dte2T, revp, arlx1i, brlx, denom1;
 } Consts;
 
-static void set_evp_parameters(Consts *k, double dt, int ndte)
+/* xmin = min(global_minval(dxt, tmask), global_minval(dyt, tmask)), ice_dyn_shared.F90:220-223;
+ * only the revised-EVP branch uses it */
+static void set_evp_parameters(Consts *k, double dt, int ndte, int revised_evp, double xmin)
 {
     k->p166 = c1 / 6.0;
     k->p333 = c1 / 3.0;
@@ -42,9 +44,18 @@ static void set_evp_parameters(Consts *k, double dt, int ndte)
         double tdamp2 = c2 * eyc * dt;   /* :217 */
         k->dte2T = k->dte / tdamp2;      /* :218 */
     }
-    k->revp = c0;                        /* :240 */
-    k->arlx1i = k->dte2T;                /* :241 */
-    k->brlx = dt * k->dtei;              /* :242 */
+    if (revised_evp) {                   /* Bouillon et al. 2013, :225-233 */
+        const double Se = 0.86;          /* :226 */
+        const double xi = 5.5e-3;        /* :227 */
+        const double gamma = p25 * 1.e11 * dt;            /* :228 */
+        k->revp = c1;                    /* :231 */
+        k->arlx1i = c2 * xi / Se;        /* :232 */
+        k->brlx = c2 * Se * xi * gamma / (xmin * xmin);   /* :233  xmin**2 */
+    } else {
+        k->revp = c0;                    /* :240 */
+        k->arlx1i = k->dte2T;            /* :241 */
+        k->brlx = dt * k->dtei;          /* :242 */
+    }
     k->denom1 = c1 / (c1 + k->arlx1i);   /* :257 */
 }
 
@@ -687,7 +698,20 @@ int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
 #ifdef _OPENMP
     if (cfg->nthreads > 0) omp_set_num_threads(cfg->nthreads);
 #endif
-    set_evp_parameters(&K, cfg->dt_init, cfg->ndte);
+    {
+        /* global_minval over the physical T cells with tmask (ice_global_reductions), :220-223 */
+        double xmin = 1.0e300;
+        const int gx = d->nx + 2;
+        for (int j = 1; j <= d->ny; ++j)
+            for (int i = 1; i <= d->nx; ++i) {
+                const size_t q = (size_t)j * gx + i;
+                if (g->tmask[q]) {
+                    if (g->dxt[q] < xmin) xmin = g->dxt[q];
+                    if (g->dyt[q] < xmin) xmin = g->dyt[q];
+                }
+            }
+        set_evp_parameters(&K, cfg->dt_init, cfg->ndte, cfg->revised_evp, xmin);
+    }
 
     /* ---- scatter to blocks ---- */
     double **dxt = split_r8(d, g->dxt), **dyt = split_r8(d, g->dyt);

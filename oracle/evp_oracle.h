@@ -58,6 +58,8 @@ typedef struct {
     double cosw, sinw;        /* ocean turning angle                              */
     double rhow, rhoi, rhos, gravit;
     double a_min, m_min;      /* ice_dyn_shared.F90:60-61                         */
+    int revised_evp;          /* Bouillon et al. 2013 (ice_dyn_shared.F90:230-233): revp = 1,
+                                 arlx1i / brlx from xmin, stresses zeroed every call (:492-504) */
 } evp_oracle_cfg;
 
 /* grid arrays, ghosts valid as the reference's init_grid2 leaves them */

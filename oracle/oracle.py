@@ -24,7 +24,8 @@ class Cfg(C.Structure):
                                        "ns_tripole", "grid_tripole", "tilt_mode",
                                        "strength_masked", "nthreads")] + \
                [(n, C.c_double) for n in ("dt_init", "cosw", "sinw", "rhow", "rhoi", "rhos",
-                                          "gravit", "a_min", "m_min")]
+                                          "gravit", "a_min", "m_min")] + \
+               [("revised_evp", C.c_int)]
 
 
 _GRID_R8 = ("dxt", "dyt", "dxhy", "dyhx", "cxp", "cyp", "cxm", "cym", "tarea", "uarea",
@@ -86,14 +87,14 @@ def _ip(a):
 
 
 def make_cfg(dom, ndte, dt_init, nslabs=1, nthreads=0, cosw=1.0, sinw=0.0, tilt_mode=0,
-             strength_masked=0) -> Cfg:
+             strength_masked=0, revised_evp=False) -> Cfg:
     from cice5_b200 import fixtures as fx
     return Cfg(nx_global=dom.nx, ny_global=dom.ny, nslabs=nslabs, ndte=ndte,
                ew_cyclic=int(dom.ew_cyclic), ns_tripole=int(dom.ns_tripole),
                grid_tripole=int(dom.grid_tripole), tilt_mode=tilt_mode,
                strength_masked=strength_masked, nthreads=nthreads, dt_init=dt_init,
                cosw=cosw, sinw=sinw, rhow=fx.RHOW, rhoi=fx.RHOI, rhos=fx.RHOS,
-               gravit=fx.GRAVIT, a_min=1.0e-3, m_min=1.0e-2)
+               gravit=fx.GRAVIT, a_min=1.0e-3, m_min=1.0e-2, revised_evp=int(revised_evp))
 
 
 def run_case(case, nslabs=1, nthreads=0, dt_init=None, **cfg_kw):

@@ -138,3 +138,40 @@ def test_umax_sanity():
     """check_umax (ice_diagnostics.F90:340-364): |u| stays below umax_stab = 1 m/s."""
     c = _run(fx.make_case("gx3", "full", ndte=120))
     assert np.hypot(c.io["uvel"], c.io["vvel"]).max() < 1.0
+
+
+# ---- revised EVP (SURVEY.md 8f row 3; ice_dyn_shared.F90:225-233,492-504,715,732-734) ----------
+
+@pytest.mark.parametrize("grid", ["gx3", "tp"])
+def test_revised_evp_c_oracle_equals_numpy_and_is_slab_independent(grid):
+    g = fx.synthetic_tripole(62, 40) if grid == "tp" else fx.make_grid(grid)
+    case = fx.make_case(g, "full", ndte=15, dt=3600.0)
+    a = _run(case, revised_evp=True)
+    b = clone_case(case)
+    evp_numpy.evp(b, revised_evp=True)
+    compare_cases(b, a, bitwise=True)
+    compare_cases(_run(case, revised_evp=True, nslabs=2), a, bitwise=True)
+    classic = _run(case)
+    assert not np.array_equal(phys(a.io["uvel"]), phys(classic.io["uvel"]))      # really another scheme
+
+
+def test_revised_evp_parameters_and_stress_reset():
+    """revp = 1, 1/alpha = 2 xi / Se, beta = 2 Se xi gamma / xmin^2 with xmin over tmask cells; the 12
+    stresses restart from zero on every call (evp_prep2 :492-504), so a second call with the same
+    forcing does not depend on the stresses the first one left."""
+    g = fx.make_grid("gx3")
+    tm = g.f["tmask"][1:-1, 1:-1] > 0
+    xmin = min(g.f["dxt"][1:-1, 1:-1][tm].min(), g.f["dyt"][1:-1, 1:-1][tm].min())
+    ecci, arlx1i, brlx, denom1 = evp_numpy.evp_parameters(3600.0, 120, True, xmin)
+    assert arlx1i == 2.0 * 5.5e-3 / 0.86 and denom1 == 1.0 / (1.0 + arlx1i)
+    assert brlx == 2.0 * 0.86 * 5.5e-3 * (0.25 * 1.0e11 * 3600.0) / (xmin * xmin)
+    case = fx.make_case(g, "full", ndte=20)
+    a = _run(case, revised_evp=True)
+    b = clone_case(a)
+    for n in fx.STRESS_FIELDS:
+        b.io[n] = np.random.default_rng(1).normal(size=b.io[n].shape) * 1.0e3     # garbage stresses in
+    b.out = fx.zeroed_outputs(case.dom)
+    a.out = fx.zeroed_outputs(case.dom)
+    orc.run_case(a, revised_evp=True)
+    orc.run_case(b, revised_evp=True)
+    compare_cases(b, a, bitwise=True)
