@@ -17,6 +17,7 @@
 #include "evp_kernels.cuh"
 #include "evp_prep.cuh"
 #include "evp_subcycle_tma.cuh"
+#include "evp_strength.cuh"
 
 using namespace evp;
 
@@ -105,6 +106,11 @@ struct evp_handle {
     bool use_tma = false;         // subcycle kernel v2 (TMA ring) instead of v1 (register sweep)
     int sm_count = 148;
     CUtensorMap mapS, mapS2, mapT1, mapT3, mapT4, mapT10, mapU, mapU8, mapM;
+    // device ice_strength (evp_gpu_upload_itd): aice0, aicen(ncat), vicen(ncat) planes of the arena's
+    // pitch in their own allocation; strength_from_itd = the last upload had in->strength == NULL
+    double *itd = nullptr;
+    evp_itd_t itd_cfg;
+    bool itd_ready = false, strength_from_itd = false;
     bool have_ht = false;         // HTE / HTN were given: compact metric rows are possible
     evp_stats_t stats;
     unsigned long long h_counts[2];
@@ -402,6 +408,7 @@ int evp_gpu_finalize(evp_handle_t *h)
         if (h->peer_opened[r]) cudaIpcCloseMemHandle(h->peer_arena[r]);
     for (auto &ev : h->ev) if (ev) cudaEventDestroy(ev);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    if (h->itd) cudaFree(h->itd);
     if (h->arena) cudaFree(h->arena);
     delete h;
     return EVP_OK;
@@ -508,7 +515,12 @@ int evp_gpu_upload(evp_handle_t *h, const evp_in_t *in, const evp_inout_t *io)
                              in->uocn, in->vocn, in->ss_tltx, in->ss_tlty, in->Cdn_ocn, in->strength};
     const int dstp[12] = {I_AICE, I_VICE, I_VSNO, I_AICE_INIT, I_STRAIRXT, I_STRAIRYT,
                           I_UOCN, I_VOCN, I_SSTLTX, I_SSTLTY, I_CW, I_STRENGTH};
-    for (int p = 0; p < 12; ++p) TRY(h2d(h, dstp[p], src[p]));
+    if (!in->strength && !h->itd_ready) return EVP_ERR_ARG;      // neither the host's strength nor an ITD
+    h->strength_from_itd = in->strength == nullptr;
+    for (int p = 0; p < 12; ++p) {
+        if (dstp[p] == I_STRENGTH && h->strength_from_itd) continue;      // computed on the device
+        TRY(h2d(h, dstp[p], src[p]));
+    }
     // dynamic state always lands in copy A
     TRY(h2d(h, S_UA, io->uvel));
     TRY(h2d(h, S_VA, io->vvel));
@@ -520,6 +532,33 @@ int evp_gpu_upload(evp_handle_t *h, const evp_in_t *in, const evp_inout_t *io)
     TRY(h2d_i(h, 2, io->iceumask));
     h->parity = 0;
     h->uploaded = true;
+    return EVP_OK;
+}
+
+int evp_gpu_upload_itd(evp_handle_t *h, const evp_itd_t *itd)
+{
+    if (!h || !itd || !itd->aicen || !itd->vicen || !itd->aice0) return EVP_ERR_ARG;
+    if (itd->ncat < 1 || itd->ncat > 16) return EVP_ERR_UNSUPPORTED;
+    if (itd->kstrength < 0 || itd->kstrength > 1 || itd->krdg_partic < 0 || itd->krdg_partic > 1 ||
+        itd->krdg_redist < 0 || itd->krdg_redist > 1)
+        return EVP_ERR_UNSUPPORTED;
+    CK(cudaSetDevice(h->cfg.device));
+    const size_t nplanes = 2 * (size_t)itd->ncat + 1;
+    if (!h->itd || h->itd_cfg.ncat != itd->ncat) {
+        if (h->itd) { CK(cudaFree(h->itd)); h->itd = nullptr; }
+        CK(cudaMalloc(&h->itd, nplanes * h->plane_elems * sizeof(double)));
+    }
+    h->itd_cfg = *itd;
+    const size_t hostplane = (size_t)h->nxb * h->nyb;
+    for (size_t p = 0; p < nplanes; ++p) {      // [0] aice0, [1 .. ncat] aicen, [ncat+1 .. 2 ncat] vicen
+        const double *src = p == 0 ? itd->aice0
+                          : p <= (size_t)itd->ncat ? itd->aicen + (p - 1) * hostplane
+                                                   : itd->vicen + (p - 1 - itd->ncat) * hostplane;
+        CK(cudaMemcpy2DAsync(h->itd + p * h->plane_elems, (size_t)h->ld * sizeof(double), src,
+                             (size_t)h->nxb * sizeof(double), (size_t)h->nxb * sizeof(double), h->nyb,
+                             cudaMemcpyHostToDevice, h->stream));
+    }
+    h->itd_ready = true;
     return EVP_OK;
 }
 
@@ -830,10 +869,27 @@ void build_program(evp_handle *h, double dt, Program &P)
             to_ugrid4_kernel<<<grid2d(h), 128, 0, s>>>(a);
             ++L.n;
         }
+        if (h->strength_from_itd) {     // ice_strength on the device (:291-301), into the input plane
+            const evp_itd_t &it = h->itd_cfg;
+            StrengthArgs sa;
+            sa.nxb = h->nxb; sa.nyb = h->nyb; sa.ld = h->ld;
+            sa.ncat = it.ncat; sa.kstrength = it.kstrength; sa.krdg_partic = it.krdg_partic;
+            sa.krdg_redist = it.krdg_redist; sa.mu_rdg = it.mu_rdg; sa.Cf = it.Cf;
+            sa.Cp = 0.5 * cfg.gravit * (cfg.rhow - cfg.rhoi) * cfg.rhoi / cfg.rhow;
+            sa.cat_stride = h->plane_elems;
+            sa.aice = h->plane(I_AICE); sa.vice = h->plane(I_VICE);
+            sa.aice0 = h->itd; sa.aicen = h->itd + h->plane_elems;
+            sa.vicen = h->itd + (1 + (size_t)it.ncat) * h->plane_elems;
+            sa.strength = h->plane(I_STRENGTH);
+            ice_strength_kernel<<<grid2d(h), 128, 0, s>>>(sa);
+            ++L.n;
+        }
         {   // evp_prep2 + ice_strength masking (:260-301)
             Prep2Args a;
             a.g = h->g; a.dt = dt; a.a_min = cfg.a_min; a.m_min = cfg.m_min; a.cosw = cfg.cosw; a.sinw = cfg.sinw;
             a.gravit = cfg.gravit; a.tilt_mode = cfg.tilt_mode; a.strength_masked = cfg.strength_masked;
+            // Rothrock strength from the device: list semantics (0 outside icetmask == 1, ice_mechred.F90:2175)
+            if (h->strength_from_itd && h->itd_cfg.kstrength == 1) a.strength_masked = 1;
             a.aiu = h->plane(W_AIU); a.umass = h->plane(W_UMASS); a.fcor = h->plane(G_FCOR);
             a.uocn = h->plane(I_UOCN); a.vocn = h->plane(I_VOCN); a.strairx = h->plane(O_STRAIRX);
             a.strairy = h->plane(O_STRAIRY); a.ss_tltx = h->plane(I_SSTLTX); a.ss_tlty = h->plane(I_SSTLTY);

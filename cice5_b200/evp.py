@@ -45,6 +45,11 @@ class GridS(C.Structure):
     _fields_ = [(n, _DP) for n in GRID_R8] + [("tmask", _IP), ("umask", _IP), ("HTE", _DP), ("HTN", _DP)]
 
 
+class ItdS(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("ncat", "kstrength", "krdg_partic", "krdg_redist")] + \
+               [("mu_rdg", C.c_double), ("Cf", C.c_double), ("aicen", _DP), ("vicen", _DP), ("aice0", _DP)]
+
+
 class InS(C.Structure):
     _fields_ = [(n, _DP) for n in IN_R8]
 
@@ -68,7 +73,7 @@ class Stats(C.Structure):
 EXPORTS = ("evp_gpu_init", "evp_gpu_set_grid", "evp_gpu_run", "evp_gpu_upload", "evp_gpu_compute",
            "evp_gpu_download", "evp_gpu_compute_group", "evp_gpu_get_stats", "evp_gpu_synchronize", "evp_gpu_peer_blob_size",
            "evp_gpu_get_peer_blob", "evp_gpu_set_peers", "evp_gpu_finalize", "evp_gpu_strerror",
-           "evp_gpu_last_cuda_error", "evp_gpu_device_count", "evp_gpu_get_trace")
+           "evp_gpu_last_cuda_error", "evp_gpu_device_count", "evp_gpu_get_trace", "evp_gpu_upload_itd")
 
 _libs: dict = {}
 
@@ -178,7 +183,7 @@ class EvpGpu:
         s = InS()
         for n in IN_R8:
             key = "Cw" if n == "Cdn_ocn" and "Cdn_ocn" not in inp else n
-            setattr(s, n, _dp(inp[key]))
+            setattr(s, n, _dp(inp.get(key)) if n == "strength" else _dp(inp[key]))   # strength: optional
         return s
 
     @staticmethod
@@ -207,6 +212,21 @@ class EvpGpu:
         """``call evp(dt)``: host arrays in, host arrays out (H2D + device solve + D2H)."""
         i, s, o = self._in_struct(inp), self._io_struct(io), self._out_struct(out)
         self._check(self.lib.evp_gpu_run(self._h, C.c_double(dt), C.byref(i), C.byref(s), C.byref(o)))
+
+    def upload_itd(self, aicen, vicen, aice0, kstrength=1, krdg_partic=1, krdg_redist=1, mu_rdg=3.0,
+                   Cf=17.0):
+        """Thickness distribution for the device ice_strength (source/ice_mechred.F90:2111-2269; the
+        call evp makes at source/ice_dyn_evp.F90:291-301).  aicen / vicen: (ncat, ny_block, nx_block).
+        Afterwards `strength` may be missing (None) from the per-call inputs."""
+        aicen = np.ascontiguousarray(aicen)
+        vicen = np.ascontiguousarray(vicen)
+        if aicen.shape != vicen.shape or aicen.shape[1:] != self.shape or aice0.shape != self.shape:
+            raise EvpError(f"ITD arrays must be (ncat, {self.shape[0]}, {self.shape[1]})")
+        s = ItdS(ncat=aicen.shape[0], kstrength=kstrength, krdg_partic=krdg_partic,
+                 krdg_redist=krdg_redist, mu_rdg=mu_rdg, Cf=Cf, aicen=_dp(aicen), vicen=_dp(vicen),
+                 aice0=_dp(aice0))
+        self._check(self.lib.evp_gpu_upload_itd(self._h, C.byref(s)))
+        self._keep = [aicen, vicen, aice0]           # copies are asynchronous on the handle's stream
 
     def upload(self, inp, io):
         i, s = self._in_struct(inp), self._io_struct(io)

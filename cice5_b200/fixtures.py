@@ -374,6 +374,22 @@ def ice_state(grid: Grid, scenario: str = "full") -> dict:
     return s
 
 
+ITD_WEIGHTS = (0.1, 0.2, 0.3, 0.25, 0.15)          # 5-category split of aice
+ITD_THICKNESS = (0.3, 0.7, 1.0, 1.5, 2.5)          # thickness multipliers of the categories
+
+
+def ice_itd(state: dict) -> dict:
+    """5-category thickness distribution consistent with `aice`, `vice` of ice_state:
+    aicen = w_n * aice, vicen proportional to w_n * m_n and summing to vice; aice0 = 1 - aice."""
+    aice, vice = state["aice"], state["vice"]
+    w = np.array(ITD_WEIGHTS)
+    m = np.array(ITD_THICKNESS)
+    norm = float((w * m).sum())
+    aicen = np.stack([wn * aice for wn in w])
+    vicen = np.stack([(wn * mn / norm) * vice for wn, mn in zip(w, m)])
+    return {"aicen": aicen, "vicen": vicen, "aice0": 1.0 - aice}
+
+
 def forcing(grid: Grid, state: dict, step: int = 0, steps_per_cycle: int = 240) -> dict:
     """Wind stress on T cells (translating cyclone), ocean gyre on U points, zero tilt,
     constant ocean drag (SURVEY.md section 8d 'Forcing')."""

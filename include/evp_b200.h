@@ -91,6 +91,19 @@ typedef struct {
     const double *strength;     /* host ice_strength result on the block's physical T cells */
 } evp_in_t;
 
+/* Optional: the thickness distribution, so that ice_strength (source/ice_mechred.F90:2111-2269, called by
+ * evp at source/ice_dyn_evp.F90:291-301) runs on the device instead of on the host.  After
+ * evp_gpu_upload_itd, evp_in_t.strength may be NULL.  aicen / vicen: (nx_block, ny_block, ncat). */
+typedef struct {
+    int ncat;                   /* ice_domain_size.F90 ncat (<= 16)                                   */
+    int kstrength;              /* 1 Rothrock 75, 0 Hibler 79           (ice_mechred.F90:55-56)       */
+    int krdg_partic;            /* 0 Thorndike 75, 1 exponential        (:57-58)                      */
+    int krdg_redist;            /* 0 Hibler 80, 1 exponential           (:59-60)                      */
+    double mu_rdg, Cf;          /* namelist (ice_init.F90:276-277: 3, 17)                             */
+    const double *aicen, *vicen;
+    const double *aice0;        /* open-water fraction (ice_state.F90)                                */
+} evp_itd_t;
+
 /* Persistent dynamic state, read and written (ice_state.F90:143-144; ice_flux.F90:95-107). */
 typedef struct {
     double *uvel, *vvel;
@@ -116,6 +129,9 @@ typedef struct {
 
 int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **h);
 int evp_gpu_set_grid(evp_handle_t *h, const evp_grid_t *g);
+
+/* per call, before evp_gpu_run / evp_gpu_upload when evp_in_t.strength is NULL */
+int evp_gpu_upload_itd(evp_handle_t *h, const evp_itd_t *itd);
 
 /* == one call of evp(dt): upload + compute + download */
 int evp_gpu_run(evp_handle_t *h, double dt, const evp_in_t *in, evp_inout_t *io, evp_out_t *out);

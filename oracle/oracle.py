@@ -57,7 +57,8 @@ class Stats(C.Structure):
 
 def build(force: bool = False) -> str:
     if force or not os.path.exists(_SO) or \
-            os.path.getmtime(_SO) < os.path.getmtime(os.path.join(_HERE, "evp_oracle.c")):
+            os.path.getmtime(_SO) < max(os.path.getmtime(os.path.join(_HERE, f))
+                                        for f in ("evp_oracle.c", "strength_oracle.c")):
         subprocess.run(["make", "-C", _HERE] + (["-B"] if force else []), check=True,
                        stdout=subprocess.DEVNULL)
     return _SO
@@ -138,3 +139,26 @@ def principal_stress(sp1, sm1, s121, prs):
     lib().evp_oracle_principal_stress(C.c_longlong(sp1.size), _dp(sp1), _dp(sm1), _dp(s121),
                                       _dp(prs), _dp(sig1), _dp(sig2))
     return sig1, sig2
+
+
+class StrengthCfg(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("nx", "ny", "ncat", "kstrength", "krdg_partic", "krdg_redist")] + \
+               [(n, C.c_double) for n in ("mu_rdg", "Cf", "rhow", "rhoi", "gravit")]
+
+
+def ice_strength(dom, aice, vice, aice0, aicen, vicen, cellmask=None, kstrength=1, krdg_partic=1,
+                 krdg_redist=1, mu_rdg=3.0, Cf=17.0):
+    """ice_strength (source/ice_mechred.F90:2111-2269) on global-with-ghost planes; aicen / vicen
+    are (ncat, ny+2, nx+2).  cellmask (int32, non-zero = in the icellt list) or None = all cells."""
+    from cice5_b200 import fixtures as fx
+    ncat = aicen.shape[0]
+    cfg = StrengthCfg(nx=dom.nx, ny=dom.ny, ncat=ncat, kstrength=kstrength, krdg_partic=krdg_partic,
+                      krdg_redist=krdg_redist, mu_rdg=mu_rdg, Cf=Cf, rhow=fx.RHOW, rhoi=fx.RHOI,
+                      gravit=fx.GRAVIT)
+    out = np.zeros(aice.shape)
+    f = lib().strength_oracle_run
+    rc = f(C.byref(cfg), _dp(aice), _dp(vice), _dp(aice0), _dp(np.ascontiguousarray(aicen)),
+           _dp(np.ascontiguousarray(vicen)), _ip(cellmask) if cellmask is not None else None, _dp(out))
+    if rc != 0:
+        raise RuntimeError(f"strength_oracle_run failed with status {rc}")
+    return out

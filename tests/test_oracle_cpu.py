@@ -175,3 +175,62 @@ def test_revised_evp_parameters_and_stress_reset():
     orc.run_case(a, revised_evp=True)
     orc.run_case(b, revised_evp=True)
     compare_cases(b, a, bitwise=True)
+
+
+# ---- ice_strength (ice_mechred.F90:2111-2269, ridge_itd :936-1285) ---------
+
+def _itd_case(grid, scen):
+    g = fx.make_grid(grid)
+    st = fx.ice_state(g, scen)
+    return g, st, fx.ice_itd(st)
+
+
+@pytest.mark.parametrize("grid,scen", [("gx3", "full"), ("tp1", "caps")])
+@pytest.mark.parametrize("partic,redist", [(0, 0), (0, 1), (1, 0), (1, 1)])
+def test_strength_c_oracle_equals_numpy_restatement(grid, scen, partic, redist):
+    from oracle import strength_numpy as sn
+    g, st, itd = _itd_case(grid, scen)
+    a = orc.ice_strength(g.dom, st["aice"], st["vice"], itd["aice0"], itd["aicen"], itd["vicen"],
+                         krdg_partic=partic, krdg_redist=redist)
+    b = sn.ice_strength(st["aice"], st["vice"], itd["aice0"], itd["aicen"], itd["vicen"],
+                        krdg_partic=partic, krdg_redist=redist, rhow=fx.RHOW, rhoi=fx.RHOI, gravit=fx.GRAVIT)
+    assert np.isfinite(a).all() and (a >= 0).all() and a.max() > 1.0e3
+    if partic == 0:
+        assert np.array_equal(a, b)                       # no exp: the same IEEE operations
+    else:                                                 # numpy's vector exp vs libm: last-bit differences
+        assert np.max(np.abs(a - b) / np.maximum(np.abs(a), 1e-300)) < 4e-16
+
+
+def test_strength_list_semantics_hibler_and_itd_fixture():
+    g, st, itd = _itd_case("gx3", "caps")
+    assert np.allclose(itd["aicen"].sum(axis=0), st["aice"], rtol=0, atol=1e-15)
+    assert np.allclose(itd["vicen"].sum(axis=0), st["vice"], rtol=1e-14, atol=0)
+    mask = (st["aice"] > 0.5).astype(np.int32)
+    full = orc.ice_strength(g.dom, st["aice"], st["vice"], itd["aice0"], itd["aicen"], itd["vicen"])
+    lst = orc.ice_strength(g.dom, st["aice"], st["vice"], itd["aice0"], itd["aicen"], itd["vicen"],
+                           cellmask=mask)
+    assert np.array_equal(lst, np.where(mask != 0, full, 0.0))      # 0 outside the list (:2175)
+    hib = orc.ice_strength(g.dom, st["aice"], st["vice"], itd["aice0"], itd["aicen"], itd["vicen"],
+                           kstrength=0)
+    # fixtures' Hibler strength (:2263); numpy's vector exp and libm's differ in the last bit
+    assert np.allclose(phys(hib), phys(st["strength"]), rtol=4e-16, atol=0) and hib.max() > 1e4
+    assert not hib[0, :].any() and not hib[:, 0].any()               # physical cells only
+
+
+def test_strength_single_category_closed_form():
+    """One category of thickness h under 100 % cover, Thorndike participation, Hibler 80
+    redistribution: G = (0, 0, 1), apartic(1) = 1, so
+    strength = Cf Cp (-h^2 + (hmax^3 - hmin^3) / (3 (hmax - hmin)) / k) / (1 - 1/k)."""
+    g = fx.make_grid("gx3")
+    shape = g.f["tmask"].shape
+    h = 2.0
+    aicen = np.ones((1,) + shape)
+    vicen = np.full((1,) + shape, h)
+    s = orc.ice_strength(g.dom, np.ones(shape), vicen[0], np.zeros(shape), aicen, vicen,
+                         krdg_partic=0, krdg_redist=0)
+    hmin = min(2 * h, h + 1.0)
+    hmax = max(2 * np.sqrt(25.0 * h), hmin + 1e-11)
+    k = 0.5 * (hmin + hmax) / h
+    Cp = 0.5 * fx.GRAVIT * (fx.RHOW - fx.RHOI) * fx.RHOI / fx.RHOW
+    want = 17.0 * Cp * (-h * h + (hmax ** 3 - hmin ** 3) / (3 * (hmax - hmin)) / k) / (1 - 1 / k)
+    assert abs(s[5, 5] - want) <= 1e-12 * want
