@@ -137,6 +137,12 @@ def cpu_sample(args, case_fn, nthreads=0):
                       f"-ffp-contract=off; the Fortran+MPI reference cannot be built in this image"}
 
 
+def workload_name(args, dom, dt):
+    """config.workload: the same string for both arms."""
+    return (f"{args.grid} {dom.nx}x{dom.ny} tripole (AusCOM 0.1 deg shape), scenario {args.scenario}, "
+            f"ndte={args.ndte}, dt={dt}")
+
+
 def run_reference(args, rank):
     if rank != 0:
         return
@@ -155,10 +161,13 @@ def run_reference(args, rank):
     dom = grid.dom
     out = {"impl": "reference", "metric": "EVP cell-subcycles/s", "value": v, "unit": "cell-subcycles/s",
            "n_gpus": args.gpus, "steps": len(vals), "warmup": min(args.warmup, 1),
-           "ms_per_step": None, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "ms_per_step": None, "higher_is_better": True, "vs_baseline": None,
            "dtype": "f64", "data": "synthetic",
-           "config": {"workload": f"{args.grid} {dom.nx}x{dom.ny} tripole, scenario {args.scenario}, "
-                                  f"ndte=120 (CPU sample: ndte={args.cpu_ndte} per step)"},
+           "scaling": "strong",
+           "config": {"workload": workload_name(args, dom, dt),
+                      "decomposition": "one block, OpenMP over the rows (host cores)",
+                      "grid_cells": dom.nx * dom.ny,
+                      "cpu_sample": f"each step = one evp call with ndte={args.cpu_ndte} instead of {args.ndte}"},
            "cpu_baseline": {**{k: r[k] for k in ("unit", "cores", "kind", "sample")}, "value": v,
                             "loop_value": statistics.median(loops)},
            "e2e": {"value": v, "unit": "cell-subcycles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -331,8 +340,7 @@ def main():
                "n_gpus": N, "steps": args.steps, "warmup": args.warmup,
                "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
                "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-               "config": {"workload": f"{args.grid} {dom.nx}x{dom.ny} tripole (AusCOM 0.1 deg shape), "
-                                      f"scenario {args.scenario}, ndte={args.ndte}, dt={dt}",
+               "config": {"workload": workload_name(args, dom, dt),
                           "decomposition": (f"{N} x-slab(s) of {dom.nx // N} columns" if starts is None else
                                             f"{N} x-slabs balanced by ocean cells, first columns {starts}"),
                           "active_t_cells": act_phys, "grid_cells": dom.nx * dom.ny,
