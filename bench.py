@@ -139,8 +139,8 @@ def cpu_sample(args, case_fn, nthreads=0):
 
 def workload_name(args, dom, dt):
     """config.workload: the same string for both arms."""
-    return (f"{args.grid} {dom.nx}x{dom.ny} tripole (AusCOM 0.1 deg shape), scenario {args.scenario}, "
-            f"ndte={args.ndte}, dt={dt}")
+    shape = " (AusCOM 0.1 deg shape)" if args.grid == "tp01" else ""
+    return f"{args.grid} {dom.nx}x{dom.ny} tripole{shape}, scenario {args.scenario}, ndte={args.ndte}, dt={dt}"
 
 
 def run_reference(args, rank):

@@ -1117,6 +1117,22 @@ int evp_gpu_run(evp_handle_t *h, double dt, const evp_in_t *in, evp_inout_t *io,
     return EVP_OK;
 }
 
+int evp_gpu_principal_stress(evp_handle_t *h, double *sig1, double *sig2)
+{
+    if (!h || !sig1 || !sig2) return EVP_ERR_ARG;
+    if (!h->uploaded) return EVP_ERR_STATE;
+    CK(cudaSetDevice(h->cfg.device));
+    const int S = h->parity ? S_STRB : S_STRA;          // the copy that holds the current stresses
+    principal_stress_kernel<<<grid2d(h), 128, 0, h->stream>>>(h->nxb, h->nyb, h->ld, h->plane(S), h->plane(S + 4),
+                                                            h->plane(S + 8), h->plane(O_PRSSIG), h->plane(W_1),
+                                                            h->plane(W_2));
+    CK(cudaGetLastError());
+    TRY(d2h(h, W_1, sig1));
+    TRY(d2h(h, W_2, sig2));
+    CK(cudaStreamSynchronize(h->stream));
+    return EVP_OK;
+}
+
 int evp_gpu_get_trace(evp_handle_t *h, unsigned long long *buf, int n)
 {
     if (!h || !buf) return EVP_ERR_ARG;

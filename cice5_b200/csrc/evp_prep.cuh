@@ -359,4 +359,24 @@ __global__ void double_to_int_kernel(const double *in, int *out, size_t n)
     if (q < n) out[q] = (int)in[q];
 }
 
+// ---- principal_stress (diagnostic for history; source/ice_dyn_shared.F90:853-893) -------------
+// sig1, sig2 = (stressp_1 +- sqrt(stressm_1^2 + 4 stress12_1^2)) / 2 / prs_sig over the whole block,
+// spval_dbl (1e30) where prs_sig <= puny.
+__global__ void principal_stress_kernel(int nxb, int nyb, int ld, const double *stressp_1, const double *stressm_1,
+                                        const double *stress12_1, const double *prs_sig, double *sig1, double *sig2)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+    if (c >= nxb || r >= nyb) return;
+    const size_t q = (size_t)r * ld + c;
+    const double p = prs_sig[q];
+    double s1 = 1.0e30, s2 = 1.0e30;
+    if (p > 1.0e-11) {
+        const double root = sqrt(stressm_1[q] * stressm_1[q] + 4.0 * (stress12_1[q] * stress12_1[q]));
+        s1 = (0.5 * (stressp_1[q] + root)) / p;
+        s2 = (0.5 * (stressp_1[q] - root)) / p;
+    }
+    sig1[q] = s1;
+    sig2[q] = s2;
+}
+
 }  // namespace evp

@@ -73,7 +73,8 @@ class Stats(C.Structure):
 EXPORTS = ("evp_gpu_init", "evp_gpu_set_grid", "evp_gpu_run", "evp_gpu_upload", "evp_gpu_compute",
            "evp_gpu_download", "evp_gpu_compute_group", "evp_gpu_get_stats", "evp_gpu_synchronize", "evp_gpu_peer_blob_size",
            "evp_gpu_get_peer_blob", "evp_gpu_set_peers", "evp_gpu_finalize", "evp_gpu_strerror",
-           "evp_gpu_last_cuda_error", "evp_gpu_device_count", "evp_gpu_get_trace", "evp_gpu_upload_itd")
+           "evp_gpu_last_cuda_error", "evp_gpu_device_count", "evp_gpu_get_trace", "evp_gpu_upload_itd",
+           "evp_gpu_principal_stress")
 
 _libs: dict = {}
 
@@ -243,6 +244,12 @@ class EvpGpu:
         st = Stats()
         self._check(self.lib.evp_gpu_get_stats(self._h, C.byref(st)))
         return st
+
+    def principal_stress(self):
+        """sig1, sig2 (principal_stress, source/ice_dyn_shared.F90:853-893) of the resident state."""
+        s1, s2 = np.empty(self.shape), np.empty(self.shape)
+        self._check(self.lib.evp_gpu_principal_stress(self._h, _dp(s1), _dp(s2)))
+        return s1, s2
 
     def trace(self):
         """(ndte, 8) uint64 device timestamps of the last compute (needs EVP_B200_TRACE=1)."""

@@ -150,6 +150,11 @@ int evp_gpu_synchronize(evp_handle_t *h);
 
 /* Multi-GPU (one task per GPU): every task exports a blob, the host gathers the blobs of all
  * tasks in rank order (MPI_Allgather in the shim) and hands them back. */
+/* principal_stress (source/ice_dyn_shared.F90:853-893; called by the history writer,
+ * source/ice_history.F90:1921) from the device-resident stressp_1, stressm_1, stress12_1, prs_sig of
+ * the last evp: sig1, sig2 over the whole block, spval_dbl = 1e30 where prs_sig <= puny. */
+int evp_gpu_principal_stress(evp_handle_t *h, double *sig1, double *sig2);
+
 /* Diagnostics (library started with EVP_B200_TRACE=1): per subcycle 8 x u64 device timestamps in
  * ns: [0] subcycle kernel start, [1] its last CTA done, [2] peers signalled, [3] fold wait begin,
  * [4] fold wait end.  No reference counterpart (the reference's timers are ice_timers.F90). */

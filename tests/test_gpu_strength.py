@@ -57,3 +57,23 @@ def test_strength_default_modes_within_ulps(grid, scenario):
     assert (b > 0).any() and np.array_equal(a == 0, b == 0)
     assert np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300)) <= 1.0e-15 * 8
     compare_cases(got, ref, fields_io=STATE, tol=REL_TOL)
+
+
+def test_principal_stress_from_resident_state_bitwise():
+    """sig1 / sig2 (ice_dyn_shared.F90:853-893) from the device-resident stresses and prs_sig of
+    the last evp call == the oracle's principal_stress on the downloaded fields, bit for bit."""
+    from oracle import oracle as orc
+    g = fx.make_grid("gx3")
+    case = fx.make_case(g, "full", ndte=120)
+    got = clone_case(case)
+    e = evp.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True)
+    try:
+        e.set_grid(g.f)
+        e.evp(case.dt, got.inp, got.io, got.out)
+        s1, s2 = e.principal_stress()
+    finally:
+        e.close()
+    r1, r2 = orc.principal_stress(got.io["stressp_1"], got.io["stressm_1"], got.io["stress12_1"],
+                                  got.out["prs_sig"])
+    assert np.array_equal(s1, r1) and np.array_equal(s2, r2)
+    assert (s1 != 1.0e30).any() and (s1 == 1.0e30).any()

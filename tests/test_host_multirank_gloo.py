@@ -71,3 +71,36 @@ def test_slab_unslab_roundtrip(n):
     rng = np.random.default_rng(n)
     a = rng.standard_normal((12, 34))
     assert np.array_equal(fx.unslab([fx.slab(a, r, n) for r in range(n)]), a)
+
+
+def test_unequal_slabs_roundtrip_and_bounds():
+    rng = np.random.default_rng(7)
+    a = rng.standard_normal((9, 42))                       # nx = 40
+    starts = [0, 3, 17, 19, 33]
+    parts = [fx.slab(a, r, 5, starts) for r in range(5)]
+    assert [p.shape[1] - 2 for p in parts] == [3, 14, 2, 14, 7]
+    assert np.array_equal(fx.unslab(parts), a)
+    assert fx.slab_bounds(40, 4) == [0, 10, 20, 30, 40]
+
+
+@pytest.mark.parametrize("nranks", [2, 4, 8])
+def test_balanced_slab_starts_minimise_the_heaviest_rank(nranks):
+    """Strip-aligned partition (fixtures.balanced_slab_starts): boundaries on multiples of the strip
+    width, every rank non-empty, and the maximum work not worse than equal slabs of whole strips."""
+    g = fx.make_grid("tp1")
+    ocean = g.f["tmask"][1:-1, 1:-1] > 0
+    strip = 31
+    starts = fx.balanced_slab_starts(ocean, nranks, strip=strip)
+    b = starts + [g.dom.nx]
+    assert starts[0] == 0 and all(x % strip == 0 for x in starts) and all(np.diff(b) >= 2)
+
+    def work(lo, hi):
+        return sum(ocean[:, k:min(k + strip, hi)].any(axis=1).sum() for k in range(lo, hi, strip))
+    heaviest = max(work(b[r], b[r + 1]) for r in range(nranks))
+    nstrips = -(-g.dom.nx // strip)
+    per = -(-nstrips // nranks)
+    eq = [min(r * per * strip, g.dom.nx) for r in range(nranks)] + [g.dom.nx]
+    assert heaviest <= max(work(eq[r], eq[r + 1]) for r in range(nranks) if eq[r] < eq[r + 1])
+    # narrow grid: falls back to cutting the cumulative ocean-cell count
+    s2 = fx.balanced_slab_starts(ocean[:, :40], 8, strip=124)
+    assert len(s2) == 8 and s2[0] == 0 and all(np.diff(s2 + [40]) >= 2)
