@@ -195,9 +195,8 @@ def main():
     dist = None
     if world > 1:
         # stdout carries exactly one JSON line: NCCL's own banner ("NCCL version ...", printed to
-        # stdout when the box exports NCCL_DEBUG=VERSION) goes to stderr instead
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO"):
-            os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        # stdout whenever the box exports NCCL_DEBUG) goes to stderr instead
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         import torch.distributed as dist_
         dist = dist_
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
