@@ -79,3 +79,15 @@ def test_product_path_never_imports_oracle():
         src = open(sys.modules[mod].__file__ if mod in sys.modules else
                    os.path.join(ROOT, *mod.split(".")) + ".py").read()
         assert "import oracle" not in src and "from oracle" not in src
+
+
+def test_header_is_plain_c():
+    """The boundary is a C ABI (bound from Fortran iso_c_binding): the header must compile as C99."""
+    import shutil
+    import subprocess
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if cc is None:
+        pytest.skip("no C compiler")
+    r = subprocess.run([cc, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c",
+                        os.path.join(ROOT, "include", "evp_b200.h")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
