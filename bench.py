@@ -7,7 +7,7 @@ One "step" = one call of evp(dt): prep kernels, the ndte-subcycle loop, finish k
             HOST buffers in, host buffers out, H2D + D2H inside the timed region
   roofline  the fused subcycle kernel against the measured HBM copy bandwidth, 392 algorithmic
             bytes per active cell-subcycle (SURVEY.md section 8d / DESIGN.md)
-  cpu_baseline  the CPU restatement (oracle/, `kind: port`) on the host cores, bounded sample
+  cpu_baseline  the CPU restatement (oracle/, `kind: port`) on the host cores, one whole evp call
 `--impl reference` times that CPU restatement alone (the reference is Fortran + MPI and cannot be
 built in this image; DESIGN.md "Oracle").
 Launch: `python bench.py` (N = 1) or `python -m torch.distributed.run --nproc-per-node N bench.py
@@ -54,7 +54,8 @@ def parse():
                     help="do not pass HTE/HTN: fetch all 8 metric planes + tinyarea every subcycle")
     ap.add_argument("--equal-slabs", action="store_true",
                     help="N > 1: nx/N columns per GPU instead of slabs balanced by ocean cells")
-    ap.add_argument("--cpu-ndte", type=int, default=24, help="subcycles of the CPU sample")
+    ap.add_argument("--cpu-ndte", type=int, default=120,
+                    help="subcycles of the CPU sample (120 = one whole evp call, about 25 s on 16 cores)")
     return ap.parse_args()
 
 
