@@ -168,7 +168,8 @@ def run_reference(args, rank):
            "config": {"workload": workload_name(args, dom, dt),
                       "decomposition": "one block, OpenMP over the rows (host cores)",
                       "grid_cells": dom.nx * dom.ny,
-                      "cpu_sample": f"each step = one evp call with ndte={args.cpu_ndte} instead of {args.ndte}"},
+                      "cpu_sample": ("each step = one whole evp call" if args.cpu_ndte == args.ndte else
+                                     f"each step = one evp call with ndte={args.cpu_ndte} instead of {args.ndte}")},
            "cpu_baseline": {**{k: r[k] for k in ("unit", "cores", "kind", "sample")}, "value": v,
                             "loop_value": statistics.median(loops)},
            "e2e": {"value": v, "unit": "cell-subcycles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
