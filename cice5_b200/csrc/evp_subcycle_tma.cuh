@@ -49,6 +49,15 @@ constexpr int kSortThreads = 64;
 constexpr int kItemBoundary = 0x40000000;    // tag of a work item that stores into peer memory
 // stage word bits written by the producer
 constexpr unsigned kMetaState = 1u, kMetaCompact = 2u, kMetaTinyFromMetrics = 4u, kMetaHtnExtra = 8u, kMetaT = 16u;
+// EVP_TMA_MERGE_UV = 1 (experiment for round 2, NOT yet run on hardware, off by default): an item
+// has no separate first stage for the velocities of row r0-1; they ride in the U-coefficient slots
+// of the stage of row r0 (unused there: stepu starts at row r0+1), HTN of row r0-1 in slot 11.
+// Saves one ring turn-around (one exposed DRAM latency with 2 stages) per item.
+#ifndef EVP_TMA_MERGE_UV
+#define EVP_TMA_MERGE_UV 0
+#endif
+constexpr bool kMergeUv = EVP_TMA_MERGE_UV != 0;
+constexpr unsigned kMetaUvBelow = 32u, kMetaHtnBelow = 64u;
 constexpr int kMaskBoxW = 128 + 16;          // per mask box; kTmaBoxW / 128 boxes per row
 constexpr int kMaskBoxes = kTmaBoxW / 128;
 constexpr int kMaskFlagOff = 256 * (kMaskBoxes - 1) + kMaskBoxW + 48;     // stage word after the mask bytes (16-byte aligned)     // the byte mask is fetched from a 16-byte aligned column (TMA
@@ -211,7 +220,7 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                 const int r0 = 1 + chunk * a.rows_per_chunk;
                 const int rend = min(r0 + a.rows_per_chunk, a.ny + 1);
                 const unsigned char *fl = p.tile_flags + (size_t)strip * p.flags_ld;
-                for (int j = r0 - 1; j <= rend; ++j) {
+                for (int j = kMergeUv ? r0 : r0 - 1; j <= rend; ++j) {
                     // what this row segment needs: T data if it has an active T cell; U data of the
                     // row below if that row has an active U cell; the state (u, v, stresses) if this
                     // row or the next one has an active T cell or this row an active U cell.  The top
@@ -225,13 +234,18 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     // the next row, if compact, recomputes its metrics from HTN of this row too
                     const bool nextT = j + 1 <= rend && ((f1 & 1u) || j + 1 >= a.ny - 2) && (f1 & 4u);
                     const bool htn_extra = nextT && !(needT && cmp);
+                    // merged first stage: velocities (and HTN) of row r0-1 under the old rule for that row
+                    const bool first = kMergeUv && j == r0;
+                    const bool uv_below = first && ((((fm1 | f0) & 1u) || (fm1 & 2u)) || j - 1 >= a.ny - 2);
+                    const bool htn_below = first && needT && cmp;
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
                     unsigned char *sb = ring + (size_t)stage * kStageBytes;
                     unsigned char *tb = sb + kStateDepth * kTmaBoxW * 8;
                     unsigned char *mk = sb + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8;
                     *reinterpret_cast<volatile unsigned *>(mk + kMaskFlagOff) =
                         (needS ? kMetaState : 0u) | (cmp ? kMetaCompact : 0u) | (tinym ? kMetaTinyFromMetrics : 0u) |
-                        (htn_extra ? kMetaHtnExtra : 0u) | (needT ? kMetaT : 0u);
+                        (htn_extra ? kMetaHtnExtra : 0u) | (needT ? kMetaT : 0u) | (uv_below ? kMetaUvBelow : 0u) |
+                        (htn_below ? kMetaHtnBelow : 0u);
                     *reinterpret_cast<volatile int *>(mk + kMaskFlagOff + 4) = item_tag;
                     const int tdepth = cmp ? (tinym ? 3 : 4) : 10;
                     unsigned bytes = kMaskBoxW * kMaskBoxes;
@@ -239,6 +253,8 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     if (needS) bytes += (uv_only ? 2 : kStateDepth) * kTmaBoxW * 8;
                     if (needT) bytes += (tdepth + (LAST ? 1 : 0)) * kTmaBoxW * 8;
                     if (htn_extra) bytes += kTmaBoxW * 8;
+                    if (uv_below) bytes += 2 * kTmaBoxW * 8;
+                    if (htn_below) bytes += kTmaBoxW * 8;
                     if (needU) bytes += (p.water_is_ocn ? kUDepth - 2 : kUDepth) * kTmaBoxW * 8;
                     mbar_expect_tx(&full_bar[stage], bytes);
 #pragma unroll
@@ -257,6 +273,11 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     if (needU)
                         tma_load_3d(sb + (kStateDepth + kTDepth) * kTmaBoxW * 8, &mapU, &full_bar[stage], x0, j - 1,
                                     p.plane_u);
+                    if (uv_below)       // needU is false on the first row of an item: the U slots are free
+                        tma_load_3d(sb + (kStateDepth + kTDepth) * kTmaBoxW * 8, &mapS2, &full_bar[stage], x0, j - 1,
+                                    p.plane_state);
+                    if (htn_below)      // htn_extra is false here (needT && cmp): slot 11 is free
+                        tma_load_3d(tb + kSlotHtnExtra * kTmaBoxW * 8, &mapT1, &full_bar[stage], x0, j - 1, p.plane_t + 1);
                     if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
                 }
             }
@@ -305,12 +326,21 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             const double *st = reinterpret_cast<const double *>(ring + (size_t)stage * kStageBytes);
             const unsigned meta = *reinterpret_cast<const unsigned *>(
                 ring + (size_t)stage * kStageBytes + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8 + kMaskFlagOff);
-            loaded_s = (meta & kMetaState) != 0u;
-            if (meta & kMetaHtnExtra) htn_s = st[(kStateDepth + kSlotHtnExtra) * kTmaBoxW + bi];
-            u_s = st[bi]; v_s = st[kTmaBoxW + bi]; uw_s = st[bi - 1]; vw_s = st[kTmaBoxW + bi - 1];
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&empty_bar[stage]);
-            if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
+            if (!kMergeUv) {
+                loaded_s = (meta & kMetaState) != 0u;
+                if (meta & kMetaHtnExtra) htn_s = st[(kStateDepth + kSlotHtnExtra) * kTmaBoxW + bi];
+                u_s = st[bi]; v_s = st[kTmaBoxW + bi]; uw_s = st[bi - 1]; vw_s = st[kTmaBoxW + bi - 1];
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty_bar[stage]);
+                if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
+            } else {
+                // this stage is row r0 itself: take the row-below values out of the U slots / slot 11
+                // and keep the stage (the row loop waits on the same, completed, phase again)
+                const double *ub = st + (kStateDepth + kTDepth) * kTmaBoxW;
+                loaded_s = (meta & kMetaUvBelow) != 0u;
+                if (meta & kMetaHtnBelow) htn_s = st[(kStateDepth + kSlotHtnExtra) * kTmaBoxW + bi];
+                u_s = ub[bi]; v_s = ub[kTmaBoxW + bi]; uw_s = ub[bi - 1]; vw_s = ub[kTmaBoxW + bi - 1];
+            }
         }
         double s1p = 0.0, s5p = 0.0, n2p = 0.0, n7p = 0.0;
         unsigned mprev = 0;
