@@ -14,6 +14,7 @@
 // T coefficients + activity mask of row j, U coefficients of row j-1.
 #pragma once
 #include <cuda.h>
+#include <cstdio>
 
 #include "evp_kernels.cuh"
 
@@ -57,6 +58,12 @@ constexpr unsigned kMetaState = 1u, kMetaCompact = 2u, kMetaTinyFromMetrics = 4u
 #define EVP_TMA_MERGE_UV 0
 #endif
 constexpr bool kMergeUv = EVP_TMA_MERGE_UV != 0;
+// EVP_TMA_ITEMTRACE = 1 (diagnosis builds only): every 16th CTA of the LAST-subcycle launch prints one
+// line per work item -- "ITEM cta item rows t_start t_end" in globaltimer ns relative to the CTA's
+// start -- so that the per-CTA timeline of a launch can be reconstructed (who waits for what at N = 8).
+#ifndef EVP_TMA_ITEMTRACE
+#define EVP_TMA_ITEMTRACE 0
+#endif
 constexpr unsigned kMetaUvBelow = 32u, kMetaHtnBelow = 64u;
 constexpr int kMaskBoxW = 128 + 16;          // per mask box; kTmaBoxW / 128 boxes per row
 constexpr int kMaskBoxes = kTmaBoxW / 128;
@@ -290,6 +297,9 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
     const int ld = a.ld;
     const int bi = 1 + warp * kUColsPerWarp + lane;                     // my column inside the box
     bool in_bnd = false;                                                // boundary items taken, not yet counted
+#if EVP_TMA_ITEMTRACE
+    const unsigned long long t_cta = global_ns();
+#endif
     if (p.trace && blockIdx.x == 0 && threadIdx.x == 0) p.trace[0] = global_ns();
     for (;;) {
         mbar_wait(&full_bar[stage], phase);                             // first stage of the next item
@@ -317,6 +327,9 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
         const bool tcol = c <= a.nxl + 1;
         const bool ucol = lane < kUColsPerWarp && c <= a.nxl;
         const bool tstore_col = tcol && (lane < kUColsPerWarp || c == a.nxl + 1);
+#if EVP_TMA_ITEMTRACE
+        const unsigned long long t_item = global_ns();
+#endif
 
         // row r0-1: velocities only
         double u_s, v_s, uw_s, vw_s;
@@ -486,6 +499,10 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             s1p = str[0]; s5p = str[4]; n2p = e2; n7p = e7;
             u_s = u_c; v_s = v_c; uw_s = uw_c; vw_s = vw_c; mprev = m; loaded_s = loaded_c;
         }
+#if EVP_TMA_ITEMTRACE
+        if (LAST && threadIdx.x == 0 && (blockIdx.x & 15) == 0)
+            printf("ITEM %d %d %d %llu %llu\n", (int)blockIdx.x, item, rend - r0 + 1, t_item - t_cta, global_ns() - t_cta);
+#endif
     }
     if (p.fused_signal || p.trace) {
         __threadfence_system();
