@@ -58,6 +58,25 @@ def build(force: bool = False, verbose: bool = False) -> list[str]:
     return outs
 
 
+def build_variant(name: str, defines: list[str], strict: bool = True) -> str:
+    """Experiment build (kernel-tuning knobs, diagnosis options): lib/exp_<name>.so from the same
+    sources with extra -D flags; load it with EVP_B200_LIB=<path>.  Never the product library."""
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    os.makedirs(LIBDIR, exist_ok=True)
+    out = os.path.join(LIBDIR, f"exp_{name}.so")
+    extra = VARIANTS["libevp_b200_strict.so" if strict else "libevp_b200.so"]
+    cmd = [nvcc, *ARCH, "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-shared", *extra, *defines,
+           "-o", out, *[os.path.join(CSRC, s) for s in SOURCES]]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
+    return out
+
+
 if __name__ == "__main__":
     import sys
-    print("\n".join(build(force="--force" in sys.argv, verbose="-v" in sys.argv)))
+    if "--variant" in sys.argv:        # python -m cice5_b200.build --variant mergeuv -DEVP_TMA_MERGE_UV=1
+        i = sys.argv.index("--variant")
+        print(build_variant(sys.argv[i + 1], [a for a in sys.argv[i + 2:] if a.startswith("-D")]))
+    else:
+        print("\n".join(build(force="--force" in sys.argv, verbose="-v" in sys.argv)))
