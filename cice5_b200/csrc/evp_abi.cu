@@ -456,6 +456,8 @@ int evp_gpu_set_grid(evp_handle_t *h, const evp_grid_t *gr)
 {
     if (!h || !gr) return EVP_ERR_ARG;
     CK(cudaSetDevice(h->cfg.device));
+    // a captured loop holds the constants and flags derived from the grid: drop it
+    for (auto &ge : h->loop_graph) if (ge) { CK(cudaGraphExecDestroy(ge)); ge = nullptr; }
     const double *src[14] = {gr->dxt, gr->dyt, gr->dxhy, gr->dyhx, gr->cxp, gr->cyp, gr->cxm, gr->cym,
                              gr->tarea, gr->uarea, gr->tarear, gr->uarear, gr->tinyarea, gr->fcor};
     const int dstp[14] = {G_DXT, G_DYT, G_DXHY, G_DYHX, G_CXP, G_CYP, G_CXM, G_CYM,
