@@ -91,3 +91,15 @@ def test_header_is_plain_c():
     r = subprocess.run([cc, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c",
                         os.path.join(ROOT, "include", "evp_b200.h")], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
+
+
+def test_slab_start_validation_precedes_device_probe(have_gpu):
+    """Unequal x-slabs (evp_config_t.slab_start): inconsistent boundaries are argument errors, a
+    consistent set gets as far as the device probe."""
+    with pytest.raises(evp.EvpError, match="first column per rank"):
+        evp.EvpGpu(100, 116, 120, 3600.0, nranks=3, rank=0, slab_start=[0, 40])            # wrong length
+    with pytest.raises(evp.EvpError, match="unsupported"):
+        evp.EvpGpu(100, 116, 120, 3600.0, nranks=3, rank=1, slab_start=[0, 40, 41])        # 1-column slab
+    if not have_gpu:
+        with pytest.raises(evp.EvpError, match="no usable CUDA device|no CPU fallback"):
+            evp.EvpGpu(100, 116, 120, 3600.0, nranks=3, rank=2, slab_start=[0, 30, 71])    # 3 does not divide 100
