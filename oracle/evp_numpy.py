@@ -2,7 +2,7 @@
 
 Written from the Fortran (not from evp_oracle.c) to cross-check the C oracle: the two must agree
 BITWISE (numpy evaluates the same IEEE operations element-wise, no FMA contraction).  Only tests/
-may import this.  PARITY UNPINNED: see oracle/evp_oracle.h.  Citations relative to the reference:
+may import this.  Parity status: see oracle/evp_oracle.h.  Citations relative to the reference:
   source/ice_dyn_evp.F90:68-510 (evp), :520-849 (stress)
   source/ice_dyn_shared.F90:185-259, 270-365, 377-614, 623-748, 757-844
   source/ice_grid.F90:1799-1958 ; halos: cice5_b200.fixtures.halo_update (serial/ice_boundary.F90:630-896)

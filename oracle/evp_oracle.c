@@ -1,6 +1,6 @@
 /*
  * evp_oracle.c -- CPU restatement of CICE5 evp(dt).  TEST INFRASTRUCTURE ONLY; see
- * evp_oracle.h for scope, citations and the "parity unpinned" note.
+ * evp_oracle.h for scope, citations and the "parity partly pinned" note.
  *
  * Build: gcc -O2 -fopenmp -ffp-contract=off -fno-fast-math -shared -fPIC  (oracle/Makefile)
  * Evaluation order follows the Fortran statement by statement; x**2 is x*x.
@@ -67,6 +67,8 @@ typedef struct {
     int nxb, nyb;       /* block dims incl. ghosts */
     int ilo, ihi, jlo, jhi;
     int ew_cyclic, ns_tripole;
+    int no_halo;        /* unit-comparison mode: every halo update is skipped (one block, its ghost
+                           cells stay as given) -- see evp_oracle_cfg.no_halo */
 } Dom;
 
 #define IX(d, i, j) ((size_t)((j) - 1) * (size_t)(d)->nxb + (size_t)((i) - 1))
@@ -165,7 +167,9 @@ enum { KIND_SCALAR = 0, KIND_VECTOR = 1 };
 static void halo_r8(const Dom *d, double **f, int loc, int kind, double fill)
 {
     const int nx = d->nx, ny = d->ny;
-    double *G = (double *)malloc(sizeof(double) * (size_t)nx * (size_t)ny);
+    double *G;
+    if (d->no_halo) return;
+    G = (double *)malloc(sizeof(double) * (size_t)nx * (size_t)ny);
 
     /* the sends: every block's physical cells */
     for (int b = 0; b < d->nslabs; ++b)
@@ -245,7 +249,9 @@ static void halo_r8(const Dom *d, double **f, int loc, int kind, double fill)
 
 static void halo_i4(const Dom *d, int **f, int loc, int kind, int fill)
 {
-    double **t = alloc_slabs(d);
+    double **t;
+    if (d->no_halo) return;
+    t = alloc_slabs(d);
     size_t n = (size_t)d->nxb * (size_t)d->nyb;
     for (int b = 0; b < d->nslabs; ++b)
         for (size_t q = 0; q < n; ++q) t[b][q] = (double)f[b][q];
@@ -263,6 +269,7 @@ static void halo_stress(const Dom *d, double **a1, double **a2)
 {
     const int nx = d->nx, ny = d->ny;
     double *buf2;
+    if (d->no_halo) return;
     for (int b = 0; b < d->nslabs; ++b) {
         /* srcBlock == 0 entries: south row (and E/W ghosts when not cyclic) */
         for (int i = 1; i <= d->nxb; ++i) a1[b][IX(d, i, 1)] = 0.0;
@@ -693,6 +700,8 @@ int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
     d->nxb = d->nxl + 2; d->nyb = d->ny + 2;
     d->ilo = 2; d->ihi = d->nxl + 1; d->jlo = 2; d->jhi = d->ny + 1;
     d->ew_cyclic = cfg->ew_cyclic; d->ns_tripole = cfg->ns_tripole;
+    d->no_halo = cfg->no_halo;
+    if (d->no_halo && d->nslabs != 1) return 6;
     n = (size_t)d->nxb * (size_t)d->nyb;
     if (d->nxl < 2 || d->ny < 2) return 5;
 #ifdef _OPENMP
@@ -914,6 +923,7 @@ static void cfg_to_dom(const evp_oracle_cfg *cfg, Dom *d)
     d->nxb = d->nxl + 2; d->nyb = d->ny + 2;
     d->ilo = 2; d->ihi = d->nxl + 1; d->jlo = 2; d->jhi = d->ny + 1;
     d->ew_cyclic = cfg->ew_cyclic; d->ns_tripole = cfg->ns_tripole;
+    d->no_halo = 0;
 }
 
 int evp_oracle_halo_r8(const evp_oracle_cfg *cfg, double *a, int loc, int kind, double fill)

@@ -16,11 +16,19 @@
  *   serial/ice_boundary.F90:3269-3443 ice_HaloUpdate_stress
  *   mpi/ice_boundary.F90:2625-2632    ghost-ring pre-fill of the MPI build
  *
- * PARITY UNPINNED: the reference ships no tests, golden logs or fixtures for this
- * path and cannot be compiled in this image (no Fortran compiler), so this
- * restatement is pinned only by reading the source, by its own invariants
- * (decomposition independence, seam symmetry, free drift) and by an independent
- * numpy restatement (oracle/evp_numpy.py).
+ * PARITY PARTLY PINNED.  The reference ships no tests, golden logs or fixtures for this
+ * path and cannot be compiled in this image (no Fortran compiler).  What pins this file:
+ *   - ARITHMETIC (set_evp_parameters, evp_prep1, to_ugrid, evp_prep2, stress, stepu, evp_finish,
+ *     to_tgrid, principal_stress; ice_strength in strength_oracle.c): the reference's own subroutine
+ *     texts are executed mechanically from the checkout (tests/golden/fortran_exec.py, a
+ *     Fortran-subset interpreter; tests/golden/make_reference_vectors.py) and the outputs committed
+ *     as tests/golden/ref_block_vectors.npz; in `no_halo` mode this oracle must reproduce them BIT
+ *     FOR BIT (tests/test_oracle_reference_text.py: default build, -Dcoupled, AusCOM with a turning
+ *     angle, revised EVP).  An interpreter, not a compiled run: compiler-specific contraction / -ftz
+ *     choices of a real build are not represented.
+ *   - HALO / TRIPOLE code and the driver's call order: still UNPINNED -- restated by hand, defended
+ *     by invariants (decomposition independence, seam symmetry, free drift) and by an independent
+ *     numpy restatement (oracle/evp_numpy.py).
  *
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl
  * reference legs may load this code.  The product path never does.
@@ -60,6 +68,11 @@ typedef struct {
     double a_min, m_min;      /* ice_dyn_shared.F90:60-61                         */
     int revised_evp;          /* Bouillon et al. 2013 (ice_dyn_shared.F90:230-233): revp = 1,
                                  arlx1i / brlx from xmin, stresses zeroed every call (:492-504) */
+    int no_halo;              /* 1: skip every halo update (nslabs must be 1): the block sequence
+                                 prep1 -> to_ugrid -> prep2 -> ndte x (stress, stepu) -> finish -> to_tgrid
+                                 on the ghost cells as given -- the mode in which the oracle is compared
+                                 with the reference's subroutine texts executed mechanically
+                                 (tests/golden/make_reference_vectors.py)                            */
 } evp_oracle_cfg;
 
 /* grid arrays, ghosts valid as the reference's init_grid2 leaves them */

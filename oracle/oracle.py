@@ -1,8 +1,9 @@
 """ctypes wrapper around oracle/_build/libevp_oracle.so (TEST INFRASTRUCTURE ONLY).
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
-import this module (see oracle/evp_oracle.h).  PARITY UNPINNED: no reference golden vectors
-exist for this path and the Fortran reference cannot be compiled in this image.
+import this module (see oracle/evp_oracle.h).  PARITY PARTLY PINNED: the arithmetic is pinned bit for
+bit to the reference's subroutine texts executed mechanically (tests/test_oracle_reference_text.py);
+the halo / tripole code is not (no Fortran compiler in this image).
 """
 from __future__ import annotations
 
@@ -25,7 +26,7 @@ class Cfg(C.Structure):
                                        "strength_masked", "nthreads")] + \
                [(n, C.c_double) for n in ("dt_init", "cosw", "sinw", "rhow", "rhoi", "rhos",
                                           "gravit", "a_min", "m_min")] + \
-               [("revised_evp", C.c_int)]
+               [("revised_evp", C.c_int), ("no_halo", C.c_int)]
 
 
 _GRID_R8 = ("dxt", "dyt", "dxhy", "dyhx", "cxp", "cyp", "cxm", "cym", "tarea", "uarea",
@@ -88,14 +89,14 @@ def _ip(a):
 
 
 def make_cfg(dom, ndte, dt_init, nslabs=1, nthreads=0, cosw=1.0, sinw=0.0, tilt_mode=0,
-             strength_masked=0, revised_evp=False) -> Cfg:
+             strength_masked=0, revised_evp=False, no_halo=False) -> Cfg:
     from cice5_b200 import fixtures as fx
     return Cfg(nx_global=dom.nx, ny_global=dom.ny, nslabs=nslabs, ndte=ndte,
                ew_cyclic=int(dom.ew_cyclic), ns_tripole=int(dom.ns_tripole),
                grid_tripole=int(dom.grid_tripole), tilt_mode=tilt_mode,
                strength_masked=strength_masked, nthreads=nthreads, dt_init=dt_init,
                cosw=cosw, sinw=sinw, rhow=fx.RHOW, rhoi=fx.RHOI, rhos=fx.RHOS,
-               gravit=fx.GRAVIT, a_min=1.0e-3, m_min=1.0e-2, revised_evp=int(revised_evp))
+               gravit=fx.GRAVIT, a_min=1.0e-3, m_min=1.0e-2, revised_evp=int(revised_evp), no_halo=int(no_halo))
 
 
 def run_case(case, nslabs=1, nthreads=0, dt_init=None, **cfg_kw):

@@ -12,8 +12,10 @@
  * icetmask == 1, physical cells and the N/E ghost ring), strength = 0 everywhere else
  * (ice_mechred.F90:2175); evp then fills the ghosts with a halo update (:311).
  *
- * PARITY UNPINNED like the rest of the oracle (no golden vectors, no Fortran compiler); the
- * independent numpy restatement is oracle/strength_numpy.py.  exp() and sqrt() are libm's.
+ * Pinned bit for bit to the reference's own ice_strength / ridge_itd text, executed mechanically
+ * (tests/golden/make_reference_vectors.py -> tests/test_oracle_reference_text.py, all four
+ * krdg_partic x krdg_redist combinations and kstrength = 0); an independent numpy restatement is
+ * oracle/strength_numpy.py.  exp() and sqrt() are libm's.
  *
  * Arrays: (ny+2) x (nx+2) global-with-ghost planes, i fastest; aicen / vicen are ncat such planes
  * one after the other (Fortran (nx_block, ny_block, ncat)).  `cellmask` selects the cells of the

@@ -1,5 +1,6 @@
 /* strength_oracle.h -- CPU restatement of ice_strength (source/ice_mechred.F90:2111-2269).
- * TEST INFRASTRUCTURE (see evp_oracle.h); PARITY UNPINNED. */
+ * TEST INFRASTRUCTURE (see evp_oracle.h); pinned bit for bit to the reference text executed mechanically
+ * (tests/test_oracle_reference_text.py), see evp_oracle.h. */
 #ifndef STRENGTH_ORACLE_H
 #define STRENGTH_ORACLE_H
 #ifdef __cplusplus

@@ -1,6 +1,7 @@
 """The CPU oracle against (a) an independent numpy restatement written from the Fortran, (b) the
-invariants the reference guarantees, (c) its own committed golden vectors.  PARITY UNPINNED: the
-reference ships no golden vectors for this path."""
+invariants the reference guarantees, (c) its own committed golden vectors.  The reference ships no
+golden vectors for this path; tests/test_oracle_reference_text.py pins the
+oracle's arithmetic to the reference's subroutine texts instead."""
 import os
 
 import numpy as np
