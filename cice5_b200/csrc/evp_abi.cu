@@ -649,7 +649,8 @@ struct Builder {
     void sync() { if (h->cfg.nranks > 1) prog.push_back(Op{true, nullptr}); }
 
     // ice_HaloUpdate of one device plane: push edges / top rows into the inboxes, sync, apply
-    void halo(int plane, int loc, double sgn, double fill)
+    // first_pair: kFirstPair3D for the levels of fld2 (ice_HaloUpdate3DR8), see fold_necorner_column
+    void halo(int plane, int loc, double sgn, double fill, int first_pair = kFirstPair2D)
     {
         evp_handle *hh = h;
         const int buf = (seq++) & 1;
@@ -668,11 +669,12 @@ struct Builder {
             return EVP_OK;
         });
         sync();
-        op([hh, plane, loc, sgn, fill, buf](Launcher &L) {
+        op([hh, plane, loc, sgn, fill, buf, first_pair](Launcher &L) {
             const Geom &g = hh->g;
             const int na = g.nxl + 2 + g.ny;
             halo_apply_kernel<<<(na + 255) / 256, 256, 0, L.s()>>>(hh->plane(plane), g, hh->ib, hh->inbox(buf), loc,
-                                                                sgn, fill, hh->west_closed(), hh->east_closed());
+                                                                sgn, fill, hh->west_closed(), hh->east_closed(),
+                                                                first_pair);
             ++L.n;
             CK(cudaGetLastError());
             return EVP_OK;
@@ -927,8 +929,8 @@ void build_program(evp_handle *h, double dt, Program &P)
         return EVP_OK;
     });
     B.halo(W_STRENGTH, 0, +1.0, 0.0);                          // :311
-    B.halo(Ucur, 1, -1.0, 0.0);                                // :314 (fld2)
-    B.halo(Vcur, 1, -1.0, 0.0);
+    B.halo(Ucur, 1, -1.0, 0.0, kFirstPair3D);                  // :314 (fld2: the 3-D routine)
+    B.halo(Vcur, 1, -1.0, 0.0, kFirstPair3D);
     B.op([h, pb, Ucur, Uoth](Launcher &L) {
         // the other ping-pong copy must carry the same ghost ring where the loop never writes
         // (south row, closed E-W edges, open north row): start it as a copy of the current one

@@ -325,17 +325,24 @@ evp_subcycle_kernel(const __grid_constant__ LoopArgs a)
 // the top physical row r = ny is replaced by the (anti)symmetrised average, the ghost row
 // r = ny+1 by the mirrored row ny-1.  own = this column's row-ny value before the fold,
 // src_top / src_below = rows ny / ny-1 of the fold source column (global column nx - ig).
+// first_pair: first column pair (i, nx - i) that is averaged -- kFirstPair2D in ice_HaloUpdate2DR8
+// (mpi/ice_boundary.F90:1562), kFirstPair3D in ice_HaloUpdate3DR8, the routine the velocity pair fld2
+// goes through (ice_dyn_evp.F90:314, :397): its loop starts at nxGlobal/2 - lenUsedTripoleBuf + 1
+// (mpi/ice_boundary.F90:2817) and ice_HaloCreate leaves lenUsedTripoleBuf = nxGlobal/2 - 1 (:1067-1071),
+// so the pair (1, nx-1) next to the pole is mirrored with its sign but not averaged.  Pinned by executing
+// the reference text (tests/golden/make_halo_vectors.py, tests/test_oracle_reference_text.py).
+constexpr int kFirstPair2D = 1, kFirstPair3D = 2;
 __device__ __forceinline__ void fold_necorner_column(double *plane, int ld, int ny, int c, int ig,
                                                      int nx, double own, double src_below,
-                                                     double src_top, double sgn)
+                                                     double src_top, double sgn, int first_pair)
 {
     const int m = (nx - ig == 0) ? nx : nx - ig;
     const int half = nx / 2;
     double x;
-    if (ig >= 1 && ig <= half - 1) {
+    if (ig >= first_pair && ig <= half - 1) {
         x = 0.5 * (own + sgn * src_top);               // xavg; copy-out gives sgn*(sgn*xavg)
         x = sgn * (sgn * x);
-    } else if (m >= 1 && m <= half - 1) {
+    } else if (m >= first_pair && m <= half - 1) {
         x = sgn * (0.5 * (src_top + sgn * own));       // sgn * xavg of the pair (m, ig)
     } else {
         x = sgn * src_top;                             // self-mirrored / unpaired points
@@ -420,9 +427,10 @@ __global__ void fold_uv_kernel(double *u, double *v, int ld, int nxl, int ny, in
     int ig = lo + c;
     if (ig < 1) ig += nx;
     if (ig > nx) ig -= nx;
-    fold_necorner_column(u, ld, ny, c, ig, nx, u[(size_t)ny * ld + c], inbox[c], inbox[inbox_ld + c], -1.0);
+    fold_necorner_column(u, ld, ny, c, ig, nx, u[(size_t)ny * ld + c], inbox[c], inbox[inbox_ld + c], -1.0,
+                         kFirstPair3D);
     fold_necorner_column(v, ld, ny, c, ig, nx, v[(size_t)ny * ld + c], inbox[2 * inbox_ld + c],
-                         inbox[3 * inbox_ld + c], -1.0);
+                         inbox[3 * inbox_ld + c], -1.0, kFirstPair3D);
 }
 
 }  // namespace evp

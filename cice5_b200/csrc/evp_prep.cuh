@@ -97,7 +97,7 @@ __global__ void halo_push_kernel(const __grid_constant__ PushArgs a)
 // loc 0 = center (ghost row only), 1 = NEcorner (top physical row averaged + ghost row).
 // sgn = +1 scalar, -1 vector.
 __global__ void halo_apply_kernel(double *plane, Geom g, InboxGeom ib, double *inbox, int loc,
-                                  double sgn, double fill, int west_closed, int east_closed)
+                                  double sgn, double fill, int west_closed, int east_closed, int first_pair)
 {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int nxb = g.nxl + 2;
@@ -115,7 +115,7 @@ __global__ void halo_apply_kernel(double *plane, Geom g, InboxGeom ib, double *i
                 else if (c == g.nxl + 1) own = east_closed ? fill : inbox_col(inbox, ib, 1)[g.ny];
                 else own = plane[(size_t)g.ny * g.ld + c];
                 fold_necorner_column(plane, g.ld, g.ny, c, glob_col(g, c), g.nx_global, own,
-                                     in_below[c], in_top[c], sgn);
+                                     in_below[c], in_top[c], sgn, first_pair);
             }
         } else {
             plane[(size_t)(g.ny + 1) * g.ld + c] = fill;           // open / closed north

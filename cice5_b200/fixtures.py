@@ -62,10 +62,13 @@ def _wrap_cols(dom: Domain, a: np.ndarray, fill: float) -> None:
 
 
 def halo_update(dom: Domain, a: np.ndarray, loc: int = CENTER, kind: int = SCALAR,
-                fill: float = 0.0) -> np.ndarray:
+                fill: float = 0.0, first_pair: int = 1) -> np.ndarray:
     """``ice_HaloUpdate`` on a global-with-ghost array, in place (MPI pre-fill semantics).
 
-    Only ``center`` and ``NEcorner`` locations are supported (all that ``evp`` uses)."""
+    Only ``center`` and ``NEcorner`` locations are supported (all that ``evp`` uses).
+    ``first_pair``: first column pair (i, nx-i) of the top row the NE-corner fold averages: 1 in the
+    2-D routine, 2 in the 3-D routine of the MPI build that the velocity pair ``fld2`` goes through
+    (mpi/ice_boundary.F90:2817 with lenUsedTripoleBuf = nx/2 - 1 from :1067-1071)."""
     nx, ny = dom.nx, dom.ny
     assert a.shape == (ny + 2, nx + 2)
     a[0, :] = fill
@@ -86,7 +89,7 @@ def halo_update(dom: Domain, a: np.ndarray, loc: int = CENTER, kind: int = SCALA
             isrc[isrc > nx] -= nx
             a[ny + 1, :] = isign * buf2[isrc - 1]
         elif loc == NECORNER:
-            for i in range(1, nx // 2):     # i = 1 .. nx/2 - 1
+            for i in range(first_pair, nx // 2):     # i = first_pair .. nx/2 - 1
                 m = nx - i
                 x1, x2 = buf2[i - 1], buf2[m - 1]
                 xavg = 0.5 * (x1 + isign * x2)
@@ -226,13 +229,18 @@ def _continents(nx: int, ny: int, tlat_deg: np.ndarray) -> np.ndarray:
     return land
 
 
-def synthetic_tripole(nx: int, ny: int, name: str = "") -> Grid:
+def synthetic_tripole(nx: int, ny: int, name: str = "", wet_poles: bool = False) -> Grid:
     """Synthetic tripole (u-fold) grid, E-W cyclic ('Metrics', 'Masks').
 
     Latitude runs from -78 to +89.5 deg for Coriolis and the ice caps; the zonal metric uses
     cos(min(|lat|, 65 deg)) so that cells do not collapse towards the (synthetic) pole, as on a
     real tripole grid whose northern cap is roughly isotropic.  The i-perturbations are built
     explicitly symmetric under the fold maps (E face: i -> nx-i, N face: i -> nx+1-i).
+
+    ``wet_poles``: leave ocean around the two singular points of the fold (unlike any real grid, whose
+    poles sit inland) and open the whole top rows, so that the U points next to the pole carry ice: the
+    only place where the 2-D and 3-D halo routines of the reference differ (``halo_update``'s
+    ``first_pair``).
     """
     dom = Domain(nx, ny, ew_cyclic=True, ns_tripole=True, ns_open=False, grid_tripole=True,
                  name=name or f"tripole_{nx}x{ny}")
@@ -256,6 +264,8 @@ def synthetic_tripole(nx: int, ny: int, name: str = "") -> Grid:
     for ic in (nx // 2, nx):
         cols = [(ic - 1) % nx, ic % nx]                  # T columns ic, ic+1 (0-based ic-1, ic)
         land[ny - 2:, cols] = True
+    if wet_poles:
+        land[ny - 4:, :] = False
     # symmetrise the land mask across the fold for the top rows (T cell i <-> nx+1-i)
     top = land[ny - 3:, :]
     land[ny - 3:, :] = top | top[:, ::-1]

@@ -243,8 +243,8 @@ def evp(case, cosw=1.0, sinw=0.0, tilt_mode=0, strength_masked=0, dt_init=None, 
     else:
         strength[P] = inp["strength"][P]
     fx.halo_update(dom, strength, fx.CENTER, fx.SCALAR, 0.0)
-    fx.halo_update(dom, u, fx.NECORNER, fx.VECTOR, 0.0)
-    fx.halo_update(dom, v, fx.NECORNER, fx.VECTOR, 0.0)
+    fx.halo_update(dom, u, fx.NECORNER, fx.VECTOR, 0.0, first_pair=2)         # fld2: ice_HaloUpdate3DR8
+    fx.halo_update(dom, v, fx.NECORNER, fx.VECTOR, 0.0, first_pair=2)
     out["strength_out"][...] = strength
     out["icetmask"][...] = icetmask
     Cw = inp["Cw"]
@@ -268,8 +268,8 @@ def evp(case, cosw=1.0, sinw=0.0, tilt_mode=0, strength_masked=0, dt_init=None, 
         u[ice] = un[ice]; v[ice] = vn[ice]
         out["strintx"][ice] = sx[ice]; out["strinty"][ice] = sy[ice]
         out["strocnx"][ice] = taux[ice]; out["strocny"][ice] = tauy[ice]
-        fx.halo_update(dom, u, fx.NECORNER, fx.VECTOR, 0.0)
-        fx.halo_update(dom, v, fx.NECORNER, fx.VECTOR, 0.0)
+        fx.halo_update(dom, u, fx.NECORNER, fx.VECTOR, 0.0, first_pair=2)
+        fx.halo_update(dom, v, fx.NECORNER, fx.VECTOR, 0.0, first_pair=2)
     if dom.grid_tripole:                                                       # :416-481
         def hs(a1, a2):
             top = a2[dom.ny, 1:dom.nx + 1].copy()

@@ -164,7 +164,17 @@ static void merge_i4(const Dom *d, int **f, int *g)
 enum { LOC_CENTER = 0, LOC_NECORNER = 1 };
 enum { KIND_SCALAR = 0, KIND_VECTOR = 1 };
 
-static void halo_r8(const Dom *d, double **f, int loc, int kind, double fill)
+/* first_pair: first column pair (i, nx - i) of the degenerate top row that the NE-corner fold averages.
+ * The 2-D routine starts at i = 1 (mpi/ice_boundary.F90:1562, serial :817).  The 3-D routine of the MPI
+ * build -- the one the velocity pair fld2 goes through (ice_dyn_evp.F90:314, :397) -- starts at
+ * i = nxGlobal/2 - lenUsedTripoleBuf + 1 (mpi/ice_boundary.F90:2817), and ice_HaloCreate leaves
+ * lenUsedTripoleBuf = nxGlobal/2 - 1 for a halo that spans the whole top row (:1067-1071, a length
+ * taken as a difference of indices), so that loop starts at i = 2: the pair (1, nx - 1) next to the
+ * pole is mirrored with its sign but NOT averaged.  Found by executing the reference text
+ * (tests/golden/make_halo_vectors.py); reproduced here because parity is with the reference.        */
+enum { FIRST_PAIR_2D = 1, FIRST_PAIR_3D = 2 };
+
+static void halo_r8_ex(const Dom *d, double **f, int loc, int kind, double fill, int first_pair)
 {
     const int nx = d->nx, ny = d->ny;
     double *G;
@@ -212,7 +222,7 @@ static void halo_r8(const Dom *d, double **f, int loc, int kind, double fill)
             ioffset = 0; joffset = 0;                 /* :804-807 */
         } else {
             ioffset = 1; joffset = 1;                 /* :809-812 */
-            for (int i = 1; i <= nx / 2 - 1; ++i) {   /* :817-824 */
+            for (int i = first_pair; i <= nx / 2 - 1; ++i) {   /* :817-824 */
                 int iDst = nx - i;
                 double x1 = buf2[i - 1], x2 = buf2[iDst - 1];
                 double xavg = 0.5 * (x1 + isign * x2);
@@ -245,6 +255,17 @@ static void halo_r8(const Dom *d, double **f, int loc, int kind, double fill)
         free(buf2);
     }
     free(G);
+}
+
+static void halo_r8(const Dom *d, double **f, int loc, int kind, double fill)
+{
+    halo_r8_ex(d, f, loc, kind, fill, FIRST_PAIR_2D);
+}
+
+/* ice_HaloUpdate3DR8 of one level of fld2 (the velocity pair) */
+static void halo_r8_fld2(const Dom *d, double **f, int loc, int kind, double fill)
+{
+    halo_r8_ex(d, f, loc, kind, fill, FIRST_PAIR_3D);
 }
 
 static void halo_i4(const Dom *d, int **f, int loc, int kind, int fill)
@@ -826,8 +847,8 @@ int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
     }
     /* :311-315 */
     halo_r8(d, strength, LOC_CENTER, KIND_SCALAR, 0.0);
-    halo_r8(d, uvel, LOC_NECORNER, KIND_VECTOR, 0.0);
-    halo_r8(d, vvel, LOC_NECORNER, KIND_VECTOR, 0.0);
+    halo_r8_fld2(d, uvel, LOC_NECORNER, KIND_VECTOR, 0.0);            /* fld2: the 3-D routine */
+    halo_r8_fld2(d, vvel, LOC_NECORNER, KIND_VECTOR, 0.0);
 
     /* ---- subcycling :336-410 ---- */
     t_loop0 = now_s();
@@ -844,8 +865,8 @@ int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
                   strocnx[b], strocny[b], strintx[b], strinty[b], uvel_init[b],
                   vvel_init[b], uvel[b], vvel[b]);
         }
-        halo_r8(d, uvel, LOC_NECORNER, KIND_VECTOR, 0.0);                 /* :397 */
-        halo_r8(d, vvel, LOC_NECORNER, KIND_VECTOR, 0.0);
+        halo_r8_fld2(d, uvel, LOC_NECORNER, KIND_VECTOR, 0.0);            /* :397 */
+        halo_r8_fld2(d, vvel, LOC_NECORNER, KIND_VECTOR, 0.0);
     }
     t_loop1 = now_s();
 
@@ -938,6 +959,18 @@ int evp_oracle_halo_r8(const evp_oracle_cfg *cfg, double *a, int loc, int kind, 
     return 0;
 }
 
+int evp_oracle_halo_r8_fld2(const evp_oracle_cfg *cfg, double *a, int loc, int kind, double fill)
+{
+    Dom dom; double **f;
+    if (!cfg || !a || cfg->nx_global % (cfg->nslabs > 0 ? cfg->nslabs : 1)) return 1;
+    cfg_to_dom(cfg, &dom);
+    f = split_r8(&dom, a);
+    halo_r8_fld2(&dom, f, loc, kind, fill);
+    merge_r8(&dom, f, a);
+    free_slabs(&dom, (void **)f);
+    return 0;
+}
+
 int evp_oracle_halo_i4(const evp_oracle_cfg *cfg, int *a, int loc, int kind, int fill)
 {
     Dom dom; int **f;
@@ -947,6 +980,20 @@ int evp_oracle_halo_i4(const evp_oracle_cfg *cfg, int *a, int loc, int kind, int
     halo_i4(&dom, f, loc, kind, fill);
     merge_i4(&dom, f, a);
     free_slabs(&dom, (void **)f);
+    return 0;
+}
+
+int evp_oracle_halo_stress(const evp_oracle_cfg *cfg, double *a1, const double *a2)
+{
+    Dom dom; double **f1, **f2;
+    if (!cfg || !a1 || !a2 || cfg->nx_global % (cfg->nslabs > 0 ? cfg->nslabs : 1)) return 1;
+    cfg_to_dom(cfg, &dom);
+    f1 = split_r8(&dom, a1);
+    f2 = split_r8(&dom, a2);
+    halo_stress(&dom, f1, f2);
+    merge_r8(&dom, f1, a1);
+    free_slabs(&dom, (void **)f1);
+    free_slabs(&dom, (void **)f2);
     return 0;
 }
 

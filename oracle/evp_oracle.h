@@ -26,9 +26,18 @@
  *     FOR BIT (tests/test_oracle_reference_text.py: default build, -Dcoupled, AusCOM with a turning
  *     angle, revised EVP).  An interpreter, not a compiled run: compiler-specific contraction / -ftz
  *     choices of a real build are not represented.
- *   - HALO / TRIPOLE code and the driver's call order: still UNPINNED -- restated by hand, defended
- *     by invariants (decomposition independence, seam symmetry, free drift) and by an independent
- *     numpy restatement (oracle/evp_numpy.py).
+ *   - HALO / TRIPOLE code: the reference's create_blocks, ice_HaloCreate, ice_HaloMsgCreate and
+ *     ice_HaloUpdate2DR8 / 3DR8 / 2DI4 / _stress of the MPI build are executed the same way on one task
+ *     (tests/golden/make_halo_vectors.py -> ref_halo_vectors.npz) for tripole, open and closed domains
+ *     cut into 1x1 ... 4x1 blocks; the halo functions here must reproduce every cell of every block,
+ *     ghosts included, bit for bit, for 1 / 2 / 4 slabs.  Two findings: the 3-D routine that carries
+ *     the velocity pair does not average the column pair (1, nx-1) of the tripole's top row
+ *     (reproduced: halo_r8_ex, FIRST_PAIR_3D); ice_HaloUpdate_stress never writes the ring cells that
+ *     have no source, which this oracle sets to the 0 they hold in any run of the reference (stated
+ *     in the test).
+ *   - STILL UNPINNED: the driver's call order (evp, source/ice_dyn_evp.F90:68-510) is restated by hand,
+ *     defended by invariants (decomposition independence, free drift) and an independent numpy
+ *     restatement (oracle/evp_numpy.py).
  *
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl
  * reference legs may load this code.  The product path never does.
@@ -113,7 +122,12 @@ int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
 /* Stand-alone halo updates on a global-with-ghost array (for fixtures & tests).
  * loc: 0 = center, 1 = NEcorner.  kind: 0 = scalar, 1 = vector.               */
 int evp_oracle_halo_r8(const evp_oracle_cfg *cfg, double *a, int loc, int kind, double fill);
+/* the same through ice_HaloUpdate3DR8 (one level of the velocity pair fld2): the NE-corner fold leaves
+ * the column pair (1, nx-1) unaveraged, see halo_r8_ex in evp_oracle.c */
+int evp_oracle_halo_r8_fld2(const evp_oracle_cfg *cfg, double *a, int loc, int kind, double fill);
 int evp_oracle_halo_i4(const evp_oracle_cfg *cfg, int *a, int loc, int kind, int fill);
+/* ice_HaloUpdate_stress(array1, array2, halo, center, scalar): array1's ghosts from array2 */
+int evp_oracle_halo_stress(const evp_oracle_cfg *cfg, double *a1, const double *a2);
 
 /* principal_stress, ice_dyn_shared.F90:853-893 (diagnostic, n elements) */
 void evp_oracle_principal_stress(long long n, const double *stressp_1, const double *stressm_1,

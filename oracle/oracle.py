@@ -3,7 +3,7 @@
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
 import this module (see oracle/evp_oracle.h).  PARITY PARTLY PINNED: the arithmetic is pinned bit for
 bit to the reference's subroutine texts executed mechanically (tests/test_oracle_reference_text.py);
-the halo / tripole code is not (no Fortran compiler in this image).
+so is the halo / tripole code (MPI build, one task); the driver's call order is restated by hand.
 """
 from __future__ import annotations
 
@@ -133,6 +133,29 @@ def halo_r8(dom, a, loc, kind, fill=0.0, nslabs=1):
     rc = lib().evp_oracle_halo_r8(C.byref(cfg), _dp(a), loc, kind, C.c_double(fill))
     assert rc == 0
     return a
+
+
+def halo_r8_fld2(dom, a, loc, kind, fill=0.0, nslabs=1):
+    """One level of the velocity pair through ice_HaloUpdate3DR8 (pair (1, nx-1) of the fold not averaged)."""
+    cfg = make_cfg(dom, 1, 1.0, nslabs)
+    rc = lib().evp_oracle_halo_r8_fld2(C.byref(cfg), _dp(a), loc, kind, C.c_double(fill))
+    assert rc == 0
+    return a
+
+
+def halo_i4(dom, a, loc, kind, fill=0, nslabs=1):
+    cfg = make_cfg(dom, 1, 1.0, nslabs)
+    rc = lib().evp_oracle_halo_i4(C.byref(cfg), _ip(a), loc, kind, C.c_int(fill))
+    assert rc == 0
+    return a
+
+
+def halo_stress(dom, a1, a2, nslabs=1):
+    """ice_HaloUpdate_stress: ghosts of a1 from a2 (both global-with-ghost planes); a1 in place."""
+    cfg = make_cfg(dom, 1, 1.0, nslabs)
+    rc = lib().evp_oracle_halo_stress(C.byref(cfg), _dp(a1), _dp(a2))
+    assert rc == 0
+    return a1
 
 
 def principal_stress(sp1, sm1, s121, prs):

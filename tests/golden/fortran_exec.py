@@ -1,22 +1,30 @@
 """Mechanical execution of the reference's own Fortran statements (TEST INFRASTRUCTURE).
 
-No Fortran compiler exists in this image, so the arithmetic subroutines of the path cannot be
-compiled -- but they are written in a small, regular subset of Fortran 90 (do loops, block and
-one-line ifs, assignments to scalars / array elements, calls, intrinsics sqrt exp max min abs sign),
-and in that subset an array reference `a(i,j)` is also a valid Python call.  This module reads a
-subroutine straight out of the reference checkout, applies the C preprocessor conditionals, joins
-continuation lines, rewrites the control statements line by line into Python and executes the result
-with IEEE doubles (Python floats: same operations, same left-to-right order, no contraction).
+No Fortran compiler exists in this image, so the subroutines of the path cannot be compiled -- but
+they are written in a small, regular subset of Fortran 90, and in that subset an array reference
+`a(i,j)` is also a valid Python call.  This module reads a subroutine or function straight out of
+the reference checkout, applies the C preprocessor conditionals, joins continuation lines, rewrites
+the statements line by line into Python and executes the result with IEEE doubles (Python floats:
+same operations, same left-to-right order, no contraction; integer `/` truncates as in Fortran).
 Nothing is transcribed by hand: the statements that run are the reference's text.
 
-It is used ONLY by tests/golden/make_reference_vectors.py, in the build container (the reference
-does not travel to the GPU box); the vectors it produces are committed under tests/golden/.
+Subset: declarations (explicit-shape, deferred-shape, pointer, optional, intent, local parameters),
+do / do while / named do, block and one-line if, select case (values, ranges, strings, default),
+assignments to scalars, elements, sections and whole arrays, pointer assignment, derived-type
+components (`halo%srcLocalAddr(1,n)`, `all_blocks(n)%ilo`), allocate / deallocate / allocated,
+array constructors, calls with positional and keyword arguments whose non-intent(in) scalars are
+copied back, functions with a result variable, module variables (globals of the Module), the
+intrinsics sqrt exp max min abs sign mod real int size count any maxval minval huge present trim.
+A statement outside the subset (I/O aside, which is skipped) raises if execution reaches it
+(`UNTRANSLATED` lists them); calls to routines that were not loaded (timers, MPI_*) are no-ops.
 
-Not supported (not needed by the subroutines used): where/forall, array-valued expressions other
-than `a(:,:) = scalar`, derived types, I/O, goto, select case, character data.
+It is used ONLY by tests/golden/make_reference_vectors.py and tests/golden/make_halo_vectors.py, in
+the build container (the reference does not travel to the GPU box); the vectors they produce are
+committed under tests/golden/.
 """
 from __future__ import annotations
 
+import ast
 import math
 import re
 
@@ -48,23 +56,68 @@ class FArr:
     def _ix(self, idx):
         if not isinstance(idx, tuple):
             idx = (idx,)
-        return tuple(int(i) - l for i, l in zip(idx, self.lo))
+        if len(idx) != self.a.ndim:
+            raise IndexError(f"rank mismatch: {len(idx)} subscripts for rank {self.a.ndim}")
+        out = []
+        for i, l in zip(idx, self.lo):
+            if isinstance(i, slice):
+                out.append(slice(None if i.start is None else int(i.start) - l,
+                                 None if i.stop is None else int(i.stop) - l + 1))
+            else:
+                k = int(i) - l
+                if k < 0:
+                    raise IndexError(f"index {idx} below lower bounds {self.lo}")
+                out.append(k)
+        return tuple(out)
 
     def __call__(self, *idx):
         ix = self._ix(idx)
-        if any(i < 0 for i in ix):
-            raise IndexError(f"index {idx} below lower bounds {self.lo}")
+        if any(isinstance(i, slice) for i in ix):          # array section: a view, lower bounds 1
+            f = FArr.__new__(FArr)
+            f.a = self.a[ix]
+            f.lo = (1,) * f.a.ndim
+            return f
         v = self.a[ix]
-        return v.item()
+        return v.item() if isinstance(v, np.generic) else v
 
     def __setitem__(self, idx, val):
         ix = self._ix(idx)
-        if any(i < 0 for i in ix):
-            raise IndexError(f"index {idx} below lower bounds {self.lo}")
-        self.a[ix] = val
+        self.a[ix] = val.a if isinstance(val, FArr) else val
 
     def fill(self, val):
-        self.a[...] = val
+        self.a[...] = val.a if isinstance(val, FArr) else val
+
+    # whole-array comparisons (count(a /= 0), any(abs(a) /= n)): plain numpy logical arrays
+    def __ne__(self, o):
+        return self.a != (o.a if isinstance(o, FArr) else o)
+
+    def __eq__(self, o):
+        return self.a == (o.a if isinstance(o, FArr) else o)
+
+    def __gt__(self, o):
+        return self.a > (o.a if isinstance(o, FArr) else o)
+
+    def __lt__(self, o):
+        return self.a < (o.a if isinstance(o, FArr) else o)
+
+    __hash__ = object.__hash__
+
+
+class Obj:
+    """A derived-type variable: components are attributes."""
+
+    def __repr__(self):
+        return "Obj(" + ", ".join(f"{k}={v!r}" for k, v in vars(self).items() if not isinstance(v, FArr)) + ")"
+
+
+class _Null:
+    """A disassociated pointer (present as an actual argument, unlike None = absent optional)."""
+
+    def __repr__(self):
+        return "NULL"
+
+
+NULL = _Null()
 
 
 def _sign(a, b):
@@ -75,8 +128,85 @@ def _real(x, *_, **__):
     return float(x)
 
 
-INTRINSICS = {"sqrt": math.sqrt, "exp": math.exp, "max": max, "min": min, "abs": abs, "sign": _sign,
-              "real": _real, "present": lambda x: x is not None, "int": int, "mod": lambda a, b: math.fmod(a, b)}
+def _mod(a, b):
+    r = math.fmod(a, b)
+    return int(r) if isinstance(a, int) and isinstance(b, int) else r
+
+
+def _div(a, b):
+    """Fortran `/`: truncating for two integers, IEEE division otherwise."""
+    if isinstance(a, int) and isinstance(b, int) and not isinstance(a, bool):
+        q = abs(a) // abs(b)
+        return q if (a >= 0) == (b >= 0) else -q
+    return a / b
+
+
+def _size(x, dim=None):
+    return x.a.shape[dim - 1] if dim else x.a.size
+
+
+def _aset(cur, val):
+    """`name = value` where name may be a whole array (filled in place) or a scalar (rebound)."""
+    if isinstance(cur, FArr):
+        cur.fill(val)
+        return cur
+    return val
+
+
+def _setcomp(obj, comp, val):
+    """`obj%comp = value`: fills an array component, rebinds anything else."""
+    cur = getattr(obj, comp, None)
+    if isinstance(cur, FArr) and not isinstance(val, FArr):
+        cur.fill(val)
+    else:
+        setattr(obj, comp, val)
+
+
+def _out(f, r, key, old):
+    """Value of a non-intent(in) dummy after a call, for writing back into the actual argument."""
+    names = getattr(f, "__fargs__", None)
+    if names is None or not isinstance(r, dict):
+        return old
+    if isinstance(key, int):
+        if key >= len(names):
+            return old
+        key = names[key]
+    return r[key] if key in getattr(f, "__fout__", ()) and key in r else old
+
+
+def _alloc(bounds, kind=None):
+    a = FArr(bounds, dtype=object)
+    if kind == "derived":
+        for k in np.ndindex(a.a.shape):
+            a.a[k] = Obj()
+    return a
+
+
+def _abort(msg=""):
+    raise RuntimeError("abort_ice: " + str(msg))
+
+
+def fstub(args, out=()):
+    """Mark a Python stand-in for a Fortran subroutine: dummy names in order, non-intent(in) ones."""
+    def deco(fn):
+        fn.__fargs__, fn.__fout__ = list(args), set(out)
+        return fn
+    return deco
+
+
+def _abs(x):
+    return np.abs(x.a) if isinstance(x, FArr) else abs(x)
+
+
+INTRINSICS = {"sqrt": math.sqrt, "exp": math.exp, "max": max, "min": min, "abs": _abs, "sign": _sign,
+              "any": lambda x: bool(np.any(x)), "huge": lambda x: 2147483647 if isinstance(x, int) else 1.7976931348623157e308,
+              "_vec": lambda v: np.array(v, dtype=object), "count": lambda x: int(np.count_nonzero(x)),
+              "maxval": lambda x: max(x.a.ravel().tolist()) if _size(x) else -2147483647,
+              "minval": lambda x: min(x.a.ravel().tolist()) if _size(x) else 2147483647,
+              "real": _real, "present": lambda x: x is not None, "int": int, "mod": _mod, "_div": _div,
+              "size": _size, "allocated": lambda x: isinstance(x, FArr), "associated": lambda x: isinstance(x, FArr),
+              "trim": lambda s: s.rstrip(), "_aset": _aset, "_setcomp": _setcomp, "_out": _out, "_alloc": _alloc,
+              "_all": slice(None), "Obj": Obj, "NULL": NULL, "abort_ice": _abort}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -144,9 +274,11 @@ def preprocess(text: str, defined=()) -> list:
 
 
 def find_subroutine(lines: list, name: str) -> list:
+    """Logical lines of `subroutine name` / `function name`, header included, `end` line excluded."""
     name = name.lower()
-    start = next(i for i, l in enumerate(lines) if re.match(rf"subroutine {name}\b", l))
-    end = next(i for i in range(start, len(lines)) if re.match(rf"end subroutine( {name})?\b", lines[i]))
+    head = re.compile(rf"^(recursive )?(subroutine|function) {name}\b")
+    start = next(i for i, l in enumerate(lines) if head.match(l))
+    end = next(i for i in range(start + 1, len(lines)) if re.match(r"^end ?(subroutine|function)\b", lines[i]))
     return lines[start:end]
 
 
@@ -226,6 +358,7 @@ def _rewrite_pow(e: str) -> str:
 def expr(e: str) -> str:
     e = re.sub(r"([\d.])_(dbl_kind|int_kind|real_kind|r8)\b", r"\1", e)   # 1.0_dbl_kind, 2106._dbl_kind
     e = re.sub(r"(\d\.?\d*)d([+-]?\d+)", r"\1e\2", e)                     # 1.0d0
+    e = e.replace("(/", "_vec([").replace("/)", "])")                      # array constructor
     e = e.replace("/=", "!=")
     e = re.sub(r"\s*%\s*", ".", e)                                        # this_block%ilo
     for f, p in ((".and.", " and "), (".or.", " or "), (".not.", " not "), (".true.", " True "),
@@ -233,6 +366,7 @@ def expr(e: str) -> str:
                  (".ge.", ">="), (".le.", "<=")):
         e = e.replace(f, p)
     e = re.sub(r",\s*kind\s*=\s*\w+", "", e)                              # real(x, kind=dbl_kind)
+    e = re.sub(r"(?<=[(,])\s*:\s*(?=[,)])", "_all", e)                    # a(:,n): whole extent
     # integer powers as repeated products, the way compilers expand them (x**2 -> x*x, x**3 -> (x*x)*x);
     # Python's float ** goes through libm pow(), which is not the same operation
     e = _rewrite_pow(e)
@@ -251,99 +385,309 @@ def _matching_paren(s: str, start: int) -> int:
     raise ValueError(s)
 
 
-def _assignment(stmt: str) -> str:
-    # find the '=' of the assignment: first '=' at depth 0 that is not part of ==, /=, <=, >=
-    depth = 0
+_NAME = re.compile(r"^[a-z_]\w*$")
+
+
+def _top_level(s: str, ch: str) -> int:
+    """Index of the LAST occurrence of ch outside parentheses, or -1."""
+    depth, found = 0, -1
+    for i, c in enumerate(s):
+        if c == "(":
+            depth += 1
+        elif c == ")":
+            depth -= 1
+        elif c == ch and depth == 0:
+            found = i
+    return found
+
+
+def _split_assignment(stmt: str):
+    """(lhs, op, rhs) with op '=' or '=>'; None if stmt is not an assignment."""
+    depth, quote = 0, None
     for i, ch in enumerate(stmt):
-        if ch == "(":
+        if quote:
+            if ch == quote:
+                quote = None
+        elif ch in "'\"":
+            quote = ch
+        elif ch == "(":
             depth += 1
         elif ch == ")":
             depth -= 1
         elif ch == "=" and depth == 0 and stmt[i + 1:i + 2] != "=" and stmt[i - 1] not in "=/<>":
-            lhs, rhs = stmt[:i].strip(), stmt[i + 1:].strip()
-            m = re.match(r"^([a-z_]\w*)\s*\((.*)\)$", lhs)
-            if m:
-                idx = m.group(2)
-                if re.fullmatch(r"[\s:,]*", idx):                          # a(:,:) = scalar
-                    return f"{m.group(1)}.fill({expr(rhs)})"
-                return f"{m.group(1)}[{expr(idx)}] = {expr(rhs)}"
-            return f"{lhs} = {expr(rhs)}"
-    raise ValueError("not an assignment: " + stmt)
+            if stmt[i + 1:i + 2] == ">":
+                return stmt[:i].strip(), "=>", stmt[i + 2:].strip()
+            return stmt[:i].strip(), "=", stmt[i + 1:].strip()
+    return None
 
 
-def _simple(stmt: str, callable_names) -> str:
+class _Ctx:
+    """What the translator knows about the routine being translated."""
+
+    def __init__(self, callable_names, derived_arrays):
+        self.callable = set(callable_names)
+        self.derived = set(derived_arrays)
+        self.scalars = set()      # declared here, scalar (dummies included)
+        self.arrays = set()       # declared here, array (explicit or deferred shape)
+        self.assigned = set()     # simple names rebound by a statement
+        self.result = None        # function result variable
+
+    def declared(self, name):
+        return name in self.scalars or name in self.arrays
+
+
+def _assignment(stmt: str, ctx: _Ctx) -> str:
+    parts = _split_assignment(stmt)
+    if parts is None:
+        raise ValueError("not an assignment: " + stmt)
+    lhs, op, rhs = parts
+    value = expr(rhs)
+    k = _top_level(lhs, "%")
+    if k >= 0:                                                             # component of a derived type
+        base, comp = expr(lhs[:k]), lhs[k + 1:].strip()
+        m = re.match(r"^([a-z_]\w*)\s*\((.*)\)$", comp)
+        if m:
+            return f"{base}.{m.group(1)}[{expr(m.group(2))}] = {value}"
+        if op == "=>":
+            return f"{base}.{comp} = {value}"
+        return f"_setcomp({base}, {comp!r}, {value})"
+    m = re.match(r"^([a-z_]\w*)\s*\((.*)\)$", lhs)
+    if m:
+        idx = m.group(2)
+        if re.fullmatch(r"[\s:,]*", idx):                                  # a(:,:) = scalar or array
+            return f"{m.group(1)}.fill({value})"
+        return f"{m.group(1)}[{expr(idx)}] = {value}"
+    ctx.assigned.add(lhs)
+    if op == "=>" or lhs in ctx.scalars:
+        return f"{lhs} = {value}"
+    if lhs in ctx.arrays:
+        return f"{lhs} = _aset({lhs}, {value})"
+    return f"{lhs} = _aset(globals().get({lhs!r}), {value})"               # module variable
+
+
+def _call(stmt: str, ctx: _Ctx) -> list:
+    m = re.match(r"call ([a-z_]\w*)\s*(\((.*)\))?$", stmt)
+    name, args = m.group(1), split_top(m.group(3) or "")
+    if name == "abort_ice":
+        return [f"abort_ice({m.group(3) or ''})"]
+    if name not in ctx.callable:
+        return ["pass"]                                                    # timers, diagnostics
+    actual, back = [], []
+    for pos, a in enumerate(args):
+        km = re.match(r"^([a-z_]\w*)\s*=(?!=)\s*(.*)$", a)
+        key, val = (repr(km.group(1)), km.group(2).strip()) if km else (str(pos), a)
+        actual.append((km.group(1) + "=" if km else "") + expr(val))
+        if _NAME.match(val) and ctx.declared(val):                         # a variable that can come back
+            back.append(f"{val} = _out({name}, _r, {key}, {val})")
+            ctx.assigned.add(val)
+    return [f"_r = {name}({', '.join(actual)})"] + back
+
+
+def _simple(stmt: str, ctx: _Ctx) -> list:
     if stmt.startswith("call "):
-        m = re.match(r"call ([a-z_]\w*)\s*(\(.*\))?$", stmt)
-        if m.group(1) not in callable_names:
-            return "pass"                                                  # timers, abort_ice, ...
-        return f"{m.group(1)}{expr(m.group(2) or '()')}"
+        return _call(stmt, ctx)
     if stmt == "return":
-        return "return"
-    if stmt in ("continue",) or stmt.startswith(("write", "print")):
-        return "pass"
-    return _assignment(stmt)
+        return ["return " + (ctx.result or "locals()")]
+    if stmt == "exit":
+        return ["break"]
+    if stmt == "cycle":
+        return ["continue"]
+    if stmt == "continue" or stmt.startswith(("write", "print", "nullify", "format")):
+        return ["pass"]
+    m = re.match(r"^allocate\s*\((.*)\)$", stmt)
+    if m:
+        out = []
+        for item in split_top(m.group(1)):
+            if re.match(r"^stat\s*=", item):
+                out.append(f"{item.split('=')[1].strip()} = 0")
+                continue
+            open_ = item.rindex("(", 0, _matching_open(item))
+            target, dims = item[:open_].strip(), split_top(item[open_ + 1:-1])
+            bounds = ", ".join("(" + (expr(d.split(":")[0]) if ":" in d else "1") + ", " + expr(d.split(":")[-1]) + ")"
+                               for d in dims)
+            kind = "'derived'" if target in ctx.derived else "None"
+            if "%" in target:
+                out.append(f"{expr(target)} = _alloc([{bounds}], {kind})")
+            else:
+                ctx.assigned.add(target)
+                out.append(f"{target} = _alloc([{bounds}], {kind})")
+        return out
+    m = re.match(r"^deallocate\s*\((.*)\)$", stmt)
+    if m:
+        out = []
+        for item in split_top(m.group(1)):
+            if re.match(r"^stat\s*=", item):
+                out.append(f"{item.split('=')[1].strip()} = 0")
+            elif "%" in item:
+                out.append(f"{expr(item)} = None")
+            else:
+                ctx.assigned.add(item)
+                out.append(f"{item} = None")
+        return out
+    return [_assignment(stmt, ctx)]
 
 
-def translate(sub_lines: list, callable_names=()) -> tuple:
-    """(python source of a function body, dummy argument names, local array declarations)."""
-    header = sub_lines[0]
-    m = re.match(r"subroutine ([a-z_]\w*)\s*\((.*)\)", header)
-    name, args = m.group(1), [a.strip() for a in m.group(2).split(",")]
-    decl_arrays = {}            # name -> list of "lo:hi" strings
-    optional = set()
-    body, ind = [], 1
+def _matching_open(item: str) -> int:
+    """Index just past the '(' that matches the final ')' of item (item ends with ')')."""
+    depth = 0
+    for i in range(len(item) - 1, -1, -1):
+        if item[i] == ")":
+            depth += 1
+        elif item[i] == "(":
+            depth -= 1
+            if depth == 0:
+                return i + 1
+    raise ValueError(item)
+
+
+_PYKEYWORD = re.compile(r"(?<![.\w])(is|as|from|lambda|pass|del|def|class|with|yield|try|raise|global|import|assert|"
+                        r"except|finally|nonlocal|break|for|len)(?![.\w])")
+UNTRANSLATED = []      # (routine, statement, why): statements that raise if execution reaches them
+
+_TYPE_INIT = (("integer", "0"), ("real", "0.0"), ("double", "0.0"), ("logical", "False"), ("character", "''"),
+              ("type", "Obj()"))
+
+
+def translate(sub_lines: list, callable_names=(), derived_arrays=()):
+    """One subroutine / function of the reference -> the source of a Python function.
+
+    Returns (name, python source).  Subroutines return locals() (the caller copies the non-intent(in)
+    scalars back); functions return their result variable."""
+    ctx = _Ctx(callable_names, derived_arrays)
+    m = re.match(r"^(?:recursive )?(subroutine|function) ([a-z_]\w*)\s*(?:\((.*?)\))?\s*(?:result\s*\(\s*(\w+)\s*\))?$",
+                 sub_lines[0])
+    kind, name = m.group(1), m.group(2)
+    args = [a.strip() for a in (m.group(3) or "").split(",") if a.strip()]
+    if kind == "function":
+        ctx.result = m.group(4) or name
+    optional, not_in, init = set(), set(), []
+    body, ind, selects = [], 1, []
+
+    def emit(stmts, level=None):
+        pad = "    " * (ind if level is None else level)
+        body.extend(pad + s for s in stmts)
+
     for l in sub_lines[1:]:
-        if l.startswith(("use ", "implicit ", "include ", "save", "external ")):
+        l = _PYKEYWORD.sub(r"\1_", l)                                       # `is`, `lambda`, ... as variable names
+        if l.startswith(("use ", "implicit ", "include ", "save", "external ", "intrinsic ")) or l == "contains":
             continue
         if _DECL.match(l) and "::" in l:
             attrs, names = l.split("::", 1)
-            dm = re.search(r"dimension\s*\((.*?)\)\s*(,|$)", attrs)
             common = None
-            if dm:
+            if "dimension" in attrs:
                 k = attrs.index("dimension")
                 close = _matching_paren(attrs, attrs.index("(", k))
                 common = split_top(attrs[attrs.index("(", k) + 1:close])
+            typ = next(v for key, v in _TYPE_INIT if attrs.startswith(key))
             for item in split_top(names):
-                im = re.match(r"^([a-z_]\w*)\s*(\((.*)\))?", item)
+                im = re.match(r"^([a-z_]\w*)\s*(\((.*)\))?\s*(=.*)?$", item)
                 nm = im.group(1)
                 dims = split_top(im.group(3)) if im.group(3) else common
-                if dims:
-                    decl_arrays[nm] = (dims, "logical" if attrs.startswith("logical") else
-                                       "integer" if attrs.startswith("integer") else "real")
                 if "optional" in attrs:
                     optional.add(nm)
+                if "intent(in)" not in attrs.replace(" ", ""):
+                    not_in.add(nm)
+                if "parameter" in attrs:                                   # local named constant
+                    ctx.scalars.add(nm)
+                    init.append(f"{nm} = {expr(im.group(4)[1:])}")
+                    continue
+                if dims:
+                    ctx.arrays.add(nm)
+                    if nm in args:
+                        continue
+                    if any(d.strip() == ":" for d in dims):                # deferred shape
+                        init.append(f"{nm} = {'NULL' if 'pointer' in attrs else 'None'}")
+                    else:
+                        b = ", ".join("(" + (expr(d.split(":")[0]) if ":" in d else "1") + ", " +
+                                      expr(d.split(":")[-1]) + ")" for d in dims)
+                        dt = {"False": "bool", "0": "int", "0.0": "float"}.get(typ, "object")
+                        init.append(f"{nm} = FArr([{b}], dtype={dt})")
+                else:
+                    ctx.scalars.add(nm)
+                    if nm not in args:
+                        init.append(f"{nm} = {'NULL' if 'pointer' in attrs else typ}")
             continue
-        pad = "    " * ind
+        l = re.sub(r"^[a-z_]\w*\s*:\s*(?=do\b)", "", l)                     # construct names
         if re.match(r"^do [a-z_]\w*\s*=", l):
             mm = re.match(r"^do ([a-z_]\w*)\s*=\s*(.*)$", l)
             parts = split_top(mm.group(2))
-            lo, hi = expr(parts[0]), expr(parts[1])
             step = expr(parts[2]) if len(parts) > 2 else "1"
-            body.append(f"{pad}for {mm.group(1)} in _frange({lo}, {hi}, {step}):")
+            emit([f"for {mm.group(1)} in _frange({expr(parts[0])}, {expr(parts[1])}, {step}):"])
             ind += 1
-        elif l in ("enddo", "end do", "endif", "end if"):
+            emit(["pass"])
+        elif re.match(r"^do while\s*\(", l):
+            emit([f"while {expr(l[l.index('(') + 1:_matching_paren(l, l.index('('))])}:"])
+            ind += 1
+            emit(["pass"])
+        elif re.match(r"^end ?(do|if)\b", l):
+            ind -= 1
+        elif re.match(r"^select case\s*\(", l):
+            depth = len(selects)
+            emit([f"_sel{depth} = {expr(l[l.index('(') + 1:_matching_paren(l, l.index('('))])}"])
+            selects.append(True)                                           # True: no case emitted yet
+            ind += 1
+        elif l.startswith("case"):
+            depth = len(selects) - 1
+            if l.replace(" ", "") == "casedefault":
+                emit(["else:" if not selects[depth] else "if True:"], ind - 1)
+            else:
+                tests = []
+                for item in split_top(l[l.index("(") + 1:_matching_paren(l, l.index("("))]):
+                    if _top_level(item, ":") >= 0:
+                        lo, hi = item.split(":")
+                        tests.append(f"({expr(lo)} <= _sel{depth} <= {expr(hi)})")
+                    else:
+                        tests.append(f"_sel{depth} == {expr(item)}")
+                emit([("if " if selects[depth] else "elif ") + " or ".join(tests) + ":"], ind - 1)
+            selects[depth] = False
+            emit(["pass"])
+        elif re.match(r"^end ?select\b", l):
+            selects.pop()
             ind -= 1
         elif re.match(r"^(else\s*if|elseif)\s*\(", l):
             close = _matching_paren(l, l.index("("))
-            body.append("    " * (ind - 1) + f"elif {expr(l[l.index('(') + 1:close])}:")
+            emit([f"elif {expr(l[l.index('(') + 1:close])}:"], ind - 1)
+            emit(["pass"])
         elif l == "else":
-            body.append("    " * (ind - 1) + "else:")
-        elif l.startswith("if"):
+            emit(["else:"], ind - 1)
+            emit(["pass"])
+        elif re.match(r"^if\s*\(", l):
             close = _matching_paren(l, l.index("("))
             cond, rest = expr(l[l.index("(") + 1:close]), l[close + 1:].strip()
+            emit([f"if {cond}:"])
             if rest == "then":
-                body.append(f"{pad}if {cond}:")
                 ind += 1
+                emit(["pass"])
             else:
-                body.append(f"{pad}if {cond}: {_simple(rest, callable_names)}")
+                emit(_simple(rest, ctx), ind + 1)
         else:
-            body.append(pad + _simple(l, callable_names))
-    locals_ = {k: v for k, v in decl_arrays.items() if k not in args}
-    return name, args, optional, locals_, body
+            try:
+                emit(_simple(l, ctx))
+            except Exception as e:                                         # outside the subset: fails if reached
+                UNTRANSLATED.append((name, l, repr(e)))
+                emit([f"raise NotImplementedError({l!r})"])
+    glob = sorted(n for n in ctx.assigned if not ctx.declared(n) and n != ctx.result and _NAME.match(n))
+    if ctx.result and not ctx.declared(ctx.result):
+        init.insert(0, f"{ctx.result} = 0")
+    sig = ", ".join(a + ("=None" if a in optional else "") for a in args)
+    head = [f"def {name}({sig}):"] + (["    global " + ", ".join(glob)] if glob else []) + ["    " + s for s in init]
+    tail = ["    return " + (ctx.result or "locals()")]
+    return name, args, not_in, "\n".join(head + body + tail) + "\n"
 
 
 def _frange(lo, hi, step=1):
     return range(int(lo), int(hi) + (1 if step > 0 else -1), int(step))
+
+
+class _FortranDivision(ast.NodeTransformer):
+    """`/` between two integers truncates in Fortran: route every division through _div()."""
+
+    def visit_BinOp(self, node):
+        self.generic_visit(node)
+        if isinstance(node.op, ast.Div):
+            return ast.copy_location(ast.Call(func=ast.Name(id="_div", ctx=ast.Load()), args=[node.left, node.right],
+                                              keywords=[]), node)
+        return node
 
 
 class Module:
@@ -357,19 +701,15 @@ class Module:
             self.ns.update(ns)
         self.source = {}
 
-    def load(self, lines: list, names, callable_names=()):
+    def load(self, lines: list, names, callable_names=(), derived_arrays=()):
+        known = set(callable_names) | set(n.lower() for n in names) | \
+            {k for k, v in self.ns.items() if hasattr(v, "__fargs__")}
         for n in names:
-            name, args, optional, locals_, body = translate(find_subroutine(lines, n), tuple(callable_names) + tuple(names))
-            sig = ", ".join(a + ("=None" if a in optional else "") for a in args)
-            pre = []
-            for k, (dims, typ) in locals_.items():
-                b = ", ".join("(" + (d.split(":")[0] if ":" in d else "1") + ", " + d.split(":")[-1] + ")" for d in
-                              (expr(x) for x in dims))
-                dt = {"logical": "bool", "integer": "int", "real": "float"}[typ]
-                pre.append(f"    {k} = FArr([{b}], dtype={dt})")
-            src = f"def {name}({sig}):\n" + "\n".join(pre + body) + "\n    return locals()\n"
+            name, args, not_in, src = translate(find_subroutine(lines, n), known, derived_arrays)
             self.source[name] = src
-            exec(compile(src, f"<reference:{name}>", "exec"), self.ns)
+            tree = ast.fix_missing_locations(_FortranDivision().visit(ast.parse(src)))
+            exec(compile(tree, f"<reference:{name}>", "exec"), self.ns)
+            self.ns[name].__fargs__, self.ns[name].__fout__ = args, not_in
         return self
 
     def call(self, name, **kw):

@@ -124,8 +124,8 @@ def run_reference_sequence(m, g, s, revised_evp=False, ndte=None):
               dxt=F["dxt"], dyt=F["dyt"], tmask=tmask, nblocks=1, blocks_ice=lambda i: i,
               get_block=lambda *_: blk,
               global_minval=lambda arr, _d, msk: float(arr.a[1:-1, 1:-1][msk.a[1:-1, 1:-1]].min()))
-    k = m.call("set_evp_parameters", dt=DT)
-    ns.update({n: k[n] for n in ("dte", "dtei", "ecci", "dte2t", "revp", "arlx1i", "brlx", "denom1")})
+    m.call("set_evp_parameters", dt=DT)          # sets the module variables dtei, ecci, dte2t, revp, arlx1i, ...
+    k = ns
 
     z = lambda: fe.FArr([(1, NXB), (1, NYB)])
     zi = lambda: fe.FArr([(1, NXB), (1, NYB)], dtype=int)

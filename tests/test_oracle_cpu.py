@@ -235,3 +235,26 @@ def test_strength_single_category_closed_form():
     Cp = 0.5 * fx.GRAVIT * (fx.RHOW - fx.RHOI) * fx.RHOI / fx.RHOW
     want = 17.0 * Cp * (-h * h + (hmax ** 3 - hmin ** 3) / (3 * (hmax - hmin)) / k) / (1 - 1 / k)
     assert abs(s[5, 5] - want) <= 1e-12 * want
+
+
+def test_wet_pole_tripole_velocity_fold_skips_the_pole_pair():
+    """The velocity pair goes through the reference's 3-D halo routine, whose NE-corner fold does not
+    average the column pair (1, nx-1) next to the pole (oracle/evp_oracle.c halo_r8_ex; pinned to the
+    reference text by tests/test_oracle_reference_text.py).  On real grids those U points are land; the
+    `wet_poles` fixture puts ice on them: C oracle == numpy restatement bit for bit, 1 == 2 == 4 slabs,
+    every other pair of the top row antisymmetric, the pole pair swapped with its sign but not averaged."""
+    g = fx.synthetic_tripole(48, 24, wet_poles=True)
+    nx, ny = g.dom.nx, g.dom.ny
+    assert g.f["umask"][ny, 1] and g.f["umask"][ny, nx - 1]
+    case = fx.make_case(g, "full", ndte=12, dt=3600.0)
+    a = _run(case)
+    b = clone_case(case)
+    evp_numpy.evp(b)
+    compare_cases(b, a, bitwise=True)
+    for n in (2, 4):
+        compare_cases(_run(case, nslabs=n), a, bitwise=True)
+    for f in ("uvel", "vvel"):
+        top = a.io[f][ny, 1:nx + 1]
+        i = np.arange(2, nx // 2)
+        assert np.array_equal(top[i - 1], -top[nx - i - 1])
+        assert top[0] != 0.0 and top[0] != -top[nx - 2]
