@@ -1,6 +1,6 @@
 /*
  * evp_oracle.c -- CPU restatement of CICE5 evp(dt).  TEST INFRASTRUCTURE ONLY; see
- * evp_oracle.h for scope, citations and the "parity partly pinned" note.
+ * evp_oracle.h for scope, citations and the parity note.
  *
  * Build: gcc -O2 -fopenmp -ffp-contract=off -fno-fast-math -shared -fPIC  (oracle/Makefile)
  * Evaluation order follows the Fortran statement by statement; x**2 is x*x.

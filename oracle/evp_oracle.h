@@ -16,7 +16,7 @@
  *   serial/ice_boundary.F90:3269-3443 ice_HaloUpdate_stress
  *   mpi/ice_boundary.F90:2625-2632    ghost-ring pre-fill of the MPI build
  *
- * PARITY PARTLY PINNED.  The reference ships no tests, golden logs or fixtures for this
+ * PARITY PINNED TO THE REFERENCE TEXT (through an interpreter).  The reference ships no tests, golden logs or fixtures for this
  * path and cannot be compiled in this image (no Fortran compiler).  What pins this file:
  *   - ARITHMETIC (set_evp_parameters, evp_prep1, to_ugrid, evp_prep2, stress, stepu, evp_finish,
  *     to_tgrid, principal_stress; ice_strength in strength_oracle.c): the reference's own subroutine
@@ -35,9 +35,16 @@
  *     (reproduced: halo_r8_ex, FIRST_PAIR_3D); ice_HaloUpdate_stress never writes the ring cells that
  *     have no source, which this oracle sets to the 0 they hold in any run of the reference (stated
  *     in the test).
- *   - STILL UNPINNED: the driver's call order (evp, source/ice_dyn_evp.F90:68-510) is restated by hand,
- *     defended by invariants (decomposition independence, free drift) and an independent numpy
- *     restatement (oracle/evp_numpy.py).
+ *   - THE WHOLE CALL: the driver itself (subroutine evp, source/ice_dyn_evp.F90:68-510) is executed the
+ *     same way on tripole and open domains cut into 1x1 ... 4x1 blocks, calling the reference's own
+ *     subroutines and halo code (tests/golden/make_driver_vectors.py -> ref_driver_vectors.npz: default
+ *     build, -Dcoupled, revised EVP, ice on the tripole's poles); evp_oracle_run with halos on and 1 / 2 / 4
+ *     slabs must reproduce all 34 inout / out fields bit for bit on every physical cell, and the
+ *     halo-updated ones (uvel, vvel, strength) on every ghost cell.
+ *   - Caveat: an interpreter is not a compiler -- contraction / -ftz choices of a real ifort build are
+ *     not represented -- and the generic ice_HaloUpdate interface, ice_distributionGet* (one task) and
+ *     the global reductions are stood in for.  Further defended by invariants (decomposition
+ *     independence, free drift) and an independent numpy restatement (oracle/evp_numpy.py).
  *
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl
  * reference legs may load this code.  The product path never does.

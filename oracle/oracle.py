@@ -1,9 +1,9 @@
 """ctypes wrapper around oracle/_build/libevp_oracle.so (TEST INFRASTRUCTURE ONLY).
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
-import this module (see oracle/evp_oracle.h).  PARITY PARTLY PINNED: the arithmetic is pinned bit for
-bit to the reference's subroutine texts executed mechanically (tests/test_oracle_reference_text.py);
-so is the halo / tripole code (MPI build, one task); the driver's call order is restated by hand.
+import this module (see oracle/evp_oracle.h).  PARITY PINNED TO THE REFERENCE TEXT: arithmetic, halo /
+tripole code (MPI build, one task) and the whole evp driver are executed mechanically from the
+reference checkout and the oracle reproduces them bit for bit (tests/test_oracle_reference_text.py).
 """
 from __future__ import annotations
 

@@ -480,6 +480,10 @@ def _call(stmt: str, ctx: _Ctx) -> list:
         if _NAME.match(val) and ctx.declared(val):                         # a variable that can come back
             back.append(f"{val} = _out({name}, _r, {key}, {val})")
             ctx.assigned.add(val)
+            continue
+        em = re.match(r"^([a-z_]\w*)\s*\((.*)\)$", val)                    # an array element: icellt(iblk)
+        if em and em.group(1) in ctx.arrays and ":" not in em.group(2):
+            back.append(f"{em.group(1)}[{expr(em.group(2))}] = _out({name}, _r, {key}, {expr(val)})")
     return [f"_r = {name}({', '.join(actual)})"] + back
 
 
@@ -662,7 +666,10 @@ def translate(sub_lines: list, callable_names=(), derived_arrays=()):
                 emit(_simple(rest, ctx), ind + 1)
         else:
             try:
-                emit(_simple(l, ctx))
+                stmts = _simple(l, ctx)
+                for s_ in stmts:
+                    ast.parse(s_)
+                emit(stmts)
             except Exception as e:                                         # outside the subset: fails if reached
                 UNTRANSLATED.append((name, l, repr(e)))
                 emit([f"raise NotImplementedError({l!r})"])

@@ -241,3 +241,77 @@ def test_halo_stress_matches_reference_text(hvec, name):
     if nbx * nby == 1:                                      # (ring cells shared by two blocks have two entry values)
         rest = on_ring & ~sourced & ~zeroed
         assert np.array_equal(want[rest], after[rest])
+
+
+# ---------------------------------------------------------------------------------------------
+# the whole call: the reference's driver `evp` (source/ice_dyn_evp.F90:68-510) executed mechanically on
+# several blocks with the reference's own halo code (tests/golden/make_driver_vectors.py)
+# ---------------------------------------------------------------------------------------------
+DRIVER_NPZ = os.path.join(os.path.dirname(__file__), "golden", "ref_driver_vectors.npz")
+DRIVER_CASES = ("tripole_2x2", "tripole_wet_4x1", "tripole_coupled_1x1", "open_3x2", "open_revised_2x1")
+HALOED = ("uvel", "vvel", "strength")         # fields whose ghost cells the driver updates before it returns
+
+
+@pytest.fixture(scope="module")
+def dvec():
+    return np.load(DRIVER_NPZ)
+
+
+def driver_case(dvec, name):
+    nx, ny, bsx, bsy, nbx, nby, ndte = (int(x) for x in dvec[name + "__dims"])
+    cyc, trip, gtrip, coupled, revised = (int(x) for x in dvec[name + "__flags"])
+    dom = fx.Domain(nx, ny, ew_cyclic=bool(cyc), ns_tripole=bool(trip), ns_open=not trip,
+                    grid_tripole=bool(gtrip), name=name)
+    get = lambda part, n: np.ascontiguousarray(dvec[f"{name}__{part}__{n}"])
+    grid = fx.Grid(dom=dom, f={n: get("grid", n) for n in tuple(fx.GRID_FIELDS) + ("tmask", "umask")})
+    inp = {n: get("in", n) for n in fx.IN_FIELDS}
+    io = {n: get("io", n) for n in fx.INOUT_FIELDS}
+    io["iceumask"] = get("io", "iceumask")
+    # the reference computes the strength inside evp (ice_strength on the icellt list); the oracle takes
+    # it as an input on every cell and masks it to the list (strength_masked = 1)
+    inp["strength"] = orc.ice_strength(dom, inp["aice"], inp["vice"], get("itd", "aice0"), get("itd", "aicen"),
+                                       get("itd", "vicen"))
+    case = fx.Case(grid=grid, dt=float(dvec[name + "__dt"]), ndte=ndte, inp=inp, io=io, out=fx.zeroed_outputs(dom))
+    kw = dict(tilt_mode=coupled, revised_evp=bool(revised), strength_masked=1)
+    return case, kw, (bsx, bsy, nbx, nby)
+
+
+@pytest.mark.parametrize("name", DRIVER_CASES)
+def test_whole_call_matches_reference_driver_text(dvec, name):
+    case0, kw, layout = driver_case(dvec, name)
+    bsx, bsy, nbx, nby = layout
+    for nslabs in [n for n in (1, 2, 4) if case0.dom.nx % n == 0]:
+        case = fx.Case(grid=case0.grid, dt=case0.dt, ndte=case0.ndte, inp=case0.inp,
+                       io={k: v.copy() for k, v in case0.io.items()}, out=fx.zeroed_outputs(case0.dom))
+        orc.run_case(case, nslabs=nslabs, **kw)
+        checked = 0
+        for key in dvec.files:
+            if not key.startswith(name + "__out__"):
+                continue
+            n = key.split("__")[2]
+            ref = dvec[key]
+            mine = case.io[n] if n in case.io else case.out["strength_out" if n == "strength" else n]
+            mine = blocks_from_global(mine.astype(np.float64), layout)
+            assert np.array_equal(mine[:, 1:-1, 1:-1], ref[:, 1:-1, 1:-1]), (n, nslabs, "physical cells")
+            if n in HALOED or nbx * nby == 1:          # ghost cells too, where the global array defines them
+                assert np.array_equal(mine, ref), (n, nslabs, "ghost cells")
+            checked += 1
+        assert checked == 34
+    assert np.abs(phys_of(case.io["uvel"])).max() > 0.05 and np.abs(phys_of(case.io["stressp_1"])).max() > 1.0
+
+
+def phys_of(a):
+    return a[1:-1, 1:-1]
+
+
+def test_driver_cases_are_distinct(dvec):
+    """tilt from the sea-surface slope, revised EVP and the wet poles each change the answer."""
+    u = {n: dvec[n + "__out__uvel"] for n in DRIVER_CASES}
+    assert u["tripole_2x2"].shape != u["tripole_wet_4x1"].shape
+    arlx1i, brlx, denom1, revp, ecci = dvec["open_revised_2x1__consts"]
+    assert revp == 1.0
+    assert dvec["open_3x2__consts"][3] == 0.0
+    top = dvec["tripole_wet_4x1__out__uvel"]
+    nx = int(dvec["tripole_wet_4x1__dims"][0])
+    # block 1 holds column 1, the last block column nx-1, of the top physical row: not antisymmetric
+    assert top[0, -2, 1] != 0.0 and top[0, -2, 1] != -top[-1, -2, -3]
