@@ -1,0 +1,355 @@
+// cuda_emu.cpp -- TEST INFRASTRUCTURE: see cuda_emu.h.
+#include "cuda_emu.h"
+
+#include <stdio.h>
+
+namespace emu {
+
+thread_local Fiber *cur = nullptr;
+static thread_local Block *cur_block = nullptr;
+
+uint64_t now_ns()
+{
+    return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(
+               std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// ---- fibers ------------------------------------------------------------------------------------------
+static const size_t kStack = 256 * 1024;
+
+void yield()
+{
+    Fiber *f = cur;
+    swapcontext(&f->ctx, &f->block->sched);
+}
+
+static void fiber_main()
+{
+    Fiber *f = cur;
+    (*f->block->body)();
+    f->finished = true;
+    f->block->exited++;
+    f->warp->exited++;
+    f->warp->exited_mask |= 1u << f->lane;
+    swapcontext(&f->ctx, &f->block->sched);     // never resumed
+}
+
+// stacks are kept per host thread and reused from launch to launch
+static thread_local std::vector<void *> stack_pool;
+
+static void run_block(dim3 grid, dim3 block, uint3 bid, const std::function<void()> &body)
+{
+    Block b;
+    b.nthreads = (int)(block.x * block.y * block.z);
+    b.body = &body;
+    b.fibers.resize(b.nthreads);
+    b.warps.resize((b.nthreads + 31) / 32);
+    while ((int)stack_pool.size() < b.nthreads) stack_pool.push_back(malloc(kStack));
+    for (int t = 0; t < b.nthreads; ++t) {
+        Fiber &f = b.fibers[t];
+        f.tid = uint3{(unsigned)(t % block.x), (unsigned)((t / block.x) % block.y), (unsigned)(t / (block.x * block.y))};
+        f.bid = bid; f.bdim = block; f.gdim = grid;
+        f.block = &b; f.warp = &b.warps[t / 32]; f.lane = t % 32;
+        f.stack = stack_pool[t];
+        getcontext(&f.ctx);
+        f.ctx.uc_stack.ss_sp = f.stack;
+        f.ctx.uc_stack.ss_size = kStack;
+        f.ctx.uc_link = nullptr;
+        makecontext(&f.ctx, fiber_main, 0);
+    }
+    for (size_t w = 0; w < b.warps.size(); ++w) {
+        const int n = b.nthreads - (int)w * 32;
+        b.warps[w].lanes = n > 32 ? 32 : n;
+    }
+    Block *saved_block = cur_block;
+    Fiber *saved = cur;
+    cur_block = &b;
+    long long idle_rounds = 0;
+    while (b.exited < b.nthreads) {
+        const int before = b.exited;
+        for (int t = 0; t < b.nthreads; ++t) {
+            Fiber &f = b.fibers[t];
+            if (f.finished) continue;
+            cur = &f;
+            swapcontext(&b.sched, &f.ctx);
+        }
+        if (b.exited == before) {
+            if (++idle_rounds > 200000000LL) { fprintf(stderr, "cuda_emu: block makes no progress (deadlocked collective?)\n"); abort(); }
+        } else {
+            idle_rounds = 0;
+        }
+    }
+    cur = saved;
+    cur_block = saved_block;
+}
+
+void run_grid(dim3 grid, dim3 block, const std::function<void()> &body)
+{
+    for (unsigned z = 0; z < grid.z; ++z)
+        for (unsigned y = 0; y < grid.y; ++y)
+            for (unsigned x = 0; x < grid.x; ++x) run_block(grid, block, uint3{x, y, z}, body);
+}
+
+// ---- collectives ---------------------------------------------------------------------------------------
+Exchange rendezvous(unsigned mask, uint64_t v, bool pred)
+{
+    Fiber *f = cur;
+    Warp *w = f->warp;
+    if (w->lanes < 32) mask &= (1u << w->lanes) - 1u;
+    const int need = __builtin_popcount(mask);
+    while (w->phase != 0) yield();                        // the previous collective is still being read
+    w->slot[f->lane] = v;
+    if (pred) w->pred |= 1u << f->lane;
+    w->arrived_mask |= 1u << f->lane;
+    ++w->arrived;
+    (void)need;
+    // complete when every lane of the mask that has not returned is here (a returned lane named in a
+    // full mask is tolerated, as on Volta and later)
+    while (w->phase != 1) {
+        if (w->arrived >= __builtin_popcount(mask & ~w->exited_mask)) { w->phase = 1; break; }
+        yield();
+    }
+    const int readers = w->arrived;
+    Exchange e;
+    memcpy(e.slot, w->slot, sizeof(e.slot));
+    e.pred = w->pred & mask;
+    e.mask = w->arrived_mask;
+    if (++w->done == readers) { w->arrived = w->done = 0; w->pred = 0; w->arrived_mask = 0; w->phase = 0; }
+    return e;
+}
+
+}  // namespace emu
+
+unsigned __activemask()
+{
+    // rendezvous of the lanes that have not returned: wait until everyone else has arrived here or exited
+    emu::Fiber *f = emu::cur;
+    emu::Warp *w = f->warp;
+    while (w->phase != 0) emu::yield();
+    w->arrived_mask |= 1u << f->lane;
+    ++w->arrived;
+    while (w->phase == 0 && w->arrived + w->exited < w->lanes) emu::yield();
+    w->phase = 1;
+    const unsigned m = w->arrived_mask;
+    if (++w->done == w->arrived) { w->arrived = w->done = 0; w->arrived_mask = 0; w->pred = 0; w->phase = 0; }
+    return m;
+}
+
+void __syncthreads()
+{
+    emu::Fiber *f = emu::cur;
+    emu::Block *b = f->block;
+    while (b->bar_phase != 0) emu::yield();
+    ++b->bar_arrived;
+    while (b->bar_phase == 0 && b->bar_arrived + b->exited < b->nthreads) emu::yield();
+    b->bar_phase = 1;
+    if (++b->bar_done == b->bar_arrived) { b->bar_arrived = b->bar_done = 0; b->bar_phase = 0; }
+}
+
+void emu_ptx_unavailable(const char *what)
+{
+    fprintf(stderr, "cuda_emu: PTX that has no host stand-in was reached: %s\n", what);
+    abort();
+}
+
+// ---- streams: one worker thread each, in-order queue ----------------------------------------------------
+namespace emu {
+
+struct Stream {
+    std::mutex m;
+    std::condition_variable cv, idle;
+    std::deque<std::function<void()>> q;
+    bool busy = false, stop = false, capturing = false;
+    std::vector<std::function<void()>> captured;
+    std::thread worker;
+    Stream() : worker([this] { loop(); }) {}
+    ~Stream()
+    {
+        { std::lock_guard<std::mutex> l(m); stop = true; }
+        cv.notify_all();
+        worker.join();
+    }
+    void loop()
+    {
+        for (;;) {
+            std::function<void()> fn;
+            {
+                std::unique_lock<std::mutex> l(m);
+                cv.wait(l, [this] { return stop || !q.empty(); });
+                if (q.empty()) return;
+                fn = std::move(q.front());
+                q.pop_front();
+                busy = true;
+            }
+            fn();
+            {
+                std::lock_guard<std::mutex> l(m);
+                busy = false;
+                if (q.empty()) idle.notify_all();
+            }
+        }
+    }
+    void push(std::function<void()> fn)
+    {
+        { std::lock_guard<std::mutex> l(m); q.push_back(std::move(fn)); }
+        cv.notify_one();
+    }
+    void sync()
+    {
+        std::unique_lock<std::mutex> l(m);
+        idle.wait(l, [this] { return q.empty() && !busy; });
+    }
+};
+
+struct Event { uint64_t t = 0; };
+struct Graph { std::vector<std::function<void()>> nodes; };
+
+static std::mutex g_streams_m;
+static std::vector<Stream *> g_streams;
+static Stream *default_stream()
+{
+    static Stream *s = [] { Stream *x = new Stream; std::lock_guard<std::mutex> l(g_streams_m); g_streams.push_back(x); return x; }();
+    return s;
+}
+
+void enqueue(cudaStream_t s, std::function<void()> fn)
+{
+    if (!s) s = default_stream();
+    if (s->capturing) { s->captured.push_back(std::move(fn)); return; }
+    s->push(std::move(fn));
+}
+
+}  // namespace emu
+
+// ---- runtime API -------------------------------------------------------------------------------------------
+const char *cudaGetErrorString(cudaError_t e) { return e == cudaSuccess ? "no error" : "cuda_emu error"; }
+cudaError_t cudaGetLastError() { return cudaSuccess; }
+cudaError_t cudaSetDevice(int) { return cudaSuccess; }
+cudaError_t cudaGetDeviceCount(int *n) { *n = 8; return cudaSuccess; }
+cudaError_t cudaDeviceGetAttribute(int *v, cudaDeviceAttr, int) { *v = 4; return cudaSuccess; }
+cudaError_t cudaGetDeviceProperties(cudaDeviceProp *p, int)
+{
+    memset(p, 0, sizeof(*p));
+    snprintf(p->name, sizeof(p->name), "cuda_emu (host)");
+    p->multiProcessorCount = 4; p->major = 10; p->minor = 0; p->totalGlobalMem = (size_t)8 << 30;
+    return cudaSuccess;
+}
+cudaError_t cudaDeviceSynchronize()
+{
+    std::vector<emu::Stream *> all;
+    { std::lock_guard<std::mutex> l(emu::g_streams_m); all = emu::g_streams; }
+    for (auto *s : all) s->sync();
+    return cudaSuccess;
+}
+cudaError_t cudaDeviceEnablePeerAccess(int, unsigned) { return cudaSuccess; }
+cudaError_t cudaMalloc(void **p, size_t n)
+{
+    void *q = nullptr;
+    if (posix_memalign(&q, 256, n ? n : 1)) return cudaErrorMemoryAllocation;
+    memset(q, 0xFF, n);                          // uninitialised device memory: NaN doubles, -1 ints
+    *p = q;
+    return cudaSuccess;
+}
+cudaError_t cudaFree(void *p) { free(p); return cudaSuccess; }
+cudaError_t cudaMemcpy(void *d, const void *s, size_t n, cudaMemcpyKind)
+{
+    memcpy(d, s, n);                             // the streams here are all non-blocking: no implicit sync
+    return cudaSuccess;
+}
+// Pageable host memory, as the callers of the C ABI hand in: a host-to-device copy is staged before the
+// call returns (the caller may free or reuse its buffer at once), a device-to-host copy has completed when
+// the call returns.
+cudaError_t cudaMemcpyAsync(void *d, const void *s, size_t n, cudaMemcpyKind k, cudaStream_t st)
+{
+    return cudaMemcpy2DAsync(d, n, s, n, n, 1, k, st);
+}
+cudaError_t cudaMemcpy2DAsync(void *d, size_t dp, const void *s, size_t sp, size_t w, size_t h, cudaMemcpyKind k, cudaStream_t st)
+{
+    if (k == cudaMemcpyHostToDevice) {
+        auto stage = std::make_shared<std::vector<char>>(w * h);
+        for (size_t r = 0; r < h; ++r) memcpy(stage->data() + r * w, (const char *)s + r * sp, w);
+        emu::enqueue(st, [=] { for (size_t r = 0; r < h; ++r) memcpy((char *)d + r * dp, stage->data() + r * w, w); });
+        return cudaSuccess;
+    }
+    emu::enqueue(st, [=] { for (size_t r = 0; r < h; ++r) memcpy((char *)d + r * dp, (const char *)s + r * sp, w); });
+    if (k == cudaMemcpyDeviceToHost && !(st && st->capturing)) cudaStreamSynchronize(st);
+    return cudaSuccess;
+}
+cudaError_t cudaMemset(void *d, int v, size_t n) { memset(d, v, n); return cudaSuccess; }
+cudaError_t cudaMemsetAsync(void *d, int v, size_t n, cudaStream_t st)
+{
+    emu::enqueue(st, [=] { memset(d, v, n); });
+    return cudaSuccess;
+}
+cudaError_t cudaStreamCreateWithFlags(cudaStream_t *s, unsigned)
+{
+    *s = new emu::Stream;
+    std::lock_guard<std::mutex> l(emu::g_streams_m);
+    emu::g_streams.push_back(*s);
+    return cudaSuccess;
+}
+cudaError_t cudaStreamDestroy(cudaStream_t s)
+{
+    if (!s) return cudaSuccess;
+    s->sync();
+    {
+        std::lock_guard<std::mutex> l(emu::g_streams_m);
+        for (size_t i = 0; i < emu::g_streams.size(); ++i)
+            if (emu::g_streams[i] == s) { emu::g_streams.erase(emu::g_streams.begin() + i); break; }
+    }
+    delete s;
+    return cudaSuccess;
+}
+cudaError_t cudaStreamSynchronize(cudaStream_t s) { (s ? s : emu::default_stream())->sync(); return cudaSuccess; }
+cudaError_t cudaStreamBeginCapture(cudaStream_t s, cudaStreamCaptureMode)
+{
+    s->sync();
+    s->capturing = true;
+    s->captured.clear();
+    return cudaSuccess;
+}
+cudaError_t cudaStreamEndCapture(cudaStream_t s, cudaGraph_t *g)
+{
+    s->capturing = false;
+    *g = new emu::Graph{std::move(s->captured)};
+    s->captured.clear();
+    return cudaSuccess;
+}
+cudaError_t cudaGraphInstantiate(cudaGraphExec_t *e, cudaGraph_t g, unsigned long long) { *e = new emu::Graph(*g); return cudaSuccess; }
+cudaError_t cudaGraphLaunch(cudaGraphExec_t e, cudaStream_t s)
+{
+    for (auto &n : e->nodes) emu::enqueue(s, n);
+    return cudaSuccess;
+}
+cudaError_t cudaGraphDestroy(cudaGraph_t g) { delete g; return cudaSuccess; }
+cudaError_t cudaGraphExecDestroy(cudaGraphExec_t g) { delete g; return cudaSuccess; }
+cudaError_t cudaEventCreate(cudaEvent_t *e) { *e = new emu::Event; return cudaSuccess; }
+cudaError_t cudaEventDestroy(cudaEvent_t e) { delete e; return cudaSuccess; }
+cudaError_t cudaEventRecord(cudaEvent_t e, cudaStream_t s)
+{
+    emu::enqueue(s, [e] { e->t = emu::now_ns(); });
+    return cudaSuccess;
+}
+cudaError_t cudaEventElapsedTime(float *ms, cudaEvent_t a, cudaEvent_t b)
+{
+    *ms = (float)((double)(b->t - a->t) * 1e-6);
+    return cudaSuccess;
+}
+cudaError_t cudaIpcGetMemHandle(cudaIpcMemHandle_t *h, void *p)
+{
+    memset(h, 0, sizeof(*h));
+    memcpy(h->reserved, &p, sizeof(p));
+    return cudaSuccess;
+}
+cudaError_t cudaIpcOpenMemHandle(void **p, cudaIpcMemHandle_t h, unsigned)
+{
+    memcpy(p, h.reserved, sizeof(*p));
+    return cudaSuccess;
+}
+cudaError_t cudaIpcCloseMemHandle(void *) { return cudaSuccess; }
+cudaError_t cudaGetDriverEntryPoint(const char *, void **fn, unsigned long long, cudaDriverEntryPointQueryResult *q)
+{
+    *fn = nullptr;                               // no tensor maps on the host: the TMA kernel cannot run here
+    if (q) *q = cudaDriverEntryPointSymbolNotFound;
+    return cudaSuccess;
+}

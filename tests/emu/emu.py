@@ -1,0 +1,179 @@
+"""Host execution of the REAL device sources (TEST INFRASTRUCTURE -- see tests/emu/cuda_emu.h).
+
+`build()` copies cice5_b200/csrc/*.cu{,h} into tests/emu/_build/src with three mechanical rewrites and
+compiles them with g++ against tests/emu/cuda_emu.{h,cpp}:
+
+  * `#include <cuda_runtime.h>` / `<cuda.h>`            -> `#include "cuda_emu.h"`
+  * `kernel<<<grid, block, smem, stream>>>(args...)`    -> `emu::launch(grid, block, smem, stream, kernel, args...)`
+  * `asm volatile("<ptx>" : outs : ins : clobbers);`    -> the host stand-in of the three instructions of the
+    cross-rank flags (st.release.sys / ld.acquire.sys / globaltimer), `emu_ptx_unavailable()` for everything
+    else (mbarrier, cp.async.bulk: the TMA kernel cannot run on a host and is never launched here)
+
+Nothing else is touched: prep, halo, fold, strength, finish, the register-sweep subcycle kernel, the program
+builder, the CUDA-graph path and the multi-rank flag barrier all run from the product's own text.  The
+result, tests/emu/_build/libevp_emu.so, exports the product's C ABI; `patched()` swaps it into
+cice5_b200.evp for the duration of a test.  The product never loads it: cice5_b200 has no reference to
+this directory, and a missing CUDA library is still a hard error there.
+"""
+from __future__ import annotations
+
+import contextlib
+import ctypes as C
+import os
+import re
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+CSRC = os.path.join(ROOT, "cice5_b200", "csrc")
+BUILD = os.path.join(HERE, "_build")
+LIB = os.path.join(BUILD, "libevp_emu.so")
+
+_LAUNCH = re.compile(r"([A-Za-z_]\w*)\s*<<<(.*?)>>>\s*\(", re.S)
+
+
+def _balanced(s: str, i: int) -> int:
+    """Index of the ')' that closes the '(' at s[i]."""
+    depth, quote = 0, None
+    for k in range(i, len(s)):
+        ch = s[k]
+        if quote:
+            if ch == "\\":
+                continue
+            if ch == quote and s[k - 1] != "\\":
+                quote = None
+        elif ch == '"':
+            quote = ch
+        elif ch == "(":
+            depth += 1
+        elif ch == ")":
+            depth -= 1
+            if depth == 0:
+                return k
+    raise ValueError("unbalanced parentheses")
+
+
+def _operands(section: str) -> list:
+    """C expressions of `"constraint"(expr), ...`."""
+    out, i = [], 0
+    while True:
+        m = re.compile(r'"[^"]*"\s*\(').search(section, i)
+        if not m:
+            return out
+        close = _balanced(section, m.end() - 1)
+        out.append(section[m.end():close].strip())
+        i = close + 1
+
+
+def _rewrite_asm(text: str) -> str:
+    out, i = [], 0
+    pat = re.compile(r"asm\s+volatile\s*\(")
+    while True:
+        m = pat.search(text, i)
+        if not m:
+            out.append(text[i:])
+            return "".join(out)
+        close = _balanced(text, m.end() - 1)
+        body = text[m.end():close]
+        end = text.index(";", close) + 1
+        # split template : outputs : inputs : clobbers at top-level colons outside string literals
+        parts, depth, quote, cur = [], 0, None, ""
+        k = 0
+        while k < len(body):
+            ch = body[k]
+            if quote:
+                cur += ch
+                if ch == quote and body[k - 1] != "\\":
+                    quote = None
+            elif ch == '"':
+                quote = ch
+                cur += ch
+            elif ch == "(":
+                depth += 1
+                cur += ch
+            elif ch == ")":
+                depth -= 1
+                cur += ch
+            elif ch == ":" and depth == 0:
+                if body[k + 1:k + 2] == ":":            # '::' = empty section
+                    parts.append(cur)
+                    parts.append("")
+                    cur = ""
+                    k += 2
+                    continue
+                parts.append(cur)
+                cur = ""
+            else:
+                cur += ch
+            k += 1
+        parts.append(cur)
+        template = " ".join(re.findall(r'"((?:[^"\\]|\\.)*)"', parts[0]))
+        outs = _operands(parts[1]) if len(parts) > 1 else []
+        ins = _operands(parts[2]) if len(parts) > 2 else []
+        if "st.release.sys.global.u64" in template:
+            rep = f"emu_st_release_u64((void *)({ins[0]}), ({ins[1]}));"
+        elif "ld.acquire.sys.global.u64" in template:
+            rep = f"{outs[0]} = emu_ld_acquire_u64((const void *)({ins[0]}));"
+        elif "globaltimer" in template:
+            rep = f"{outs[0]} = emu::now_ns();"
+        else:
+            first = template.split(";")[0].strip().replace('"', "'")[:60]
+            rep = "".join(f"{o} = {{}}; " for o in outs if re.fullmatch(r"[A-Za-z_]\w*", o)) + \
+                f'emu_ptx_unavailable("{first}");'
+        out.append(text[i:m.start()] + rep)
+        i = end
+
+
+def transform(text: str) -> str:
+    text = re.sub(r"#include\s*<cuda_runtime\.h>|#include\s*<cuda\.h>", '#include "cuda_emu.h"', text)
+    text = _LAUNCH.sub(lambda m: f"emu::launch({m.group(2)}, {m.group(1)}, ", text)
+    text = _rewrite_asm(text)
+    # dynamic shared memory of the TMA kernel: a host array so that the (never executed) code compiles
+    text = re.sub(r"extern\s+__shared__\s+(.*?)(\w+)\s*\[\s*\]\s*;", r"static \1\2[1];", text)
+    text = text.replace("__shared__", "static")
+    return text
+
+
+def build(force: bool = False) -> str:
+    srcdir = os.path.join(BUILD, "src")
+    os.makedirs(srcdir, exist_ok=True)
+    sources = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh")))
+    deps = [os.path.join(CSRC, f) for f in sources] + [os.path.join(HERE, f) for f in ("cuda_emu.h", "cuda_emu.cpp", "emu.py")]
+    deps.append(os.path.join(ROOT, "include", "evp_b200.h"))
+    if not force and os.path.exists(LIB) and all(os.path.getmtime(d) <= os.path.getmtime(LIB) for d in deps):
+        return LIB
+    for f in sources:
+        out = transform(open(os.path.join(CSRC, f)).read())
+        out = out.replace('"../../include/evp_b200.h"', f'"{os.path.join(ROOT, "include", "evp_b200.h")}"')
+        with open(os.path.join(srcdir, f + (".cpp" if f.endswith(".cu") else "")), "w") as fh:
+            fh.write(out)
+    cmd = ["g++", "-std=c++17", "-O1", "-g", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared", "-pthread",
+           "-DEVP_STRICT=1", "-w", "-I", HERE, "-I", srcdir, "-o", LIB,
+           os.path.join(srcdir, "evp_abi.cu.cpp"), os.path.join(HERE, "cuda_emu.cpp")]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("g++ failed:\n" + " ".join(cmd) + "\n" + (r.stdout + r.stderr)[-6000:])
+    return LIB
+
+
+@contextlib.contextmanager
+def patched():
+    """cice5_b200.evp bound to the host build of its own sources (sweep kernel) inside the `with` block."""
+    from cice5_b200 import evp
+    lib_path = build()
+    saved_libs, saved_env = dict(evp._libs), os.environ.get("EVP_B200_KERNEL")
+    os.environ["EVP_B200_KERNEL"] = "sweep"
+    lib = C.CDLL(lib_path)
+    lib.evp_gpu_strerror.restype = C.c_char_p
+    lib.evp_gpu_last_cuda_error.restype = C.c_char_p
+    evp._libs.clear()
+    evp._libs.update({True: lib, False: lib})
+    try:
+        yield evp
+    finally:
+        evp._libs.clear()
+        evp._libs.update(saved_libs)
+        if saved_env is None:
+            os.environ.pop("EVP_B200_KERNEL", None)
+        else:
+            os.environ["EVP_B200_KERNEL"] = saved_env

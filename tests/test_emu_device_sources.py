@@ -1,0 +1,258 @@
+"""The product's OWN device and ABI sources, compiled for the host and run without a GPU.
+
+tests/emu/ rewrites nothing but the launch syntax, the CUDA headers and three PTX instructions of
+cice5_b200/csrc and builds the result with g++ against a small stand-in of the CUDA runtime (streams are
+threads, threads of a block are fibers, warp collectives are rendezvous; tests/emu/cuda_emu.h).  The
+C ABI library that comes out is driven through cice5_b200.evp exactly as the CUDA library is in the
+`-m gpu` tests, and must equal the CPU oracle -- and the vectors made from the reference's own text --
+BIT FOR BIT.  What this covers that had no hardware run yet: revised EVP, the device ice_strength,
+principal_stress, the velocity fold's unaveraged pole pair, the comparison with the reference-text
+vectors, tiny domains; and it re-checks on the host what the GPU suite validated: prep / halo / fold /
+finish kernels, the program builder, the CUDA-graph path, the multi-rank flag barrier, unequal slabs.
+What it cannot cover: the TMA subcycle kernel (mbarrier / cp.async.bulk PTX has no host stand-in; the
+register-sweep kernel computes the subcycles here), memory-model behaviour of a real device, speed.
+
+This is test infrastructure.  The product never loads the host build (nothing under cice5_b200/ refers
+to tests/emu/) and keeps failing loudly when its CUDA library is missing."""
+import numpy as np
+import pytest
+
+from cice5_b200 import fixtures as fx
+from oracle import oracle as orc
+from tests.emu import emu
+from tests.util import STATE, clone_case, compare_cases, phys
+from tests.test_gpu_parity import OUT_CHECK
+
+pytestmark = [pytest.mark.timeout(600)]
+
+
+@pytest.fixture(scope="module")
+def dev():
+    with emu.patched() as evp:
+        yield evp
+
+
+def _oracle(case, **kw):
+    ref = clone_case(case)
+    orc.run_case(ref, **kw)
+    return ref
+
+
+def test_host_build_exports_the_product_abi(dev):
+    import ctypes as C
+    lib = C.CDLL(emu.build())
+    for name in dev.EXPORTS:
+        assert hasattr(lib, name), name
+
+
+@pytest.mark.parametrize("grid,scenario,ndte,kw", [
+    ("gx3", "full", 8, {}),
+    ("gx3", "caps", 7, dict(cosw=0.9, sinw=float(np.sqrt(1 - 0.81)), tilt_mode=1)),
+    ("tripole", "full", 9, {}),
+    ("tripole_wet", "full", 6, {}),
+])
+def test_one_rank_bitwise(dev, grid, scenario, ndte, kw):
+    g = {"tripole": lambda: fx.synthetic_tripole(96, 40), "tripole_wet": lambda: fx.synthetic_tripole(96, 40, wet_poles=True)
+         }.get(grid, lambda: fx.make_grid(grid))()
+    case = fx.make_case(g, scenario, ndte=ndte, dt=3600.0)
+    ref = _oracle(case, **kw)
+    got = clone_case(case)
+    st = dev.run_case(got, strict=True, **kw)
+    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+    assert np.array_equal(phys(got.io["iceumask"]), phys(ref.io["iceumask"]))
+    assert st.active_t_cells > 0 and st.kernel_launches > ndte
+    if grid == "tripole_wet":                                   # the 3-D halo routine's pole pair
+        top = got.io["uvel"][g.dom.ny, 1:g.dom.nx + 1]
+        assert top[0] != 0.0 and top[0] != -top[g.dom.nx - 2]
+
+
+@pytest.mark.parametrize("nranks,starts", [(2, None), (4, None), (3, [0, 20, 60])])
+def test_ranks_two_calls_bitwise(dev, nranks, starts):
+    """x-slabs with the in-kernel flag barrier (streams are threads here, so the spin-waits are real),
+    equal and unequal slabs, state carried from one call to the next, on the wet-pole tripole."""
+    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
+    case = fx.make_case(grid, "full", ndte=5, dt=3600.0)
+    ref, got = clone_case(case), clone_case(case)
+    g = dev.EvpGroup(case.dom, case.ndte, case.dt, nranks, strict=True, slab_start=starts)
+    try:
+        g.set_grid(grid.f)
+        for _ in range(2):
+            ref.out, got.out = fx.zeroed_outputs(case.dom), fx.zeroed_outputs(case.dom)
+            orc.run_case(ref)
+            g.evp(case.dt, got.inp, got.io, got.out)
+            compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+    finally:
+        g.close()
+
+
+def test_cuda_graph_path_and_odd_ndte(dev):
+    """The ndte loop captured once per starting ping-pong parity and replayed: three calls with an odd ndte
+    (the state alternates between the two copies of the planes), graph on and off."""
+    grid = fx.synthetic_tripole(48, 24)
+    case = fx.make_case(grid, "full", ndte=5, dt=3600.0)
+    for graph in (True, False):
+        ref, got = clone_case(case), clone_case(case)
+        e = dev.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True, use_cuda_graph=graph)
+        try:
+            e.set_grid(grid.f)
+            for _ in range(3):
+                ref.out, got.out = fx.zeroed_outputs(case.dom), fx.zeroed_outputs(case.dom)
+                orc.run_case(ref)
+                e.evp(case.dt, got.inp, got.io, got.out)
+                compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+        finally:
+            e.close()
+
+
+def _xmin(grid):
+    tm = grid.f["tmask"][1:-1, 1:-1] > 0
+    return float(min(grid.f["dxt"][1:-1, 1:-1][tm].min(), grid.f["dyt"][1:-1, 1:-1][tm].min()))
+
+
+def test_revised_evp_bitwise(dev):
+    """REVISED instantiations of the subcycle kernel, prep2's stress reset, constants from xmin."""
+    grid = fx.make_grid("gx3")
+    case = fx.make_case(grid, "full", ndte=6)
+    ref = _oracle(case, revised_evp=True)
+    got = clone_case(case)
+    dev.run_case(got, strict=True, revised_evp=True)
+    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+    classic = _oracle(case)
+    assert not np.array_equal(phys(ref.io["uvel"]), phys(classic.io["uvel"]))
+
+
+def test_revised_evp_two_ranks_two_calls_bitwise(dev):
+    grid = fx.synthetic_tripole(96, 40)
+    case = fx.make_case(grid, "full", ndte=5, dt=3600.0)
+    ref, got = clone_case(case), clone_case(case)
+    g = dev.EvpGroup(case.dom, case.ndte, case.dt, 2, strict=True, revised_evp=True, xmin=_xmin(grid))
+    try:
+        g.set_grid(grid.f)
+        for _ in range(2):
+            ref.out, got.out = fx.zeroed_outputs(case.dom), fx.zeroed_outputs(case.dom)
+            orc.run_case(ref, revised_evp=True)
+            g.evp(case.dt, got.inp, got.io, got.out)
+            compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+    finally:
+        g.close()
+
+
+@pytest.mark.parametrize("modes", [dict(krdg_partic=1, krdg_redist=1), dict(krdg_partic=0, krdg_redist=0),
+                                   dict(krdg_partic=0, krdg_redist=1), dict(krdg_partic=1, krdg_redist=0),
+                                   dict(kstrength=0)])
+def test_device_ice_strength_bitwise(dev, modes):
+    """ice_strength_kernel from the uploaded thickness distribution.  On the host both sides call libm's
+    exp, so even the exponential participation function must agree bit for bit (on a GPU: a few ulp)."""
+    grid = fx.make_grid("gx3")
+    case = fx.make_case(grid, "caps", ndte=4)
+    itd = fx.ice_itd(case.inp)
+    ref = clone_case(case)
+    ref.inp["strength"] = orc.ice_strength(grid.dom, case.inp["aice"], case.inp["vice"], itd["aice0"], itd["aicen"],
+                                           itd["vicen"], **modes)
+    masked = 0 if modes.get("kstrength", 1) == 0 else 1
+    orc.run_case(ref, strength_masked=masked)
+    got = clone_case(case)
+    got.inp.pop("strength")
+    e = dev.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True)
+    try:
+        e.set_grid(grid.f)
+        e.upload_itd(itd["aicen"], itd["vicen"], itd["aice0"], **modes)
+        e.evp(case.dt, got.inp, got.io, got.out)
+    finally:
+        e.close()
+    assert (phys(ref.out["strength_out"]) > 0).any()
+    assert np.array_equal(phys(got.out["strength_out"]), phys(ref.out["strength_out"]))
+    compare_cases(got, ref, fields_io=STATE, fields_out=("divu", "shear", "strocnxT"), bitwise=True)
+
+
+def test_principal_stress_bitwise(dev):
+    grid = fx.make_grid("gx3")
+    case = fx.make_case(grid, "full", ndte=6)
+    got = clone_case(case)
+    e = dev.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True)
+    try:
+        e.set_grid(grid.f)
+        e.evp(case.dt, got.inp, got.io, got.out)
+        s1, s2 = e.principal_stress()
+    finally:
+        e.close()
+    r1, r2 = orc.principal_stress(got.io["stressp_1"], got.io["stressm_1"], got.io["stress12_1"], got.out["prs_sig"])
+    assert np.array_equal(s1, r1) and np.array_equal(s2, r2)
+    assert (s1 != 1.0e30).any() and (s1 == 1.0e30).any()
+
+
+def test_resident_state_upload_compute_download(dev):
+    """upload once, compute twice, download: equals two evp calls of the oracle with the same forcing."""
+    grid = fx.synthetic_tripole(48, 24)
+    case = fx.make_case(grid, "full", ndte=4, dt=3600.0)
+    ref = clone_case(case)
+    orc.run_case(ref)
+    ref.out = fx.zeroed_outputs(case.dom)
+    orc.run_case(ref)
+    got = clone_case(case)
+    e = dev.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True)
+    try:
+        e.set_grid(grid.f)
+        e.upload(got.inp, got.io)
+        e.compute(case.dt)
+        e.compute(case.dt)
+        e.download(got.io, got.out)
+    finally:
+        e.close()
+    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+
+
+# ---- the device sources against the reference's own text, no oracle in between ---------------------------
+from tests.test_oracle_reference_text import DRIVER_CASES, DRIVER_NPZ, HALOED, blocks_from_global, driver_case  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def dvec():
+    return np.load(DRIVER_NPZ)
+
+
+def _check_reference_text(dvec, name, case, layout):
+    _bsx, _bsy, nbx, nby = layout
+    checked = 0
+    for key in dvec.files:
+        if not key.startswith(name + "__out__"):
+            continue
+        n = key.split("__")[2]
+        ref = dvec[key]
+        mine = case.io[n] if n in case.io else case.out["strength_out" if n == "strength" else n]
+        mine = blocks_from_global(mine.astype(np.float64), layout)
+        assert np.array_equal(mine[:, 1:-1, 1:-1], ref[:, 1:-1, 1:-1]), (n, "physical cells")
+        if n in HALOED or nbx * nby == 1:
+            assert np.array_equal(mine, ref), (n, "ghost cells")
+        checked += 1
+    assert checked == 34
+
+
+@pytest.mark.parametrize("name", DRIVER_CASES)
+def test_device_sources_match_reference_text(dev, dvec, name):
+    case, kw, layout = driver_case(dvec, name)
+    dev.run_case(case, strict=True, **kw)
+    _check_reference_text(dvec, name, case, layout)
+
+
+@pytest.mark.parametrize("name", ["tripole_2x2", "tripole_wet_4x1", "open_3x2"])
+def test_device_sources_match_reference_text_two_ranks(dev, dvec, name):
+    case, kw, layout = driver_case(dvec, name)
+    g = dev.EvpGroup(case.dom, case.ndte, case.dt, 2, strict=True, **kw)
+    try:
+        g.set_grid(case.grid.f)
+        g.evp(case.dt, case.inp, case.io, case.out)
+    finally:
+        g.close()
+    _check_reference_text(dvec, name, case, layout)
+
+
+def test_product_loader_has_no_host_fallback():
+    """cice5_b200 must not know about the host build: no reference to tests/emu anywhere in the package."""
+    import os
+    pkg = os.path.dirname(fx.__file__)
+    for root, _dirs, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".F90")):
+                text = open(os.path.join(root, f), errors="replace").read()
+                assert "tests/emu" not in text and "libevp_emu" not in text and "cuda_emu" not in text, f
