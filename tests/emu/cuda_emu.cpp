@@ -37,7 +37,26 @@ static void fiber_main()
 // stacks are kept per host thread and reused from launch to launch
 static thread_local std::vector<void *> stack_pool;
 
-static void run_block(dim3 grid, dim3 block, uint3 bid, const std::function<void()> &body)
+// ---- 32-bit "shared" handles -----------------------------------------------------------------------------
+struct Region { uintptr_t base; };
+static thread_local std::vector<Region> regions;
+static const uintptr_t kRegionSpan = (uintptr_t)1 << 24;
+
+static void shared_regions_reset(void *smem, size_t bytes)
+{
+    regions.clear();
+    if (smem)
+        for (uintptr_t b = (uintptr_t)smem; b < (uintptr_t)smem + bytes; b += kRegionSpan) regions.push_back(Region{b});
+}
+
+static void *from_handle(unsigned h)
+{
+    const unsigned r = h >> 24;
+    if (r >= regions.size()) { fprintf(stderr, "cuda_emu: bad shared handle %#x\n", h); abort(); }
+    return (void *)(regions[r].base + (h & 0xFFFFFFu));
+}
+
+static void run_block(dim3 grid, dim3 block, uint3 bid, size_t smem, const std::function<void()> &body)
 {
     Block b;
     b.nthreads = (int)(block.x * block.y * block.z);
@@ -61,6 +80,13 @@ static void run_block(dim3 grid, dim3 block, uint3 bid, const std::function<void
         const int n = b.nthreads - (int)w * 32;
         b.warps[w].lanes = n > 32 ? 32 : n;
     }
+    void *smem_raw = nullptr;
+    if (smem) {
+        if (posix_memalign(&smem_raw, 1024, smem)) abort();
+        memset(smem_raw, 0xFF, smem);
+        b.smem = smem_raw;
+    }
+    shared_regions_reset(smem_raw, smem);
     Block *saved_block = cur_block;
     Fiber *saved = cur;
     cur_block = &b;
@@ -81,14 +107,17 @@ static void run_block(dim3 grid, dim3 block, uint3 bid, const std::function<void
     }
     cur = saved;
     cur_block = saved_block;
+    free(smem_raw);
 }
 
-void run_grid(dim3 grid, dim3 block, const std::function<void()> &body)
+void run_grid(dim3 grid, dim3 block, size_t smem, const std::function<void()> &body)
 {
     for (unsigned z = 0; z < grid.z; ++z)
         for (unsigned y = 0; y < grid.y; ++y)
-            for (unsigned x = 0; x < grid.x; ++x) run_block(grid, block, uint3{x, y, z}, body);
+            for (unsigned x = 0; x < grid.x; ++x) run_block(grid, block, uint3{x, y, z}, smem, body);
 }
+
+void *dynamic_smem() { return cur->block->smem; }
 
 // ---- collectives ---------------------------------------------------------------------------------------
 Exchange rendezvous(unsigned mask, uint64_t v, bool pred)
@@ -144,6 +173,112 @@ void __syncthreads()
     while (b->bar_phase == 0 && b->bar_arrived + b->exited < b->nthreads) emu::yield();
     b->bar_phase = 1;
     if (++b->bar_done == b->bar_arrived) { b->bar_arrived = b->bar_done = 0; b->bar_phase = 0; }
+}
+
+size_t __cvta_generic_to_shared(const void *p)
+{
+    using namespace emu;
+    const uintptr_t a = (uintptr_t)p;
+    for (size_t r = 0; r < regions.size(); ++r)
+        if (a >= regions[r].base && a - regions[r].base < kRegionSpan) return (r << 24) | (a - regions[r].base);
+    regions.push_back(Region{a & ~(uintptr_t)0xFFF});
+    if (regions.size() > 255) { fprintf(stderr, "cuda_emu: too many shared regions\n"); abort(); }
+    return ((regions.size() - 1) << 24) | (a - regions.back().base);
+}
+
+// ---- mbarrier: the 64-bit word in shared memory holds the whole state --------------------------------------
+namespace {
+struct MBar { int32_t tx; uint16_t pending; uint16_t count_phase; };   // count in bits 0-14, phase in bit 15
+static_assert(sizeof(MBar) == 8, "mbarrier state is one 64-bit word");
+inline void mbar_check(MBar *m)
+{
+    if (m->pending == 0 && m->tx == 0) {
+        m->count_phase ^= 0x8000u;
+        m->pending = m->count_phase & 0x7FFFu;
+    }
+}
+}  // namespace
+
+void emu_mbar_init(unsigned bar, unsigned count)
+{
+    MBar *m = (MBar *)emu::from_handle(bar);
+    m->tx = 0; m->pending = (uint16_t)count; m->count_phase = (uint16_t)count;
+}
+void emu_mbar_arrive(unsigned bar)
+{
+    MBar *m = (MBar *)emu::from_handle(bar);
+    if (m->pending == 0) { fprintf(stderr, "cuda_emu: mbarrier over-arrival\n"); abort(); }
+    --m->pending;
+    mbar_check(m);
+}
+void emu_mbar_expect_tx(unsigned bar, unsigned bytes)
+{
+    MBar *m = (MBar *)emu::from_handle(bar);
+    m->tx += (int32_t)bytes;
+    emu_mbar_arrive(bar);
+}
+unsigned emu_mbar_try_wait(unsigned bar, unsigned parity)
+{
+    MBar *m = (MBar *)emu::from_handle(bar);
+    const unsigned phase = (m->count_phase >> 15) & 1u;
+    if (phase != (parity & 1u)) return 1u;       // the phase with that parity has completed
+    emu::yield();
+    return 0u;
+}
+
+// ---- tensor maps: base, rank, element size, extents, byte strides, box ---------------------------------------
+namespace {
+struct TMap { void *base; uint64_t rank, esize, dim[3], stride[2], box[3]; };
+static_assert(sizeof(TMap) <= sizeof(CUtensorMap), "tensor map fits the opaque type");
+CUresult emu_encode_tiled(CUtensorMap *out, CUtensorMapDataType dt, cuuint32_t rank, void *base, const cuuint64_t *dims,
+                          const cuuint64_t *strides, const cuuint32_t *box, const cuuint32_t *, CUtensorMapInterleave,
+                          CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill)
+{
+    if (rank < 1 || rank > 3) return 1;
+    TMap t;
+    memset(&t, 0, sizeof(t));
+    t.base = base; t.rank = rank; t.esize = dt == CU_TENSOR_MAP_DATA_TYPE_FLOAT64 ? 8 : 1;
+    for (unsigned d = 0; d < 3; ++d) { t.dim[d] = d < rank ? dims[d] : 1; t.box[d] = d < rank ? box[d] : 1; }
+    for (unsigned d = 0; d + 1 < rank; ++d) t.stride[d] = strides[d];
+    memset(out, 0, sizeof(*out));
+    memcpy(out, &t, sizeof(t));
+    return CUDA_SUCCESS;
+}
+}  // namespace
+
+void emu_tma_load(unsigned dst, const CUtensorMap *map, unsigned bar, int rank, int x, int y, int z)
+{
+    TMap t;
+    memcpy(&t, map, sizeof(t));
+    if ((int)t.rank != rank) { fprintf(stderr, "cuda_emu: tensor map rank mismatch\n"); abort(); }
+    char *d = (char *)emu::from_handle(dst);
+    const long long c0[3] = {x, y, z};
+    for (uint64_t k = 0; k < t.box[2]; ++k)
+        for (uint64_t j = 0; j < t.box[1]; ++j)
+            for (uint64_t i = 0; i < t.box[0]; ++i) {
+                const long long c[3] = {c0[0] + (long long)i, c0[1] + (long long)j, c0[2] + (long long)k};
+                const bool in = c[0] >= 0 && c[0] < (long long)t.dim[0] && c[1] >= 0 && c[1] < (long long)t.dim[1] &&
+                                c[2] >= 0 && c[2] < (long long)t.dim[2];
+                if (in)
+                    memcpy(d, (const char *)t.base + c[0] * t.esize + c[1] * t.stride[0] + c[2] * t.stride[1], t.esize);
+                else
+                    memset(d, 0, t.esize);                        // out-of-bounds elements read as zero
+                d += t.esize;
+            }
+    MBar *m = (MBar *)emu::from_handle(bar);
+    m->tx -= (int32_t)(t.box[0] * t.box[1] * t.box[2] * t.esize);
+    mbar_check(m);
+}
+
+void emu_bar_sync(int id, int nthreads)
+{
+    emu::Block *b = emu::cur->block;
+    emu::Block::Named &n = b->named[id & 15];
+    while (n.phase != 0) emu::yield();
+    ++n.arrived;
+    while (n.phase == 0 && n.arrived < nthreads) emu::yield();
+    n.phase = 1;
+    if (++n.done == n.arrived) { n.arrived = n.done = 0; n.phase = 0; }
 }
 
 void emu_ptx_unavailable(const char *what)
@@ -349,7 +484,7 @@ cudaError_t cudaIpcOpenMemHandle(void **p, cudaIpcMemHandle_t h, unsigned)
 cudaError_t cudaIpcCloseMemHandle(void *) { return cudaSuccess; }
 cudaError_t cudaGetDriverEntryPoint(const char *, void **fn, unsigned long long, cudaDriverEntryPointQueryResult *q)
 {
-    *fn = nullptr;                               // no tensor maps on the host: the TMA kernel cannot run here
-    if (q) *q = cudaDriverEntryPointSymbolNotFound;
+    *fn = (void *)&emu_encode_tiled;             // the only driver entry point the sources ask for
+    if (q) *q = cudaDriverEntryPointSuccess;
     return cudaSuccess;
 }

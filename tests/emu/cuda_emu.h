@@ -5,8 +5,8 @@
 // It exists because rows of DESIGN.md section 8 were written after the round's GPU budget was spent: this is
 // how their device code gets executed at all before its first hardware run.  It is NOT a product path and
 // NOT a fallback: nothing under cice5_b200/ knows about it, the library it produces lives under
-// tests/emu/_build/ and is loaded only by tests/emu/emu.py, and the TMA subcycle kernel (mbarrier /
-// cp.async.bulk PTX) cannot run here at all -- only the register-sweep kernel (EVP_B200_KERNEL=sweep).
+// tests/emu/_build/ and is loaded only by tests/emu/emu.py.  It says nothing about speed, and nothing about
+// the memory model or the asynchrony of a real device: a missing fence or a race between CTAs cannot show here.
 //
 // Model: a kernel launch is a closure queued on its stream; a stream is a host thread that runs its queue
 // in order (so several "ranks" in one process overlap exactly as on a device, and their flag spin-waits
@@ -91,12 +91,15 @@ struct Block {
     std::vector<Warp> warps;
     int nthreads = 0, exited = 0;
     int bar_phase = 0, bar_arrived = 0, bar_done = 0;
+    struct Named { int phase = 0, arrived = 0, done = 0; } named[16];     // bar.sync id, n
+    void *smem = nullptr;                                                  // dynamic shared memory of this block
     const std::function<void()> *body = nullptr;
 };
 
 extern thread_local Fiber *cur;
 void yield();                                   // back to the block scheduler
-void run_grid(dim3 grid, dim3 block, const std::function<void()> &body);
+void run_grid(dim3 grid, dim3 block, size_t smem, const std::function<void()> &body);
+void *dynamic_smem();
 uint64_t now_ns();
 
 // ---- warp rendezvous: every lane in `mask` deposits `v`, all read the table once it is complete --------
@@ -144,7 +147,20 @@ inline unsigned __reduce_or_sync(unsigned mask, unsigned v)
 }
 inline long long __double_as_longlong(double d) { return emu::from_bits<long long>(emu::to_bits(d)); }
 inline double __longlong_as_double(long long v) { return emu::from_bits<double>(emu::to_bits(v)); }
-inline size_t __cvta_generic_to_shared(const void *p) { return (size_t)p; }
+// "shared-space addresses" are 32-bit in the PTX the sources use: a handle into a per-host-thread table of
+// regions (region << 24 | offset), translated back by the mbarrier / TMA stand-ins below
+size_t __cvta_generic_to_shared(const void *p);
+
+// ---- mbarrier, bulk tensor copies, named barriers: what the TMA subcycle kernel is made of -------------
+// (operands are the 32-bit shared handles above).  A copy is carried out when it is issued and then
+// completes its bytes on the barrier; waiting lanes yield until the phase they wait for has flipped.
+void emu_mbar_init(unsigned bar, unsigned count);
+void emu_mbar_arrive(unsigned bar);
+void emu_mbar_expect_tx(unsigned bar, unsigned bytes);
+unsigned emu_mbar_try_wait(unsigned bar, unsigned parity);
+struct CUtensorMap;
+void emu_tma_load(unsigned dst, const CUtensorMap *map, unsigned bar, int rank, int x, int y, int z);
+void emu_bar_sync(int id, int nthreads);
 inline void __threadfence() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 inline void __threadfence_system() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 inline void __syncwarp(unsigned mask = 0xffffffffu) { emu::rendezvous(mask, 0, false); }
@@ -242,9 +258,9 @@ enum CUtensorMapFloatOOBfill { CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE = 0 };
 namespace emu {
 void enqueue(cudaStream_t s, std::function<void()> fn);
 template <class F, class... A>
-inline void launch(dim3 grid, dim3 block, size_t /*smem*/, cudaStream_t stream, F kernel, A... args)
+inline void launch(dim3 grid, dim3 block, size_t smem, cudaStream_t stream, F kernel, A... args)
 {
     std::function<void()> body = [=]() { kernel(args...); };
-    enqueue(stream, [=]() { run_grid(grid, block, body); });
+    enqueue(stream, [=]() { run_grid(grid, block, smem, body); });
 }
 }  // namespace emu

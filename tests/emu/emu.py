@@ -5,12 +5,15 @@ compiles them with g++ against tests/emu/cuda_emu.{h,cpp}:
 
   * `#include <cuda_runtime.h>` / `<cuda.h>`            -> `#include "cuda_emu.h"`
   * `kernel<<<grid, block, smem, stream>>>(args...)`    -> `emu::launch(grid, block, smem, stream, kernel, args...)`
-  * `asm volatile("<ptx>" : outs : ins : clobbers);`    -> the host stand-in of the three instructions of the
-    cross-rank flags (st.release.sys / ld.acquire.sys / globaltimer), `emu_ptx_unavailable()` for everything
-    else (mbarrier, cp.async.bulk: the TMA kernel cannot run on a host and is never launched here)
+  * `asm volatile("<ptx>" : outs : ins : clobbers);`    -> the host stand-in of that instruction: the cross-rank
+    flags (st.release.sys / ld.acquire.sys / globaltimer) and what the TMA kernel is made of (mbarrier init /
+    arrive / expect_tx / try_wait, cp.async.bulk.tensor 2-D and 3-D with zero fill outside the tensor,
+    bar.sync id, fences); `emu_ptx_unavailable()` for anything else
+  * `extern __shared__ T x[];` -> the block's dynamic buffer; `__shared__` -> `static thread_local`
 
-Nothing else is touched: prep, halo, fold, strength, finish, the register-sweep subcycle kernel, the program
-builder, the CUDA-graph path and the multi-rank flag barrier all run from the product's own text.  The
+Nothing else is touched: prep, halo, fold, strength, finish, both subcycle kernels (the TMA ring with its
+producer warp, work queue and item list, and the register sweep), the program builder, the CUDA-graph path
+and the multi-rank flag barrier all run from the product's own text.  The
 result, tests/emu/_build/libevp_emu.so, exports the product's C ABI; `patched()` swaps it into
 cice5_b200.evp for the duration of a test.  The product never loads it: cice5_b200 has no reference to
 this directory, and a missing CUDA library is still a hard error there.
@@ -116,6 +119,22 @@ def _rewrite_asm(text: str) -> str:
             rep = f"{outs[0]} = emu_ld_acquire_u64((const void *)({ins[0]}));"
         elif "globaltimer" in template:
             rep = f"{outs[0]} = emu::now_ns();"
+        elif "mbarrier.init" in template:
+            rep = f"emu_mbar_init({ins[0]}, {ins[1]});"
+        elif "mbarrier.arrive.expect_tx" in template:
+            rep = f"emu_mbar_expect_tx({ins[0]}, {ins[1]});"
+        elif "mbarrier.arrive" in template:
+            rep = f"emu_mbar_arrive({ins[0]});"
+        elif "mbarrier.try_wait.parity" in template:
+            rep = f"{outs[0]} = emu_mbar_try_wait({ins[0]}, {ins[1]});"
+        elif "cp.async.bulk.tensor.3d" in template:
+            rep = f"emu_tma_load({ins[0]}, {ins[1]}, {ins[2]}, 3, {ins[3]}, {ins[4]}, {ins[5]});"
+        elif "cp.async.bulk.tensor.2d" in template:
+            rep = f"emu_tma_load({ins[0]}, {ins[1]}, {ins[2]}, 2, {ins[3]}, {ins[4]}, 0);"
+        elif template.startswith("bar.sync"):
+            rep = f"emu_bar_sync({template.split()[1].rstrip(',')}, {ins[0]});"
+        elif template.startswith("fence."):
+            rep = "std::atomic_thread_fence(std::memory_order_seq_cst);"
         else:
             first = template.split(";")[0].strip().replace('"', "'")[:60]
             rep = "".join(f"{o} = {{}}; " for o in outs if re.fullmatch(r"[A-Za-z_]\w*", o)) + \
@@ -128,13 +147,22 @@ def transform(text: str) -> str:
     text = re.sub(r"#include\s*<cuda_runtime\.h>|#include\s*<cuda\.h>", '#include "cuda_emu.h"', text)
     text = _LAUNCH.sub(lambda m: f"emu::launch({m.group(2)}, {m.group(1)}, ", text)
     text = _rewrite_asm(text)
-    # dynamic shared memory of the TMA kernel: a host array so that the (never executed) code compiles
-    text = re.sub(r"extern\s+__shared__\s+(.*?)(\w+)\s*\[\s*\]\s*;", r"static \1\2[1];", text)
-    text = text.replace("__shared__", "static")
+    # dynamic shared memory: the block's buffer; static shared variables: per host thread (the blocks of a
+    # launch run one after the other on their stream's thread, and shared memory starts undefined anyway)
+    text = re.sub(r"extern\s+__shared__\s+(?:__align__\(\d+\)\s+)?([\w ]+?)\s*(\w+)\s*\[\s*\]\s*;",
+                  r"\1 *\2 = (\1 *)emu::dynamic_smem();", text)
+    text = text.replace("__shared__", "static thread_local")
     return text
 
 
-def build(force: bool = False) -> str:
+def build(force: bool = False, defines=()) -> str:
+    """defines: extra -D flags (kernel variants, e.g. ("-DEVP_TMA_MERGE_UV=1",)): a separate library each."""
+    tag = "".join(re.sub(r"\W+", "_", d) for d in defines)
+    lib = LIB if not defines else LIB.replace(".so", f"{tag}.so")
+    return _build(lib, force, tuple(defines))
+
+
+def _build(LIB: str, force: bool, defines: tuple) -> str:
     srcdir = os.path.join(BUILD, "src")
     os.makedirs(srcdir, exist_ok=True)
     sources = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh")))
@@ -148,7 +176,7 @@ def build(force: bool = False) -> str:
         with open(os.path.join(srcdir, f + (".cpp" if f.endswith(".cu") else "")), "w") as fh:
             fh.write(out)
     cmd = ["g++", "-std=c++17", "-O1", "-g", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared", "-pthread",
-           "-DEVP_STRICT=1", "-w", "-I", HERE, "-I", srcdir, "-o", LIB,
+           "-DEVP_STRICT=1", *defines, "-w", "-I", HERE, "-I", srcdir, "-o", LIB,
            os.path.join(srcdir, "evp_abi.cu.cpp"), os.path.join(HERE, "cuda_emu.cpp")]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
@@ -157,12 +185,13 @@ def build(force: bool = False) -> str:
 
 
 @contextlib.contextmanager
-def patched():
-    """cice5_b200.evp bound to the host build of its own sources (sweep kernel) inside the `with` block."""
+def patched(kernel: str = "tma", defines=()):
+    """cice5_b200.evp bound to the host build of its own sources inside the `with` block;
+    kernel = "tma" (the product's default subcycle kernel) or "sweep"."""
     from cice5_b200 import evp
-    lib_path = build()
+    lib_path = build(defines=defines)
     saved_libs, saved_env = dict(evp._libs), os.environ.get("EVP_B200_KERNEL")
-    os.environ["EVP_B200_KERNEL"] = "sweep"
+    os.environ["EVP_B200_KERNEL"] = kernel
     lib = C.CDLL(lib_path)
     lib.evp_gpu_strerror.restype = C.c_char_p
     lib.evp_gpu_last_cuda_error.restype = C.c_char_p

@@ -9,8 +9,10 @@ BIT FOR BIT.  What this covers that had no hardware run yet: revised EVP, the de
 principal_stress, the velocity fold's unaveraged pole pair, the comparison with the reference-text
 vectors, tiny domains; and it re-checks on the host what the GPU suite validated: prep / halo / fold /
 finish kernels, the program builder, the CUDA-graph path, the multi-rank flag barrier, unequal slabs.
-What it cannot cover: the TMA subcycle kernel (mbarrier / cp.async.bulk PTX has no host stand-in; the
-register-sweep kernel computes the subcycles here), memory-model behaviour of a real device, speed.
+Both subcycle kernels run: the TMA ring (mbarrier and cp.async.bulk.tensor have host stand-ins: a copy is
+carried out when issued and completes its bytes on the barrier) and the register sweep.  What it cannot
+cover: the memory model and the asynchrony of a real device (a missing fence, a stage released too early
+or a race between CTAs does not show here), and speed.
 
 This is test infrastructure.  The product never loads the host build (nothing under cice5_b200/ refers
 to tests/emu/) and keeps failing loudly when its CUDA library is missing."""
@@ -26,9 +28,11 @@ from tests.test_gpu_parity import OUT_CHECK
 pytestmark = [pytest.mark.timeout(600)]
 
 
-@pytest.fixture(scope="module")
-def dev():
-    with emu.patched() as evp:
+@pytest.fixture(scope="module", params=["tma", "sweep"])
+def dev(request):
+    """cice5_b200.evp bound to the host build; every test runs with the TMA ring kernel (the product's
+    default: producer warp, mbarriers, tensor-map copies, work queue, item list) and with the register sweep."""
+    with emu.patched(kernel=request.param) as evp:
         yield evp
 
 
@@ -256,3 +260,24 @@ def test_product_loader_has_no_host_fallback():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".F90")):
                 text = open(os.path.join(root, f), errors="replace").read()
                 assert "tests/emu" not in text and "libevp_emu" not in text and "cuda_emu" not in text, f
+
+
+def test_merge_uv_variant_bitwise():
+    """-DEVP_TMA_MERGE_UV=1 (the velocities of row r0-1 ride in the first full stage of an item instead of a
+    stage of their own): written and compile-checked in round 1, never run on
+    hardware -- its first execution anywhere.  Same answers, bit for bit, 1 and 2 ranks."""
+    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
+    case = fx.make_case(grid, "full", ndte=5, dt=3600.0)
+    ref = _oracle(case)
+    with emu.patched(kernel="tma", defines=("-DEVP_TMA_MERGE_UV=1",)) as evp:
+        got = clone_case(case)
+        evp.run_case(got, strict=True)
+        compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+        got = clone_case(case)
+        g = evp.EvpGroup(case.dom, case.ndte, case.dt, 2, strict=True)
+        try:
+            g.set_grid(grid.f)
+            g.evp(case.dt, got.inp, got.io, got.out)
+        finally:
+            g.close()
+        compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
