@@ -104,6 +104,8 @@ struct evp_handle {
     cudaGraphExec_t loop_graph[2] = {nullptr, nullptr};   // per starting ping-pong parity
     int h_error = 0;
     bool use_tma = false;         // subcycle kernel v2 (TMA ring) instead of v1 (register sweep)
+    bool fold_in_kernel = false;  // EVP_B200_FOLD=kernel: tripole fold inside the TMA subcycle kernel (experiment)
+    bool shared_stream = false;   // inside evp_gpu_compute_group with more than one rank
     int sm_count = 148;
     CUtensorMap mapS, mapS2, mapT1, mapT3, mapT4, mapT10, mapU, mapU8, mapM;
     // device ice_strength (evp_gpu_upload_itd): aice0, aicen(ncat), vicen(ncat) planes of the arena's
@@ -387,6 +389,8 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
     {
         const char *kv = getenv("EVP_B200_KERNEL");          // "tma" (default) | "sweep"
         h->use_tma = !(kv && strcmp(kv, "sweep") == 0);
+        const char *fv = getenv("EVP_B200_FOLD");            // "launch" (default) | "kernel"
+        h->fold_in_kernel = fv && strcmp(fv, "kernel") == 0;
         cudaDeviceProp prop;
         CK(cudaGetDeviceProperties(&prop, cfg->device));
         h->sm_count = prop.multiProcessorCount;
@@ -763,8 +767,13 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
     // N > 1 on a tripole grid with the TMA kernel: the cross-rank barrier between the subcycle
     // kernel and the fold is fused into both -- the last CTA to finish signals the peers, the fold
     // kernel waits for theirs -- 2 launches per subcycle instead of 4
-    const bool fused_sync = h->cfg.nranks > 1 && h->use_tma && h->g.tripole;
-    B.op([h, from_parity, last, buf, ksub, fused_sync](Launcher &L) {
+    // EVP_B200_FOLD=kernel (experiment): the fold moves into the subcycle kernel as
+    // well -- 1 launch per subcycle, on one rank too
+    // (not when all ranks share one stream of one device, evp_gpu_compute_group: a kernel that waits for a
+    // peer whose kernel is queued behind it would never end)
+    const bool fold_in_kernel = h->fold_in_kernel && !h->shared_stream && h->use_tma && h->g.tripole;
+    const bool fused_sync = (h->cfg.nranks > 1 || fold_in_kernel) && h->use_tma && h->g.tripole;
+    B.op([h, from_parity, last, buf, ksub, fused_sync, fold_in_kernel](Launcher &L) {
         const Geom &g = h->g;
         LoopArgs a;
         fill_loop_args(h, from_parity, buf, a);
@@ -788,6 +797,7 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
             t.items = h->t_items;
             t.queue = h->queue(ksub - 1); t.item_list = h->item_list(); t.item_count = h->item_count();
             t.fused_signal = fused_sync ? 1 : 0;
+            t.fold_in_kernel = fold_in_kernel ? 1 : 0;
             t.done = h->done(ksub - 1); t.done_bnd = h->done_bnd(ksub - 1);
             fill_sync_args(h, t.sync);
             t.trace = h->trace(ksub - 1);
@@ -809,7 +819,7 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
         return EVP_OK;
     });
     if (!fused_sync) B.sync();
-    if (h->g.tripole) {
+    if (h->g.tripole && !fold_in_kernel) {
         B.op([h, from_parity, buf, fused_sync, ksub](Launcher &L) {
             const Geom &g = h->g;
             double *u1 = h->plane(from_parity ? S_UA : S_UB), *v1 = h->plane(from_parity ? S_VA : S_VB);
@@ -1088,6 +1098,7 @@ int evp_gpu_compute_group(evp_handle_t **hs, int n, double dt)
     for (int r = 0; r < n; ++r) {
         CK(cudaStreamSynchronize(hs[r]->stream));
         hs[r]->stream = hs[0]->own_stream;             // one shared stream
+        hs[r]->shared_stream = n > 1;
         build_program(hs[r], dt, P[r]);
         L.push_back(Launcher{hs[r]});
         if (P[r].ops.size() != P[0].ops.size()) return EVP_ERR_STATE;
@@ -1107,6 +1118,7 @@ int evp_gpu_compute_group(evp_handle_t **hs, int n, double dt)
     for (int r = 0; r < n; ++r) {
         int rc2 = (rc == EVP_OK) ? finish_compute(hs[r], P[r], L[r].n, n_after - n_before) : rc;
         hs[r]->stream = hs[r]->own_stream;
+        hs[r]->shared_stream = false;
         if (rc2 != EVP_OK) rc = rc2;
     }
     return rc;

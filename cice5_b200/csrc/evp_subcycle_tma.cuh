@@ -89,6 +89,11 @@ struct TmaArgs {
     // fused cross-rank signal: every CTA counts itself in `done` when its stores are out; the last
     // one bumps the epoch and releases it to the peers (what halo_signal_kernel does otherwise)
     int fused_signal;
+    // fold_in_kernel (EVP_B200_FOLD=kernel, off by default): the CTA that completes the boundary count
+    // -- or the last CTA when no boundary item holds ice -- also waits for the peers' signals and folds the
+    // new u, v itself, while the other CTAs work on the interior items: no fold_uv_kernel launch, one
+    // launch per subcycle, the exchange hidden behind the interior.  Implies fused_signal.
+    int fold_in_kernel;
     int *done, *done_bnd;        // finished CTAs / finished boundary items of this launch
     SyncArgs sync;
     // timing trace of this launch (EVP_B200_TRACE=1), globaltimer ns: [0] first CTA start, [1] last
@@ -158,9 +163,36 @@ __device__ __forceinline__ void metric_terms(double hte, double hte_w, double ht
     m[7] = -__dsub_rn(__dmul_rn(1.5, hte_w), __dmul_rn(0.5, hte));              // cym
 }
 
+// The tripole fold of the new velocities by the consumer warps of ONE CTA (fold_in_kernel): what
+// fold_uv_kernel does with do_wait = 1.  Every boundary item of this rank is complete and fenced (the
+// caller completed the count) and this rank's signal is out; thread r waits for peer r's signal, then the
+// columns are folded kTmaConsumers*32 at a time.  Loads bypass L1 (other SMs / peers wrote the data).
+__device__ __noinline__ void fold_by_this_cta(const TmaArgs &p, int warp, int lane)
+{
+    const LoopArgs &a = p.a;
+    const int t = warp * 32 + lane;
+    if (p.trace && t == 0) p.trace[3] = global_ns();
+    peer_wait(p.sync, t);
+    asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
+    __threadfence_system();
+    if (p.trace && t == 0) p.trace[4] = global_ns();
+    const double *inbox = a.inbox[a.rank];
+    const int ild = a.inbox_ld;
+    for (int c = t; c <= a.nxl + 1; c += kTmaConsumers * 32) {
+        int ig = a.lo + c;
+        if (ig < 1) ig += a.nx_global;
+        if (ig > a.nx_global) ig -= a.nx_global;
+        const size_t top = (size_t)a.ny * a.ld + c;
+        fold_necorner_column(a.u1, a.ld, a.ny, c, ig, a.nx_global, __ldcg(a.u1 + top), __ldcg(inbox + c),
+                             __ldcg(inbox + ild + c), -1.0, kFirstPair3D);
+        fold_necorner_column(a.v1, a.ld, a.ny, c, ig, a.nx_global, __ldcg(a.v1 + top), __ldcg(inbox + 2 * ild + c),
+                             __ldcg(inbox + 3 * ild + c), -1.0, kFirstPair3D);
+    }
+}
+
 // Consumer warps of one CTA: `n` more boundary items are complete (all their stores into peer
 // memory issued).  Fence once, count; the CTA that completes the count releases the epoch.
-__device__ __noinline__ void boundary_done(const TmaArgs &p, int *bnd_count, int warp, int lane)
+__device__ __noinline__ void boundary_done(const TmaArgs &p, int *bnd_count, int *fold_fire, int warp, int lane)
 {
     __threadfence_system();                          // my stores into peer memory are out
     asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
@@ -178,6 +210,11 @@ __device__ __noinline__ void boundary_done(const TmaArgs &p, int *bnd_count, int
             peer_signal_warp(p.sync, lane);
             if (p.trace && lane == 0) p.trace[2] = global_ns();
         }
+        if (p.fold_in_kernel && lane == 0) *fold_fire = fire;
+    }
+    if (p.fold_in_kernel) {                          // all consumer warps: did this CTA complete the count?
+        asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
+        if (*fold_fire) fold_by_this_cta(p, warp, lane);
     }
 }
 
@@ -192,6 +229,7 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
     extern __shared__ __align__(1024) unsigned char ring[];
     __shared__ unsigned long long full_bar[kTmaStages], empty_bar[kTmaStages];
     __shared__ int bnd_count;                        // boundary items taken by this CTA (thread 0 only)
+    __shared__ int fold_fire;                        // fold_in_kernel: this CTA does the fold
     const LoopArgs &a = p.a;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -309,7 +347,7 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             // this CTA has left the boundary items (they come first in the queue): count them;
             // whoever completes the count signals the peers, and the interior items of every rank
             // are computed while the signals travel
-            if (p.fused_signal) boundary_done(p, &bnd_count, warp, lane);
+            if (p.fused_signal) boundary_done(p, &bnd_count, &fold_fire, warp, lane);
             in_bnd = false;
         }
         if (item_tag < 0) break;
@@ -522,6 +560,11 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                 peer_signal_warp(p.sync, lane);
                 if (p.trace && lane == 0) p.trace[2] = global_ns();
             }
+            if (p.fold_in_kernel && lane == 0) fold_fire = last && p.item_count[1] == 0;
+        }
+        if (p.fold_in_kernel) {
+            asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
+            if (fold_fire) fold_by_this_cta(p, warp, lane);
         }
     }
 }

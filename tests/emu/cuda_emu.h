@@ -138,6 +138,8 @@ template <class T> inline T __shfl_down_sync(unsigned mask, T v, unsigned delta)
     return src > 31 ? v : emu::from_bits<T>(e.slot[src]);
 }
 inline int __popc(unsigned x) { return __builtin_popcount(x); }
+template <class T> inline T __ldcg(const T *p) { return *(const volatile T *)p; }
+template <class T> inline T __ldg(const T *p) { return *p; }
 inline unsigned __reduce_or_sync(unsigned mask, unsigned v)
 {
     emu::Exchange e = emu::rendezvous(mask, v, false);

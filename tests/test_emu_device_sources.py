@@ -281,3 +281,88 @@ def test_merge_uv_variant_bitwise():
         finally:
             g.close()
         compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+
+
+def _compute_on_threads(ranks, dt):
+    """One host thread per rank, each on its own stream -- the in-process picture of one process per GPU
+    (evp_gpu_compute_group puts all ranks on ONE stream of one device, where a kernel that waits for a peer
+    queued behind it can never end; there the fold stays a launch of its own)."""
+    import threading
+    errors = []
+
+    def run(e):
+        try:
+            e.compute(dt)
+        except Exception as ex:                      # noqa: BLE001
+            errors.append(ex)
+
+    threads = [threading.Thread(target=run, args=(e,)) for e in ranks]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    if errors:
+        raise errors[0]
+
+
+@pytest.mark.parametrize("nranks,threads", [(1, False), (2, True), (4, True), (2, False)])
+def test_fold_in_kernel_variant_bitwise(monkeypatch, nranks, threads):
+    """EVP_B200_FOLD=kernel: the CTA that completes the boundary count waits for the
+    peers and folds the new velocities itself -- one launch per subcycle instead of two.  Same answers bit for
+    bit on 1, 2 and 4 ranks, two calls, wet poles; and the launch count really drops.  (2, False): through
+    evp_gpu_compute_group, where the option must switch itself off.)"""
+    monkeypatch.setenv("EVP_B200_FOLD", "kernel")
+    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
+    case = fx.make_case(grid, "full", ndte=5, dt=3600.0)
+    ref, got = clone_case(case), clone_case(case)
+    with emu.patched(kernel="tma") as evp:
+        if threads:
+            monkeypatch.setattr(evp, "compute_group", _compute_on_threads)
+        g = evp.EvpGroup(case.dom, case.ndte, case.dt, nranks, strict=True)
+        try:
+            g.set_grid(grid.f)
+            for _ in range(2):
+                ref.out, got.out = fx.zeroed_outputs(case.dom), fx.zeroed_outputs(case.dom)
+                orc.run_case(ref)
+                stats = g.evp(case.dt, got.inp, got.io, got.out)
+                compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+            per_subcycle = 1 if (threads or nranks == 1) else 2
+            assert all(s.loop_kernel_launches == per_subcycle * case.ndte for s in stats)
+        finally:
+            g.close()
+
+
+def test_fold_in_kernel_when_no_boundary_item_holds_ice(monkeypatch):
+    """Ice in the south only: no boundary item, the last CTA of the launch signals and folds."""
+    monkeypatch.setenv("EVP_B200_FOLD", "kernel")
+    grid = fx.synthetic_tripole(96, 40)
+    case = fx.make_case(grid, "caps", ndte=4, dt=3600.0)
+    for k in ("aice", "vice", "vsno", "aice_init"):
+        case.inp[k][20:, :] = 0.0                       # no ice in the northern half
+    ref, got = clone_case(case), clone_case(case)
+    orc.run_case(ref)
+    assert np.abs(phys(ref.io["uvel"])).max() > 0.0
+    with emu.patched(kernel="tma") as evp:
+        evp.run_case(got, strict=True)
+    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+
+
+def test_ranks_on_threads_default_path(monkeypatch):
+    """The default multi-rank path (last CTA signals, fold_uv_kernel waits) with one thread and one stream per
+    rank, i.e. with the ranks really overlapping, as one process per GPU does."""
+    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
+    case = fx.make_case(grid, "full", ndte=5, dt=3600.0)
+    ref, got = clone_case(case), clone_case(case)
+    with emu.patched(kernel="tma") as evp:
+        monkeypatch.setattr(evp, "compute_group", _compute_on_threads)
+        g = evp.EvpGroup(case.dom, case.ndte, case.dt, 4, strict=True)
+        try:
+            g.set_grid(grid.f)
+            for _ in range(2):
+                ref.out, got.out = fx.zeroed_outputs(case.dom), fx.zeroed_outputs(case.dom)
+                orc.run_case(ref)
+                stats = g.evp(case.dt, got.inp, got.io, got.out)
+                compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+            assert all(s.loop_kernel_launches == 2 * case.ndte for s in stats)
+        finally:
+            g.close()

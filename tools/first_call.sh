@@ -36,6 +36,9 @@ for v in mergeuv; do
   EVP_B200_LIB=$lib run parity_$v 400 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "tp1 or tripole or gx3"
   EVP_B200_LIB=$lib run bench_$v 300 python bench.py --no-cpu-baseline --no-e2e
 done
+# 4b. the in-kernel tripole fold (EVP_B200_FOLD=kernel, one launch per subcycle): parity, then the bench
+EVP_B200_FOLD=kernel run parity_foldkernel 400 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "tp1 or tripole"
+EVP_B200_FOLD=kernel run bench_foldkernel 300 python bench.py --no-cpu-baseline --no-e2e
 # 5. launch list of the default bench (the kernel's share of the step), never a bench value
 run ncu_launches 400 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv \
     --log-file "$O.launches.csv" python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e
