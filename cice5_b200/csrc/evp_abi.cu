@@ -100,6 +100,13 @@ struct evp_handle {
     int parity = 0;               // which ping-pong copy holds the current state (0 = A)
     int halo_seq = 0;             // halo operations issued in this compute (inbox buffer = seq & 1)
     cudaStream_t stream = nullptr, own_stream = nullptr;
+    // EVP_B200_EARLY_D2H=1 (experiment): evp_gpu_run copies the outputs that are
+    // final before the subcycle loop back on a second stream while the loop runs
+    cudaStream_t copy_stream = nullptr;
+    bool early_d2h = false;
+    evp_inout_t *early_io = nullptr;   // set by evp_gpu_run for the duration of its compute
+    evp_out_t *early_out = nullptr;
+    bool early_issued = false;         // the early copies of this call are on copy_stream
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaGraphExec_t loop_graph[2] = {nullptr, nullptr};   // per starting ping-pong parity
     int h_error = 0;
@@ -384,6 +391,11 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
     CK(cudaMemset(h->arena, 0, h->arena_bytes));
     CK(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
     h->stream = h->own_stream;
+    {
+        const char *ev = getenv("EVP_B200_EARLY_D2H");
+        h->early_d2h = ev && strcmp(ev, "1") == 0;
+        if (h->early_d2h) CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    }
     for (auto &ev : h->ev) CK(cudaEventCreate(&ev));
     memset(&h->stats, 0, sizeof(h->stats));
     {
@@ -411,6 +423,7 @@ int evp_gpu_finalize(evp_handle_t *h)
     for (int r = 0; r < kMaxRanks; ++r)
         if (h->peer_opened[r]) cudaIpcCloseMemHandle(h->peer_arena[r]);
     for (auto &ev : h->ev) if (ev) cudaEventDestroy(ev);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     if (h->itd) cudaFree(h->itd);
     if (h->arena) cudaFree(h->arena);
@@ -440,18 +453,18 @@ static int h2d_i(evp_handle *h, int p, const int *src)
                          (size_t)h->nxb * sizeof(int), h->nyb, cudaMemcpyHostToDevice, h->stream));
     return EVP_OK;
 }
-static int d2h_i(evp_handle *h, int p, int *dst)
+static int d2h_i(evp_handle *h, int p, int *dst, cudaStream_t s = nullptr)
 {
     if (!dst) return EVP_OK;
     CK(cudaMemcpy2DAsync(dst, (size_t)h->nxb * sizeof(int), h->iplane(p), (size_t)h->ld * sizeof(int),
-                         (size_t)h->nxb * sizeof(int), h->nyb, cudaMemcpyDeviceToHost, h->stream));
+                         (size_t)h->nxb * sizeof(int), h->nyb, cudaMemcpyDeviceToHost, s ? s : h->stream));
     return EVP_OK;
 }
-static int d2h(evp_handle *h, int p, double *dst)
+static int d2h(evp_handle *h, int p, double *dst, cudaStream_t s = nullptr)
 {
     if (!dst) return EVP_OK;
     CK(cudaMemcpy2DAsync(dst, (size_t)h->nxb * sizeof(double), h->plane(p), (size_t)h->ld * sizeof(double),
-                         (size_t)h->nxb * sizeof(double), h->nyb, cudaMemcpyDeviceToHost, h->stream));
+                         (size_t)h->nxb * sizeof(double), h->nyb, cudaMemcpyDeviceToHost, s ? s : h->stream));
     return EVP_OK;
 }
 #define TRY(x) do { int rc_ = (x); if (rc_ != EVP_OK) return rc_; } while (0)
@@ -568,11 +581,38 @@ int evp_gpu_upload_itd(evp_handle_t *h, const evp_itd_t *itd)
     return EVP_OK;
 }
 
+// outputs O_STRAIRX + p that no kernel touches after evp_prep2 (ice_dyn_evp.F90:240-310): strairx, strairy,
+// strtltx, strtlty, uvel_init, vvel_init; likewise fm, iceumask, tmass and strength (after its halo update)
+static const bool kFinalBeforeLoop[17] = {true, true, true, true, false, false, false, false, false, false,
+                                          false, false, false, false, false, true, true};
+
+// EVP_B200_EARLY_D2H: called by evp_gpu_compute once every launch of the call is enqueued.  The copies wait
+// on the event that closes the prep phase and then run on copy_stream beside the subcycle loop.
+static int issue_early_d2h(evp_handle *h)
+{
+    evp_inout_t *io = h->early_io;
+    evp_out_t *out = h->early_out;
+    if (!h->early_d2h || !io || !out || h->shared_stream) return EVP_OK;
+    cudaStream_t s = h->copy_stream;
+    CK(cudaStreamWaitEvent(s, h->ev[1], 0));
+    double *dst[17] = {out->strairx, out->strairy, out->strtltx, out->strtlty, nullptr, nullptr, nullptr, nullptr,
+                       nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, out->uvel_init, out->vvel_init};
+    h->early_issued = true;
+    for (int p = 0; p < 17; ++p)
+        if (kFinalBeforeLoop[p]) TRY(d2h(h, O_STRAIRX + p, dst[p], s));
+    TRY(d2h(h, W_TMASS, out->tmass, s));
+    TRY(d2h(h, W_STRENGTH, out->strength, s));
+    TRY(d2h(h, S_FM, io->fm, s));
+    TRY(d2h_i(h, 2, io->iceumask, s));
+    return EVP_OK;
+}
+
 int evp_gpu_download(evp_handle_t *h, evp_inout_t *io, evp_out_t *out)
 {
     if (!h) return EVP_ERR_ARG;
     if (!h->uploaded) return EVP_ERR_STATE;
     CK(cudaSetDevice(h->cfg.device));
+    const bool early = h->early_issued && io == h->early_io && out == h->early_out;   // those are on their way
     if (io) {
         const int U = h->parity ? S_UB : S_UA, V = h->parity ? S_VB : S_VA;
         const int S = h->parity ? S_STRB : S_STRA;
@@ -583,19 +623,28 @@ int evp_gpu_download(evp_handle_t *h, evp_inout_t *io, evp_out_t *out)
             TRY(d2h(h, S + 4 + c, io->stressm[c]));
             TRY(d2h(h, S + 8 + c, io->stress12[c]));
         }
-        TRY(d2h(h, S_FM, io->fm));
-        TRY(d2h_i(h, 2, io->iceumask));
+        if (!early) {
+            TRY(d2h(h, S_FM, io->fm));
+            TRY(d2h_i(h, 2, io->iceumask));
+        }
     }
     if (out) {
         double *dst[17] = {out->strairx, out->strairy, out->strtltx, out->strtlty, out->strocnx, out->strocny,
                            out->strintx, out->strinty, out->strocnxT, out->strocnyT, out->divu, out->shear,
                            out->rdg_conv, out->rdg_shear, out->prs_sig, out->uvel_init, out->vvel_init};
-        for (int p = 0; p < 17; ++p) TRY(d2h(h, O_STRAIRX + p, dst[p]));
-        TRY(d2h(h, W_TMASS, out->tmass));
-        TRY(d2h(h, W_STRENGTH, out->strength));
+        for (int p = 0; p < 17; ++p)
+            if (!(early && kFinalBeforeLoop[p])) TRY(d2h(h, O_STRAIRX + p, dst[p]));
+        if (!early) {
+            TRY(d2h(h, W_TMASS, out->tmass));
+            TRY(d2h(h, W_STRENGTH, out->strength));
+        }
         TRY(d2h_i(h, 3, out->icetmask));
     }
     CK(cudaStreamSynchronize(h->stream));
+    if (early) {
+        CK(cudaStreamSynchronize(h->copy_stream));
+        h->early_issued = false;
+    }
     return EVP_OK;
 }
 
@@ -1075,6 +1124,10 @@ int evp_gpu_compute(evp_handle_t *h, double dt)
     long long n_loop = 0;
     TRY(exec_range(L, P, 0, P.loop_begin));
     TRY(exec_loop(L, P, n_loop));
+    // once the loop is enqueued: a copy into pageable memory blocks this thread, but beside the running loop;
+    // and before the finish phase, whose last step (the counters, 16 bytes into the pageable handle) blocks
+    // until the whole call is through
+    TRY(issue_early_d2h(h));
     TRY(exec_range(L, P, P.loop_end, P.ops.size()));
     CK(cudaGetLastError());
     return finish_compute(h, P, L.n, n_loop);
@@ -1128,9 +1181,19 @@ int evp_gpu_run(evp_handle_t *h, double dt, const evp_in_t *in, evp_inout_t *io,
 {
     if (!h || !in || !io) return EVP_ERR_ARG;
     TRY(evp_gpu_upload(h, in, io));
-    TRY(evp_gpu_compute(h, dt));
-    TRY(evp_gpu_download(h, io, out));
-    return EVP_OK;
+    h->early_io = io; h->early_out = out; h->early_issued = false;
+    const int rc = evp_gpu_compute(h, dt);
+    h->early_io = nullptr; h->early_out = nullptr;
+    if (rc != EVP_OK) {
+        if (h->early_issued) { cudaStreamSynchronize(h->copy_stream); h->early_issued = false; }
+        return rc;
+    }
+    const bool early = h->early_issued;
+    h->early_io = io; h->early_out = out;            // lets download recognise the buffers of this call
+    const int rc2 = evp_gpu_download(h, io, out);
+    h->early_io = nullptr; h->early_out = nullptr;
+    (void)early;
+    return rc2;
 }
 
 int evp_gpu_principal_stress(evp_handle_t *h, double *sig1, double *sig2)

@@ -336,7 +336,7 @@ struct Stream {
     }
 };
 
-struct Event { uint64_t t = 0; };
+struct Event { uint64_t t = 0; std::atomic<uint64_t> issued{0}, done{0}; };
 struct Graph { std::vector<std::function<void()>> nodes; };
 
 static std::mutex g_streams_m;
@@ -462,7 +462,14 @@ cudaError_t cudaEventCreate(cudaEvent_t *e) { *e = new emu::Event; return cudaSu
 cudaError_t cudaEventDestroy(cudaEvent_t e) { delete e; return cudaSuccess; }
 cudaError_t cudaEventRecord(cudaEvent_t e, cudaStream_t s)
 {
-    emu::enqueue(s, [e] { e->t = emu::now_ns(); });
+    const uint64_t g = ++e->issued;
+    emu::enqueue(s, [e, g] { e->t = emu::now_ns(); e->done.store(g, std::memory_order_release); });
+    return cudaSuccess;
+}
+cudaError_t cudaStreamWaitEvent(cudaStream_t s, cudaEvent_t e, unsigned)
+{
+    const uint64_t g = e->issued.load();         // the most recent record at the time of this call
+    emu::enqueue(s, [e, g] { while (e->done.load(std::memory_order_acquire) < g) std::this_thread::yield(); });
     return cudaSuccess;
 }
 cudaError_t cudaEventElapsedTime(float *ms, cudaEvent_t a, cudaEvent_t b)

@@ -237,6 +237,7 @@ cudaError_t cudaEventCreate(cudaEvent_t *);
 cudaError_t cudaEventDestroy(cudaEvent_t);
 cudaError_t cudaEventRecord(cudaEvent_t, cudaStream_t = nullptr);
 cudaError_t cudaEventElapsedTime(float *, cudaEvent_t, cudaEvent_t);
+cudaError_t cudaStreamWaitEvent(cudaStream_t, cudaEvent_t, unsigned = 0);
 cudaError_t cudaIpcGetMemHandle(cudaIpcMemHandle_t *, void *);
 cudaError_t cudaIpcOpenMemHandle(void **, cudaIpcMemHandle_t, unsigned);
 cudaError_t cudaIpcCloseMemHandle(void *);

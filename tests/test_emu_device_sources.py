@@ -366,3 +366,31 @@ def test_ranks_on_threads_default_path(monkeypatch):
             assert all(s.loop_kernel_launches == 2 * case.ndte for s in stats)
         finally:
             g.close()
+
+
+@pytest.mark.parametrize("kernel", ["tma", "sweep"])
+def test_early_download_variant_bitwise(monkeypatch, kernel):
+    """EVP_B200_EARLY_D2H=1: evp_gpu_run copies the ten outputs that are final
+    before the subcycle loop back on a second stream while the loop runs.  Streams are threads here, so a copy
+    that did not wait for the prep phase, or a download that did not wait for the copy stream, would read
+    unfinished planes.  Three calls on one handle, same buffers and fresh buffers."""
+    monkeypatch.setenv("EVP_B200_EARLY_D2H", "1")
+    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
+    case = fx.make_case(grid, "full", ndte=6, dt=3600.0)
+    ref, got = clone_case(case), clone_case(case)
+    with emu.patched(kernel=kernel) as evp:
+        e = evp.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True)
+        try:
+            e.set_grid(grid.f)
+            for call in range(3):
+                ref.out = fx.zeroed_outputs(case.dom)
+                got.out = {k: np.full_like(v, -12345) for k, v in fx.zeroed_outputs(case.dom).items()}
+                if call == 2:                                   # other buffers: nothing may be cached by address
+                    got.io = {k: v.copy() for k, v in got.io.items()}
+                orc.run_case(ref)
+                e.evp(case.dt, got.inp, got.io, got.out)
+                compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+                for k in ("strairx", "strtltx", "uvel_init", "tmass", "strength_out"):
+                    assert np.array_equal(got.out[k], ref.out[k]), k      # ghost cells included
+        finally:
+            e.close()

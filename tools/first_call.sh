@@ -39,6 +39,9 @@ done
 # 4b. the in-kernel tripole fold (EVP_B200_FOLD=kernel, one launch per subcycle): parity, then the bench
 EVP_B200_FOLD=kernel run parity_foldkernel 400 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "tp1 or tripole"
 EVP_B200_FOLD=kernel run bench_foldkernel 300 python bench.py --no-cpu-baseline --no-e2e
+# 4c. early download of the outputs that are final before the loop (EVP_B200_EARLY_D2H=1): parity, then e2e
+EVP_B200_EARLY_D2H=1 run parity_earlyd2h 400 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "gx3 or tp1"
+EVP_B200_EARLY_D2H=1 run bench_earlyd2h 300 python bench.py --no-cpu-baseline
 # 5. launch list of the default bench (the kernel's share of the step), never a bench value
 run ncu_launches 400 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv \
     --log-file "$O.launches.csv" python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e
