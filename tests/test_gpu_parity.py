@@ -145,8 +145,8 @@ def test_tilt_and_turning_angle_options():
 def test_rejects_unsupported_configs():
     with pytest.raises(evp.EvpError):
         evp.EvpGpu(100, 116, 120, 3600.0, kdyn=2)
-    with pytest.raises(evp.EvpError):
-        evp.EvpGpu(100, 116, 120, 3600.0, revised_evp=True)
+    with pytest.raises(evp.EvpError):                 # revised EVP on a split domain needs the global xmin
+        evp.EvpGpu(100, 116, 120, 3600.0, revised_evp=True, rank=0, nranks=2)
     with pytest.raises(evp.EvpError):
         evp.EvpGpu(100, 116, 120, 3600.0, device=99)
 
