@@ -15,8 +15,6 @@ uint64_t now_ns()
 }
 
 // ---- fibers ------------------------------------------------------------------------------------------
-static const size_t kStack = 256 * 1024;
-
 void yield()
 {
     Fiber *f = cur;
@@ -34,20 +32,15 @@ static void fiber_main()
     swapcontext(&f->ctx, &f->block->sched);     // never resumed
 }
 
-// stacks are kept per host thread and reused from launch to launch
-static thread_local std::vector<void *> stack_pool;
+// stacks are kept per host thread and reused from launch to launch: one set per resident block
+static const int kResident = 16;
+static const size_t kStack = 96 * 1024;
+static thread_local std::vector<void *> stack_pool[kResident];
 
 // ---- 32-bit "shared" handles -----------------------------------------------------------------------------
 struct Region { uintptr_t base; };
 static thread_local std::vector<Region> regions;
 static const uintptr_t kRegionSpan = (uintptr_t)1 << 24;
-
-static void shared_regions_reset(void *smem, size_t bytes)
-{
-    regions.clear();
-    if (smem)
-        for (uintptr_t b = (uintptr_t)smem; b < (uintptr_t)smem + bytes; b += kRegionSpan) regions.push_back(Region{b});
-}
 
 static void *from_handle(unsigned h)
 {
@@ -56,20 +49,23 @@ static void *from_handle(unsigned h)
     return (void *)(regions[r].base + (h & 0xFFFFFFu));
 }
 
-static void run_block(dim3 grid, dim3 block, uint3 bid, size_t smem, const std::function<void()> &body)
+static Block *make_block(dim3 grid, dim3 block, uint3 bid, size_t smem, const std::function<void()> &body, int slot)
 {
-    Block b;
+    Block *bp = new Block;
+    Block &b = *bp;
     b.nthreads = (int)(block.x * block.y * block.z);
     b.body = &body;
+    b.slot = slot;
     b.fibers.resize(b.nthreads);
     b.warps.resize((b.nthreads + 31) / 32);
-    while ((int)stack_pool.size() < b.nthreads) stack_pool.push_back(malloc(kStack));
+    std::vector<void *> &pool = stack_pool[slot];
+    while ((int)pool.size() < b.nthreads) pool.push_back(malloc(kStack));
     for (int t = 0; t < b.nthreads; ++t) {
         Fiber &f = b.fibers[t];
         f.tid = uint3{(unsigned)(t % block.x), (unsigned)((t / block.x) % block.y), (unsigned)(t / (block.x * block.y))};
         f.bid = bid; f.bdim = block; f.gdim = grid;
         f.block = &b; f.warp = &b.warps[t / 32]; f.lane = t % 32;
-        f.stack = stack_pool[t];
+        f.stack = pool[t];
         getcontext(&f.ctx);
         f.ctx.uc_stack.ss_sp = f.stack;
         f.ctx.uc_stack.ss_size = kStack;
@@ -80,44 +76,84 @@ static void run_block(dim3 grid, dim3 block, uint3 bid, size_t smem, const std::
         const int n = b.nthreads - (int)w * 32;
         b.warps[w].lanes = n > 32 ? 32 : n;
     }
-    void *smem_raw = nullptr;
     if (smem) {
-        if (posix_memalign(&smem_raw, 1024, smem)) abort();
-        memset(smem_raw, 0xFF, smem);
-        b.smem = smem_raw;
+        if (posix_memalign(&b.smem, 1024, smem)) abort();
+        memset(b.smem, 0xFF, smem);
+        for (uintptr_t a = (uintptr_t)b.smem; a < (uintptr_t)b.smem + smem; a += kRegionSpan) regions.push_back(Region{a});
     }
-    shared_regions_reset(smem_raw, smem);
-    Block *saved_block = cur_block;
-    Fiber *saved = cur;
-    cur_block = &b;
-    long long idle_rounds = 0;
-    while (b.exited < b.nthreads) {
-        const int before = b.exited;
-        for (int t = 0; t < b.nthreads; ++t) {
-            Fiber &f = b.fibers[t];
-            if (f.finished) continue;
-            cur = &f;
-            swapcontext(&b.sched, &f.ctx);
-        }
-        if (b.exited == before) {
-            if (++idle_rounds > 200000000LL) { fprintf(stderr, "cuda_emu: block makes no progress (deadlocked collective?)\n"); abort(); }
-        } else {
-            idle_rounds = 0;
-        }
+    return bp;
+}
+
+static void free_block(Block *b)
+{
+    free(b->smem);
+    for (auto &s : b->statics) free(s.second);
+    delete b;
+}
+
+// one turn: every live fiber of the block runs until it yields or returns
+static void turn(Block &b)
+{
+    for (int t = 0; t < b.nthreads; ++t) {
+        Fiber &f = b.fibers[t];
+        if (f.finished) continue;
+        cur = &f;
+        swapcontext(&b.sched, &f.ctx);
     }
-    cur = saved;
-    cur_block = saved_block;
-    free(smem_raw);
 }
 
 void run_grid(dim3 grid, dim3 block, size_t smem, const std::function<void()> &body)
 {
-    for (unsigned z = 0; z < grid.z; ++z)
-        for (unsigned y = 0; y < grid.y; ++y)
-            for (unsigned x = 0; x < grid.x; ++x) run_block(grid, block, uint3{x, y, z}, smem, body);
+    Fiber *saved = cur;
+    regions.clear();
+    const unsigned long long total = (unsigned long long)grid.x * grid.y * grid.z;
+    unsigned long long next = 0;
+    Block *resident[kResident] = {nullptr};
+    int live = 0;
+    long long idle_rounds = 0;
+    auto admit = [&](int slot) {
+        const unsigned x = (unsigned)(next % grid.x), y = (unsigned)((next / grid.x) % grid.y),
+                       z = (unsigned)(next / ((unsigned long long)grid.x * grid.y));
+        ++next;
+        resident[slot] = make_block(grid, block, uint3{x, y, z}, smem, body, slot);
+        ++live;
+    };
+    for (int s = 0; s < kResident && next < total; ++s) admit(s);
+    while (live > 0) {
+        bool progress = false;
+        for (int s = 0; s < kResident; ++s) {
+            Block *b = resident[s];
+            if (!b) continue;
+            const int before = b->exited;
+            turn(*b);
+            if (b->exited != before) progress = true;
+            if (b->exited == b->nthreads) {
+                free_block(b);
+                resident[s] = nullptr;
+                --live;
+                progress = true;
+                if (next < total) admit(s);
+            }
+        }
+        if (progress) idle_rounds = 0;
+        else if (++idle_rounds > 50000000LL) { fprintf(stderr, "cuda_emu: grid makes no progress (deadlocked collective?)\n"); abort(); }
+    }
+    cur = saved;
 }
 
 void *dynamic_smem() { return cur->block->smem; }
+
+void *block_static(int id, size_t bytes)
+{
+    Block *b = cur->block;
+    for (auto &s : b->statics)
+        if (s.first == id) return s.second;
+    void *p = nullptr;
+    if (posix_memalign(&p, 64, bytes ? bytes : 1)) abort();
+    memset(p, 0xFF, bytes);                      // shared memory starts undefined
+    b->statics.emplace_back(id, p);
+    return p;
+}
 
 // ---- collectives ---------------------------------------------------------------------------------------
 Exchange rendezvous(unsigned mask, uint64_t v, bool pred)

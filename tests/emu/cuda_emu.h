@@ -10,7 +10,9 @@
 //
 // Model: a kernel launch is a closure queued on its stream; a stream is a host thread that runs its queue
 // in order (so several "ranks" in one process overlap exactly as on a device, and their flag spin-waits
-// make progress).  Inside a launch the blocks run one after the other; the threads of a block are
+// make progress).  Inside a launch up to 16 blocks are resident at a time and take turns (a block that
+// ends makes room for the next one of the grid), so the work queue, the counters and the "last block" logic
+// of a persistent grid see several CTAs in flight; the threads of a block are
 // ucontext fibers scheduled round-robin, switching only at __syncthreads and at warp collectives
 // (__shfl_*_sync, __ballot_sync, __activemask), which are implemented as rendezvous of the lanes named in
 // the mask.  Divergence is not modelled: __activemask() is a rendezvous of the lanes of the warp that have
@@ -93,6 +95,8 @@ struct Block {
     int bar_phase = 0, bar_arrived = 0, bar_done = 0;
     struct Named { int phase = 0, arrived = 0, done = 0; } named[16];     // bar.sync id, n
     void *smem = nullptr;                                                  // dynamic shared memory of this block
+    std::vector<std::pair<int, void *>> statics;                           // `__shared__` variables, by declaration
+    int slot = 0;                                                          // which set of fiber stacks it uses
     const std::function<void()> *body = nullptr;
 };
 
@@ -100,6 +104,7 @@ extern thread_local Fiber *cur;
 void yield();                                   // back to the block scheduler
 void run_grid(dim3 grid, dim3 block, size_t smem, const std::function<void()> &body);
 void *dynamic_smem();
+void *block_static(int id, size_t bytes);         // storage of one `__shared__` declaration, per block
 uint64_t now_ns();
 
 // ---- warp rendezvous: every lane in `mask` deposits `v`, all read the table once it is complete --------

@@ -9,7 +9,7 @@ compiles them with g++ against tests/emu/cuda_emu.{h,cpp}:
     flags (st.release.sys / ld.acquire.sys / globaltimer) and what the TMA kernel is made of (mbarrier init /
     arrive / expect_tx / try_wait, cp.async.bulk.tensor 2-D and 3-D with zero fill outside the tensor,
     bar.sync id, fences); `emu_ptx_unavailable()` for anything else
-  * `extern __shared__ T x[];` -> the block's dynamic buffer; `__shared__` -> `static thread_local`
+  * `extern __shared__ T x[];` -> the block's dynamic buffer; `__shared__ T x[N];` -> per-block storage
 
 Nothing else is touched: prep, halo, fold, strength, finish, both subcycle kernels (the TMA ring with its
 producer warp, work queue and item list, and the register sweep), the program builder, the CUDA-graph path
@@ -143,6 +143,24 @@ def _rewrite_asm(text: str) -> str:
         i = end
 
 
+_SHARED = re.compile(r"^([ \t]*)__shared__\s+(?:__align__\(\d+\)\s+)?([A-Za-z_][\w ]*?)\s+([A-Za-z_]\w*\s*(?:\[[^;]*)?);",
+                     re.M)
+_shared_ids = [0]
+
+
+def _shared_decl(m) -> str:
+    """`__shared__ T a[N], b;` -> references into per-block storage (several blocks are resident at a time)."""
+    indent, typ, decls = m.group(1), m.group(2).strip(), m.group(3)
+    out = []
+    for d in [x.strip() for x in re.split(r",(?![^\[]*\])", decls)]:
+        dm = re.match(r"^([A-Za-z_]\w*)\s*((?:\[[^\]]*\])*)$", d)
+        name, dims = dm.group(1), dm.group(2)
+        _shared_ids[0] += 1
+        out.append(f"{indent}auto &{name} = *reinterpret_cast<{typ} (*){dims}>(emu::block_static({_shared_ids[0]}, "
+                   f"sizeof({typ}{dims})));")
+    return "\n".join(out)
+
+
 def transform(text: str) -> str:
     text = re.sub(r"#include\s*<cuda_runtime\.h>|#include\s*<cuda\.h>", '#include "cuda_emu.h"', text)
     text = _LAUNCH.sub(lambda m: f"emu::launch({m.group(2)}, {m.group(1)}, ", text)
@@ -151,7 +169,8 @@ def transform(text: str) -> str:
     # launch run one after the other on their stream's thread, and shared memory starts undefined anyway)
     text = re.sub(r"extern\s+__shared__\s+(?:__align__\(\d+\)\s+)?([\w ]+?)\s*(\w+)\s*\[\s*\]\s*;",
                   r"\1 *\2 = (\1 *)emu::dynamic_smem();", text)
-    text = text.replace("__shared__", "static thread_local")
+    text = _SHARED.sub(_shared_decl, text)
+    assert "__shared__" not in text
     return text
 
 

@@ -394,3 +394,28 @@ def test_early_download_variant_bitwise(monkeypatch, kernel):
                     assert np.array_equal(got.out[k], ref.out[k]), k      # ghost cells included
         finally:
             e.close()
+
+
+def test_plain_c_host_example_on_the_host_build(tmp_path):
+    """examples/evp_host.c (init -> set_grid -> run -> get_stats -> finalize from C99, no Python in the
+    loop) linked against the host build: the numbers the oracle gives for that closed basin."""
+    import os
+    import re
+    import shutil
+    import subprocess
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if cc is None:
+        pytest.skip("no C compiler")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib = emu.build()
+    exe = str(tmp_path / "evp_host_emu")
+    r = subprocess.run([cc, "-O2", "-std=c99", "-Wall", "-I", os.path.join(root, "include"),
+                        os.path.join(root, "examples", "evp_host.c"), "-L", os.path.dirname(lib), "-levp_emu",
+                        f"-Wl,-rpath,{os.path.dirname(lib)}", "-lm", "-o", exe], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    m = re.search(r"uvel = (\S+)\s+vvel = (\S+)", r.stdout)
+    u, v = float(m.group(1)), float(m.group(2))
+    assert abs(u - 1.154007e-01) <= 2e-6 * 1.154007e-01 and abs(v + 2.511930e-02) <= 2e-6 * 2.511930e-02
+    assert "5828 active T cells" in r.stdout
