@@ -1188,11 +1188,9 @@ int evp_gpu_run(evp_handle_t *h, double dt, const evp_in_t *in, evp_inout_t *io,
         if (h->early_issued) { cudaStreamSynchronize(h->copy_stream); h->early_issued = false; }
         return rc;
     }
-    const bool early = h->early_issued;
     h->early_io = io; h->early_out = out;            // lets download recognise the buffers of this call
     const int rc2 = evp_gpu_download(h, io, out);
     h->early_io = nullptr; h->early_out = nullptr;
-    (void)early;
     return rc2;
 }
 

@@ -58,6 +58,11 @@ constexpr unsigned kMetaState = 1u, kMetaCompact = 2u, kMetaTinyFromMetrics = 4u
 #define EVP_TMA_MERGE_UV 0
 #endif
 constexpr bool kMergeUv = EVP_TMA_MERGE_UV != 0;
+// EVP_TMA_STATIC_FIRST = 1 (experiment, not yet run on hardware, off by default): see the producer loop
+#ifndef EVP_TMA_STATIC_FIRST
+#define EVP_TMA_STATIC_FIRST 0
+#endif
+constexpr bool kStaticFirst = EVP_TMA_STATIC_FIRST != 0;
 // EVP_TMA_ITEMTRACE = 1 (diagnosis builds only): every 16th CTA of the LAST-subcycle launch prints one
 // line per work item -- "ITEM cta item rows t_start t_end" in globaltimer ns relative to the CTA's
 // start -- so that the per-CTA timeline of a launch can be reconstructed (who waits for what at N = 8).
@@ -249,8 +254,14 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
         // ------------------------------ producer ------------------------------
         if (lane == 0) {
             const int nitems = p.item_count[0], nbnd = p.item_count[1];
+            bool first_item = true;
             for (;;) {
-                const int q = atomicAdd(p.queue, 1);
+                // EVP_TMA_STATIC_FIRST: the first item of a CTA is its own index in the list (the list starts
+                // with the boundary items, heaviest first), the queue hands out the rest -- one atomic round
+                // trip less before the first TMA of every launch
+                const int q = (kStaticFirst && first_item) ? (int)blockIdx.x
+                                                           : (kStaticFirst ? (int)gridDim.x : 0) + atomicAdd(p.queue, 1);
+                first_item = false;
                 if (q >= nitems) {                                      // queue drained: tell the consumers
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
                     unsigned char *mk = ring + (size_t)stage * kStageBytes + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8;

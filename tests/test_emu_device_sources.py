@@ -262,6 +262,31 @@ def test_product_loader_has_no_host_fallback():
                 assert "tests/emu" not in text and "libevp_emu" not in text and "cuda_emu" not in text, f
 
 
+@pytest.mark.parametrize("defines", [("-DEVP_TMA_STATIC_FIRST=1",),
+                                     ("-DEVP_TMA_STATIC_FIRST=1", "-DEVP_TMA_MERGE_UV=1")])
+def test_static_first_item_variant_bitwise(monkeypatch, defines):
+    """-DEVP_TMA_STATIC_FIRST=1 (the first item of every CTA is its own index in the item list, the queue
+    hands out the rest), alone and together with MERGE_UV and the in-kernel fold, 1 and 4 ranks."""
+    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
+    case = fx.make_case(grid, "full", ndte=5, dt=3600.0)
+    ref = _oracle(case)
+    if len(defines) == 2:
+        monkeypatch.setenv("EVP_B200_FOLD", "kernel")
+    with emu.patched(kernel="tma", defines=defines) as evp:
+        got = clone_case(case)
+        evp.run_case(got, strict=True)
+        compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+        monkeypatch.setattr(evp, "compute_group", _compute_on_threads)
+        got = clone_case(case)
+        g = evp.EvpGroup(case.dom, case.ndte, case.dt, 4, strict=True)
+        try:
+            g.set_grid(grid.f)
+            g.evp(case.dt, got.inp, got.io, got.out)
+        finally:
+            g.close()
+        compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+
+
 def test_merge_uv_variant_bitwise():
     """-DEVP_TMA_MERGE_UV=1 (the velocities of row r0-1 ride in the first full stage of an item instead of a
     stage of their own): written and compile-checked in round 1, never run on

@@ -3,6 +3,8 @@
 # the default path is re-measured, and the prepared kernel variants are A/B-ed.  Results under gpurun_out/.
 #
 #   here, first:  python -m cice5_b200.build --variant mergeuv -DEVP_TMA_MERGE_UV=1
+#                 python -m cice5_b200.build --variant staticfirst -DEVP_TMA_STATIC_FIRST=1
+#                 python -m cice5_b200.build --variant r2all -DEVP_TMA_MERGE_UV=1 -DEVP_TMA_STATIC_FIRST=1
 #   then:         /usr/local/graft/bin/gpurun --timeout 1500 -- 'bash tools/first_call.sh'
 #   afterwards:   python tools/first_call_report.py
 #
@@ -30,7 +32,7 @@ done
 run bench 400 python bench.py
 run bench_reference 300 python bench.py --impl reference --steps 2 --warmup 1
 # 4. prepared variants: parity on the tripole cases first, then the kernel-only bench
-for v in mergeuv; do
+for v in mergeuv staticfirst r2all; do
   lib=cice5_b200/lib/exp_$v.so
   [ -f "$lib" ] || continue
   EVP_B200_LIB=$lib run parity_$v 400 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "tp1 or tripole or gx3"
@@ -39,6 +41,8 @@ done
 # 4b. the in-kernel tripole fold (EVP_B200_FOLD=kernel, one launch per subcycle): parity, then the bench
 EVP_B200_FOLD=kernel run parity_foldkernel 400 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "tp1 or tripole"
 EVP_B200_FOLD=kernel run bench_foldkernel 300 python bench.py --no-cpu-baseline --no-e2e
+[ -f cice5_b200/lib/exp_r2all.so ] && EVP_B200_FOLD=kernel EVP_B200_LIB=cice5_b200/lib/exp_r2all.so \
+  run bench_r2all_foldkernel 300 python bench.py --no-cpu-baseline --no-e2e
 # 4c. early download of the outputs that are final before the loop (EVP_B200_EARLY_D2H=1): parity, then e2e
 EVP_B200_EARLY_D2H=1 run parity_earlyd2h 400 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "gx3 or tp1"
 EVP_B200_EARLY_D2H=1 run bench_earlyd2h 300 python bench.py --no-cpu-baseline
