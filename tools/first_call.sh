@@ -5,7 +5,7 @@
 #   here, first:  python -m cice5_b200.build --variant mergeuv -DEVP_TMA_MERGE_UV=1
 #                 python -m cice5_b200.build --variant staticfirst -DEVP_TMA_STATIC_FIRST=1
 #                 python -m cice5_b200.build --variant r2all -DEVP_TMA_MERGE_UV=1 -DEVP_TMA_STATIC_FIRST=1
-#   then:         /usr/local/graft/bin/gpurun --timeout 1500 -- 'bash tools/first_call.sh'
+#   then:         /usr/local/graft/bin/gpurun --timeout 2700 -- 'bash tools/first_call.sh'   (about 40 GPU-minutes; the steps are ordered by importance)
 #   afterwards:   python tools/first_call_report.py
 #
 # Every step runs under its own timeout so that one hang cannot take the box (a strike) or the other steps.
