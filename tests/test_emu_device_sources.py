@@ -444,3 +444,44 @@ def test_plain_c_host_example_on_the_host_build(tmp_path):
     u, v = float(m.group(1)), float(m.group(2))
     assert abs(u - 1.154007e-01) <= 2e-6 * 1.154007e-01 and abs(v + 2.511930e-02) <= 2e-6 * 2.511930e-02
     assert "5828 active T cells" in r.stdout
+
+
+def test_random_small_domains_bitwise(dev):
+    """A dozen random domains per kernel (tools/fuzz_on_emulator.py runs hundreds): sizes down to 4 x 4,
+    wet and dry poles, no ice at all, ice in the south only, 1-4 ranks, revised EVP, tilt, turning angle."""
+    rng = np.random.default_rng(20261104)
+    for _ in range(12):
+        tripole = rng.random() < 0.6
+        nx = int(rng.integers(2, 30)) * 2 if tripole else int(rng.integers(4, 50))
+        ny = int(rng.integers(4, 24))
+        grid = fx.synthetic_tripole(nx, ny, wet_poles=bool(rng.random() < 0.5)) if tripole else fx.synthetic_displaced(nx, ny)
+        case = fx.make_case(grid, ["full", "caps"][int(rng.integers(0, 2))], ndte=int(rng.integers(1, 5)), dt=3600.0)
+        mode = rng.random()
+        if mode < 0.15:
+            for k in ("aice", "vice", "vsno", "aice_init"):
+                case.inp[k][...] = 0.0
+        elif mode < 0.3:
+            for k in ("aice", "vice", "vsno", "aice_init"):
+                case.inp[k][ny // 2:, :] = 0.0
+        kw = {}
+        if rng.random() < 0.3:
+            kw["revised_evp"] = True
+        if rng.random() < 0.3:
+            kw["tilt_mode"] = 1
+        if rng.random() < 0.3:
+            kw.update(cosw=0.9, sinw=float(np.sqrt(1 - 0.81)))
+        ref = _oracle(case, **kw)
+        nr = int(rng.choice([r for r in (1, 2, 3, 4) if nx % r == 0 and nx // r >= 2]))
+        got = clone_case(case)
+        if nr == 1:
+            dev.run_case(got, strict=True, **kw)
+        else:
+            if kw.get("revised_evp"):
+                kw["xmin"] = _xmin(grid)
+            g = dev.EvpGroup(case.dom, case.ndte, case.dt, nr, strict=True, **kw)
+            try:
+                g.set_grid(grid.f)
+                g.evp(case.dt, got.inp, got.io, got.out)
+            finally:
+                g.close()
+        compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
