@@ -47,6 +47,16 @@ CASES = {
     "open_3x2": (lambda: fx.synthetic_displaced(18, 12), 6, 6, (), False, 4, "full"),
     "open_revised_2x1": (lambda: fx.synthetic_displaced(18, 12), 9, 12, (), True, 3, "full"),
 }
+# The reference's real gx3 grid and the 1-degree tripole: too large to commit field by field -- their inputs
+# are regenerated from cice5_b200.fixtures (deterministic) and only SHA-256 digests of the inputs and of every
+# output block array go to tests/golden/ref_driver_digests.json (`--big`, a few minutes of interpreter time).
+BIG_CASES = {
+    "gx3_real_1x1": (lambda: fx.make_grid("gx3"), 100, 116, (), False, 3, "full"),
+    "gx3_real_2x2": (lambda: fx.make_grid("gx3"), 50, 58, (), False, 3, "full"),
+    "tp1_4x2": (lambda: fx.make_grid("tp1"), 90, 150, (), False, 2, "caps"),
+}
+DIGESTS = os.path.join(HERE, "ref_driver_digests.json")
+
 STATE_R8 = ("aice", "vice", "vsno", "aice_init", "aice0", "strairxt", "strairyt", "uocn", "vocn", "ss_tltx",
             "ss_tlty", "cdn_ocn", "strength", "uvel", "vvel", "fm", "strairx", "strairy", "strtltx", "strtlty",
             "strocnx", "strocny", "strintx", "strinty", "strocnxt", "strocnyt", "divu", "shear", "rdg_conv",
@@ -155,9 +165,15 @@ def blocks_of(arr):
     return np.ascontiguousarray(np.transpose(np.asarray(arr.a, dtype=float), (2, 1, 0)))
 
 
-def main(out_path=OUT):
+def _digest(a) -> str:
+    import hashlib
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def main(out_path=OUT, big=False):
     pack = {}
-    for cname, (factory, bsx, bsy, macros, revised, ndte, scenario) in CASES.items():
+    digests = {}
+    for cname, (factory, bsx, bsy, macros, revised, ndte, scenario) in (BIG_CASES if big else CASES).items():
         grid = factory()
         dom = grid.dom
         case = fx.make_case(grid, scenario, ndte=ndte, dt=3600.0)
@@ -190,6 +206,25 @@ def main(out_path=OUT):
         # --- init_evp's share (set_evp_parameters), then the driver
         m.call("set_evp_parameters", dt=case.dt)
         m.call("evp", dt=case.dt)
+        outs = {"uvel": "uvel", "vvel": "vvel", "fm": "fm", "strairx": "strairx", "strairy": "strairy",
+                "strtltx": "strtltx", "strtlty": "strtlty", "strocnx": "strocnx", "strocny": "strocny",
+                "strintx": "strintx", "strinty": "strinty", "strocnxT": "strocnxt", "strocnyT": "strocnyt",
+                "divu": "divu", "shear": "shear", "rdg_conv": "rdg_conv", "rdg_shear": "rdg_shear",
+                "prs_sig": "prs_sig", "uvel_init": "uvel_init", "vvel_init": "vvel_init", "strength": "strength"}
+        outs.update({k: k for k in io if k.startswith("stress")})
+        if big:                                    # digests only; physical cells and whole blocks separately
+            d = {"dims": [dom.nx, dom.ny, bsx, bsy, int(g["nblocks_x"]), int(g["nblocks_y"]), ndte],
+                 "scenario": scenario, "dt": case.dt,
+                 "inputs": {n: _digest(v) for n, v in list(inp.items()) + list(io.items()) + list(itd.items())},
+                 "grid": {n: _digest(grid.f[n]) for n in fx.GRID_FIELDS + ("tmask", "umask")},
+                 "physical": {}, "blocks": {}}
+            for n, fn in list(outs.items()) + [("iceumask", "iceumask")]:
+                blk = blocks_of(g[fn])
+                d["physical"][n] = _digest(blk[:, 1:-1, 1:-1])
+                d["blocks"][n] = _digest(blk)
+            digests[cname] = d
+            print(cname, "done", flush=True)
+            continue
         # --- store
         key = cname + "__"
         pack[key + "dims"] = np.array([dom.nx, dom.ny, bsx, bsy, g["nblocks_x"], g["nblocks_y"], ndte], np.int64)
@@ -204,12 +239,6 @@ def main(out_path=OUT):
             pack[key + "io__" + n] = v
         for n, v in itd.items():
             pack[key + "itd__" + n] = v
-        outs = {"uvel": "uvel", "vvel": "vvel", "fm": "fm", "strairx": "strairx", "strairy": "strairy",
-                "strtltx": "strtltx", "strtlty": "strtlty", "strocnx": "strocnx", "strocny": "strocny",
-                "strintx": "strintx", "strinty": "strinty", "strocnxT": "strocnxt", "strocnyT": "strocnyt",
-                "divu": "divu", "shear": "shear", "rdg_conv": "rdg_conv", "rdg_shear": "rdg_shear",
-                "prs_sig": "prs_sig", "uvel_init": "uvel_init", "vvel_init": "vvel_init", "strength": "strength"}
-        outs.update({k: k for k in io if k.startswith("stress")})
         for n, fn in outs.items():
             pack[key + "out__" + n] = blocks_of(g[fn])
         pack[key + "out__iceumask"] = blocks_of(g["iceumask"]).astype(np.int32)
@@ -218,9 +247,15 @@ def main(out_path=OUT):
         print("statements outside the interpreter's subset (raise if reached):")
         for u_ in sorted(set(fe.UNTRANSLATED)):
             print("   ", u_)
+    if big:
+        import json
+        with open(DIGESTS, "w") as fh:
+            json.dump(digests, fh, indent=1, sort_keys=True)
+        print(f"{DIGESTS}: {len(digests)} cases")
+        return
     np.savez_compressed(out_path, **pack)
     print(f"{out_path}: {len(pack)} arrays, {os.path.getsize(out_path) / 1024:.0f} KiB")
 
 
 if __name__ == "__main__":
-    main()
+    main(big="--big" in sys.argv)

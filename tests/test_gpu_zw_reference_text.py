@@ -68,3 +68,21 @@ def test_device_matches_reference_text_two_ranks(dvec, name):
     finally:
         g.close()
     _check(dvec, name, case, layout)
+
+
+@pytest.mark.parametrize("name,nranks", [("gx3_real_1x1", 1), ("gx3_real_2x2", 2), ("tp1_4x2", 1), ("tp1_4x2", 4)])
+def test_device_matches_reference_digests(name, nranks):
+    """The reference's real gx3 grid and the 1-degree tripole: the reference-text outputs are kept as SHA-256
+    digests (tests/golden/ref_driver_digests.json), the inputs are regenerated from the fixtures."""
+    from tests.test_oracle_reference_text import check_digests, digest_case
+    case, kw, layout, d = digest_case(name)
+    if nranks == 1:
+        evp.run_case(case, strict=True, **kw)
+    else:
+        g = evp.EvpGroup(case.dom, case.ndte, case.dt, nranks, strict=True, **kw)
+        try:
+            g.set_grid(case.grid.f)
+            g.evp(case.dt, case.inp, case.io, case.out)
+        finally:
+            g.close()
+    check_digests(case, layout, d)

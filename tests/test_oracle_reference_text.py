@@ -315,3 +315,55 @@ def test_driver_cases_are_distinct(dvec):
     nx = int(dvec["tripole_wet_4x1__dims"][0])
     # block 1 holds column 1, the last block column nx-1, of the top physical row: not antisymmetric
     assert top[0, -2, 1] != 0.0 and top[0, -2, 1] != -top[-1, -2, -3]
+
+
+# ---------------------------------------------------------------------------------------------
+# the same on the reference's REAL gx3 grid (global_gx3.grid / .kmt) and on the 1-degree tripole: the
+# inputs are regenerated from cice5_b200.fixtures, the reference-text outputs are kept as SHA-256 digests
+# (tests/golden/make_driver_vectors.py --big -> ref_driver_digests.json)
+# ---------------------------------------------------------------------------------------------
+DIGESTS = os.path.join(os.path.dirname(__file__), "golden", "ref_driver_digests.json")
+
+
+def _sha(a):
+    import hashlib
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def digest_case(name):
+    """(case, oracle keywords, block layout, stored digests) of one --big case; skips if the regenerated
+    inputs are not the ones the digests were made from (another numpy / libm: nothing to compare then)."""
+    import json
+    d = json.load(open(DIGESTS))[name]
+    nx, ny, bsx, bsy, nbx, nby, ndte = d["dims"]
+    grid = fx.make_grid("gx3" if name.startswith("gx3") else "tp1")
+    case = fx.make_case(grid, d["scenario"], ndte=ndte, dt=d["dt"])
+    itd = fx.ice_itd(case.inp)
+    have = {n: _sha(v) for n, v in list(case.inp.items()) + list(case.io.items()) + list(itd.items())}
+    have_grid = {n: _sha(grid.f[n]) for n in tuple(fx.GRID_FIELDS) + ("tmask", "umask")}
+    if have != d["inputs"] or have_grid != d["grid"]:
+        pytest.skip("fixtures regenerate different bits here than where the digests were made")
+    case.inp["strength"] = orc.ice_strength(grid.dom, case.inp["aice"], case.inp["vice"], itd["aice0"], itd["aicen"],
+                                            itd["vicen"])
+    return case, dict(strength_masked=1), (bsx, bsy, nbx, nby), d
+
+
+def check_digests(case, layout, d):
+    _bsx, _bsy, nbx, nby = layout
+    bad = []
+    for n, want in d["physical"].items():
+        mine = case.io[n] if n in case.io else case.out["strength_out" if n == "strength" else n]
+        blk = blocks_from_global(mine.astype(np.float64), layout)
+        if _sha(blk[:, 1:-1, 1:-1]) != want:
+            bad.append(n + " (physical)")
+        if (n in HALOED or nbx * nby == 1) and _sha(blk) != d["blocks"][n]:
+            bad.append(n + " (ghosts)")
+    assert not bad, bad
+    assert len(d["physical"]) == 34
+
+
+@pytest.mark.parametrize("name,nslabs", [("gx3_real_1x1", 1), ("gx3_real_2x2", 2), ("tp1_4x2", 4)])
+def test_whole_call_matches_reference_digests(name, nslabs):
+    case, kw, layout, d = digest_case(name)
+    orc.run_case(case, nslabs=nslabs, **kw)
+    check_digests(case, layout, d)
