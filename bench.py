@@ -127,12 +127,17 @@ def cpu_sample(args, case_fn, nthreads=0):
     ksub loop plus the whole call."""
     from oracle import oracle as orc
     case = case_fn(args.cpu_ndte)
+    if nthreads == 0:
+        # every core this process may run on, set explicitly: torchrun exports OMP_NUM_THREADS=1
+        # to its ranks, which would otherwise leave the reference arm of an N > 1 run on one thread
+        nthreads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     t0 = time.perf_counter()
     st = orc.run_case(case, nslabs=1, nthreads=nthreads)
     wall = time.perf_counter() - t0
     cs = st.active_t_cells * args.cpu_ndte
     return {"value": cs / st.total_seconds, "loop_value": cs / st.loop_seconds, "unit": "cell-subcycles/s",
-            "cores": os.cpu_count() if nthreads == 0 else nthreads, "kind": "port",
+            "seconds": st.total_seconds,
+            "cores": nthreads, "kind": "port",
             "sample": f"{args.grid} {args.scenario}, one evp call with ndte={args.cpu_ndte} "
                       f"({cs:.3g} cell-subcycles, {wall:.1f} s wall); oracle/evp_oracle.c, gcc -O2 -fopenmp "
                       f"-ffp-contract=off; the Fortran+MPI reference cannot be built in this image"}
@@ -150,19 +155,19 @@ def run_reference(args, rank):
     from cice5_b200 import fixtures as fx
     grid = fx.make_grid(args.grid)
     dt = fx.GRID_DT.get(args.grid, 3600.0)
-    vals, loops = [], []
+    vals, loops, secs = [], [], []
     t_all = time.perf_counter()
     for it in range(args.warmup + args.steps):
         if it >= 1 and time.perf_counter() - t_all > 150:      # keep the whole run bounded
             break
         r = cpu_sample(args, lambda n: fx.make_case(grid, args.scenario, ndte=n, dt=dt))
         if it >= min(args.warmup, 1):
-            vals.append(r["value"]); loops.append(r["loop_value"])
+            vals.append(r["value"]); loops.append(r["loop_value"]); secs.append(r["seconds"])
     v = statistics.median(vals)
     dom = grid.dom
     out = {"impl": "reference", "metric": "EVP cell-subcycles/s", "value": v, "unit": "cell-subcycles/s",
            "n_gpus": args.gpus, "steps": len(vals), "warmup": min(args.warmup, 1),
-           "ms_per_step": None, "higher_is_better": True, "vs_baseline": None,
+           "ms_per_step": 1e3 * statistics.median(secs), "higher_is_better": True, "vs_baseline": None,
            "dtype": "f64", "data": "synthetic",
            "scaling": "strong",
            "config": {"workload": workload_name(args, dom, dt),

@@ -472,7 +472,16 @@ static void stress(const Dom *d, const Consts *k, int ksub, int ndte, const List
     double *stressm_1 = sm[0], *stressm_2 = sm[1], *stressm_3 = sm[2], *stressm_4 = sm[3];
     double *stress12_1 = s12[0], *stress12_2 = s12[1], *stress12_3 = s12[2], *stress12_4 = s12[3];
 
-    memset(str, 0, sizeof(double) * 8 * n);                               /* :613 */
+    {   /* :613, str(:,:,:) = c0.  The reference does this once per block and its blocks run in parallel
+         * (MPI tasks / OpenMP over iblk); with one block here, the fill is shared between the threads. */
+        const size_t total = 8 * n, piece = (size_t)1 << 18;
+        const long npieces = (long)((total + piece - 1) / piece);
+#pragma omp parallel for schedule(static)
+        for (long c = 0; c < npieces; ++c) {
+            const size_t lo = (size_t)c * piece, len = (lo + piece <= total) ? piece : total - lo;
+            memset(str + lo, 0, sizeof(double) * len);
+        }
+    }
 
 #pragma omp parallel for schedule(static)
     for (int ij = 0; ij < L->icellt; ++ij) {
