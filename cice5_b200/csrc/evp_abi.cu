@@ -89,6 +89,7 @@ struct evp_handle {
     size_t arena_bytes = 0;
     size_t off_planes = 0, off_inbox = 0, off_flags = 0, off_int = 0, off_mask = 0, off_counts = 0, off_tflags = 0;
     int tflags_ld = 0, tstrips = 0;
+    int t_n_small = 0, t_rows_small = 0;         // EVP_B200_GUIDED: the first t_n_small chunks are short
     int t_rpc = 0, t_chunks = 0, t_items = 0;    // TMA kernel work items: (strip, chunk of t_rpc rows)
     size_t off_trace = 0;                        // u64 trace[ndte][8] (EVP_B200_TRACE=1)
     bool trace_on = false;
@@ -375,7 +376,17 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
         if (const char *ev = getenv("EVP_B200_RPC")) rpc = atoi(ev);      // tuning experiments
         rpc = rpc < 2 ? 2 : (rpc > 64 ? 64 : rpc);
         h->t_rpc = (int)rpc;
-        h->t_chunks = (g.ny + h->t_rpc - 1) / h->t_rpc;
+        // EVP_B200_GUIDED="percent,rows" (experiment, -DEVP_TMA_GUIDED=1 builds only): that share of the rows, from the
+        // south end, is cut into chunks of `rows` rows; they sort behind the full chunks in the work list
+        if (const char *gv = kGuided ? getenv("EVP_B200_GUIDED") : nullptr) {
+            int pct = 0, rs = 0;
+            if (sscanf(gv, "%d,%d", &pct, &rs) == 2 && pct > 0 && pct <= 100 && rs >= 2 && rs < h->t_rpc) {
+                h->t_rows_small = rs;
+                h->t_n_small = (int)((long long)g.ny * pct / 100 / rs);
+            }
+        }
+        const int rows_left = g.ny - h->t_n_small * h->t_rows_small;
+        h->t_chunks = h->t_n_small + (rows_left + h->t_rpc - 1) / h->t_rpc;
         h->t_items = h->tstrips * h->t_chunks;
     }
     h->trace_on = getenv("EVP_B200_TRACE") != nullptr;
@@ -844,6 +855,7 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
             t.a.rows_per_chunk = h->t_rpc;
             t.chunks = h->t_chunks;
             t.items = h->t_items;
+            t.n_small = h->t_n_small; t.rows_small = h->t_rows_small;
             t.queue = h->queue(ksub - 1); t.item_list = h->item_list(); t.item_count = h->item_count();
             t.fused_signal = fused_sync ? 1 : 0;
             t.fold_in_kernel = fold_in_kernel ? 1 : 0;
@@ -979,7 +991,8 @@ void build_program(evp_handle *h, double dt, Program &P)
             dim3 grid(h->tstrips, (h->g.ny + 4 + 3) / 4);
             tile_flags_kernel<<<grid, 128, 0, s>>>(h->mask(), h->ldm, h->g.nxl, h->g.ny, h->tstrips, h->tflags(),
                                                   h->tflags_ld, h->gflags());
-            item_list_kernel<<<1, kSortThreads, 0, s>>>(h->tflags(), h->tflags_ld, h->tstrips, h->t_chunks, h->t_rpc, h->g.ny,
+            item_list_kernel<<<1, kSortThreads, 0, s>>>(h->tflags(), h->tflags_ld, h->tstrips, h->t_chunks, h->t_rpc,
+                                                h->t_n_small, h->t_rows_small, h->g.ny,
                                                 h->g.tripole ? 1 : 0, h->west_closed() ? 0 : 1, h->east_closed() ? 0 : 1,
                                                 h->item_list(), h->item_count(), h->queue(0), 3 * h->cfg.ndte);
             L.n += 2;

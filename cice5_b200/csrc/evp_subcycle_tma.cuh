@@ -69,6 +69,12 @@ constexpr bool kStaticFirst = EVP_TMA_STATIC_FIRST != 0;
 #ifndef EVP_TMA_ITEMTRACE
 #define EVP_TMA_ITEMTRACE 0
 #endif
+// EVP_TMA_GUIDED = 1 (experiment, not yet run on hardware, off by default): two-tier row chunks, see
+// TmaArgs::n_small.  A compile-time switch so that the default build keeps the code that was measured.
+#ifndef EVP_TMA_GUIDED
+#define EVP_TMA_GUIDED 0
+#endif
+constexpr bool kGuided = EVP_TMA_GUIDED != 0;
 constexpr unsigned kMetaUvBelow = 32u, kMetaHtnBelow = 64u;
 constexpr int kMaskBoxW = 128 + 16;          // per mask box; kTmaBoxW / 128 boxes per row
 constexpr int kMaskBoxes = kTmaBoxW / 128;
@@ -104,7 +110,21 @@ struct TmaArgs {
     // timing trace of this launch (EVP_B200_TRACE=1), globaltimer ns: [0] first CTA start, [1] last
     // CTA done, [2] peers signalled; the fold kernel adds [3] wait begin, [4] wait end
     unsigned long long *trace;
+    // guided item sizes (-DEVP_TMA_GUIDED=1 builds with EVP_B200_GUIDED set; n_small = 0 otherwise): the
+    // first n_small row chunks have rows_small rows instead of a.rows_per_chunk.  The list is drawn heaviest
+    // first, so the short items come last and the end of a launch is ragged by a short item, not a full one.
+    int n_small, rows_small;
 };
+
+// Rows of a chunk: T rows r0 .. rend, U rows r0 .. rend-1 (chunks [0, n_small) are the short ones).
+__host__ __device__ __forceinline__ void chunk_rows(int chunk, int rpc, int n_small, int rows_small, int ny,
+                                                    int &r0, int &rend)
+{
+    const bool small = chunk < n_small;
+    r0 = 1 + (small ? chunk * rows_small : n_small * rows_small + (chunk - n_small) * rpc);
+    const int top = r0 + (small ? rows_small : rpc);
+    rend = top < ny + 1 ? top : ny + 1;
+}
 
 __device__ __forceinline__ unsigned smem_u32(const void *p)
 {
@@ -273,8 +293,9 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                 const int item_tag = item | (q < nbnd ? kItemBoundary : 0);
                 const int strip = item % p.strips, chunk = item / p.strips;
                 const int x0 = strip * kTmaUCols;                       // box column 0 = U column c0 - 1
-                const int r0 = 1 + chunk * a.rows_per_chunk;
-                const int rend = min(r0 + a.rows_per_chunk, a.ny + 1);
+                int r0 = 1 + chunk * a.rows_per_chunk;
+                int rend = min(r0 + a.rows_per_chunk, a.ny + 1);
+                if (kGuided) chunk_rows(chunk, a.rows_per_chunk, p.n_small, p.rows_small, a.ny, r0, rend);
                 const unsigned char *fl = p.tile_flags + (size_t)strip * p.flags_ld;
                 for (int j = kMergeUv ? r0 : r0 - 1; j <= rend; ++j) {
                     // what this row segment needs: T data if it has an active T cell; U data of the
@@ -371,8 +392,9 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
         const int c = 1 + strip * kTmaUCols + warp * kUColsPerWarp + lane;   // T column (U column if lane < 31)
         const bool warp_on = (c - lane) <= a.nxl;                       // warp-uniform
         const int mshift = (strip * kTmaUCols) & 15;                    // mask box starts this many bytes early
-        const int r0 = 1 + chunk * a.rows_per_chunk;
-        const int rend = min(r0 + a.rows_per_chunk, a.ny + 1);
+        int r0 = 1 + chunk * a.rows_per_chunk;
+        int rend = min(r0 + a.rows_per_chunk, a.ny + 1);
+        if (kGuided) chunk_rows(chunk, a.rows_per_chunk, p.n_small, p.rows_small, a.ny, r0, rend);
         const bool tcol = c <= a.nxl + 1;
         const bool ucol = lane < kUColsPerWarp && c <= a.nxl;
         const bool tstore_col = tcol && (lane < kUColsPerWarp || c == a.nxl + 1);
@@ -646,8 +668,8 @@ __global__ void metric_flags_kernel(const __grid_constant__ MetricCheckArgs a)
 // where the loop never writes), so it is dropped -- except the chunks that reach the top rows of a
 // tripole grid, whose velocities feed the fold every subcycle.  The order inside one weight class
 // is not deterministic; results do not depend on the order of the items.
-__global__ void item_list_kernel(const unsigned char *flags, int flags_ld, int strips, int chunks, int rpc, int ny,
-                                 int tripole, int bnd_west, int bnd_east, int *list, int *count, int *queues,
+__global__ void item_list_kernel(const unsigned char *flags, int flags_ld, int strips, int chunks, int rpc,
+                                 int n_small, int rows_small, int ny, int tripole, int bnd_west, int bnd_east, int *list, int *count, int *queues,
                                  int nqueues)
 {
     // Stable counting sort, one block of kSortThreads threads, thread t owns a contiguous range of
@@ -668,7 +690,8 @@ __global__ void item_list_kernel(const unsigned char *flags, int flags_ld, int s
     for (int pass = 0; pass < 2; ++pass) {
         for (int item = i0; item < i1; ++item) {
             const int strip = item % strips, chunk = item / strips;
-            const int r0 = 1 + chunk * rpc, rend = min(r0 + rpc, ny + 1);
+            int r0, rend;
+            chunk_rows(chunk, rpc, n_small, rows_small, ny, r0, rend);
             const unsigned char *fl = flags + (size_t)strip * flags_ld;
             int w = 0;
             for (int j = r0 - 1; j <= rend + 1; ++j) w += (fl[j] & 3u) != 0u;    // activity bits only

@@ -357,6 +357,32 @@ def test_fold_in_kernel_variant_bitwise(monkeypatch, nranks, threads):
             g.close()
 
 
+@pytest.mark.parametrize("rpc,guided,nranks,scenario,defines", [
+    ("9", "40,2", 1, "full", ()), ("8", "100,3", 2, "full", ()), ("5", "30,4", 1, "caps", ()),
+    ("7", "60,2", 4, "full", ("-DEVP_TMA_MERGE_UV=1", "-DEVP_TMA_STATIC_FIRST=1")), ("6", "35,7", 1, "full", ())])
+def test_guided_item_sizes_bitwise(monkeypatch, rpc, guided, nranks, scenario, defines):
+    """-DEVP_TMA_GUIDED=1 with EVP_B200_GUIDED="percent,rows" (DESIGN.md section 9, 1f): the southern share of
+    the rows is cut into short chunks that the heaviest-first work list hands out last.  Pure scheduling: the
+    same answers bit for bit, whatever the split, alone and with the other round-2 variants (last case:
+    rows >= rows-per-item, the option must switch itself off)."""
+    monkeypatch.setenv("EVP_B200_RPC", rpc)
+    monkeypatch.setenv("EVP_B200_GUIDED", guided)
+    grid = fx.synthetic_tripole(96, 43, wet_poles=True)
+    case = fx.make_case(grid, scenario, ndte=4, dt=3600.0)
+    ref, got = clone_case(case), clone_case(case)
+    with emu.patched(kernel="tma", defines=("-DEVP_TMA_GUIDED=1", *defines)) as evp:
+        g = evp.EvpGroup(case.dom, case.ndte, case.dt, nranks, strict=True)
+        try:
+            g.set_grid(grid.f)
+            for _ in range(2):
+                ref.out, got.out = fx.zeroed_outputs(case.dom), fx.zeroed_outputs(case.dom)
+                orc.run_case(ref)
+                g.evp(case.dt, got.inp, got.io, got.out)
+                compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+        finally:
+            g.close()
+
+
 def test_fold_in_kernel_when_no_boundary_item_holds_ice(monkeypatch):
     """Ice in the south only: no boundary item, the last CTA of the launch signals and folds."""
     monkeypatch.setenv("EVP_B200_FOLD", "kernel")

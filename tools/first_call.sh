@@ -5,6 +5,8 @@
 #   here, first:  python -m cice5_b200.build --variant mergeuv -DEVP_TMA_MERGE_UV=1
 #                 python -m cice5_b200.build --variant staticfirst -DEVP_TMA_STATIC_FIRST=1
 #                 python -m cice5_b200.build --variant r2all -DEVP_TMA_MERGE_UV=1 -DEVP_TMA_STATIC_FIRST=1
+#                 python -m cice5_b200.build --variant guided -DEVP_TMA_GUIDED=1
+#                 python -m cice5_b200.build --variant r2guided -DEVP_TMA_MERGE_UV=1 -DEVP_TMA_STATIC_FIRST=1 -DEVP_TMA_GUIDED=1
 #   then:         /usr/local/graft/bin/gpurun --timeout 2700 -- 'bash tools/first_call.sh'   (about 40 GPU-minutes; the steps are ordered by importance)
 #   afterwards:   python tools/first_call_report.py
 #
@@ -43,6 +45,14 @@ EVP_B200_FOLD=kernel run parity_foldkernel 400 python -m pytest tests/test_gpu_p
 EVP_B200_FOLD=kernel run bench_foldkernel 300 python bench.py --no-cpu-baseline --no-e2e
 [ -f cice5_b200/lib/exp_r2all.so ] && EVP_B200_FOLD=kernel EVP_B200_LIB=cice5_b200/lib/exp_r2all.so \
   run bench_r2all_foldkernel 300 python bench.py --no-cpu-baseline --no-e2e
+# 4d. guided item sizes (-DEVP_TMA_GUIDED=1 libraries with EVP_B200_GUIDED="percent,rows": short items at the
+#     end of the work list): parity, then the bench, alone and on top of the other two variants
+for v in guided r2guided; do
+  lib=cice5_b200/lib/exp_$v.so
+  [ -f "$lib" ] || continue
+  EVP_B200_GUIDED=30,3 EVP_B200_LIB=$lib run parity_$v 400 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "tp1 or tripole"
+  EVP_B200_GUIDED=30,3 EVP_B200_LIB=$lib run bench_$v 300 python bench.py --no-cpu-baseline --no-e2e
+done
 # 4c. early download of the outputs that are final before the loop (EVP_B200_EARLY_D2H=1): parity, then e2e
 EVP_B200_EARLY_D2H=1 run parity_earlyd2h 400 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "gx3 or tp1"
 EVP_B200_EARLY_D2H=1 run bench_earlyd2h 300 python bench.py --no-cpu-baseline
