@@ -89,6 +89,7 @@ struct evp_handle {
     size_t arena_bytes = 0;
     size_t off_planes = 0, off_inbox = 0, off_flags = 0, off_int = 0, off_mask = 0, off_counts = 0, off_tflags = 0;
     int tflags_ld = 0, tstrips = 0;
+    bool strair_given = false;                   // evp_in_t.strax/stray given: strairx/y are copies of them
     int t_n_small = 0, t_rows_small = 0;         // EVP_B200_GUIDED: the first t_n_small chunks are short
     int t_rpc = 0, t_chunks = 0, t_items = 0;    // TMA kernel work items: (strip, chunk of t_rpc rows)
     size_t off_trace = 0;                        // u64 trace[ndte][8] (EVP_B200_TRACE=1)
@@ -546,7 +547,12 @@ int evp_gpu_upload(evp_handle_t *h, const evp_in_t *in, const evp_inout_t *io)
     const int dstp[12] = {I_AICE, I_VICE, I_VSNO, I_AICE_INIT, I_STRAIRXT, I_STRAIRYT,
                           I_UOCN, I_VOCN, I_SSTLTX, I_SSTLTY, I_CW, I_STRENGTH};
     if (!in->strength && !h->itd_ready) return EVP_ERR_ARG;      // neither the host's strength nor an ITD
+    if ((in->strax == nullptr) != (in->stray == nullptr)) return EVP_ERR_ARG;
     h->strength_from_itd = in->strength == nullptr;
+    // ACCESS, .not. calc_strair (ice_dyn_evp.F90:220-229): strairxT/yT reach no output of the call then
+    // (evp_prep1's copy of them is overwritten), so the coupler's U-grid stress takes their planes
+    h->strair_given = in->strax != nullptr;
+    if (h->strair_given) { src[4] = in->strax; src[5] = in->stray; }
     for (int p = 0; p < 12; ++p) {
         if (dstp[p] == I_STRENGTH && h->strength_from_itd) continue;      // computed on the device
         TRY(h2d(h, dstp[p], src[p]));
@@ -943,6 +949,11 @@ void build_program(evp_handle *h, double dt, Program &P)
             a.in[3] = h->plane(W_2); a.out[3] = h->plane(O_STRAIRY);
             to_ugrid4_kernel<<<grid2d(h), 128, 0, s>>>(a);
             ++L.n;
+        }
+        if (h->strair_given) {          // strairx(:,:,:) = strax(:,:,:) instead of t2ugrid_vector (:227-228)
+            const size_t pbytes = h->plane_elems * sizeof(double);
+            CK(cudaMemcpyAsync(h->plane(O_STRAIRX), h->plane(I_STRAIRXT), pbytes, cudaMemcpyDeviceToDevice, s));
+            CK(cudaMemcpyAsync(h->plane(O_STRAIRY), h->plane(I_STRAIRYT), pbytes, cudaMemcpyDeviceToDevice, s));
         }
         if (h->strength_from_itd) {     // ice_strength on the device (:291-301), into the input plane
             const evp_itd_t &it = h->itd_cfg;

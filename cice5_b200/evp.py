@@ -51,7 +51,7 @@ class ItdS(C.Structure):
 
 
 class InS(C.Structure):
-    _fields_ = [(n, _DP) for n in IN_R8]
+    _fields_ = [(n, _DP) for n in IN_R8] + [("strax", _DP), ("stray", _DP)]
 
 
 class InOutS(C.Structure):
@@ -185,6 +185,9 @@ class EvpGpu:
         for n in IN_R8:
             key = "Cw" if n == "Cdn_ocn" and "Cdn_ocn" not in inp else n
             setattr(s, n, _dp(inp.get(key)) if n == "strength" else _dp(inp[key]))   # strength: optional
+        if inp.get("strax") is not None or inp.get("stray") is not None:
+            # ACCESS build with calc_strair = .false. (source/ice_dyn_evp.F90:220-229)
+            s.strax, s.stray = _dp(inp.get("strax")), _dp(inp.get("stray"))
         return s
 
     @staticmethod

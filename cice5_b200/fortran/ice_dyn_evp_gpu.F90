@@ -44,6 +44,7 @@
       type, bind(C) :: evp_in_t
          type(c_ptr) :: aice, vice, vsno, aice_init, strairxT, strairyT, uocn, vocn
          type(c_ptr) :: ss_tltx, ss_tlty, Cdn_ocn, strength
+         type(c_ptr) :: strax, stray         ! optional (c_null_ptr): ACCESS, .not. calc_strair
       end type
 
       type, bind(C) :: evp_inout_t
@@ -212,6 +213,10 @@
 ! == subroutine evp(dt) of the reference (source/ice_dyn_evp.F90:68)
       subroutine evp (dt)
       use ice_atmo, only: Cdn_ocn
+#ifdef ACCESS
+      use ice_atmo, only: calc_strair
+      use ice_flux, only: strax, stray
+#endif
       use ice_blocks, only: block, get_block, nx_block, ny_block
       use ice_domain, only: blocks_ice
       use ice_flux, only: rdg_conv, rdg_shear, prs_sig, strairxT, strairyT, &
@@ -256,6 +261,13 @@
       in%uocn = c_loc(uocn(1,1,1)); in%vocn = c_loc(vocn(1,1,1))
       in%ss_tltx = c_loc(ss_tltx(1,1,1)); in%ss_tlty = c_loc(ss_tlty(1,1,1))
       in%Cdn_ocn = c_loc(Cdn_ocn(1,1,1)); in%strength = c_loc(strength(1,1,1))
+      in%strax = c_null_ptr;  in%stray = c_null_ptr
+#ifdef ACCESS
+      ! source/ice_dyn_evp.F90:220-229: the coupler's wind stress is already on the U grid
+      if (.not. calc_strair) then
+         in%strax = c_loc(strax(1,1,1));  in%stray = c_loc(stray(1,1,1))
+      endif
+#endif
       io%uvel = c_loc(uvel(1,1,1)); io%vvel = c_loc(vvel(1,1,1))
       io%stressp = [c_loc(stressp_1(1,1,1)), c_loc(stressp_2(1,1,1)), c_loc(stressp_3(1,1,1)), c_loc(stressp_4(1,1,1))]
       io%stressm = [c_loc(stressm_1(1,1,1)), c_loc(stressm_2(1,1,1)), c_loc(stressm_3(1,1,1)), c_loc(stressm_4(1,1,1))]

@@ -89,6 +89,12 @@ typedef struct {
     const double *strairxT, *strairyT, *uocn, *vocn, *ss_tltx, *ss_tlty;
     const double *Cdn_ocn;
     const double *strength;     /* host ice_strength result on the block's physical T cells */
+    /* optional (NULL = the default build).  #ifdef ACCESS with calc_strair = .false.
+     * (source/ice_dyn_evp.F90:220-229): the coupler's wind stress, already on the U grid and
+     * multiplied by aice; strairx/y become copies of these arrays (ghost cells included) and the
+     * T->U averaging of strairxT/yT (:240-241) is not used.  Both or neither; the same choice on
+     * every rank. */
+    const double *strax, *stray;
 } evp_in_t;
 
 /* Optional: the thickness distribution, so that ice_strength (source/ice_mechred.F90:2111-2269, called by

@@ -823,13 +823,22 @@ int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
         to_ugrid(d, tmass[b], umass[b], tarea[b], uarea[b]);
         to_ugrid(d, aice_init[b], aiu[b], tarea[b], uarea[b]);
     }
-    /* :240-241 t2ugrid_vector (ice_grid.F90:1799-1823) */
-    FOR_BLOCKS memcpy(work1[b], strairx[b], sizeof(double) * n);
-    halo_r8(d, work1, LOC_CENTER, KIND_VECTOR, 0.0);
-    FOR_BLOCKS to_ugrid(d, work1[b], strairx[b], tarea[b], uarea[b]);
-    FOR_BLOCKS memcpy(work1[b], strairy[b], sizeof(double) * n);
-    halo_r8(d, work1, LOC_CENTER, KIND_VECTOR, 0.0);
-    FOR_BLOCKS to_ugrid(d, work1[b], strairy[b], tarea[b], uarea[b]);
+    if (s->strax && s->stray) {
+        /* :220-229 (#ifdef ACCESS, .not. calc_strair): strairx(:,:,:) = strax(:,:,:), ghosts included */
+        double **strax = split_r8(d, s->strax), **stray = split_r8(d, s->stray);
+        FOR_BLOCKS memcpy(strairx[b], strax[b], sizeof(double) * n);
+        FOR_BLOCKS memcpy(strairy[b], stray[b], sizeof(double) * n);
+        free_slabs(d, (void **)strax);
+        free_slabs(d, (void **)stray);
+    } else {
+        /* :240-241 t2ugrid_vector (ice_grid.F90:1799-1823) */
+        FOR_BLOCKS memcpy(work1[b], strairx[b], sizeof(double) * n);
+        halo_r8(d, work1, LOC_CENTER, KIND_VECTOR, 0.0);
+        FOR_BLOCKS to_ugrid(d, work1[b], strairx[b], tarea[b], uarea[b]);
+        FOR_BLOCKS memcpy(work1[b], strairy[b], sizeof(double) * n);
+        halo_r8(d, work1, LOC_CENTER, KIND_VECTOR, 0.0);
+        FOR_BLOCKS to_ugrid(d, work1[b], strairy[b], tarea[b], uarea[b]);
+    }
 
     /* ---- :247-308 ---- */
     FOR_BLOCKS {

@@ -113,6 +113,10 @@ typedef struct {
     double *strocnxT, *strocnyT, *divu, *shear, *rdg_conv, *rdg_shear, *prs_sig;
     double *uvel_init, *vvel_init, *tmass, *strength;
     int *icetmask;             /* diagnostic: mask after its halo update */
+    /* in, optional (NULL: the default build).  The ACCESS build with calc_strair = .false.
+     * (source/ice_dyn_evp.F90:220-245): strairx/y are the coupler's U-grid stresses, copied whole,
+     * and t2ugrid_vector is not called. */
+    const double *strax, *stray;
 } evp_oracle_state;
 
 typedef struct {

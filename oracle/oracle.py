@@ -48,7 +48,7 @@ class StateS(C.Structure):
     _fields_ = [(n, _DP) for n in _STATE_IN] + [("uvel", _DP), ("vvel", _DP),
                ("stressp", _DP * 4), ("stressm", _DP * 4), ("stress12", _DP * 4),
                ("iceumask", _IP), ("fm", _DP)] + [(n, _DP) for n in _STATE_OUT] + \
-               [("icetmask", _IP)]
+               [("icetmask", _IP), ("strax", _DP), ("stray", _DP)]
 
 
 class Stats(C.Structure):
@@ -121,6 +121,8 @@ def run_case(case, nslabs=1, nthreads=0, dt_init=None, **cfg_kw):
     for n in _STATE_OUT:
         setattr(s, n, _dp(out["strength_out" if n == "strength" else n]))
     s.icetmask = _ip(out["icetmask"])
+    if inp.get("strax") is not None:           # ACCESS build, calc_strair = .false.
+        s.strax, s.stray = _dp(inp["strax"]), _dp(inp["stray"])
     st = Stats()
     rc = lib().evp_oracle_run(C.byref(cfg), C.byref(g), C.byref(s), C.c_double(case.dt), C.byref(st))
     if rc != 0:

@@ -46,6 +46,9 @@ CASES = {
     "tripole_coupled_1x1": (lambda: fx.synthetic_tripole(24, 12), 24, 12, ("coupled",), False, 3, "caps"),
     "open_3x2": (lambda: fx.synthetic_displaced(18, 12), 6, 6, (), False, 4, "full"),
     "open_revised_2x1": (lambda: fx.synthetic_displaced(18, 12), 9, 12, (), True, 3, "full"),
+    # the ACCESS build with calc_strair = .false. (ice_dyn_evp.F90:220-245): strairx/y are the coupler's
+    # U-grid stresses strax/stray, t2ugrid_vector is skipped
+    "tripole_access_2x1": (lambda: fx.synthetic_tripole(24, 12), 12, 12, ("ACCESS",), False, 3, "full"),
 }
 # The reference's real gx3 grid and the 1-degree tripole: too large to commit field by field -- their inputs
 # are regenerated from cice5_b200.fixtures (deterministic) and only SHA-256 digests of the inputs and of every
@@ -111,7 +114,7 @@ def machine(dom, bsx, bsy, macros, revised_evp, ndte):
              nblocks_tot=0, buftripoler8=None, buftripolei4=None, buftripoler4=None, bufsizesend=0, bufsizerecv=0,
              bufsendr8=None, bufrecvr8=None, bufsendi4=None, bufrecvi4=None, bufsendr4=None, bufrecvr4=None,
              ndte=ndte, revised_evp=revised_evp, maskhalo_dyn=False, ncat=NCAT, kstrength=1, krdg_partic=1,
-             krdg_redist=1, mu_rdg=3.0, cf=17.0, grid_type="tripole" if dom.grid_tripole else "displaced_pole")
+             krdg_redist=1, mu_rdg=3.0, cf=17.0, calc_strair="ACCESS" not in macros, grid_type="tripole" if dom.grid_tripole else "displaced_pole")
     m.load(src["blocks"], ["get_block_parameter", "create_blocks", "ice_blocksgetnbrid", "get_block"],
            derived_arrays=["all_blocks"])
     m.load(src["bnd"], ["ice_haloincrementmsgcount", "ice_halomsgcreate", "ice_halocreate", "ice_haloupdate2dr8",
@@ -195,6 +198,9 @@ def main(out_path=OUT, big=False):
                "vocn": inp["vocn"], "ss_tltx": inp["ss_tltx"], "ss_tlty": inp["ss_tlty"], "cdn_ocn": inp["Cw"],
                "uvel": io["uvel"], "vvel": io["vvel"], "fm": io["fm"]}
         src.update({k: io[k] for k in io if k.startswith("stress")})
+        if "ACCESS" in macros:                     # wind stress from the coupler, already on the U grid
+            inp = dict(inp, strax=0.7 * inp["strairyT"] + 0.01, stray=-1.3 * inp["strairxT"])
+            src.update(strax=inp["strax"], stray=inp["stray"])
         for n in STATE_R8:
             g[n] = scatter(m, wins, src.get(n, zero))
         g["iceumask"] = scatter(m, wins, io["iceumask"] > 0, dtype=bool)
@@ -229,7 +235,7 @@ def main(out_path=OUT, big=False):
         key = cname + "__"
         pack[key + "dims"] = np.array([dom.nx, dom.ny, bsx, bsy, g["nblocks_x"], g["nblocks_y"], ndte], np.int64)
         pack[key + "flags"] = np.array([int(dom.ew_cyclic), int(dom.ns_tripole), int(dom.grid_tripole),
-                                        int("coupled" in macros), int(revised)], np.int64)
+                                        int("coupled" in macros), int(revised), int("ACCESS" in macros)], np.int64)
         pack[key + "dt"] = np.float64(case.dt)
         for n in fx.GRID_FIELDS + ("tmask", "umask"):
             pack[key + "grid__" + n] = grid.f[n]

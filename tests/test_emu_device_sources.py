@@ -239,7 +239,7 @@ def test_device_sources_match_reference_text(dev, dvec, name):
     _check_reference_text(dvec, name, case, layout)
 
 
-@pytest.mark.parametrize("name", ["tripole_2x2", "tripole_wet_4x1", "open_3x2"])
+@pytest.mark.parametrize("name", ["tripole_2x2", "tripole_wet_4x1", "open_3x2", "tripole_access_2x1"])
 def test_device_sources_match_reference_text_two_ranks(dev, dvec, name):
     case, kw, layout = driver_case(dvec, name)
     g = dev.EvpGroup(case.dom, case.ndte, case.dt, 2, strict=True, **kw)
@@ -249,6 +249,14 @@ def test_device_sources_match_reference_text_two_ranks(dev, dvec, name):
     finally:
         g.close()
     _check_reference_text(dvec, name, case, layout)
+
+
+def test_strax_without_stray_is_rejected(dev, dvec):
+    """evp_in_t.strax / stray (ACCESS, calc_strair = .false.): both or neither."""
+    case, kw, _ = driver_case(dvec, "tripole_access_2x1")
+    case.inp["stray"] = None
+    with pytest.raises(dev.EvpError):
+        dev.run_case(case, strict=True, **kw)
 
 
 def test_product_loader_has_no_host_fallback():

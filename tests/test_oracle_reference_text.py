@@ -248,7 +248,8 @@ def test_halo_stress_matches_reference_text(hvec, name):
 # several blocks with the reference's own halo code (tests/golden/make_driver_vectors.py)
 # ---------------------------------------------------------------------------------------------
 DRIVER_NPZ = os.path.join(os.path.dirname(__file__), "golden", "ref_driver_vectors.npz")
-DRIVER_CASES = ("tripole_2x2", "tripole_wet_4x1", "tripole_coupled_1x1", "open_3x2", "open_revised_2x1")
+DRIVER_CASES = ("tripole_2x2", "tripole_wet_4x1", "tripole_coupled_1x1", "open_3x2", "open_revised_2x1",
+                "tripole_access_2x1")
 HALOED = ("uvel", "vvel", "strength")         # fields whose ghost cells the driver updates before it returns
 
 
@@ -259,12 +260,14 @@ def dvec():
 
 def driver_case(dvec, name):
     nx, ny, bsx, bsy, nbx, nby, ndte = (int(x) for x in dvec[name + "__dims"])
-    cyc, trip, gtrip, coupled, revised = (int(x) for x in dvec[name + "__flags"])
+    cyc, trip, gtrip, coupled, revised, access = (int(x) for x in dvec[name + "__flags"])
     dom = fx.Domain(nx, ny, ew_cyclic=bool(cyc), ns_tripole=bool(trip), ns_open=not trip,
                     grid_tripole=bool(gtrip), name=name)
     get = lambda part, n: np.ascontiguousarray(dvec[f"{name}__{part}__{n}"])
     grid = fx.Grid(dom=dom, f={n: get("grid", n) for n in tuple(fx.GRID_FIELDS) + ("tmask", "umask")})
     inp = {n: get("in", n) for n in fx.IN_FIELDS}
+    if access:      # ACCESS build, calc_strair = .false.: the coupler's U-grid wind stress (ice_dyn_evp.F90:220-229)
+        inp["strax"], inp["stray"] = get("in", "strax"), get("in", "stray")
     io = {n: get("io", n) for n in fx.INOUT_FIELDS}
     io["iceumask"] = get("io", "iceumask")
     # the reference computes the strength inside evp (ice_strength on the icellt list); the oracle takes
@@ -311,6 +314,9 @@ def test_driver_cases_are_distinct(dvec):
     arlx1i, brlx, denom1, revp, ecci = dvec["open_revised_2x1__consts"]
     assert revp == 1.0
     assert dvec["open_3x2__consts"][3] == 0.0
+    # strairx is the coupler's field, ghost cells included, not the T-grid stress averaged to U points
+    assert np.array_equal(dvec["tripole_access_2x1__out__strairx"][0], dvec["tripole_access_2x1__in__strax"][:, :14])
+    assert np.abs(dvec["tripole_access_2x1__out__uvel"]).max() > 0.05
     top = dvec["tripole_wet_4x1__out__uvel"]
     nx = int(dvec["tripole_wet_4x1__dims"][0])
     # block 1 holds column 1, the last block column nx-1, of the top physical row: not antisymmetric
