@@ -320,7 +320,8 @@ def main():
         e2e_ms = allmax((time.perf_counter() - t0) * 1e3)
         plane = inp["aice"].nbytes
         iplane = io["iceumask"].nbytes
-        h2d = 12 * plane + 14 * plane + iplane
+        # in: 12 fields less ss_tltx/y, which tilt_mode = 0 does not read (not uploaded); inout: u, v, 12 stresses, iceumask
+        h2d = 10 * plane + 14 * plane + iplane
         d2h = 15 * plane + iplane + 19 * plane + iplane
         e2e = {"value": cs_per_step * args.steps / (e2e_ms * 1e-3), "unit": "cell-subcycles/s",
                "h2d_bytes_per_step": int(allsum(float(h2d))), "d2h_bytes_per_step": int(allsum(float(d2h))),

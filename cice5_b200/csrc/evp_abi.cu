@@ -555,6 +555,9 @@ int evp_gpu_upload(evp_handle_t *h, const evp_in_t *in, const evp_inout_t *io)
     if (h->strair_given) { src[4] = in->strax; src[5] = in->stray; }
     for (int p = 0; p < 12; ++p) {
         if (dstp[p] == I_STRENGTH && h->strength_from_itd) continue;      // computed on the device
+        // the sea-surface slope is read only where the tilt comes from it (#ifdef coupled,
+        // ice_dyn_shared.F90:601-602): two planes less to upload otherwise; the pointers may be NULL then
+        if ((dstp[p] == I_SSTLTX || dstp[p] == I_SSTLTY) && h->cfg.tilt_mode == 0) continue;
         TRY(h2d(h, dstp[p], src[p]));
     }
     // dynamic state always lands in copy A

@@ -86,7 +86,8 @@ typedef struct {
 /* Per-call inputs (ice_state.F90:54-56,155; ice_flux.F90:37-48; ice_atmo.F90:40). */
 typedef struct {
     const double *aice, *vice, *vsno, *aice_init;
-    const double *strairxT, *strairyT, *uocn, *vocn, *ss_tltx, *ss_tlty;
+    const double *strairxT, *strairyT, *uocn, *vocn;
+    const double *ss_tltx, *ss_tlty;    /* read (and uploaded) only when tilt_mode == 1; may be NULL otherwise */
     const double *Cdn_ocn;
     const double *strength;     /* host ice_strength result on the block's physical T cells */
     /* optional (NULL = the default build).  #ifdef ACCESS with calc_strair = .false.
