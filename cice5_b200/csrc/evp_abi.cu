@@ -34,6 +34,7 @@ thread_local char g_cuda_err[512] = "";
             return EVP_ERR_CUDA;                                                              \
         }                                                                                     \
     } while (0)
+#define TRY(x) do { int rc_ = (x); if (rc_ != EVP_OK) return rc_; } while (0)
 
 // ---- plane directory ----------------------------------------------------------------------
 enum Plane {
@@ -89,6 +90,7 @@ struct evp_handle {
     size_t arena_bytes = 0;
     size_t off_planes = 0, off_inbox = 0, off_flags = 0, off_int = 0, off_mask = 0, off_counts = 0, off_tflags = 0;
     int tflags_ld = 0, tstrips = 0;
+    std::vector<void *> pinned;                  // host arrays page-locked by evp_gpu_pin_host_arrays
     bool strair_given = false;                   // evp_in_t.strax/stray given: strairx/y are copies of them
     int t_n_small = 0, t_rows_small = 0;         // EVP_B200_GUIDED: the first t_n_small chunks are short
     int t_rpc = 0, t_chunks = 0, t_items = 0;    // TMA kernel work items: (strip, chunk of t_rpc rows)
@@ -439,7 +441,47 @@ int evp_gpu_finalize(evp_handle_t *h)
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     if (h->itd) cudaFree(h->itd);
     if (h->arena) cudaFree(h->arena);
+    for (void *p : h->pinned) cudaHostUnregister(p);
     delete h;
+    return EVP_OK;
+}
+
+int evp_gpu_pin_host_arrays(evp_handle_t *h, const evp_in_t *in, const evp_inout_t *io, const evp_out_t *out)
+{
+    if (!h) return EVP_ERR_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    const size_t cells = (size_t)h->nxb * h->nyb;
+    auto pin = [h](const void *cp, size_t bytes) -> int {
+        void *p = const_cast<void *>(cp);
+        if (!p) return EVP_OK;
+        for (void *q : h->pinned) if (q == p) return EVP_OK;
+        const cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterDefault);
+        if (e == cudaErrorHostMemoryAlreadyRegistered) { (void)cudaGetLastError(); return EVP_OK; }   // the caller's own
+        if (e != cudaSuccess) {
+            snprintf(g_cuda_err, sizeof(g_cuda_err), "cudaHostRegister(%zu bytes): %s", bytes, cudaGetErrorString(e));
+            (void)cudaGetLastError();
+            return EVP_ERR_CUDA;
+        }
+        h->pinned.push_back(p);
+        return EVP_OK;
+    };
+    const size_t r8 = cells * sizeof(double), i4 = cells * sizeof(int);
+    if (in) {
+        const double *f[14] = {in->aice, in->vice, in->vsno, in->aice_init, in->strairxT, in->strairyT, in->uocn,
+                               in->vocn, in->ss_tltx, in->ss_tlty, in->Cdn_ocn, in->strength, in->strax, in->stray};
+        for (const double *p : f) TRY(pin(p, r8));
+    }
+    if (io) {
+        TRY(pin(io->uvel, r8)); TRY(pin(io->vvel, r8)); TRY(pin(io->fm, r8)); TRY(pin(io->iceumask, i4));
+        for (int c = 0; c < 4; ++c) { TRY(pin(io->stressp[c], r8)); TRY(pin(io->stressm[c], r8)); TRY(pin(io->stress12[c], r8)); }
+    }
+    if (out) {
+        double *f[19] = {out->strairx, out->strairy, out->strtltx, out->strtlty, out->strocnx, out->strocny, out->strintx,
+                         out->strinty, out->strocnxT, out->strocnyT, out->divu, out->shear, out->rdg_conv, out->rdg_shear,
+                         out->prs_sig, out->uvel_init, out->vvel_init, out->tmass, out->strength};
+        for (double *p : f) TRY(pin(p, r8));
+        TRY(pin(out->icetmask, i4));
+    }
     return EVP_OK;
 }
 
@@ -479,7 +521,6 @@ static int d2h(evp_handle *h, int p, double *dst, cudaStream_t s = nullptr)
                          (size_t)h->nxb * sizeof(double), h->nyb, cudaMemcpyDeviceToHost, s ? s : h->stream));
     return EVP_OK;
 }
-#define TRY(x) do { int rc_ = (x); if (rc_ != EVP_OK) return rc_; } while (0)
 
 int evp_gpu_set_grid(evp_handle_t *h, const evp_grid_t *gr)
 {

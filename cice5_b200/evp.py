@@ -74,7 +74,7 @@ EXPORTS = ("evp_gpu_init", "evp_gpu_set_grid", "evp_gpu_run", "evp_gpu_upload", 
            "evp_gpu_download", "evp_gpu_compute_group", "evp_gpu_get_stats", "evp_gpu_synchronize", "evp_gpu_peer_blob_size",
            "evp_gpu_get_peer_blob", "evp_gpu_set_peers", "evp_gpu_finalize", "evp_gpu_strerror",
            "evp_gpu_last_cuda_error", "evp_gpu_device_count", "evp_gpu_get_trace", "evp_gpu_upload_itd",
-           "evp_gpu_principal_stress")
+           "evp_gpu_principal_stress", "evp_gpu_pin_host_arrays")
 
 _libs: dict = {}
 
@@ -216,6 +216,24 @@ class EvpGpu:
         """``call evp(dt)``: host arrays in, host arrays out (H2D + device solve + D2H)."""
         i, s, o = self._in_struct(inp), self._io_struct(io), self._out_struct(out)
         self._check(self.lib.evp_gpu_run(self._h, C.c_double(dt), C.byref(i), C.byref(s), C.byref(o)))
+
+    def pin_host(self, inp=None, io=None, out=None):
+        """Page-lock the caller's arrays once (evp_gpu_pin_host_arrays): for hosts whose arrays keep their
+        addresses, as the reference's static module arrays do.  Already page-locked arrays are left alone."""
+        si = self._in_struct_partial(inp) if inp is not None else None
+        sio = self._io_struct(io) if io is not None else None
+        so = self._out_struct(out) if out is not None else None
+        self.__dict__.setdefault("_keep_pinned", []).append((inp, io, out))     # the arrays must outlive the handle
+        self._check(self.lib.evp_gpu_pin_host_arrays(self._h, C.byref(si) if si else None,
+                                                     C.byref(sio) if sio else None, C.byref(so) if so else None))
+
+    @staticmethod
+    def _in_struct_partial(inp):
+        s = InS()
+        for n in IN_R8 + ("strax", "stray"):
+            key = "Cw" if n == "Cdn_ocn" and "Cdn_ocn" not in inp else n
+            setattr(s, n, _dp(inp.get(key)))
+        return s
 
     def upload_itd(self, aicen, vicen, aice0, kstrength=1, krdg_partic=1, krdg_redist=1, mu_rdg=3.0,
                    Cf=17.0):

@@ -171,6 +171,13 @@ int evp_gpu_peer_blob_size(void);
 int evp_gpu_get_peer_blob(evp_handle_t *h, void *blob);
 int evp_gpu_set_peers(evp_handle_t *h, const void *blobs_all_ranks);
 
+/* Optional, for hosts whose arrays keep their addresses (the reference's module arrays are static:
+ * source/ice_state.F90, ice_flux.F90): page-lock every non-NULL array of the three structs once, so that
+ * the per-call copies of evp_gpu_run run at the full host-link rate and asynchronously instead of through the
+ * driver's staging buffer.  Arrays that are already page-locked are left alone.  The registrations are
+ * released by evp_gpu_finalize; the arrays must outlive the handle.  Any argument may be NULL. */
+int evp_gpu_pin_host_arrays(evp_handle_t *h, const evp_in_t *in, const evp_inout_t *io, const evp_out_t *out);
+
 int evp_gpu_finalize(evp_handle_t *h);
 const char *evp_gpu_strerror(int status);
 const char *evp_gpu_last_cuda_error(void);

@@ -3,6 +3,9 @@
 
 #include <stdio.h>
 
+#include <mutex>
+#include <set>
+
 namespace emu {
 
 thread_local Fiber *cur = nullptr;
@@ -395,6 +398,17 @@ void enqueue(cudaStream_t s, std::function<void()> fn)
 // ---- runtime API -------------------------------------------------------------------------------------------
 const char *cudaGetErrorString(cudaError_t e) { return e == cudaSuccess ? "no error" : "cuda_emu error"; }
 cudaError_t cudaGetLastError() { return cudaSuccess; }
+namespace { std::mutex g_reg_mu; std::set<void *> g_registered; }
+cudaError_t cudaHostRegister(void *p, size_t, unsigned)
+{
+    std::lock_guard<std::mutex> lk(g_reg_mu);
+    return g_registered.insert(p).second ? cudaSuccess : cudaErrorHostMemoryAlreadyRegistered;
+}
+cudaError_t cudaHostUnregister(void *p)
+{
+    std::lock_guard<std::mutex> lk(g_reg_mu);
+    return g_registered.erase(p) ? cudaSuccess : cudaErrorInvalidValue;
+}
 cudaError_t cudaSetDevice(int) { return cudaSuccess; }
 cudaError_t cudaGetDeviceCount(int *n) { *n = 8; return cudaSuccess; }
 cudaError_t cudaDeviceGetAttribute(int *v, cudaDeviceAttr, int) { *v = 4; return cudaSuccess; }

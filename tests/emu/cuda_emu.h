@@ -190,7 +190,7 @@ inline unsigned long long emu_ld_acquire_u64(const void *p) { return __atomic_lo
 
 // ---- runtime API -----------------------------------------------------------------------------------------
 enum cudaError_t { cudaSuccess = 0, cudaErrorInvalidValue = 1, cudaErrorMemoryAllocation = 2, cudaErrorNotSupported = 801,
-                   cudaErrorPeerAccessAlreadyEnabled = 704 };
+                   cudaErrorPeerAccessAlreadyEnabled = 704, cudaErrorHostMemoryAlreadyRegistered = 712 };
 typedef cudaError_t cudaError;
 enum cudaMemcpyKind { cudaMemcpyHostToHost, cudaMemcpyHostToDevice, cudaMemcpyDeviceToHost, cudaMemcpyDeviceToDevice,
                       cudaMemcpyDefault };
@@ -215,6 +215,10 @@ typedef cudaGraphExec_t cudaGraphExec;
 
 const char *cudaGetErrorString(cudaError_t);
 cudaError_t cudaGetLastError();
+enum { cudaHostRegisterDefault = 0 };
+// page-locking: the host build keeps a set of registered ranges so that double registration is reported
+cudaError_t cudaHostRegister(void *, size_t, unsigned);
+cudaError_t cudaHostUnregister(void *);
 cudaError_t cudaSetDevice(int);
 cudaError_t cudaGetDeviceCount(int *);
 cudaError_t cudaDeviceGetAttribute(int *, cudaDeviceAttr, int);

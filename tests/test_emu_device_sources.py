@@ -251,6 +251,24 @@ def test_device_sources_match_reference_text_two_ranks(dev, dvec, name):
     _check_reference_text(dvec, name, case, layout)
 
 
+def test_pinned_host_arrays(dev):
+    """evp_gpu_pin_host_arrays: page-locks the caller's arrays once (twice is harmless), results unchanged,
+    registrations released with the handle."""
+    grid = fx.synthetic_tripole(40, 20)
+    case = fx.make_case(grid, "full", ndte=3, dt=3600.0)
+    ref, got = clone_case(case), clone_case(case)
+    orc.run_case(ref)
+    e = dev.EvpGpu.for_domain(got.dom, got.ndte, got.dt, strict=True)
+    try:
+        e.set_grid(grid.f)
+        e.pin_host(got.inp, got.io, got.out)
+        e.pin_host(got.inp, got.io, None)
+        e.evp(got.dt, got.inp, got.io, got.out)
+    finally:
+        e.close()
+    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+
+
 def test_strax_without_stray_is_rejected(dev, dvec):
     """evp_in_t.strax / stray (ACCESS, calc_strair = .false.): both or neither."""
     case, kw, _ = driver_case(dvec, "tripole_access_2x1")

@@ -24,10 +24,10 @@ nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > "$
 run tests_validated 900 python -m pytest tests -m gpu -x -q --deselect tests/test_gpu_revised_evp.py \
     --deselect tests/test_gpu_strength.py --deselect tests/test_gpu_zw_reference_text.py \
     --deselect tests/test_gpu_zx_wet_pole.py --deselect tests/test_gpu_zy_fullsize.py \
-    --deselect tests/test_gpu_zz_c_host.py
+    --deselect tests/test_gpu_zz_c_host.py --deselect tests/test_gpu_zv_pinned_host.py
 # 2. the rows whose first hardware run is pending, one file per process (a sticky CUDA error in one
 #    cannot poison the next), xfail marks ignored so that a failure shows its traceback
-for f in zw_reference_text zx_wet_pole revised_evp strength zz_c_host zy_fullsize; do
+for f in zw_reference_text zx_wet_pole revised_evp strength zz_c_host zv_pinned_host zy_fullsize; do
   run pending_$f 600 python -m pytest tests/test_gpu_$f.py -m gpu -q --runxfail -rA
 done
 # 3. the default bench line (also the reference arm, for the ratio)
