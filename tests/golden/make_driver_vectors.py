@@ -49,6 +49,14 @@ CASES = {
     # the ACCESS build with calc_strair = .false. (ice_dyn_evp.F90:220-245): strairx/y are the coupler's
     # U-grid stresses strax/stray, t2ugrid_vector is skipped
     "tripole_access_2x1": (lambda: fx.synthetic_tripole(24, 12), 12, 12, ("ACCESS",), False, 3, "full"),
+    # the ACCESS-OM production build, bld/Macros.nci:72,81: -DAusCOM -Dcoupled -DACCESS, with the namelist's ocean
+    # turning angle (cosw, sinw are variables there, ice_dyn_shared.F90:66-72) and use_ocnslope = .false.
+    # (drivers/auscom/cpl_parameters.F90:31: the tilt comes from the currents although `coupled` is defined) ...
+    "tripole_auscom_2x2": (lambda: fx.synthetic_tripole(24, 12), 12, 6, ("AusCOM", "coupled", "ACCESS"), False, 3, "full",
+                           {"use_ocnslope": False, "angle_deg": 25.0}),
+    # ... and with use_ocnslope = .true. (tilt from the sea-surface slope)
+    "tripole_auscom_slope_1x2": (lambda: fx.synthetic_tripole(24, 12), 24, 6, ("AusCOM", "coupled", "ACCESS"), False, 3,
+                                 "caps", {"use_ocnslope": True, "angle_deg": 0.0}),
 }
 # The reference's real gx3 grid and the 1-degree tripole: too large to commit field by field -- their inputs
 # are regenerated from cice5_b200.fixtures (deterministic) and only SHA-256 digests of the inputs and of every
@@ -72,7 +80,7 @@ def _lines(rel, defined=()):
     return fe.preprocess(open(os.path.join(REF, rel)).read(), defined)
 
 
-def machine(dom, bsx, bsy, macros, revised_evp, ndte):
+def machine(dom, bsx, bsy, macros, revised_evp, ndte, extra=None):
     ew = "cyclic" if dom.ew_cyclic else "closed"
     ns = "tripole" if dom.ns_tripole else "open"
     nsd = {"block_size_x": bsx, "block_size_y": bsy}
@@ -84,6 +92,10 @@ def machine(dom, bsx, bsy, macros, revised_evp, ndte):
         fe.parse_parameters(src[k], nsd)
     m = fe.Module(nsd)
     g = m.ns
+    if "AusCOM" in macros:          # namelist variables of that build (ice_init.F90:167; cpl_parameters.F90:31)
+        import math
+        a = math.radians(extra["angle_deg"])
+        g.update(cosw=math.cos(a), sinw=math.sin(a), use_ocnslope=extra["use_ocnslope"])
 
     @fe.fstub(["dist", "nprocs", "communicator", "numlocalblocks"], out=["nprocs", "communicator", "numlocalblocks"])
     def ice_distributionget(dist, nprocs=None, communicator=None, numlocalblocks=None):
@@ -176,12 +188,14 @@ def _digest(a) -> str:
 def main(out_path=OUT, big=False):
     pack = {}
     digests = {}
-    for cname, (factory, bsx, bsy, macros, revised, ndte, scenario) in (BIG_CASES if big else CASES).items():
+    for cname, spec in (BIG_CASES if big else CASES).items():
+        factory, bsx, bsy, macros, revised, ndte, scenario = spec[:7]
+        extra = spec[7] if len(spec) > 7 else None
         grid = factory()
         dom = grid.dom
         case = fx.make_case(grid, scenario, ndte=ndte, dt=3600.0)
         itd = fx.ice_itd(case.inp)
-        m = machine(dom, bsx, bsy, macros, revised, ndte)
+        m = machine(dom, bsx, bsy, macros, revised, ndte, extra)
         g = m.ns
         wins = windows(m, dom, bsx, bsy)
         shape = (dom.ny + 2, dom.nx + 2)
@@ -201,7 +215,7 @@ def main(out_path=OUT, big=False):
         if "ACCESS" in macros:                     # wind stress from the coupler, already on the U grid
             inp = dict(inp, strax=0.7 * inp["strairyT"] + 0.01, stray=-1.3 * inp["strairxT"])
             src.update(strax=inp["strax"], stray=inp["stray"])
-        for n in STATE_R8:
+        for n in STATE_R8 + (("sicemass",) if "AusCOM" in macros else ()):
             g[n] = scatter(m, wins, src.get(n, zero))
         g["iceumask"] = scatter(m, wins, io["iceumask"] > 0, dtype=bool)
         for n4, a4 in (("aicen", itd["aicen"]), ("vicen", itd["vicen"])):
@@ -235,7 +249,9 @@ def main(out_path=OUT, big=False):
         key = cname + "__"
         pack[key + "dims"] = np.array([dom.nx, dom.ny, bsx, bsy, g["nblocks_x"], g["nblocks_y"], ndte], np.int64)
         pack[key + "flags"] = np.array([int(dom.ew_cyclic), int(dom.ns_tripole), int(dom.grid_tripole),
-                                        int("coupled" in macros), int(revised), int("ACCESS" in macros)], np.int64)
+                                        int("coupled" in macros and not ("AusCOM" in macros and not extra["use_ocnslope"])),
+                                        int(revised), int("ACCESS" in macros)], np.int64)
+        pack[key + "angle"] = np.array([g["cosw"], g["sinw"]], float)
         pack[key + "dt"] = np.float64(case.dt)
         for n in fx.GRID_FIELDS + ("tmask", "umask"):
             pack[key + "grid__" + n] = grid.f[n]

@@ -249,7 +249,7 @@ def test_halo_stress_matches_reference_text(hvec, name):
 # ---------------------------------------------------------------------------------------------
 DRIVER_NPZ = os.path.join(os.path.dirname(__file__), "golden", "ref_driver_vectors.npz")
 DRIVER_CASES = ("tripole_2x2", "tripole_wet_4x1", "tripole_coupled_1x1", "open_3x2", "open_revised_2x1",
-                "tripole_access_2x1")
+                "tripole_access_2x1", "tripole_auscom_2x2", "tripole_auscom_slope_1x2")
 HALOED = ("uvel", "vvel", "strength")         # fields whose ghost cells the driver updates before it returns
 
 
@@ -275,7 +275,8 @@ def driver_case(dvec, name):
     inp["strength"] = orc.ice_strength(dom, inp["aice"], inp["vice"], get("itd", "aice0"), get("itd", "aicen"),
                                        get("itd", "vicen"))
     case = fx.Case(grid=grid, dt=float(dvec[name + "__dt"]), ndte=ndte, inp=inp, io=io, out=fx.zeroed_outputs(dom))
-    kw = dict(tilt_mode=coupled, revised_evp=bool(revised), strength_masked=1)
+    cosw, sinw = (float(x) for x in dvec[name + "__angle"])          # (1, 0) except in the AusCOM build's cases
+    kw = dict(tilt_mode=coupled, revised_evp=bool(revised), strength_masked=1, cosw=cosw, sinw=sinw)
     return case, kw, (bsx, bsy, nbx, nby)
 
 
@@ -317,6 +318,10 @@ def test_driver_cases_are_distinct(dvec):
     # strairx is the coupler's field, ghost cells included, not the T-grid stress averaged to U points
     assert np.array_equal(dvec["tripole_access_2x1__out__strairx"][0], dvec["tripole_access_2x1__in__strax"][:, :14])
     assert np.abs(dvec["tripole_access_2x1__out__uvel"]).max() > 0.05
+    # the production macro set: turning angle on, tilt from the currents although `coupled` is defined
+    assert dvec["tripole_auscom_2x2__angle"][1] > 0.4 and int(dvec["tripole_auscom_2x2__flags"][3]) == 0
+    assert int(dvec["tripole_auscom_slope_1x2__flags"][3]) == 1
+    assert not np.array_equal(dvec["tripole_auscom_2x2__out__uvel"], dvec["tripole_2x2__out__uvel"])
     top = dvec["tripole_wet_4x1__out__uvel"]
     nx = int(dvec["tripole_wet_4x1__dims"][0])
     # block 1 holds column 1, the last block column nx-1, of the top physical row: not antisymmetric
