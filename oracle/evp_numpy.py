@@ -196,10 +196,13 @@ def evp(case, cosw=1.0, sinw=0.0, tilt_mode=0, strength_masked=0, dt_init=None, 
     icetmask = im.astype(np.int32)
     umass = to_ugrid(tmass, g["tarea"], g["uarea"])                           # :218-219
     aiu = to_ugrid(inp["aice_init"], g["tarea"], g["uarea"])
-    w = inp["strairxT"].copy(); fx.halo_update(dom, w, fx.CENTER, fx.VECTOR, 0.0)   # :240-241
-    strairx = to_ugrid(w, g["tarea"], g["uarea"])
-    w = inp["strairyT"].copy(); fx.halo_update(dom, w, fx.CENTER, fx.VECTOR, 0.0)
-    strairy = to_ugrid(w, g["tarea"], g["uarea"])
+    if inp.get("strax") is not None:          # ACCESS, .not. calc_strair (:220-229): the coupler's U-grid stress
+        strairx, strairy = inp["strax"].copy(), inp["stray"].copy()
+    else:
+        w = inp["strairxT"].copy(); fx.halo_update(dom, w, fx.CENTER, fx.VECTOR, 0.0)   # :240-241
+        strairx = to_ugrid(w, g["tarea"], g["uarea"])
+        w = inp["strairyT"].copy(); fx.halo_update(dom, w, fx.CENTER, fx.VECTOR, 0.0)
+        strairy = to_ugrid(w, g["tarea"], g["uarea"])
     # evp_prep2 (ice_dyn_shared.F90:484-612)
     for n in fx.STRESS_FIELDS:
         if revised_evp:

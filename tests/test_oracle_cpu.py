@@ -23,10 +23,13 @@ def _run(case, **kw):
 @pytest.mark.parametrize("grid,scen,kw", [
     ("gx3", "full", {}),
     ("gx3", "caps", dict(cosw=0.9, sinw=float(np.sqrt(1 - 0.81)), tilt_mode=1, strength_masked=1)),
-    ("tp", "full", {}), ("tp", "caps", dict(strength_masked=1))])
+    ("tp", "full", {}), ("tp", "caps", dict(strength_masked=1)), ("tp_strax", "full", {})])
 def test_c_oracle_equals_numpy_restatement_bitwise(grid, scen, kw):
-    g = fx.synthetic_tripole(62, 40) if grid == "tp" else fx.make_grid(grid)
+    g = fx.synthetic_tripole(62, 40) if grid.startswith("tp") else fx.make_grid(grid)
     case = fx.make_case(g, scen, ndte=15, dt=3600.0)
+    if grid == "tp_strax":         # ACCESS build, calc_strair = .false. (ice_dyn_evp.F90:220-229)
+        case.inp["strax"] = 0.7 * case.inp["strairyT"] + 0.01
+        case.inp["stray"] = -1.3 * case.inp["strairxT"]
     a = _run(case, **kw)
     b = clone_case(case)
     nt, nu = evp_numpy.evp(b, **kw)
