@@ -301,6 +301,30 @@ def synthetic_displaced(nx: int, ny: int, kmt: np.ndarray | None = None, name: s
     return g
 
 
+def synthetic_closed(nx: int, ny: int, name: str = "") -> Grid:
+    """A regional basin: E-W and N-S closed (`ew_boundary_type = ns_boundary_type = 'closed'`), ocean up to
+    the west, east and north edges (only the two southern rows are land), so that the filled ghost ring of a
+    domain without neighbours matters to the cells next to it."""
+    dom = Domain(nx, ny, ew_cyclic=False, ns_tripole=False, ns_open=False, grid_tripole=False,
+                 name=name or f"closed_{nx}x{ny}")
+    dphi = np.deg2rad(20.0) / ny
+    dlam = np.deg2rad(40.0) / nx
+    j = np.arange(1, ny + 1, dtype="f8")
+    i = np.arange(1, nx + 1, dtype="f8")
+    ulat = np.deg2rad(60.0) + dphi * j
+    tlat = ulat - 0.5 * dphi
+    HTE = np.broadcast_to(RADIUS * dphi * (1.0 + 0.07 * np.sin(1.3 * i)), (ny, nx)).copy()
+    HTN = (RADIUS * np.cos(ulat) * dlam)[:, None] * (1.0 + 0.05 * np.cos(0.9 * i))[None, :]
+    ULAT = np.broadcast_to(ulat[:, None], (ny, nx)).copy()
+    kmt = np.ones((ny, nx), np.int32)
+    kmt[:2, :] = 0
+    kmt[ny // 2, nx // 3] = 0                        # an island
+    g = build_grid(dom, HTN, HTE, ULAT, kmt)
+    g.tlat = np.broadcast_to(tlat[:, None], (ny, nx)).copy()
+    g.tlon = np.broadcast_to(((i - 0.5) * dlam)[None, :], (ny, nx)).copy()
+    return g
+
+
 def gx3_grid() -> Grid:
     """The reference's real gx3 grid (100 x 116, displaced pole, E-W cyclic, N-S open;
     ``input_templates/gx3/ice_in:43-62``), lengths converted cm -> m as ``ice_grid.F90:1436``."""

@@ -46,6 +46,8 @@ CASES = {
     "tripole_coupled_1x1": (lambda: fx.synthetic_tripole(24, 12), 24, 12, ("coupled",), False, 3, "caps"),
     "open_3x2": (lambda: fx.synthetic_displaced(18, 12), 6, 6, (), False, 4, "full"),
     "open_revised_2x1": (lambda: fx.synthetic_displaced(18, 12), 9, 12, (), True, 3, "full"),
+    # a regional basin: E-W and N-S closed, ocean up to three of its edges
+    "closed_2x2": (lambda: fx.synthetic_closed(16, 12), 8, 6, (), False, 4, "full"),
     # the ACCESS build with calc_strair = .false. (ice_dyn_evp.F90:220-245): strairx/y are the coupler's
     # U-grid stresses strax/stray, t2ugrid_vector is skipped
     "tripole_access_2x1": (lambda: fx.synthetic_tripole(24, 12), 12, 12, ("ACCESS",), False, 3, "full"),
@@ -82,7 +84,7 @@ def _lines(rel, defined=()):
 
 def machine(dom, bsx, bsy, macros, revised_evp, ndte, extra=None):
     ew = "cyclic" if dom.ew_cyclic else "closed"
-    ns = "tripole" if dom.ns_tripole else "open"
+    ns = "tripole" if dom.ns_tripole else ("open" if dom.ns_open else "closed")
     nsd = {"block_size_x": bsx, "block_size_y": bsy}
     fe.parse_parameters(_lines("drivers/cice/ice_constants.F90"), nsd)
     src = {k: _lines(v, macros) for k, v in (("blocks", "source/ice_blocks.F90"), ("bnd", "mpi/ice_boundary.F90"),
@@ -250,7 +252,8 @@ def main(out_path=OUT, big=False):
         pack[key + "dims"] = np.array([dom.nx, dom.ny, bsx, bsy, g["nblocks_x"], g["nblocks_y"], ndte], np.int64)
         pack[key + "flags"] = np.array([int(dom.ew_cyclic), int(dom.ns_tripole), int(dom.grid_tripole),
                                         int("coupled" in macros and not ("AusCOM" in macros and not extra["use_ocnslope"])),
-                                        int(revised), int("ACCESS" in macros)], np.int64)
+                                        int(revised), int("ACCESS" in macros),
+                                        int(not dom.ns_tripole and not dom.ns_open)], np.int64)
         pack[key + "angle"] = np.array([g["cosw"], g["sinw"]], float)
         pack[key + "dt"] = np.float64(case.dt)
         for n in fx.GRID_FIELDS + ("tmask", "umask"):

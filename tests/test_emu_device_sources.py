@@ -239,7 +239,7 @@ def test_device_sources_match_reference_text(dev, dvec, name):
     _check_reference_text(dvec, name, case, layout)
 
 
-@pytest.mark.parametrize("name", ["tripole_2x2", "tripole_wet_4x1", "open_3x2", "tripole_access_2x1", "tripole_auscom_2x2"])
+@pytest.mark.parametrize("name", ["tripole_2x2", "tripole_wet_4x1", "open_3x2", "tripole_access_2x1", "tripole_auscom_2x2", "closed_2x2"])
 def test_device_sources_match_reference_text_two_ranks(dev, dvec, name):
     case, kw, layout = driver_case(dvec, name)
     g = dev.EvpGroup(case.dom, case.ndte, case.dt, 2, strict=True, **kw)

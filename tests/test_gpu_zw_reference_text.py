@@ -58,7 +58,7 @@ def test_device_matches_reference_text_one_rank(dvec, name):
     _check(dvec, name, case, layout)
 
 
-@pytest.mark.parametrize("name", ["tripole_2x2", "tripole_wet_4x1", "open_3x2", "tripole_access_2x1", "tripole_auscom_2x2"])
+@pytest.mark.parametrize("name", ["tripole_2x2", "tripole_wet_4x1", "open_3x2", "tripole_access_2x1", "tripole_auscom_2x2", "closed_2x2"])
 def test_device_matches_reference_text_two_ranks(dvec, name):
     case, kw, layout = driver_case(dvec, name)
     g = evp.EvpGroup(case.dom, case.ndte, case.dt, 2, strict=True, **kw)

@@ -249,7 +249,7 @@ def test_halo_stress_matches_reference_text(hvec, name):
 # ---------------------------------------------------------------------------------------------
 DRIVER_NPZ = os.path.join(os.path.dirname(__file__), "golden", "ref_driver_vectors.npz")
 DRIVER_CASES = ("tripole_2x2", "tripole_wet_4x1", "tripole_coupled_1x1", "open_3x2", "open_revised_2x1",
-                "tripole_access_2x1", "tripole_auscom_2x2", "tripole_auscom_slope_1x2")
+                "tripole_access_2x1", "tripole_auscom_2x2", "tripole_auscom_slope_1x2", "closed_2x2")
 HALOED = ("uvel", "vvel", "strength")         # fields whose ghost cells the driver updates before it returns
 
 
@@ -260,8 +260,8 @@ def dvec():
 
 def driver_case(dvec, name):
     nx, ny, bsx, bsy, nbx, nby, ndte = (int(x) for x in dvec[name + "__dims"])
-    cyc, trip, gtrip, coupled, revised, access = (int(x) for x in dvec[name + "__flags"])
-    dom = fx.Domain(nx, ny, ew_cyclic=bool(cyc), ns_tripole=bool(trip), ns_open=not trip,
+    cyc, trip, gtrip, coupled, revised, access, ns_closed = (int(x) for x in dvec[name + "__flags"])
+    dom = fx.Domain(nx, ny, ew_cyclic=bool(cyc), ns_tripole=bool(trip), ns_open=not trip and not ns_closed,
                     grid_tripole=bool(gtrip), name=name)
     get = lambda part, n: np.ascontiguousarray(dvec[f"{name}__{part}__{n}"])
     grid = fx.Grid(dom=dom, f={n: get("grid", n) for n in tuple(fx.GRID_FIELDS) + ("tmask", "umask")})
