@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Random small domains through the host build of the device sources (tests/emu) against the CPU oracle, bit for
-bit: tripole / displaced-pole grids of 4..78 x 4..29 cells, wet or dry poles, full / caps / half / no ice, 1-4
-ranks, classic / revised EVP, both tilt modes, a turning angle.
+bit: tripole / displaced-pole / closed-basin grids of 4..78 x 4..29 cells, wet or dry poles, full / caps / half /
+no ice, 1-4 ranks, classic / revised EVP, both tilt modes, a turning angle, the coupler's wind stress (strax/stray).
 
     python tools/fuzz_on_emulator.py SEED [tma|sweep] [CASES]
     EVP_B200_FOLD=kernel EVP_B200_EARLY_D2H=1 FUZZ_DEFINES="-DEVP_TMA_MERGE_UV=1 -DEVP_TMA_STATIC_FIRST=1" \\
@@ -38,7 +38,9 @@ with emu.patched(kernel=kernel, defines=defines) as evp:
         ndte = int(rng.integers(1, 6))
         wet = bool(tripole and rng.random() < 0.5)
         try:
-            grid = fx.synthetic_tripole(nx, ny, wet_poles=wet) if tripole else fx.synthetic_displaced(nx, ny)
+            closed = bool(not tripole and rng.random() < 0.35)
+            grid = fx.synthetic_tripole(nx, ny, wet_poles=wet) if tripole else (
+                fx.synthetic_closed(nx, ny) if closed else fx.synthetic_displaced(nx, ny))
             case = fx.make_case(grid, scen, ndte=ndte, dt=3600.0)
             mode = rng.random()
             if mode < 0.15:
@@ -46,6 +48,9 @@ with emu.patched(kernel=kernel, defines=defines) as evp:
             elif mode < 0.3:
                 for k in ("aice", "vice", "vsno", "aice_init"): case.inp[k][ny // 2:, :] = 0.0
             kw = {}
+            if rng.random() < 0.25:
+                case.inp["strax"] = 0.7 * case.inp["strairyT"] + 0.01
+                case.inp["stray"] = -1.3 * case.inp["strairxT"]
             if rng.random() < 0.3: kw["revised_evp"] = True
             if rng.random() < 0.3: kw["tilt_mode"] = 1
             if rng.random() < 0.3: kw.update(cosw=0.9, sinw=float(np.sqrt(1 - 0.81)))
