@@ -33,7 +33,7 @@ def pytest_collection_modifyitems(config, items):
         if tm is None:
             item.add_marker(pytest.mark.timeout(900, method="thread"))
         elif "method" not in tm.kwargs and len(tm.args) < 2:
-            item.add_marker(pytest.mark.timeout(*tm.args, method="thread", **tm.kwargs))
+            item.add_marker(pytest.mark.timeout(*tm.args, method="thread", **tm.kwargs), append=False)
 
 
 def _pending_on_hardware(item) -> bool:
