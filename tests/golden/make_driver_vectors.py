@@ -67,6 +67,9 @@ BIG_CASES = {
     "gx3_real_1x1": (lambda: fx.make_grid("gx3"), 100, 116, (), False, 3, "full"),
     "gx3_real_2x2": (lambda: fx.make_grid("gx3"), 50, 58, (), False, 3, "full"),
     "tp1_4x2": (lambda: fx.make_grid("tp1"), 90, 150, (), False, 2, "caps"),
+    # BASELINE.json's "ACCESS-OM 1 degree tripole 360x300" in its production build (bld/Macros.nci:72,81)
+    "tp1_auscom_4x2": (lambda: fx.make_grid("tp1"), 90, 150, ("AusCOM", "coupled", "ACCESS"), False, 2, "caps",
+                       {"use_ocnslope": False, "angle_deg": 25.0}),
 }
 DIGESTS = os.path.join(HERE, "ref_driver_digests.json")
 
@@ -236,7 +239,9 @@ def main(out_path=OUT, big=False):
         outs.update({k: k for k in io if k.startswith("stress")})
         if big:                                    # digests only; physical cells and whole blocks separately
             d = {"dims": [dom.nx, dom.ny, bsx, bsy, int(g["nblocks_x"]), int(g["nblocks_y"]), ndte],
-                 "scenario": scenario, "dt": case.dt,
+                 "scenario": scenario, "dt": case.dt, "access": "ACCESS" in macros,
+                 "kw": {"cosw": float(g["cosw"]), "sinw": float(g["sinw"]),
+                        "tilt_mode": int("coupled" in macros and not ("AusCOM" in macros and not extra["use_ocnslope"]))},
                  "inputs": {n: _digest(v) for n, v in list(inp.items()) + list(io.items()) + list(itd.items())},
                  "grid": {n: _digest(grid.f[n]) for n in fx.GRID_FIELDS + ("tmask", "umask")},
                  "physical": {}, "blocks": {}}

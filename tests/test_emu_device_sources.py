@@ -539,9 +539,10 @@ def test_random_small_domains_bitwise(dev):
         compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
 
 
-@pytest.mark.parametrize("name", ["gx3_real_1x1", "gx3_real_2x2"])
+@pytest.mark.parametrize("name", ["gx3_real_1x1", "gx3_real_2x2", "tp1_auscom_4x2"])
 def test_device_sources_match_reference_digests_on_the_real_gx3_grid(dev, name):
-    """The reference's real gx3 grid file: device sources == the reference text (SHA-256 of every field)."""
+    """The reference's real gx3 grid file, and the 1-degree tripole in the ACCESS-OM production build: device
+    sources == the reference text (SHA-256 of every field)."""
     from tests.test_oracle_reference_text import check_digests, digest_case
     case, kw, layout, d = digest_case(name)
     dev.run_case(case, strict=True, **kw)

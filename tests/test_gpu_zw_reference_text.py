@@ -70,7 +70,8 @@ def test_device_matches_reference_text_two_ranks(dvec, name):
     _check(dvec, name, case, layout)
 
 
-@pytest.mark.parametrize("name,nranks", [("gx3_real_1x1", 1), ("gx3_real_2x2", 2), ("tp1_4x2", 1), ("tp1_4x2", 4)])
+@pytest.mark.parametrize("name,nranks", [("gx3_real_1x1", 1), ("gx3_real_2x2", 2), ("tp1_4x2", 1), ("tp1_4x2", 4),
+                                         ("tp1_auscom_4x2", 1), ("tp1_auscom_4x2", 2)])
 def test_device_matches_reference_digests(name, nranks):
     """The reference's real gx3 grid and the 1-degree tripole: the reference-text outputs are kept as SHA-256
     digests (tests/golden/ref_driver_digests.json), the inputs are regenerated from the fixtures."""

@@ -350,13 +350,16 @@ def digest_case(name):
     grid = fx.make_grid("gx3" if name.startswith("gx3") else "tp1")
     case = fx.make_case(grid, d["scenario"], ndte=ndte, dt=d["dt"])
     itd = fx.ice_itd(case.inp)
+    if d.get("access"):        # the coupler's wind stress, exactly as tests/golden/make_driver_vectors.py makes it
+        case.inp["strax"] = 0.7 * case.inp["strairyT"] + 0.01
+        case.inp["stray"] = -1.3 * case.inp["strairxT"]
     have = {n: _sha(v) for n, v in list(case.inp.items()) + list(case.io.items()) + list(itd.items())}
     have_grid = {n: _sha(grid.f[n]) for n in tuple(fx.GRID_FIELDS) + ("tmask", "umask")}
     if have != d["inputs"] or have_grid != d["grid"]:
         pytest.skip("fixtures regenerate different bits here than where the digests were made")
     case.inp["strength"] = orc.ice_strength(grid.dom, case.inp["aice"], case.inp["vice"], itd["aice0"], itd["aicen"],
                                             itd["vicen"])
-    return case, dict(strength_masked=1), (bsx, bsy, nbx, nby), d
+    return case, dict(strength_masked=1, **d.get("kw", {})), (bsx, bsy, nbx, nby), d
 
 
 def check_digests(case, layout, d):
@@ -373,7 +376,7 @@ def check_digests(case, layout, d):
     assert len(d["physical"]) == 34
 
 
-@pytest.mark.parametrize("name,nslabs", [("gx3_real_1x1", 1), ("gx3_real_2x2", 2), ("tp1_4x2", 4)])
+@pytest.mark.parametrize("name,nslabs", [("gx3_real_1x1", 1), ("gx3_real_2x2", 2), ("tp1_4x2", 4), ("tp1_auscom_4x2", 2)])
 def test_whole_call_matches_reference_digests(name, nslabs):
     case, kw, layout, d = digest_case(name)
     orc.run_case(case, nslabs=nslabs, **kw)
