@@ -11,6 +11,8 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    config.addinivalue_line("markers", "isolated: device test run in a child pytest process of its own "
+                                       "(code on its first hardware run); a failure of the child is a failure")
 
 
 def _have_gpu() -> bool:
@@ -37,23 +39,22 @@ def pytest_collection_modifyitems(config, items):
 
 
 def _pending_on_hardware(item) -> bool:
-    return item.get_closest_marker("gpu") is not None and item.get_closest_marker("xfail") is not None
+    return item.get_closest_marker("gpu") is not None and item.get_closest_marker("isolated") is not None
 
 
 @pytest.hookimpl(tryfirst=True)
 def pytest_pyfunc_call(pyfuncitem):
-    """Device tests still waiting for their first hardware run (gpu + xfail marks) execute in a child
-    pytest process of their own, killed at its deadline: a hang or a sticky CUDA error in code that
-    has never met a device cannot stall or poison the validated suite running in this process."""
+    """Device tests marked `isolated` (code on its first hardware run) execute in a child pytest
+    process of their own, killed at its deadline: a hang or a sticky CUDA error in code that has
+    never met a device cannot stall or poison the rest of the suite.  No xfail is involved: a
+    failing child fails the test (round 1 hid a real failure behind xfail(strict=False))."""
     import subprocess
-    if (not _pending_on_hardware(pyfuncitem) or os.environ.get("EVP_TEST_CHILD")
-            or pyfuncitem.config.getoption("runxfail", False)):
+    if not _pending_on_hardware(pyfuncitem) or os.environ.get("EVP_TEST_CHILD"):
         return None
     tm = pyfuncitem.get_closest_marker("timeout")
     limit = max(30.0, float(tm.args[0]) - 30.0) if tm and tm.args else 270.0
     env = dict(os.environ, EVP_TEST_CHILD="1")
-    cmd = [sys.executable, "-m", "pytest", pyfuncitem.nodeid, "-m", "gpu", "-q", "-x", "--runxfail",
-           "-p", "no:cacheprovider"]
+    cmd = [sys.executable, "-m", "pytest", pyfuncitem.nodeid, "-m", "gpu", "-q", "-x", "-p", "no:cacheprovider"]
     try:
         r = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=limit)
     except subprocess.TimeoutExpired:

@@ -5,7 +5,7 @@ restarted from zero in evp_prep2 (:492-504), revp in stepu (:715,732-734).
 
 NOT YET RUN ON HARDWARE: this row was written after the round's GPU budget was spent (DESIGN.md
 section 8); the CPU oracle side is tested in tests/test_oracle_cpu.py.  The tests are marked
-xfail(strict=False) until their first run on a B200 so that a defect here cannot hide the
+(first hardware run: round 1 end tier, all passed) -- a defect here must not hide behind the
 validated classic-EVP parity suite behind `pytest -x`; an XPASS is the expected outcome."""
 import numpy as np
 import pytest
@@ -14,8 +14,7 @@ from cice5_b200 import evp, fixtures as fx
 from tests.util import clone_case, compare_cases, phys
 from tests.test_gpu_parity import OUT_CHECK
 
-pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300), pytest.mark.usefixtures("subcycle_kernel"),
-              pytest.mark.xfail(strict=False, reason="revised EVP: first hardware run pending (round 1 GPU budget spent)")]
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300), pytest.mark.usefixtures("subcycle_kernel")]
 
 
 def _xmin(grid):

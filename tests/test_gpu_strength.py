@@ -17,8 +17,7 @@ import pytest
 from cice5_b200 import evp, fixtures as fx
 from tests.util import STATE, REL_TOL, clone_case, compare_cases, phys
 
-pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300),
-              pytest.mark.xfail(strict=False, reason="device ice_strength: first hardware run pending (round 1 GPU budget spent)")]
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300)]
 
 
 def _run_pair(grid, scenario, ndte, **modes):

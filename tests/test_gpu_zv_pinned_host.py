@@ -15,8 +15,7 @@ from cice5_b200 import evp, fixtures as fx
 from tests.util import clone_case, compare_cases
 from tests.test_gpu_parity import OUT_CHECK
 
-pytestmark = [pytest.mark.gpu, pytest.mark.timeout(600),
-              pytest.mark.xfail(strict=False, reason="evp_gpu_pin_host_arrays: first hardware run pending")]
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(600)]
 
 
 def _timed_calls(e, case, n=3):

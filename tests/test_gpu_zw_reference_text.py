@@ -25,8 +25,7 @@ import pytest
 from cice5_b200 import evp, fixtures as fx
 from tests.test_oracle_reference_text import DRIVER_CASES, DRIVER_NPZ, HALOED, blocks_from_global, driver_case
 
-pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300), pytest.mark.usefixtures("subcycle_kernel"),
-              pytest.mark.xfail(strict=False, reason="device vs reference text: first hardware run pending")]
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300), pytest.mark.usefixtures("subcycle_kernel")]
 
 
 @pytest.fixture(scope="module")

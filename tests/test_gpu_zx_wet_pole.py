@@ -19,8 +19,7 @@ from cice5_b200 import evp, fixtures as fx
 from tests.util import clone_case, compare_cases, phys
 from tests.test_gpu_parity import OUT_CHECK
 
-pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300), pytest.mark.usefixtures("subcycle_kernel"),
-              pytest.mark.xfail(strict=False, reason="wet-pole velocity fold: first hardware run pending")]
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300), pytest.mark.usefixtures("subcycle_kernel")]
 
 
 def _case():

@@ -13,8 +13,7 @@ from cice5_b200 import evp, fixtures as fx
 from tests.util import clone_case, compare_cases, phys
 from tests.test_gpu_parity import OUT_CHECK, _oracle
 
-pytestmark = [pytest.mark.gpu, pytest.mark.timeout(900),
-              pytest.mark.xfail(strict=False, reason="full-size parity: first hardware run pending (round 1 GPU budget spent)")]
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(900)]
 
 
 def test_quarter_degree_one_call_bitwise():

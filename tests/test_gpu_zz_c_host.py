@@ -41,7 +41,6 @@ def test_c_host_links_and_fails_loudly_without_a_device(tmp_path, have_gpu):
 
 @pytest.mark.gpu
 @pytest.mark.timeout(300)
-@pytest.mark.xfail(strict=False, reason="C host example: first hardware run pending (round 1 GPU budget spent)")
 def test_c_host_runs_evp_and_matches_the_oracle(tmp_path):
     r = subprocess.run([_compile(tmp_path)], capture_output=True, text=True, timeout=240)
     assert r.returncode == 0, r.stdout + r.stderr
