@@ -9,10 +9,13 @@
 // Everything of ridge_itd that the strength needs is a running scalar here: the cumulative
 // distribution G(n) is swept once for its normalisation and once more for the participation
 // function, so no per-category arrays live in registers beyond what one category needs.
-// exp / sqrt are CUDA's (<= 1 ulp); the CPU oracle uses libm, so parity of `strength` is to a few
-// ulp, not bitwise, when krdg_partic = 1 (the default).
+// sqrt is IEEE; exp is evp_exp (evp_exp.h): double-double evaluation rounded once, correctly rounded, the
+// same definition the CPU oracle compiles -- so `strength` is bitwise equal to the oracle in every mode,
+// the default exponential participation function included (CUDA's own exp is 1 ulp and differs from every
+// libm; at ndte = 120 that ulp grows beyond 1e-10 on ill-conditioned states).
 #pragma once
 #include "evp_kernels.cuh"
+#include "evp_exp.h"
 
 namespace evp {
 
@@ -34,7 +37,7 @@ __global__ void ice_strength_kernel(const __grid_constant__ StrengthArgs a)
 
     if (a.kstrength != 1) {        // Hibler 79 on the physical cells (:2259-2265), 0 elsewhere
         const bool phys = c >= 1 && c <= a.nxb - 2 && r >= 1 && r <= a.nyb - 2;
-        a.strength[q] = phys ? 2.75e4 * a.vice[q] * exp(-20.0 * (1.0 - a.aice[q])) : 0.0;
+        a.strength[q] = phys ? 2.75e4 * a.vice[q] * evp_exp(-20.0 * (1.0 - a.aice[q])) : 0.0;
         return;
     }
 
@@ -48,11 +51,11 @@ __global__ void ice_strength_kernel(const __grid_constant__ StrengthArgs a)
     const double work = 1.0 / Gtop;
 
     const double Gstari = 1.0 / Gstar, astari = 1.0 / astar;
-    const double xtmp = 1.0 / (1.0 - exp(-astari));                  // :1108
+    const double xtmp = 1.0 / (1.0 - evp_exp(-astari));                  // :1108
     // participation of open water, category 0 (:1085-1095 / :1110-1122)
     double Gm1 = 0.0;                       // Gsum(n-1), normalised (Gsum(-1) = 0 is never scaled)
     double Gn = G0raw * work;               // Gsum(n)
-    double Em1 = exp(-Gm1 * astari) * xtmp, En = exp(-Gn * astari) * xtmp;
+    double Em1 = evp_exp(-Gm1 * astari) * xtmp, En = evp_exp(-Gn * astari) * xtmp;
     auto partic = [&](double lo, double hi, double elo, double ehi) -> double {
         if (a.krdg_partic != 0) return elo - ehi;
         if (hi < Gstar) return Gstari * (hi - lo) * (2.0 - (lo + hi) * Gstari);
@@ -68,7 +71,7 @@ __global__ void ice_strength_kernel(const __grid_constant__ StrengthArgs a)
         if (present) Graw = Graw + an;
         Gm1 = Gn; Em1 = En;
         Gn = Graw * work;
-        En = exp(-Gn * astari) * xtmp;
+        En = evp_exp(-Gn * astari) * xtmp;
         const double ap = partic(Gm1, Gn, Em1, En);
         double krdg = 1.0, hrmin = 0.0, hrmax = 0.0, hrexp = 0.0, hi = 0.0;
         if (present) {

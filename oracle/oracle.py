@@ -59,7 +59,8 @@ class Stats(C.Structure):
 def build(force: bool = False) -> str:
     if force or not os.path.exists(_SO) or \
             os.path.getmtime(_SO) < max(os.path.getmtime(os.path.join(_HERE, f))
-                                        for f in ("evp_oracle.c", "strength_oracle.c")):
+                                        for f in ("evp_oracle.c", "strength_oracle.c", "strength_oracle.h",
+                                                  "../cice5_b200/csrc/evp_exp.h")):
         subprocess.run(["make", "-C", _HERE] + (["-B"] if force else []), check=True,
                        stdout=subprocess.DEVNULL)
     return _SO
@@ -169,18 +170,19 @@ def principal_stress(sp1, sm1, s121, prs):
 
 class StrengthCfg(C.Structure):
     _fields_ = [(n, C.c_int) for n in ("nx", "ny", "ncat", "kstrength", "krdg_partic", "krdg_redist")] + \
-               [(n, C.c_double) for n in ("mu_rdg", "Cf", "rhow", "rhoi", "gravit")]
+               [(n, C.c_double) for n in ("mu_rdg", "Cf", "rhow", "rhoi", "gravit")] + [("exp_mode", C.c_int)]
 
 
 def ice_strength(dom, aice, vice, aice0, aicen, vicen, cellmask=None, kstrength=1, krdg_partic=1,
-                 krdg_redist=1, mu_rdg=3.0, Cf=17.0):
+                 krdg_redist=1, mu_rdg=3.0, Cf=17.0, cr_exp=False):
     """ice_strength (source/ice_mechred.F90:2111-2269) on global-with-ghost planes; aicen / vicen
-    are (ncat, ny+2, nx+2).  cellmask (int32, non-zero = in the icellt list) or None = all cells."""
+    are (ncat, ny+2, nx+2).  cellmask (int32, non-zero = in the icellt list) or None = all cells.
+    cr_exp: the correctly rounded evp_exp (what the device uses) instead of libm's exp."""
     from cice5_b200 import fixtures as fx
     ncat = aicen.shape[0]
     cfg = StrengthCfg(nx=dom.nx, ny=dom.ny, ncat=ncat, kstrength=kstrength, krdg_partic=krdg_partic,
                       krdg_redist=krdg_redist, mu_rdg=mu_rdg, Cf=Cf, rhow=fx.RHOW, rhoi=fx.RHOI,
-                      gravit=fx.GRAVIT)
+                      gravit=fx.GRAVIT, exp_mode=1 if cr_exp else 0)
     out = np.zeros(aice.shape)
     f = lib().strength_oracle_run
     rc = f(C.byref(cfg), _dp(aice), _dp(vice), _dp(aice0), _dp(np.ascontiguousarray(aicen)),
@@ -188,3 +190,11 @@ def ice_strength(dom, aice, vice, aice0, aicen, vicen, cellmask=None, kstrength=
     if rc != 0:
         raise RuntimeError(f"strength_oracle_run failed with status {rc}")
     return out
+
+
+def cr_exp(x):
+    """evp_exp (cice5_b200/csrc/evp_exp.h, the exp shared by the device kernels and this oracle) on an array."""
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    y = np.empty_like(x)
+    lib().strength_oracle_cr_exp(C.c_longlong(x.size), _dp(x), _dp(y))
+    return y

@@ -15,7 +15,10 @@
  * Pinned bit for bit to the reference's own ice_strength / ridge_itd text, executed mechanically
  * (tests/golden/make_reference_vectors.py -> tests/test_oracle_reference_text.py, all four
  * krdg_partic x krdg_redist combinations and kstrength = 0); an independent numpy restatement is
- * oracle/strength_numpy.py.  exp() and sqrt() are libm's.
+ * oracle/strength_numpy.py.  sqrt() is IEEE; exp() is libm's (cfg->exp_mode = 0: what the mechanical
+ * execution of the reference text used) or evp_exp (exp_mode = 1: correctly rounded, the same definition the
+ * device kernel compiles -- the two differ where glibc's exp is not correctly rounded, about 1 argument in
+ * 1000, by one ulp).
  *
  * Arrays: (ny+2) x (nx+2) global-with-ghost planes, i fastest; aicen / vicen are ncat such planes
  * one after the other (Fortran (nx_block, ny_block, ncat)).  `cellmask` selects the cells of the
@@ -25,6 +28,9 @@
 #include <stddef.h>
 
 #include "strength_oracle.h"
+/* the one definition of the correctly rounded exp shared with the device kernels (a header of plain IEEE
+ * operations, no device code): exp_mode = 1 */
+#include "../cice5_b200/csrc/evp_exp.h"
 
 #define NCAT_MAX 16
 
@@ -42,6 +48,8 @@ int strength_oracle_run(const strength_oracle_cfg *cfg, const double *aice, cons
     const double Gstar = 0.15, astar = 0.05, maxraft = c1, Hstar = 25.0;
     const double Pstar = 2.75e4, Cstar = 20.0;
     const double Gstari = c1 / Gstar, astari = c1 / astar;                /* :982-984 */
+    const int cr = cfg->exp_mode == 1;
+#define EXPF(x) (cr ? evp_exp(x) : exp(x))
     if (ncat < 1 || ncat > NCAT_MAX) return 1;
 
     for (size_t q = 0; q < n; ++q) strength[q] = c0;                       /* :2175 */
@@ -51,7 +59,7 @@ int strength_oracle_run(const strength_oracle_cfg *cfg, const double *aice, cons
         for (int j = 1; j <= cfg->ny; ++j)                                 /* jlo..jhi, ilo..ihi */
             for (int i = 1; i <= cfg->nx; ++i) {
                 const size_t q = (size_t)j * gx + i;
-                strength[q] = Pstar * vice[q] * exp(-Cstar * (c1 - aice[q]));
+                strength[q] = Pstar * vice[q] * EXPF(-Cstar * (c1 - aice[q]));
             }
         return 0;
     }
@@ -91,8 +99,8 @@ int strength_oracle_run(const strength_oracle_cfg *cfg, const double *aice, cons
                     apartic[k] = Gstari * (Gstar - Gsum[k - 1]) * (c2 - (Gsum[k - 1] + Gstar) * Gstari);
             }
         } else {                                                           /* exponential, :1108-1122 */
-            const double xtmp = c1 / (c1 - exp(-astari));
-            for (int k = -1; k <= ncat; ++k) Gsum[k] = exp(-Gsum[k] * astari) * xtmp;
+            const double xtmp = c1 / (c1 - EXPF(-astari));
+            for (int k = -1; k <= ncat; ++k) Gsum[k] = EXPF(-Gsum[k] * astari) * xtmp;
             for (int k = 0; k <= ncat; ++k) apartic[k] = Gsum[k - 1] - Gsum[k];
         }
 
@@ -145,4 +153,11 @@ int strength_oracle_run(const strength_oracle_cfg *cfg, const double *aice, cons
         strength[q] = cfg->Cf * Cp * str / aksum;                          /* :2249 */
     }
     return 0;
+}
+#undef EXPF
+
+/* evp_exp on n arguments: lets tests/test_oracle_cpu.py check the shared definition against exact arithmetic */
+void strength_oracle_cr_exp(long long n, const double *x, double *y)
+{
+    for (long long i = 0; i < n; ++i) y[i] = evp_exp(x[i]);
 }

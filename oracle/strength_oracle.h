@@ -15,12 +15,17 @@ typedef struct {
     int krdg_redist;     /* 0 Hibler 80, 1 exponential (default)      (:59-60)                    */
     double mu_rdg, Cf;   /* namelist: 3 / 17 (ice_init.F90:276-277)                               */
     double rhow, rhoi, gravit;
+    int exp_mode;        /* 0: libm exp (what the reference-text vectors were produced with);
+                          * 1: evp_exp (cice5_b200/csrc/evp_exp.h), the correctly rounded exp the device uses */
 } strength_oracle_cfg;
 
 /* strength = 0 outside the list; cellmask NULL = every cell is in the list */
 int strength_oracle_run(const strength_oracle_cfg *cfg, const double *aice, const double *vice,
                         const double *aice0, const double *aicen, const double *vicen,
                         const int *cellmask, double *strength);
+
+/* y[i] = evp_exp(x[i]) (cice5_b200/csrc/evp_exp.h) */
+void strength_oracle_cr_exp(long long n, const double *x, double *y);
 
 #ifdef __cplusplus
 }

@@ -185,7 +185,8 @@ def _build(LIB: str, force: bool, defines: tuple) -> str:
     srcdir = os.path.join(BUILD, "src")
     os.makedirs(srcdir, exist_ok=True)
     sources = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh")))
-    deps = [os.path.join(CSRC, f) for f in sources] + [os.path.join(HERE, f) for f in ("cuda_emu.h", "cuda_emu.cpp", "emu.py")]
+    plain = sorted(f for f in os.listdir(CSRC) if f.endswith(".h"))      # plain C headers: included as they are
+    deps = [os.path.join(CSRC, f) for f in sources + plain] + [os.path.join(HERE, f) for f in ("cuda_emu.h", "cuda_emu.cpp", "emu.py")]
     deps.append(os.path.join(ROOT, "include", "evp_b200.h"))
     if not force and os.path.exists(LIB) and all(os.path.getmtime(d) <= os.path.getmtime(LIB) for d in deps):
         return LIB
@@ -195,7 +196,7 @@ def _build(LIB: str, force: bool, defines: tuple) -> str:
         with open(os.path.join(srcdir, f + (".cpp" if f.endswith(".cu") else "")), "w") as fh:
             fh.write(out)
     cmd = ["g++", "-std=c++17", "-O1", "-g", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared", "-pthread",
-           "-DEVP_STRICT=1", *defines, "-w", "-I", HERE, "-I", srcdir, "-o", LIB,
+           "-DEVP_STRICT=1", *defines, "-w", "-I", HERE, "-I", srcdir, "-I", CSRC, "-o", LIB,
            os.path.join(srcdir, "evp_abi.cu.cpp"), os.path.join(HERE, "cuda_emu.cpp")]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:

@@ -145,14 +145,15 @@ def test_revised_evp_two_ranks_two_calls_bitwise(dev):
                                    dict(krdg_partic=0, krdg_redist=1), dict(krdg_partic=1, krdg_redist=0),
                                    dict(kstrength=0)])
 def test_device_ice_strength_bitwise(dev, modes):
-    """ice_strength_kernel from the uploaded thickness distribution.  On the host both sides call libm's
-    exp, so even the exponential participation function must agree bit for bit (on a GPU: a few ulp)."""
+    """ice_strength_kernel from the uploaded thickness distribution.  Both sides evaluate the correctly rounded
+    evp_exp (csrc/evp_exp.h), so even the exponential participation function must agree bit for bit -- here
+    and on a GPU."""
     grid = fx.make_grid("gx3")
     case = fx.make_case(grid, "caps", ndte=4)
     itd = fx.ice_itd(case.inp)
     ref = clone_case(case)
     ref.inp["strength"] = orc.ice_strength(grid.dom, case.inp["aice"], case.inp["vice"], itd["aice0"], itd["aicen"],
-                                           itd["vicen"], **modes)
+                                           itd["vicen"], cr_exp=True, **modes)
     masked = 0 if modes.get("kstrength", 1) == 0 else 1
     orc.run_case(ref, strength_masked=masked)
     got = clone_case(case)

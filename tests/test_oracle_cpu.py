@@ -4,6 +4,8 @@ golden vectors for this path; tests/test_oracle_reference_text
 oracle's arithmetic to the reference's subroutine texts instead."""
 import os
 
+import math
+
 import numpy as np
 import pytest
 
@@ -203,6 +205,39 @@ def test_strength_c_oracle_equals_numpy_restatement(grid, scen, partic, redist):
         assert np.array_equal(a, b)                       # no exp: the same IEEE operations
     else:                                                 # numpy's vector exp vs libm: last-bit differences
         assert np.max(np.abs(a - b) / np.maximum(np.abs(a), 1e-300)) < 4e-16
+
+
+def test_cr_exp_is_correctly_rounded():
+    """evp_exp (csrc/evp_exp.h: the one exp the device kernels and the oracle share) against exact rational
+    arithmetic: decimal's exp at 70 digits, rounded to the nearest double by Fraction.__float__.  Arguments:
+    the path's domain [-20, 0] densely, the whole normal range sparsely, the structured values ridge_itd
+    produces (-G/astar with G = k/n), and edge values."""
+    from decimal import Decimal, getcontext
+    from fractions import Fraction
+    getcontext().prec = 70
+    rng = np.random.default_rng(20261105)
+    xs = np.concatenate([rng.uniform(-20.0, 0.0, 6000), rng.uniform(-700.0, 700.0, 1500),
+                         -np.arange(0, 1001, 7) / 1000.0 / 0.05, -rng.uniform(0, 1, 500) * (1.0 / 0.05),
+                         np.array([0.0, -0.0, 1.0, -1.0, -20.0, 1e-300, -1e-300, 1e-17, -1e-17, 0.5, -0.5,
+                                   2.0 ** -30, -(2.0 ** -30), 88.0, -88.0, 699.5, -699.5])])
+    got = orc.cr_exp(xs)
+    want = np.array([float(Fraction(Decimal(float(x)).exp())) for x in xs])
+    assert np.array_equal(got, want), f"{np.count_nonzero(got != want)} of {xs.size} not correctly rounded"
+    # libm's exp is within one ulp of it (and not always equal: that is why the device cannot use "the" exp)
+    lm = np.array([math.exp(float(x)) for x in xs])
+    assert np.max(np.abs(lm - want) / np.spacing(want)) <= 1.0
+
+
+@pytest.mark.parametrize("partic,redist,ks", [(1, 1, 1), (1, 0, 1), (1, 1, 0)])
+def test_strength_with_cr_exp_within_ulps_of_libm_build(partic, redist, ks):
+    """exp_mode 1 (evp_exp, the device's) against exp_mode 0 (libm, what the reference-text vectors pin):
+    the same statements, exp differing by at most one ulp in about one argument in a thousand."""
+    g, st, itd = _itd_case("tp1", "caps")
+    kw = dict(kstrength=ks, krdg_partic=partic, krdg_redist=redist)
+    a = orc.ice_strength(g.dom, st["aice"], st["vice"], itd["aice0"], itd["aicen"], itd["vicen"], **kw)
+    b = orc.ice_strength(g.dom, st["aice"], st["vice"], itd["aice0"], itd["aicen"], itd["vicen"], cr_exp=True, **kw)
+    assert np.array_equal(a == 0, b == 0) and b.max() > 1.0e3
+    assert np.max(np.abs(a - b) / np.maximum(np.abs(a), 1e-300)) < 2e-14
 
 
 def test_strength_list_semantics_hibler_and_itd_fixture():

@@ -34,13 +34,5 @@ run ncu_launches 400 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,d
     --log-file "$O.launches.csv" python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e
 run ncu_full 600 ncu --set full --import-source on --clock-control none -k regex:evp_subcycle_tma_kernel -s 130 -c 2 \
     -o "$O.subcycle_full" -f python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e
-# sanitizers on the small grids
-for tool in memcheck synccheck racecheck; do
-  for k in tma sweep; do
-    run san_${tool}_gx3_$k 300 compute-sanitizer --tool $tool --error-exitcode 9 python tools/sanitize_case.py gx3 $k 3
-    run san_${tool}_tp_$k 300 compute-sanitizer --tool $tool --error-exitcode 9 python tools/sanitize_case.py tp96x40 $k 3
-  done
-done
-run san_memcheck_tp_tma_r2 300 compute-sanitizer --tool memcheck --error-exitcode 9 python tools/sanitize_case.py tp96x40 tma 3 2
 grep -h '^{' "$O".bench*.log | cut -c1-300
 cat "$O.rc"
