@@ -17,6 +17,7 @@
 #include "evp_kernels.cuh"
 #include "evp_prep.cuh"
 #include "evp_subcycle_tma.cuh"
+#include "evp_loop_tma.cuh"
 #include "evp_strength.cuh"
 
 using namespace evp;
@@ -92,30 +93,26 @@ struct evp_handle {
     int tflags_ld = 0, tstrips = 0;
     std::vector<void *> pinned;                  // host arrays page-locked by evp_gpu_pin_host_arrays
     bool strair_given = false;                   // evp_in_t.strax/stray given: strairx/y are copies of them
-    int t_n_small = 0, t_rows_small = 0;         // EVP_B200_GUIDED: the first t_n_small chunks are short
     int t_rpc = 0, t_chunks = 0, t_items = 0;    // TMA kernel work items: (strip, chunk of t_rpc rows)
     size_t off_trace = 0;                        // u64 trace[ndte][8] (EVP_B200_TRACE=1)
     bool trace_on = false;
     size_t off_gflags = 0;                       // per strip row: bit2 metrics, bit3 tinyarea reproducible from HTE/HTN
-    size_t off_queue = 0;                        // int queue[ndte], done[ndte], done_bnd[ndte], item_count[2], item_list[t_items]
+    size_t off_queue = 0;                        // int queue[ndte], done[ndte], done_bnd[ndte], item_count[4], item_list[t_items]
+    // dependency counters of the persistent loop kernel (evp_loop_tma.cuh), u64: topflag[8], fold_flag, top_count,
+    // pad to 16, wflag[t_chunks], eflag[t_chunks], tflag[t_items].  Peers write topflag / wflag / eflag, so the
+    // region sits before every per-rank-sized one and t_chunks is the same on all ranks.
+    size_t off_lflags = 0;
+    bool use_loop = false;        // the ndte loop as ONE persistent kernel (default with the TMA kernel; EVP_B200_LOOP=0: off)
     char *peer_arena[kMaxRanks] = {nullptr};
     bool peer_opened[kMaxRanks] = {false};
     bool grid_set = false, uploaded = false, peers_set = false;
     int parity = 0;               // which ping-pong copy holds the current state (0 = A)
     int halo_seq = 0;             // halo operations issued in this compute (inbox buffer = seq & 1)
     cudaStream_t stream = nullptr, own_stream = nullptr;
-    // EVP_B200_EARLY_D2H=1 (experiment): evp_gpu_run copies the outputs that are
-    // final before the subcycle loop back on a second stream while the loop runs
-    cudaStream_t copy_stream = nullptr;
-    bool early_d2h = false;
-    evp_inout_t *early_io = nullptr;   // set by evp_gpu_run for the duration of its compute
-    evp_out_t *early_out = nullptr;
-    bool early_issued = false;         // the early copies of this call are on copy_stream
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaGraphExec_t loop_graph[2] = {nullptr, nullptr};   // per starting ping-pong parity
     int h_error = 0;
     bool use_tma = false;         // subcycle kernel v2 (TMA ring) instead of v1 (register sweep)
-    bool fold_in_kernel = false;  // EVP_B200_FOLD=kernel: tripole fold inside the TMA subcycle kernel (experiment)
     bool shared_stream = false;   // inside evp_gpu_compute_group with more than one rank
     int sm_count = 148;
     CUtensorMap mapS, mapS2, mapT1, mapT3, mapT4, mapT10, mapU, mapU8, mapM;
@@ -159,7 +156,12 @@ struct evp_handle {
     int *done(int ksub) const { return reinterpret_cast<int *>(arena + off_queue) + cfg.ndte + ksub; }
     int *done_bnd(int ksub) const { return reinterpret_cast<int *>(arena + off_queue) + 2 * cfg.ndte + ksub; }
     int *item_count() const { return reinterpret_cast<int *>(arena + off_queue) + 3 * cfg.ndte; }   // [2]
-    int *item_list() const { return reinterpret_cast<int *>(arena + off_queue) + 3 * cfg.ndte + 2; }
+    int *item_list() const { return reinterpret_cast<int *>(arena + off_queue) + 3 * cfg.ndte + 4; }
+    unsigned long long *lflags(int rank = -1) const
+    {
+        char *base = (rank < 0 || rank == cfg.rank) ? arena : peer_arena[rank];
+        return reinterpret_cast<unsigned long long *>(base + off_lflags);
+    }
     unsigned long long *counts() const
     {
         return reinterpret_cast<unsigned long long *>(arena + off_counts);
@@ -255,6 +257,10 @@ int make_tensor_maps(evp_handle *h)
     CK(cudaFuncSetAttribute(evp_subcycle_tma_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                             kTmaStages * kStageBytes));
     CK(cudaFuncSetAttribute(evp_subcycle_tma_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            kTmaStages * kStageBytes));
+    CK(cudaFuncSetAttribute(evp_loop_tma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            kTmaStages * kStageBytes));
+    CK(cudaFuncSetAttribute(evp_loop_tma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                             kTmaStages * kStageBytes));
     return EVP_OK;
 }
@@ -362,39 +368,30 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
     h->off_counts = off; off = align_up(off + 64, 256);
     h->tstrips = (g.nxl + kTmaUCols - 1) / kTmaUCols;
     h->tflags_ld = (int)align_up((size_t)h->nyb + 4, 16);
-    h->off_tflags = off; off = align_up(off + (size_t)h->tstrips * h->tflags_ld, 256);
-    h->off_gflags = off; off = align_up(off + (size_t)h->tstrips * h->tflags_ld, 256);
-    {   // work items of the TMA kernel: enough of them (about 8 per resident CTA) that the dynamic
-        // queue evens out land / open-ocean items, tall enough that the redundant first row of an
-        // item (velocities of row r0-1) stays a few per cent; small grids: one item per CTA
+    {   // work items of the TMA kernels: (strip of 124 U columns) x (chunk of t_rpc rows).  The chunk height is
+        // derived from the WIDEST slab so that every rank cuts its rows the same way: the persistent loop kernel
+        // matches a tile with its E-W neighbour on the next rank by chunk number.
         int sms = 148;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device);
         const long long slots = (long long)kTmaBlocksPerSM * sms;
-        // rows per item: about 4 items per resident CTA (drawn heaviest first from the dynamic
-        // queue, so land / open-ocean items even out), at most 32 rows (a grid that is mostly
-        // ice-free keeps enough items: caps scenario, 48 rows: -17 %); the cost of an item beyond
-        // its rows is one extra stage with the velocities of row r0-1
-        long long rpc = ((long long)h->tstrips * g.ny + 4 * slots - 1) / (4 * slots);
+        const long long wstrips = (maxw + kTmaUCols - 1) / kTmaUCols;
+        // about 4 items per resident CTA, at most 32 rows (a grid that is mostly ice-free keeps enough items:
+        // caps scenario, 48 rows: -17 %), at least 4; the cost of an item beyond its rows is one extra stage
+        // with the velocities of row r0-1
+        long long rpc = (wstrips * g.ny + 4 * slots - 1) / (4 * slots);
         rpc = rpc < 4 ? 4 : (rpc > 32 ? 32 : rpc);
         if (const char *ev = getenv("EVP_B200_RPC")) rpc = atoi(ev);      // tuning experiments
         rpc = rpc < 2 ? 2 : (rpc > 64 ? 64 : rpc);
         h->t_rpc = (int)rpc;
-        // EVP_B200_GUIDED="percent,rows" (experiment, -DEVP_TMA_GUIDED=1 builds only): that share of the rows, from the
-        // south end, is cut into chunks of `rows` rows; they sort behind the full chunks in the work list
-        if (const char *gv = kGuided ? getenv("EVP_B200_GUIDED") : nullptr) {
-            int pct = 0, rs = 0;
-            if (sscanf(gv, "%d,%d", &pct, &rs) == 2 && pct > 0 && pct <= 100 && rs >= 2 && rs < h->t_rpc) {
-                h->t_rows_small = rs;
-                h->t_n_small = (int)((long long)g.ny * pct / 100 / rs);
-            }
-        }
-        const int rows_left = g.ny - h->t_n_small * h->t_rows_small;
-        h->t_chunks = h->t_n_small + (rows_left + h->t_rpc - 1) / h->t_rpc;
+        h->t_chunks = (g.ny + h->t_rpc - 1) / h->t_rpc;
         h->t_items = h->tstrips * h->t_chunks;
     }
+    h->off_lflags = off; off = align_up(off + (16 + 2 * (size_t)h->t_chunks + h->t_items) * sizeof(unsigned long long), 256);
+    h->off_tflags = off; off = align_up(off + (size_t)h->tstrips * h->tflags_ld, 256);
+    h->off_gflags = off; off = align_up(off + (size_t)h->tstrips * h->tflags_ld, 256);
     h->trace_on = getenv("EVP_B200_TRACE") != nullptr;
     h->off_trace = off;  off = align_up(off + (size_t)cfg->ndte * 8 * sizeof(unsigned long long), 256);
-    h->off_queue = off;  off = align_up(off + (3 * (size_t)cfg->ndte + 2 + h->t_items) * sizeof(int), 256);
+    h->off_queue = off;  off = align_up(off + (3 * (size_t)cfg->ndte + 4 + h->t_items) * sizeof(int), 256);
     h->arena_bytes = off;
     cudaError_t e = cudaMalloc(&h->arena, h->arena_bytes);
     if (e != cudaSuccess) {
@@ -405,18 +402,13 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
     CK(cudaMemset(h->arena, 0, h->arena_bytes));
     CK(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
     h->stream = h->own_stream;
-    {
-        const char *ev = getenv("EVP_B200_EARLY_D2H");
-        h->early_d2h = ev && strcmp(ev, "1") == 0;
-        if (h->early_d2h) CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
-    }
     for (auto &ev : h->ev) CK(cudaEventCreate(&ev));
     memset(&h->stats, 0, sizeof(h->stats));
     {
         const char *kv = getenv("EVP_B200_KERNEL");          // "tma" (default) | "sweep"
         h->use_tma = !(kv && strcmp(kv, "sweep") == 0);
-        const char *fv = getenv("EVP_B200_FOLD");            // "launch" (default) | "kernel"
-        h->fold_in_kernel = fv && strcmp(fv, "kernel") == 0;
+        const char *lv = getenv("EVP_B200_LOOP");            // "1" (default) | "0": one launch per subcycle
+        h->use_loop = h->use_tma && !(lv && strcmp(lv, "0") == 0);
         cudaDeviceProp prop;
         CK(cudaGetDeviceProperties(&prop, cfg->device));
         h->sm_count = prop.multiProcessorCount;
@@ -437,7 +429,6 @@ int evp_gpu_finalize(evp_handle_t *h)
     for (int r = 0; r < kMaxRanks; ++r)
         if (h->peer_opened[r]) cudaIpcCloseMemHandle(h->peer_arena[r]);
     for (auto &ev : h->ev) if (ev) cudaEventDestroy(ev);
-    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     if (h->itd) cudaFree(h->itd);
     if (h->arena) cudaFree(h->arena);
@@ -642,38 +633,11 @@ int evp_gpu_upload_itd(evp_handle_t *h, const evp_itd_t *itd)
     return EVP_OK;
 }
 
-// outputs O_STRAIRX + p that no kernel touches after evp_prep2 (ice_dyn_evp.F90:240-310): strairx, strairy,
-// strtltx, strtlty, uvel_init, vvel_init; likewise fm, iceumask, tmass and strength (after its halo update)
-static const bool kFinalBeforeLoop[17] = {true, true, true, true, false, false, false, false, false, false,
-                                          false, false, false, false, false, true, true};
-
-// EVP_B200_EARLY_D2H: called by evp_gpu_compute once every launch of the call is enqueued.  The copies wait
-// on the event that closes the prep phase and then run on copy_stream beside the subcycle loop.
-static int issue_early_d2h(evp_handle *h)
-{
-    evp_inout_t *io = h->early_io;
-    evp_out_t *out = h->early_out;
-    if (!h->early_d2h || !io || !out || h->shared_stream) return EVP_OK;
-    cudaStream_t s = h->copy_stream;
-    CK(cudaStreamWaitEvent(s, h->ev[1], 0));
-    double *dst[17] = {out->strairx, out->strairy, out->strtltx, out->strtlty, nullptr, nullptr, nullptr, nullptr,
-                       nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, out->uvel_init, out->vvel_init};
-    h->early_issued = true;
-    for (int p = 0; p < 17; ++p)
-        if (kFinalBeforeLoop[p]) TRY(d2h(h, O_STRAIRX + p, dst[p], s));
-    TRY(d2h(h, W_TMASS, out->tmass, s));
-    TRY(d2h(h, W_STRENGTH, out->strength, s));
-    TRY(d2h(h, S_FM, io->fm, s));
-    TRY(d2h_i(h, 2, io->iceumask, s));
-    return EVP_OK;
-}
-
 int evp_gpu_download(evp_handle_t *h, evp_inout_t *io, evp_out_t *out)
 {
     if (!h) return EVP_ERR_ARG;
     if (!h->uploaded) return EVP_ERR_STATE;
     CK(cudaSetDevice(h->cfg.device));
-    const bool early = h->early_issued && io == h->early_io && out == h->early_out;   // those are on their way
     if (io) {
         const int U = h->parity ? S_UB : S_UA, V = h->parity ? S_VB : S_VA;
         const int S = h->parity ? S_STRB : S_STRA;
@@ -684,28 +648,20 @@ int evp_gpu_download(evp_handle_t *h, evp_inout_t *io, evp_out_t *out)
             TRY(d2h(h, S + 4 + c, io->stressm[c]));
             TRY(d2h(h, S + 8 + c, io->stress12[c]));
         }
-        if (!early) {
-            TRY(d2h(h, S_FM, io->fm));
-            TRY(d2h_i(h, 2, io->iceumask));
-        }
+        TRY(d2h(h, S_FM, io->fm));
+        TRY(d2h_i(h, 2, io->iceumask));
     }
     if (out) {
         double *dst[17] = {out->strairx, out->strairy, out->strtltx, out->strtlty, out->strocnx, out->strocny,
                            out->strintx, out->strinty, out->strocnxT, out->strocnyT, out->divu, out->shear,
                            out->rdg_conv, out->rdg_shear, out->prs_sig, out->uvel_init, out->vvel_init};
         for (int p = 0; p < 17; ++p)
-            if (!(early && kFinalBeforeLoop[p])) TRY(d2h(h, O_STRAIRX + p, dst[p]));
-        if (!early) {
-            TRY(d2h(h, W_TMASS, out->tmass));
-            TRY(d2h(h, W_STRENGTH, out->strength));
-        }
+            TRY(d2h(h, O_STRAIRX + p, dst[p]));
+        TRY(d2h(h, W_TMASS, out->tmass));
+        TRY(d2h(h, W_STRENGTH, out->strength));
         TRY(d2h_i(h, 3, out->icetmask));
     }
     CK(cudaStreamSynchronize(h->stream));
-    if (early) {
-        CK(cudaStreamSynchronize(h->copy_stream));
-        h->early_issued = false;
-    }
     return EVP_OK;
 }
 
@@ -727,6 +683,19 @@ struct Launcher {
     cudaStream_t s() const { return h->stream; }
 };
 
+// the persistent loop kernel needs its own stream per rank (a kernel must never wait for a kernel queued
+// behind it): evp_gpu_compute_group, which drives all ranks through one stream, keeps a launch per subcycle
+bool loop_mode(const evp_handle *h) { return h->use_loop && h->use_tma && !h->shared_stream; }
+
+// device-side waits give up after this long (EVP_B200_SYNC_TIMEOUT_S, default 10 s): the error word is set,
+// every later wait of the call returns at once and the call ends with EVP_ERR_PEER
+unsigned long long sync_timeout_ns()
+{
+    double s = 10.0;
+    if (const char *ev = getenv("EVP_B200_SYNC_TIMEOUT_S")) { const double v = atof(ev); if (v > 0.0) s = v; }
+    return (unsigned long long)(s * 1.0e9);
+}
+
 void fill_sync_args(const evp_handle *h, SyncArgs &a)
 {
     memset(&a, 0, sizeof(a));
@@ -734,7 +703,7 @@ void fill_sync_args(const evp_handle *h, SyncArgs &a)
     a.epoch = h->flags() + kMaxRanks;
     for (int r = 0; r < h->cfg.nranks; ++r) a.flags[r] = h->flags(r);
     a.error = h->dev_error();
-    a.timeout_ns = 10ull * 1000ull * 1000ull * 1000ull;
+    a.timeout_ns = sync_timeout_ns();
 }
 
 int launch_signal(Launcher &L)
@@ -869,6 +838,58 @@ void fill_loop_args(const evp_handle *h, int from_parity, int inbox_buf, LoopArg
     a.k = h->k;
 }
 
+// all ndte subcycles as one persistent kernel (evp_loop_tma.cuh): work items ordered by (subcycle, item),
+// per-tile dependency counters instead of launch boundaries and cross-rank barriers
+void add_loop(Builder &B, int from_parity)
+{
+    evp_handle *h = B.h;
+    const int buf0 = B.seq & 1;
+    B.seq += h->cfg.ndte;                        // one inbox buffer per subcycle, alternating
+    B.op([h, from_parity, buf0](Launcher &L) {
+        LoopTmaArgs t;
+        memset(&t, 0, sizeof(t));
+        fill_loop_args(h, from_parity, buf0, t.a);
+        t.a.rows_per_chunk = h->t_rpc;
+        const int nr = h->cfg.nranks;
+        t.plane_state[0] = S_UA; t.plane_state[1] = S_UB;
+        t.plane_t = kTGroup; t.plane_u = kUGroup;
+        t.state[0] = h->plane(S_UA); t.state[1] = h->plane(S_UB);
+        if (!h->west_closed()) { t.west_state[0] = h->plane(S_UA, h->west()); t.west_state[1] = h->plane(S_UB, h->west()); }
+        if (!h->east_closed()) { t.east_state[0] = h->plane(S_UA, h->east()); t.east_state[1] = h->plane(S_UB, h->east()); }
+        t.plane_elems = h->plane_elems;
+        for (int b = 0; b < 2; ++b)
+            for (int r = 0; r < nr; ++r) t.inbox[b][r] = h->inbox(b, r);
+        t.parity0 = from_parity; t.inbox0 = buf0;
+        t.strips = h->tstrips; t.chunks = h->t_chunks; t.nsteps = h->cfg.ndte;
+        t.has_fold = h->g.tripole ? 1 : 0;
+        t.queue = h->queue(0); t.item_list = h->item_list(); t.item_count = h->item_count();
+        t.tile_flags = h->tflags(); t.flags_ld = h->tflags_ld;
+        t.water_is_ocn = (h->cfg.cosw == 1.0 && h->cfg.sinw == 0.0) ? 1 : 0;
+        t.puny = 1.0e-11;
+        unsigned long long *lf = h->lflags();
+        t.topflag = lf; t.fold_flag = lf + 8; t.top_count = lf + 9;
+        t.tflag = lf + 16 + 2 * (size_t)h->t_chunks;
+        t.ew_self = (nr == 1 && h->g.ew_cyclic) ? 1 : 0;
+        if (nr > 1 && !h->west_closed()) { t.wflag = lf + 16; t.pub_w = h->lflags(h->west()) + 16 + h->t_chunks; }
+        if (nr > 1 && !h->east_closed()) { t.eflag = lf + 16 + h->t_chunks; t.pub_e = h->lflags(h->east()) + 16; }
+        for (int r = 0; r < nr; ++r) t.pub_top[r] = h->lflags(r);
+        t.rank = h->cfg.rank; t.nranks = nr;
+        t.error = h->dev_error();
+        t.timeout_ns = sync_timeout_ns();
+        const CUtensorMap &mapU = t.water_is_ocn ? h->mapU8 : h->mapU;
+        const int slots = kTmaBlocksPerSM * h->sm_count;
+        const long long want = 2LL * (h->t_items + 1);        // small grids: two subcycles' worth of CTAs in flight
+        const int grid = (int)(want < slots ? want : slots);
+        const size_t smem = (size_t)kTmaStages * kStageBytes;
+        auto kern = h->cfg.revised_evp ? evp_loop_tma_kernel<true> : evp_loop_tma_kernel<false>;
+        kern<<<grid, (kTmaConsumers + 1) * 32, smem, L.s()>>>(h->mapS, h->mapS2, h->mapT1, h->mapT3, h->mapT4, h->mapT10,
+                                                               mapU, h->mapM, t);
+        ++L.n;
+        return EVP_OK;
+    });
+    B.sync();      // the peers' last fold has read its inbox before the post-loop halos write into it
+}
+
 // one subcycle: stress + stepu + halo pushes fused; [sync]; then the tripole fold of the new u, v
 void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
 {
@@ -877,13 +898,8 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
     // N > 1 on a tripole grid with the TMA kernel: the cross-rank barrier between the subcycle
     // kernel and the fold is fused into both -- the last CTA to finish signals the peers, the fold
     // kernel waits for theirs -- 2 launches per subcycle instead of 4
-    // EVP_B200_FOLD=kernel (experiment): the fold moves into the subcycle kernel as
-    // well -- 1 launch per subcycle, on one rank too
-    // (not when all ranks share one stream of one device, evp_gpu_compute_group: a kernel that waits for a
-    // peer whose kernel is queued behind it would never end)
-    const bool fold_in_kernel = h->fold_in_kernel && !h->shared_stream && h->use_tma && h->g.tripole;
-    const bool fused_sync = (h->cfg.nranks > 1 || fold_in_kernel) && h->use_tma && h->g.tripole;
-    B.op([h, from_parity, last, buf, ksub, fused_sync, fold_in_kernel](Launcher &L) {
+    const bool fused_sync = h->cfg.nranks > 1 && h->use_tma && h->g.tripole;
+    B.op([h, from_parity, last, buf, ksub, fused_sync](Launcher &L) {
         const Geom &g = h->g;
         LoopArgs a;
         fill_loop_args(h, from_parity, buf, a);
@@ -905,10 +921,8 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
             t.a.rows_per_chunk = h->t_rpc;
             t.chunks = h->t_chunks;
             t.items = h->t_items;
-            t.n_small = h->t_n_small; t.rows_small = h->t_rows_small;
             t.queue = h->queue(ksub - 1); t.item_list = h->item_list(); t.item_count = h->item_count();
             t.fused_signal = fused_sync ? 1 : 0;
-            t.fold_in_kernel = fold_in_kernel ? 1 : 0;
             t.done = h->done(ksub - 1); t.done_bnd = h->done_bnd(ksub - 1);
             fill_sync_args(h, t.sync);
             t.trace = h->trace(ksub - 1);
@@ -930,7 +944,7 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
         return EVP_OK;
     });
     if (!fused_sync) B.sync();
-    if (h->g.tripole && !fold_in_kernel) {
+    if (h->g.tripole) {
         B.op([h, from_parity, buf, fused_sync, ksub](Launcher &L) {
             const Geom &g = h->g;
             double *u1 = h->plane(from_parity ? S_UA : S_UB), *v1 = h->plane(from_parity ? S_VA : S_VB);
@@ -1046,10 +1060,21 @@ void build_program(evp_handle *h, double dt, Program &P)
             dim3 grid(h->tstrips, (h->g.ny + 4 + 3) / 4);
             tile_flags_kernel<<<grid, 128, 0, s>>>(h->mask(), h->ldm, h->g.nxl, h->g.ny, h->tstrips, h->tflags(),
                                                   h->tflags_ld, h->gflags());
+            ItemListLoop lp;
+            memset(&lp, 0, sizeof(lp));
+            if (loop_mode(h)) {
+                const int nr = h->cfg.nranks;
+                lp.natural = 1;
+                lp.misc = h->lflags();
+                lp.tflag = h->lflags() + 16 + 2 * (size_t)h->t_chunks;
+                // my edge strips are the east ghost tiles of my west neighbour and the west ghost tiles of my east one
+                if (nr > 1 && !h->west_closed()) lp.pub_w = h->lflags(h->west()) + 16 + h->t_chunks;
+                if (nr > 1 && !h->east_closed()) lp.pub_e = h->lflags(h->east()) + 16;
+            }
             item_list_kernel<<<1, kSortThreads, 0, s>>>(h->tflags(), h->tflags_ld, h->tstrips, h->t_chunks, h->t_rpc,
-                                                h->t_n_small, h->t_rows_small, h->g.ny,
+                                                h->g.ny,
                                                 h->g.tripole ? 1 : 0, h->west_closed() ? 0 : 1, h->east_closed() ? 0 : 1,
-                                                h->item_list(), h->item_count(), h->queue(0), 3 * h->cfg.ndte);
+                                                h->item_list(), h->item_count(), h->queue(0), 3 * h->cfg.ndte, lp);
             L.n += 2;
         }
         CK(cudaGetLastError());
@@ -1070,9 +1095,14 @@ void build_program(evp_handle *h, double dt, Program &P)
     // ---- subcycling (:336-410) ----
     P.loop_begin = P.ops.size();
     int par = cur;
-    for (int ksub = 1; ksub <= cfg.ndte; ++ksub) {
-        add_subcycle(B, par, ksub == cfg.ndte, ksub);
-        par ^= 1;
+    if (loop_mode(h)) {
+        add_loop(B, par);
+        par ^= cfg.ndte & 1;
+    } else {
+        for (int ksub = 1; ksub <= cfg.ndte; ++ksub) {
+            add_subcycle(B, par, ksub == cfg.ndte, ksub);
+            par ^= 1;
+        }
     }
     P.loop_end = P.ops.size();
     P.end_parity = par;
@@ -1192,10 +1222,6 @@ int evp_gpu_compute(evp_handle_t *h, double dt)
     long long n_loop = 0;
     TRY(exec_range(L, P, 0, P.loop_begin));
     TRY(exec_loop(L, P, n_loop));
-    // once the loop is enqueued: a copy into pageable memory blocks this thread, but beside the running loop;
-    // and before the finish phase, whose last step (the counters, 16 bytes into the pageable handle) blocks
-    // until the whole call is through
-    TRY(issue_early_d2h(h));
     TRY(exec_range(L, P, P.loop_end, P.ops.size()));
     CK(cudaGetLastError());
     return finish_compute(h, P, L.n, n_loop);
@@ -1249,17 +1275,8 @@ int evp_gpu_run(evp_handle_t *h, double dt, const evp_in_t *in, evp_inout_t *io,
 {
     if (!h || !in || !io) return EVP_ERR_ARG;
     TRY(evp_gpu_upload(h, in, io));
-    h->early_io = io; h->early_out = out; h->early_issued = false;
-    const int rc = evp_gpu_compute(h, dt);
-    h->early_io = nullptr; h->early_out = nullptr;
-    if (rc != EVP_OK) {
-        if (h->early_issued) { cudaStreamSynchronize(h->copy_stream); h->early_issued = false; }
-        return rc;
-    }
-    h->early_io = io; h->early_out = out;            // lets download recognise the buffers of this call
-    const int rc2 = evp_gpu_download(h, io, out);
-    h->early_io = nullptr; h->early_out = nullptr;
-    return rc2;
+    TRY(evp_gpu_compute(h, dt));
+    return evp_gpu_download(h, io, out);
 }
 
 int evp_gpu_principal_stress(evp_handle_t *h, double *sig1, double *sig2)

@@ -192,7 +192,8 @@ __device__ __forceinline__ void stress_cell(
 // Push a freshly computed top-row velocity (U rows ny-1, ny) into the tripole inbox of every
 // rank whose local columns (ghosts included) fold onto this global column
 // (copy-in :3737-3750, copy-out source nx - ig :3768 with ioffset = 1 :811,874-877).
-__device__ __forceinline__ void tripole_push(const LoopArgs &a, int c, int rowsel, double u, double v)
+__device__ __forceinline__ void tripole_push(const LoopArgs &a, double *const *inbox, int c, int rowsel, double u,
+                                             double v)
 {
     const int ig = a.lo + c;                  // global column, 1-based
     int X = a.nx_global - ig;                 // the column whose fold source is ig
@@ -200,19 +201,23 @@ __device__ __forceinline__ void tripole_push(const LoopArgs &a, int c, int rowse
     int t, ct, wt;                            // owner, local column on rank t (1..wt)
     slab_owner(a.start, a.nranks, X, t, ct, wt);
     const size_t urow = (size_t)(0 + rowsel) * a.inbox_ld, vrow = (size_t)(2 + rowsel) * a.inbox_ld;
-    a.inbox[t][urow + ct] = u;
-    a.inbox[t][vrow + ct] = v;
+    inbox[t][urow + ct] = u;
+    inbox[t][vrow + ct] = v;
     if (ct == 1) {                            // also the east ghost of rank t-1
         const int t2 = (t + a.nranks - 1) % a.nranks;
         const int w2 = a.start[t2 + 1] - a.start[t2];
-        a.inbox[t2][urow + w2 + 1] = u;
-        a.inbox[t2][vrow + w2 + 1] = v;
+        inbox[t2][urow + w2 + 1] = u;
+        inbox[t2][vrow + w2 + 1] = v;
     }
     if (ct == wt) {                           // also the west ghost of rank t+1
         const int t2 = (t + 1) % a.nranks;
-        a.inbox[t2][urow] = u;
-        a.inbox[t2][vrow] = v;
+        inbox[t2][urow] = u;
+        inbox[t2][vrow] = v;
     }
+}
+__device__ __forceinline__ void tripole_push(const LoopArgs &a, int c, int rowsel, double u, double v)
+{
+    tripole_push(a, a.inbox, c, rowsel, u, v);
 }
 
 template <bool LAST, bool REVISED = false>

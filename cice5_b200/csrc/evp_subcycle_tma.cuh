@@ -50,32 +50,6 @@ constexpr int kSortThreads = 64;
 constexpr int kItemBoundary = 0x40000000;    // tag of a work item that stores into peer memory
 // stage word bits written by the producer
 constexpr unsigned kMetaState = 1u, kMetaCompact = 2u, kMetaTinyFromMetrics = 4u, kMetaHtnExtra = 8u, kMetaT = 16u;
-// EVP_TMA_MERGE_UV = 1 (experiment for round 2, NOT yet run on hardware, off by default): an item
-// has no separate first stage for the velocities of row r0-1; they ride in the U-coefficient slots
-// of the stage of row r0 (unused there: stepu starts at row r0+1), HTN of row r0-1 in slot 11.
-// Saves one ring turn-around (one exposed DRAM latency with 2 stages) per item.
-#ifndef EVP_TMA_MERGE_UV
-#define EVP_TMA_MERGE_UV 0
-#endif
-constexpr bool kMergeUv = EVP_TMA_MERGE_UV != 0;
-// EVP_TMA_STATIC_FIRST = 1 (experiment, not yet run on hardware, off by default): see the producer loop
-#ifndef EVP_TMA_STATIC_FIRST
-#define EVP_TMA_STATIC_FIRST 0
-#endif
-constexpr bool kStaticFirst = EVP_TMA_STATIC_FIRST != 0;
-// EVP_TMA_ITEMTRACE = 1 (diagnosis builds only): every 16th CTA of the LAST-subcycle launch prints one
-// line per work item -- "ITEM cta item rows t_start t_end" in globaltimer ns relative to the CTA's
-// start -- so that the per-CTA timeline of a launch can be reconstructed (who waits for what at N = 8).
-#ifndef EVP_TMA_ITEMTRACE
-#define EVP_TMA_ITEMTRACE 0
-#endif
-// EVP_TMA_GUIDED = 1 (experiment, not yet run on hardware, off by default): two-tier row chunks, see
-// TmaArgs::n_small.  A compile-time switch so that the default build keeps the code that was measured.
-#ifndef EVP_TMA_GUIDED
-#define EVP_TMA_GUIDED 0
-#endif
-constexpr bool kGuided = EVP_TMA_GUIDED != 0;
-constexpr unsigned kMetaUvBelow = 32u, kMetaHtnBelow = 64u;
 constexpr int kMaskBoxW = 128 + 16;          // per mask box; kTmaBoxW / 128 boxes per row
 constexpr int kMaskBoxes = kTmaBoxW / 128;
 constexpr int kMaskFlagOff = 256 * (kMaskBoxes - 1) + kMaskBoxW + 48;     // stage word after the mask bytes (16-byte aligned)     // the byte mask is fetched from a 16-byte aligned column (TMA
@@ -100,30 +74,18 @@ struct TmaArgs {
     // fused cross-rank signal: every CTA counts itself in `done` when its stores are out; the last
     // one bumps the epoch and releases it to the peers (what halo_signal_kernel does otherwise)
     int fused_signal;
-    // fold_in_kernel (EVP_B200_FOLD=kernel, off by default): the CTA that completes the boundary count
-    // -- or the last CTA when no boundary item holds ice -- also waits for the peers' signals and folds the
-    // new u, v itself, while the other CTAs work on the interior items: no fold_uv_kernel launch, one
-    // launch per subcycle, the exchange hidden behind the interior.  Implies fused_signal.
-    int fold_in_kernel;
     int *done, *done_bnd;        // finished CTAs / finished boundary items of this launch
     SyncArgs sync;
     // timing trace of this launch (EVP_B200_TRACE=1), globaltimer ns: [0] first CTA start, [1] last
     // CTA done, [2] peers signalled; the fold kernel adds [3] wait begin, [4] wait end
     unsigned long long *trace;
-    // guided item sizes (-DEVP_TMA_GUIDED=1 builds with EVP_B200_GUIDED set; n_small = 0 otherwise): the
-    // first n_small row chunks have rows_small rows instead of a.rows_per_chunk.  The list is drawn heaviest
-    // first, so the short items come last and the end of a launch is ragged by a short item, not a full one.
-    int n_small, rows_small;
 };
 
-// Rows of a chunk: T rows r0 .. rend, U rows r0 .. rend-1 (chunks [0, n_small) are the short ones).
-__host__ __device__ __forceinline__ void chunk_rows(int chunk, int rpc, int n_small, int rows_small, int ny,
-                                                    int &r0, int &rend)
+// Rows of a chunk: T rows r0 .. rend, U rows r0 .. rend-1
+__host__ __device__ __forceinline__ void chunk_rows(int chunk, int rpc, int ny, int &r0, int &rend)
 {
-    const bool small = chunk < n_small;
-    r0 = 1 + (small ? chunk * rows_small : n_small * rows_small + (chunk - n_small) * rpc);
-    const int top = r0 + (small ? rows_small : rpc);
-    rend = top < ny + 1 ? top : ny + 1;
+    r0 = 1 + chunk * rpc;
+    rend = r0 + rpc < ny + 1 ? r0 + rpc : ny + 1;
 }
 
 __device__ __forceinline__ unsigned smem_u32(const void *p)
@@ -188,36 +150,9 @@ __device__ __forceinline__ void metric_terms(double hte, double hte_w, double ht
     m[7] = -__dsub_rn(__dmul_rn(1.5, hte_w), __dmul_rn(0.5, hte));              // cym
 }
 
-// The tripole fold of the new velocities by the consumer warps of ONE CTA (fold_in_kernel): what
-// fold_uv_kernel does with do_wait = 1.  Every boundary item of this rank is complete and fenced (the
-// caller completed the count) and this rank's signal is out; thread r waits for peer r's signal, then the
-// columns are folded kTmaConsumers*32 at a time.  Loads bypass L1 (other SMs / peers wrote the data).
-__device__ __noinline__ void fold_by_this_cta(const TmaArgs &p, int warp, int lane)
-{
-    const LoopArgs &a = p.a;
-    const int t = warp * 32 + lane;
-    if (p.trace && t == 0) p.trace[3] = global_ns();
-    peer_wait(p.sync, t);
-    asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
-    __threadfence_system();
-    if (p.trace && t == 0) p.trace[4] = global_ns();
-    const double *inbox = a.inbox[a.rank];
-    const int ild = a.inbox_ld;
-    for (int c = t; c <= a.nxl + 1; c += kTmaConsumers * 32) {
-        int ig = a.lo + c;
-        if (ig < 1) ig += a.nx_global;
-        if (ig > a.nx_global) ig -= a.nx_global;
-        const size_t top = (size_t)a.ny * a.ld + c;
-        fold_necorner_column(a.u1, a.ld, a.ny, c, ig, a.nx_global, __ldcg(a.u1 + top), __ldcg(inbox + c),
-                             __ldcg(inbox + ild + c), -1.0, kFirstPair3D);
-        fold_necorner_column(a.v1, a.ld, a.ny, c, ig, a.nx_global, __ldcg(a.v1 + top), __ldcg(inbox + 2 * ild + c),
-                             __ldcg(inbox + 3 * ild + c), -1.0, kFirstPair3D);
-    }
-}
-
 // Consumer warps of one CTA: `n` more boundary items are complete (all their stores into peer
 // memory issued).  Fence once, count; the CTA that completes the count releases the epoch.
-__device__ __noinline__ void boundary_done(const TmaArgs &p, int *bnd_count, int *fold_fire, int warp, int lane)
+__device__ __noinline__ void boundary_done(const TmaArgs &p, int *bnd_count, int warp, int lane)
 {
     __threadfence_system();                          // my stores into peer memory are out
     asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
@@ -235,11 +170,6 @@ __device__ __noinline__ void boundary_done(const TmaArgs &p, int *bnd_count, int
             peer_signal_warp(p.sync, lane);
             if (p.trace && lane == 0) p.trace[2] = global_ns();
         }
-        if (p.fold_in_kernel && lane == 0) *fold_fire = fire;
-    }
-    if (p.fold_in_kernel) {                          // all consumer warps: did this CTA complete the count?
-        asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
-        if (*fold_fire) fold_by_this_cta(p, warp, lane);
     }
 }
 
@@ -254,7 +184,6 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
     extern __shared__ __align__(1024) unsigned char ring[];
     __shared__ unsigned long long full_bar[kTmaStages], empty_bar[kTmaStages];
     __shared__ int bnd_count;                        // boundary items taken by this CTA (thread 0 only)
-    __shared__ int fold_fire;                        // fold_in_kernel: this CTA does the fold
     const LoopArgs &a = p.a;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -274,14 +203,8 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
         // ------------------------------ producer ------------------------------
         if (lane == 0) {
             const int nitems = p.item_count[0], nbnd = p.item_count[1];
-            bool first_item = true;
             for (;;) {
-                // EVP_TMA_STATIC_FIRST: the first item of a CTA is its own index in the list (the list starts
-                // with the boundary items, heaviest first), the queue hands out the rest -- one atomic round
-                // trip less before the first TMA of every launch
-                const int q = (kStaticFirst && first_item) ? (int)blockIdx.x
-                                                           : (kStaticFirst ? (int)gridDim.x : 0) + atomicAdd(p.queue, 1);
-                first_item = false;
+                const int q = atomicAdd(p.queue, 1);
                 if (q >= nitems) {                                      // queue drained: tell the consumers
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
                     unsigned char *mk = ring + (size_t)stage * kStageBytes + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8;
@@ -293,11 +216,10 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                 const int item_tag = item | (q < nbnd ? kItemBoundary : 0);
                 const int strip = item % p.strips, chunk = item / p.strips;
                 const int x0 = strip * kTmaUCols;                       // box column 0 = U column c0 - 1
-                int r0 = 1 + chunk * a.rows_per_chunk;
-                int rend = min(r0 + a.rows_per_chunk, a.ny + 1);
-                if (kGuided) chunk_rows(chunk, a.rows_per_chunk, p.n_small, p.rows_small, a.ny, r0, rend);
+                int r0, rend;
+                chunk_rows(chunk, a.rows_per_chunk, a.ny, r0, rend);
                 const unsigned char *fl = p.tile_flags + (size_t)strip * p.flags_ld;
-                for (int j = kMergeUv ? r0 : r0 - 1; j <= rend; ++j) {
+                for (int j = r0 - 1; j <= rend; ++j) {
                     // what this row segment needs: T data if it has an active T cell; U data of the
                     // row below if that row has an active U cell; the state (u, v, stresses) if this
                     // row or the next one has an active T cell or this row an active U cell.  The top
@@ -311,18 +233,13 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     // the next row, if compact, recomputes its metrics from HTN of this row too
                     const bool nextT = j + 1 <= rend && ((f1 & 1u) || j + 1 >= a.ny - 2) && (f1 & 4u);
                     const bool htn_extra = nextT && !(needT && cmp);
-                    // merged first stage: velocities (and HTN) of row r0-1 under the old rule for that row
-                    const bool first = kMergeUv && j == r0;
-                    const bool uv_below = first && ((((fm1 | f0) & 1u) || (fm1 & 2u)) || j - 1 >= a.ny - 2);
-                    const bool htn_below = first && needT && cmp;
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
                     unsigned char *sb = ring + (size_t)stage * kStageBytes;
                     unsigned char *tb = sb + kStateDepth * kTmaBoxW * 8;
                     unsigned char *mk = sb + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8;
                     *reinterpret_cast<volatile unsigned *>(mk + kMaskFlagOff) =
                         (needS ? kMetaState : 0u) | (cmp ? kMetaCompact : 0u) | (tinym ? kMetaTinyFromMetrics : 0u) |
-                        (htn_extra ? kMetaHtnExtra : 0u) | (needT ? kMetaT : 0u) | (uv_below ? kMetaUvBelow : 0u) |
-                        (htn_below ? kMetaHtnBelow : 0u);
+                        (htn_extra ? kMetaHtnExtra : 0u) | (needT ? kMetaT : 0u);
                     *reinterpret_cast<volatile int *>(mk + kMaskFlagOff + 4) = item_tag;
                     const int tdepth = cmp ? (tinym ? 3 : 4) : 10;
                     unsigned bytes = kMaskBoxW * kMaskBoxes;
@@ -330,8 +247,6 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     if (needS) bytes += (uv_only ? 2 : kStateDepth) * kTmaBoxW * 8;
                     if (needT) bytes += (tdepth + (LAST ? 1 : 0)) * kTmaBoxW * 8;
                     if (htn_extra) bytes += kTmaBoxW * 8;
-                    if (uv_below) bytes += 2 * kTmaBoxW * 8;
-                    if (htn_below) bytes += kTmaBoxW * 8;
                     if (needU) bytes += (p.water_is_ocn ? kUDepth - 2 : kUDepth) * kTmaBoxW * 8;
                     mbar_expect_tx(&full_bar[stage], bytes);
 #pragma unroll
@@ -350,11 +265,6 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                     if (needU)
                         tma_load_3d(sb + (kStateDepth + kTDepth) * kTmaBoxW * 8, &mapU, &full_bar[stage], x0, j - 1,
                                     p.plane_u);
-                    if (uv_below)       // needU is false on the first row of an item: the U slots are free
-                        tma_load_3d(sb + (kStateDepth + kTDepth) * kTmaBoxW * 8, &mapS2, &full_bar[stage], x0, j - 1,
-                                    p.plane_state);
-                    if (htn_below)      // htn_extra is false here (needT && cmp): slot 11 is free
-                        tma_load_3d(tb + kSlotHtnExtra * kTmaBoxW * 8, &mapT1, &full_bar[stage], x0, j - 1, p.plane_t + 1);
                     if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
                 }
             }
@@ -367,9 +277,6 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
     const int ld = a.ld;
     const int bi = 1 + warp * kUColsPerWarp + lane;                     // my column inside the box
     bool in_bnd = false;                                                // boundary items taken, not yet counted
-#if EVP_TMA_ITEMTRACE
-    const unsigned long long t_cta = global_ns();
-#endif
     if (p.trace && blockIdx.x == 0 && threadIdx.x == 0) p.trace[0] = global_ns();
     for (;;) {
         mbar_wait(&full_bar[stage], phase);                             // first stage of the next item
@@ -379,7 +286,7 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             // this CTA has left the boundary items (they come first in the queue): count them;
             // whoever completes the count signals the peers, and the interior items of every rank
             // are computed while the signals travel
-            if (p.fused_signal) boundary_done(p, &bnd_count, &fold_fire, warp, lane);
+            if (p.fused_signal) boundary_done(p, &bnd_count, warp, lane);
             in_bnd = false;
         }
         if (item_tag < 0) break;
@@ -392,15 +299,11 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
         const int c = 1 + strip * kTmaUCols + warp * kUColsPerWarp + lane;   // T column (U column if lane < 31)
         const bool warp_on = (c - lane) <= a.nxl;                       // warp-uniform
         const int mshift = (strip * kTmaUCols) & 15;                    // mask box starts this many bytes early
-        int r0 = 1 + chunk * a.rows_per_chunk;
-        int rend = min(r0 + a.rows_per_chunk, a.ny + 1);
-        if (kGuided) chunk_rows(chunk, a.rows_per_chunk, p.n_small, p.rows_small, a.ny, r0, rend);
+        int r0, rend;
+        chunk_rows(chunk, a.rows_per_chunk, a.ny, r0, rend);
         const bool tcol = c <= a.nxl + 1;
         const bool ucol = lane < kUColsPerWarp && c <= a.nxl;
         const bool tstore_col = tcol && (lane < kUColsPerWarp || c == a.nxl + 1);
-#if EVP_TMA_ITEMTRACE
-        const unsigned long long t_item = global_ns();
-#endif
 
         // row r0-1: velocities only
         double u_s, v_s, uw_s, vw_s;
@@ -410,21 +313,12 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             const double *st = reinterpret_cast<const double *>(ring + (size_t)stage * kStageBytes);
             const unsigned meta = *reinterpret_cast<const unsigned *>(
                 ring + (size_t)stage * kStageBytes + (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8 + kMaskFlagOff);
-            if (!kMergeUv) {
-                loaded_s = (meta & kMetaState) != 0u;
-                if (meta & kMetaHtnExtra) htn_s = st[(kStateDepth + kSlotHtnExtra) * kTmaBoxW + bi];
-                u_s = st[bi]; v_s = st[kTmaBoxW + bi]; uw_s = st[bi - 1]; vw_s = st[kTmaBoxW + bi - 1];
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&empty_bar[stage]);
-                if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
-            } else {
-                // this stage is row r0 itself: take the row-below values out of the U slots / slot 11
-                // and keep the stage (the row loop waits on the same, completed, phase again)
-                const double *ub = st + (kStateDepth + kTDepth) * kTmaBoxW;
-                loaded_s = (meta & kMetaUvBelow) != 0u;
-                if (meta & kMetaHtnBelow) htn_s = st[(kStateDepth + kSlotHtnExtra) * kTmaBoxW + bi];
-                u_s = ub[bi]; v_s = ub[kTmaBoxW + bi]; uw_s = ub[bi - 1]; vw_s = ub[kTmaBoxW + bi - 1];
-            }
+            loaded_s = (meta & kMetaState) != 0u;
+            if (meta & kMetaHtnExtra) htn_s = st[(kStateDepth + kSlotHtnExtra) * kTmaBoxW + bi];
+            u_s = st[bi]; v_s = st[kTmaBoxW + bi]; uw_s = st[bi - 1]; vw_s = st[kTmaBoxW + bi - 1];
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[stage]);
+            if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
         }
         double s1p = 0.0, s5p = 0.0, n2p = 0.0, n7p = 0.0;
         unsigned mprev = 0;
@@ -570,10 +464,6 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
             s1p = str[0]; s5p = str[4]; n2p = e2; n7p = e7;
             u_s = u_c; v_s = v_c; uw_s = uw_c; vw_s = vw_c; mprev = m; loaded_s = loaded_c;
         }
-#if EVP_TMA_ITEMTRACE
-        if (LAST && threadIdx.x == 0 && (blockIdx.x & 15) == 0)
-            printf("ITEM %d %d %d %llu %llu\n", (int)blockIdx.x, item, rend - r0 + 1, t_item - t_cta, global_ns() - t_cta);
-#endif
     }
     if (p.fused_signal || p.trace) {
         __threadfence_system();
@@ -593,11 +483,6 @@ evp_subcycle_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_c
                 peer_signal_warp(p.sync, lane);
                 if (p.trace && lane == 0) p.trace[2] = global_ns();
             }
-            if (p.fold_in_kernel && lane == 0) fold_fire = last && p.item_count[1] == 0;
-        }
-        if (p.fold_in_kernel) {
-            asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
-            if (fold_fire) fold_by_this_cta(p, warp, lane);
         }
     }
 }
@@ -668,9 +553,18 @@ __global__ void metric_flags_kernel(const __grid_constant__ MetricCheckArgs a)
 // where the loop never writes), so it is dropped -- except the chunks that reach the top rows of a
 // tripole grid, whose velocities feed the fold every subcycle.  The order inside one weight class
 // is not deterministic; results do not depend on the order of the items.
+// Per call, for the persistent loop kernel (evp_loop_tma.cuh): `natural` keeps the items in item order (south to
+// north, the order the dependency wavefront wants) and the dependency counters are reset -- 0 for an item
+// that will run, all ones for an item without ice (it never runs, and never has to be waited for); the edge
+// strips' counters also into the E-W neighbours' ghost arrays.  count[2] = items that reach the top rows.
+struct ItemListLoop {
+    int natural;
+    unsigned long long *misc;              // topflag[8], fold_flag, top_count: zeroed
+    unsigned long long *tflag, *pub_w, *pub_e;
+};
 __global__ void item_list_kernel(const unsigned char *flags, int flags_ld, int strips, int chunks, int rpc,
-                                 int n_small, int rows_small, int ny, int tripole, int bnd_west, int bnd_east, int *list, int *count, int *queues,
-                                 int nqueues)
+                                 int ny, int tripole, int bnd_west, int bnd_east, int *list, int *count, int *queues,
+                                 int nqueues, ItemListLoop lp)
 {
     // Stable counting sort, one block of kSortThreads threads, thread t owns a contiguous range of
     // items.  key = weight (rows of the item with ice, 0 .. rpc + 3 <= 67) + kW for boundary items
@@ -681,9 +575,13 @@ __global__ void item_list_kernel(const unsigned char *flags, int flags_ld, int s
     constexpr int kW = 80, kBins = 2 * kW;
     __shared__ int hist[kSortThreads][kBins];
     __shared__ int binbase[kBins];
+    __shared__ int ntop;
     const int t = threadIdx.x;
+    if (t == 0) ntop = 0;
+    if (lp.misc && t < 10) lp.misc[t] = 0ull;
     for (int q = t; q < nqueues; q += blockDim.x) queues[q] = 0;
     for (int q = 0; q < kBins; ++q) hist[t][q] = 0;
+    __syncthreads();
     const int items = strips * chunks;
     const int per = (items + kSortThreads - 1) / kSortThreads;
     const int i0 = min(t * per, items), i1 = min(i0 + per, items);
@@ -691,14 +589,21 @@ __global__ void item_list_kernel(const unsigned char *flags, int flags_ld, int s
         for (int item = i0; item < i1; ++item) {
             const int strip = item % strips, chunk = item / strips;
             int r0, rend;
-            chunk_rows(chunk, rpc, n_small, rows_small, ny, r0, rend);
+            chunk_rows(chunk, rpc, ny, r0, rend);
             const unsigned char *fl = flags + (size_t)strip * flags_ld;
             int w = 0;
             for (int j = r0 - 1; j <= rend + 1; ++j) w += (fl[j] & 3u) != 0u;    // activity bits only
             if (w == 0 && tripole && rend >= ny - 2) w = 1;
+            if (pass == 0 && lp.tflag) {
+                const unsigned long long v = w == 0 ? ~0ull : 0ull;
+                lp.tflag[item] = v;
+                if (strip == 0 && lp.pub_w) lp.pub_w[chunk] = v;
+                if (strip == strips - 1 && lp.pub_e) lp.pub_e[chunk] = v;
+                if (w != 0 && tripole && rend >= ny) atomicAdd(&ntop, 1);
+            }
             if (w == 0) continue;
             const bool bnd = (strip == 0 && bnd_west) || (strip == strips - 1 && bnd_east) || (tripole && rend >= ny - 2);
-            const int key = min(w, kW - 1) + (bnd ? kW : 0);
+            const int key = lp.natural ? 1 : min(w, kW - 1) + (bnd ? kW : 0);
             if (pass == 0) ++hist[t][key];
             else list[binbase[key] + hist[t][key]++] = item;
         }
@@ -706,6 +611,7 @@ __global__ void item_list_kernel(const unsigned char *flags, int flags_ld, int s
         if (pass == 0) {
             if (t == 0) {
                 int off = 0;
+                count[1] = 0;
                 for (int key = kBins - 1; key >= 1; --key) {
                     if (key == kW - 1) count[1] = off;          // everything before: boundary items
                     binbase[key] = off;
@@ -716,6 +622,7 @@ __global__ void item_list_kernel(const unsigned char *flags, int flags_ld, int s
                     }
                 }
                 count[0] = off;
+                count[2] = ntop;
             }
             __syncthreads();
         }

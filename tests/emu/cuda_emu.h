@@ -171,7 +171,13 @@ void emu_bar_sync(int id, int nthreads);
 inline void __threadfence() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 inline void __threadfence_system() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 inline void __syncwarp(unsigned mask = 0xffffffffu) { emu::rendezvous(mask, 0, false); }
-inline void __nanosleep(unsigned) { std::this_thread::yield(); }
+inline void __nanosleep(unsigned)
+{
+    // a spinning thread gives way to the other fibers of its block and to the other resident blocks (a CTA of the
+    // persistent loop kernel waits for counters that other CTAs of the same launch publish), then to other streams
+    if (emu::cur) emu::yield();
+    std::this_thread::yield();
+}
 inline unsigned long long atomicAdd(unsigned long long *p, unsigned long long v) { return __atomic_fetch_add(p, v, __ATOMIC_SEQ_CST); }
 inline int atomicAdd(int *p, int v) { return __atomic_fetch_add(p, v, __ATOMIC_SEQ_CST); }
 inline unsigned atomicAdd(unsigned *p, unsigned v) { return __atomic_fetch_add(p, v, __ATOMIC_SEQ_CST); }

@@ -289,52 +289,6 @@ def test_product_loader_has_no_host_fallback():
                 assert "tests/emu" not in text and "libevp_emu" not in text and "cuda_emu" not in text, f
 
 
-@pytest.mark.parametrize("defines", [("-DEVP_TMA_STATIC_FIRST=1",),
-                                     ("-DEVP_TMA_STATIC_FIRST=1", "-DEVP_TMA_MERGE_UV=1")])
-def test_static_first_item_variant_bitwise(monkeypatch, defines):
-    """-DEVP_TMA_STATIC_FIRST=1 (the first item of every CTA is its own index in the item list, the queue
-    hands out the rest), alone and together with MERGE_UV and the in-kernel fold, 1 and 4 ranks."""
-    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
-    case = fx.make_case(grid, "full", ndte=5, dt=3600.0)
-    ref = _oracle(case)
-    if len(defines) == 2:
-        monkeypatch.setenv("EVP_B200_FOLD", "kernel")
-    with emu.patched(kernel="tma", defines=defines) as evp:
-        got = clone_case(case)
-        evp.run_case(got, strict=True)
-        compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
-        monkeypatch.setattr(evp, "compute_group", _compute_on_threads)
-        got = clone_case(case)
-        g = evp.EvpGroup(case.dom, case.ndte, case.dt, 4, strict=True)
-        try:
-            g.set_grid(grid.f)
-            g.evp(case.dt, got.inp, got.io, got.out)
-        finally:
-            g.close()
-        compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
-
-
-def test_merge_uv_variant_bitwise():
-    """-DEVP_TMA_MERGE_UV=1 (the velocities of row r0-1 ride in the first full stage of an item instead of a
-    stage of their own): written and compile-checked in round 1, never run on
-    hardware -- its first execution anywhere.  Same answers, bit for bit, 1 and 2 ranks."""
-    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
-    case = fx.make_case(grid, "full", ndte=5, dt=3600.0)
-    ref = _oracle(case)
-    with emu.patched(kernel="tma", defines=("-DEVP_TMA_MERGE_UV=1",)) as evp:
-        got = clone_case(case)
-        evp.run_case(got, strict=True)
-        compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
-        got = clone_case(case)
-        g = evp.EvpGroup(case.dom, case.ndte, case.dt, 2, strict=True)
-        try:
-            g.set_grid(grid.f)
-            g.evp(case.dt, got.inp, got.io, got.out)
-        finally:
-            g.close()
-        compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
-
-
 def _compute_on_threads(ranks, dt):
     """One host thread per rank, each on its own stream -- the in-process picture of one process per GPU
     (evp_gpu_compute_group puts all ranks on ONE stream of one device, where a kernel that waits for a peer
@@ -357,121 +311,69 @@ def _compute_on_threads(ranks, dt):
         raise errors[0]
 
 
-@pytest.mark.parametrize("nranks,threads", [(1, False), (2, True), (4, True), (2, False)])
-def test_fold_in_kernel_variant_bitwise(monkeypatch, nranks, threads):
-    """EVP_B200_FOLD=kernel: the CTA that completes the boundary count waits for the
-    peers and folds the new velocities itself -- one launch per subcycle instead of two.  Same answers bit for
-    bit on 1, 2 and 4 ranks, two calls, wet poles; and the launch count really drops.  (2, False): through
-    evp_gpu_compute_group, where the option must switch itself off.)"""
-    monkeypatch.setenv("EVP_B200_FOLD", "kernel")
-    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
-    case = fx.make_case(grid, "full", ndte=5, dt=3600.0)
+def _group_case(evp, monkeypatch, grid, case, nranks, starts=None, threads=True, calls=2, **kw):
+    """`calls` evp calls of an EvpGroup against the oracle, bit for bit; ranks on threads (one stream each: the
+    persistent loop kernel is the path) or through evp_gpu_compute_group (one stream: a launch per subcycle)."""
     ref, got = clone_case(case), clone_case(case)
-    with emu.patched(kernel="tma") as evp:
-        if threads:
-            monkeypatch.setattr(evp, "compute_group", _compute_on_threads)
-        g = evp.EvpGroup(case.dom, case.ndte, case.dt, nranks, strict=True)
-        try:
-            g.set_grid(grid.f)
-            for _ in range(2):
-                ref.out, got.out = fx.zeroed_outputs(case.dom), fx.zeroed_outputs(case.dom)
-                orc.run_case(ref)
-                stats = g.evp(case.dt, got.inp, got.io, got.out)
-                compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
-            per_subcycle = 1 if (threads or nranks == 1) else 2
-            assert all(s.loop_kernel_launches == per_subcycle * case.ndte for s in stats)
-        finally:
-            g.close()
-
-
-@pytest.mark.parametrize("rpc,guided,nranks,scenario,defines", [
-    ("9", "40,2", 1, "full", ()), ("8", "100,3", 2, "full", ()), ("5", "30,4", 1, "caps", ()),
-    ("7", "60,2", 4, "full", ("-DEVP_TMA_MERGE_UV=1", "-DEVP_TMA_STATIC_FIRST=1")), ("6", "35,7", 1, "full", ())])
-def test_guided_item_sizes_bitwise(monkeypatch, rpc, guided, nranks, scenario, defines):
-    """-DEVP_TMA_GUIDED=1 with EVP_B200_GUIDED="percent,rows" (DESIGN.md section 9, 1f): the southern share of
-    the rows is cut into short chunks that the heaviest-first work list hands out last.  Pure scheduling: the
-    same answers bit for bit, whatever the split, alone and with the other round-2 variants (last case:
-    rows >= rows-per-item, the option must switch itself off)."""
-    monkeypatch.setenv("EVP_B200_RPC", rpc)
-    monkeypatch.setenv("EVP_B200_GUIDED", guided)
-    grid = fx.synthetic_tripole(96, 43, wet_poles=True)
-    case = fx.make_case(grid, scenario, ndte=4, dt=3600.0)
-    ref, got = clone_case(case), clone_case(case)
-    with emu.patched(kernel="tma", defines=("-DEVP_TMA_GUIDED=1", *defines)) as evp:
-        g = evp.EvpGroup(case.dom, case.ndte, case.dt, nranks, strict=True)
-        try:
-            g.set_grid(grid.f)
-            for _ in range(2):
-                ref.out, got.out = fx.zeroed_outputs(case.dom), fx.zeroed_outputs(case.dom)
-                orc.run_case(ref)
-                g.evp(case.dt, got.inp, got.io, got.out)
-                compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
-        finally:
-            g.close()
-
-
-def test_fold_in_kernel_when_no_boundary_item_holds_ice(monkeypatch):
-    """Ice in the south only: no boundary item, the last CTA of the launch signals and folds."""
-    monkeypatch.setenv("EVP_B200_FOLD", "kernel")
-    grid = fx.synthetic_tripole(96, 40)
-    case = fx.make_case(grid, "caps", ndte=4, dt=3600.0)
-    for k in ("aice", "vice", "vsno", "aice_init"):
-        case.inp[k][20:, :] = 0.0                       # no ice in the northern half
-    ref, got = clone_case(case), clone_case(case)
-    orc.run_case(ref)
-    assert np.abs(phys(ref.io["uvel"])).max() > 0.0
-    with emu.patched(kernel="tma") as evp:
-        evp.run_case(got, strict=True)
-    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
-
-
-def test_ranks_on_threads_default_path(monkeypatch):
-    """The default multi-rank path (last CTA signals, fold_uv_kernel waits) with one thread and one stream per
-    rank, i.e. with the ranks really overlapping, as one process per GPU does."""
-    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
-    case = fx.make_case(grid, "full", ndte=5, dt=3600.0)
-    ref, got = clone_case(case), clone_case(case)
-    with emu.patched(kernel="tma") as evp:
+    if threads:
         monkeypatch.setattr(evp, "compute_group", _compute_on_threads)
-        g = evp.EvpGroup(case.dom, case.ndte, case.dt, 4, strict=True)
-        try:
-            g.set_grid(grid.f)
-            for _ in range(2):
-                ref.out, got.out = fx.zeroed_outputs(case.dom), fx.zeroed_outputs(case.dom)
-                orc.run_case(ref)
-                stats = g.evp(case.dt, got.inp, got.io, got.out)
-                compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
-            assert all(s.loop_kernel_launches == 2 * case.ndte for s in stats)
-        finally:
-            g.close()
+    g = evp.EvpGroup(case.dom, case.ndte, case.dt, nranks, strict=True, slab_start=starts, **kw)
+    try:
+        g.set_grid(grid.f)
+        for _ in range(calls):
+            ref.out, got.out = fx.zeroed_outputs(case.dom), fx.zeroed_outputs(case.dom)
+            orc.run_case(ref, **({"revised_evp": True} if kw.get("revised_evp") else {}))
+            stats = g.evp(case.dt, got.inp, got.io, got.out)
+            compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+    finally:
+        g.close()
+    return stats
 
 
-@pytest.mark.parametrize("kernel", ["tma", "sweep"])
-def test_early_download_variant_bitwise(monkeypatch, kernel):
-    """EVP_B200_EARLY_D2H=1: evp_gpu_run copies the ten outputs that are final
-    before the subcycle loop back on a second stream while the loop runs.  Streams are threads here, so a copy
-    that did not wait for the prep phase, or a download that did not wait for the copy stream, would read
-    unfinished planes.  Three calls on one handle, same buffers and fresh buffers."""
-    monkeypatch.setenv("EVP_B200_EARLY_D2H", "1")
+@pytest.mark.parametrize("nranks,starts,rpc", [(1, None, None), (2, None, None), (4, None, "3"), (3, [0, 20, 60], "5"),
+                                               (8, None, "2")])
+def test_loop_kernel_tripole_ranks_on_threads_bitwise(monkeypatch, nranks, starts, rpc):
+    """evp_loop_tma_kernel (all ndte subcycles in one launch, per-tile dependency counters, the fold as an item):
+    1 to 8 ranks really overlapping (a thread and a stream per rank), equal and unequal slabs, several chunk
+    heights, ice on the poles, two calls -- and exactly one loop launch per rank and call."""
+    if rpc:
+        monkeypatch.setenv("EVP_B200_RPC", rpc)
     grid = fx.synthetic_tripole(96, 40, wet_poles=True)
-    case = fx.make_case(grid, "full", ndte=6, dt=3600.0)
-    ref, got = clone_case(case), clone_case(case)
-    with emu.patched(kernel=kernel) as evp:
-        e = evp.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True)
-        try:
-            e.set_grid(grid.f)
-            for call in range(3):
-                ref.out = fx.zeroed_outputs(case.dom)
-                got.out = {k: np.full_like(v, -12345) for k, v in fx.zeroed_outputs(case.dom).items()}
-                if call == 2:                                   # other buffers: nothing may be cached by address
-                    got.io = {k: v.copy() for k, v in got.io.items()}
-                orc.run_case(ref)
-                e.evp(case.dt, got.inp, got.io, got.out)
-                compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
-                for k in ("strairx", "strtltx", "uvel_init", "tmass", "strength_out"):
-                    assert np.array_equal(got.out[k], ref.out[k]), k      # ghost cells included
-        finally:
-            e.close()
+    case = fx.make_case(grid, "full", ndte=7, dt=3600.0)
+    with emu.patched(kernel="tma") as evp:
+        stats = _group_case(evp, monkeypatch, grid, case, nranks, starts)
+        assert all(s.loop_kernel_launches == (1 if nranks == 1 else 3) for s in stats)      # + signal, wait at N > 1
+
+
+@pytest.mark.parametrize("gridname,nranks", [("open", 1), ("open", 3), ("closed", 2), ("caps", 2), ("wide", 2)])
+def test_loop_kernel_other_boundaries_on_threads_bitwise(monkeypatch, gridname, nranks):
+    """The same without a fold (cyclic / open, closed basin), with tiles that hold no ice and are never run
+    (caps scenario: their counters start at all ones), and with several strips per rank (wide: 300 columns)."""
+    monkeypatch.setenv("EVP_B200_RPC", "4")
+    if gridname == "open":
+        grid = fx.synthetic_displaced(60, 30, name="open60")
+    elif gridname == "closed":
+        grid = fx.synthetic_closed(40, 24, name="closed40")
+    elif gridname == "wide":
+        grid = fx.synthetic_tripole(300, 18, "wide300", wet_poles=True)
+    else:
+        grid = fx.synthetic_tripole(96, 40, "caps96")
+    case = fx.make_case(grid, "caps" if gridname == "caps" else "full", ndte=6, dt=3600.0)
+    with emu.patched(kernel="tma") as evp:
+        _group_case(evp, monkeypatch, grid, case, nranks)
+
+
+def test_loop_kernel_revised_evp_and_loop_switch(monkeypatch):
+    """revised EVP through the loop kernel (2 ranks on threads); EVP_B200_LOOP=0 brings back a launch per
+    subcycle with the same answers."""
+    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
+    case = fx.make_case(grid, "full", ndte=5, dt=3600.0)
+    xmin = _xmin(grid)
+    with emu.patched(kernel="tma") as evp:
+        _group_case(evp, monkeypatch, grid, case, 2, revised_evp=True, xmin=xmin)
+        monkeypatch.setenv("EVP_B200_LOOP", "0")
+        stats = _group_case(evp, monkeypatch, grid, case, 2)
+        assert all(s.loop_kernel_launches == 2 * case.ndte for s in stats)
 
 
 def test_plain_c_host_example_on_the_host_build(tmp_path):
