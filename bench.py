@@ -54,6 +54,9 @@ def parse():
                     help="do not pass HTE/HTN: fetch all 8 metric planes + tinyarea every subcycle")
     ap.add_argument("--equal-slabs", action="store_true",
                     help="N > 1: nx/N columns per GPU instead of slabs balanced by ocean cells")
+    ap.add_argument("--no-parity", action="store_true", help="skip the bitwise comparison with the oracle")
+    ap.add_argument("--no-other-configs", action="store_true",
+                    help="skip the short measurements of the other BASELINE grid shapes")
     ap.add_argument("--cpu-ndte", type=int, default=120,
                     help="subcycles of the CPU sample (120 = one whole evp call, about 25 s on 16 cores)")
     return ap.parse_args()
@@ -116,17 +119,19 @@ class ClockSampler:
 def pinned_like(a):
     import torch
     t = torch.empty(a.shape, dtype=torch.float64 if a.dtype == np.float64 else torch.int32,
-                    pin_memory=True)
+                    pin_memory=torch.cuda.is_available())
     v = t.numpy()
     v[...] = a
     return t, v
 
 
-def cpu_sample(args, case_fn, nthreads=0):
+def cpu_sample(args, case_fn, nthreads=0, keep=None):
     """Oracle (CPU restatement) on the same workload with fewer subcycles; cell-subcycles/s of the
-    ksub loop plus the whole call."""
+    ksub loop plus the whole call.  keep: a list that receives the finished case (the parity leg reuses it)."""
     from oracle import oracle as orc
     case = case_fn(args.cpu_ndte)
+    if keep is not None:
+        keep.append(case)
     if nthreads == 0:
         # every core this process may run on, set explicitly: torchrun exports OMP_NUM_THREADS=1
         # to its ranks, which would otherwise leave the reference arm of an N > 1 run on one thread
@@ -143,10 +148,15 @@ def cpu_sample(args, case_fn, nthreads=0):
                       f"-ffp-contract=off; the Fortran+MPI reference cannot be built in this image"}
 
 
-def workload_name(args, dom, dt):
+SHAPES = {"gx3": "displaced pole, real grid + kmt (BASELINE configs[0])", "gx1": "displaced pole, real kmt (configs[1])",
+          "tp1": "tripole, ACCESS-OM 1 deg shape (configs[2])", "tp025": "tripole, ACCESS-OM 0.25 deg shape (configs[3])",
+          "tp01": "tripole, AusCOM 0.1 deg shape (configs[4])", "tp01s8": "tripole, one eighth of tp01 (tuning proxy)"}
+
+
+def workload_name(args, dom, dt, grid=None):
     """config.workload: the same string for both arms."""
-    shape = " (AusCOM 0.1 deg shape)" if args.grid == "tp01" else ""
-    return f"{args.grid} {dom.nx}x{dom.ny} tripole{shape}, scenario {args.scenario}, ndte={args.ndte}, dt={dt}"
+    g = grid or args.grid
+    return f"{g} {dom.nx}x{dom.ny} {SHAPES.get(g, '')}, scenario {args.scenario}, ndte={args.ndte}, dt={dt}"
 
 
 def run_reference(args, rank):
@@ -182,49 +192,86 @@ def run_reference(args, rank):
     print(json.dumps(out), flush=True)
 
 
-def main():
-    args = parse()
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    if args.impl == "reference":
-        run_reference(args, rank)
-        return 0
-    if world != args.gpus:
-        if world == 1 and args.gpus > 1:
-            raise SystemExit("launch N > 1 with torch.distributed.run --nproc-per-node N")
-    import torch
+PARITY_IO = ("uvel", "vvel") + tuple(f"stress{k}_{c}" for k in ("p", "m", "12") for c in (1, 2, 3, 4)) + ("fm", "iceumask")
+PARITY_OUT = ("strairx", "strairy", "strtltx", "strtlty", "strocnx", "strocny", "strintx", "strinty", "strocnxT",
+              "strocnyT", "divu", "shear", "rdg_conv", "rdg_shear", "prs_sig", "uvel_init", "vvel_init", "tmass",
+              "strength_out", "icetmask")
+
+
+def _digest(a):
+    import hashlib
+    return hashlib.sha256(np.ascontiguousarray(a[1:-1, 1:-1]).tobytes()).hexdigest()
+
+
+class Ctx:
+    """torch.distributed plumbing of one bench process (control plane only: the data plane is peer memory)."""
+
+    def __init__(self):
+        import torch
+        self.torch = torch
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        torch.cuda.set_device(self.local_rank)
+        self.dist = None
+        if self.world > 1:
+            # stdout carries exactly one JSON line: NCCL's own banner goes to stderr
+            os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+            import torch.distributed as dist_
+            self.dist = dist_
+            dist_.init_process_group("nccl", device_id=torch.device("cuda", self.local_rank))
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def _red(self, x, op):
+        if self.dist is None:
+            return x
+        t = self.torch.tensor([x], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    def allmax(self, x):
+        return self._red(x, self.dist.ReduceOp.MAX if self.dist else None)
+
+    def allmin(self, x):
+        return self._red(x, self.dist.ReduceOp.MIN if self.dist else None)
+
+    def allsum(self, x):
+        return self._red(x, self.dist.ReduceOp.SUM if self.dist else None)
+
+    def gather(self, obj):
+        if self.dist is None:
+            return [obj]
+        out = [None] * self.world if self.rank == 0 else None
+        self.dist.gather_object(obj, out, dst=0)
+        return out
+
+    def bcast(self, obj):
+        if self.dist is None:
+            return obj
+        box = [obj]
+        self.dist.broadcast_object_list(box, src=0)
+        return box[0]
+
+
+def measure(ctx, args, gridname, scenario, steps, warmup, do_e2e, do_parity, ref_case=None, traffic=None):
+    """One workload on the N ranks of this run: device-resident throughput, optional e2e through evp_gpu_run,
+    optional bitwise comparison of one whole evp call (ndte as benchmarked, same handles / peers / graph /
+    streams as the timed legs) with the oracle.  Returns the result dictionary on rank 0 (None elsewhere)."""
     from cice5_b200 import evp, fixtures as fx
-
-    if evp.device_count() < 1:
-        raise SystemExit("bench.py: no CUDA device; the EVP path has no CPU fallback")
-    torch.cuda.set_device(local_rank)
-    dist = None
-    if world > 1:
-        # stdout carries exactly one JSON line: NCCL's own banner ("NCCL version ...", printed to
-        # stdout whenever the box exports NCCL_DEBUG) goes to stderr instead
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        import torch.distributed as dist_
-        dist = dist_
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # ---- workload: the named grid split into N x-slabs (the reference's slenderX1 decomposition);
-    # total work is fixed as N grows, so scaling is STRONG.
-    grid = fx.make_grid(args.grid)
+    rank, N, local_rank = ctx.rank, ctx.world, ctx.local_rank
+    grid = fx.make_grid(gridname)
     dom = grid.dom
-    dt = fx.GRID_DT.get(args.grid, 3600.0)
-    case = fx.make_case(grid, args.scenario, ndte=args.ndte, dt=dt)
-    N = world
+    dt = fx.GRID_DT.get(gridname, 3600.0)
+    case = fx.make_case(grid, scenario, ndte=args.ndte, dt=dt)
 
     # x-slab boundaries: balanced by ocean T cells per column (static, from the land mask -- the
     # reference balances its block distribution the same way), or equal widths
     starts = None
-    if N > 1 and not args.equal_slabs:
+    if N > 1 and (not args.equal_slabs or dom.nx % N):
         starts = fx.balanced_slab_starts(grid.f["tmask"][1:-1, 1:-1] > 0, N)
 
     def sl(a):
@@ -242,40 +289,85 @@ def main():
 
     gridf = {k: sl(grid.f[k]) for k in evp.GRID_R8 + ("tmask", "umask", "HTE", "HTN")}
     inp, io, out = pin(case.inp), pin(case.io), pin(case.out)
+    io0 = {k: v.copy() for k, v in io.items()}          # the state before the first call
 
     e = evp.EvpGpu.for_domain(dom, args.ndte, dt, rank=rank, nranks=N, device=local_rank,
                               strict=not args.fma, use_cuda_graph=not args.no_graph,
                               compact_metrics=not args.no_compact_metrics, slab_start=starts)
     e.set_grid(gridf)
     if N > 1:
-        blob = e.peer_blob()
         blobs = [None] * N
-        dist.all_gather_object(blobs, blob)
+        ctx.dist.all_gather_object(blobs, e.peer_blob())
         e.set_peers(blobs)
-    e.upload(inp, io)
+
+    # ---- parity: ONE whole call from the initial state, every inout / out field, bitwise ----
+    parity = None
+    if do_parity:
+        e.upload(inp, io0)
+        e.compute(dt)
+        pio = {k: np.zeros_like(v) for k, v in io.items()}
+        pout = {k: np.zeros_like(v) for k, v in out.items()}
+        e.download(pio, pout)
+        mine = {k: _digest(pio[k]) for k in PARITY_IO}
+        mine.update({k: _digest(pout[k]) for k in PARITY_OUT})
+        umax_p = float(max(np.abs(pio["uvel"]).max(), np.abs(pio["vvel"]).max()))
+        allh = ctx.gather(mine)
+        verdict = None
+        if rank == 0:
+            from oracle import oracle as orc
+            t0 = time.perf_counter()
+            if ref_case is None:
+                ref_case = fx.make_case(grid, scenario, ndte=args.ndte, dt=dt)
+                orc.run_case(ref_case, nslabs=1, nthreads=len(os.sched_getaffinity(0)))
+            bad = []
+            for r in range(N):
+                for k in PARITY_IO + PARITY_OUT:
+                    ref = (ref_case.io if k in PARITY_IO else ref_case.out)[k]
+                    ref = fx.slab(ref, r, N, starts) if N > 1 else ref
+                    if _digest(ref) != allh[r][k]:
+                        bad.append((r, k))
+            verdict = {"bitwise": not bad, "fields": len(PARITY_IO) + len(PARITY_OUT), "nranks": N, "ndte": args.ndte,
+                       "mismatches": bad[:20], "oracle_s": round(time.perf_counter() - t0, 1),
+                       "what": "one whole evp call from the initial state through the benchmarked handles, every "
+                               "inout/out field of every rank's slab, SHA-256 of the physical cells against "
+                               "oracle/evp_oracle.c run as one block"}
+        verdict = ctx.bcast(verdict)
+        max_rel = 0.0
+        if not verdict["bitwise"]:
+            # diagnosis only: the relative size of the differences, field by field on the failing ranks
+            refs = ctx.bcast({k: (ref_case.io if k in PARITY_IO else ref_case.out)[k] for k in PARITY_IO + PARITY_OUT}
+                             if rank == 0 else None)
+            for (r, k) in verdict["mismatches"]:
+                if r == rank:
+                    ref = sl(refs[k])[1:-1, 1:-1].astype("f8")
+                    got = (pio if k in PARITY_IO else pout)[k][1:-1, 1:-1].astype("f8")
+                    den = np.abs(ref).max()
+                    max_rel = max(max_rel, float(np.abs(got - ref).max() / den) if den > 0 else float("inf"))
+        verdict["max_rel"] = ctx.allmax(max_rel)
+        verdict["umax"] = ctx.allmax(umax_p)
+        parity = verdict
 
     # ---- device-resident: W warm-up + K timed steps ----
-    for _ in range(args.warmup):
+    e.upload(inp, io0)
+    for _ in range(warmup):
         e.compute(dt)
     sampler = ClockSampler(local_rank)
-    barrier()
+    ctx.barrier()
     if rank == 0:
         sampler.start()
     t0 = time.perf_counter()
     dev_ms, loop_ms, launches = 0.0, 0.0, 0
-    for _ in range(args.steps):
+    for _ in range(steps):
         e.compute(dt)
         st = e.stats()
         dev_ms += st.total_ms
         loop_ms += st.loop_ms
         launches += st.kernel_launches
-    barrier()
+    ctx.barrier()
     wall_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.stop() if rank == 0 else None
     st = e.stats()
-    if os.environ.get("EVP_B200_TRACE"):
-        # per-subcycle timeline of the last call (device globaltimer): where the time between two
-        # subcycle kernels goes at N > 1
+    if os.environ.get("EVP_B200_TRACE") and st.loop_kernel_launches > 3:
         tr = e.trace().astype(np.int64)
         k = tr[:-1]
         med = lambda x: float(np.median(x)) / 1e3
@@ -283,94 +375,148 @@ def main():
               f"signal {med(k[:, 2] - k[:, 1]):.1f}  to-fold {med(k[:, 3] - k[:, 2]):.1f}  "
               f"wait {med(k[:, 4] - k[:, 3]):.1f}  fold+next-launch {med(tr[1:, 0] - k[:, 4]):.1f}  "
               f"period {med(tr[1:, 0] - k[:, 0]):.1f}", file=sys.stderr, flush=True)
-    act_t, act_u = st.active_t_cells, st.active_u_cells
+    act_t = st.active_t_cells
     loop_launches = st.loop_kernel_launches
+    # the state after W + K calls: finite, and moving
+    sio = {k: np.zeros_like(v) for k, v in io.items()}
+    e.download(sio, None)
+    fin_v = all(bool(np.isfinite(sio[k]).all()) for k in PARITY_IO if k != "iceumask")
+    umax_v = float(max(np.abs(sio["uvel"]).max(), np.abs(sio["vvel"]).max()))
 
-    def allmax(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def allsum(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
-
-    dev_ms = allmax(dev_ms)
-    loop_ms = allmax(loop_ms)
-    wall_ms = allmax(wall_ms)
-    # active cells: physical T cells only (the redundant ghost ring is not counted twice)
-    act_phys = allsum(float(act_t))
+    dev_ms_r, loop_ms_r = dev_ms, loop_ms
+    dev_ms = ctx.allmax(dev_ms)
+    loop_ms = ctx.allmax(loop_ms)
+    loop_ms_min = ctx.allmin(loop_ms_r)
+    wall_ms = ctx.allmax(wall_ms)
+    act_max = ctx.allmax(float(act_t))
+    act_phys = ctx.allsum(float(act_t))        # physical T cells only (the redundant ghost ring is not counted twice)
     cs_per_step = act_phys * args.ndte
-    value = cs_per_step * args.steps / (dev_ms * 1e-3)
+    value = cs_per_step * steps / (dev_ms * 1e-3)
+    check_value = {"all_finite": ctx.allmin(1.0 if fin_v else 0.0) == 1.0, "umax": ctx.allmax(umax_v)}
 
     # ---- e2e through evp_gpu_run with host buffers ----
     e2e = None
-    if not args.no_e2e:
+    if do_e2e:
+        for k, v in io0.items():
+            io[k][...] = v
         e.evp(dt, inp, io, out)                      # warm
-        barrier()
+        ctx.barrier()
         t0 = time.perf_counter()
-        for _ in range(args.steps):
+        for _ in range(steps):
             e.evp(dt, inp, io, out)
-        barrier()
-        e2e_ms = allmax((time.perf_counter() - t0) * 1e3)
+        ctx.barrier()
+        e2e_ms = ctx.allmax((time.perf_counter() - t0) * 1e3)
         plane = inp["aice"].nbytes
         iplane = io["iceumask"].nbytes
         # in: 12 fields less ss_tltx/y, which tilt_mode = 0 does not read (not uploaded); inout: u, v, 12 stresses, iceumask
         h2d = 10 * plane + 14 * plane + iplane
         d2h = 15 * plane + iplane + 19 * plane + iplane
-        e2e = {"value": cs_per_step * args.steps / (e2e_ms * 1e-3), "unit": "cell-subcycles/s",
-               "h2d_bytes_per_step": int(allsum(float(h2d))), "d2h_bytes_per_step": int(allsum(float(d2h))),
-               "ms_per_step": e2e_ms / args.steps,
+        fin_e = all(bool(np.isfinite(io[k]).all()) for k in PARITY_IO if k != "iceumask") and \
+            all(bool(np.isfinite(out[k]).all()) for k in PARITY_OUT if k != "icetmask")
+        umax_e = float(max(np.abs(io["uvel"]).max(), np.abs(io["vvel"]).max()))
+        e2e = {"value": cs_per_step * steps / (e2e_ms * 1e-3), "unit": "cell-subcycles/s",
+               "h2d_bytes_per_step": int(ctx.allsum(float(h2d))), "d2h_bytes_per_step": int(ctx.allsum(float(d2h))),
+               "ms_per_step": e2e_ms / steps,
+               "all_finite": ctx.allmin(1.0 if fin_e else 0.0) == 1.0, "umax": ctx.allmax(umax_e),
                "note": "evp_gpu_run: pinned host arrays -> H2D -> evp -> D2H of all inout + out fields"}
 
+    res = None
     if rank == 0:
         peak, peak_src = measured_peaks()
-        # the dominant kernel = the fused subcycle kernel; its average duration is the loop's CUDA
-        # event time / ndte (the loop also holds the 1-block tripole fold kernel per subcycle)
-        sub_ms = loop_ms / (args.steps * args.ndte)
-        ach = ALG_BYTES * (act_phys / N) / (sub_ms * 1e-3) / 1e9
+        # the dominant kernel: the persistent loop kernel runs all ndte subcycles in one launch, so "one launch
+        # of the old per-subcycle kernel" is the loop's CUDA-event time / ndte
+        sub_ms = loop_ms / (steps * args.ndte)
+        ach = ALG_BYTES * act_max / (sub_ms * 1e-3) / 1e9
+        loop_kernel = loop_launches <= 3
         roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": NCU_TRAFFIC.get((args.grid, args.scenario, N, not args.no_compact_metrics)),
-                "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum per launch, "
-                                  "profiles/r01_launches_tp01_final.md (null for other workloads)",
-                "peak_source": peak_src,
-                "kernel": "evp_subcycle_tma_kernel<false> (fused stress + stepu + E-W halo, TMA ring)"
-                          if os.environ.get("EVP_B200_KERNEL", "tma") != "sweep" else "evp_subcycle_kernel<false>",
-                "note": "achieved = 392 algorithmic B x active cells of one launch / (ndte-loop CUDA-event time / "
-                        "ndte); the loop also holds the small tripole fold kernel of every subcycle.  The kernel "
-                        "really moves fewer bytes than the algorithmic 392 B/cell (compact metric rows, merged "
-                        "coefficient planes): see traffic",
-                "alg_bytes_per_cell_subcycle": ALG_BYTES, "avg_launch_ms": sub_ms,
-                "active_cells_per_launch": act_phys / N}
+                "traffic": traffic, "peak_source": peak_src,
+                "kernel": ("evp_loop_tma_kernel (all ndte subcycles: fused stress + stepu + halo, TMA ring)" if loop_kernel
+                           else "evp_subcycle_tma_kernel<false>" if os.environ.get("EVP_B200_KERNEL", "tma") != "sweep"
+                           else "evp_subcycle_kernel<false>"),
+                "note": "achieved = 392 algorithmic B x active cells of the busiest rank x ndte / CUDA-event time of the "
+                        "ndte loop; traffic = ncu DRAM bytes per subcycle of the same workload (profiles/), null if not "
+                        "captured for it",
+                "alg_bytes_per_cell_subcycle": ALG_BYTES, "avg_subcycle_ms": sub_ms,
+                "active_cells_per_launch": act_max}
         res = {"metric": "EVP cell-subcycles/s", "value": value, "unit": "cell-subcycles/s",
-               "n_gpus": N, "steps": args.steps, "warmup": args.warmup,
-               "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+               "n_gpus": N, "steps": steps, "warmup": warmup,
+               "ms_per_step": dev_ms / steps, "higher_is_better": True,
                "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-               "config": {"workload": workload_name(args, dom, dt),
+               "config": {"workload": workload_name(args, dom, dt, gridname),
                           "decomposition": (f"{N} x-slab(s) of {dom.nx // N} columns" if starts is None else
                                             f"{N} x-slabs balanced by ocean cells, first columns {starts}"),
                           "active_t_cells": act_phys, "grid_cells": dom.nx * dom.ny,
-                          "l2": "working set per subcycle (~3 GB) exceeds the 126 MB L2; no flush needed"},
-               "loop_ms_per_step": loop_ms / args.steps, "wall_ms_per_step": wall_ms / args.steps,
-               "grid_value": dom.nx * dom.ny * args.ndte * args.steps / (dev_ms * 1e-3),
-               "roofline": roof, "clocks": clocks, "e2e": e2e,
+                          "l2": ("working set per subcycle exceeds the 126 MB L2; no flush needed"
+                                 if ALG_BYTES * act_max > L2_BYTES else
+                                 "working set per subcycle fits the L2 (an L2-resident configuration by nature: the "
+                                 "same state is swept ndte times per call); reported for completeness")},
+               "loop_ms_per_step": loop_ms / steps, "loop_ms_per_step_fastest_rank": loop_ms_min / steps,
+               "wall_ms_per_step": wall_ms / steps,
+               "us_per_subcycle": 1e3 * sub_ms,
+               "grid_value": dom.nx * dom.ny * args.ndte * steps / (dev_ms * 1e-3),
+               "roofline": roof, "clocks": clocks, "value_check": check_value, "parity": parity, "e2e": e2e,
                "gpu_launches": int(launches), "loop_kernel_launches_per_step": int(loop_launches)}
-        if not args.no_cpu_baseline and N == 1:
-            try:
-                res["cpu_baseline"] = cpu_sample(
-                    args, lambda n: fx.make_case(grid, args.scenario, ndte=n, dt=dt))
-            except Exception as ex:       # the oracle is only the reported baseline
-                res["cpu_baseline"] = {"value": None, "error": str(ex)}
-        print(json.dumps(res), flush=True)
     e.close()
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
+    return res
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args, int(os.environ.get("RANK", "0")))
+        return 0
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus and world == 1 and args.gpus > 1:
+        raise SystemExit("launch N > 1 with torch.distributed.run --nproc-per-node N")
+    from cice5_b200 import evp, fixtures as fx
+    if evp.device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device; the EVP path has no CPU fallback")
+    ctx = Ctx()
+    rank, N = ctx.rank, ctx.world
+
+    # CPU baseline first (rank 0, N = 1): its finished case is also the reference of the parity leg
+    cpu, ref_case = None, None
+    if rank == 0 and N == 1 and not args.no_cpu_baseline:
+        try:
+            grid = fx.make_grid(args.grid)
+            dt = fx.GRID_DT.get(args.grid, 3600.0)
+            kept = []
+            cpu = cpu_sample(args, lambda n: fx.make_case(grid, args.scenario, ndte=n, dt=dt), keep=kept)
+            if args.cpu_ndte == args.ndte:
+                ref_case = kept[0]
+        except Exception as ex:       # the oracle is only the reported baseline
+            cpu = {"value": None, "error": str(ex)}
+
+    traffic = NCU_TRAFFIC.get((args.grid, args.scenario, N, not args.no_compact_metrics))
+    res = measure(ctx, args, args.grid, args.scenario, args.steps, args.warmup, not args.no_e2e,
+                  not args.no_parity, ref_case, traffic)
+    others = {}
+    if not args.no_other_configs and args.grid == "tp01":
+        # the other BASELINE grid shapes, short runs (not bench lines of their own: SURVEY 8d table)
+        for g in ("gx3", "gx1", "tp1", "tp025"):
+            if N > 1 and g in ("gx3", "gx1") and N > 2:
+                continue                           # 100 / 320 columns: narrower than one strip per rank beyond 2 ranks
+            try:
+                r = measure(ctx, args, g, args.scenario, 10, 3, False, not args.no_parity, None, None)
+            except Exception as ex:               # noqa: BLE001
+                r = {"error": str(ex)[:200]} if rank == 0 else None
+            if rank == 0:
+                others[g] = r if "error" in r else {
+                    "workload": r["config"]["workload"], "value": r["value"], "us_per_subcycle": r["us_per_subcycle"],
+                    "ms_per_step": r["ms_per_step"], "roofline_frac": r["roofline"]["frac"],
+                    "active_t_cells": r["config"]["active_t_cells"],
+                    "regime": "HBM" if ALG_BYTES * r["roofline"]["active_cells_per_launch"] > L2_BYTES else "L2-resident",
+                    "parity": r["parity"], "value_check": r["value_check"],
+                    "loop_kernel_launches_per_step": r["loop_kernel_launches_per_step"]}
+    if rank == 0:
+        if cpu is not None:
+            res["cpu_baseline"] = cpu
+        if others:
+            res["other_configs"] = others
+        print(json.dumps(res), flush=True)
+    if ctx.dist is not None:
+        ctx.dist.barrier()
+        ctx.dist.destroy_process_group()
     return 0
 
 

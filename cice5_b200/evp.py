@@ -257,9 +257,12 @@ class EvpGpu:
     def compute(self, dt):
         self._check(self.lib.evp_gpu_compute(self._h, C.c_double(dt)))
 
-    def download(self, io, out):
-        s, o = self._io_struct(io), self._out_struct(out)
-        self._check(self.lib.evp_gpu_download(self._h, C.byref(s), C.byref(o)))
+    def download(self, io, out=None):
+        """Resident state -> host arrays; io or out may be None (nothing of that group is copied)."""
+        s = self._io_struct(io) if io is not None else None
+        o = self._out_struct(out) if out is not None else None
+        self._check(self.lib.evp_gpu_download(self._h, C.byref(s) if s is not None else None,
+                                              C.byref(o) if o is not None else None))
 
     def stats(self) -> Stats:
         st = Stats()
