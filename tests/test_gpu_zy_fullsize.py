@@ -1,11 +1,9 @@
 """Parity at the BASELINE sizes (configs[3] 1440x1080 and configs[4] 3600x2700), where the work
 list has thousands of items, 12 / 30 strips, compact metric rows on almost every row segment and
-the tripole fold runs at full width.  The oracle finishes these in seconds only for a short call,
-so the 0.1 degree grid runs ndte = 6 (and 4 for the 3-rank group); the property checked is the same
-as everywhere else: every inout / out field BITWISE equal to the CPU oracle.
-
-Added after the round's GPU budget was spent: xfail(strict=False) until the first hardware run
-(DESIGN.md section 8); the code under test is the validated default path, only the size is new."""
+the tripole fold runs at full width.  The property checked is the same as everywhere else: every inout
+/ out field BITWISE equal to the CPU oracle -- including the configuration bench.py times: 0.1 degree,
+ndte = 120, "full" and "caps" (the oracle needs about 20 s per call on the box's host cores).  The
+3-rank group on one device runs a short call (it drives the launch-per-subcycle path)."""
 import numpy as np
 import pytest
 
@@ -22,6 +20,21 @@ def test_quarter_degree_one_call_bitwise():
     got = clone_case(case)
     st = evp.run_case(got, strict=True, use_cuda_graph=True)
     assert st.active_t_cells > 100000
+    compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+    assert np.array_equal(phys(got.io["iceumask"]), phys(ref.io["iceumask"]))
+
+
+@pytest.mark.parametrize("scenario,active", [("full", 7630364), ("caps", None)])
+def test_tenth_degree_full_call_bitwise(scenario, active):
+    """BASELINE configs[4] exactly as benchmarked: 3600 x 2700, ndte = 120, one whole evp call."""
+    grid = fx.make_grid("tp01")
+    case = fx.make_case(grid, scenario, ndte=120)
+    ref = _oracle(case)
+    got = clone_case(case)
+    st = evp.run_case(got, strict=True, use_cuda_graph=True)
+    if active is not None:
+        assert st.active_t_cells == active
+    assert st.active_t_cells > 1000000 and float(np.abs(got.io["uvel"]).max()) > 1.0e-3
     compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
     assert np.array_equal(phys(got.io["iceumask"]), phys(ref.io["iceumask"]))
 
