@@ -23,6 +23,10 @@ VARIANTS = {
 }
 
 
+class NoCompiler(RuntimeError):
+    """nvcc is not on this box (the GPU box runs the prebuilt libraries)."""
+
+
 def lib_path(strict: bool = False) -> str:
     return os.path.join(LIBDIR, "libevp_b200_strict.so" if strict else "libevp_b200.so")
 
@@ -36,6 +40,10 @@ def _stale(out: str) -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+def is_stale(out: str) -> bool:
+    return _stale(out)
+
+
 def build(force: bool = False, verbose: bool = False) -> list[str]:
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     os.makedirs(LIBDIR, exist_ok=True)
@@ -46,7 +54,7 @@ def build(force: bool = False, verbose: bool = False) -> list[str]:
         if not force and not _stale(out):
             continue
         if not os.path.exists(nvcc):
-            raise RuntimeError(f"nvcc not found and {out} is missing or stale")
+            raise NoCompiler(f"nvcc not found and {out} is missing or stale")
         cmd = [nvcc, *ARCH, "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-shared",
                *(["-Xptxas", "-v"] if verbose else []), *extra, "-o", out,
                *[os.path.join(CSRC, s) for s in SOURCES]]

@@ -92,6 +92,12 @@ struct evp_handle {
     size_t off_planes = 0, off_inbox = 0, off_flags = 0, off_int = 0, off_mask = 0, off_counts = 0, off_tflags = 0;
     int tflags_ld = 0, tstrips = 0;
     std::vector<void *> pinned;                  // host arrays page-locked by evp_gpu_pin_host_arrays
+    // dense staging area for host <-> device copies (kRepackMax arrays of nxb * nyb doubles), allocated on first use
+    char *stage = nullptr;
+    std::vector<std::pair<void *, int>> batch_dst;   // pending batch: (plane pointer, is_int) in staging order
+    // resident-state protocol of evp_gpu_run (evp_gpu_set_resident)
+    bool resident = false, state_valid = false;
+    unsigned dl_mask = EVP_DL_ALL;
     bool strair_given = false;                   // evp_in_t.strax/stray given: strairx/y are copies of them
     int t_rpc = 0, t_chunks = 0, t_items = 0;    // TMA kernel work items: (strip, chunk of t_rpc rows)
     size_t off_trace = 0;                        // u64 trace[ndte][8] (EVP_B200_TRACE=1)
@@ -431,6 +437,7 @@ int evp_gpu_finalize(evp_handle_t *h)
     for (auto &ev : h->ev) if (ev) cudaEventDestroy(ev);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     if (h->itd) cudaFree(h->itd);
+    if (h->stage) cudaFree(h->stage);
     if (h->arena) cudaFree(h->arena);
     for (void *p : h->pinned) cudaHostUnregister(p);
     delete h;
@@ -484,34 +491,88 @@ int evp_gpu_synchronize(evp_handle_t *h)
     return EVP_OK;
 }
 
-static int h2d(evp_handle *h, int p, const double *src)
+}  // extern "C"
+
+// ---- host <-> device copies: dense staging + one repack kernel per batch (evp_prep.cuh) ----
+static int stage_ready(evp_handle *h)
+{
+    if (h->stage) return EVP_OK;
+    const size_t bytes = (size_t)kRepackMax * h->nxb * h->nyb * sizeof(double);
+    cudaError_t e = cudaMalloc(&h->stage, bytes);
+    if (e != cudaSuccess) {
+        snprintf(g_cuda_err, sizeof(g_cuda_err), "cudaMalloc(staging, %zu bytes): %s", bytes, cudaGetErrorString(e));
+        return EVP_ERR_CUDA;
+    }
+    return EVP_OK;
+}
+static char *stage_slot(evp_handle *h, size_t k) { return h->stage + k * (size_t)h->nxb * h->nyb * sizeof(double); }
+
+template <bool TO_PLANES>
+static int repack(evp_handle *h)
+{
+    if (h->batch_dst.empty()) return EVP_OK;
+    RepackArgs a;
+    memset(&a, 0, sizeof(a));
+    a.n = (int)h->batch_dst.size(); a.nxb = h->nxb; a.nyb = h->nyb; a.ld = h->ld;
+    for (int k = 0; k < a.n; ++k) {
+        a.pitched[k] = h->batch_dst[k].first; a.dense[k] = stage_slot(h, k); a.is_int[k] = (unsigned char)h->batch_dst[k].second;
+    }
+    dim3 grid((h->nxb + 127) / 128, h->nyb, a.n);
+    auto kern = repack_kernel<TO_PLANES>;
+    kern<<<grid, 128, 0, h->stream>>>(a);
+    CK(cudaGetLastError());
+    return EVP_OK;
+}
+// H2D: queue the dense copy of one array; h2d_flush() moves the batch into the planes
+static int h2d_any(evp_handle *h, void *plane, const void *src, int is_int)
 {
     if (!src) return EVP_ERR_ARG;
-    CK(cudaMemcpy2DAsync(h->plane(p), (size_t)h->ld * sizeof(double), src, (size_t)h->nxb * sizeof(double),
-                         (size_t)h->nxb * sizeof(double), h->nyb, cudaMemcpyHostToDevice, h->stream));
+    TRY(stage_ready(h));
+    if ((int)h->batch_dst.size() == kRepackMax) { TRY(repack<true>(h)); h->batch_dst.clear(); }
+    const size_t bytes = (size_t)h->nxb * h->nyb * (is_int ? sizeof(int) : sizeof(double));
+    CK(cudaMemcpyAsync(stage_slot(h, h->batch_dst.size()), src, bytes, cudaMemcpyHostToDevice, h->stream));
+    h->batch_dst.emplace_back(plane, is_int);
     return EVP_OK;
 }
-static int h2d_i(evp_handle *h, int p, const int *src)
+static int h2d(evp_handle *h, int p, const double *src) { return h2d_any(h, h->plane(p), src, 0); }
+static int h2d_i(evp_handle *h, int p, const int *src) { return h2d_any(h, h->iplane(p), src, 1); }
+static int h2d_flush(evp_handle *h)
 {
-    if (!src) return EVP_ERR_ARG;
-    CK(cudaMemcpy2DAsync(h->iplane(p), (size_t)h->ld * sizeof(int), src, (size_t)h->nxb * sizeof(int),
-                         (size_t)h->nxb * sizeof(int), h->nyb, cudaMemcpyHostToDevice, h->stream));
-    return EVP_OK;
+    const int rc = repack<true>(h);
+    h->batch_dst.clear();
+    return rc;
 }
-static int d2h_i(evp_handle *h, int p, int *dst, cudaStream_t s = nullptr)
-{
-    if (!dst) return EVP_OK;
-    CK(cudaMemcpy2DAsync(dst, (size_t)h->nxb * sizeof(int), h->iplane(p), (size_t)h->ld * sizeof(int),
-                         (size_t)h->nxb * sizeof(int), h->nyb, cudaMemcpyDeviceToHost, s ? s : h->stream));
-    return EVP_OK;
-}
-static int d2h(evp_handle *h, int p, double *dst, cudaStream_t s = nullptr)
-{
-    if (!dst) return EVP_OK;
-    CK(cudaMemcpy2DAsync(dst, (size_t)h->nxb * sizeof(double), h->plane(p), (size_t)h->ld * sizeof(double),
-                         (size_t)h->nxb * sizeof(double), h->nyb, cudaMemcpyDeviceToHost, s ? s : h->stream));
-    return EVP_OK;
-}
+// D2H: collect (plane, host pointer) pairs, then one repack kernel and one dense copy per array
+struct D2HBatch {
+    evp_handle *h;
+    std::vector<void *> host;
+    int add(void *plane, void *dst, int is_int)
+    {
+        if (!dst) return EVP_OK;
+        if ((int)h->batch_dst.size() == kRepackMax) TRY(flush());
+        h->batch_dst.emplace_back(plane, is_int);
+        host.push_back(dst);
+        return EVP_OK;
+    }
+    int r8(int p, double *dst) { return add(h->plane(p), dst, 0); }
+    int i4(int p, int *dst) { return add(h->iplane(p), dst, 1); }
+    int flush()
+    {
+        if (h->batch_dst.empty()) return EVP_OK;
+        TRY(stage_ready(h));
+        TRY(repack<false>(h));
+        for (size_t k = 0; k < host.size(); ++k) {
+            const size_t bytes = (size_t)h->nxb * h->nyb * (h->batch_dst[k].second ? sizeof(int) : sizeof(double));
+            CK(cudaMemcpyAsync(host[k], stage_slot(h, k), bytes, cudaMemcpyDeviceToHost, h->stream));
+        }
+        // the staging slots are reused by the next batch: it is enqueued behind these copies on the same stream
+        h->batch_dst.clear();
+        host.clear();
+        return EVP_OK;
+    }
+};
+
+extern "C" {
 
 int evp_gpu_set_grid(evp_handle_t *h, const evp_grid_t *gr)
 {
@@ -550,6 +611,7 @@ int evp_gpu_set_grid(evp_handle_t *h, const evp_grid_t *gr)
         // extrapolated row j = 1, halo-filled ghost rows, AusCOM's file tarea ...) keeps the planes
         TRY(h2d(h, G_HTE, gr->HTE));
         TRY(h2d(h, G_HTN, gr->HTN));
+        TRY(h2d_flush(h));
         if (h->use_tma) {
             MetricCheckArgs m;
             m.hte = h->plane(G_HTE); m.htn = h->plane(G_HTN);
@@ -564,15 +626,18 @@ int evp_gpu_set_grid(evp_handle_t *h, const evp_grid_t *gr)
     }
     TRY(h2d_i(h, 0, gr->tmask));
     TRY(h2d_i(h, 1, gr->umask));
+    TRY(h2d_flush(h));
     CK(cudaStreamSynchronize(h->stream));
     h->grid_set = true;
     return EVP_OK;
 }
 
+// io == NULL: only the per-call inputs go up, the dynamic state stays as the last evp left it on the device
 int evp_gpu_upload(evp_handle_t *h, const evp_in_t *in, const evp_inout_t *io)
 {
-    if (!h || !in || !io) return EVP_ERR_ARG;
+    if (!h || !in) return EVP_ERR_ARG;
     if (!h->grid_set) return EVP_ERR_STATE;
+    if (!io && !h->uploaded) return EVP_ERR_STATE;               // no resident state yet
     CK(cudaSetDevice(h->cfg.device));
     const double *src[12] = {in->aice, in->vice, in->vsno, in->aice_init, in->strairxT, in->strairyT,
                              in->uocn, in->vocn, in->ss_tltx, in->ss_tlty, in->Cdn_ocn, in->strength};
@@ -592,17 +657,21 @@ int evp_gpu_upload(evp_handle_t *h, const evp_in_t *in, const evp_inout_t *io)
         if ((dstp[p] == I_SSTLTX || dstp[p] == I_SSTLTY) && h->cfg.tilt_mode == 0) continue;
         TRY(h2d(h, dstp[p], src[p]));
     }
-    // dynamic state always lands in copy A
-    TRY(h2d(h, S_UA, io->uvel));
-    TRY(h2d(h, S_VA, io->vvel));
-    for (int c = 0; c < 4; ++c) {
-        TRY(h2d(h, S_STRA + c, io->stressp[c]));
-        TRY(h2d(h, S_STRA + 4 + c, io->stressm[c]));
-        TRY(h2d(h, S_STRA + 8 + c, io->stress12[c]));
+    if (io) {
+        // dynamic state always lands in copy A
+        TRY(h2d(h, S_UA, io->uvel));
+        TRY(h2d(h, S_VA, io->vvel));
+        for (int c = 0; c < 4; ++c) {
+            TRY(h2d(h, S_STRA + c, io->stressp[c]));
+            TRY(h2d(h, S_STRA + 4 + c, io->stressm[c]));
+            TRY(h2d(h, S_STRA + 8 + c, io->stress12[c]));
+        }
+        TRY(h2d_i(h, 2, io->iceumask));
+        h->parity = 0;
+        h->uploaded = true;
+        h->state_valid = true;
     }
-    TRY(h2d_i(h, 2, io->iceumask));
-    h->parity = 0;
-    h->uploaded = true;
+    TRY(h2d_flush(h));
     return EVP_OK;
 }
 
@@ -625,43 +694,71 @@ int evp_gpu_upload_itd(evp_handle_t *h, const evp_itd_t *itd)
         const double *src = p == 0 ? itd->aice0
                           : p <= (size_t)itd->ncat ? itd->aicen + (p - 1) * hostplane
                                                    : itd->vicen + (p - 1 - itd->ncat) * hostplane;
-        CK(cudaMemcpy2DAsync(h->itd + p * h->plane_elems, (size_t)h->ld * sizeof(double), src,
-                             (size_t)h->nxb * sizeof(double), (size_t)h->nxb * sizeof(double), h->nyb,
-                             cudaMemcpyHostToDevice, h->stream));
+        TRY(h2d_any(h, h->itd + p * h->plane_elems, src, 0));
     }
+    TRY(h2d_flush(h));
     h->itd_ready = true;
+    return EVP_OK;
+}
+
+static int download_groups(evp_handle *h, evp_inout_t *io, evp_out_t *out, unsigned mask)
+{
+    if (!h->uploaded) return EVP_ERR_STATE;
+    CK(cudaSetDevice(h->cfg.device));
+    D2HBatch B{h, {}};
+    h->batch_dst.clear();
+    if (io) {
+        const int U = h->parity ? S_UB : S_UA, V = h->parity ? S_VB : S_VA;
+        const int S = h->parity ? S_STRB : S_STRA;
+        if (mask & EVP_DL_VELOCITY) { TRY(B.r8(U, io->uvel)); TRY(B.r8(V, io->vvel)); }
+        if (mask & EVP_DL_STRESS)
+            for (int c = 0; c < 4; ++c) {
+                TRY(B.r8(S + c, io->stressp[c]));
+                TRY(B.r8(S + 4 + c, io->stressm[c]));
+                TRY(B.r8(S + 8 + c, io->stress12[c]));
+            }
+        if (mask & EVP_DL_HISTORY) { TRY(B.r8(S_FM, io->fm)); TRY(B.i4(2, io->iceumask)); }
+    }
+    if (out) {
+        double *dst[17] = {out->strairx, out->strairy, out->strtltx, out->strtlty, out->strocnx, out->strocny,
+                           out->strintx, out->strinty, out->strocnxT, out->strocnyT, out->divu, out->shear,
+                           out->rdg_conv, out->rdg_shear, out->prs_sig, out->uvel_init, out->vvel_init};
+        // groups of the 17 output planes (evp_out_t order)
+        static const unsigned grp[17] = {EVP_DL_HISTORY, EVP_DL_HISTORY, EVP_DL_HISTORY, EVP_DL_HISTORY, EVP_DL_HISTORY,
+                                         EVP_DL_HISTORY, EVP_DL_HISTORY, EVP_DL_HISTORY, EVP_DL_OCN_T, EVP_DL_OCN_T,
+                                         EVP_DL_DEFORM, EVP_DL_DEFORM, EVP_DL_DEFORM, EVP_DL_DEFORM, EVP_DL_HISTORY,
+                                         EVP_DL_HISTORY, EVP_DL_HISTORY};
+        for (int p = 0; p < 17; ++p)
+            if (mask & grp[p]) TRY(B.r8(O_STRAIRX + p, dst[p]));
+        if (mask & EVP_DL_HISTORY) {
+            TRY(B.r8(W_TMASS, out->tmass));
+            TRY(B.r8(W_STRENGTH, out->strength));
+            TRY(B.i4(3, out->icetmask));
+        }
+    }
+    TRY(B.flush());
+    CK(cudaStreamSynchronize(h->stream));
     return EVP_OK;
 }
 
 int evp_gpu_download(evp_handle_t *h, evp_inout_t *io, evp_out_t *out)
 {
     if (!h) return EVP_ERR_ARG;
-    if (!h->uploaded) return EVP_ERR_STATE;
-    CK(cudaSetDevice(h->cfg.device));
-    if (io) {
-        const int U = h->parity ? S_UB : S_UA, V = h->parity ? S_VB : S_VA;
-        const int S = h->parity ? S_STRB : S_STRA;
-        TRY(d2h(h, U, io->uvel));
-        TRY(d2h(h, V, io->vvel));
-        for (int c = 0; c < 4; ++c) {
-            TRY(d2h(h, S + c, io->stressp[c]));
-            TRY(d2h(h, S + 4 + c, io->stressm[c]));
-            TRY(d2h(h, S + 8 + c, io->stress12[c]));
-        }
-        TRY(d2h(h, S_FM, io->fm));
-        TRY(d2h_i(h, 2, io->iceumask));
-    }
-    if (out) {
-        double *dst[17] = {out->strairx, out->strairy, out->strtltx, out->strtlty, out->strocnx, out->strocny,
-                           out->strintx, out->strinty, out->strocnxT, out->strocnyT, out->divu, out->shear,
-                           out->rdg_conv, out->rdg_shear, out->prs_sig, out->uvel_init, out->vvel_init};
-        for (int p = 0; p < 17; ++p)
-            TRY(d2h(h, O_STRAIRX + p, dst[p]));
-        TRY(d2h(h, W_TMASS, out->tmass));
-        TRY(d2h(h, W_STRENGTH, out->strength));
-        TRY(d2h_i(h, 3, out->icetmask));
-    }
-    CK(cudaStreamSynchronize(h->stream));
+    return download_groups(h, io, out, EVP_DL_ALL);
+}
+
+int evp_gpu_set_resident(evp_handle_t *h, int resident, unsigned download_mask)
+{
+    if (!h || (download_mask & ~(unsigned)EVP_DL_ALL)) return EVP_ERR_ARG;
+    h->resident = resident != 0;
+    h->dl_mask = download_mask;
+    return EVP_OK;
+}
+
+int evp_gpu_invalidate_state(evp_handle_t *h)
+{
+    if (!h) return EVP_ERR_ARG;
+    h->state_valid = false;
     return EVP_OK;
 }
 
@@ -1248,9 +1345,10 @@ int evp_gpu_compute_group(evp_handle_t **hs, int n, double dt)
         hs[r]->shared_stream = n > 1;
         build_program(hs[r], dt, P[r]);
         L.push_back(Launcher{hs[r]});
-        if (P[r].ops.size() != P[0].ops.size()) return EVP_ERR_STATE;
     }
     int rc = EVP_OK;
+    for (int r = 0; r < n; ++r)
+        if (P[r].ops.size() != P[0].ops.size()) rc = EVP_ERR_STATE;
     long long n_before = 0, n_after = 0;
     for (size_t i = 0; i < P[0].ops.size() && rc == EVP_OK; ++i) {
         if (i == P[0].loop_begin) n_before = L[0].n;
@@ -1274,9 +1372,100 @@ int evp_gpu_compute_group(evp_handle_t **hs, int n, double dt)
 int evp_gpu_run(evp_handle_t *h, double dt, const evp_in_t *in, evp_inout_t *io, evp_out_t *out)
 {
     if (!h || !in || !io) return EVP_ERR_ARG;
-    TRY(evp_gpu_upload(h, in, io));
+    // resident protocol: the state goes up only when the device does not hold it (first call, invalidated)
+    const bool state_up = !h->resident || !h->state_valid || !h->uploaded;
+    TRY(evp_gpu_upload(h, in, state_up ? io : nullptr));
     TRY(evp_gpu_compute(h, dt));
-    return evp_gpu_download(h, io, out);
+    return download_groups(h, io, out, h->resident ? h->dl_mask : (unsigned)EVP_DL_ALL);
+}
+
+}  // extern "C"
+
+namespace {
+// the steps of restartfile's stress fix-up (source/ice_restart_driver.F90:370-394, 431-466) for one handle
+void build_restart_fixup(evp_handle *h, std::vector<Op> &ops)
+{
+    Builder B{h, ops};
+    const int S = h->parity ? S_STRB : S_STRA;
+    B.sync();                                                    // every rank's state is uploaded
+    if (h->cfg.grid_tripole) {                                   // :370-394
+        for (int f = 0; f < 3; ++f) {
+            const int b = S + 4 * f;
+            B.halo_stress(b + 0, b + 2); B.halo_stress(b + 2, b + 0);
+            B.halo_stress(b + 1, b + 3); B.halo_stress(b + 3, b + 1);
+        }
+    }
+    B.op([h, S](Launcher &L) {                                   // :431-466
+        dim3 grid((h->nxb + h->nyb + 127) / 128, 12);
+        zero_sw_ghosts_kernel<<<grid, 128, 0, L.s()>>>(h->plane(S), h->plane_elems, h->nxb, h->nyb, h->ld);
+        ++L.n;
+        CK(cudaGetLastError());
+        return EVP_OK;
+    });
+    B.sync();                                                    // inbox buffers are free again
+}
+int finish_fixup(evp_handle *h)
+{
+    CK(cudaMemcpyAsync(&h->h_error, h->dev_error(), sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (h->h_error) {
+        snprintf(g_cuda_err, sizeof(g_cuda_err), "halo wait timed out: a peer rank did not arrive");
+        return EVP_ERR_PEER;
+    }
+    return EVP_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int evp_gpu_restart_fixup(evp_handle_t *h)
+{
+    if (!h) return EVP_ERR_ARG;
+    if (!h->grid_set || !h->uploaded || !h->peers_set) return EVP_ERR_STATE;
+    CK(cudaSetDevice(h->cfg.device));
+    std::vector<Op> ops;
+    build_restart_fixup(h, ops);
+    Launcher L{h};
+    for (const Op &op : ops) {
+        if (op.sync) { TRY(launch_signal(L)); TRY(launch_wait(L)); }
+        else TRY(op.fn(L));
+    }
+    return finish_fixup(h);
+}
+
+// all ranks of a one-device group on one stream, steps interleaved (see evp_gpu_compute_group)
+int evp_gpu_restart_fixup_group(evp_handle_t **hs, int n)
+{
+    if (!hs || n < 1 || n > kMaxRanks) return EVP_ERR_ARG;
+    for (int r = 0; r < n; ++r) {
+        if (!hs[r] || hs[r]->cfg.nranks != n || hs[r]->cfg.rank != r) return EVP_ERR_ARG;
+        if (!hs[r]->grid_set || !hs[r]->uploaded || !hs[r]->peers_set) return EVP_ERR_STATE;
+        if (hs[r]->cfg.device != hs[0]->cfg.device) return EVP_ERR_UNSUPPORTED;
+    }
+    CK(cudaSetDevice(hs[0]->cfg.device));
+    std::vector<std::vector<Op>> P(n);
+    std::vector<Launcher> L;
+    for (int r = 0; r < n; ++r) {
+        CK(cudaStreamSynchronize(hs[r]->stream));
+        hs[r]->stream = hs[0]->own_stream;
+        build_restart_fixup(hs[r], P[r]);
+        L.push_back(Launcher{hs[r]});
+    }
+    int rc = EVP_OK;
+    for (size_t i = 0; i < P[0].size() && rc == EVP_OK; ++i) {
+        if (P[0][i].sync) {
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = launch_signal(L[r]);
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = launch_wait(L[r]);
+        } else {
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = P[r][i].fn(L[r]);
+        }
+    }
+    for (int r = 0; r < n; ++r) {
+        const int rc2 = rc == EVP_OK ? finish_fixup(hs[r]) : rc;
+        hs[r]->stream = hs[r]->own_stream;
+        if (rc2 != EVP_OK) rc = rc2;
+    }
+    return rc;
 }
 
 int evp_gpu_principal_stress(evp_handle_t *h, double *sig1, double *sig2)
@@ -1289,8 +1478,11 @@ int evp_gpu_principal_stress(evp_handle_t *h, double *sig1, double *sig2)
                                                             h->plane(S + 8), h->plane(O_PRSSIG), h->plane(W_1),
                                                             h->plane(W_2));
     CK(cudaGetLastError());
-    TRY(d2h(h, W_1, sig1));
-    TRY(d2h(h, W_2, sig2));
+    D2HBatch B{h, {}};
+    h->batch_dst.clear();
+    TRY(B.r8(W_1, sig1));
+    TRY(B.r8(W_2, sig2));
+    TRY(B.flush());
     CK(cudaStreamSynchronize(h->stream));
     return EVP_OK;
 }

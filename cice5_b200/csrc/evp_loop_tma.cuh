@@ -39,6 +39,11 @@
 namespace evp {
 
 constexpr int kItemFold = 0x20000000;        // tag of the fold item of a subcycle
+// timing experiments (bit mask, never the product): 1 no writer-side fences, 2 no reader-side proxy fence,
+// 4 no dependency polls at all (wrong answers at N > 1 / small grids), 8 last subcycle with the LAST = false body
+#ifndef EVP_LOOP_EXP
+#define EVP_LOOP_EXP 0
+#endif
 
 struct LoopTmaArgs {
     LoopArgs a;                  // geometry, constants, last-subcycle outputs, uvel_init (state pointers unused)
@@ -113,6 +118,161 @@ __device__ __forceinline__ const unsigned long long *neighbour_counter(const Loo
     return p.tflag + (size_t)chunk * p.strips + strip;
 }
 
+// The row sweep of one work item (strip, rows r0 .. rend) of one subcycle by the consumer warps: stress on T rows
+// r0 .. rend, stepu on U rows r0 .. rend-1, new state into copy par^1 (+ the neighbours' ghost columns and the
+// tripole inboxes).  Same statements as the consumer loop of evp_subcycle_tma_kernel.
+template <bool LAST, bool REVISED>
+__device__ __forceinline__ void sweep_item(const LoopTmaArgs &p, unsigned char *ring, unsigned long long *full_bar,
+                                           unsigned long long *empty_bar, int &stage, unsigned &phase, int strip, int r0,
+                                           int rend, int par, int ibuf, int warp, int lane)
+{
+    const LoopArgs &a = p.a;
+    const Consts &k = a.k;
+    const int ld = a.ld;
+    const size_t pe = p.plane_elems;
+    constexpr int kMetaOff = (kStateDepth + kTDepth + kUDepth) * kTmaBoxW * 8;
+    const int bi = 1 + warp * kUColsPerWarp + lane;                     // my column inside the box
+    double *const snew = p.state[par ^ 1];
+    double *const u1 = snew, *const v1 = snew + pe;
+    const int c = 1 + strip * kTmaUCols + warp * kUColsPerWarp + lane;   // T column (U column if lane < 31)
+    const bool warp_on = (c - lane) <= a.nxl;                       // warp-uniform
+    const int mshift = (strip * kTmaUCols) & 15;                    // mask box starts this many bytes early
+    const bool tcol = c <= a.nxl + 1;
+    const bool ucol = lane < kUColsPerWarp && c <= a.nxl;
+    const bool tstore_col = tcol && (lane < kUColsPerWarp || c == a.nxl + 1);
+    double *const uW = p.west_state[par ^ 1], *const uE = p.east_state[par ^ 1];
+
+    // row r0-1: velocities only
+    double u_s, v_s, uw_s, vw_s;
+    double htn_s = 0.0;                                             // HTN of the row below (compact rows)
+    bool loaded_s;                                                  // state of the row below was fetched
+    {
+        const double *st = reinterpret_cast<const double *>(ring + (size_t)stage * kStageBytes);
+        const unsigned meta = *reinterpret_cast<const unsigned *>(
+            ring + (size_t)stage * kStageBytes + kMetaOff + kMaskFlagOff);
+        loaded_s = (meta & kMetaState) != 0u;
+        if (meta & kMetaHtnExtra) htn_s = st[(kStateDepth + kSlotHtnExtra) * kTmaBoxW + bi];
+        u_s = st[bi]; v_s = st[kTmaBoxW + bi]; uw_s = st[bi - 1]; vw_s = st[kTmaBoxW + bi - 1];
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[stage]);
+        if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
+    }
+    double s1p = 0.0, s5p = 0.0, n2p = 0.0, n7p = 0.0;
+    unsigned mprev = 0;
+
+    for (int r = r0; r <= rend; ++r) {
+        mbar_wait(&full_bar[stage], phase);
+        const double *st = reinterpret_cast<const double *>(ring + (size_t)stage * kStageBytes);
+        const double *tc = st + kStateDepth * kTmaBoxW;
+        const double *uc = tc + kTDepth * kTmaBoxW;
+        const unsigned char *mk = reinterpret_cast<const unsigned char *>(uc + kUDepth * kTmaBoxW);
+        const unsigned meta = *reinterpret_cast<const unsigned *>(mk + kMaskFlagOff);
+        const bool loaded_c = (meta & kMetaState) != 0u;
+        const double u_c = st[bi], v_c = st[kTmaBoxW + bi];
+        const double uw_c = st[bi - 1], vw_c = st[kTmaBoxW + bi - 1];
+        const int mpos = bi + mshift;                               // mask box b covers bytes [128 b, 128 b + 144)
+        const int mbox = min(mpos >> 7, kMaskBoxes - 1);            // and sits 256 b bytes into the mask area
+        const unsigned m = (warp_on && tcol) ? mk[mbox * 256 + (mpos - mbox * 128)] : 0u;
+        const bool tact = (m & 1u) != 0;
+        const bool uact = warp_on && ucol && (mprev & 2u) && r > r0;
+        const bool any_t = __ballot_sync(0xffffffffu, tact) != 0u;
+        double s[12], tco[11], uco[kUDepth];
+        // tco: dxt dyt dxhy dyhx cxp cyp cxm cym tinyarea strength tarear
+        if (any_t) {
+#pragma unroll
+            for (int q = 0; q < 12; ++q) s[q] = st[(2 + q) * kTmaBoxW + bi];
+            if (meta & kMetaCompact) {
+                // metric terms from HTE / HTN by the reference's own formulas (ice_grid.F90:354-367,1456,1536);
+                // set_grid checked that they reproduce the host arrays bit for bit on this row segment
+                const double hte = tc[bi], hte_w = tc[bi - 1], htn = tc[kTmaBoxW + bi];
+                metric_terms(hte, hte_w, htn, htn_s, tco);
+                tco[9] = tc[2 * kTmaBoxW + bi];
+                tco[8] = (meta & kMetaTinyFromMetrics) ? __dmul_rn(p.puny, __dmul_rn(tco[0], tco[1]))
+                                                       : tc[3 * kTmaBoxW + bi];
+            } else {
+                tco[9] = tc[bi]; tco[8] = tc[kTmaBoxW + bi];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) tco[q] = tc[(2 + q) * kTmaBoxW + bi];
+            }
+            if (LAST) tco[10] = tc[kSlotTarear * kTmaBoxW + bi];
+        }
+        // southern HTN of the next row
+        if ((meta & (kMetaCompact | kMetaT)) == (kMetaCompact | kMetaT)) htn_s = tc[kTmaBoxW + bi];
+        else if (meta & kMetaHtnExtra) htn_s = tc[kSlotHtnExtra * kTmaBoxW + bi];
+
+        const size_t idx = (size_t)r * ld + c;
+        double str[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+        if (tact) {
+            double divu, shear, rdg_conv, rdg_shear, prs_sig;
+            stress_cell<LAST>(k, u_c, uw_c, u_s, uw_s, v_c, vw_c, v_s, vw_s, tco[0], tco[1], tco[2], tco[3],
+                              tco[4], tco[5], tco[6], tco[7], tco[8], tco[9], LAST ? tco[10] : 0.0, s, str, divu,
+                              shear, rdg_conv, rdg_shear, prs_sig);
+            if (tstore_col && (r < rend || r == a.ny + 1)) {
+                double *sp = snew + 2 * pe + idx;
+#pragma unroll
+                for (int q = 0; q < 12; ++q) sp[q * pe] = s[q];
+                if (LAST) {
+                    a.divu[idx] = divu; a.shear[idx] = shear; a.rdg_conv[idx] = rdg_conv;
+                    a.rdg_shear[idx] = rdg_shear; a.prs_sig[idx] = prs_sig;
+                }
+            }
+        }
+        const double e2 = shfl_down1(str[1]), e4 = shfl_down1(str[3]);
+        const double e7 = shfl_down1(str[6]), e8 = shfl_down1(str[7]);
+
+        if (r > r0 && warp_on && loaded_s) {                        // stepu on U row r-1 (:700-746)
+            const size_t iu = idx - ld;
+            double unew = u_s, vnew = v_s;
+            if (uact) {
+#pragma unroll
+                for (int q = 0; q < kUDepth - 2; ++q) uco[q] = uc[q * kTmaBoxW + bi];
+                uco[8] = p.water_is_ocn ? uco[1] : uc[8 * kTmaBoxW + bi];
+                uco[9] = p.water_is_ocn ? uco[2] : uc[9 * kTmaBoxW + bi];
+                // uco: aiu*rhow*Cw uocn vocn forcex forcey umassdti fm uarear waterx watery
+                const double uold = u_s, vold = v_s;
+                const double du = uco[1] - uold, dv = uco[2] - vold;
+                const double vrel = uco[0] * sqrt(du * du + dv * dv);
+                const double taux = vrel * uco[8], tauy = vrel * uco[9];
+                const double umdt = uco[5], fm = uco[6];
+                const double cca = (k.brlx + k.revp) * umdt + vrel * k.cosw;
+                const double ccb = fm + copysign(1.0, fm) * vrel * k.sinw;
+                const double ab2 = cca * cca + ccb * ccb;
+                const double uar = uco[7];
+                const double strintx = uar * (s1p + n2p + str[2] + e4);
+                const double strinty = uar * (s5p + str[5] + n7p + e8);
+                // revised EVP (revp = 1) also needs uvel_init (:731-734): two direct global loads,
+                // only in the REVISED instantiation
+                const double cc1 = strintx + uco[3] + taux +
+                                   umdt * (REVISED ? k.brlx * uold + k.revp * a.uvel_init[iu] : k.brlx * uold);
+                const double cc2 = strinty + uco[4] + tauy +
+                                   umdt * (REVISED ? k.brlx * vold + k.revp * a.vvel_init[iu] : k.brlx * vold);
+                unew = (cca * cc1 + ccb * cc2) / ab2;
+                vnew = (cca * cc2 - ccb * cc1) / ab2;
+                if (LAST) { a.strintx[iu] = strintx; a.strinty[iu] = strinty; }
+            }
+            if (ucol) {
+                u1[iu] = unew; v1[iu] = vnew;
+                if (c == 1 && uW) {
+                    const size_t ig = (size_t)(r - 1) * ld + a.nxl_west + 1;
+                    uW[ig] = unew; uW[pe + ig] = vnew;
+                }
+                if (c == a.nxl && uE) {
+                    const size_t ig = (size_t)(r - 1) * ld;
+                    uE[ig] = unew; uE[pe + ig] = vnew;
+                }
+                if (a.tripole && r - 1 >= a.ny - 1)
+                    tripole_push(a, p.inbox[ibuf], c, (r - 1) - (a.ny - 1), unew, vnew);
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[stage]);              // row done: slot free
+        if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
+        s1p = str[0]; s5p = str[4]; n2p = e2; n7p = e7;
+        u_s = u_c; v_s = v_c; uw_s = uw_c; vw_s = vw_c; mprev = m; loaded_s = loaded_c;
+    }
+
+}
+
 template <bool REVISED>
 __global__ void __launch_bounds__((kTmaConsumers + 1) * 32, kTmaBlocksPerSM)
 evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_constant__ CUtensorMap mapS2,
@@ -176,7 +336,7 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
             if (k > 0) {
                 // dependencies: the 3 x 3 tiles around this one have finished subcycle k-1 (lanes 0..8 poll
                 // one counter each), and, for a tile that reads rows ny / ny+1, the fold of k-1 (lane 9)
-                if (lane < 9) {
+                if ((EVP_LOOP_EXP & 4) == 0 && lane < 9) {
                     const unsigned long long *f = neighbour_counter(p, strip + lane % 3 - 1, chunk + lane / 3 - 1);
                     if (f) wait_counter(f, (unsigned long long)k, p.error, p.timeout_ns);
                 } else if (lane == 9 && p.has_fold && rend >= a.ny) {
@@ -185,7 +345,7 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
                 __syncwarp();
                 // the planes were written through the generic proxy (other SMs, other GPUs); TMA reads them
                 // through the async proxy
-                asm volatile("fence.proxy.async.global;" ::: "memory");
+                if ((EVP_LOOP_EXP & 2) == 0) asm volatile("fence.proxy.async.global;" ::: "memory");
             }
             if (lane == 0) {
                 const int par = p.parity0 ^ (k & 1);
@@ -289,154 +449,21 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
             continue;
         }
 
-        const bool last = step == p.nsteps - 1;
         const int strip = item % p.strips, chunk = item / p.strips;
-        const int c = 1 + strip * kTmaUCols + warp * kUColsPerWarp + lane;   // T column (U column if lane < 31)
-        const bool warp_on = (c - lane) <= a.nxl;                       // warp-uniform
-        const int mshift = (strip * kTmaUCols) & 15;                    // mask box starts this many bytes early
         int r0, rend;
         chunk_rows(chunk, a.rows_per_chunk, a.ny, r0, rend);
-        const bool tcol = c <= a.nxl + 1;
-        const bool ucol = lane < kUColsPerWarp && c <= a.nxl;
-        const bool tstore_col = tcol && (lane < kUColsPerWarp || c == a.nxl + 1);
-        double *const uW = p.west_state[par ^ 1], *const uE = p.east_state[par ^ 1];
-
-        // row r0-1: velocities only
-        double u_s, v_s, uw_s, vw_s;
-        double htn_s = 0.0;                                             // HTN of the row below (compact rows)
-        bool loaded_s;                                                  // state of the row below was fetched
-        {
-            const double *st = reinterpret_cast<const double *>(ring + (size_t)stage * kStageBytes);
-            const unsigned meta = *reinterpret_cast<const unsigned *>(mk0 + kMaskFlagOff);
-            loaded_s = (meta & kMetaState) != 0u;
-            if (meta & kMetaHtnExtra) htn_s = st[(kStateDepth + kSlotHtnExtra) * kTmaBoxW + bi];
-            u_s = st[bi]; v_s = st[kTmaBoxW + bi]; uw_s = st[bi - 1]; vw_s = st[kTmaBoxW + bi - 1];
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&empty_bar[stage]);
-            if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
-        }
-        double s1p = 0.0, s5p = 0.0, n2p = 0.0, n7p = 0.0;
-        unsigned mprev = 0;
-
-        for (int r = r0; r <= rend; ++r) {
-            mbar_wait(&full_bar[stage], phase);
-            const double *st = reinterpret_cast<const double *>(ring + (size_t)stage * kStageBytes);
-            const double *tc = st + kStateDepth * kTmaBoxW;
-            const double *uc = tc + kTDepth * kTmaBoxW;
-            const unsigned char *mk = reinterpret_cast<const unsigned char *>(uc + kUDepth * kTmaBoxW);
-            const unsigned meta = *reinterpret_cast<const unsigned *>(mk + kMaskFlagOff);
-            const bool loaded_c = (meta & kMetaState) != 0u;
-            const double u_c = st[bi], v_c = st[kTmaBoxW + bi];
-            const double uw_c = st[bi - 1], vw_c = st[kTmaBoxW + bi - 1];
-            const int mpos = bi + mshift;                               // mask box b covers bytes [128 b, 128 b + 144)
-            const int mbox = min(mpos >> 7, kMaskBoxes - 1);            // and sits 256 b bytes into the mask area
-            const unsigned m = (warp_on && tcol) ? mk[mbox * 256 + (mpos - mbox * 128)] : 0u;
-            const bool tact = (m & 1u) != 0;
-            const bool uact = warp_on && ucol && (mprev & 2u) && r > r0;
-            const bool any_t = __ballot_sync(0xffffffffu, tact) != 0u;
-            double s[12], tco[11], uco[kUDepth];
-            // tco: dxt dyt dxhy dyhx cxp cyp cxm cym tinyarea strength tarear
-            if (any_t) {
-#pragma unroll
-                for (int q = 0; q < 12; ++q) s[q] = st[(2 + q) * kTmaBoxW + bi];
-                if (meta & kMetaCompact) {
-                    // metric terms from HTE / HTN by the reference's own formulas (ice_grid.F90:354-367,1456,1536);
-                    // set_grid checked that they reproduce the host arrays bit for bit on this row segment
-                    const double hte = tc[bi], hte_w = tc[bi - 1], htn = tc[kTmaBoxW + bi];
-                    metric_terms(hte, hte_w, htn, htn_s, tco);
-                    tco[9] = tc[2 * kTmaBoxW + bi];
-                    tco[8] = (meta & kMetaTinyFromMetrics) ? __dmul_rn(p.puny, __dmul_rn(tco[0], tco[1]))
-                                                           : tc[3 * kTmaBoxW + bi];
-                } else {
-                    tco[9] = tc[bi]; tco[8] = tc[kTmaBoxW + bi];
-#pragma unroll
-                    for (int q = 0; q < 8; ++q) tco[q] = tc[(2 + q) * kTmaBoxW + bi];
-                }
-                tco[10] = last ? tc[kSlotTarear * kTmaBoxW + bi] : 0.0;
-            }
-            // southern HTN of the next row
-            if ((meta & (kMetaCompact | kMetaT)) == (kMetaCompact | kMetaT)) htn_s = tc[kTmaBoxW + bi];
-            else if (meta & kMetaHtnExtra) htn_s = tc[kSlotHtnExtra * kTmaBoxW + bi];
-
-            const size_t idx = (size_t)r * ld + c;
-            double str[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-            if (tact) {
-                double divu, shear, rdg_conv, rdg_shear, prs_sig;
-                if (last)
-                    stress_cell<true>(k, u_c, uw_c, u_s, uw_s, v_c, vw_c, v_s, vw_s, tco[0], tco[1], tco[2], tco[3],
-                                      tco[4], tco[5], tco[6], tco[7], tco[8], tco[9], tco[10], s, str, divu, shear,
-                                      rdg_conv, rdg_shear, prs_sig);
-                else
-                    stress_cell<false>(k, u_c, uw_c, u_s, uw_s, v_c, vw_c, v_s, vw_s, tco[0], tco[1], tco[2], tco[3],
-                                       tco[4], tco[5], tco[6], tco[7], tco[8], tco[9], 0.0, s, str, divu, shear,
-                                       rdg_conv, rdg_shear, prs_sig);
-                if (tstore_col && (r < rend || r == a.ny + 1)) {
-                    double *sp = snew + 2 * pe + idx;
-#pragma unroll
-                    for (int q = 0; q < 12; ++q) sp[q * pe] = s[q];
-                    if (last) {
-                        a.divu[idx] = divu; a.shear[idx] = shear; a.rdg_conv[idx] = rdg_conv;
-                        a.rdg_shear[idx] = rdg_shear; a.prs_sig[idx] = prs_sig;
-                    }
-                }
-            }
-            const double e2 = shfl_down1(str[1]), e4 = shfl_down1(str[3]);
-            const double e7 = shfl_down1(str[6]), e8 = shfl_down1(str[7]);
-
-            if (r > r0 && warp_on && loaded_s) {                        // stepu on U row r-1 (:700-746)
-                const size_t iu = idx - ld;
-                double unew = u_s, vnew = v_s;
-                if (uact) {
-#pragma unroll
-                    for (int q = 0; q < kUDepth - 2; ++q) uco[q] = uc[q * kTmaBoxW + bi];
-                    uco[8] = p.water_is_ocn ? uco[1] : uc[8 * kTmaBoxW + bi];
-                    uco[9] = p.water_is_ocn ? uco[2] : uc[9 * kTmaBoxW + bi];
-                    // uco: aiu*rhow*Cw uocn vocn forcex forcey umassdti fm uarear waterx watery
-                    const double uold = u_s, vold = v_s;
-                    const double du = uco[1] - uold, dv = uco[2] - vold;
-                    const double vrel = uco[0] * sqrt(du * du + dv * dv);
-                    const double taux = vrel * uco[8], tauy = vrel * uco[9];
-                    const double umdt = uco[5], fm = uco[6];
-                    const double cca = (k.brlx + k.revp) * umdt + vrel * k.cosw;
-                    const double ccb = fm + copysign(1.0, fm) * vrel * k.sinw;
-                    const double ab2 = cca * cca + ccb * ccb;
-                    const double uar = uco[7];
-                    const double strintx = uar * (s1p + n2p + str[2] + e4);
-                    const double strinty = uar * (s5p + str[5] + n7p + e8);
-                    // revised EVP (revp = 1) also needs uvel_init (:731-734): two direct global loads,
-                    // only in the REVISED instantiation
-                    const double cc1 = strintx + uco[3] + taux +
-                                       umdt * (REVISED ? k.brlx * uold + k.revp * a.uvel_init[iu] : k.brlx * uold);
-                    const double cc2 = strinty + uco[4] + tauy +
-                                       umdt * (REVISED ? k.brlx * vold + k.revp * a.vvel_init[iu] : k.brlx * vold);
-                    unew = (cca * cc1 + ccb * cc2) / ab2;
-                    vnew = (cca * cc2 - ccb * cc1) / ab2;
-                    if (last) { a.strintx[iu] = strintx; a.strinty[iu] = strinty; }
-                }
-                if (ucol) {
-                    u1[iu] = unew; v1[iu] = vnew;
-                    if (c == 1 && uW) {
-                        const size_t ig = (size_t)(r - 1) * ld + a.nxl_west + 1;
-                        uW[ig] = unew; uW[pe + ig] = vnew;
-                    }
-                    if (c == a.nxl && uE) {
-                        const size_t ig = (size_t)(r - 1) * ld;
-                        uE[ig] = unew; uE[pe + ig] = vnew;
-                    }
-                    if (a.tripole && r - 1 >= a.ny - 1)
-                        tripole_push(a, p.inbox[ibuf], c, (r - 1) - (a.ny - 1), unew, vnew);
-                }
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&empty_bar[stage]);              // row done: slot free
-            if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
-            s1p = str[0]; s5p = str[4]; n2p = e2; n7p = e7;
-            u_s = u_c; v_s = v_c; uw_s = uw_c; vw_s = vw_c; mprev = m; loaded_s = loaded_c;
-        }
+        // two instantiations of the row sweep: the last subcycle also fetches tarear and writes divu, shear,
+        // rdg_*, prs_sig, strint* (a run-time flag inside one body cost registers in all the others)
+        if (step == p.nsteps - 1 && (EVP_LOOP_EXP & 8) == 0)
+            sweep_item<true, REVISED>(p, ring, full_bar, empty_bar, stage, phase, strip, r0, rend, par, ibuf, warp, lane);
+        else
+            sweep_item<false, REVISED>(p, ring, full_bar, empty_bar, stage, phase, strip, r0, rend, par, ibuf, warp, lane);
 
         // ---- publish: this tile has finished subcycle `step` ----
-        if (p.nranks > 1) __threadfence_system(); else __threadfence();
-        asm volatile("fence.proxy.async.global;" ::: "memory");
+        if ((EVP_LOOP_EXP & 1) == 0) {
+            if (p.nranks > 1) __threadfence_system(); else __threadfence();
+            asm volatile("fence.proxy.async.global;" ::: "memory");
+        }
         asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
         if (tid == 0) {
             const unsigned long long done = (unsigned long long)step + 1;

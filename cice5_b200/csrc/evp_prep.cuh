@@ -145,6 +145,42 @@ __global__ void halo_stress_apply_kernel(double *a1, Geom g, InboxGeom ib, doubl
     }
 }
 
+// ---- host <-> device staging: the caller's arrays are dense (nx_block x ny_block), the arena's planes are
+// pitched (rows on 128-byte lines for TMA).  One contiguous copy per array over the host link, then ONE kernel
+// that moves all arrays of the batch between the dense staging area and their planes (round 1 issued a
+// row-pitched 2-D copy per array: 3.6 kB rows at N = 8 ran at 13 GB/s).
+constexpr int kRepackMax = 48;
+struct RepackArgs {
+    int n, nxb, nyb, ld;
+    void *pitched[kRepackMax];          // plane in the arena (double or int32)
+    void *dense[kRepackMax];            // staging area
+    unsigned char is_int[kRepackMax];
+};
+template <bool TO_PLANES>
+__global__ void repack_kernel(const __grid_constant__ RepackArgs a)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y, k = blockIdx.z;
+    if (c >= a.nxb) return;
+    const size_t ip = (size_t)r * a.ld + c, id = (size_t)r * a.nxb + c;
+    if (a.is_int[k]) {
+        int *p = static_cast<int *>(a.pitched[k]), *d = static_cast<int *>(a.dense[k]);
+        if (TO_PLANES) p[ip] = d[id]; else d[id] = p[ip];
+    } else {
+        double *p = static_cast<double *>(a.pitched[k]), *d = static_cast<double *>(a.dense[k]);
+        if (TO_PLANES) p[ip] = d[id]; else d[id] = p[ip];
+    }
+}
+
+// restart hand-off (source/ice_restart_driver.F90:431-466): the unused south ghost row and west ghost column
+// of the 12 stresses are zeroed after a restart file has been read
+__global__ void zero_sw_ghosts_kernel(double *s0, size_t plane_elems, int nxb, int nyb, int ld)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x, q = blockIdx.y;
+    double *s = s0 + (size_t)q * plane_elems;
+    if (t < nxb) s[t] = 0.0;                                   // j = 1 (nghost = 1)
+    else if (t < nxb + nyb) s[(size_t)(t - nxb) * ld] = 0.0;   // i = 1
+}
+
 // ---- cross-rank synchronisation: SyncArgs, peer_signal, peer_wait live in evp_kernels.cuh ---------
 __global__ void halo_signal_kernel(const __grid_constant__ SyncArgs a)
 {

@@ -74,7 +74,11 @@ EXPORTS = ("evp_gpu_init", "evp_gpu_set_grid", "evp_gpu_run", "evp_gpu_upload", 
            "evp_gpu_download", "evp_gpu_compute_group", "evp_gpu_get_stats", "evp_gpu_synchronize", "evp_gpu_peer_blob_size",
            "evp_gpu_get_peer_blob", "evp_gpu_set_peers", "evp_gpu_finalize", "evp_gpu_strerror",
            "evp_gpu_last_cuda_error", "evp_gpu_device_count", "evp_gpu_get_trace", "evp_gpu_upload_itd",
-           "evp_gpu_principal_stress", "evp_gpu_pin_host_arrays")
+           "evp_gpu_principal_stress", "evp_gpu_pin_host_arrays", "evp_gpu_set_resident",
+           "evp_gpu_invalidate_state", "evp_gpu_restart_fixup", "evp_gpu_restart_fixup_group")
+
+# download groups of the resident-state protocol (include/evp_b200.h)
+DL_VELOCITY, DL_STRESS, DL_DEFORM, DL_OCN_T, DL_HISTORY, DL_ALL = 1, 2, 4, 8, 16, 31
 
 _libs: dict = {}
 
@@ -89,11 +93,15 @@ def load_library(strict: bool = True):
     if strict in _libs:
         return _libs[strict]
     path = os.environ.get("EVP_B200_LIB") or _build.lib_path(strict)   # override: kernel-tuning experiments
-    try:
-        _build.build()
-    except Exception:
-        if not os.path.exists(path):
-            raise
+    if not os.environ.get("EVP_B200_LIB"):
+        # refuse a stale library: a compile failure of edited sources must not let the tests and the bench run
+        # (and report parity for) code that no longer builds; only "no nvcc on this box" is tolerated, and only
+        # when the library on disk is newer than every source (the GPU box runs the prebuilt file)
+        try:
+            _build.build()
+        except _build.NoCompiler:
+            if not os.path.exists(path) or _build.is_stale(path):
+                raise
     if not os.path.exists(path):
         raise EvpError(f"CUDA extension {path} is missing: build it with `python -m cice5_b200.build`")
     lib = C.CDLL(path)
@@ -264,6 +272,18 @@ class EvpGpu:
         self._check(self.lib.evp_gpu_download(self._h, C.byref(s) if s is not None else None,
                                               C.byref(o) if o is not None else None))
 
+    def set_resident(self, resident=True, download_mask=DL_VELOCITY | DL_DEFORM | DL_OCN_T):
+        """Resident-state protocol of evp(): the dynamic state goes up only when the device does not hold it;
+        only the groups of `download_mask` come back (default: what transport, ridging and the coupler read)."""
+        self._check(self.lib.evp_gpu_set_resident(self._h, C.c_int(int(resident)), C.c_uint(download_mask)))
+
+    def invalidate_state(self):
+        self._check(self.lib.evp_gpu_invalidate_state(self._h))
+
+    def restart_fixup(self):
+        """What restartfile does to freshly read stresses (ice_restart_driver.F90:370-394,431-466), in place."""
+        self._check(self.lib.evp_gpu_restart_fixup(self._h))
+
     def stats(self) -> Stats:
         st = Stats()
         self._check(self.lib.evp_gpu_get_stats(self._h, C.byref(st)))
@@ -367,6 +387,26 @@ class EvpGroup:
             if out[k] is not None:
                 out[k][...] = self._fx.unslab([p[1][k] for p in parts])
         return [e.stats() for e in self.ranks]
+
+    def upload(self, inp, io):
+        for r, e in enumerate(self.ranks):
+            e.upload(self._slabs(inp, r), self._slabs(io, r))
+
+    def download(self, io, out):
+        parts = []
+        for r, e in enumerate(self.ranks):
+            sio, so = self._slabs(io, r), self._slabs(out, r)
+            e.download(sio, so)
+            parts.append((sio, so))
+        for k in io:
+            io[k][...] = self._fx.unslab([p[0][k] for p in parts])
+        for k in out:
+            if out[k] is not None:
+                out[k][...] = self._fx.unslab([p[1][k] for p in parts])
+
+    def restart_fixup(self):
+        arr = (C.c_void_p * self.n)(*[e._h for e in self.ranks])
+        self.ranks[0]._check(self.ranks[0].lib.evp_gpu_restart_fixup_group(arr, self.n))
 
     def close(self):
         for e in self.ranks:

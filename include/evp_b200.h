@@ -148,6 +148,36 @@ int evp_gpu_upload(evp_handle_t *h, const evp_in_t *in, const evp_inout_t *io);
 int evp_gpu_compute(evp_handle_t *h, double dt);
 int evp_gpu_download(evp_handle_t *h, evp_inout_t *io, evp_out_t *out);
 
+/* Resident-state protocol of evp_gpu_run.  The dynamic state (uvel, vvel, the 12 stresses,
+ * iceumask) lives on the device between calls -- evp is its only writer in the reference's time step
+ * (source/ice_step_mod.F90:1119-1141) -- so a call only has to move what changed on the host and what the host
+ * reads next:
+ *   resident = 1: evp_gpu_run uploads evp_in_t every call, evp_inout_t only on the first call and after
+ *                 evp_gpu_invalidate_state (a restart was read, the host edited the state);
+ *   download_mask: which groups evp_gpu_run copies back (pointers that are NULL are skipped as before):
+ *     EVP_DL_VELOCITY  uvel, vvel                      -> transport_remap (ice_step_mod.F90:1126-1130)
+ *     EVP_DL_DEFORM    divu, shear, rdg_conv, rdg_shear -> step_ridge / ridge_ice (:1139), history
+ *     EVP_DL_OCN_T     strocnxT, strocnyT              -> coupler (ice_flux.F90:52-53), restart
+ *     EVP_DL_STRESS    the 12 stresses                 -> restart files only (ice_restart_driver.F90:122-176)
+ *     EVP_DL_HISTORY   everything else (strair*, strtlt*, strocnx/y, strint*, prs_sig, uvel_init, vvel_init,
+ *                      tmass, strength, icetmask, fm, iceumask) -> history accumulation / diagnostics
+ * evp_gpu_download(h, io, out) still returns every array at any time (history / restart steps).
+ * Default: resident = 0, mask = EVP_DL_ALL: every array goes up and comes back, as in round 1. */
+enum { EVP_DL_VELOCITY = 1, EVP_DL_STRESS = 2, EVP_DL_DEFORM = 4, EVP_DL_OCN_T = 8, EVP_DL_HISTORY = 16,
+       EVP_DL_ALL = 31 };
+int evp_gpu_set_resident(evp_handle_t *h, int resident, unsigned download_mask);
+int evp_gpu_invalidate_state(evp_handle_t *h);
+
+/* Restart hand-off on the resident state, after the host has read a restart file into
+ * its arrays and uploaded them (evp_gpu_upload, or the next evp_gpu_run after evp_gpu_invalidate_state):
+ * what restartfile does to the stresses once they are read (source/ice_restart_driver.F90:370-394: the 12
+ * ice_HaloUpdate_stress calls of a tripole grid, same pairing as ice_dyn_evp.F90:416-481; :431-466: zero the
+ * unused south ghost row and west ghost column of the 12 stresses) -- on the device, in place.  With several
+ * ranks every rank calls it (it contains cross-rank halo exchanges, like evp_gpu_compute). */
+int evp_gpu_restart_fixup(evp_handle_t *h);
+/* the same for the ranks of a one-device group (see evp_gpu_compute_group) */
+int evp_gpu_restart_fixup_group(evp_handle_t **handles, int n);
+
 /* Several ranks driven by one host thread (handles of ranks 0..n-1 on ONE device, e.g. tests with
  * fewer GPUs than ranks): steps are interleaved on one stream so that no kernel ever waits. */
 int evp_gpu_compute_group(evp_handle_t **handles, int n, double dt);

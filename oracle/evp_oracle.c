@@ -1015,6 +1015,32 @@ int evp_oracle_halo_stress(const evp_oracle_cfg *cfg, double *a1, const double *
     return 0;
 }
 
+/* What restartfile does to the 12 stresses once they are read (source/ice_restart_driver.F90): on a tripole
+ * grid the 12 ice_HaloUpdate_stress calls (:370-394, the pairing of ice_dyn_evp.F90:416-481), then the unused
+ * south ghost row and west ghost column of every block are zeroed (:431-466, j = 1..nghost / i = 1..nghost).
+ * s[12]: stressp_1..4, stressm_1..4, stress12_1..4 as global-with-ghost planes, in place. */
+int evp_oracle_restart_fixup(const evp_oracle_cfg *cfg, double *const *s)
+{
+    Dom dom; double **f[12];
+    if (!cfg || !s || cfg->nx_global % (cfg->nslabs > 0 ? cfg->nslabs : 1)) return 1;
+    cfg_to_dom(cfg, &dom);
+    for (int q = 0; q < 12; ++q) f[q] = split_r8(&dom, s[q]);
+    if (cfg->grid_tripole) {
+        for (int g = 0; g < 3; ++g) {
+            double ***b = f + 4 * g;
+            halo_stress(&dom, b[0], b[2]);  halo_stress(&dom, b[2], b[0]);
+            halo_stress(&dom, b[1], b[3]);  halo_stress(&dom, b[3], b[1]);
+        }
+    }
+    for (int q = 0; q < 12; ++q)
+        for (int b = 0; b < dom.nslabs; ++b) {
+            for (int i = 1; i <= dom.nxb; ++i) f[q][b][IX(&dom, i, 1)] = 0.0;
+            for (int j = 1; j <= dom.nyb; ++j) f[q][b][IX(&dom, 1, j)] = 0.0;
+        }
+    for (int q = 0; q < 12; ++q) { merge_r8(&dom, f[q], s[q]); free_slabs(&dom, (void **)f[q]); }
+    return 0;
+}
+
 /* principal_stress, ice_dyn_shared.F90:853-893; spval_dbl = 1e30 (ice_constants.F90) */
 void evp_oracle_principal_stress(long long n, const double *stressp_1, const double *stressm_1,
                                  const double *stress12_1, const double *prs_sig,

@@ -140,6 +140,10 @@ int evp_oracle_halo_i4(const evp_oracle_cfg *cfg, int *a, int loc, int kind, int
 /* ice_HaloUpdate_stress(array1, array2, halo, center, scalar): array1's ghosts from array2 */
 int evp_oracle_halo_stress(const evp_oracle_cfg *cfg, double *a1, const double *a2);
 
+/* restartfile's treatment of freshly read stresses (source/ice_restart_driver.F90:370-394, 431-466): 12 x
+ * ice_HaloUpdate_stress on a tripole grid, then zero south ghost row / west ghost column.  s[12] in place. */
+int evp_oracle_restart_fixup(const evp_oracle_cfg *cfg, double *const *s);
+
 /* principal_stress, ice_dyn_shared.F90:853-893 (diagnostic, n elements) */
 void evp_oracle_principal_stress(long long n, const double *stressp_1, const double *stressm_1,
                                  const double *stress12_1, const double *prs_sig,

@@ -161,6 +161,16 @@ def halo_stress(dom, a1, a2, nslabs=1):
     return a1
 
 
+def restart_fixup(dom, io, nslabs=1):
+    """ice_restart_driver.F90:370-394,431-466 on the 12 stresses of `io` (global-with-ghost planes), in place."""
+    from cice5_b200 import fixtures as fx
+    cfg = make_cfg(dom, 1, 1.0, nslabs)
+    arr = (_DP * 12)(*[_dp(io[n]) for n in fx.STRESS_FIELDS])
+    rc = lib().evp_oracle_restart_fixup(C.byref(cfg), arr)
+    assert rc == 0
+    return io
+
+
 def principal_stress(sp1, sm1, s121, prs):
     sig1, sig2 = np.empty_like(sp1), np.empty_like(sp1)
     lib().evp_oracle_principal_stress(C.c_longlong(sp1.size), _dp(sp1), _dp(sm1), _dp(s121),

@@ -450,3 +450,78 @@ def test_device_sources_match_reference_digests_on_the_real_gx3_grid(dev, name):
     case, kw, layout, d = digest_case(name)
     dev.run_case(case, strict=True, **kw)
     check_digests(case, layout, d)
+
+
+def _rand_stresses(case, seed=7):
+    rng = np.random.default_rng(seed)
+    for n in fx.STRESS_FIELDS:
+        case.io[n][...] = rng.standard_normal(case.io[n].shape) * 1.0e3      # ghost cells hold garbage too
+
+
+@pytest.mark.parametrize("nranks", [1, 2, 4])
+def test_restart_fixup_bitwise(dev, nranks):
+    """evp_gpu_restart_fixup == restartfile's treatment of freshly read stresses (ice_restart_driver.F90:370-394:
+    12 x ice_HaloUpdate_stress on a tripole grid; :431-466: south ghost row, west ghost column zeroed), every cell
+    of every stress incl. the outer ghost ring, 1 / 2 / 4 ranks; a closed basin too (no halo part)."""
+    for grid in (fx.synthetic_tripole(96, 40, wet_poles=True), fx.synthetic_closed(40, 24, name="closed40")):
+        case = fx.make_case(grid, "full", ndte=2, dt=3600.0)
+        _rand_stresses(case)
+        ref, got = clone_case(case), clone_case(case)
+        orc.restart_fixup(case.dom, ref.io)
+        g = dev.EvpGroup(case.dom, case.ndte, case.dt, nranks, strict=True)
+        try:
+            g.set_grid(grid.f)
+            g.upload(got.inp, got.io)
+            g.restart_fixup()
+            g.download(got.io, got.out)
+        finally:
+            g.close()
+        for n in fx.STRESS_FIELDS:
+            assert np.array_equal(got.io[n], ref.io[n]), (grid.dom.name, n)
+            assert not got.io[n][0, :].any() and not got.io[n][:, 0].any()
+        if grid.dom.ns_tripole:
+            assert got.io["stressp_1"][-1, 1:-1].any()
+
+
+def test_resident_protocol_of_evp_gpu_run(dev):
+    """evp_gpu_set_resident: the state goes up once, later calls upload only the inputs and bring back only the
+    groups of the mask -- the host arrays of the other groups must stay untouched, the downloaded ones must
+    equal a full-copy run bit for bit over three calls, and evp_gpu_download afterwards returns everything."""
+    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
+    case = fx.make_case(grid, "full", ndte=5, dt=3600.0)
+    ref = clone_case(case)
+    got = clone_case(case)
+    mask = dev.DL_VELOCITY | dev.DL_DEFORM | dev.DL_OCN_T
+    minimal = ("uvel", "vvel", "divu", "shear", "rdg_conv", "rdg_shear", "strocnxT", "strocnyT")
+    e = dev.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True)
+    try:
+        e.set_grid(grid.f)
+        e.set_resident(True, mask)
+        for call in range(3):
+            orc.run_case(ref)
+            got.out = {k: np.full_like(v, -777) for k, v in got.out.items()}
+            stale = {k: v.copy() for k, v in got.io.items()}
+            if call > 0:                       # resident: whatever the host holds in its state arrays is ignored
+                for n in fx.STRESS_FIELDS:
+                    got.io[n][...] = 123.0
+                stale = {k: v.copy() for k, v in got.io.items()}
+            e.evp(case.dt, got.inp, got.io, got.out)
+            for n in minimal:
+                a = got.io[n] if n in got.io else got.out[n]
+                b = ref.io[n] if n in ref.io else ref.out[n]
+                assert np.array_equal(phys(a), phys(b)), (call, n)
+            for n in fx.STRESS_FIELDS:          # not in the mask: host copy untouched
+                assert np.array_equal(got.io[n], stale[n]), n
+            assert (got.out["strairx"] == -777).all() and (got.out["prs_sig"] == -777).all()
+        e.download(got.io, got.out)              # history / restart step: everything
+        compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
+        # a restart was read on the host: invalidate, the next call uploads the state again
+        e.invalidate_state()
+        for k in ref.io:
+            got.io[k][...] = case.io[k]
+            ref.io[k][...] = case.io[k]
+        orc.run_case(ref)
+        e.evp(case.dt, got.inp, got.io, got.out)
+        assert np.array_equal(phys(got.io["uvel"]), phys(ref.io["uvel"]))
+    finally:
+        e.close()

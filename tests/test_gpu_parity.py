@@ -34,7 +34,7 @@ def test_one_call_bitwise_strict(grid, scenario):
     ref = _oracle(case)
     got = clone_case(case)
     st = evp.run_case(got, strict=True)
-    assert st.active_t_cells > 0 and st.loop_kernel_launches >= 120
+    assert st.active_t_cells > 0 and st.loop_kernel_launches >= 1
     compare_cases(got, ref, fields_out=OUT_CHECK, bitwise=True)
     assert np.array_equal(phys(got.io["iceumask"]), phys(ref.io["iceumask"]))
 
