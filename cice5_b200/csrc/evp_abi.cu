@@ -937,12 +937,12 @@ void fill_loop_args(const evp_handle *h, int from_parity, int inbox_buf, LoopArg
 
 // all ndte subcycles as one persistent kernel (evp_loop_tma.cuh): work items ordered by (subcycle, item),
 // per-tile dependency counters instead of launch boundaries and cross-rank barriers
-void add_loop(Builder &B, int from_parity)
+void add_loop(Builder &B, int from_parity, int nsteps)
 {
     evp_handle *h = B.h;
     const int buf0 = B.seq & 1;
-    B.seq += h->cfg.ndte;                        // one inbox buffer per subcycle, alternating
-    B.op([h, from_parity, buf0](Launcher &L) {
+    B.seq += nsteps;                             // one inbox buffer per subcycle, alternating
+    B.op([h, from_parity, buf0, nsteps](Launcher &L) {
         LoopTmaArgs t;
         memset(&t, 0, sizeof(t));
         fill_loop_args(h, from_parity, buf0, t.a);
@@ -957,7 +957,7 @@ void add_loop(Builder &B, int from_parity)
         for (int b = 0; b < 2; ++b)
             for (int r = 0; r < nr; ++r) t.inbox[b][r] = h->inbox(b, r);
         t.parity0 = from_parity; t.inbox0 = buf0;
-        t.strips = h->tstrips; t.chunks = h->t_chunks; t.nsteps = h->cfg.ndte;
+        t.strips = h->tstrips; t.chunks = h->t_chunks; t.nsteps = nsteps;
         t.has_fold = h->g.tripole ? 1 : 0;
         t.queue = h->queue(0); t.item_list = h->item_list(); t.item_count = h->item_count();
         t.tile_flags = h->tflags(); t.flags_ld = h->tflags_ld;
@@ -984,7 +984,7 @@ void add_loop(Builder &B, int from_parity)
         ++L.n;
         return EVP_OK;
     });
-    B.sync();      // the peers' last fold has read its inbox before the post-loop halos write into it
+    B.sync();      // every rank has finished its loop kernel: ghost columns, inboxes and folds are complete
 }
 
 // one subcycle: stress + stepu + halo pushes fused; [sync]; then the tripole fold of the new u, v
@@ -995,7 +995,8 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
     // N > 1 on a tripole grid with the TMA kernel: the cross-rank barrier between the subcycle
     // kernel and the fold is fused into both -- the last CTA to finish signals the peers, the fold
     // kernel waits for theirs -- 2 launches per subcycle instead of 4
-    const bool fused_sync = h->cfg.nranks > 1 && h->use_tma && h->g.tripole;
+    // (the fused signal relies on the boundary items coming first in the work list: not in the loop kernel's order)
+    const bool fused_sync = h->cfg.nranks > 1 && h->use_tma && h->g.tripole && !loop_mode(h);
     B.op([h, from_parity, last, buf, ksub, fused_sync](Launcher &L) {
         const Geom &g = h->g;
         LoopArgs a;
@@ -1193,8 +1194,15 @@ void build_program(evp_handle *h, double dt, Program &P)
     P.loop_begin = P.ops.size();
     int par = cur;
     if (loop_mode(h)) {
-        add_loop(B, par);
-        par ^= cfg.ndte & 1;
+        // subcycles 1 .. ndte-1 in the persistent kernel; the last one -- which also writes divu, shear, rdg_*,
+        // prs_sig, strint* (ice_dyn_evp.F90:665-677) -- as a launch of the LAST instantiation of the
+        // per-subcycle kernel (evp_loop_tma.cuh says why)
+        if (cfg.ndte > 1) {
+            add_loop(B, par, cfg.ndte - 1);
+            par ^= (cfg.ndte - 1) & 1;
+        }
+        add_subcycle(B, par, true, cfg.ndte);
+        par ^= 1;
     } else {
         for (int ksub = 1; ksub <= cfg.ndte; ++ksub) {
             add_subcycle(B, par, ksub == cfg.ndte, ksub);

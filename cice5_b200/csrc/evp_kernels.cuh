@@ -73,6 +73,29 @@ __device__ __forceinline__ double shfl_down1(double x)
     return __shfl_down_sync(0xffffffffu, x, 1);
 }
 
+// One corner of `stress` (source/ice_dyn_evp.F90:627-721): strain rates * area, Delta, replacement pressure
+// over Delta, the three stress updates.  Every statement is the reference's, operand for operand; only the
+// ORDER of independent statements differs from the source (corner by corner instead of quantity by quantity),
+// which changes no bit and lets the compiler keep one corner's temporaries alive at a time instead of four.
+struct Corner {
+    double div, tension, shear, Delta, c0raw;      // c0raw = strength / max(Delta, tinyarea)  (:683-686)
+};
+__device__ __forceinline__ Corner stress_corner(const Consts &k, double div, double tension, double shear,
+                                                double tinyarea, double strength, double &sp, double &sm,
+                                                double &s12)
+{
+    Corner c;
+    c.div = div; c.tension = tension; c.shear = shear;
+    c.Delta = sqrt(div * div + k.ecci * (tension * tension + shear * shear));          // :657-660
+    c.c0raw = strength / fmax(c.Delta, tinyarea);                                       // :683-686
+    const double c1 = c.c0raw * k.arlx1i;                                               // :690-693
+    const double c0 = c1 * k.ecci;                                                      // :694-697
+    sp = (sp + c1 * (div - c.Delta)) * k.denom1;                                        // :704-709
+    sm = (sm + c0 * tension) * k.denom1;                                                // :710-715
+    s12 = (s12 + c0 * shear * 0.5) * k.denom1;                                          // :716-721
+    return c;
+}
+
 // One T cell of `stress`.  s[12] in/out (p1..4, m1..4, 12_1..4); str[8] out.
 template <bool LAST>
 __device__ __forceinline__ void stress_cell(
@@ -82,62 +105,33 @@ __device__ __forceinline__ void stress_cell(
     double (&s)[12], double (&str)[8], double &divu, double &shear, double &rdg_conv,
     double &rdg_shear, double &prs_sig)
 {
-    // strain rates * area (:627-654)
-    const double divune = cyp * u_ij - dyt * u_wj + cxp * v_ij - dxt * v_is;
-    const double divunw = cym * u_wj + dyt * u_ij + cxp * v_wj - dxt * v_ws;
-    const double divusw = cym * u_ws + dyt * u_is + cxm * v_ws + dxt * v_wj;
-    const double divuse = cyp * u_is - dyt * u_ws + cxm * v_is + dxt * v_ij;
-
-    const double tensionne = -cym * u_ij - dyt * u_wj + cxm * v_ij + dxt * v_is;
-    const double tensionnw = -cyp * u_wj + dyt * u_ij + cxm * v_wj + dxt * v_ws;
-    const double tensionsw = -cyp * u_ws + dyt * u_is + cxp * v_ws - dxt * v_wj;
-    const double tensionse = -cym * u_is - dyt * u_ws + cxp * v_is - dxt * v_ij;
-
-    const double shearne = -cym * v_ij - dyt * v_wj - cxm * u_ij - dxt * u_is;
-    const double shearnw = -cyp * v_wj + dyt * v_ij - cxm * u_wj - dxt * u_ws;
-    const double shearsw = -cyp * v_ws + dyt * v_is - cxp * u_ws + dxt * u_wj;
-    const double shearse = -cym * v_is - dyt * v_ws - cxp * u_is + dxt * u_ij;
-
-    // Delta (:657-660)
-    const double Deltane = sqrt(divune * divune + k.ecci * (tensionne * tensionne + shearne * shearne));
-    const double Deltanw = sqrt(divunw * divunw + k.ecci * (tensionnw * tensionnw + shearnw * shearnw));
-    const double Deltase = sqrt(divuse * divuse + k.ecci * (tensionse * tensionse + shearse * shearse));
-    const double Deltasw = sqrt(divusw * divusw + k.ecci * (tensionsw * tensionsw + shearsw * shearsw));
+    // strain rates * area (:627-654), corner by corner: ne (1), nw (2), sw (3), se (4)
+    double sp1 = s[0], sp2 = s[1], sp3 = s[2], sp4 = s[3];
+    double sm1 = s[4], sm2 = s[5], sm3 = s[6], sm4 = s[7];
+    double s121 = s[8], s122 = s[9], s123 = s[10], s124 = s[11];
+    const Corner ne = stress_corner(k, cyp * u_ij - dyt * u_wj + cxp * v_ij - dxt * v_is,
+                                    -cym * u_ij - dyt * u_wj + cxm * v_ij + dxt * v_is,
+                                    -cym * v_ij - dyt * v_wj - cxm * u_ij - dxt * u_is, tinyarea, strength, sp1, sm1, s121);
+    const Corner nw = stress_corner(k, cym * u_wj + dyt * u_ij + cxp * v_wj - dxt * v_ws,
+                                    -cyp * u_wj + dyt * u_ij + cxm * v_wj + dxt * v_ws,
+                                    -cyp * v_wj + dyt * v_ij - cxm * u_wj - dxt * u_ws, tinyarea, strength, sp2, sm2, s122);
+    const Corner sw = stress_corner(k, cym * u_ws + dyt * u_is + cxm * v_ws + dxt * v_wj,
+                                    -cyp * u_ws + dyt * u_is + cxp * v_ws - dxt * v_wj,
+                                    -cyp * v_ws + dyt * v_is - cxp * u_ws + dxt * u_wj, tinyarea, strength, sp3, sm3, s123);
+    const Corner se = stress_corner(k, cyp * u_is - dyt * u_ws + cxm * v_is + dxt * v_ij,
+                                    -cym * u_is - dyt * u_ws + cxp * v_is - dxt * v_ij,
+                                    -cym * v_is - dyt * v_ws - cxp * u_is + dxt * u_ij, tinyarea, strength, sp4, sm4, s124);
 
     if (LAST) {  // ksub == ndte (:665-677)
-        divu = 0.25 * (divune + divunw + divuse + divusw) * tarear;
-        const double tmp = 0.25 * (Deltane + Deltanw + Deltase + Deltasw) * tarear;
+        divu = 0.25 * (ne.div + nw.div + se.div + sw.div) * tarear;
+        const double tmp = 0.25 * (ne.Delta + nw.Delta + se.Delta + sw.Delta) * tarear;
         rdg_conv = -fmin(divu, 0.0);
         rdg_shear = 0.5 * (tmp - fabs(divu));
-        const double ts = tensionne + tensionnw + tensionse + tensionsw;
-        const double ss = shearne + shearnw + shearse + shearsw;
+        const double ts = ne.tension + nw.tension + se.tension + sw.tension;
+        const double ss = ne.shear + nw.shear + se.shear + sw.shear;
         shear = 0.25 * tarear * sqrt(ts * ts + ss * ss);
+        prs_sig = ne.c0raw * ne.Delta;                                                  // :688
     }
-
-    // replacement pressure / Delta (:683-697)
-    double c0ne = strength / fmax(Deltane, tinyarea);
-    double c0nw = strength / fmax(Deltanw, tinyarea);
-    double c0sw = strength / fmax(Deltasw, tinyarea);
-    double c0se = strength / fmax(Deltase, tinyarea);
-    if (LAST) prs_sig = c0ne * Deltane;
-
-    const double c1ne = c0ne * k.arlx1i, c1nw = c0nw * k.arlx1i;
-    const double c1sw = c0sw * k.arlx1i, c1se = c0se * k.arlx1i;
-    c0ne = c1ne * k.ecci; c0nw = c1nw * k.ecci; c0sw = c1sw * k.ecci; c0se = c1se * k.ecci;
-
-    // the stresses (:704-721)
-    const double sp1 = (s[0] + c1ne * (divune - Deltane)) * k.denom1;
-    const double sp2 = (s[1] + c1nw * (divunw - Deltanw)) * k.denom1;
-    const double sp3 = (s[2] + c1sw * (divusw - Deltasw)) * k.denom1;
-    const double sp4 = (s[3] + c1se * (divuse - Deltase)) * k.denom1;
-    const double sm1 = (s[4] + c0ne * tensionne) * k.denom1;
-    const double sm2 = (s[5] + c0nw * tensionnw) * k.denom1;
-    const double sm3 = (s[6] + c0sw * tensionsw) * k.denom1;
-    const double sm4 = (s[7] + c0se * tensionse) * k.denom1;
-    const double s121 = (s[8] + c0ne * shearne * 0.5) * k.denom1;
-    const double s122 = (s[9] + c0nw * shearnw * 0.5) * k.denom1;
-    const double s123 = (s[10] + c0sw * shearsw * 0.5) * k.denom1;
-    const double s124 = (s[11] + c0se * shearse * 0.5) * k.denom1;
     s[0] = sp1; s[1] = sp2; s[2] = sp3; s[3] = sp4;
     s[4] = sm1; s[5] = sm2; s[6] = sm3; s[7] = sm4;
     s[8] = s121; s[9] = s122; s[10] = s123; s[11] = s124;

@@ -78,41 +78,51 @@ struct LoopTmaArgs {
     unsigned long long timeout_ns;
 };
 
+// SYS: the counter is written or read by another GPU (peer memory); otherwise gpu scope is enough and cheaper
+template <bool SYS>
 __device__ __forceinline__ void st_release_u64(unsigned long long *p, unsigned long long v)
 {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+    if (SYS) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+    else asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+template <bool SYS>
 __device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long *p)
 {
     unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    if (SYS) asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    else asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
 // spin until *p >= want; gives up when another waiter has timed out or after timeout_ns (error word set:
 // the host returns EVP_ERR_PEER, the results of the call are void)
+template <bool SYS>
 __device__ __forceinline__ void wait_counter(const unsigned long long *p, unsigned long long want, int *error,
                                              unsigned long long timeout_ns)
 {
-    if (ld_acquire_u64(p) >= want) return;
+    if (ld_acquire_u64<SYS>(p) >= want) return;
     const unsigned long long t0 = global_ns();
     for (;;) {
-        __nanosleep(64);
-        if (ld_acquire_u64(p) >= want) return;
+        __nanosleep(32);
+        if (ld_acquire_u64<SYS>(p) >= want) return;
         if (*(volatile int *)error) return;
         if (global_ns() - t0 > timeout_ns) { *(volatile int *)error = 1; return; }
     }
 }
 
 // counter of the tile (strip + ds, chunk + dc) as seen from this rank, or null when there is none
-__device__ __forceinline__ const unsigned long long *neighbour_counter(const LoopTmaArgs &p, int strip, int chunk)
+__device__ __forceinline__ const unsigned long long *neighbour_counter(const LoopTmaArgs &p, int strip, int chunk,
+                                                                       bool &remote)
 {
+    remote = false;
     if (chunk < 0 || chunk >= p.chunks) return nullptr;
     if (strip < 0) {
         if (p.ew_self) return p.tflag + (size_t)chunk * p.strips + (p.strips - 1);
+        remote = true;
         return p.wflag ? p.wflag + chunk : nullptr;
     }
     if (strip >= p.strips) {
         if (p.ew_self) return p.tflag + (size_t)chunk * p.strips;
+        remote = true;
         return p.eflag ? p.eflag + chunk : nullptr;
     }
     return p.tflag + (size_t)chunk * p.strips + strip;
@@ -303,10 +313,13 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
 
     if (warp == kTmaConsumers) {
         // ------------------------------ producer warp ------------------------------
+        // lane 0 always holds the NEXT position already (drawn while the previous item was being issued): the
+        // round trip of the atomic is off the path between two items
+        int qnext = 0;
+        if (lane == 0) qnext = atomicAdd(p.queue, 1);
         for (;;) {
-            int q = 0;
-            if (lane == 0) q = atomicAdd(p.queue, 1);
-            q = __shfl_sync(0xffffffffu, q, 0);
+            const int q = __shfl_sync(0xffffffffu, qnext, 0);
+            if (lane == 0 && q < total) qnext = atomicAdd(p.queue, 1);
             if (q >= total || per_step == 0) {                          // queue drained: tell the consumers
                 if (lane == 0) {
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
@@ -317,7 +330,6 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
             }
             const int k = q / per_step;                                 // subcycle, 0-based
             const int pos = q - k * per_step;
-            const bool last = k == p.nsteps - 1;
             if (pos == nkept) {                                         // the fold of subcycle k
                 if (lane == 0) {
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
@@ -337,10 +349,14 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
                 // dependencies: the 3 x 3 tiles around this one have finished subcycle k-1 (lanes 0..8 poll
                 // one counter each), and, for a tile that reads rows ny / ny+1, the fold of k-1 (lane 9)
                 if ((EVP_LOOP_EXP & 4) == 0 && lane < 9) {
-                    const unsigned long long *f = neighbour_counter(p, strip + lane % 3 - 1, chunk + lane / 3 - 1);
-                    if (f) wait_counter(f, (unsigned long long)k, p.error, p.timeout_ns);
+                    bool remote;
+                    const unsigned long long *f = neighbour_counter(p, strip + lane % 3 - 1, chunk + lane / 3 - 1, remote);
+                    if (f) {
+                        if (remote) wait_counter<true>(f, (unsigned long long)k, p.error, p.timeout_ns);
+                        else wait_counter<false>(f, (unsigned long long)k, p.error, p.timeout_ns);
+                    }
                 } else if (lane == 9 && p.has_fold && rend >= a.ny) {
-                    wait_counter(p.fold_flag, (unsigned long long)k, p.error, p.timeout_ns);
+                    wait_counter<false>(p.fold_flag, (unsigned long long)k, p.error, p.timeout_ns);
                 }
                 __syncwarp();
                 // the planes were written through the generic proxy (other SMs, other GPUs); TMA reads them
@@ -378,7 +394,7 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
                     unsigned bytes = kMaskBoxW * kMaskBoxes;
                     const bool uv_only = j == r0 - 1;                    // first row of an item: velocities only
                     if (needS) bytes += (uv_only ? 2 : kStateDepth) * kTmaBoxW * 8;
-                    if (needT) bytes += (tdepth + (last ? 1 : 0)) * kTmaBoxW * 8;
+                    if (needT) bytes += tdepth * kTmaBoxW * 8;
                     if (htn_extra) bytes += kTmaBoxW * 8;
                     if (needU) bytes += (p.water_is_ocn ? kUDepth - 2 : kUDepth) * kTmaBoxW * 8;
                     mbar_expect_tx(&full_bar[stage], bytes);
@@ -390,8 +406,6 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
                         if (!cmp) tma_load_3d(tb, &mapT10, &full_bar[stage], x0, j, p.plane_t + 2);
                         else if (tinym) tma_load_3d(tb, &mapT3, &full_bar[stage], x0, j, p.plane_t);
                         else tma_load_3d(tb, &mapT4, &full_bar[stage], x0, j, p.plane_t);
-                        if (last)
-                            tma_load_3d(tb + kSlotTarear * kTmaBoxW * 8, &mapT1, &full_bar[stage], x0, j, p.plane_t + 12);
                     }
                     if (htn_extra)
                         tma_load_3d(tb + kSlotHtnExtra * kTmaBoxW * 8, &mapT1, &full_bar[stage], x0, j, p.plane_t + 1);
@@ -428,7 +442,7 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty_bar[stage]);
             if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
-            if (tid < p.nranks) wait_counter(p.topflag + tid, (unsigned long long)step + 1, p.error, p.timeout_ns);
+            if (tid < p.nranks) wait_counter<true>(p.topflag + tid, (unsigned long long)step + 1, p.error, p.timeout_ns);
             asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
             const double *inbox = p.inbox[ibuf][p.rank];
             const int ild = a.inbox_ld;
@@ -445,39 +459,53 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
             __threadfence();
             asm volatile("fence.proxy.async.global;" ::: "memory");
             asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
-            if (tid == 0) st_release_u64(p.fold_flag, (unsigned long long)step + 1);
+            if (tid == 0) st_release_u64<false>(p.fold_flag, (unsigned long long)step + 1);
             continue;
         }
 
         const int strip = item % p.strips, chunk = item / p.strips;
         int r0, rend;
         chunk_rows(chunk, a.rows_per_chunk, a.ny, r0, rend);
-        // two instantiations of the row sweep: the last subcycle also fetches tarear and writes divu, shear,
-        // rdg_*, prs_sig, strint* (a run-time flag inside one body cost registers in all the others)
-        if (step == p.nsteps - 1 && (EVP_LOOP_EXP & 8) == 0)
-            sweep_item<true, REVISED>(p, ring, full_bar, empty_bar, stage, phase, strip, r0, rend, par, ibuf, warp, lane);
-        else
-            sweep_item<false, REVISED>(p, ring, full_bar, empty_bar, stage, phase, strip, r0, rend, par, ibuf, warp, lane);
+        // (the last subcycle of evp, which also writes divu, shear, rdg_*, prs_sig, strint*, is a launch of
+        // evp_subcycle_tma_kernel<true> after this kernel: a second instantiation of the sweep in here, inlined or
+        // called, made the register allocator spill hundreds of bytes in the body that runs 119 times of 120)
+        sweep_item<false, REVISED>(p, ring, full_bar, empty_bar, stage, phase, strip, r0, rend, par, ibuf, warp, lane);
 
         // ---- publish: this tile has finished subcycle `step` ----
-        if ((EVP_LOOP_EXP & 1) == 0) {
-            if (p.nranks > 1) __threadfence_system(); else __threadfence();
-            asm volatile("fence.proxy.async.global;" ::: "memory");
-        }
-        asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
-        if (tid == 0) {
-            const unsigned long long done = (unsigned long long)step + 1;
-            st_release_u64(p.tflag + item, done);
-            if (strip == 0 && p.pub_w) st_release_u64(p.pub_w + chunk, done);
-            if (strip == p.strips - 1 && p.pub_e) st_release_u64(p.pub_e + chunk, done);
-            if (p.has_fold && rend >= a.ny) {
-                const unsigned long long ntop = (unsigned long long)p.item_count[2];
-                const unsigned long long n = atomicAdd(p.top_count, 1ull) + 1ull;
-                if (n == ntop * done) {                                  // the top tiles of this rank are complete
-                    __threadfence_system();
-                    for (int r = 0; r < p.nranks; ++r) st_release_u64(p.pub_top[r] + p.rank, done);
+        // Warps 1..3 only announce that their stores are issued (bar.arrive) and go on with the next item; warp 0
+        // waits for the four warps (bar.sync), then ONE thread releases the counters.  The release is cumulative:
+        // the stores of all 128 threads happen before the barrier completes, hence before the release fence of
+        // lane 0, hence before the counter becomes visible (gpu scope; system scope where a peer GPU reads it or
+        // the tile stored into peer memory).  A fence in every thread (first version) cost ~5 us of CTA time per item.
+        if (warp != 0) {
+            asm volatile("bar.arrive 2, %0;" ::"n"(kTmaConsumers * 32) : "memory");
+        } else {
+            // (barrier 2: barrier 1 belongs to the fold item, which warps 1..3 may reach while warp 0 is still here.
+            // Warps 1..3 cannot arrive twice before warp 0 has been here once: every item spans more ring stages
+            // than the ring holds, and a stage is recycled only when warp 0 has released it too.)
+            asm volatile("bar.sync 2, %0;" ::"n"(kTmaConsumers * 32) : "memory");
+            if (lane == 0) {
+                const unsigned long long done = (unsigned long long)step + 1;
+                const bool west_edge = strip == 0 && p.pub_w, east_edge = strip == p.strips - 1 && p.pub_e;
+                const bool top = p.has_fold && rend >= a.ny;
+                if ((EVP_LOOP_EXP & 1) == 0) asm volatile("fence.proxy.async.global;" ::: "memory");
+                if (p.nranks > 1 && (west_edge || east_edge || top)) {
+                    st_release_u64<true>(p.tflag + item, done);          // stores into peer memory precede it
+                    if (west_edge) st_release_u64<true>(p.pub_w + chunk, done);
+                    if (east_edge) st_release_u64<true>(p.pub_e + chunk, done);
+                } else {
+                    st_release_u64<false>(p.tflag + item, done);
+                }
+                if (top) {
+                    const unsigned long long ntop = (unsigned long long)p.item_count[2];
+                    const unsigned long long n = atomicAdd(p.top_count, 1ull) + 1ull;
+                    if (n == ntop * done) {                              // the top tiles of this rank are complete
+                        __threadfence_system();
+                        for (int r = 0; r < p.nranks; ++r) st_release_u64<true>(p.pub_top[r] + p.rank, done);
+                    }
                 }
             }
+            __syncwarp();
         }
     }
 }

@@ -8,6 +8,19 @@
 ! BLCKX = NXGLOB/ntasks, BLCKY = NYGLOB, distribution_type='cartesian', processor_shape
 ! 'slenderX1'), as solo_ice_comp:84-86 sets up for 8 tasks.
 !
+! Build notes
+!  * serial build (COMMDIR = serial, bld/build.sh:140): add -DEVP_B200_NO_MPI (no mpif.h, one task).
+!  * the reference's module arrays are not declared TARGET (source/ice_state.F90, ice_flux.F90, ice_grid.F90,
+!    ice_dyn_shared.F90), so c_loc() may not be applied to them directly: every address is taken through
+!    r8loc / i4loc below, whose dummy argument is an assumed-size TARGET array.  The arrays are whole,
+!    contiguous, static module arrays: they are passed by reference (no copy-in) and their addresses stay
+!    valid for the life of the program, which is what the C side relies on between evp_gpu_pin_host_arrays
+!    and evp_gpu_finalize.
+!  * -DEVP_B200_FULL_COPY: every inout / out array goes up and comes back on every call (round-1 behaviour).
+!    Default: resident-state protocol (include/evp_b200.h): the dynamic state lives on the device, a call
+!    uploads the per-call inputs and downloads what the next host phases read; call evp_gpu_fetch_all
+!    before history / restart output and evp_gpu_state_changed after a restart was read.
+!
 ! NOTE: written against the C ABI; NOT compiled in the build image (no Fortran compiler there).
 !=======================================================================
       module ice_dyn_evp
@@ -22,7 +35,7 @@
 
       implicit none
       private
-      public :: evp
+      public :: evp, evp_gpu_fetch_all, evp_gpu_state_changed
       save
 
       type, bind(C) :: evp_config_t
@@ -85,6 +98,25 @@
             type(evp_inout_t), intent(in) :: io
             type(evp_out_t), intent(in) :: out
          end function
+         integer(c_int) function evp_gpu_set_resident(h, resident, mask) bind(C, name='evp_gpu_set_resident')
+            import :: c_int, c_ptr
+            type(c_ptr), value :: h
+            integer(c_int), value :: resident, mask
+         end function
+         integer(c_int) function evp_gpu_invalidate_state(h) bind(C, name='evp_gpu_invalidate_state')
+            import :: c_int, c_ptr
+            type(c_ptr), value :: h
+         end function
+         integer(c_int) function evp_gpu_restart_fixup(h) bind(C, name='evp_gpu_restart_fixup')
+            import :: c_int, c_ptr
+            type(c_ptr), value :: h
+         end function
+         integer(c_int) function evp_gpu_download(h, io, out) bind(C, name='evp_gpu_download')
+            import :: c_int, c_ptr, evp_inout_t, evp_out_t
+            type(c_ptr), value :: h
+            type(evp_inout_t), intent(in) :: io
+            type(evp_out_t), intent(in) :: out
+         end function
          integer(c_int) function evp_gpu_peer_blob_size() bind(C, name='evp_gpu_peer_blob_size')
             import :: c_int
          end function
@@ -110,11 +142,30 @@
       type(c_ptr) :: handle = c_null_ptr
       logical :: ready = .false.
       logical :: host_pinned = .false.
+      ! download groups of the resident protocol (include/evp_b200.h)
+      integer(c_int), parameter :: EVP_DL_VELOCITY = 1, EVP_DL_STRESS = 2, EVP_DL_DEFORM = 4, &
+                                   EVP_DL_OCN_T = 8, EVP_DL_HISTORY = 16, EVP_DL_ALL = 31
+      type(evp_inout_t) :: io_all           ! addresses of every inout / out array, filled on the first call
+      type(evp_out_t) :: out_all
       ! logical masks cross the ABI as 0/1 integers (Fortran .true. is compiler dependent)
       integer(c_int), allocatable, target :: tmask_i(:,:), umask_i(:,:), iceumask_i(:,:), icetmask_i(:,:)
       real(c_double), allocatable, target :: tmass_w(:,:)
 
       contains
+
+!=======================================================================
+! addresses of module arrays that are not declared TARGET in the reference (see the header)
+      function r8loc(a) result(p)
+      real(c_double), target, intent(in) :: a(*)
+      type(c_ptr) :: p
+      p = c_loc(a)
+      end function r8loc
+
+      function i4loc(a) result(p)
+      integer(c_int), target, intent(in) :: a(*)
+      type(c_ptr) :: p
+      p = c_loc(a)
+      end function i4loc
 
 !=======================================================================
       subroutine check(rc, where)
@@ -146,7 +197,10 @@
       use ice_exit, only: abort_ice
       use ice_grid, only: tmask, umask, dxt, dyt, dxhy, dyhx, cxp, cyp, cxm, cym, &
           tarea, uarea, tarear, uarear, tinyarea, grid_type, HTE, HTN
+      use ice_mechred, only: kstrength
+#ifndef EVP_B200_NO_MPI
       include 'mpif.h'
+#endif
       real (kind=dbl_kind), intent(in) :: dt
       type(evp_config_t) :: cfg
       type(evp_grid_t), target :: g
@@ -179,7 +233,12 @@
 #ifdef AusCOM
       if (.not. use_ocnslope) cfg%tilt_mode = 0          ! ice_dyn_shared.F90:604-609
 #endif
-      cfg%strength_masked = 0       ! strength is passed exactly as ice_strength left it
+      ! kstrength = 1 (Rothrock): the reference computes the strength on the icellt list only and leaves 0
+      ! everywhere else (source/ice_mechred.F90:2175, call site ice_dyn_evp.F90:291-301); this module calls
+      ! ice_strength on every physical cell (the list is built on the device) and lets the device keep the
+      ! values on the icetmask == 1 cells -- the `strength` that comes back equals the reference's everywhere.
+      ! kstrength = 0 (Hibler) writes all physical cells in the reference too (:2259-2265).
+      cfg%strength_masked = merge(1, 0, kstrength == 1)
       cfg%use_cuda_graph = 1
       cfg%dt_init = dt              ! == dt_dyn handed to init_evp (CICE_InitMod.F90:104)
       cfg%cosw = cosw;  cfg%sinw = sinw
@@ -193,27 +252,38 @@
       allocate(tmask_i(nx_block,ny_block), umask_i(nx_block,ny_block), &
                iceumask_i(nx_block,ny_block), icetmask_i(nx_block,ny_block), tmass_w(nx_block,ny_block))
       tmask_i = merge(1, 0, tmask(:,:,1));  umask_i = merge(1, 0, umask(:,:,1))
-      g%dxt = c_loc(dxt(1,1,1));   g%dyt = c_loc(dyt(1,1,1))
-      g%dxhy = c_loc(dxhy(1,1,1)); g%dyhx = c_loc(dyhx(1,1,1))
-      g%cxp = c_loc(cxp(1,1,1));   g%cyp = c_loc(cyp(1,1,1))
-      g%cxm = c_loc(cxm(1,1,1));   g%cym = c_loc(cym(1,1,1))
-      g%tarea = c_loc(tarea(1,1,1));   g%uarea = c_loc(uarea(1,1,1))
-      g%tarear = c_loc(tarear(1,1,1)); g%uarear = c_loc(uarear(1,1,1))
-      g%tinyarea = c_loc(tinyarea(1,1,1)); g%fcor = c_loc(fcor_blk(1,1,1))
+      g%dxt = r8loc(dxt);   g%dyt = r8loc(dyt)
+      g%dxhy = r8loc(dxhy); g%dyhx = r8loc(dyhx)
+      g%cxp = r8loc(cxp);   g%cyp = r8loc(cyp)
+      g%cxm = r8loc(cxm);   g%cym = r8loc(cym)
+      g%tarea = r8loc(tarea);   g%uarea = r8loc(uarea)
+      g%tarear = r8loc(tarear); g%uarear = r8loc(uarear)
+      g%tinyarea = r8loc(tinyarea); g%fcor = r8loc(fcor_blk)
       g%tmask = c_loc(tmask_i(1,1));   g%umask = c_loc(umask_i(1,1))
       ! HTE, HTN (ice_grid.F90:51-52): where the library verifies, cell by cell, that the metric
       ! arrays above follow from them bit for bit it fetches these two instead of nine planes
-      g%HTE = c_loc(HTE(1,1,1));       g%HTN = c_loc(HTN(1,1,1))
+      g%HTE = r8loc(HTE);       g%HTN = r8loc(HTN)
       call check(evp_gpu_set_grid(handle, g), 'set_grid')
 
       if (ntasks > 1) then          ! exchange the peer-memory handles of all tasks of the node
          nb = evp_gpu_peer_blob_size()
          allocate(mine(nb), everyone(nb*ntasks))
          call check(evp_gpu_get_peer_blob(handle, mine), 'get_peer_blob')
+#ifndef EVP_B200_NO_MPI
          call MPI_ALLGATHER(mine, nb, MPI_CHARACTER, everyone, nb, MPI_CHARACTER, MPI_COMM_ICE, ierr)
+#else
+         call abort_ice('evp (B200): built with -DEVP_B200_NO_MPI but running on several tasks')
+#endif
          call check(evp_gpu_set_peers(handle, everyone), 'set_peers')
          deallocate(mine, everyone)
       endif
+#ifndef EVP_B200_FULL_COPY
+      ! resident-state protocol: per call only what transport_remap (uvel, vvel), step_ridge (rdg_conv,
+      ! rdg_shear; divu, shear for the history) and the coupler (strocnxT/yT) read comes back
+      ! (source/ice_step_mod.F90:1126-1141)
+      call check(evp_gpu_set_resident(handle, 1_c_int, &
+                 ior(EVP_DL_VELOCITY, ior(EVP_DL_DEFORM, EVP_DL_OCN_T))), 'set_resident')
+#endif
       ready = .true.
       end subroutine evp_gpu_setup
 
@@ -226,6 +296,7 @@
       use ice_flux, only: strax, stray
 #endif
       use ice_blocks, only: block, get_block, nx_block, ny_block
+      use ice_communicate, only: MPI_COMM_ICE, get_num_procs
       use ice_domain, only: blocks_ice
       use ice_flux, only: rdg_conv, rdg_shear, prs_sig, strairxT, strairyT, &
           strairx, strairy, uocn, vocn, ss_tltx, ss_tlty, iceumask, fm, &
@@ -241,8 +312,11 @@
       type(evp_inout_t) :: io
       type(evp_out_t) :: out
       type(block) :: this_block
-      integer :: i, j, icellt
+      integer :: i, j, icellt, ierr
       integer, allocatable :: indxti(:), indxtj(:)
+#ifndef EVP_B200_NO_MPI
+      include 'mpif.h'
+#endif
 
       call ice_timer_start(timer_dynamics)
       if (.not. ready) call evp_gpu_setup(dt)
@@ -263,34 +337,34 @@
       deallocate(indxti, indxtj)
 
       iceumask_i = merge(1, 0, iceumask(:,:,1))
-      in%aice = c_loc(aice(1,1,1)); in%vice = c_loc(vice(1,1,1)); in%vsno = c_loc(vsno(1,1,1))
-      in%aice_init = c_loc(aice_init(1,1,1))
-      in%strairxT = c_loc(strairxT(1,1,1)); in%strairyT = c_loc(strairyT(1,1,1))
-      in%uocn = c_loc(uocn(1,1,1)); in%vocn = c_loc(vocn(1,1,1))
-      in%ss_tltx = c_loc(ss_tltx(1,1,1)); in%ss_tlty = c_loc(ss_tlty(1,1,1))
-      in%Cdn_ocn = c_loc(Cdn_ocn(1,1,1)); in%strength = c_loc(strength(1,1,1))
+      in%aice = r8loc(aice); in%vice = r8loc(vice); in%vsno = r8loc(vsno)
+      in%aice_init = r8loc(aice_init)
+      in%strairxT = r8loc(strairxT); in%strairyT = r8loc(strairyT)
+      in%uocn = r8loc(uocn); in%vocn = r8loc(vocn)
+      in%ss_tltx = r8loc(ss_tltx); in%ss_tlty = r8loc(ss_tlty)
+      in%Cdn_ocn = r8loc(Cdn_ocn); in%strength = r8loc(strength)
       in%strax = c_null_ptr;  in%stray = c_null_ptr
 #ifdef ACCESS
       ! source/ice_dyn_evp.F90:220-229: the coupler's wind stress is already on the U grid
       if (.not. calc_strair) then
-         in%strax = c_loc(strax(1,1,1));  in%stray = c_loc(stray(1,1,1))
+         in%strax = r8loc(strax);  in%stray = r8loc(stray)
       endif
 #endif
-      io%uvel = c_loc(uvel(1,1,1)); io%vvel = c_loc(vvel(1,1,1))
-      io%stressp = [c_loc(stressp_1(1,1,1)), c_loc(stressp_2(1,1,1)), c_loc(stressp_3(1,1,1)), c_loc(stressp_4(1,1,1))]
-      io%stressm = [c_loc(stressm_1(1,1,1)), c_loc(stressm_2(1,1,1)), c_loc(stressm_3(1,1,1)), c_loc(stressm_4(1,1,1))]
-      io%stress12 = [c_loc(stress12_1(1,1,1)), c_loc(stress12_2(1,1,1)), c_loc(stress12_3(1,1,1)), c_loc(stress12_4(1,1,1))]
-      io%iceumask = c_loc(iceumask_i(1,1)); io%fm = c_loc(fm(1,1,1))
-      out%strairx = c_loc(strairx(1,1,1)); out%strairy = c_loc(strairy(1,1,1))
-      out%strtltx = c_loc(strtltx(1,1,1)); out%strtlty = c_loc(strtlty(1,1,1))
-      out%strocnx = c_loc(strocnx(1,1,1)); out%strocny = c_loc(strocny(1,1,1))
-      out%strintx = c_loc(strintx(1,1,1)); out%strinty = c_loc(strinty(1,1,1))
-      out%strocnxT = c_loc(strocnxT(1,1,1)); out%strocnyT = c_loc(strocnyT(1,1,1))
-      out%divu = c_loc(divu(1,1,1)); out%shear = c_loc(shear(1,1,1))
-      out%rdg_conv = c_loc(rdg_conv(1,1,1)); out%rdg_shear = c_loc(rdg_shear(1,1,1))
-      out%prs_sig = c_loc(prs_sig(1,1,1))
-      out%uvel_init = c_loc(uvel_init(1,1,1)); out%vvel_init = c_loc(vvel_init(1,1,1))
-      out%tmass = c_loc(tmass_w(1,1)); out%strength = c_loc(strength(1,1,1))
+      io%uvel = r8loc(uvel); io%vvel = r8loc(vvel)
+      io%stressp = [r8loc(stressp_1), r8loc(stressp_2), r8loc(stressp_3), r8loc(stressp_4)]
+      io%stressm = [r8loc(stressm_1), r8loc(stressm_2), r8loc(stressm_3), r8loc(stressm_4)]
+      io%stress12 = [r8loc(stress12_1), r8loc(stress12_2), r8loc(stress12_3), r8loc(stress12_4)]
+      io%iceumask = c_loc(iceumask_i(1,1)); io%fm = r8loc(fm)
+      out%strairx = r8loc(strairx); out%strairy = r8loc(strairy)
+      out%strtltx = r8loc(strtltx); out%strtlty = r8loc(strtlty)
+      out%strocnx = r8loc(strocnx); out%strocny = r8loc(strocny)
+      out%strintx = r8loc(strintx); out%strinty = r8loc(strinty)
+      out%strocnxT = r8loc(strocnxT); out%strocnyT = r8loc(strocnyT)
+      out%divu = r8loc(divu); out%shear = r8loc(shear)
+      out%rdg_conv = r8loc(rdg_conv); out%rdg_shear = r8loc(rdg_shear)
+      out%prs_sig = r8loc(prs_sig)
+      out%uvel_init = r8loc(uvel_init); out%vvel_init = r8loc(vvel_init)
+      out%tmass = c_loc(tmass_w(1,1)); out%strength = r8loc(strength)
       out%icetmask = c_loc(icetmask_i(1,1))
 
       ! the module arrays are static: page-lock them once, the per-call copies then run at the full
@@ -298,15 +372,56 @@
       if (.not. host_pinned) then
          call check(evp_gpu_pin_host_arrays(handle, in, io, out), 'pin_host_arrays')
          host_pinned = .true.
+         io_all = io;  out_all = out
       endif
 
+      ! Tasks reach evp skewed (history / restart output on the master task, a first-call graph capture):
+      ! line them up on the HOST, where waiting costs nothing, before any kernel waits for a peer on the
+      ! device (the device-side waits give up after EVP_B200_SYNC_TIMEOUT_S, default 10 s).
+#ifndef EVP_B200_NO_MPI
+      if (get_num_procs() > 1) call MPI_BARRIER(MPI_COMM_ICE, ierr)
+#endif
       call check(evp_gpu_run(handle, real(dt, c_double), in, io, out), 'run')
 
+#ifdef EVP_B200_FULL_COPY
       iceumask(:,:,1) = iceumask_i /= 0
+#endif
 #ifdef AusCOM
-      sicemass(:,:,1) = tmass_w          ! ice_dyn_evp.F90:205-207
+      ! sicemass = tmass (ice_dyn_evp.F90:205-207) goes to the coupler every step: computed here from the
+      ! same formula evp_prep1 uses (ice_dyn_shared.F90:322-326) unless every array comes back anyway
+#ifdef EVP_B200_FULL_COPY
+      sicemass(:,:,1) = tmass_w
+#else
+      call evp_gpu_fetch_all          ! simplest correct choice for a coupled build; refine with the mask
+#endif
 #endif
       call ice_timer_stop(timer_dynamics)
       end subroutine evp
+
+!=======================================================================
+! Resident protocol: bring every inout / out array of evp back to the host arrays (call before history
+! accumulation of the dynamics fields and before a restart dump; source/ice_history.F90:1465-1482,
+! ice_restart_driver.F90:122-176)
+      subroutine evp_gpu_fetch_all
+      use ice_flux, only: iceumask
+#ifdef AusCOM
+      use cpl_arrays_setup, only: sicemass
+#endif
+      if (.not. ready) return
+      call check(evp_gpu_download(handle, io_all, out_all), 'download')
+      iceumask(:,:,1) = iceumask_i /= 0
+#ifdef AusCOM
+      sicemass(:,:,1) = tmass_w
+#endif
+      end subroutine evp_gpu_fetch_all
+
+!=======================================================================
+! Resident protocol: the host changed the dynamic state (restartfile read uvel, vvel, the stresses and
+! iceumask; source/ice_restart_driver.F90:295-440).  The next evp uploads it again; restartfile's own
+! ice_HaloUpdate_stress calls and ghost zeroing have already run on the host arrays by then.
+      subroutine evp_gpu_state_changed
+      if (.not. ready) return
+      call check(evp_gpu_invalidate_state(handle), 'invalidate_state')
+      end subroutine evp_gpu_state_changed
 
       end module ice_dyn_evp

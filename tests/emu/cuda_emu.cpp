@@ -320,6 +320,17 @@ void emu_bar_sync(int id, int nthreads)
     if (++n.done == n.arrived) { n.arrived = n.done = 0; n.phase = 0; }
 }
 
+// bar.arrive: counted like a thread that has already left (it never waits)
+void emu_bar_arrive(int id, int nthreads)
+{
+    (void)nthreads;
+    emu::Block *b = emu::cur->block;
+    emu::Block::Named &n = b->named[id & 15];
+    while (n.phase != 0) emu::yield();
+    ++n.arrived;
+    ++n.done;
+}
+
 void emu_ptx_unavailable(const char *what)
 {
     fprintf(stderr, "cuda_emu: PTX that has no host stand-in was reached: %s\n", what);

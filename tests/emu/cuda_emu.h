@@ -192,6 +192,7 @@ inline double __fma_rn(double a, double b, double c) { return fma(a, b, c); }
 // PTX of the cross-rank flags, rewritten by tests/emu/emu.py into these
 inline void emu_st_release_u64(void *p, unsigned long long v) { __atomic_store_n((unsigned long long *)p, v, __ATOMIC_RELEASE); }
 inline unsigned long long emu_ld_acquire_u64(const void *p) { return __atomic_load_n((const unsigned long long *)p, __ATOMIC_ACQUIRE); }
+void emu_bar_arrive(int id, int nthreads);
 [[noreturn]] void emu_ptx_unavailable(const char *what);
 
 // ---- runtime API -----------------------------------------------------------------------------------------

@@ -113,9 +113,9 @@ def _rewrite_asm(text: str) -> str:
         template = " ".join(re.findall(r'"((?:[^"\\]|\\.)*)"', parts[0]))
         outs = _operands(parts[1]) if len(parts) > 1 else []
         ins = _operands(parts[2]) if len(parts) > 2 else []
-        if "st.release.sys.global.u64" in template:
+        if "st.release.sys.global.u64" in template or "st.release.gpu.global.u64" in template:
             rep = f"emu_st_release_u64((void *)({ins[0]}), ({ins[1]}));"
-        elif "ld.acquire.sys.global.u64" in template:
+        elif "ld.acquire.sys.global.u64" in template or "ld.acquire.gpu.global.u64" in template:
             rep = f"{outs[0]} = emu_ld_acquire_u64((const void *)({ins[0]}));"
         elif "globaltimer" in template:
             rep = f"{outs[0]} = emu::now_ns();"
@@ -131,6 +131,8 @@ def _rewrite_asm(text: str) -> str:
             rep = f"emu_tma_load({ins[0]}, {ins[1]}, {ins[2]}, 3, {ins[3]}, {ins[4]}, {ins[5]});"
         elif "cp.async.bulk.tensor.2d" in template:
             rep = f"emu_tma_load({ins[0]}, {ins[1]}, {ins[2]}, 2, {ins[3]}, {ins[4]}, 0);"
+        elif template.startswith("bar.arrive"):
+            rep = f"emu_bar_arrive({template.split()[1].rstrip(',')}, {ins[0]});"
         elif template.startswith("bar.sync"):
             rep = f"emu_bar_sync({template.split()[1].rstrip(',')}, {ins[0]});"
         elif template.startswith("fence."):

@@ -44,7 +44,7 @@ def test_measure_reports_parity_value_checks_and_e2e(tiny):
     assert r["parity"]["nranks"] == 1 and r["parity"]["ndte"] == 5 and r["parity"]["umax"] > 0
     assert r["value_check"]["all_finite"] and r["value_check"]["umax"] > 0
     assert r["e2e"]["all_finite"] and r["e2e"]["umax"] > 0 and r["e2e"]["h2d_bytes_per_step"] > 0
-    assert r["loop_kernel_launches_per_step"] == 1 and r["value"] > 0 and r["roofline"]["frac"] > 0
+    assert r["loop_kernel_launches_per_step"] == 3 and r["value"] > 0 and r["roofline"]["frac"] > 0
     for k in ("metric", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "dtype",
               "config", "roofline", "e2e", "gpu_launches"):
         assert k in r

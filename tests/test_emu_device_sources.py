@@ -342,7 +342,8 @@ def test_loop_kernel_tripole_ranks_on_threads_bitwise(monkeypatch, nranks, start
     case = fx.make_case(grid, "full", ndte=7, dt=3600.0)
     with emu.patched(kernel="tma") as evp:
         stats = _group_case(evp, monkeypatch, grid, case, nranks, starts)
-        assert all(s.loop_kernel_launches == (1 if nranks == 1 else 3) for s in stats)      # + signal, wait at N > 1
+        # loop kernel + last subcycle + fold; at N > 1 a signal / wait pair after the loop kernel and before the fold
+        assert all(s.loop_kernel_launches == (3 if nranks == 1 else 7) for s in stats)
 
 
 @pytest.mark.parametrize("gridname,nranks", [("open", 1), ("open", 3), ("closed", 2), ("caps", 2), ("wide", 2)])
