@@ -18,6 +18,67 @@ import torch.distributed as dist
 from cice5_b200 import evp, fixtures as fx
 
 
+def evolve_run(args, e, grid, case, sl, rank, world, starts):
+    """The 10-day parity run on N processes: forcing of call `step` on every rank, state carried on the device
+    slabs and in the oracle, every inout field + strocnxT/yT, divu, shear compared after EVERY call."""
+    import json
+    import time
+    from tests.util import STATE, clone_case, phys, rel_errors
+    dom = case.dom
+    report = ("strocnxT", "strocnyT", "divu", "shear")
+    io = sl(case.io)
+    ref = clone_case(case) if rank == 0 else None
+    if rank == 0:
+        from oracle import oracle as orc
+    stats = {}
+    bitwise = True
+    t0 = time.perf_counter()
+    for step in range(args.calls):
+        f = fx.forcing(grid, case.inp, step, steps_per_cycle=240)
+        inp = dict(case.inp)
+        inp.update(f)
+        out = sl(fx.zeroed_outputs(dom))
+        e.evp(case.dt, sl(inp), io, out)
+        gathered = [None] * world
+        small = ({k: io[k] for k in STATE + ("iceumask",)}, {k: out[k] for k in report})
+        dist.gather_object(small, gathered if rank == 0 else None, dst=0)
+        if rank == 0:
+            ref.inp.update({k: v.copy() for k, v in f.items()})
+            ref.out = fx.zeroed_outputs(dom)
+            orc.run_case(ref)
+            for group, names in ((0, STATE), (1, report)):
+                for n in names:
+                    x = fx.unslab([g[group][n] for g in gathered])
+                    r = (ref.io if group == 0 else ref.out)[n]
+                    if not np.array_equal(phys(x), phys(r)):
+                        bitwise = False
+                    ei, er = rel_errors(x, r)
+                    d = stats.setdefault(n, {"max_inf": 0.0, "max_rms": 0.0})
+                    d["max_inf"] = max(d["max_inf"], float(ei)); d["max_rms"] = max(d["max_rms"], float(er))
+                    d["final_inf"], d["final_rms"] = float(ei), float(er)
+            if not np.array_equal(phys(fx.unslab([g[0]["iceumask"] for g in gathered])), phys(ref.io["iceumask"])):
+                bitwise = False
+    ok = True
+    if rank == 0:
+        vel = max(stats[n]["max_inf"] for n in ("uvel", "vvel"))
+        velr = max(stats[n]["max_rms"] for n in ("uvel", "vvel"))
+        st = max(stats[n]["max_inf"] for n in fx.STRESS_FIELDS)
+        str_ = max(stats[n]["max_rms"] for n in fx.STRESS_FIELDS)
+        rep = {"grid": args.grid, "scenario": args.scenario, "calls": args.calls, "ndte": args.ndte, "nranks": world,
+               "processes": world, "slab_starts": starts, "bitwise_all_calls": bitwise,
+               "vel_max_inf": vel, "vel_max_rms": velr, "stress_max_inf": st, "stress_max_rms": str_,
+               "vel_final_inf": max(stats[n]["final_inf"] for n in ("uvel", "vvel")),
+               "oracle_umax_final": float(np.abs(phys(ref.io["uvel"])).max()), "wall_s": time.perf_counter() - t0,
+               "fields": stats}
+        print("TENDAY " + json.dumps({k: v for k, v in rep.items() if k != "fields"}), flush=True)
+        if args.out:
+            os.makedirs(os.path.dirname(os.path.abspath(args.out)), exist_ok=True)
+            with open(args.out, "w") as fh:
+                json.dump(rep, fh, indent=1)
+        ok = bitwise
+    return ok
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--grid", default="tp1")
@@ -26,6 +87,10 @@ def main():
     ap.add_argument("--calls", type=int, default=2)
     ap.add_argument("--graph", type=int, default=1)
     ap.add_argument("--balanced", type=int, default=1, help="slabs balanced by ocean cells")
+    ap.add_argument("--evolve", type=int, default=0,
+                    help="1: the forcing evolves from call to call (the 10-day run of SURVEY 8d: 240 calls) and EVERY "
+                         "call is compared; prints max / final err_inf and err_rms per field group")
+    ap.add_argument("--out", default=None, help="JSON report (rank 0)")
     args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
@@ -45,6 +110,12 @@ def main():
     dist.all_gather_object(blobs, e.peer_blob())
     e.set_peers(blobs)
     inp, io = sl(case.inp), sl(case.io)
+    if args.evolve:
+        ok = evolve_run(args, e, grid, case, sl, rank, world, starts)
+        e.close()
+        dist.barrier()
+        dist.destroy_process_group()
+        sys.exit(0 if ok else 1)
     for call in range(args.calls):
         out = sl(fx.zeroed_outputs(dom))
         e.evp(case.dt, inp, io, out)
