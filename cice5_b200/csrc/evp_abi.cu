@@ -36,6 +36,17 @@ thread_local char g_cuda_err[512] = "";
         }                                                                                     \
     } while (0)
 #define TRY(x) do { int rc_ = (x); if (rc_ != EVP_OK) return rc_; } while (0)
+// inside evp_gpu_init, once the handle exists: a failing call releases everything the handle holds so far
+#define CKH(call)                                                                             \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if (e_ != cudaSuccess) {                                                              \
+            snprintf(g_cuda_err, sizeof(g_cuda_err), "%s:%d %s: %s", __FILE__, __LINE__, #call, \
+                     cudaGetErrorString(e_));                                                 \
+            evp_gpu_finalize(h);                                                              \
+            return EVP_ERR_CUDA;                                                              \
+        }                                                                                     \
+    } while (0)
 
 // ---- plane directory ----------------------------------------------------------------------
 enum Plane {
@@ -326,11 +337,12 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
         for (int r = 0; r < cfg->nranks; ++r) start[r] = r * (cfg->nx_global / cfg->nranks);
     }
     start[cfg->nranks] = cfg->nx_global;
-    int maxw = 0;
+    int maxw = 0, minw = cfg->nx_global;
     for (int r = 0; r < cfg->nranks; ++r) {
         const int w = start[r + 1] - start[r];
         if (w < 2) return EVP_ERR_UNSUPPORTED;
         if (w > maxw) maxw = w;
+        if (w < minw) minw = w;
     }
     if (cfg->nx_block != start[cfg->rank + 1] - start[cfg->rank] + 2 || cfg->ny_block != cfg->ny_global + 2)
         return EVP_ERR_ARG;
@@ -349,6 +361,12 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
     evp_handle *h = new (std::nothrow) evp_handle();
     if (!h) return EVP_ERR_ARG;
     h->cfg = *cfg;
+    {
+        const char *kv = getenv("EVP_B200_KERNEL");          // "tma" (default) | "sweep"
+        h->use_tma = !(kv && strcmp(kv, "sweep") == 0);
+        const char *lv = getenv("EVP_B200_LOOP");            // "1" (default) | "0": one launch per subcycle
+        h->use_loop = h->use_tma && !(lv && strcmp(lv, "0") == 0);
+    }
     set_evp_parameters(*cfg, h->k);
     h->nxb = cfg->nx_block; h->nyb = cfg->ny_block;
     // rows start on 128-byte boundaries (TMA, sectors); the pitch is that of the widest slab so that
@@ -380,12 +398,21 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
         int sms = 148;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device);
         const long long slots = (long long)kTmaBlocksPerSM * sms;
-        const long long wstrips = (maxw + kTmaUCols - 1) / kTmaUCols;
-        // about 4 items per resident CTA, at most 32 rows (a grid that is mostly ice-free keeps enough items:
-        // caps scenario, 48 rows: -17 %), at least 4; the cost of an item beyond its rows is one extra stage
-        // with the velocities of row r0-1
-        long long rpc = (wstrips * g.ny + 4 * slots - 1) / (4 * slots);
-        rpc = rpc < 4 ? 4 : (rpc > 32 ? 32 : rpc);
+        // launch per subcycle: about 4 items per resident CTA (drawn heaviest first, so land / open-ocean items even
+        // out the ragged end of a launch), at most 32 rows, at least 4.  Loop kernel: no ragged end to even out, so
+        // items as tall as possible (each costs one redundant T row and one velocity-only stage) while every rank
+        // keeps about 1.5 x as many items per subcycle as resident CTAs -- a tile's neighbours of the previous
+        // subcycle must have left the CTAs by the time it is drawn (measured on the N = 8 per-GPU proxy, 4 strips:
+        // 75.4 us at 12-16 rows, 83 at 20, 85 at 4; tp01: 520 / 511 / 507 us at 16 / 32 / 48 rows)
+        const long long wstrips = (maxw + kTmaUCols - 1) / kTmaUCols, nstrips = (minw + kTmaUCols - 1) / kTmaUCols;
+        long long rpc;
+        if (h->use_loop) {
+            rpc = (2 * nstrips * g.ny) / (3 * slots);
+            rpc = rpc < 2 ? 2 : (rpc > 48 ? 48 : rpc);
+        } else {
+            rpc = (wstrips * g.ny + 4 * slots - 1) / (4 * slots);
+            rpc = rpc < 4 ? 4 : (rpc > 32 ? 32 : rpc);
+        }
         if (const char *ev = getenv("EVP_B200_RPC")) rpc = atoi(ev);      // tuning experiments
         rpc = rpc < 2 ? 2 : (rpc > 64 ? 64 : rpc);
         h->t_rpc = (int)rpc;
@@ -402,21 +429,18 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
     cudaError_t e = cudaMalloc(&h->arena, h->arena_bytes);
     if (e != cudaSuccess) {
         snprintf(g_cuda_err, sizeof(g_cuda_err), "cudaMalloc(%zu bytes): %s", h->arena_bytes, cudaGetErrorString(e));
-        delete h;
+        h->arena = nullptr;
+        evp_gpu_finalize(h);
         return EVP_ERR_CUDA;
     }
-    CK(cudaMemset(h->arena, 0, h->arena_bytes));
-    CK(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+    CKH(cudaMemset(h->arena, 0, h->arena_bytes));
+    CKH(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
     h->stream = h->own_stream;
-    for (auto &ev : h->ev) CK(cudaEventCreate(&ev));
+    for (auto &ev : h->ev) CKH(cudaEventCreate(&ev));
     memset(&h->stats, 0, sizeof(h->stats));
     {
-        const char *kv = getenv("EVP_B200_KERNEL");          // "tma" (default) | "sweep"
-        h->use_tma = !(kv && strcmp(kv, "sweep") == 0);
-        const char *lv = getenv("EVP_B200_LOOP");            // "1" (default) | "0": one launch per subcycle
-        h->use_loop = h->use_tma && !(lv && strcmp(lv, "0") == 0);
         cudaDeviceProp prop;
-        CK(cudaGetDeviceProperties(&prop, cfg->device));
+        CKH(cudaGetDeviceProperties(&prop, cfg->device));
         h->sm_count = prop.multiProcessorCount;
         if (h->use_tma) { int rc = make_tensor_maps(h); if (rc != EVP_OK) { evp_gpu_finalize(h); return rc; } }
     }
