@@ -31,10 +31,10 @@ import numpy as np
 
 ALG_BYTES = 392.0          # per active cell-subcycle (49 doubles), SURVEY.md section 8d
 L2_BYTES = 126e6
-# dram__bytes_read.sum + dram__bytes_write.sum of one evp_subcycle_tma_kernel<false> launch on the
-# default workload (tp01 full, 1 GPU), from the ncu pass in profiles/r01_launches_tp01_final.md;
-# only quoted for exactly that workload
-NCU_TRAFFIC = {("tp01", "full", 1, True): 1.7716e9 + 0.8417e9}
+# dram__bytes_read.sum + dram__bytes_write.sum PER SUBCYCLE of evp_loop_tma_kernel on the default workload
+# (tp01 full, 1 GPU: 219.20 + 104.83 GB over the 119 subcycles of one launch), from the ncu --set full capture in
+# profiles/r02_loop_ncu.md; only quoted for exactly that workload
+NCU_TRAFFIC = {("tp01", "full", 1, True): (219.202653e9 + 104.833455e9) / 119.0}
 
 
 def parse():
