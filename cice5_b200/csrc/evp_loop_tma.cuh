@@ -39,8 +39,9 @@
 namespace evp {
 
 constexpr int kItemFold = 0x20000000;        // tag of the fold item of a subcycle
-// timing experiments (bit mask, never the product): 1 no writer-side fences, 2 no reader-side proxy fence,
-// 4 no dependency polls at all (wrong answers at N > 1 / small grids), 8 last subcycle with the LAST = false body
+// timing experiments (bit mask, never the product): 1 no writer-side proxy fence, 2 no reader-side proxy fence,
+// 4 no dependency polls at all (wrong answers at N > 1 / small grids), 16 no E-W ghost stores into peer memory,
+// 32 gpu-scope release even where a peer reads, 64 no tripole inbox stores (16 / 32 / 64: wrong answers at N > 1)
 #ifndef EVP_LOOP_EXP
 #define EVP_LOOP_EXP 0
 #endif
@@ -262,15 +263,16 @@ __device__ __forceinline__ void sweep_item(const LoopTmaArgs &p, unsigned char *
             }
             if (ucol) {
                 u1[iu] = unew; v1[iu] = vnew;
-                if (c == 1 && uW) {
+                const bool no_ew = (EVP_LOOP_EXP & 16) && p.nranks > 1;
+                if (!no_ew && c == 1 && uW) {
                     const size_t ig = (size_t)(r - 1) * ld + a.nxl_west + 1;
                     uW[ig] = unew; uW[pe + ig] = vnew;
                 }
-                if (c == a.nxl && uE) {
+                if (!no_ew && c == a.nxl && uE) {
                     const size_t ig = (size_t)(r - 1) * ld;
                     uE[ig] = unew; uE[pe + ig] = vnew;
                 }
-                if (a.tripole && r - 1 >= a.ny - 1)
+                if (a.tripole && r - 1 >= a.ny - 1 && !((EVP_LOOP_EXP & 64) && p.nranks > 1))
                     tripole_push(a, p.inbox[ibuf], c, (r - 1) - (a.ny - 1), unew, vnew);
             }
         }
@@ -489,12 +491,14 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
                 const bool west_edge = strip == 0 && p.pub_w, east_edge = strip == p.strips - 1 && p.pub_e;
                 const bool top = p.has_fold && rend >= a.ny;
                 if ((EVP_LOOP_EXP & 1) == 0) asm volatile("fence.proxy.async.global;" ::: "memory");
-                if (p.nranks > 1 && (west_edge || east_edge || top)) {
+                if ((EVP_LOOP_EXP & 32) == 0 && p.nranks > 1 && (west_edge || east_edge || top)) {
                     st_release_u64<true>(p.tflag + item, done);          // stores into peer memory precede it
                     if (west_edge) st_release_u64<true>(p.pub_w + chunk, done);
                     if (east_edge) st_release_u64<true>(p.pub_e + chunk, done);
                 } else {
                     st_release_u64<false>(p.tflag + item, done);
+                    if ((EVP_LOOP_EXP & 32) && west_edge) st_release_u64<false>(p.pub_w + chunk, done);
+                    if ((EVP_LOOP_EXP & 32) && east_edge) st_release_u64<false>(p.pub_e + chunk, done);
                 }
                 if (top) {
                     const unsigned long long ntop = (unsigned long long)p.item_count[2];

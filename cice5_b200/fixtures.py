@@ -352,12 +352,13 @@ GRIDS = {
     "tp01": lambda: synthetic_tripole(3600, 2700, "tp01"),     # AusCOM 0.1 deg
     # tuning proxy, not a BASELINE config: the cells ONE GPU owns when tp01 is cut into 8 x-slabs
     "tp01s8": lambda: synthetic_tripole(450, 2700, "tp01s8"),
+    "tp01s16": lambda: synthetic_tripole(226, 2700, "tp01s16"),
 }
 
 # dt per grid: the model time steps these resolutions are run with (1 h for the coarse grids,
 # shorter for the eddy-rich ones); ndte = 120 everywhere (BASELINE.json configs).
 GRID_DT = {"gx3": 3600.0, "gx1": 3600.0, "tp1": 3600.0, "tp025": 1800.0, "tp01": 600.0,
-           "tp01s8": 600.0}
+           "tp01s8": 600.0, "tp01s16": 600.0}
 
 
 def make_grid(name: str) -> Grid:
