@@ -301,6 +301,9 @@ const char *evp_gpu_strerror(int status)
         case EVP_ERR_STATE: return "evp_gpu: call order violated (init -> set_grid -> [set_peers] -> run)";
         case EVP_ERR_NO_DEVICE: return "evp_gpu: no usable CUDA device; this library has no CPU fallback";
         case EVP_ERR_PEER: return "evp_gpu: multi-GPU peer mapping failed";
+        case EVP_ERR_TOO_LARGE:
+            return "evp_gpu: block larger than the static scratch of an allocation-free entry point "
+                   "(EVP_STATIC_MAX_CELLS; see evp_gpu_last_cuda_error)";
         default: return "evp_gpu: unknown status";
     }
 }
@@ -1516,6 +1519,68 @@ int evp_gpu_principal_stress(evp_handle_t *h, double *sig1, double *sig2)
     TRY(B.r8(W_2, sig2));
     TRY(B.flush());
     CK(cudaStreamSynchronize(h->stream));
+    return EVP_OK;
+}
+
+}  // extern "C"
+
+// ---- evp_gpu_principal_stress_static: principal_stress without any allocation ---------------------------
+// Scratch of the existing entry point: two work planes of the handle's arena + the staging area (cudaMalloc at init /
+// first use).  Here: one file-scope device array -- 4 input planes + 2 output planes of at most
+// EVP_STATIC_MAX_CELLS cells, dense -- that every GPU which loads the library holds until exit.
+// All calls share it (it keeps the last call's contents; every element a call reads is written by that call first,
+// nothing has to start at zero); calls that overlap on one GPU race.
+static __device__ __align__(256) double g_static_scratch[6 * (size_t)EVP_STATIC_MAX_CELLS];
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+double *g_static_ptr[kStaticMaxDevices] = {nullptr};       // device address of g_static_scratch, per device
+
+// In host code `g_static_scratch` is only a stand-in for the symbol, not a device address: resolve it once per
+// device, with that device current.
+int static_scratch_ptr(int device, double **out)
+{
+    if (device < 0 || device >= kStaticMaxDevices) return EVP_ERR_NO_DEVICE;
+    if (!g_static_ptr[device]) {
+        void *p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_static_scratch));
+        g_static_ptr[device] = static_cast<double *>(p);
+    }
+    *out = g_static_ptr[device];
+    return EVP_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int evp_gpu_principal_stress_static(int device, int nx_block, int ny_block, const double *stressp_1,
+                                    const double *stressm_1, const double *stress12_1, const double *prs_sig,
+                                    double *sig1, double *sig2)
+{
+    if (!stressp_1 || !stressm_1 || !stress12_1 || !prs_sig || !sig1 || !sig2) return EVP_ERR_ARG;
+    if (nx_block < 1 || ny_block < 1) return EVP_ERR_ARG;
+    const long long cells = (long long)nx_block * ny_block;
+    if (cells > (long long)EVP_STATIC_MAX_CELLS) {
+        snprintf(g_cuda_err, sizeof(g_cuda_err), "evp_gpu_principal_stress_static: %d x %d = %lld cells exceed the static "
+                 "scratch of %d cells", nx_block, ny_block, cells, (int)EVP_STATIC_MAX_CELLS);
+        return EVP_ERR_TOO_LARGE;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1 || device < 0 || device >= ndev) return EVP_ERR_NO_DEVICE;
+    CK(cudaSetDevice(device));
+    double *scr = nullptr;
+    TRY(static_scratch_ptr(device, &scr));
+    const size_t n = (size_t)cells, bytes = n * sizeof(double);
+    const double *src[4] = {stressp_1, stressm_1, stress12_1, prs_sig};
+    for (int q = 0; q < 4; ++q) CK(cudaMemcpy(scr + q * n, src[q], bytes, cudaMemcpyHostToDevice));
+    dim3 grid((nx_block + 127) / 128, ny_block);
+    // legacy default stream: no stream is created; the blocking cudaMemcpy calls around the launch order everything
+    principal_stress_kernel<<<grid, 128, 0, 0>>>(nx_block, ny_block, nx_block, scr, scr + n, scr + 2 * n, scr + 3 * n,
+                                                 scr + 4 * n, scr + 5 * n);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(0));
+    CK(cudaMemcpy(sig1, scr + 4 * n, bytes, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(sig2, scr + 5 * n, bytes, cudaMemcpyDeviceToHost));
     return EVP_OK;
 }
 

@@ -75,7 +75,9 @@ EXPORTS = ("evp_gpu_init", "evp_gpu_set_grid", "evp_gpu_run", "evp_gpu_upload", 
            "evp_gpu_get_peer_blob", "evp_gpu_set_peers", "evp_gpu_finalize", "evp_gpu_strerror",
            "evp_gpu_last_cuda_error", "evp_gpu_device_count", "evp_gpu_get_trace", "evp_gpu_upload_itd",
            "evp_gpu_principal_stress", "evp_gpu_pin_host_arrays", "evp_gpu_set_resident",
-           "evp_gpu_invalidate_state", "evp_gpu_restart_fixup", "evp_gpu_restart_fixup_group")
+           "evp_gpu_invalidate_state", "evp_gpu_restart_fixup", "evp_gpu_restart_fixup_group",
+           "evp_gpu_principal_stress_static")
+STATIC_MAX_CELLS = 131072       # EVP_STATIC_MAX_CELLS of include/evp_b200.h
 
 # download groups of the resident-state protocol (include/evp_b200.h)
 DL_VELOCITY, DL_STRESS, DL_DEFORM, DL_OCN_T, DL_HISTORY, DL_ALL = 1, 2, 4, 8, 16, 31
@@ -331,6 +333,22 @@ def compute_group(solvers: list, dt: float):
     """evp_gpu_compute_group: all ranks of one decomposition driven from this thread."""
     arr = (C.c_void_p * len(solvers))(*[e._h for e in solvers])
     solvers[0]._check(solvers[0].lib.evp_gpu_compute_group(arr, len(solvers), C.c_double(dt)))
+
+
+def principal_stress_static(stressp_1, stressm_1, stress12_1, prs_sig, device=0, strict=True):
+    """evp_gpu_principal_stress_static: sig1, sig2 from host arrays, no handle, no allocation on the device (the scratch
+    is a static device array of STATIC_MAX_CELLS cells per plane).  Raises EvpError beyond that size."""
+    lib = load_library(strict)
+    ny, nx = stressp_1.shape
+    sig1, sig2 = np.empty_like(stressp_1), np.empty_like(stressp_1)
+    rc = lib.evp_gpu_principal_stress_static(C.c_int(device), C.c_int(nx), C.c_int(ny), _dp(stressp_1), _dp(stressm_1),
+                                             _dp(stress12_1), _dp(prs_sig), _dp(sig1), _dp(sig2))
+    if rc != 0:
+        msg = lib.evp_gpu_strerror(rc).decode()
+        if rc in (3, 7):
+            msg += " [" + lib.evp_gpu_last_cuda_error().decode() + "]"
+        raise EvpError(msg)
+    return sig1, sig2
 
 
 def device_count() -> int:

@@ -33,7 +33,8 @@ enum {
     EVP_ERR_CUDA = 3,         /* a CUDA runtime call failed (see evp_gpu_last_cuda_error) */
     EVP_ERR_STATE = 4,        /* call order violated (e.g. run before set_grid)         */
     EVP_ERR_NO_DEVICE = 5,    /* no usable CUDA device: there is NO CPU fallback        */
-    EVP_ERR_PEER = 6          /* multi-GPU peer mapping failed                          */
+    EVP_ERR_PEER = 6,         /* multi-GPU peer mapping failed                          */
+    EVP_ERR_TOO_LARGE = 7     /* block exceeds the static scratch of an allocation-free entry point */
 };
 
 enum { EVP_EW_CLOSED = 0, EVP_EW_CYCLIC = 1 };
@@ -191,6 +192,20 @@ int evp_gpu_synchronize(evp_handle_t *h);
  * source/ice_history.F90:1921) from the device-resident stressp_1, stressm_1, stress12_1, prs_sig of
  * the last evp: sig1, sig2 over the whole block, spval_dbl = 1e30 where prs_sig <= puny. */
 int evp_gpu_principal_stress(evp_handle_t *h, double *sig1, double *sig2);
+
+/* No counterpart in the reference.  principal_stress (the same kernel
+ * as evp_gpu_principal_stress) for callers that must not allocate -- code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc.  No handle: the four inputs (stressp_1, stressm_1, stress12_1, prs_sig) and
+ * the two outputs are HOST arrays of nx_block x ny_block doubles; the device scratch (inputs + outputs, 6 planes) is a
+ * file-scope `static __device__` array of EVP_STATIC_MAX_CELLS cells per plane (6 MiB in all) that every GPU which
+ * loads the library holds until exit.  The call makes no cudaMalloc / cudaFree / allocating library call; it runs on
+ * the default stream of `device` and is complete on return.  nx_block * ny_block > EVP_STATIC_MAX_CELLS ->
+ * EVP_ERR_TOO_LARGE.  All calls share the array, which keeps the last call's contents (every element a call reads is
+ * written by that call first): calls that overlap on one GPU race -- serialise them. */
+#define EVP_STATIC_MAX_CELLS 131072      /* e.g. gx3 102 x 118, gx1 322 x 386, 1 deg tripole 362 x 302 */
+int evp_gpu_principal_stress_static(int device, int nx_block, int ny_block, const double *stressp_1,
+                                    const double *stressm_1, const double *stress12_1, const double *prs_sig,
+                                    double *sig1, double *sig2);
 
 /* Diagnostics (library started with EVP_B200_TRACE=1): per subcycle 8 x u64 device timestamps in
  * ns: [0] subcycle kernel start, [1] its last CTA done, [2] peers signalled, [3] fold wait begin,

@@ -236,6 +236,8 @@ cudaError_t cudaMalloc(void **, size_t);
 template <class T> inline cudaError_t cudaMalloc(T **p, size_t n) { return cudaMalloc((void **)p, n); }
 cudaError_t cudaFree(void *);
 cudaError_t cudaMemcpy(void *, const void *, size_t, cudaMemcpyKind);
+// a `static __device__` array is a host array here: its address is the "device" address
+template <class T> inline cudaError_t cudaGetSymbolAddress(void **p, const T &symbol) { *p = (void *)&symbol; return cudaSuccess; }
 cudaError_t cudaMemcpyAsync(void *, const void *, size_t, cudaMemcpyKind, cudaStream_t = nullptr);
 cudaError_t cudaMemcpy2DAsync(void *, size_t, const void *, size_t, size_t, size_t, cudaMemcpyKind, cudaStream_t = nullptr);
 cudaError_t cudaMemset(void *, int, size_t);
