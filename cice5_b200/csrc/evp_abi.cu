@@ -119,6 +119,7 @@ struct evp_handle {
     // pad to 16, wflag[t_chunks], eflag[t_chunks], tflag[t_items].  Peers write topflag / wflag / eflag, so the
     // region sits before every per-rank-sized one and t_chunks is the same on all ranks.
     size_t off_lflags = 0;
+    size_t off_ll = 0;            // ghost mailbox of the loop kernel: u64[kLLBufs][2][nyb][4], written by the E-W neighbours
     bool use_loop = false;        // the ndte loop as ONE persistent kernel (default with the TMA kernel; EVP_B200_LOOP=0: off)
     char *peer_arena[kMaxRanks] = {nullptr};
     bool peer_opened[kMaxRanks] = {false};
@@ -174,6 +175,12 @@ struct evp_handle {
     int *done_bnd(int ksub) const { return reinterpret_cast<int *>(arena + off_queue) + 2 * cfg.ndte + ksub; }
     int *item_count() const { return reinterpret_cast<int *>(arena + off_queue) + 3 * cfg.ndte; }   // [2]
     int *item_list() const { return reinterpret_cast<int *>(arena + off_queue) + 3 * cfg.ndte + 4; }
+    unsigned long long *ll_box(int rank = -1) const
+    {
+        char *base = (rank < 0 || rank == cfg.rank) ? arena : peer_arena[rank];
+        return reinterpret_cast<unsigned long long *>(base + off_ll);
+    }
+    size_t ll_bytes() const { return (size_t)kLLBufs * 2 * nyb * 4 * sizeof(unsigned long long); }
     unsigned long long *lflags(int rank = -1) const
     {
         char *base = (rank < 0 || rank == cfg.rank) ? arena : peer_arena[rank];
@@ -422,6 +429,7 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
         h->t_chunks = (g.ny + h->t_rpc - 1) / h->t_rpc;
         h->t_items = h->tstrips * h->t_chunks;
     }
+    h->off_ll = off;     off = align_up(off + h->ll_bytes(), 256);      // (same size and offset on every rank)
     h->off_lflags = off; off = align_up(off + (16 + 2 * (size_t)h->t_chunks + h->t_items) * sizeof(unsigned long long), 256);
     h->off_tflags = off; off = align_up(off + (size_t)h->tstrips * h->tflags_ld, 256);
     h->off_gflags = off; off = align_up(off + (size_t)h->tstrips * h->tflags_ld, 256);
@@ -997,6 +1005,10 @@ void add_loop(Builder &B, int from_parity, int nsteps)
         if (nr > 1 && !h->west_closed()) { t.wflag = lf + 16; t.pub_w = h->lflags(h->west()) + 16 + h->t_chunks; }
         if (nr > 1 && !h->east_closed()) { t.eflag = lf + 16 + h->t_chunks; t.pub_e = h->lflags(h->east()) + 16; }
         for (int r = 0; r < nr; ++r) t.pub_top[r] = h->lflags(r);
+        t.ll_on = nr > 1 ? 1 : 0; t.nyb = h->nyb;
+        t.ll_my = h->ll_box();
+        if (nr > 1 && !h->west_closed()) t.ll_w = h->ll_box(h->west());
+        if (nr > 1 && !h->east_closed()) t.ll_e = h->ll_box(h->east());
         t.rank = h->cfg.rank; t.nranks = nr;
         t.error = h->dev_error();
         t.timeout_ns = sync_timeout_ns();
@@ -1011,7 +1023,21 @@ void add_loop(Builder &B, int from_parity, int nsteps)
         ++L.n;
         return EVP_OK;
     });
-    B.sync();      // every rank has finished its loop kernel: ghost columns, inboxes and folds are complete
+    B.sync();      // every rank has finished its loop kernel: mailboxes, inboxes and folds are complete
+    if (h->cfg.nranks > 1) {
+        // the ghost columns of the final planes out of the mailbox rows of the loop's last subcycle
+        B.op([h, from_parity, nsteps](Launcher &L) {
+            const int par_end = from_parity ^ (nsteps & 1);
+            const int jhi = h->g.tripole ? h->g.ny - 1 : h->g.ny;
+            dim3 grid((jhi + 127) / 128, 2);
+            ll_drain_kernel<<<grid, 128, 0, L.s()>>>(h->plane(par_end ? S_UB : S_UA), h->plane_elems, h->ld, h->g.nxl, h->nyb,
+                                                     h->ll_box(), nsteps - 1, jhi, h->west_closed() ? 0 : 1,
+                                                     h->east_closed() ? 0 : 1);
+            ++L.n;
+            CK(cudaGetLastError());
+            return EVP_OK;
+        });
+    }
 }
 
 // one subcycle: stress + stepu + halo pushes fused; [sync]; then the tripole fold of the new u, v
@@ -1106,6 +1132,9 @@ void build_program(evp_handle *h, double dt, Program &P)
         CK(cudaMemsetAsync(h->plane(O_STRAIRX), 0, pb * 17, s));   // all output planes
         CK(cudaMemsetAsync(h->plane(S_FM), 0, pb, s));
         CK(cudaMemsetAsync(h->counts(), 0, 16, s));
+        // ghost mailbox of the loop kernel: its flags count subcycles from 1 in every call (the neighbours write it only
+        // inside their loop kernels, several cross-rank barriers after this point)
+        if (h->cfg.nranks > 1 && loop_mode(h)) CK(cudaMemsetAsync(h->ll_box(), 0, h->ll_bytes(), s));
         // evp_prep1 (:194)
         Prep1Args a;
         a.g = h->g; a.rhoi = h->cfg.rhoi; a.rhos = h->cfg.rhos; a.a_min = h->cfg.a_min; a.m_min = h->cfg.m_min;

@@ -21,9 +21,12 @@
 //     whole subcycle earlier: on grids with more tiles than CTAs nobody ever waits, the end of subcycle k
 //     overlaps the start of k+1, and on small grids the kernel degenerates into a dataflow pipeline whose
 //     period is one tile + one flag round trip;
-//   * across GPUs the same counters: an edge strip publishes its counter into the neighbour rank's arena
-//     (peer memory over NVLink) after its ghost-column stores; no barrier, ranks may drift by almost a
-//     whole subcycle;
+//   * across GPUs NO fence at all: an edge strip sends its edge column to the neighbour rank as flag-in-data
+//     words (ghost mailbox, below: every 64-bit store carries 32 bits of a velocity and the subcycle number, the
+//     way NCCL's LL protocol does), and the neighbour's edge tile of the next subcycle polls the words in its OWN
+//     memory and writes the values into its ghost column before its first TMA load.  (First version: ghost values
+//     stored into the peer's planes + a system-scope release of a counter -- `st.release.sys` cost 20 us per edge
+//     item under load, profiles/r02_scaling.md.)  Ranks may drift by almost a whole subcycle;
 //   * the tripole fold of subcycle k is one more item at the end of the subcycle's positions: it waits
 //     until the top tiles of every rank have finished k (one counter per rank, published by the CTA that
 //     completes the count), folds rows ny, ny+1 of the new velocities and publishes `fold_flag`; only the
@@ -40,8 +43,7 @@ namespace evp {
 
 constexpr int kItemFold = 0x20000000;        // tag of the fold item of a subcycle
 // timing experiments (bit mask, never the product): 1 no writer-side proxy fence, 2 no reader-side proxy fence,
-// 4 no dependency polls at all (wrong answers at N > 1 / small grids), 16 no E-W ghost stores into peer memory,
-// 32 gpu-scope release even where a peer reads, 64 no tripole inbox stores (16 / 32 / 64: wrong answers at N > 1)
+// 4 no dependency polls at all (wrong answers at N > 1 / small grids)
 #ifndef EVP_LOOP_EXP
 #define EVP_LOOP_EXP 0
 #endif
@@ -77,7 +79,78 @@ struct LoopTmaArgs {
     int rank, nranks;
     int *error;
     unsigned long long timeout_ns;
+    // ghost mailbox (nranks > 1): [kLLBufs][side: 0 = my west ghost, 1 = my east ghost][row 0 .. nyb-1][4 words]
+    unsigned long long *ll_my;               // mine: the neighbours write it, I poll it
+    unsigned long long *ll_w, *ll_e;         // the west / east neighbour's (peer memory); null: no neighbour on that side
+    int ll_on, nyb;
 };
+
+// ---- ghost mailbox: flag-in-data exchange of the E-W ghost columns between ranks -------------------------
+// One row of one side = 4 words {u low, u high, v low, v high}; word = (32 bits of payload << 32) | flag, flag =
+// subcycle + 1 (never 0; the mailbox is zeroed at the start of a call), bit 31 = "row not computed this call: keep the
+// value you have".  A naturally aligned 64-bit store is single-copy atomic, so a word whose flag matches carries
+// its payload: no fence, no separate counter, and both sides only use strong (volatile) accesses -- no data race in
+// the PTX model.  Buffer = subcycle & 3: a slot is rewritten 4 subcycles later, by when the receiver has long
+// consumed it (its reader must have finished before the writer's own dependencies two subcycles on can be met).
+constexpr int kLLBufs = 4;
+constexpr unsigned kLLUnchanged = 0x80000000u;
+
+__device__ __forceinline__ volatile unsigned long long *ll_row(unsigned long long *box, int nyb, int step, int side, int row)
+{
+    return box + ((((size_t)(step & (kLLBufs - 1))) * 2 + side) * nyb + row) * 4;
+}
+__device__ __forceinline__ void ll_push(unsigned long long *box, int nyb, int step, int side, int row, double u, double v,
+                                        bool computed)
+{
+    volatile unsigned long long *w = ll_row(box, nyb, step, side, row);
+    const unsigned long long flag = (unsigned long long)(unsigned)(step + 1) | (computed ? 0u : kLLUnchanged);
+    const unsigned long long ub = (unsigned long long)__double_as_longlong(u), vb = (unsigned long long)__double_as_longlong(v);
+    w[0] = (ub << 32) | flag;
+    w[1] = (ub & 0xffffffff00000000ull) | flag;
+    w[2] = (vb << 32) | flag;
+    w[3] = (vb & 0xffffffff00000000ull) | flag;
+}
+// wait for the four words of (step, side, row); false: the sender did not compute the row (or the wait gave up)
+__device__ __forceinline__ bool ll_take(unsigned long long *box, int nyb, int step, int side, int row, double &u, double &v,
+                                        int *error, unsigned long long timeout_ns)
+{
+    volatile unsigned long long *w = ll_row(box, nyb, step, side, row);
+    const unsigned want = (unsigned)(step + 1);
+    unsigned long long x[4];
+    unsigned long long t0 = 0;
+    for (int q = 0; q < 4; ++q) {
+        for (;;) {
+            x[q] = w[q];
+            if (((unsigned)x[q] & ~kLLUnchanged) == want) break;
+            if (t0 == 0) t0 = global_ns();
+            __nanosleep(32);
+            if (*(volatile int *)error) return false;
+            if (global_ns() - t0 > timeout_ns) { *(volatile int *)error = 1; return false; }
+        }
+    }
+    if ((unsigned)x[0] & kLLUnchanged) return false;
+    u = __longlong_as_double((long long)((x[0] >> 32) | (x[1] & 0xffffffff00000000ull)));
+    v = __longlong_as_double((long long)((x[2] >> 32) | (x[3] & 0xffffffff00000000ull)));
+    return true;
+}
+
+// After the loop kernel (and the cross-rank barrier behind it): the ghost columns of the final planes from the
+// mailbox rows of the last subcycle of the loop -- inside the loop a receiver tile does this for itself one subcycle
+// later.  One thread per (row, side); rows 1 .. jhi.
+__global__ void ll_drain_kernel(double *u, size_t plane_elems, int ld, int nxl, int nyb, unsigned long long *box, int step,
+                                int jhi, int recv_w, int recv_e)
+{
+    const int j = 1 + blockIdx.x * blockDim.x + threadIdx.x, side = blockIdx.y;
+    if (j > jhi || !(side == 0 ? recv_w : recv_e)) return;
+    volatile unsigned long long *w = ll_row(box, nyb, step, side, j);
+    unsigned long long x[4];
+    for (int q = 0; q < 4; ++q) x[q] = w[q];
+    for (int q = 0; q < 4; ++q)
+        if ((unsigned)x[q] != (unsigned)(step + 1)) return;           // not sent, or "keep the value you have"
+    const size_t at = (size_t)j * ld + (side == 0 ? 0 : nxl + 1);
+    u[at] = __longlong_as_double((long long)((x[0] >> 32) | (x[1] & 0xffffffff00000000ull)));
+    u[plane_elems + at] = __longlong_as_double((long long)((x[2] >> 32) | (x[3] & 0xffffffff00000000ull)));
+}
 
 // SYS: the counter is written or read by another GPU (peer memory); otherwise gpu scope is enough and cheaper
 template <bool SYS>
@@ -119,12 +192,12 @@ __device__ __forceinline__ const unsigned long long *neighbour_counter(const Loo
     if (strip < 0) {
         if (p.ew_self) return p.tflag + (size_t)chunk * p.strips + (p.strips - 1);
         remote = true;
-        return p.wflag ? p.wflag + chunk : nullptr;
+        return (p.wflag && !p.ll_on) ? p.wflag + chunk : nullptr;
     }
     if (strip >= p.strips) {
         if (p.ew_self) return p.tflag + (size_t)chunk * p.strips;
         remote = true;
-        return p.eflag ? p.eflag + chunk : nullptr;
+        return (p.eflag && !p.ll_on) ? p.eflag + chunk : nullptr;
     }
     return p.tflag + (size_t)chunk * p.strips + strip;
 }
@@ -135,7 +208,7 @@ __device__ __forceinline__ const unsigned long long *neighbour_counter(const Loo
 template <bool LAST, bool REVISED>
 __device__ __forceinline__ void sweep_item(const LoopTmaArgs &p, unsigned char *ring, unsigned long long *full_bar,
                                            unsigned long long *empty_bar, int &stage, unsigned &phase, int strip, int r0,
-                                           int rend, int par, int ibuf, int warp, int lane)
+                                           int rend, int par, int ibuf, int step, int warp, int lane)
 {
     const LoopArgs &a = p.a;
     const Consts &k = a.k;
@@ -263,18 +336,26 @@ __device__ __forceinline__ void sweep_item(const LoopTmaArgs &p, unsigned char *
             }
             if (ucol) {
                 u1[iu] = unew; v1[iu] = vnew;
-                const bool no_ew = (EVP_LOOP_EXP & 16) && p.nranks > 1;
-                if (!no_ew && c == 1 && uW) {
-                    const size_t ig = (size_t)(r - 1) * ld + a.nxl_west + 1;
-                    uW[ig] = unew; uW[pe + ig] = vnew;
+                if (p.ll_on) {                                      // my edge columns are the neighbours' ghosts
+                    if (c == 1 && p.ll_w) ll_push(p.ll_w, p.nyb, step, 1, r - 1, unew, vnew, true);
+                    if (c == a.nxl && p.ll_e) ll_push(p.ll_e, p.nyb, step, 0, r - 1, unew, vnew, true);
+                } else {
+                    if (c == 1 && uW) {
+                        const size_t ig = (size_t)(r - 1) * ld + a.nxl_west + 1;
+                        uW[ig] = unew; uW[pe + ig] = vnew;
+                    }
+                    if (c == a.nxl && uE) {
+                        const size_t ig = (size_t)(r - 1) * ld;
+                        uE[ig] = unew; uE[pe + ig] = vnew;
+                    }
                 }
-                if (!no_ew && c == a.nxl && uE) {
-                    const size_t ig = (size_t)(r - 1) * ld;
-                    uE[ig] = unew; uE[pe + ig] = vnew;
-                }
-                if (a.tripole && r - 1 >= a.ny - 1 && !((EVP_LOOP_EXP & 64) && p.nranks > 1))
+                if (a.tripole && r - 1 >= a.ny - 1)
                     tripole_push(a, p.inbox[ibuf], c, (r - 1) - (a.ny - 1), unew, vnew);
             }
+        } else if (r > r0 && p.ll_on && ucol) {
+            // U row r-1 of this segment is not computed in this call (no ice): the neighbour must not wait for it
+            if (c == 1 && p.ll_w) ll_push(p.ll_w, p.nyb, step, 1, r - 1, 0.0, 0.0, false);
+            if (c == a.nxl && p.ll_e) ll_push(p.ll_e, p.nyb, step, 0, r - 1, 0.0, 0.0, false);
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty_bar[stage]);              // row done: slot free
@@ -359,6 +440,28 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
                     }
                 } else if (lane == 9 && p.has_fold && rend >= a.ny) {
                     wait_counter<false>(p.fold_flag, (unsigned long long)k, p.error, p.timeout_ns);
+                }
+                if (p.ll_on) {
+                    // ghost rows r0-1 .. rend of the OLD planes of this subcycle = what the neighbour's edge strip
+                    // computed in subcycle k-1: out of my mailbox into my ghost column (strong stores: the tiles above
+                    // and below write the rows we share with the same values).  Row ny of a tripole grid belongs to
+                    // the fold item, row ny+1 to nobody.
+                    double *const sold = p.state[p.parity0 ^ (k & 1)];
+                    const int jlo = r0 - 1 > 1 ? r0 - 1 : 1, jtop = p.has_fold ? a.ny - 1 : a.ny;
+                    const int jhi = rend < jtop ? rend : jtop;
+                    for (int side = 0; side < 2; ++side) {
+                        const unsigned long long *nbr = side == 0 ? p.wflag : p.eflag;
+                        if (!nbr || (side == 0 ? strip != 0 : strip != p.strips - 1)) continue;
+                        for (int j = jlo + lane; j <= jhi; j += 32) {
+                            if (nbr[(j - 1) / a.rows_per_chunk] == ~0ull) continue;      // that tile never runs
+                            double u, v;
+                            if (ll_take(p.ll_my, p.nyb, k - 1, side, j, u, v, p.error, p.timeout_ns)) {
+                                const size_t at = (size_t)j * a.ld + (side == 0 ? 0 : a.nxl + 1);
+                                *(volatile double *)(sold + at) = u;
+                                *(volatile double *)(sold + p.plane_elems + at) = v;
+                            }
+                        }
+                    }
                 }
                 __syncwarp();
                 // the planes were written through the generic proxy (other SMs, other GPUs); TMA reads them
@@ -445,6 +548,18 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
             if (lane == 0) mbar_arrive(&empty_bar[stage]);
             if (++stage == kTmaStages) { stage = 0; phase ^= 1u; }
             if (tid < p.nranks) wait_counter<true>(p.topflag + tid, (unsigned long long)step + 1, p.error, p.timeout_ns);
+            if (p.ll_on && tid >= 32 && tid < 34) {
+                // the neighbours' row-ny values (before the fold) for my two ghost columns
+                const int side = tid - 32;
+                const unsigned long long *nbr = side == 0 ? p.wflag : p.eflag;
+                double u, v;
+                if (nbr && nbr[(a.ny - 1) / a.rows_per_chunk] != ~0ull &&
+                    ll_take(p.ll_my, p.nyb, step, side, a.ny, u, v, p.error, p.timeout_ns)) {
+                    const size_t at = (size_t)a.ny * ld + (side == 0 ? 0 : a.nxl + 1);
+                    *(volatile double *)(u1 + at) = u;
+                    *(volatile double *)(v1 + at) = v;
+                }
+            }
             asm volatile("bar.sync 1, %0;" ::"n"(kTmaConsumers * 32) : "memory");
             const double *inbox = p.inbox[ibuf][p.rank];
             const int ild = a.inbox_ld;
@@ -471,7 +586,7 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
         // (the last subcycle of evp, which also writes divu, shear, rdg_*, prs_sig, strint*, is a launch of
         // evp_subcycle_tma_kernel<true> after this kernel: a second instantiation of the sweep in here, inlined or
         // called, made the register allocator spill hundreds of bytes in the body that runs 119 times of 120)
-        sweep_item<false, REVISED>(p, ring, full_bar, empty_bar, stage, phase, strip, r0, rend, par, ibuf, warp, lane);
+        sweep_item<false, REVISED>(p, ring, full_bar, empty_bar, stage, phase, strip, r0, rend, par, ibuf, step, warp, lane);
 
         // ---- publish: this tile has finished subcycle `step` ----
         // Warps 1..3 only announce that their stores are issued (bar.arrive) and go on with the next item; warp 0
@@ -488,22 +603,24 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
             asm volatile("bar.sync 2, %0;" ::"n"(kTmaConsumers * 32) : "memory");
             if (lane == 0) {
                 const unsigned long long done = (unsigned long long)step + 1;
-                const bool west_edge = strip == 0 && p.pub_w, east_edge = strip == p.strips - 1 && p.pub_e;
                 const bool top = p.has_fold && rend >= a.ny;
                 if ((EVP_LOOP_EXP & 1) == 0) asm volatile("fence.proxy.async.global;" ::: "memory");
-                if ((EVP_LOOP_EXP & 32) == 0 && p.nranks > 1 && (west_edge || east_edge || top)) {
-                    st_release_u64<true>(p.tflag + item, done);          // stores into peer memory precede it
-                    if (west_edge) st_release_u64<true>(p.pub_w + chunk, done);
-                    if (east_edge) st_release_u64<true>(p.pub_e + chunk, done);
+                if (!p.ll_on && p.nranks > 1) {
+                    // (multi-rank without the mailbox: not a product configuration; kept for completeness)
+                    st_release_u64<true>(p.tflag + item, done);
+                    if (strip == 0 && p.pub_w) st_release_u64<true>(p.pub_w + chunk, done);
+                    if (strip == p.strips - 1 && p.pub_e) st_release_u64<true>(p.pub_e + chunk, done);
                 } else {
                     st_release_u64<false>(p.tflag + item, done);
-                    if ((EVP_LOOP_EXP & 32) && west_edge) st_release_u64<false>(p.pub_w + chunk, done);
-                    if ((EVP_LOOP_EXP & 32) && east_edge) st_release_u64<false>(p.pub_e + chunk, done);
                 }
                 if (top) {
+                    // top tiles stored into the tripole inboxes of other ranks (peer memory).  Each one releases at
+                    // gpu scope (above) before it counts itself; the one that completes the count takes a SYSTEM fence
+                    // and tells every rank -- release is cumulative, so all top tiles' inbox stores are covered: one
+                    // system-scope fence per rank and subcycle.
                     const unsigned long long ntop = (unsigned long long)p.item_count[2];
                     const unsigned long long n = atomicAdd(p.top_count, 1ull) + 1ull;
-                    if (n == ntop * done) {                              // the top tiles of this rank are complete
+                    if (n == ntop * done) {
                         __threadfence_system();
                         for (int r = 0; r < p.nranks; ++r) st_release_u64<true>(p.pub_top[r] + p.rank, done);
                     }
