@@ -73,23 +73,36 @@ def measured_peaks():
 
 
 class ClockSampler:
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+    """nvidia-smi in a loop beside the run.  It is started before the warm-up (a query takes tens of ms and a timed
+    region at N = 8 is only ~0.1-0.2 s long) and the samples are selected by their time stamps: those inside the
+    timed region, or -- when fewer than two fall inside it -- those of warm-up + timed region (same kernels, same load)."""
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, device=0):
         self.p = None
         self.device = device
+        self.t0 = self.t1 = None
 
     def start(self):
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.device), f"--query-gpu={self.Q}",
-                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                       "--format=csv,noheader,nounits", "-lms", "25"],
                                       stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except Exception:
             self.p = None
 
+    def mark_begin(self):
+        import datetime
+        self.t0 = datetime.datetime.now()
+
+    def mark_end(self):
+        import datetime
+        self.t1 = datetime.datetime.now()
+
     def stop(self):
+        import datetime
         if self.p is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.p.terminate()
@@ -98,22 +111,27 @@ class ClockSampler:
         except Exception:
             self.p.kill()
             out = ""
-        sm, mx, reasons = [], [], set()
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        rows = []
         for line in out.strip().splitlines():
             f = [x.strip() for x in line.split(",")]
-            if len(f) < 7:
+            if len(f) < 8:
                 continue
             try:
-                sm.append(float(f[0])); mx.append(float(f[1]))
+                ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f")
+                rows.append((ts, float(f[1]), float(f[2]), [n for n, v in zip(names, f[4:8]) if v.lower().startswith("active")]))
             except ValueError:
                 continue
-            for n, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
+        inside = [r for r in rows if self.t0 and self.t1 and self.t0 <= r[0] <= self.t1]
+        window = "timed region"
+        if len(inside) < 2:
+            inside = [r for r in rows if not self.t1 or r[0] <= self.t1]
+            window = "warm-up + timed region (the timed region is shorter than two nvidia-smi queries)"
+        sm = [r[1] for r in inside]
+        reasons = sorted({n for r in inside for n in r[3]})
         return {"sm_mhz": statistics.median(sm) if sm else None,
-                "sm_max_mhz": max(mx) if mx else None, "samples": len(sm),
-                "reasons": sorted(reasons)}
+                "sm_max_mhz": max(r[2] for r in inside) if inside else None, "samples": len(sm),
+                "window": window, "reasons": reasons}
 
 
 def pinned_like(a):
@@ -349,12 +367,13 @@ def measure(ctx, args, gridname, scenario, steps, warmup, do_e2e, do_parity, ref
 
     # ---- device-resident: W warm-up + K timed steps ----
     e.upload(inp, io0)
-    for _ in range(warmup):
-        e.compute(dt)
     sampler = ClockSampler(local_rank)
-    ctx.barrier()
     if rank == 0:
         sampler.start()
+    for _ in range(warmup):
+        e.compute(dt)
+    ctx.barrier()
+    sampler.mark_begin()
     t0 = time.perf_counter()
     dev_ms, loop_ms, launches = 0.0, 0.0, 0
     for _ in range(steps):
@@ -365,6 +384,7 @@ def measure(ctx, args, gridname, scenario, steps, warmup, do_e2e, do_parity, ref
         launches += st.kernel_launches
     ctx.barrier()
     wall_ms = (time.perf_counter() - t0) * 1e3
+    sampler.mark_end()
     clocks = sampler.stop() if rank == 0 else None
     st = e.stats()
     if os.environ.get("EVP_B200_TRACE") and st.loop_kernel_launches > 8:
