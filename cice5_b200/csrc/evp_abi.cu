@@ -19,6 +19,7 @@
 #include "evp_subcycle_tma.cuh"
 #include "evp_loop_tma.cuh"
 #include "evp_strength.cuh"
+#include "evp_remap.cuh"
 
 using namespace evp;
 
@@ -139,6 +140,10 @@ struct evp_handle {
     double *itd = nullptr;
     evp_itd_t itd_cfg;
     bool itd_ready = false, strength_from_itd = false;
+    // horizontal transport, first stage (evp_gpu_set_transport_grid): dxu, dyu, HTN, HTE planes + the stop word
+    double *tr = nullptr;
+    int *tr_stop = nullptr;
+    int h_tr_stop = 0;
     bool have_ht = false;         // HTE / HTN were given: compact metric rows are possible
     evp_stats_t stats;
     unsigned long long h_counts[2];
@@ -472,6 +477,7 @@ int evp_gpu_finalize(evp_handle_t *h)
     for (auto &ev : h->ev) if (ev) cudaEventDestroy(ev);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     if (h->itd) cudaFree(h->itd);
+    if (h->tr) cudaFree(h->tr);
     if (h->stage) cudaFree(h->stage);
     if (h->arena) cudaFree(h->arena);
     for (void *p : h->pinned) cudaHostUnregister(p);
@@ -1530,6 +1536,139 @@ int evp_gpu_restart_fixup_group(evp_handle_t **hs, int n)
         if (rc2 != EVP_OK) rc = rc2;
     }
     return rc;
+}
+
+}  // extern "C"
+
+// ---- horizontal transport, first stage: departure points from the resident velocities -------------------
+namespace {
+// departure_points (source/ice_transport_remap.F90:1493-1670) into the work planes W_1 (dpx), W_2 (dpy), then the two
+// ghost-cell updates of horizontal_remap (:574-578)
+void build_departure(evp_handle *h, double dt, int midpt, std::vector<Op> &ops)
+{
+    Builder B{h, ops};
+    B.sync();                                                    // every rank has left its previous operation
+    B.op([h, dt, midpt](Launcher &L) {
+        DepartArgs a;
+        a.nxb = h->nxb; a.nyb = h->nyb; a.ld = h->ld; a.dt = dt; a.midpt = midpt;
+        a.u = h->plane(h->parity ? S_UB : S_UA); a.v = h->plane(h->parity ? S_VB : S_VA);
+        a.dxu = h->tr; a.dyu = h->tr + h->plane_elems; a.htn = h->tr + 2 * h->plane_elems; a.hte = h->tr + 3 * h->plane_elems;
+        a.dpx = h->plane(W_1); a.dpy = h->plane(W_2); a.stop = h->tr_stop;
+        CK(cudaMemsetAsync(h->tr_stop, 0, sizeof(int), L.s()));
+        departure_first_kernel<<<grid2d(h), 128, 0, L.s()>>>(a);
+        departure_midpt_kernel<<<grid2d(h), 128, 0, L.s()>>>(a);
+        L.n += 2;
+        CK(cudaGetLastError());
+        return EVP_OK;
+    });
+    B.halo(W_1, 1, -1.0, 0.0);                                   // ice_HaloUpdate(dpx, NEcorner, vector)
+    B.halo(W_2, 1, -1.0, 0.0);
+    B.sync();                                                    // inbox buffers are free again
+}
+int finish_departure(evp_handle *h)
+{
+    CK(cudaMemcpyAsync(&h->h_tr_stop, h->tr_stop, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(&h->h_error, h->dev_error(), sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (h->h_error) {
+        snprintf(g_cuda_err, sizeof(g_cuda_err), "halo wait timed out: a peer rank did not arrive");
+        return EVP_ERR_PEER;
+    }
+    return EVP_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int evp_gpu_set_transport_grid(evp_handle_t *h, const evp_transport_grid_t *g)
+{
+    if (!h || !g || !g->dxu || !g->dyu || !g->HTN || !g->HTE) return EVP_ERR_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    if (!h->tr) {
+        CK(cudaMalloc(&h->tr, 4 * h->plane_elems * sizeof(double) + 256));
+        CK(cudaMemset(h->tr, 0, 4 * h->plane_elems * sizeof(double) + 256));
+        h->tr_stop = reinterpret_cast<int *>(h->tr + 4 * h->plane_elems);
+    }
+    const double *src[4] = {g->dxu, g->dyu, g->HTN, g->HTE};
+    for (int q = 0; q < 4; ++q) TRY(h2d_any(h, h->tr + (size_t)q * h->plane_elems, src[q], 0));
+    TRY(h2d_flush(h));
+    CK(cudaStreamSynchronize(h->stream));
+    return EVP_OK;
+}
+
+int evp_gpu_departure_points_compute(evp_handle_t *h, double dt, int l_dp_midpt)
+{
+    if (!h || !(dt > 0.0)) return EVP_ERR_ARG;
+    if (!h->tr || !h->uploaded || !h->peers_set) return EVP_ERR_STATE;
+    CK(cudaSetDevice(h->cfg.device));
+    std::vector<Op> ops;
+    build_departure(h, dt, l_dp_midpt ? 1 : 0, ops);
+    Launcher L{h};
+    for (const Op &op : ops) {
+        if (op.sync) { TRY(launch_signal(L)); TRY(launch_wait(L)); }
+        else TRY(op.fn(L));
+    }
+    return finish_departure(h);
+}
+
+// all ranks of a one-device group on one stream, steps interleaved (see evp_gpu_compute_group)
+int evp_gpu_departure_points_group(evp_handle_t **hs, int n, double dt, int l_dp_midpt)
+{
+    if (!hs || n < 1 || n > kMaxRanks || !(dt > 0.0)) return EVP_ERR_ARG;
+    for (int r = 0; r < n; ++r) {
+        if (!hs[r] || hs[r]->cfg.nranks != n || hs[r]->cfg.rank != r) return EVP_ERR_ARG;
+        if (!hs[r]->tr || !hs[r]->uploaded || !hs[r]->peers_set) return EVP_ERR_STATE;
+        if (hs[r]->cfg.device != hs[0]->cfg.device) return EVP_ERR_UNSUPPORTED;
+    }
+    CK(cudaSetDevice(hs[0]->cfg.device));
+    std::vector<std::vector<Op>> P(n);
+    std::vector<Launcher> L;
+    for (int r = 0; r < n; ++r) {
+        CK(cudaStreamSynchronize(hs[r]->stream));
+        hs[r]->stream = hs[0]->own_stream;
+        build_departure(hs[r], dt, l_dp_midpt ? 1 : 0, P[r]);
+        L.push_back(Launcher{hs[r]});
+    }
+    int rc = EVP_OK;
+    for (size_t i = 0; i < P[0].size() && rc == EVP_OK; ++i) {
+        if (P[0][i].sync) {
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = launch_signal(L[r]);
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = launch_wait(L[r]);
+        } else {
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = P[r][i].fn(L[r]);
+        }
+    }
+    for (int r = 0; r < n; ++r) {
+        const int rc2 = rc == EVP_OK ? finish_departure(hs[r]) : rc;
+        hs[r]->stream = hs[r]->own_stream;
+        if (rc2 != EVP_OK) rc = rc2;
+    }
+    return rc;
+}
+
+int evp_gpu_departure_points_fetch(evp_handle_t *h, double *dpx, double *dpy, int *l_stop, int *istop, int *jstop)
+{
+    if (!h) return EVP_ERR_ARG;
+    if (!h->tr) return EVP_ERR_STATE;
+    CK(cudaSetDevice(h->cfg.device));
+    D2HBatch B{h, {}};
+    h->batch_dst.clear();
+    TRY(B.r8(W_1, dpx));
+    TRY(B.r8(W_2, dpy));
+    TRY(B.flush());
+    CK(cudaStreamSynchronize(h->stream));
+    const int code = h->h_tr_stop;                               // 1 + (j-1)*nxb + (i-1), Fortran i, j of the block
+    if (l_stop) *l_stop = code != 0;
+    if (istop) *istop = code ? (code - 1) % h->nxb + 1 : 0;
+    if (jstop) *jstop = code ? (code - 1) / h->nxb + 1 : 0;
+    return EVP_OK;
+}
+
+int evp_gpu_departure_points(evp_handle_t *h, double dt, int l_dp_midpt, double *dpx, double *dpy, int *l_stop, int *istop,
+                             int *jstop)
+{
+    TRY(evp_gpu_departure_points_compute(h, dt, l_dp_midpt));
+    return evp_gpu_departure_points_fetch(h, dpx, dpy, l_stop, istop, jstop);
 }
 
 int evp_gpu_principal_stress(evp_handle_t *h, double *sig1, double *sig2)

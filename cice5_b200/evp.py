@@ -76,7 +76,8 @@ EXPORTS = ("evp_gpu_init", "evp_gpu_set_grid", "evp_gpu_run", "evp_gpu_upload", 
            "evp_gpu_last_cuda_error", "evp_gpu_device_count", "evp_gpu_get_trace", "evp_gpu_upload_itd",
            "evp_gpu_principal_stress", "evp_gpu_pin_host_arrays", "evp_gpu_set_resident",
            "evp_gpu_invalidate_state", "evp_gpu_restart_fixup", "evp_gpu_restart_fixup_group",
-           "evp_gpu_principal_stress_static")
+           "evp_gpu_principal_stress_static", "evp_gpu_set_transport_grid", "evp_gpu_departure_points_compute",
+           "evp_gpu_departure_points_group", "evp_gpu_departure_points_fetch", "evp_gpu_departure_points")
 STATIC_MAX_CELLS = 131072       # EVP_STATIC_MAX_CELLS of include/evp_b200.h
 
 # download groups of the resident-state protocol (include/evp_b200.h)
@@ -286,6 +287,25 @@ class EvpGpu:
         """What restartfile does to freshly read stresses (ice_restart_driver.F90:370-394,431-466), in place."""
         self._check(self.lib.evp_gpu_restart_fixup(self._h))
 
+    def set_transport_grid(self, f):
+        """dxu, dyu, HTN, HTE of this block (evp_gpu_set_transport_grid): needed once before departure_points."""
+        g = (_DP * 4)(_dp(f["dxu"]), _dp(f["dyu"]), _dp(f["HTN"]), _dp(f["HTE"]))
+        self._keep.append([f[k] for k in ("dxu", "dyu", "HTN", "HTE")])
+        self._check(self.lib.evp_gpu_set_transport_grid(self._h, g))
+
+    def departure_points_fetch(self):
+        dpx, dpy = np.zeros(self.shape), np.zeros(self.shape)
+        ls, i_s, j_s = C.c_int(0), C.c_int(0), C.c_int(0)
+        self._check(self.lib.evp_gpu_departure_points_fetch(self._h, _dp(dpx), _dp(dpy), C.byref(ls), C.byref(i_s),
+                                                            C.byref(j_s)))
+        return dpx, dpy, bool(ls.value), i_s.value, j_s.value
+
+    def departure_points(self, dt, l_dp_midpt=True):
+        """departure_points (source/ice_transport_remap.F90:1493-1670) + the ghost update of dpx, dpy, from the resident
+        uvel, vvel.  Returns (dpx, dpy, l_stop, istop, jstop)."""
+        self._check(self.lib.evp_gpu_departure_points_compute(self._h, C.c_double(dt), C.c_int(int(l_dp_midpt))))
+        return self.departure_points_fetch()
+
     def stats(self) -> Stats:
         st = Stats()
         self._check(self.lib.evp_gpu_get_stats(self._h, C.byref(st)))
@@ -421,6 +441,19 @@ class EvpGroup:
         for k in out:
             if out[k] is not None:
                 out[k][...] = self._fx.unslab([p[1][k] for p in parts])
+
+    def set_transport_grid(self, f):
+        for r, e in enumerate(self.ranks):
+            e.set_transport_grid(self._slabs({k: f[k] for k in ("dxu", "dyu", "HTN", "HTE")}, r))
+
+    def departure_points(self, dt, l_dp_midpt=True):
+        """All ranks; returns the global dpx, dpy and the per-rank (l_stop, istop, jstop)."""
+        arr = (C.c_void_p * self.n)(*[e._h for e in self.ranks])
+        self.ranks[0]._check(self.ranks[0].lib.evp_gpu_departure_points_group(arr, self.n, C.c_double(dt),
+                                                                              C.c_int(int(l_dp_midpt))))
+        parts = [e.departure_points_fetch() for e in self.ranks]
+        return (self._fx.unslab([p[0] for p in parts]), self._fx.unslab([p[1] for p in parts]),
+                [p[2:] for p in parts])
 
     def restart_fixup(self):
         arr = (C.c_void_p * self.n)(*[e._h for e in self.ranks])

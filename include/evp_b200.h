@@ -179,6 +179,29 @@ int evp_gpu_restart_fixup(evp_handle_t *h);
 /* the same for the ranks of a one-device group (see evp_gpu_compute_group) */
 int evp_gpu_restart_fixup_group(evp_handle_t **handles, int n);
 
+/* Horizontal transport, first stage: departure_points (source/ice_transport_remap.F90:1493-1670)
+ * from the device-resident uvel, vvel of the last evp -- what horizontal_remap does first after evp in step_dynamics
+ * (source/ice_step_mod.F90:1126-1130, ice_transport_remap.F90:541-550) -- followed by the ghost-cell updates of dpx, dpy
+ * (ice_HaloUpdate, NE corner, vector; :574-578).  The velocities do not leave the device in between.
+ *   set_transport_grid: dxu, dyu, HTN, HTE (source/ice_grid.F90:48-52) of this task's block, once.
+ *   compute: dt = the transport time step; l_dp_midpt = the reference's parameter (ice_transport_driver.F90:51, .true.).
+ *            With several ranks every rank calls it (it contains halo exchanges).  The results stay on the device
+ *            (work planes that the next evp / principal_stress call reuses).
+ *   fetch:   dpx, dpy (whole block incl. ghost cells; NULL = skip) and what the reference reports on failure: l_stop,
+ *            and istop, jstop = block indices (1-based) of the last cell, in the reference's loop order, whose departure
+ *            point lies more than one cell away.  On l_stop the reference aborts (abort_ice, :558); dpx, dpy then hold the
+ *            first-order estimate on the physical cells and their ghost cells are not meaningful.
+ *   evp_gpu_departure_points = compute + fetch. */
+typedef struct {
+    const double *dxu, *dyu, *HTN, *HTE;
+} evp_transport_grid_t;
+int evp_gpu_set_transport_grid(evp_handle_t *h, const evp_transport_grid_t *g);
+int evp_gpu_departure_points_compute(evp_handle_t *h, double dt, int l_dp_midpt);
+int evp_gpu_departure_points_group(evp_handle_t **handles, int n, double dt, int l_dp_midpt);
+int evp_gpu_departure_points_fetch(evp_handle_t *h, double *dpx, double *dpy, int *l_stop, int *istop, int *jstop);
+int evp_gpu_departure_points(evp_handle_t *h, double dt, int l_dp_midpt, double *dpx, double *dpy, int *l_stop, int *istop,
+                             int *jstop);
+
 /* Several ranks driven by one host thread (handles of ranks 0..n-1 on ONE device, e.g. tests with
  * fewer GPUs than ranks): steps are interleaved on one stream so that no kernel ever waits. */
 int evp_gpu_compute_group(evp_handle_t **handles, int n, double dt);

@@ -59,7 +59,7 @@ class Stats(C.Structure):
 def build(force: bool = False) -> str:
     if force or not os.path.exists(_SO) or \
             os.path.getmtime(_SO) < max(os.path.getmtime(os.path.join(_HERE, f))
-                                        for f in ("evp_oracle.c", "strength_oracle.c", "strength_oracle.h",
+                                        for f in ("evp_oracle.c", "strength_oracle.c", "strength_oracle.h", "remap_oracle.c", "remap_oracle.h",
                                                   "../cice5_b200/csrc/evp_exp.h")):
         subprocess.run(["make", "-C", _HERE] + (["-B"] if force else []), check=True,
                        stdout=subprocess.DEVNULL)
@@ -208,3 +208,17 @@ def cr_exp(x):
     y = np.empty_like(x)
     lib().strength_oracle_cr_exp(C.c_longlong(x.size), _dp(x), _dp(y))
     return y
+
+
+def departure_points(dom, dt, uvel, vvel, dxu, dyu, HTN, HTE, l_dp_midpt=True, no_halo=False, nslabs=1):
+    """departure_points (source/ice_transport_remap.F90:1493-1670) + the ghost update of dpx, dpy that
+    horizontal_remap issues (:574-578), on global-with-ghost planes.  Returns (dpx, dpy, l_stop, istop, jstop)."""
+    cfg = make_cfg(dom, 1, 1.0, nslabs)
+    dpx, dpy = np.empty_like(uvel), np.empty_like(uvel)
+    ls, i_s, j_s = C.c_int(0), C.c_int(0), C.c_int(0)
+    rc = lib().remap_oracle_departure_points(C.byref(cfg), C.c_double(dt), C.c_int(int(l_dp_midpt)), C.c_int(int(no_halo)),
+                                             _dp(uvel), _dp(vvel), _dp(dxu), _dp(dyu), _dp(HTN), _dp(HTE), _dp(dpx), _dp(dpy),
+                                             C.byref(ls), C.byref(i_s), C.byref(j_s))
+    if rc != 0:
+        raise RuntimeError(f"remap_oracle_departure_points failed with status {rc}")
+    return dpx, dpy, bool(ls.value), i_s.value, j_s.value

@@ -527,3 +527,56 @@ def test_resident_protocol_of_evp_gpu_run(dev):
         assert np.array_equal(phys(got.io["uvel"]), phys(ref.io["uvel"]))
     finally:
         e.close()
+
+
+# ---- horizontal transport, first stage: departure_points from the resident velocities --------
+def _departure_case(dev, grid, scenario, ndte, nranks, midpt, dt_scale=1.0):
+    """evp(dt), then departure_points on the device against the oracle's (itself pinned to the reference text), bit for
+    bit on every cell of the global block, ghost ring included (1 rank) / on the cells unslab keeps (several ranks)."""
+    case = fx.make_case(grid, scenario, ndte=ndte, dt=3600.0)
+    got = clone_case(case)
+    dt = case.dt * dt_scale
+    f = grid.f
+    if nranks == 1:
+        e = dev.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True)
+        try:
+            e.set_grid(f)
+            e.set_transport_grid(f)
+            e.evp(case.dt, got.inp, got.io, got.out)
+            dpx, dpy, l_stop, istop, jstop = e.departure_points(dt, midpt)
+        finally:
+            e.close()
+        stops = [(l_stop, istop, jstop)]
+    else:
+        g = dev.EvpGroup(case.dom, case.ndte, case.dt, nranks, strict=True)
+        try:
+            g.set_grid(f)
+            g.set_transport_grid(f)
+            g.evp(case.dt, got.inp, got.io, got.out)
+            dpx, dpy, stops = g.departure_points(dt, midpt)
+        finally:
+            g.close()
+    rx, ry, r_stop, ri, rj = orc.departure_points(case.dom, dt, got.io["uvel"], got.io["vvel"], f["dxu"], f["dyu"], f["HTN"],
+                                                  f["HTE"], l_dp_midpt=midpt)
+    assert np.abs(got.io["uvel"]).max() > 1e-3
+    return dpx, dpy, stops, rx, ry, (r_stop, ri, rj)
+
+
+@pytest.mark.parametrize("nranks,midpt", [(1, True), (1, False), (2, True), (4, True)])
+def test_departure_points_bitwise(dev, nranks, midpt):
+    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
+    dpx, dpy, stops, rx, ry, ref_stop = _departure_case(dev, grid, "full", 6, nranks, midpt)
+    assert not ref_stop[0] and all(not s[0] for s in stops)
+    assert np.array_equal(dpx, rx) and np.array_equal(dpy, ry)          # ghost ring included
+    assert np.abs(rx).max() > 10.0 and rx[-1, 1:-1].any()                # metres; the fold filled the north ghost row
+
+
+def test_departure_points_gx3_and_out_of_bounds(dev):
+    """Displaced-pole grid (no fold); then a time step so long that departure points leave their cells: l_stop and the
+    indices of the last offending cell as the reference reports them, first-order values on the physical cells."""
+    grid = fx.make_grid("gx3")
+    dpx, dpy, stops, rx, ry, ref_stop = _departure_case(dev, grid, "full", 6, 1, True)
+    assert not ref_stop[0] and np.array_equal(dpx, rx) and np.array_equal(dpy, ry)
+    dpx, dpy, stops, rx, ry, ref_stop = _departure_case(dev, grid, "full", 6, 1, True, dt_scale=4.0e3)
+    assert ref_stop[0] and stops[0] == ref_stop and ref_stop[1] > 1 and ref_stop[2] > 1
+    assert np.array_equal(phys(dpx), phys(rx)) and np.array_equal(phys(dpy), phys(ry))

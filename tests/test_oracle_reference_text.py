@@ -381,3 +381,22 @@ def test_whole_call_matches_reference_digests(name, nslabs):
     case, kw, layout, d = digest_case(name)
     orc.run_case(case, nslabs=nslabs, **kw)
     check_digests(case, layout, d)
+
+
+# ---- horizontal transport, first stage: departure_points against the reference text ----------
+@pytest.mark.parametrize("name", ["slow_mid", "slow_first", "fast_mid", "stop"])
+def test_departure_points_oracle_reproduces_reference_text_bitwise(name):
+    """oracle/remap_oracle.c == source/ice_transport_remap.F90:1493-1670 executed mechanically
+    (tests/golden/make_remap_vectors.py): dpx, dpy on every cell of the block (ghost cells: the routine's own zeros),
+    l_stop, istop, jstop -- first-order and midpoint-corrected points, cells at rest, and the out-of-bounds return."""
+    from cice5_b200 import fixtures as fx
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_remap_vectors.npz"))
+    nxb, nyb = int(z["nxb"]), int(z["nyb"])
+    get = lambda k: np.ascontiguousarray(z[f"{name}/{k}"])
+    dom = fx.Domain(nx=nxb - 2, ny=nyb - 2, ew_cyclic=False, ns_open=True, name="block")
+    dpx, dpy, l_stop, istop, jstop = orc.departure_points(dom, float(z[f"{name}/dt"]), get("uvel"), get("vvel"), get("dxu"),
+                                                         get("dyu"), get("HTN"), get("HTE"),
+                                                         l_dp_midpt=bool(z[f"{name}/l_dp_midpt"]), no_halo=True)
+    assert np.array_equal(dpx, get("out/dpx")) and np.array_equal(dpy, get("out/dpy"))
+    assert (int(l_stop), istop, jstop) == (int(z[f"{name}/out/l_stop"]), int(z[f"{name}/out/istop"]), int(z[f"{name}/out/jstop"]))
+    assert (name == "stop") == l_stop and np.abs(dpx).max() > 100.0
