@@ -42,12 +42,6 @@
 namespace evp {
 
 constexpr int kItemFold = 0x20000000;        // tag of the fold item of a subcycle
-// timing experiments (bit mask, never the product): 1 no writer-side proxy fence, 2 no reader-side proxy fence,
-// 4 no dependency polls at all (wrong answers at N > 1 / small grids)
-#ifndef EVP_LOOP_EXP
-#define EVP_LOOP_EXP 0
-#endif
-
 struct LoopTmaArgs {
     LoopArgs a;                  // geometry, constants, last-subcycle outputs, uvel_init (state pointers unused)
     int plane_state[2];          // first plane of ping-pong copy A / B
@@ -431,7 +425,7 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
             if (k > 0) {
                 // dependencies: the 3 x 3 tiles around this one have finished subcycle k-1 (lanes 0..8 poll
                 // one counter each), and, for a tile that reads rows ny / ny+1, the fold of k-1 (lane 9)
-                if ((EVP_LOOP_EXP & 4) == 0 && lane < 9) {
+                if (lane < 9) {
                     bool remote;
                     const unsigned long long *f = neighbour_counter(p, strip + lane % 3 - 1, chunk + lane / 3 - 1, remote);
                     if (f) {
@@ -466,7 +460,7 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
                 __syncwarp();
                 // the planes were written through the generic proxy (other SMs, other GPUs); TMA reads them
                 // through the async proxy
-                if ((EVP_LOOP_EXP & 2) == 0) asm volatile("fence.proxy.async.global;" ::: "memory");
+                asm volatile("fence.proxy.async.global;" ::: "memory");
             }
             if (lane == 0) {
                 const int par = p.parity0 ^ (k & 1);
@@ -604,7 +598,7 @@ evp_loop_tma_kernel(const __grid_constant__ CUtensorMap mapS, const __grid_const
             if (lane == 0) {
                 const unsigned long long done = (unsigned long long)step + 1;
                 const bool top = p.has_fold && rend >= a.ny;
-                if ((EVP_LOOP_EXP & 1) == 0) asm volatile("fence.proxy.async.global;" ::: "memory");
+                asm volatile("fence.proxy.async.global;" ::: "memory");
                 if (!p.ll_on && p.nranks > 1) {
                     // (multi-rank without the mailbox: not a product configuration; kept for completeness)
                     st_release_u64<true>(p.tflag + item, done);

@@ -4,8 +4,8 @@ bit: tripole / displaced-pole / closed-basin grids of 4..78 x 4..29 cells, wet o
 no ice, 1-4 ranks, classic / revised EVP, both tilt modes, a turning angle, the coupler's wind stress (strax/stray).
 
     python tools/fuzz_on_emulator.py SEED [tma|sweep] [CASES]
-    EVP_B200_FOLD=kernel EVP_B200_EARLY_D2H=1 FUZZ_DEFINES="-DEVP_TMA_MERGE_UV=1 -DEVP_TMA_STATIC_FIRST=1" \\
-        python tools/fuzz_on_emulator.py 5 tma 40        # all experiments at once (ranks on threads)
+    FUZZ_THREADS=1 python tools/fuzz_on_emulator.py 5 tma 40      # ranks on threads: the persistent loop kernel with its
+                                                                  # tile counters and ghost mailbox between ranks
 """
 import sys, time, os, traceback
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -29,7 +29,7 @@ def on_threads(ranks, dt):
     [x.start() for x in th]; [x.join() for x in th]
     if errs: raise errs[0]
 with emu.patched(kernel=kernel, defines=defines) as evp:
-    if os.environ.get("EVP_B200_FOLD") == "kernel": evp.compute_group = on_threads
+    if os.environ.get("FUZZ_THREADS"): evp.compute_group = on_threads
     for it in range(int(sys.argv[3]) if len(sys.argv) > 3 else 30):
         tripole = rng.random() < 0.6
         nx = int(rng.integers(2, 40)) * 2 if tripole else int(rng.integers(4, 70))

@@ -2,8 +2,8 @@
 # One 8-GPU box call: strong-scaling sweep with the device timeline on, results under gpurun_out/.
 #   /usr/local/graft/bin/gpurun --gpus 8 --timeout 400 -- 'bash tools/scaling_sweep.sh "8 4 2 1" [extra bench flags]'
 # then here:  python tools/summarise_trace.py gpurun_out/scale_n*.err
-# variants: prefix the command with EVP_B200_FOLD=kernel (tripole fold inside the subcycle kernel) and / or
-# EVP_B200_LIB=cice5_b200/lib/exp_mergeuv.so; both are bitwise equal to the default on the host emulator
+# variants: prefix the command with EVP_B200_LOOP=0 (a launch per subcycle; the device timeline needs it) or
+# EVP_B200_LIB=cice5_b200/lib/exp_<name>.so (python -m cice5_b200.build --variant <name> -D...)
 NS=${1:-"8 4 2 1"}
 shift
 export EVP_B200_TRACE=1
