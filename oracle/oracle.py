@@ -210,6 +210,32 @@ def cr_exp(x):
     return y
 
 
+def construct_fields(dom, tracer_type, depend, has_dependents, hm, xav, yav, xxav, yyav, mm, tm, no_halo=False, nslabs=1,
+                     masks=False):
+    """make_masks + construct_fields + limited_gradient (source/ice_transport_remap.F90:867-1484) for categories
+    0..ncat, then (unless no_halo) the ghost updates of horizontal_remap (:579-584, :616-621).  mm: (ncat+1, ny+2, nx+2);
+    tm: (ncat, ntrace, ny+2, nx+2).  Returns a dict mc, mx, my, tc, tx, ty (+ mmask, tmask, icells with masks=True)."""
+    cfg = make_cfg(dom, 1, 1.0, nslabs)
+    mm, tm = np.ascontiguousarray(mm, dtype=np.float64), np.ascontiguousarray(tm, dtype=np.float64)
+    ncat, ntrace = tm.shape[0], tm.shape[1]
+    assert mm.shape[0] == ncat + 1
+    ia = lambda v: np.ascontiguousarray(v, dtype=np.int32)
+    tt, dp, hd = ia(tracer_type), ia(depend), ia(has_dependents)
+    o = {k: np.full(mm.shape, np.nan) for k in ("mc", "mx", "my")}
+    o.update({k: np.full(tm.shape, np.nan) for k in ("tc", "tx", "ty")})
+    if masks:
+        o["mmask"], o["tmask"] = np.full(mm.shape, np.nan), np.full(tm.shape, np.nan)
+        o["icells"] = np.zeros(ncat + 1, dtype=np.int32)
+    rc = lib().remap_oracle_construct_fields(
+        C.byref(cfg), C.c_int(ncat), C.c_int(ntrace), _ip(tt), _ip(dp), _ip(hd), C.c_int(int(no_halo)), _dp(hm), _dp(xav),
+        _dp(yav), _dp(xxav), _dp(yyav), _dp(mm), _dp(tm), _dp(o["mc"]), _dp(o["mx"]), _dp(o["my"]), _dp(o["tc"]),
+        _dp(o["tx"]), _dp(o["ty"]), _dp(o["mmask"]) if masks else None, _dp(o["tmask"]) if masks else None,
+        _ip(o["icells"]) if masks else None)
+    if rc != 0:
+        raise RuntimeError(f"remap_oracle_construct_fields failed with status {rc}")
+    return o
+
+
 def departure_points(dom, dt, uvel, vvel, dxu, dyu, HTN, HTE, l_dp_midpt=True, no_halo=False, nslabs=1):
     """departure_points (source/ice_transport_remap.F90:1493-1670) + the ghost update of dpx, dpy that
     horizontal_remap issues (:574-578), on global-with-ghost planes.  Returns (dpx, dpy, l_stop, istop, jstop)."""

@@ -1,5 +1,5 @@
-/* remap_oracle.h -- CPU restatement of the first stage of CICE5's horizontal transport:
- * departure_points (source/ice_transport_remap.F90:1493-1670) and the ghost-cell update of dpx, dpy that
+/* remap_oracle.h -- CPU restatement of the first stages of CICE5's horizontal transport:
+ * make_masks / construct_fields / limited_gradient (:867-1484), departure_points (source/ice_transport_remap.F90:1493-1670) and the ghost-cell update of dpx, dpy that
  * horizontal_remap issues after it (:574-578).  TEST INFRASTRUCTURE (see evp_oracle.h); pinned bit for bit to the
  * reference's own text executed mechanically (tests/golden/make_remap_vectors.py, tests/test_oracle_reference_text.py). */
 #ifndef REMAP_ORACLE_H
@@ -17,6 +17,18 @@ int remap_oracle_departure_points(const evp_oracle_cfg *cfg, double dt, int l_dp
                                   const double *uvel, const double *vvel, const double *dxu, const double *dyu,
                                   const double *HTN, const double *HTE, double *dpx, double *dpy,
                                   int *l_stop, int *istop, int *jstop);
+
+/* Second stage: make_masks (:867-1015) + construct_fields (:1024-1340) + limited_gradient (:1348-1484) for the
+ * open-water category 0 and the ice categories 1..ncat, as horizontal_remap calls them (:462-511), then -- unless
+ * no_halo -- the ghost-cell updates of mc, mx, my, tc, tx, ty (:579-584, :616-621; maskhalo_remap = .false.).
+ * mm: ncat+1 planes (category 0 first); tm, tc, tx, ty: planes [n-1][nt-1], n = 1..ncat, nt = 1..ntrace, i.e. the
+ * reference's (nx_block, ny_block, ntrace, ncat).  tracer_type / depend / has_dependents: init_transport's arrays
+ * (source/ice_transport_driver.F90:82-118), depend 1-based.  mmask_out / tmask_out / icells_out may be NULL. */
+int remap_oracle_construct_fields(const evp_oracle_cfg *cfg, int ncat, int ntrace, const int *tracer_type,
+                                  const int *depend, const int *has_dependents, int no_halo, const double *hm,
+                                  const double *xav, const double *yav, const double *xxav, const double *yyav,
+                                  const double *mm, const double *tm, double *mc, double *mx, double *my, double *tc,
+                                  double *tx, double *ty, double *mmask_out, double *tmask_out, int *icells_out);
 
 #ifdef __cplusplus
 }

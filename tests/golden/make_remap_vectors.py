@@ -33,6 +33,87 @@ def load():
     return m
 
 
+# ---- second stage: make_masks + construct_fields (+ limited_gradient), :867-1484 ------------------------------------
+NCAT = 2
+TRACER_TYPE = [1, 1, 1, 2, 2, 3]          # hice, hsno, Tsfc-like, qice-like (on hice), qsno-like (on hsno), a type 3
+DEPEND = [0, 0, 0, 1, 2, 4]
+
+
+def load_fields():
+    def lines(rel):
+        return fe.preprocess(open(os.path.join(REF, rel)).read(), ())
+    ns = {}
+    fe.parse_parameters(lines("drivers/cice/ice_constants.F90"), ns)
+    ns.update(nu_diag=6, my_task=0, ncat=NCAT)
+    m = fe.Module(ns)
+    m.load(lines("source/ice_transport_remap.F90"), ["make_masks", "construct_fields", "limited_gradient"])
+    return m
+
+
+def has_dependents(depend):
+    """init_transport, source/ice_transport_driver.F90:112-118"""
+    h = [False] * len(depend)
+    for d in depend:
+        if d > 0:
+            h[d - 1] = True
+    return h
+
+
+def fields_block(seed, open_frac):
+    r = np.random.default_rng(seed)
+    sh = (NYB, NXB)
+    nt = len(TRACER_TYPE)
+    hm = (r.uniform(0, 1, sh) < 0.85).astype(float)
+    mm = r.uniform(0.05, 1.0, (NCAT + 1,) + sh)
+    mm[r.uniform(0, 1, mm.shape) < open_frac] = 0.0            # no ice of this category
+    mm[r.uniform(0, 1, mm.shape) < 0.05] = 5.0e-12             # below puny
+    mm *= hm                                                   # no ice on land
+    tm = r.uniform(0.1, 2.0, (NCAT, nt) + sh)
+    tm[:, 2] = -r.uniform(0.5, 20.0, (NCAT,) + sh)             # a temperature: negative values
+    tm[r.uniform(0, 1, tm.shape) < 0.12] = 0.0                 # tracer absent (snow-free ice ...)
+    tm[r.uniform(0, 1, tm.shape) < 0.03] = 3.0e-12
+    flat = r.uniform(0, 1, sh) < 0.15                          # locally uniform fields: zero gradients, 0/0 guards
+    tm[:, :, flat] = 0.7
+    return {"hm": hm, "xav": r.uniform(-0.04, 0.04, sh), "yav": r.uniform(-0.04, 0.04, sh),
+            "xxav": r.uniform(0.07, 0.10, sh), "yyav": r.uniform(0.07, 0.10, sh), "mm": mm, "tm": tm}
+
+
+def run_fields(m, d):
+    """make_masks, then construct_fields for the open-water category and each ice category, as horizontal_remap calls
+    them (:462-511).  Arrays: mm (ncat+1, NYB, NXB) = Fortran (nx_block, ny_block, 0:ncat); tm (ncat, ntrace, NYB, NXB) =
+    Fortran (nx_block, ny_block, ntrace, ncat).  Outputs start with garbage."""
+    nt = len(TRACER_TYPE)
+    hd = has_dependents(DEPEND)
+    geo = dict(nx_block=NXB, ny_block=NYB, ilo=2, ihi=NXB - 1, jlo=2, jhi=NYB - 1, nghost=1, ntrace=nt)
+    icells = fe.FArr.from_numpy(np.zeros(NCAT + 1, dtype=np.int64), los=[0])
+    indxi = fe.FArr.from_numpy(np.zeros((NCAT + 1, NXB * NYB), dtype=np.int64), los=[1, 0])
+    indxj = fe.FArr.from_numpy(np.zeros((NCAT + 1, NXB * NYB), dtype=np.int64), los=[1, 0])
+    mm = fe.FArr.from_numpy(d["mm"], los=[1, 1, 0])
+    tm = fe.FArr.from_numpy(d["tm"])
+    mmask = fe.FArr.from_numpy(np.full((NCAT + 1, NYB, NXB), -7.0), los=[1, 1, 0])
+    tmask = fe.FArr.from_numpy(np.full((NCAT, nt, NYB, NXB), -7.0))
+    hdf = fe.FArr.from_numpy(np.array(hd))
+    m.call("make_masks", has_dependents=hdf, icells=icells, indxi=indxi, indxj=indxj, mm=mm, mmask=mmask, tm=tm,
+           tmask=tmask, **geo)
+    g = {k: fe.FArr.from_numpy(d[k]) for k in ("hm", "xav", "yav", "xxav", "yyav")}
+    mc, mx, my = (fe.FArr.from_numpy(np.full((NCAT + 1, NYB, NXB), -7.0), los=[1, 1, 0]) for _ in range(3))
+    tc, tx, ty = (fe.FArr.from_numpy(np.full((NCAT, nt, NYB, NXB), -7.0)) for _ in range(3))
+    tt, dep = fe.FArr.from_numpy(np.array(TRACER_TYPE)), fe.FArr.from_numpy(np.array(DEPEND))
+    S = slice(None)
+    m.call("construct_fields", tracer_type=tt, depend=dep, has_dependents=hdf, icells=icells(0), indxi=indxi(S, 0),
+           indxj=indxj(S, 0), mm=mm(S, S, 0), mc=mc(S, S, 0), mx=mx(S, S, 0), my=my(S, S, 0), mmask=mmask(S, S, 0),
+           **g, **geo)
+    for n in range(1, NCAT + 1):
+        m.call("construct_fields", tracer_type=tt, depend=dep, has_dependents=hdf, icells=icells(n),
+               indxi=indxi(S, n), indxj=indxj(S, n), mm=mm(S, S, n), mc=mc(S, S, n), mx=mx(S, S, n), my=my(S, S, n),
+               mmask=mmask(S, S, n), tm=tm(S, S, S, n), tc=tc(S, S, S, n), tx=tx(S, S, S, n), ty=ty(S, S, S, n),
+               tmask=tmask(S, S, S, n), **g, **geo)
+    out = {k: v.to_numpy() for k, v in (("mc", mc), ("mx", mx), ("my", my), ("tc", tc), ("tx", tx), ("ty", ty),
+                                         ("mmask", mmask), ("tmask", tmask))}
+    out["icells"] = icells.to_numpy()
+    return out
+
+
 def block(seed, speed):
     r = np.random.default_rng(seed)
     sh = (NYB, NXB)
@@ -74,6 +155,19 @@ def main():
             out[f"{name}/out/{k}"] = v
         print(name, "l_stop", res["l_stop"], "istop, jstop", res["istop"], res["jstop"],
               "max |dpx|", float(np.abs(res["dpx"]).max()))
+    mf = load_fields()
+    out.update(ncat=NCAT, tracer_type=np.array(TRACER_TYPE), depend=np.array(DEPEND),
+               has_dependents=np.array(has_dependents(DEPEND), dtype=np.int32))
+    for name, seed, open_frac in [("cf_pack", 21, 0.1), ("cf_edge", 22, 0.45)]:
+        d = fields_block(seed, open_frac)
+        res = run_fields(mf, d)
+        for k, v in d.items():
+            out[f"{name}/{k}"] = v
+        for k, v in res.items():
+            out[f"{name}/out/{k}"] = v
+        print(name, "icells", res["icells"], "max |mx|", float(np.abs(res["mx"]).max()), "max |tx|",
+              float(np.abs(res["tx"]).max()), "limited cells",
+              int(np.count_nonzero(res["tx"])))
     np.savez_compressed(OUT, **out)
     print("wrote", OUT)
 

@@ -400,3 +400,26 @@ def test_departure_points_oracle_reproduces_reference_text_bitwise(name):
     assert np.array_equal(dpx, get("out/dpx")) and np.array_equal(dpy, get("out/dpy"))
     assert (int(l_stop), istop, jstop) == (int(z[f"{name}/out/l_stop"]), int(z[f"{name}/out/istop"]), int(z[f"{name}/out/jstop"]))
     assert (name == "stop") == l_stop and np.abs(dpx).max() > 100.0
+
+
+@pytest.mark.parametrize("name", ["cf_pack", "cf_edge"])
+def test_construct_fields_oracle_reproduces_reference_text_bitwise(name):
+    """oracle/remap_oracle.c == make_masks + construct_fields + limited_gradient (source/ice_transport_remap.F90:867-1484)
+    executed mechanically for the open-water category and two ice categories with six tracers of all three types
+    (tests/golden/make_remap_vectors.py): masks, cell counts, mc, mx, my, tc, tx, ty on every cell of the block --
+    land, categories without ice, areas and tracers below puny, locally uniform fields."""
+    from cice5_b200 import fixtures as fx
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_remap_vectors.npz"))
+    nxb, nyb = int(z["nxb"]), int(z["nyb"])
+    get = lambda k: np.ascontiguousarray(z[f"{name}/{k}"])
+    dom = fx.Domain(nx=nxb - 2, ny=nyb - 2, ew_cyclic=False, ns_open=True, name="block")
+    o = orc.construct_fields(dom, z["tracer_type"], z["depend"], z["has_dependents"], get("hm"), get("xav"), get("yav"),
+                             get("xxav"), get("yyav"), get("mm"), get("tm"), no_halo=True, masks=True)
+    for k in ("mmask", "tmask", "icells", "mc", "mx", "my", "tc", "tx", "ty"):
+        want = get(f"out/{k}")
+        assert o[k].shape == want.shape and np.array_equal(o[k], want), k
+        if k != "icells":                                  # the sign of a zero too
+            assert np.array_equal(np.signbit(o[k]), np.signbit(want)), k
+    assert np.count_nonzero(o["tx"]) > 100 and np.count_nonzero(o["mx"]) > 30
+    lim = np.abs(o["tx"][:, 0]) > 0                        # the limiter bites somewhere and is idle somewhere
+    assert lim.any()
