@@ -144,6 +144,11 @@ struct evp_handle {
     double *tr = nullptr;
     int *tr_stop = nullptr;
     int h_tr_stop = 0;
+    // horizontal transport, field reconstruction (evp_gpu_set_transport_tracers): hm xav yav xxav yyav, mm(0:ncat),
+    // tm(ntrace, ncat), mc mx my (0:ncat), tc tx ty (ntrace, ncat) planes of the arena's pitch in one allocation
+    double *rc = nullptr;
+    ReconArgs rc_args;
+    bool rc_loaded = false;
     bool have_ht = false;         // HTE / HTN were given: compact metric rows are possible
     evp_stats_t stats;
     unsigned long long h_counts[2];
@@ -478,6 +483,7 @@ int evp_gpu_finalize(evp_handle_t *h)
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     if (h->itd) cudaFree(h->itd);
     if (h->tr) cudaFree(h->tr);
+    if (h->rc) cudaFree(h->rc);
     if (h->stage) cudaFree(h->stage);
     if (h->arena) cudaFree(h->arena);
     for (void *p : h->pinned) cudaHostUnregister(p);
@@ -873,13 +879,17 @@ struct Builder {
     // first_pair: kFirstPair3D for the levels of fld2 (ice_HaloUpdate3DR8), see fold_necorner_column
     void halo(int plane, int loc, double sgn, double fill, int first_pair = kFirstPair2D)
     {
+        halo_p(h->plane(plane), loc, sgn, fill, first_pair);
+    }
+    void halo_p(double *plane, int loc, double sgn, double fill, int first_pair = kFirstPair2D)
+    {
         evp_handle *hh = h;
         const int buf = (seq++) & 1;
         op([hh, plane, loc, buf](Launcher &L) {
             const Geom &g = hh->g;
             PushArgs pa;
             memset(&pa, 0, sizeof(pa));
-            pa.g = g; pa.ib = hh->ib; pa.plane = hh->plane(plane);
+            pa.g = g; pa.ib = hh->ib; pa.plane = plane;
             for (int r = 0; r < g.nranks; ++r) pa.inbox[r] = hh->inbox(buf, r);
             pa.west = hh->west_closed() ? -1 : hh->west();
             pa.east = hh->east_closed() ? -1 : hh->east();
@@ -893,7 +903,7 @@ struct Builder {
         op([hh, plane, loc, sgn, fill, buf, first_pair](Launcher &L) {
             const Geom &g = hh->g;
             const int na = g.nxl + 2 + g.ny;
-            halo_apply_kernel<<<(na + 255) / 256, 256, 0, L.s()>>>(hh->plane(plane), g, hh->ib, hh->inbox(buf), loc,
+            halo_apply_kernel<<<(na + 255) / 256, 256, 0, L.s()>>>(plane, g, hh->ib, hh->inbox(buf), loc,
                                                                 sgn, fill, hh->west_closed(), hh->east_closed(),
                                                                 first_pair);
             ++L.n;
@@ -1669,6 +1679,211 @@ int evp_gpu_departure_points(evp_handle_t *h, double dt, int l_dp_midpt, double 
 {
     TRY(evp_gpu_departure_points_compute(h, dt, l_dp_midpt));
     return evp_gpu_departure_points_fetch(h, dpx, dpy, l_stop, istop, jstop);
+}
+
+// ---- horizontal transport, field reconstruction: make_masks + construct_fields + the ghost-cell updates ----------
+}  // extern "C"
+namespace {
+// plane k of the reconstruction arena
+struct RcLayout {
+    int ncat, ntrace;
+    size_t geom(int k) const { return (size_t)k; }                                   // hm xav yav xxav yyav
+    size_t mm(int n) const { return 5 + (size_t)n; }
+    size_t tm(int k) const { return 5 + (size_t)(ncat + 1) + k; }                       // k = (n-1)*ntrace + nt
+    size_t mass(int f, int n) const { return tm(ncat * ntrace) + (size_t)f * (ncat + 1) + n; }           // f: mc mx my
+    size_t trc(int f, int k) const { return mass(3, 0) + (size_t)f * ncat * ntrace + k; }                // f: tc tx ty
+    size_t planes() const { return trc(3, 0); }
+};
+RcLayout rc_layout(const evp_handle *h) { return RcLayout{h->rc_args.ncat, h->rc_args.ntrace}; }
+
+// reconstruct_kernel, then ice_HaloUpdate of mc (center, scalar), mx, my (center, vector) and tc, tx, ty
+// (source/ice_transport_remap.F90:579-584, :616-621; maskhalo_remap = .false.)
+void build_reconstruct(evp_handle *h, std::vector<Op> &ops)
+{
+    Builder B{h, ops};
+    const RcLayout l = rc_layout(h);
+    B.sync();
+    B.op([h, l](Launcher &L) {
+        const dim3 grid((h->nxb + 127) / 128, h->nyb, l.ncat + 1);
+        reconstruct_kernel<<<grid, 128, 0, L.s()>>>(h->rc_args);
+        ++L.n;
+        CK(cudaGetLastError());
+        return EVP_OK;
+    });
+    auto pl = [h](size_t k) { return h->rc + k * h->plane_elems; };
+    for (int n = 0; n <= l.ncat; ++n) {
+        B.halo_p(pl(l.mass(0, n)), 0, 1.0, 0.0);
+        B.halo_p(pl(l.mass(1, n)), 0, -1.0, 0.0);
+        B.halo_p(pl(l.mass(2, n)), 0, -1.0, 0.0);
+    }
+    for (int k = 0; k < l.ncat * l.ntrace; ++k) {
+        B.halo_p(pl(l.trc(0, k)), 0, 1.0, 0.0);
+        B.halo_p(pl(l.trc(1, k)), 0, -1.0, 0.0);
+        B.halo_p(pl(l.trc(2, k)), 0, -1.0, 0.0);
+    }
+    B.sync();
+}
+int finish_ops(evp_handle *h)
+{
+    CK(cudaMemcpyAsync(&h->h_error, h->dev_error(), sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (h->h_error) {
+        snprintf(g_cuda_err, sizeof(g_cuda_err), "halo wait timed out: a peer rank did not arrive");
+        return EVP_ERR_PEER;
+    }
+    return EVP_OK;
+}
+}  // namespace
+extern "C" {
+
+int evp_gpu_set_transport_tracers(evp_handle_t *h, int ncat, int ntrace, const int *tracer_type, const int *depend,
+                                  const int *has_dependents, const double *hm, const double *xav, const double *yav,
+                                  const double *xxav, const double *yyav)
+{
+    if (!h || ncat < 1 || ntrace < 0 || !hm || !xav || !yav || !xxav || !yyav) return EVP_ERR_ARG;
+    if (ntrace > 0 && (!tracer_type || !depend || !has_dependents)) return EVP_ERR_ARG;
+    if (ntrace > kRemapMaxTrace) return EVP_ERR_TOO_LARGE;
+    ReconArgs a;
+    memset(&a, 0, sizeof(a));
+    int parents = 0;
+    for (int nt = 0; nt < ntrace; ++nt) {
+        const int ty = tracer_type[nt], d = depend[nt];
+        if (ty < 1 || ty > 3) return EVP_ERR_ARG;
+        a.ttype[nt] = (signed char)ty;
+        a.slot[nt] = -1;
+        if (ty == 1) {
+            if (has_dependents[nt]) {
+                if (parents == kRemapMaxParents) return EVP_ERR_TOO_LARGE;
+                a.slot[nt] = (signed char)parents++;
+            }
+        } else {
+            // the reference reads mtxav(:,:,depend(nt)) when it reaches tracer nt: the parent of a type-2 tracer is
+            // an earlier type-1 tracer flagged has_dependents (init_transport, ice_transport_driver.F90:90-118)
+            if (d < 1 || d > ntrace) return EVP_ERR_ARG;
+            if (ty == 2 && (d > nt || tracer_type[d - 1] != 1 || !has_dependents[d - 1])) return EVP_ERR_ARG;
+            a.parent[nt] = (unsigned char)(d - 1);
+        }
+    }
+    CK(cudaSetDevice(h->cfg.device));
+    const RcLayout l{ncat, ntrace};
+    if (h->rc && (h->rc_args.ncat != ncat || h->rc_args.ntrace != ntrace)) {
+        CK(cudaStreamSynchronize(h->stream));
+        CK(cudaFree(h->rc));
+        h->rc = nullptr;
+    }
+    if (!h->rc) {
+        CK(cudaMalloc(&h->rc, l.planes() * h->plane_elems * sizeof(double)));
+        CK(cudaMemset(h->rc, 0, l.planes() * h->plane_elems * sizeof(double)));
+    }
+    auto pl = [h](size_t k) { return h->rc + k * h->plane_elems; };
+    a.nxb = h->nxb; a.nyb = h->nyb; a.ld = h->ld; a.pe = h->plane_elems; a.ncat = ncat; a.ntrace = ntrace;
+    a.hm = pl(0); a.xav = pl(1); a.yav = pl(2); a.xxav = pl(3); a.yyav = pl(4);
+    a.mm = pl(l.mm(0)); a.tm = pl(l.tm(0));
+    a.mc = pl(l.mass(0, 0)); a.mx = pl(l.mass(1, 0)); a.my = pl(l.mass(2, 0));
+    a.tc = pl(l.trc(0, 0)); a.tx = pl(l.trc(1, 0)); a.ty = pl(l.trc(2, 0));
+    h->rc_args = a;
+    h->rc_loaded = false;
+    const double *src[5] = {hm, xav, yav, xxav, yyav};
+    for (int k = 0; k < 5; ++k) TRY(h2d_any(h, pl(k), src[k], 0));
+    TRY(h2d_flush(h));
+    CK(cudaStreamSynchronize(h->stream));
+    return EVP_OK;
+}
+
+int evp_gpu_construct_fields_upload(evp_handle_t *h, const double *mm, const double *tm)
+{
+    if (!h || !mm) return EVP_ERR_ARG;
+    if (!h->rc) return EVP_ERR_STATE;
+    const RcLayout l = rc_layout(h);
+    if (l.ntrace > 0 && !tm) return EVP_ERR_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    const size_t cells = (size_t)h->nxb * h->nyb;
+    auto pl = [h](size_t k) { return h->rc + k * h->plane_elems; };
+    for (int n = 0; n <= l.ncat; ++n) TRY(h2d_any(h, pl(l.mm(n)), mm + (size_t)n * cells, 0));
+    for (int k = 0; k < l.ncat * l.ntrace; ++k) TRY(h2d_any(h, pl(l.tm(k)), tm + (size_t)k * cells, 0));
+    TRY(h2d_flush(h));
+    CK(cudaStreamSynchronize(h->stream));                          // the host arrays may be reused
+    h->rc_loaded = true;
+    return EVP_OK;
+}
+
+int evp_gpu_construct_fields_compute(evp_handle_t *h)
+{
+    if (!h) return EVP_ERR_ARG;
+    if (!h->rc || !h->rc_loaded || !h->peers_set) return EVP_ERR_STATE;
+    CK(cudaSetDevice(h->cfg.device));
+    std::vector<Op> ops;
+    build_reconstruct(h, ops);
+    Launcher L{h};
+    for (const Op &op : ops) {
+        if (op.sync) { TRY(launch_signal(L)); TRY(launch_wait(L)); }
+        else TRY(op.fn(L));
+    }
+    return finish_ops(h);
+}
+
+// all ranks of a one-device group on one stream, steps interleaved (see evp_gpu_compute_group)
+int evp_gpu_construct_fields_group(evp_handle_t **hs, int n)
+{
+    if (!hs || n < 1 || n > kMaxRanks) return EVP_ERR_ARG;
+    for (int r = 0; r < n; ++r) {
+        if (!hs[r] || hs[r]->cfg.nranks != n || hs[r]->cfg.rank != r) return EVP_ERR_ARG;
+        if (!hs[r]->rc || !hs[r]->rc_loaded || !hs[r]->peers_set) return EVP_ERR_STATE;
+        if (hs[r]->cfg.device != hs[0]->cfg.device) return EVP_ERR_UNSUPPORTED;
+        if (hs[r]->rc_args.ncat != hs[0]->rc_args.ncat || hs[r]->rc_args.ntrace != hs[0]->rc_args.ntrace) return EVP_ERR_ARG;
+    }
+    CK(cudaSetDevice(hs[0]->cfg.device));
+    std::vector<std::vector<Op>> P(n);
+    std::vector<Launcher> L;
+    for (int r = 0; r < n; ++r) {
+        CK(cudaStreamSynchronize(hs[r]->stream));
+        hs[r]->stream = hs[0]->own_stream;
+        build_reconstruct(hs[r], P[r]);
+        L.push_back(Launcher{hs[r]});
+    }
+    int rc = EVP_OK;
+    for (size_t i = 0; i < P[0].size() && rc == EVP_OK; ++i) {
+        if (P[0][i].sync) {
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = launch_signal(L[r]);
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = launch_wait(L[r]);
+        } else {
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = P[r][i].fn(L[r]);
+        }
+    }
+    for (int r = 0; r < n; ++r) {
+        const int rc2 = rc == EVP_OK ? finish_ops(hs[r]) : rc;
+        hs[r]->stream = hs[r]->own_stream;
+        if (rc2 != EVP_OK) rc = rc2;
+    }
+    return rc;
+}
+
+int evp_gpu_construct_fields_fetch(evp_handle_t *h, double *mc, double *mx, double *my, double *tc, double *tx, double *ty)
+{
+    if (!h) return EVP_ERR_ARG;
+    if (!h->rc || !h->rc_loaded) return EVP_ERR_STATE;
+    CK(cudaSetDevice(h->cfg.device));
+    const RcLayout l = rc_layout(h);
+    const size_t cells = (size_t)h->nxb * h->nyb;
+    auto pl = [h](size_t k) { return h->rc + k * h->plane_elems; };
+    D2HBatch B{h, {}};
+    h->batch_dst.clear();
+    double *mass[3] = {mc, mx, my}, *trc[3] = {tc, tx, ty};
+    for (int f = 0; f < 3; ++f) {
+        if (mass[f]) for (int n = 0; n <= l.ncat; ++n) TRY(B.add(pl(l.mass(f, n)), mass[f] + (size_t)n * cells, 0));
+        if (trc[f]) for (int k = 0; k < l.ncat * l.ntrace; ++k) TRY(B.add(pl(l.trc(f, k)), trc[f] + (size_t)k * cells, 0));
+    }
+    TRY(B.flush());
+    CK(cudaStreamSynchronize(h->stream));
+    return EVP_OK;
+}
+
+int evp_gpu_construct_fields(evp_handle_t *h, const double *mm, const double *tm, double *mc, double *mx, double *my,
+                             double *tc, double *tx, double *ty)
+{
+    TRY(evp_gpu_construct_fields_upload(h, mm, tm));
+    TRY(evp_gpu_construct_fields_compute(h));
+    return evp_gpu_construct_fields_fetch(h, mc, mx, my, tc, tx, ty);
 }
 
 int evp_gpu_principal_stress(evp_handle_t *h, double *sig1, double *sig2)

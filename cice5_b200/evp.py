@@ -77,7 +77,10 @@ EXPORTS = ("evp_gpu_init", "evp_gpu_set_grid", "evp_gpu_run", "evp_gpu_upload", 
            "evp_gpu_principal_stress", "evp_gpu_pin_host_arrays", "evp_gpu_set_resident",
            "evp_gpu_invalidate_state", "evp_gpu_restart_fixup", "evp_gpu_restart_fixup_group",
            "evp_gpu_principal_stress_static", "evp_gpu_set_transport_grid", "evp_gpu_departure_points_compute",
-           "evp_gpu_departure_points_group", "evp_gpu_departure_points_fetch", "evp_gpu_departure_points")
+           "evp_gpu_departure_points_group", "evp_gpu_departure_points_fetch", "evp_gpu_departure_points",
+           "evp_gpu_set_transport_tracers", "evp_gpu_construct_fields_upload", "evp_gpu_construct_fields_compute",
+           "evp_gpu_construct_fields_group", "evp_gpu_construct_fields_fetch", "evp_gpu_construct_fields")
+REMAP_MAX_TRACE, REMAP_MAX_PARENTS = 128, 16     # EVP_REMAP_MAX_TRACE, EVP_REMAP_MAX_PARENTS of include/evp_b200.h
 STATIC_MAX_CELLS = 131072       # EVP_STATIC_MAX_CELLS of include/evp_b200.h
 
 # download groups of the resident-state protocol (include/evp_b200.h)
@@ -306,6 +309,44 @@ class EvpGpu:
         self._check(self.lib.evp_gpu_departure_points_compute(self._h, C.c_double(dt), C.c_int(int(l_dp_midpt))))
         return self.departure_points_fetch()
 
+    def set_transport_tracers(self, ncat, tracer_type, depend, has_dependents, f):
+        """init_transport's tracer tables (source/ice_transport_driver.F90:82-118) and the block's hm, xav, yav, xxav, yyav
+        (evp_gpu_set_transport_tracers): needed once before construct_fields."""
+        ia = lambda v: np.ascontiguousarray(v, dtype=np.int32)
+        tt, dp, hd = ia(tracer_type), ia(depend), ia(has_dependents)
+        if not (tt.size == dp.size == hd.size):
+            raise ValueError("tracer_type, depend, has_dependents differ in length")
+        geo = [np.ascontiguousarray(f[k], dtype=np.float64) for k in ("hm", "xav", "yav", "xxav", "yyav")]
+        for g in geo:
+            if g.shape != self.shape:
+                raise ValueError(f"transport geometry plane has shape {g.shape}, block is {self.shape}")
+        self._check(self.lib.evp_gpu_set_transport_tracers(self._h, C.c_int(int(ncat)), C.c_int(tt.size), _ip(tt), _ip(dp),
+                                                           _ip(hd), *[_dp(g) for g in geo]))
+        self._rc_shape = (int(ncat), int(tt.size))
+
+    def construct_fields_upload(self, mm, tm):
+        ncat, nt = self._rc_shape
+        mm, tm = np.ascontiguousarray(mm, dtype=np.float64), np.ascontiguousarray(tm, dtype=np.float64)
+        if mm.shape != (ncat + 1,) + self.shape or tm.shape != (ncat, nt) + self.shape:
+            raise ValueError(f"mm {mm.shape} / tm {tm.shape} do not match ncat = {ncat}, ntrace = {nt}, block {self.shape}")
+        self._check(self.lib.evp_gpu_construct_fields_upload(self._h, _dp(mm), _dp(tm) if nt else None))
+
+    def construct_fields_fetch(self):
+        ncat, nt = self._rc_shape
+        o = {k: np.zeros((ncat + 1,) + self.shape) for k in ("mc", "mx", "my")}
+        o.update({k: np.zeros((ncat, nt) + self.shape) for k in ("tc", "tx", "ty")})
+        self._check(self.lib.evp_gpu_construct_fields_fetch(self._h, *[_dp(o[k]) if o[k].size else None
+                                                                       for k in ("mc", "mx", "my", "tc", "tx", "ty")]))
+        return o
+
+    def construct_fields(self, mm, tm):
+        """make_masks + construct_fields + limited_gradient (source/ice_transport_remap.F90:867-1484) for categories
+        0..ncat and the ghost updates that follow (:579-584, :616-621).  mm: (ncat+1, ny_block, nx_block); tm: (ncat,
+        ntrace, ny_block, nx_block).  Returns a dict mc, mx, my, tc, tx, ty."""
+        self.construct_fields_upload(mm, tm)
+        self._check(self.lib.evp_gpu_construct_fields_compute(self._h))
+        return self.construct_fields_fetch()
+
     def stats(self) -> Stats:
         st = Stats()
         self._check(self.lib.evp_gpu_get_stats(self._h, C.byref(st)))
@@ -458,6 +499,20 @@ class EvpGroup:
     def restart_fixup(self):
         arr = (C.c_void_p * self.n)(*[e._h for e in self.ranks])
         self.ranks[0]._check(self.ranks[0].lib.evp_gpu_restart_fixup_group(arr, self.n))
+
+    def set_transport_tracers(self, ncat, tracer_type, depend, has_dependents, f):
+        for r, e in enumerate(self.ranks):
+            e.set_transport_tracers(ncat, tracer_type, depend, has_dependents,
+                                    self._slabs({k: f[k] for k in ("hm", "xav", "yav", "xxav", "yyav")}, r))
+
+    def construct_fields(self, mm, tm):
+        """All ranks; returns the global mc, mx, my, tc, tx, ty."""
+        for r, e in enumerate(self.ranks):
+            e.construct_fields_upload(self._fx.slab(mm, r, self.n, self.starts), self._fx.slab(tm, r, self.n, self.starts))
+        arr = (C.c_void_p * self.n)(*[e._h for e in self.ranks])
+        self.ranks[0]._check(self.ranks[0].lib.evp_gpu_construct_fields_group(arr, self.n))
+        parts = [e.construct_fields_fetch() for e in self.ranks]
+        return {k: self._fx.unslab([p[k] for p in parts]) for k in parts[0]}
 
     def close(self):
         for e in self.ranks:

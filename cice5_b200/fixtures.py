@@ -412,6 +412,54 @@ def ice_state(grid: Grid, scenario: str = "full") -> dict:
     return s
 
 
+# tracer table of the transport tests / bench: init_transport's arrays (source/ice_transport_driver.F90:82-118) for
+# hice, hsno, Tsfc, four ice-enthalpy layers, one snow-enthalpy layer and level-ice-style pond tracers (apnd on the ice
+# area with hpnd on apnd and ipnd on hpnd): all three tracer types, three tracers with dependents
+TRANSPORT_TRACERS = ("hice", "hsno", "Tsfc", "qice1", "qice2", "qice3", "qice4", "qsno1", "apnd", "hpnd", "ipnd")
+TRANSPORT_TYPE = (1, 1, 1, 2, 2, 2, 2, 2, 1, 2, 3)
+TRANSPORT_DEPEND = (0, 0, 0, 1, 1, 1, 1, 2, 0, 9, 10)
+
+
+def transport_tracers(grid, state: dict, seed: int = 0, geometry: str = "cice") -> dict:
+    """Inputs of horizontal_remap's field reconstruction (source/ice_transport_remap.F90:462-511) consistent with an
+    ice state of :func:`ice_state`: mm = (aice0, aicen) -> (6, ny+2, nx+2), tm = the tracers above per category ->
+    (5, 11, ny+2, nx+2), ghost cells included; hm = the land mask; xav, yav, xxav, yyav as init_remap sets them
+    (:236-283: 0, 0, 1/12, 1/12) or, geometry = "random", perturbed so that every term of the reconstruction is live.
+    Snow-free and pond-free patches leave tracers at zero where their parents are not."""
+    r = np.random.default_rng(seed)
+    itd = ice_itd(state)
+    sh = state["aice"].shape
+    hm = (grid.f["tmask"] != 0).astype(np.float64)
+    mm = np.concatenate([itd["aice0"][None], itd["aicen"]]) * hm
+    ncat, nt = itd["aicen"].shape[0], len(TRANSPORT_TRACERS)
+    tm = np.zeros((ncat, nt) + sh)
+    smooth = lambda lo, hi: lo + (hi - lo) * r.uniform(0.0, 1.0, sh)
+    for n in range(ncat):
+        ice = mm[n + 1] > 0.0
+        hice = np.where(ice, itd["vicen"][n] / np.where(ice, itd["aicen"][n], 1.0), 0.0) * smooth(0.8, 1.2)
+        hsno = np.where(r.uniform(0, 1, sh) < 0.7, 0.2 * smooth(0.5, 1.5), 0.0)          # snow-free patches
+        apnd = np.where(r.uniform(0, 1, sh) < 0.4, smooth(0.05, 0.6), 0.0)               # ponds on 40 % of the ice
+        tm[n, 0], tm[n, 1], tm[n, 2] = hice, hsno, -smooth(1.0, 25.0)
+        for k in range(4):
+            tm[n, 3 + k] = -smooth(2.0e8, 3.2e8)
+        tm[n, 7] = -smooth(1.0e8, 1.3e8)
+        tm[n, 8], tm[n, 9], tm[n, 10] = apnd, smooth(0.02, 0.4), smooth(0.0, 0.1)
+        tm[n] *= ice
+    d = {"hm": hm, "mm": np.ascontiguousarray(mm), "tm": tm, "tracer_type": np.array(TRANSPORT_TYPE, dtype=np.int32),
+         "depend": np.array(TRANSPORT_DEPEND, dtype=np.int32)}
+    hd = np.zeros(nt, dtype=np.int32)
+    for dep in TRANSPORT_DEPEND:
+        if dep > 0:
+            hd[dep - 1] = 1
+    d["has_dependents"] = hd
+    if geometry == "cice":
+        d.update(xav=np.zeros(sh), yav=np.zeros(sh), xxav=np.full(sh, 1.0 / 12.0), yyav=np.full(sh, 1.0 / 12.0))
+    else:
+        d.update(xav=r.uniform(-0.04, 0.04, sh), yav=r.uniform(-0.04, 0.04, sh), xxav=r.uniform(0.07, 0.10, sh),
+                 yyav=r.uniform(0.07, 0.10, sh))
+    return d
+
+
 ITD_WEIGHTS = (0.1, 0.2, 0.3, 0.25, 0.15)          # SURVEY.md 8d: 5-category split of aice
 ITD_THICKNESS = (0.3, 0.7, 1.0, 1.5, 2.5)          # thickness multipliers of the categories
 
@@ -523,9 +571,10 @@ def slab_bounds(nx: int, nranks: int, starts=None) -> list:
 
 
 def slab(a: np.ndarray, rank: int, nranks: int, starts=None) -> np.ndarray:
-    """Column slice (with ghosts) of a global-with-ghost array owned by x-slab `rank`."""
-    b = slab_bounds(a.shape[1] - 2, nranks, starts)
-    return np.ascontiguousarray(a[:, b[rank]: b[rank + 1] + 2])
+    """Column slice (with ghosts) of a global-with-ghost array (or a stack of them: leading axes are kept) owned by
+    x-slab `rank`."""
+    b = slab_bounds(a.shape[-1] - 2, nranks, starts)
+    return np.ascontiguousarray(a[..., b[rank]: b[rank + 1] + 2])
 
 
 STRIP_COLUMNS = 124      # U columns per work strip of the subcycle kernel (4 warps x 31 columns)
@@ -574,6 +623,6 @@ def balanced_slab_starts(ocean: np.ndarray, nranks: int, strip: int = STRIP_COLU
 def unslab(parts: list) -> np.ndarray:
     """Inverse of :func:`slab`: physical columns from the owner, outer ghosts from the end slabs."""
     n = len(parts)
-    cols = [p[:, (0 if r == 0 else 1):(p.shape[1] if r == n - 1 else p.shape[1] - 1)]
+    cols = [p[..., (0 if r == 0 else 1):(p.shape[-1] if r == n - 1 else p.shape[-1] - 1)]
             for r, p in enumerate(parts)]
-    return np.ascontiguousarray(np.concatenate(cols, axis=1))
+    return np.ascontiguousarray(np.concatenate(cols, axis=-1))

@@ -202,6 +202,32 @@ int evp_gpu_departure_points_fetch(evp_handle_t *h, double *dpx, double *dpy, in
 int evp_gpu_departure_points(evp_handle_t *h, double dt, int l_dp_midpt, double *dpx, double *dpy, int *l_stop, int *istop,
                              int *jstop);
 
+/* Horizontal transport, field reconstruction: make_masks (source/ice_transport_remap.F90:867-1015),
+ * construct_fields (:1024-1340) and limited_gradient (:1348-1484) for the open-water category 0 and the ice categories
+ * 1..ncat, as horizontal_remap calls them per block (:462-511), followed by its ghost-cell updates of mc, mx, my, tc,
+ * tx, ty (:579-584, :616-621; maskhalo_remap = .false., the default of ice_transport_driver.F90).
+ *   set_transport_tracers: once (again when the tracer set changes).  tracer_type / depend / has_dependents are
+ *            init_transport's arrays (source/ice_transport_driver.F90:82-118; depend 1-based; a type-2 tracer's parent
+ *            is an earlier type-1 tracer flagged has_dependents, else EVP_ERR_ARG); hm, xav, yav, xxav, yyav the
+ *            block's planes of ice_grid.F90 / ice_transport_remap.F90:300-340.  Allocates the device planes.
+ *            ntrace <= EVP_REMAP_MAX_TRACE, at most EVP_REMAP_MAX_PARENTS tracers with dependents (EVP_ERR_TOO_LARGE).
+ *   upload:  mm = aim (nx_block, ny_block, 0:ncat), tm = trm (nx_block, ny_block, ntrace, ncat) of this block with
+ *            their ghost cells filled, as horizontal_remap receives them.
+ *   compute / group: the reconstruction and the ghost-cell updates (every rank of the run calls it, like evp_gpu_run).
+ *   fetch:   mc, mx, my (nx_block, ny_block, 0:ncat) and tc, tx, ty (nx_block, ny_block, ntrace, ncat); any may be NULL.
+ *   evp_gpu_construct_fields = upload + compute + fetch. */
+#define EVP_REMAP_MAX_TRACE 128
+#define EVP_REMAP_MAX_PARENTS 16
+int evp_gpu_set_transport_tracers(evp_handle_t *h, int ncat, int ntrace, const int *tracer_type, const int *depend,
+                                  const int *has_dependents, const double *hm, const double *xav, const double *yav,
+                                  const double *xxav, const double *yyav);
+int evp_gpu_construct_fields_upload(evp_handle_t *h, const double *mm, const double *tm);
+int evp_gpu_construct_fields_compute(evp_handle_t *h);
+int evp_gpu_construct_fields_group(evp_handle_t **handles, int n);
+int evp_gpu_construct_fields_fetch(evp_handle_t *h, double *mc, double *mx, double *my, double *tc, double *tx, double *ty);
+int evp_gpu_construct_fields(evp_handle_t *h, const double *mm, const double *tm, double *mc, double *mx, double *my,
+                             double *tc, double *tx, double *ty);
+
 /* Several ranks driven by one host thread (handles of ranks 0..n-1 on ONE device, e.g. tests with
  * fewer GPUs than ranks): steps are interleaved on one stream so that no kernel ever waits. */
 int evp_gpu_compute_group(evp_handle_t **handles, int n, double dt);

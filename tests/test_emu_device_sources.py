@@ -580,3 +580,70 @@ def test_departure_points_gx3_and_out_of_bounds(dev):
     dpx, dpy, stops, rx, ry, ref_stop = _departure_case(dev, grid, "full", 6, 1, True, dt_scale=4.0e3)
     assert ref_stop[0] and stops[0] == ref_stop and ref_stop[1] > 1 and ref_stop[2] > 1
     assert np.array_equal(phys(dpx), phys(rx)) and np.array_equal(phys(dpy), phys(ry))
+
+
+# ---- horizontal transport, field reconstruction: make_masks + construct_fields -----------------
+def _construct_case(dev, grid, scenario, nranks, geometry, seed=5):
+    """construct_fields on the device against the oracle's (itself pinned to the reference text), every cell of every
+    plane, ghost ring included."""
+    case = fx.make_case(grid, scenario, ndte=6, dt=3600.0)
+    d = fx.transport_tracers(grid, case.inp, seed, geometry)
+    ncat = d["tm"].shape[0]
+    if nranks == 1:
+        e = dev.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True)
+        try:
+            e.set_transport_tracers(ncat, d["tracer_type"], d["depend"], d["has_dependents"], d)
+            got = e.construct_fields(d["mm"], d["tm"])
+            again = e.construct_fields(d["mm"], d["tm"])                  # no state carried from call to call
+        finally:
+            e.close()
+        for k in got:
+            assert np.array_equal(got[k], again[k]), k
+    else:
+        g = dev.EvpGroup(case.dom, case.ndte, case.dt, nranks, strict=True)
+        try:
+            g.set_transport_tracers(ncat, d["tracer_type"], d["depend"], d["has_dependents"], d)
+            got = g.construct_fields(d["mm"], d["tm"])
+        finally:
+            g.close()
+    want = orc.construct_fields(case.dom, d["tracer_type"], d["depend"], d["has_dependents"], d["hm"], d["xav"], d["yav"],
+                                d["xxav"], d["yyav"], d["mm"], d["tm"])
+    return got, want, d
+
+
+@pytest.mark.parametrize("nranks,geometry", [(1, "cice"), (1, "random"), (2, "random"), (4, "cice")])
+def test_construct_fields_bitwise(dev, nranks, geometry):
+    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
+    got, want, d = _construct_case(dev, grid, "caps", nranks, geometry)
+    for k in ("mc", "mx", "my", "tc", "tx", "ty"):
+        assert got[k].shape == want[k].shape and np.array_equal(got[k], want[k]), k
+        assert np.array_equal(np.signbit(got[k]), np.signbit(want[k])), k
+    assert np.count_nonzero(want["tx"][:, 0]) > 200 and np.count_nonzero(want["tx"][:, 9]) > 20    # hice; hpnd on apnd
+    assert want["tc"][:, :, -1, 1:-1].any()                              # the fold filled the north ghost row
+    assert not np.array_equal(want["tc"][:, 0], d["tm"][:, 0])           # the centre value differs from the mean
+
+
+def test_construct_fields_gx3_and_argument_errors(dev):
+    grid = fx.make_grid("gx3")
+    got, want, d = _construct_case(dev, grid, "full", 1, "random")
+    for k in ("mc", "mx", "my", "tc", "tx", "ty"):
+        assert np.array_equal(got[k], want[k]), k
+    case = fx.make_case(grid, "full", ndte=6, dt=3600.0)
+    e = dev.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True)
+    try:
+        with pytest.raises(dev.EvpError):                                # not set up yet
+            e._rc_shape = (5, 11)
+            e.construct_fields(d["mm"], d["tm"])
+        bad = d["depend"].copy()
+        bad[3] = 3                                                       # a type-2 tracer on Tsfc, which has no dependents
+        with pytest.raises(dev.EvpError):
+            e.set_transport_tracers(5, d["tracer_type"], bad, d["has_dependents"], d)
+        bad = d["depend"].copy()
+        bad[3] = 9                                                       # parent comes later in the table
+        with pytest.raises(dev.EvpError):
+            e.set_transport_tracers(5, d["tracer_type"], bad, d["has_dependents"], d)
+        many = np.ones(dev.REMAP_MAX_TRACE + 1, dtype=np.int32)
+        with pytest.raises(dev.EvpError):
+            e.set_transport_tracers(5, many, 0 * many, 0 * many, d)
+    finally:
+        e.close()

@@ -1,7 +1,8 @@
-"""Horizontal transport, first stage on the device: departure_points
-(source/ice_transport_remap.F90:1493-1670) + the ghost update of dpx, dpy (:574-578) from the resident velocities of the
-last evp, bit for bit against the oracle (oracle/remap_oracle.c, itself pinned to the reference text).  The test bodies
-are the ones the CPU tier runs on the host build of the device sources."""
+"""Horizontal transport, first stages on the device, bit for bit against the oracle
+(oracle/remap_oracle.c, itself pinned to the reference text): departure_points (source/ice_transport_remap.F90:1493-1670)
++ the ghost update of dpx, dpy (:574-578) from the resident velocities of the last evp; make_masks + construct_fields +
+limited_gradient (:867-1484) + the ghost updates of mc, mx, my, tc, tx, ty (:579-584, :616-621).  The test bodies are the
+ones the CPU tier runs on the host build of the device sources."""
 import pytest
 
 from cice5_b200 import evp
@@ -25,3 +26,24 @@ def test_departure_points_one_degree_tripole_on_device():
     grid = fx.make_grid("tp1")
     dpx, dpy, stops, rx, ry, ref_stop = shared._departure_case(evp, grid, "caps", 120, 1, True)
     assert not ref_stop[0] and np.array_equal(dpx, rx) and np.array_equal(dpy, ry)
+
+
+@pytest.mark.parametrize("nranks,geometry", [(1, "cice"), (1, "random"), (2, "random"), (4, "cice")])
+def test_construct_fields_bitwise_on_device(nranks, geometry):
+    shared.test_construct_fields_bitwise(evp, nranks, geometry)
+
+
+def test_construct_fields_gx3_and_argument_errors_on_device():
+    shared.test_construct_fields_gx3_and_argument_errors(evp)
+
+
+def test_construct_fields_one_degree_tripole_on_device():
+    """The 1-degree tripole with the full tracer table: 6 + 55 input planes, 18 + 165 output planes."""
+    from cice5_b200 import fixtures as fx
+    import numpy as np
+    grid = fx.make_grid("tp1")
+    got, want, d = shared._construct_case(evp, grid, "caps", 1, "cice")
+    for k in ("mc", "mx", "my", "tc", "tx", "ty"):
+        assert np.array_equal(got[k], want[k]), k
+        assert np.array_equal(np.signbit(got[k]), np.signbit(want[k])), k
+    assert np.count_nonzero(want["tx"]) > 10000
