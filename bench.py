@@ -55,6 +55,8 @@ def parse():
     ap.add_argument("--equal-slabs", action="store_true",
                     help="N > 1: nx/N columns per GPU instead of slabs balanced by ocean cells")
     ap.add_argument("--no-parity", action="store_true", help="skip the bitwise comparison with the oracle")
+    ap.add_argument("--no-transport", action="store_true",
+                    help="skip the transport-stage block (departure_points + field reconstruction, N = 1 only)")
     ap.add_argument("--no-other-configs", action="store_true",
                     help="skip the short measurements of the other BASELINE grid shapes")
     ap.add_argument("--cpu-ndte", type=int, default=120,
@@ -498,8 +500,56 @@ def measure(ctx, args, gridname, scenario, steps, warmup, do_e2e, do_parity, ref
                "roofline": roof, "clocks": clocks, "value_check": check_value, "parity": parity, "e2e": e2e,
                "e2e_full": e2e_full,
                "gpu_launches": int(launches), "loop_kernel_launches_per_step": int(loop_launches)}
+    if N == 1 and do_e2e and not args.no_transport and res is not None:
+        try:
+            res["transport"] = transport_block(e, args, grid, case, dt)
+        except Exception as ex:                   # noqa: BLE001 -- a side block must not cost the headline line
+            res["transport"] = {"error": str(ex)[:300]}
     e.close()
     return res
+
+
+def transport_block(e, args, grid, case, dt, steps=5, warmup=2):
+    """SURVEY.md 8f row 2, the stages of horizontal_remap that run on the device so far, on the bench workload's grid
+    (N = 1): departure_points from the velocities the timed evp calls left resident, and the field reconstruction
+    (make_masks + construct_fields + limited_gradient) of 5 ice categories x 11 tracers + open water.  Device time by
+    CUDA events inside the library (evp_gpu_get_transport_timing); bandwidth against the same measured HBM peak as the
+    main roofline.  Parity of both stages: tests/test_gpu_zt_transport.py (bitwise against the oracle up to the
+    1-degree tripole; the 0.1-degree reconstruction holds 249 planes = 19 GB on the device, its oracle twin is not run
+    here)."""
+    from cice5_b200 import fixtures as fx
+    peak, peak_src = measured_peaks()
+    cells = grid.dom.nx * grid.dom.ny
+    e.set_transport_grid(grid.f)
+    dep = []
+    for k in range(warmup + steps):
+        e.departure_points(dt, True)
+        if k >= warmup:
+            dep.append(e.transport_timing())
+    d = fx.transport_tracers(grid, case.inp, 1, "cice")
+    ncat, nt = d["tm"].shape[0], d["tm"].shape[1]
+    e.set_transport_tracers(ncat, d["tracer_type"], d["depend"], d["has_dependents"], d)
+    e.construct_fields_upload(d["mm"], d["tm"])
+    rec = []
+    for k in range(warmup + steps):
+        e.construct_fields_compute()
+        if k >= warmup:
+            rec.append(e.transport_timing())
+    med = lambda rows, key: float(np.median([r[key] for r in rows]))
+    # algorithmic bytes per cell: departure reads u, v, dxu, dyu, HTN, HTE and writes dpx, dpy twice (first-order,
+    # midpoint) -> 10 doubles; reconstruction, per ice category, reads mm + ntrace tracers + hm xav yav xxav yyav and
+    # writes mc mx my + 3 ntrace planes; open water reads mm hm xav yav and writes mc mx my
+    dep_bytes = 8 * 10 * cells
+    rec_bytes = 8 * cells * (ncat * (6 + nt) + ncat * 3 * (1 + nt) + 4 + 3)
+    dms, rms = med(dep, "departure_ms"), med(rec, "reconstruct_ms")
+    return {"grid": grid.dom.name, "ncat": ncat, "ntrace": nt, "steps": steps, "warmup": warmup,
+            "departure_points": {"kernel_ms": dms, "halo_ms": med(dep, "departure_halo_ms"), "alg_bytes": dep_bytes,
+                                 "achieved_GBps": dep_bytes / (dms * 1e-3) / 1e9, "frac": dep_bytes / (dms * 1e-3) / 1e9 / peak},
+            "construct_fields": {"kernel_ms": rms, "halo_ms": med(rec, "reconstruct_halo_ms"), "alg_bytes": rec_bytes,
+                                 "achieved_GBps": rec_bytes / (rms * 1e-3) / 1e9, "frac": rec_bytes / (rms * 1e-3) / 1e9 / peak,
+                                 "halo_updates": 3 * (ncat + 1) + 3 * ncat * nt},
+            "peak_GBps": peak, "peak_source": peak_src,
+            "parity": "tests/test_gpu_zt_transport.py: bitwise against oracle/remap_oracle.c (pinned to the reference text)"}
 
 
 def main():

@@ -149,6 +149,8 @@ struct evp_handle {
     double *rc = nullptr;
     ReconArgs rc_args;
     bool rc_loaded = false;
+    cudaEvent_t tev[3] = {nullptr, nullptr, nullptr};     // transport stage: start, kernels done, ghost updates done
+    double tr_ms[4] = {0.0, 0.0, 0.0, 0.0};               // departure kernels / halos, reconstruction kernel / halos
     bool have_ht = false;         // HTE / HTN were given: compact metric rows are possible
     evp_stats_t stats;
     unsigned long long h_counts[2];
@@ -484,6 +486,7 @@ int evp_gpu_finalize(evp_handle_t *h)
     if (h->itd) cudaFree(h->itd);
     if (h->tr) cudaFree(h->tr);
     if (h->rc) cudaFree(h->rc);
+    for (auto &ev : h->tev) if (ev) cudaEventDestroy(ev);
     if (h->stage) cudaFree(h->stage);
     if (h->arena) cudaFree(h->arena);
     for (void *p : h->pinned) cudaHostUnregister(p);
@@ -1552,12 +1555,31 @@ int evp_gpu_restart_fixup_group(evp_handle_t **hs, int n)
 
 // ---- horizontal transport, first stage: departure points from the resident velocities -------------------
 namespace {
+// device time of a transport stage: events around its kernels and around its ghost-cell updates
+void stage_mark(Builder &B, int k)
+{
+    evp_handle *h = B.h;
+    B.op([h, k](Launcher &L) {
+        if (!h->tev[k]) CK(cudaEventCreate(&h->tev[k]));
+        CK(cudaEventRecord(h->tev[k], L.s()));
+        return EVP_OK;
+    });
+}
+int stage_times(evp_handle *h, int slot)
+{
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, h->tev[0], h->tev[1])); h->tr_ms[slot] = ms;
+    CK(cudaEventElapsedTime(&ms, h->tev[1], h->tev[2])); h->tr_ms[slot + 1] = ms;
+    return EVP_OK;
+}
+
 // departure_points (source/ice_transport_remap.F90:1493-1670) into the work planes W_1 (dpx), W_2 (dpy), then the two
 // ghost-cell updates of horizontal_remap (:574-578)
 void build_departure(evp_handle *h, double dt, int midpt, std::vector<Op> &ops)
 {
     Builder B{h, ops};
     B.sync();                                                    // every rank has left its previous operation
+    stage_mark(B, 0);
     B.op([h, dt, midpt](Launcher &L) {
         DepartArgs a;
         a.nxb = h->nxb; a.nyb = h->nyb; a.ld = h->ld; a.dt = dt; a.midpt = midpt;
@@ -1571,9 +1593,11 @@ void build_departure(evp_handle *h, double dt, int midpt, std::vector<Op> &ops)
         CK(cudaGetLastError());
         return EVP_OK;
     });
+    stage_mark(B, 1);
     B.halo(W_1, 1, -1.0, 0.0);                                   // ice_HaloUpdate(dpx, NEcorner, vector)
     B.halo(W_2, 1, -1.0, 0.0);
     B.sync();                                                    // inbox buffers are free again
+    stage_mark(B, 2);
 }
 int finish_departure(evp_handle *h)
 {
@@ -1584,7 +1608,7 @@ int finish_departure(evp_handle *h)
         snprintf(g_cuda_err, sizeof(g_cuda_err), "halo wait timed out: a peer rank did not arrive");
         return EVP_ERR_PEER;
     }
-    return EVP_OK;
+    return stage_times(h, 0);
 }
 }  // namespace
 
@@ -1703,6 +1727,7 @@ void build_reconstruct(evp_handle *h, std::vector<Op> &ops)
     Builder B{h, ops};
     const RcLayout l = rc_layout(h);
     B.sync();
+    stage_mark(B, 0);
     B.op([h, l](Launcher &L) {
         const dim3 grid((h->nxb + 127) / 128, h->nyb, l.ncat + 1);
         reconstruct_kernel<<<grid, 128, 0, L.s()>>>(h->rc_args);
@@ -1710,6 +1735,7 @@ void build_reconstruct(evp_handle *h, std::vector<Op> &ops)
         CK(cudaGetLastError());
         return EVP_OK;
     });
+    stage_mark(B, 1);
     auto pl = [h](size_t k) { return h->rc + k * h->plane_elems; };
     for (int n = 0; n <= l.ncat; ++n) {
         B.halo_p(pl(l.mass(0, n)), 0, 1.0, 0.0);
@@ -1722,6 +1748,7 @@ void build_reconstruct(evp_handle *h, std::vector<Op> &ops)
         B.halo_p(pl(l.trc(2, k)), 0, -1.0, 0.0);
     }
     B.sync();
+    stage_mark(B, 2);
 }
 int finish_ops(evp_handle *h)
 {
@@ -1731,10 +1758,17 @@ int finish_ops(evp_handle *h)
         snprintf(g_cuda_err, sizeof(g_cuda_err), "halo wait timed out: a peer rank did not arrive");
         return EVP_ERR_PEER;
     }
-    return EVP_OK;
+    return stage_times(h, 2);
 }
 }  // namespace
 extern "C" {
+
+int evp_gpu_get_transport_timing(evp_handle_t *h, double ms[4])
+{
+    if (!h || !ms) return EVP_ERR_ARG;
+    for (int k = 0; k < 4; ++k) ms[k] = h->tr_ms[k];
+    return EVP_OK;
+}
 
 int evp_gpu_set_transport_tracers(evp_handle_t *h, int ncat, int ntrace, const int *tracer_type, const int *depend,
                                   const int *has_dependents, const double *hm, const double *xav, const double *yav,

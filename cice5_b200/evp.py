@@ -79,7 +79,8 @@ EXPORTS = ("evp_gpu_init", "evp_gpu_set_grid", "evp_gpu_run", "evp_gpu_upload", 
            "evp_gpu_principal_stress_static", "evp_gpu_set_transport_grid", "evp_gpu_departure_points_compute",
            "evp_gpu_departure_points_group", "evp_gpu_departure_points_fetch", "evp_gpu_departure_points",
            "evp_gpu_set_transport_tracers", "evp_gpu_construct_fields_upload", "evp_gpu_construct_fields_compute",
-           "evp_gpu_construct_fields_group", "evp_gpu_construct_fields_fetch", "evp_gpu_construct_fields")
+           "evp_gpu_construct_fields_group", "evp_gpu_construct_fields_fetch", "evp_gpu_construct_fields",
+           "evp_gpu_get_transport_timing")
 REMAP_MAX_TRACE, REMAP_MAX_PARENTS = 128, 16     # EVP_REMAP_MAX_TRACE, EVP_REMAP_MAX_PARENTS of include/evp_b200.h
 STATIC_MAX_CELLS = 131072       # EVP_STATIC_MAX_CELLS of include/evp_b200.h
 
@@ -323,6 +324,15 @@ class EvpGpu:
         self._check(self.lib.evp_gpu_set_transport_tracers(self._h, C.c_int(int(ncat)), C.c_int(tt.size), _ip(tt), _ip(dp),
                                                            _ip(hd), *[_dp(g) for g in geo]))
         self._rc_shape = (int(ncat), int(tt.size))
+
+    def transport_timing(self):
+        """Device ms of the last departure_points (kernels, ghost updates) and construct_fields (kernel, ghost updates)."""
+        ms = (C.c_double * 4)()
+        self._check(self.lib.evp_gpu_get_transport_timing(self._h, ms))
+        return {"departure_ms": ms[0], "departure_halo_ms": ms[1], "reconstruct_ms": ms[2], "reconstruct_halo_ms": ms[3]}
+
+    def construct_fields_compute(self):
+        self._check(self.lib.evp_gpu_construct_fields_compute(self._h))
 
     def construct_fields_upload(self, mm, tm):
         ncat, nt = self._rc_shape

@@ -227,6 +227,10 @@ int evp_gpu_construct_fields_group(evp_handle_t **handles, int n);
 int evp_gpu_construct_fields_fetch(evp_handle_t *h, double *mc, double *mx, double *my, double *tc, double *tx, double *ty);
 int evp_gpu_construct_fields(evp_handle_t *h, const double *mm, const double *tm, double *mc, double *mx, double *my,
                              double *tc, double *tx, double *ty);
+/* Device time (CUDA events, ms) of the last call of each transport stage on this handle: ms[0] departure_points kernels,
+ * ms[1] their two ghost updates, ms[2] the reconstruction kernel, ms[3] its ghost updates.  What the reference's
+ * timer_advect / timer_bound would show for these stages (source/ice_timers.F90); bench.py reads it. */
+int evp_gpu_get_transport_timing(evp_handle_t *h, double ms[4]);
 
 /* Several ranks driven by one host thread (handles of ranks 0..n-1 on ONE device, e.g. tests with
  * fewer GPUs than ranks): steps are interleaved on one stream so that no kernel ever waits. */

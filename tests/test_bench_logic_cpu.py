@@ -34,7 +34,7 @@ def tiny(monkeypatch):
     monkeypatch.setitem(fx.GRIDS, "tiny", lambda: fx.synthetic_tripole(96, 40, "tiny", wet_poles=True))
     monkeypatch.setitem(fx.GRID_DT, "tiny", 3600.0)
     return types.SimpleNamespace(ndte=5, fma=False, no_graph=False, no_compact_metrics=False, equal_slabs=False,
-                                 grid="tiny", scenario="full")
+                                 grid="tiny", scenario="full", no_transport=False)
 
 
 def test_measure_reports_parity_value_checks_and_e2e(tiny):
@@ -48,6 +48,11 @@ def test_measure_reports_parity_value_checks_and_e2e(tiny):
     for k in ("metric", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "dtype",
               "config", "roofline", "e2e", "gpu_launches"):
         assert k in r
+    t = r["transport"]                                   # the transport-stage block of the N = 1 bench line
+    assert "error" not in t and t["ncat"] == 5 and t["ntrace"] == 11
+    for k in ("departure_points", "construct_fields"):
+        assert t[k]["kernel_ms"] > 0 and t[k]["achieved_GBps"] > 0 and t[k]["alg_bytes"] > 0
+    assert t["construct_fields"]["halo_updates"] == 183
 
 
 def test_parity_leg_detects_a_wrong_result(tiny, monkeypatch):
