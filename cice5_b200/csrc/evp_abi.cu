@@ -120,6 +120,7 @@ struct evp_handle {
     // pad to 16, wflag[t_chunks], eflag[t_chunks], tflag[t_items].  Peers write topflag / wflag / eflag, so the
     // region sits before every per-rank-sized one and t_chunks is the same on all ranks.
     size_t off_lflags = 0;
+    size_t off_inbox_wide = 0;    // 2 buffers x kWideSlots slots of the inbox layout: halos of plane stacks (transport)
     size_t off_ll = 0;            // ghost mailbox of the loop kernel: u64[kLLBufs][2][nyb][4], written by the E-W neighbours
     bool use_loop = false;        // the ndte loop as ONE persistent kernel (default with the TMA kernel; EVP_B200_LOOP=0: off)
     char *peer_arena[kMaxRanks] = {nullptr};
@@ -148,6 +149,7 @@ struct evp_handle {
     // tm(ntrace, ncat), mc mx my (0:ncat), tc tx ty (ntrace, ncat) planes of the arena's pitch in one allocation
     double *rc = nullptr;
     ReconArgs rc_args;
+    CUtensorMap rc_map;           // (column, row, plane) over the reconstruction planes, boxes of one tile + its ring
     bool rc_loaded = false;
     cudaEvent_t tev[3] = {nullptr, nullptr, nullptr};     // transport stage: start, kernels done, ghost updates done
     double tr_ms[4] = {0.0, 0.0, 0.0, 0.0};               // departure kernels / halos, reconstruction kernel / halos
@@ -164,6 +166,11 @@ struct evp_handle {
     {
         char *base = (rank < 0 || rank == cfg.rank) ? arena : peer_arena[rank];
         return reinterpret_cast<double *>(base + off_inbox) + (size_t)buf * inbox_doubles(ib);
+    }
+    double *inbox_wide(int buf, int rank = -1) const
+    {
+        char *base = (rank < 0 || rank == cfg.rank) ? arena : peer_arena[rank];
+        return reinterpret_cast<double *>(base + off_inbox_wide) + (size_t)buf * kWideSlots * inbox_doubles(ib);
     }
     unsigned long long *flags(int rank = -1) const   // [0..kMaxRanks) slots, [kMaxRanks] epoch
     {
@@ -248,9 +255,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-// Tensor maps of the subcycle kernel v2: ONE 3-D tensor (column, row, plane) over the whole plane
-// arena, boxes of 128 columns x 1 row x depth planes; a 2-D byte tensor for the activity mask.
-int make_tensor_maps(evp_handle *h)
+int tensor_map_encoder(EncodeTiledFn *enc)
 {
     void *fn = nullptr;
     cudaDriverEntryPointQueryResult qres;
@@ -259,7 +264,16 @@ int make_tensor_maps(evp_handle *h)
         snprintf(g_cuda_err, sizeof(g_cuda_err), "cuTensorMapEncodeTiled is not available from this driver");
         return EVP_ERR_CUDA;
     }
-    EncodeTiledFn enc = reinterpret_cast<EncodeTiledFn>(fn);
+    *enc = reinterpret_cast<EncodeTiledFn>(fn);
+    return EVP_OK;
+}
+
+// Tensor maps of the subcycle kernel v2: ONE 3-D tensor (column, row, plane) over the whole plane
+// arena, boxes of 128 columns x 1 row x depth planes; a 2-D byte tensor for the activity mask.
+int make_tensor_maps(evp_handle *h)
+{
+    EncodeTiledFn enc = nullptr;
+    TRY(tensor_map_encoder(&enc));
     const cuuint64_t dims[3] = {(cuuint64_t)h->ld, (cuuint64_t)h->nyb, (cuuint64_t)NPLANES};
     const cuuint64_t strides[2] = {(cuuint64_t)h->ld * 8, (cuuint64_t)h->plane_elems * 8};
     const cuuint32_t estr[3] = {1, 1, 1};
@@ -442,6 +456,7 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
         h->t_items = h->tstrips * h->t_chunks;
     }
     h->off_ll = off;     off = align_up(off + h->ll_bytes(), 256);      // (same size and offset on every rank)
+    h->off_inbox_wide = off; off = align_up(off + 2 * (size_t)kWideSlots * inbox_doubles(h->ib) * sizeof(double), 256);   // (the same)
     h->off_lflags = off; off = align_up(off + (16 + 2 * (size_t)h->t_chunks + h->t_items) * sizeof(unsigned long long), 256);
     h->off_tflags = off; off = align_up(off + (size_t)h->tstrips * h->tflags_ld, 256);
     h->off_gflags = off; off = align_up(off + (size_t)h->tstrips * h->tflags_ld, 256);
@@ -913,6 +928,42 @@ struct Builder {
             CK(cudaGetLastError());
             return EVP_OK;
         });
+    }
+
+    // ice_HaloUpdate (center) of `nplanes` planes `stride` elements apart, 2 * kWideSlots planes per operation
+    int wide_seq = 0;
+    void halo_multi(double *plane0, int nplanes, size_t stride, double sgn, double fill)
+    {
+        evp_handle *hh = h;
+        for (int first = 0; first < nplanes; first += 2 * kWideSlots) {
+            const int np = nplanes - first < 2 * kWideSlots ? nplanes - first : 2 * kWideSlots;
+            double *plane = plane0 + (size_t)first * stride;
+            const int buf = (wide_seq++) & 1;
+            op([hh, plane, np, stride, buf](Launcher &L) {
+                const Geom &g = hh->g;
+                PushArgs pa;
+                memset(&pa, 0, sizeof(pa));
+                pa.g = g; pa.ib = hh->ib; pa.plane = plane;
+                for (int r = 0; r < g.nranks; ++r) pa.inbox[r] = hh->inbox_wide(buf, r);
+                pa.west = hh->west_closed() ? -1 : hh->west();
+                pa.east = hh->east_closed() ? -1 : hh->east();
+                pa.ioff = 0; pa.ew = 1;
+                const int nt = g.ny + (g.tripole ? g.nxl : 0);
+                halo_push_multi_kernel<<<dim3((nt + 255) / 256, np), 256, 0, L.s()>>>(pa, stride);
+                ++L.n;
+                return EVP_OK;
+            });
+            sync();
+            op([hh, plane, np, stride, sgn, fill, buf](Launcher &L) {
+                const Geom &g = hh->g;
+                const int na = g.nxl + 2 + g.ny;
+                halo_apply_multi_kernel<<<dim3((na + 255) / 256, np), 256, 0, L.s()>>>(
+                    plane, stride, g, hh->ib, hh->inbox_wide(buf), sgn, fill, hh->west_closed(), hh->east_closed());
+                ++L.n;
+                CK(cudaGetLastError());
+                return EVP_OK;
+            });
+        }
     }
 
     // ice_HaloUpdate_stress(a1, a2): a2's top physical row mirrored with center offsets
@@ -1730,22 +1781,28 @@ void build_reconstruct(evp_handle *h, std::vector<Op> &ops)
     stage_mark(B, 0);
     B.op([h, l](Launcher &L) {
         const dim3 grid((h->nxb + 127) / 128, h->nyb, l.ncat + 1);
-        reconstruct_kernel<<<grid, 128, 0, L.s()>>>(h->rc_args);
+        if (h->use_tma) {
+            ReconTmaArgs p;
+            p.a = h->rc_args;
+            p.tiles_x = (h->nxb + kRcTX - 1) / kRcTX; p.tiles_y = (h->nyb + kRcTY - 1) / kRcTY;
+            p.plane_hm = 0; p.plane_mm = (int)l.mm(0); p.plane_tm = (int)l.tm(0);
+            const long long items = (long long)p.tiles_x * p.tiles_y * (l.ncat + 1);
+            const long long slots = (long long)h->sm_count * kRcBlocksPerSM;
+            reconstruct_tma_kernel<<<(unsigned)(items < slots ? items : slots), (kRcTY + 1) * 32, 0, L.s()>>>(h->rc_map, p);
+        } else {
+            reconstruct_kernel<<<grid, 128, 0, L.s()>>>(h->rc_args);
+        }
         ++L.n;
         CK(cudaGetLastError());
         return EVP_OK;
     });
     stage_mark(B, 1);
     auto pl = [h](size_t k) { return h->rc + k * h->plane_elems; };
-    for (int n = 0; n <= l.ncat; ++n) {
-        B.halo_p(pl(l.mass(0, n)), 0, 1.0, 0.0);
-        B.halo_p(pl(l.mass(1, n)), 0, -1.0, 0.0);
-        B.halo_p(pl(l.mass(2, n)), 0, -1.0, 0.0);
-    }
-    for (int k = 0; k < l.ncat * l.ntrace; ++k) {
-        B.halo_p(pl(l.trc(0, k)), 0, 1.0, 0.0);
-        B.halo_p(pl(l.trc(1, k)), 0, -1.0, 0.0);
-        B.halo_p(pl(l.trc(2, k)), 0, -1.0, 0.0);
+    B.halo_multi(pl(l.mass(0, 0)), l.ncat + 1, h->plane_elems, 1.0, 0.0);                  // mc: center, scalar
+    B.halo_multi(pl(l.mass(1, 0)), 2 * (l.ncat + 1), h->plane_elems, -1.0, 0.0);           // mx, my: center, vector
+    if (l.ntrace > 0) {
+        B.halo_multi(pl(l.trc(0, 0)), l.ncat * l.ntrace, h->plane_elems, 1.0, 0.0);        // tc
+        B.halo_multi(pl(l.trc(1, 0)), 2 * l.ncat * l.ntrace, h->plane_elems, -1.0, 0.0);   // tx, ty
     }
     B.sync();
     stage_mark(B, 2);
@@ -1817,6 +1874,20 @@ int evp_gpu_set_transport_tracers(evp_handle_t *h, int ncat, int ntrace, const i
     a.tc = pl(l.trc(0, 0)); a.tx = pl(l.trc(1, 0)); a.ty = pl(l.trc(2, 0));
     h->rc_args = a;
     h->rc_loaded = false;
+    if (h->use_tma) {
+        EncodeTiledFn enc = nullptr;
+        TRY(tensor_map_encoder(&enc));
+        const cuuint64_t dims[3] = {(cuuint64_t)h->ld, (cuuint64_t)h->nyb, (cuuint64_t)l.planes()};
+        const cuuint64_t strides[2] = {(cuuint64_t)h->ld * 8, (cuuint64_t)h->plane_elems * 8};
+        const cuuint32_t box[3] = {(cuuint32_t)kRcBoxW, (cuuint32_t)kRcBoxH, 1}, estr[3] = {1, 1, 1};
+        const CUresult r = enc(&h->rc_map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, h->rc, dims, strides, box, estr,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) {
+            snprintf(g_cuda_err, sizeof(g_cuda_err), "cuTensorMapEncodeTiled(reconstruction) failed: %d", (int)r);
+            return EVP_ERR_CUDA;
+        }
+    }
     const double *src[5] = {hm, xav, yav, xxav, yyav};
     for (int k = 0; k < 5; ++k) TRY(h2d_any(h, pl(k), src[k], 0));
     TRY(h2d_flush(h));

@@ -128,6 +128,63 @@ __global__ void halo_apply_kernel(double *plane, Geom g, InboxGeom ib, double *i
     }
 }
 
+// ---- the generic halo for a stack of planes in one go (transport: mc mx my tc tx ty of every category) ------------
+// Plane p of the stack (blockIdx.y) uses field (p & 1) of slot (p >> 1) of a wide inbox -- kWideSlots slots with the
+// layout above, two buffers alternated per operation like the narrow ones.  Same values into the same ghost cells as
+// nplanes calls of halo_push_kernel / halo_apply_kernel; one launch each and, between ranks, one sync instead of nplanes.
+constexpr int kWideSlots = 32;
+
+__global__ void halo_push_multi_kernel(const __grid_constant__ PushArgs a, size_t plane_stride)
+{
+    const Geom &g = a.g;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x, p = blockIdx.y;
+    const double *plane = a.plane + (size_t)p * plane_stride;
+    const size_t so = (size_t)(p >> 1) * inbox_doubles(a.ib);
+    const int fo = (p & 1) * 2;
+    if (t < g.ny) {
+        const int r = t + 1;
+        if (a.west >= 0) inbox_col(a.inbox[a.west] + so, a.ib, fo + 1)[r] = plane[(size_t)r * g.ld + 1];
+        if (a.east >= 0) inbox_col(a.inbox[a.east] + so, a.ib, fo)[r] = plane[(size_t)r * g.ld + g.nxl];
+    } else if (g.tripole && t < g.ny + g.nxl) {
+        const int c = t - g.ny + 1;
+        const int ig = g.lo + c;
+        int X = g.nx_global + 1 - a.ioff - ig;
+        if (X == 0) X = g.nx_global;
+        int tr, ct, wt;
+        slab_owner(g.start, g.nranks, X, tr, ct, wt);
+#pragma unroll
+        for (int rs = 0; rs < 2; ++rs) {
+            const double v = plane[(size_t)(g.ny - 1 + rs) * g.ld + c];
+            inbox_row(a.inbox[tr] + so, a.ib, fo + rs)[ct] = v;
+            if (ct == 1) {
+                const int t2 = (tr + g.nranks - 1) % g.nranks;
+                inbox_row(a.inbox[t2] + so, a.ib, fo + rs)[g.start[t2 + 1] - g.start[t2] + 1] = v;
+            }
+            if (ct == wt) inbox_row(a.inbox[(tr + 1) % g.nranks] + so, a.ib, fo + rs)[0] = v;
+        }
+    }
+}
+
+// center fields only (loc 0): ghost row = sgn * mirrored top row, E-W ghosts, fill on closed edges
+__global__ void halo_apply_multi_kernel(double *plane0, size_t plane_stride, Geom g, InboxGeom ib, double *inbox0,
+                                        double sgn, double fill, int west_closed, int east_closed)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x, p = blockIdx.y;
+    double *plane = plane0 + (size_t)p * plane_stride;
+    double *inbox = inbox0 + (size_t)(p >> 1) * inbox_doubles(ib);
+    const int fo = (p & 1) * 2;
+    const int nxb = g.nxl + 2;
+    if (t < nxb) {
+        const int c = t;
+        plane[c] = fill;                                           // south ghost row
+        plane[(size_t)(g.ny + 1) * g.ld + c] = g.tripole ? sgn * inbox_row(inbox, ib, fo + 1)[c] : fill;
+    } else if (t < nxb + g.ny) {
+        const int r = t - nxb + 1;
+        plane[(size_t)r * g.ld] = west_closed ? fill : inbox_col(inbox, ib, fo)[r];
+        plane[(size_t)r * g.ld + g.nxl + 1] = east_closed ? fill : inbox_col(inbox, ib, fo + 1)[r];
+    }
+}
+
 // ice_HaloUpdate_stress: ghost row of a1 <- mirrored top physical row of a2 (center, +1);
 // the closed south row (and closed E-W ghosts) get 0 (:3351-3353).
 __global__ void halo_stress_apply_kernel(double *a1, Geom g, InboxGeom ib, double *inbox,

@@ -7,6 +7,7 @@
 // vvel straight from the resident EVP state: the velocities never leave the device between evp and this stage.
 #pragma once
 #include "evp_kernels.cuh"
+#include "evp_subcycle_tma.cuh"     // mbarrier / TMA helpers
 
 namespace evp {
 
@@ -92,17 +93,21 @@ constexpr double puny = 1.0e-11;
 __device__ __forceinline__ double min2(double a, double x) { return x < a ? x : a; }
 __device__ __forceinline__ double max2(double a, double x) { return x > a ? x : a; }
 
-// limited_gradient for one cell (:1404-1482).  ph[k], mk[k]: phi and phimask of the 3 x 3 neighbourhood,
-// k = (dj+1)*3 + (di+1); cx, cy: cnx, cny of the cell
-__device__ __forceinline__ void limited_gradient(const double (&ph)[9], const double (&mk)[9], double cx, double cy,
-                                                 double &gx, double &gy)
+__device__ __forceinline__ void load9(const double *f, size_t q, int ld, double (&v)[9])
 {
-    const double p = ph[4];
-    auto nb = [&](int k) { return mk[k] * ph[k] + (1.0 - mk[k]) * p; };
-    const double nw = nb(6), n = nb(7), ne = nb(8), w = nb(3), e = nb(5), sw = nb(0), s = nb(1), se = nb(2);
-    const double gxtmp = (e - w) * 0.5, gytmp = (n - s) * 0.5;
-    double pmn = nw, pmx = nw;
-    const double lst[8] = {n, ne, w, p, e, sw, s, se};
+#pragma unroll
+    for (int dj = -1; dj <= 1; ++dj)
+#pragma unroll
+        for (int di = -1; di <= 1; ++di) v[(dj + 1) * 3 + di + 1] = f[q + (ptrdiff_t)dj * ld + di];
+}
+
+// the limiter of limited_gradient (:1431-1482) on the eight masked neighbour values nb[k] (k = (dj+1)*3 + (di+1), nb[4]
+// unused) and the cell's own value p
+__device__ __forceinline__ void limit(const double (&nb)[9], double p, double cx, double cy, double &gx, double &gy)
+{
+    const double gxtmp = (nb[5] - nb[3]) * 0.5, gytmp = (nb[7] - nb[1]) * 0.5;
+    double pmn = nb[6], pmx = nb[6];                                       // nw, n, ne, w, phi(i,j), e, sw, s, se
+    const double lst[8] = {nb[7], nb[8], nb[3], p, nb[5], nb[0], nb[1], nb[2]};
 #pragma unroll
     for (int k = 0; k < 8; ++k) { pmn = min2(pmn, lst[k]); pmx = max2(pmx, lst[k]); }
     pmn = pmn - p;
@@ -112,24 +117,228 @@ __device__ __forceinline__ void limited_gradient(const double (&ph)[9], const do
     const double w3 = -(0.5 + cx) * gxtmp - (0.5 + cy) * gytmp;
     const double w4 = (0.5 - cy) * gytmp - (0.5 + cx) * gxtmp;
     const double qmn = min2(min2(min2(w1, w2), w3), w4), qmx = max2(max2(max2(w1, w2), w3), w4);
-    w1 = fabs(qmn) > fabs(pmn) ? max2(0.0, pmn / qmn) : 1.0;
-    w2 = fabs(qmx) > fabs(pmx) ? max2(0.0, pmx / qmx) : 1.0;
+    // max(c0, pmn/qmn), max(c0, pmx/qmx) (:1463-1474).  A cell that is the smallest (largest) of its neighbourhood has
+    // pmn (pmx) = 0: the quotient is a zero of either sign and max(c0, .) returns c0 -- decided here without the
+    // division, whose zero-numerator case leaves the fast path of the FP64 division sequence (in the first profile
+    // that slow path, at 6 of 32 lanes, was 40 % of all issued instructions)
+    w1 = 1.0;
+    if (fabs(qmn) > fabs(pmn)) w1 = pmn == 0.0 ? 0.0 : max2(0.0, pmn / qmn);
+    w2 = 1.0;
+    if (fabs(qmx) > fabs(pmx)) w2 = pmx == 0.0 ? 0.0 : max2(0.0, pmx / qmx);
     w1 = min2(w1, w2);
     gx = w1 * gxtmp;
     gy = w1 * gytmp;
 }
 
-__device__ __forceinline__ void load9(const double *f, size_t q, int ld, double (&v)[9])
+// limited_gradient for one cell with an arbitrary mask field (the mass gradient over hm): phimask * phi + (1 - phimask)
+// * phi(i,j) as written (:1406-1421)
+__device__ __forceinline__ void limited_gradient(const double (&ph)[9], const double (&mk)[9], double cx, double cy,
+                                                 double &gx, double &gy)
 {
+    double nb[9];
 #pragma unroll
-    for (int dj = -1; dj <= 1; ++dj)
+    for (int k = 0; k < 9; ++k) nb[k] = mk[k] * ph[k] + (1.0 - mk[k]) * ph[4];
+    limit(nb, ph[4], cx, cy, gx, gy);
+}
+
+// the same with a mask known to be exactly 1 or 0 (mmask, tmask; bit k of `bits`): 1 * phi(nb) + 0 * phi(i,j) where the
+// bit is set, 0 * phi(nb) + 1 * phi(i,j) where not -- the reference's two products and sum with the multiplications by
+// one and the subtraction 1 - mask (exact) folded; the product with zero stays (it carries the sign of a zero sum)
+__device__ __forceinline__ void limited_gradient_bits(const double (&ph)[9], unsigned bits, double cx, double cy,
+                                                      double &gx, double &gy)
+{
+    double nb[9];
+    const double p = ph[4];
 #pragma unroll
-        for (int di = -1; di <= 1; ++di) v[(dj + 1) * 3 + di + 1] = f[q + (ptrdiff_t)dj * ld + di];
+    for (int k = 0; k < 9; ++k) {
+        const bool on = (bits >> k) & 1u;
+        const double keep = on ? ph[k] : p, drop = on ? p : ph[k];
+        nb[k] = on ? keep + 0.0 * drop : 0.0 * drop + keep;
+    }
+    limit(nb, p, cx, cy, gx, gy);
 }
 }  // namespace recon
 
+// ---- the product kernel: tiles staged by TMA ---------------------------------------------------------------------
+// A work item is one tile of kRcTX x kRcTY cells of one category.  Consumer warp w owns tile row w (one cell per
+// thread); a producer warp walks the same item / plane sequence and brings the (kRcTX + 4) x (kRcTY + 2) box of each plane
+// -- mm of the category, hm, then the tracer planes in table order -- into a ring of kRcStages shared-memory stages with
+// cp.async.bulk.tensor, so that no consumer ever waits on a global load: it copies its 3 x 3 neighbourhood from the
+// stage to registers, hands the stage back and does the FP64 work.  Boxes that stick out of the block are zero-filled
+// by the TMA unit (those values are never used: only physical cells read their neighbours).  Persistent CTAs, items dealt
+// round-robin with the category as the fastest index (CTAs that run side by side share hm and the halo rows in L2).
+#ifndef EVP_RC_TY
+#define EVP_RC_TY 8
+#endif
+#ifndef EVP_RC_STAGES
+#define EVP_RC_STAGES 6
+#endif
+#ifndef EVP_RC_BLOCKS
+#define EVP_RC_BLOCKS 3
+#endif
+constexpr int kRcTX = 32, kRcTY = EVP_RC_TY, kRcStages = EVP_RC_STAGES, kRcBlocksPerSM = EVP_RC_BLOCKS;
+constexpr int kRcBoxW = kRcTX + 4, kRcBoxH = kRcTY + 2;      // box starts must be 16-byte aligned: two columns each side
+constexpr int kRcBoxBytes = kRcBoxW * kRcBoxH * 8;                         // 2880
+constexpr int kRcStageBytes = (kRcBoxBytes + 127) / 128 * 128;             // 2944
+
+struct ReconTmaArgs {
+    ReconArgs a;
+    int tiles_x, tiles_y;
+    int plane_hm, plane_mm, plane_tm;          // plane numbers (z coordinate of the tensor map) of hm, mm(0), tm(1,1)
+};
+
+__global__ void __launch_bounds__((kRcTY + 1) * 32, kRcBlocksPerSM)
+reconstruct_tma_kernel(const __grid_constant__ CUtensorMap map, const __grid_constant__ ReconTmaArgs p)
+{
+    using namespace recon;
+    __shared__ __align__(128) unsigned char ring[kRcStages * kRcStageBytes];
+    __shared__ unsigned long long full_bar[kRcStages], empty_bar[kRcStages];
+    const ReconArgs &a = p.a;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < kRcStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], kRcTY); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+    const int ncat1 = a.ncat + 1;
+    const long long nitems = (long long)p.tiles_x * p.tiles_y * ncat1;
+    int stage = 0;
+    unsigned phase = 0;
+
+    if (warp == kRcTY) {
+        // ------------------------------ producer ------------------------------
+        if (lane != 0) return;
+        for (long long it = blockIdx.x; it < nitems; it += gridDim.x) {
+            const int n = (int)(it % ncat1);
+            const long long tile = it / ncat1;
+            const int x0 = (int)(tile % p.tiles_x) * kRcTX - 2, y0 = (int)(tile / p.tiles_x) * kRcTY - 1;
+            const int nplanes = 2 + (n > 0 ? a.ntrace : 0);
+            for (int k = 0; k < nplanes; ++k) {
+                const int z = k == 0 ? p.plane_mm + n : k == 1 ? p.plane_hm : p.plane_tm + (n - 1) * a.ntrace + (k - 2);
+                mbar_wait(&empty_bar[stage], phase ^ 1u);
+                mbar_expect_tx(&full_bar[stage], kRcBoxBytes);
+                tma_load_3d(ring + (size_t)stage * kRcStageBytes, &map, &full_bar[stage], x0, y0, z);
+                if (++stage == kRcStages) { stage = 0; phase ^= 1u; }
+            }
+        }
+        return;
+    }
+
+    // ------------------------------ consumers ------------------------------
+    // stage -> registers: the 3 x 3 neighbourhood of this thread's cell (or only its centre), then the stage goes back
+    auto take = [&](double (&v)[9], bool all) {
+        mbar_wait(&full_bar[stage], phase);
+        const double *b = reinterpret_cast<const double *>(ring + (size_t)stage * kRcStageBytes) + (warp + 1) * kRcBoxW + lane + 2;
+        if (all) {
+#pragma unroll
+            for (int dj = -1; dj <= 1; ++dj)
+#pragma unroll
+                for (int di = -1; di <= 1; ++di) v[(dj + 1) * 3 + di + 1] = b[dj * kRcBoxW + di];
+        } else {
+            v[4] = b[0];
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[stage]);
+        if (++stage == kRcStages) { stage = 0; phase ^= 1u; }
+    };
+
+    for (long long it = blockIdx.x; it < nitems; it += gridDim.x) {
+        const int n = (int)(it % ncat1);
+        const long long tile = it / ncat1;
+        const int c = (int)(tile % p.tiles_x) * kRcTX + lane, r = (int)(tile / p.tiles_x) * kRcTY + warp;
+        const bool valid = c < a.nxb && r < a.nyb;
+        const bool interior = c >= 1 && c <= a.nxb - 2 && r >= 1 && r <= a.nyb - 2;
+        const size_t q = (size_t)r * a.ld + c;
+        double xav = 0.0, yav = 0.0, xxav = 0.0, yyav = 0.0;
+        if (interior) { xav = a.xav[q]; yav = a.yav[q]; if (n > 0) { xxav = a.xxav[q]; yyav = a.yyav[q]; } }
+
+        double ph[9];
+        take(ph, interior);                                                // mm of this category
+        const double m = ph[4];
+        // icells list of this category: every cell of the block for open water (:930-943), the physical cells for ice
+        // (:999-1010)
+        const bool incell = valid && (n == 0 || interior) && m > puny;
+        const double mc = incell ? m : 0.0;
+        double mx = 0.0, my = 0.0;
+        unsigned mbits = 0;                                                // mmask of the neighbourhood (:958-971)
+        if (interior) {
+#pragma unroll
+            for (int k = 0; k < 9; ++k) mbits |= (ph[k] > puny ? 1u : 0u) << k;
+        }
+        {
+            double mk[9];
+            take(mk, interior);                                            // hm
+            if (interior && mk[4] > puny) limited_gradient(ph, mk, xav, yav, mx, my);     // limited over the land mask
+        }
+        if (valid) {
+            a.mc[(size_t)n * a.pe + q] = mc;
+            a.mx[(size_t)n * a.pe + q] = mx;
+            a.my[(size_t)n * a.pe + q] = my;
+        }
+        if (n == 0 || a.ntrace == 0) continue;
+
+        const size_t t0 = (size_t)(n - 1) * a.ntrace * a.pe + q;           // this cell in tracer plane 0 of category n
+        double mxav = 0.0, myav = 0.0;
+        if (incell) {                                                      // :1139-1146
+            const double nx = mx * xxav + mc * xav, ny = my * yyav + mc * yav;
+            mxav = nx == 0.0 ? nx : nx / m;                                // m > 0: a zero keeps its sign; no slow path
+            myav = ny == 0.0 ? ny : ny / m;
+        }
+        // per tracer with dependents: centre of area * tracer and its tmask over the neighbourhood (:977-990), kept for
+        // the type-2 tracers that follow
+        double mtxav[kRemapMaxParents], mtyav[kRemapMaxParents];
+        unsigned short tbits[kRemapMaxParents];
+
+        for (int nt = 0; nt < a.ntrace; ++nt) {
+            const size_t o = t0 + (size_t)nt * a.pe;
+            double tc = 0.0, tx = 0.0, ty = 0.0;
+            const int type = a.ttype[nt];
+            if (type == 1) {                                               // :1150-1208
+                take(ph, incell);
+                if (incell) {
+                    const double t = ph[4];
+                    limited_gradient_bits(ph, mbits, mxav, myav, tx, ty);
+                    tc = t - tx * mxav - ty * myav;
+                    const int sl = a.slot[nt];
+                    if (sl >= 0) {                                         // centre of area * tracer for its dependents
+                        unsigned tb = 0;
+#pragma unroll
+                        for (int k = 0; k < 9; ++k) tb |= (fabs(ph[k]) > puny ? 1u : 0u) << k;
+                        tb &= mbits;
+                        double ax = 0.0, ay = 0.0;
+                        if ((tb >> 4) & 1u) {
+                            const double w1 = mc * tc, w2 = mc * tx + mx * tc, w3 = mc * ty + my * tc;
+                            const double w7 = 1.0 / (m * t);
+                            ax = (w1 * xav + w2 * xxav) * w7;
+                            ay = (w1 * yav + w3 * yyav) * w7;
+                        }
+                        mtxav[sl] = ax; mtyav[sl] = ay; tbits[sl] = (unsigned short)tb;
+                    }
+                }
+            } else if (type == 2) {                                        // :1210-1229
+                const int sl = a.slot[a.parent[nt]];
+                const unsigned tb = incell ? tbits[sl] : 0u;
+                const bool grad = (tb >> 4) & 1u;
+                take(ph, grad);
+                if (incell) {
+                    const double ax = mtxav[sl], ay = mtyav[sl];
+                    if (grad) limited_gradient_bits(ph, tb, ax, ay, tx, ty);
+                    tc = ph[4] - tx * ax - ty * ay;
+                }
+            } else {                                                       // :1231-1239
+                take(ph, false);
+                if (incell) tc = ph[4];
+            }
+            if (valid) { a.tc[o] = tc; a.tx[o] = tx; a.ty[o] = ty; }
+        }
+    }
+}
+
+// ---- the same work, one thread per cell and category straight from global memory (EVP_B200_KERNEL=sweep: the build without TMA) ---------
 // grid: (ceil(nxb / 128), nyb, ncat + 1); blockIdx.z = category
-__global__ void __launch_bounds__(128) reconstruct_kernel(const __grid_constant__ ReconArgs a)
+__global__ void __launch_bounds__(128, 8) reconstruct_kernel(const __grid_constant__ ReconArgs a)
 {
     using namespace recon;
     const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y, n = blockIdx.z;
@@ -143,10 +352,14 @@ __global__ void __launch_bounds__(128) reconstruct_kernel(const __grid_constant_
     const bool incell = (n == 0 || interior) && m > puny;
     const double mc = incell ? m : 0.0;
     double mx = 0.0, my = 0.0;
-    double ph[9], mk[9];
+    double ph[9];
+    unsigned mbits = 0;                                                    // mmask of the neighbourhood (:958-971)
     if (interior) {
         load9(mm, q, a.ld, ph);
+#pragma unroll
+        for (int k = 0; k < 9; ++k) mbits |= (ph[k] > puny ? 1u : 0u) << k;
         if (a.hm[q] > puny) {                                              // mass gradient, limited over the land mask
+            double mk[9];
             load9(a.hm, q, a.ld, mk);
             limited_gradient(ph, mk, a.xav[q], a.yav[q], mx, my);
         }
@@ -164,48 +377,54 @@ __global__ void __launch_bounds__(128) reconstruct_kernel(const __grid_constant_
         }
         return;
     }
-    // mmask of the neighbourhood (:958-971: 1 where mm > puny, ghost cells included); ph still holds mm
-#pragma unroll
-    for (int k = 0; k < 9; ++k) mk[k] = ph[k] > puny ? 1.0 : 0.0;
     const double xav = a.xav[q], yav = a.yav[q], xxav = a.xxav[q], yyav = a.yyav[q];
-    const double mxav = (mx * xxav + mc * xav) / m, myav = (my * yyav + mc * yav) / m;     // :1139-1146
+    const double nx = mx * xxav + mc * xav, ny = my * yyav + mc * yav;                     // :1139-1146
+    const double mxav = nx == 0.0 ? nx : nx / m, myav = ny == 0.0 ? ny : ny / m;           // m > 0: a zero keeps its sign
+    // per tracer with dependents: centre of area * tracer and its tmask over the neighbourhood (:977-990), kept for the
+    // type-2 tracers that follow
     double mtxav[kRemapMaxParents], mtyav[kRemapMaxParents];
+    unsigned short tbits[kRemapMaxParents];
 
     for (int nt = 0; nt < a.ntrace; ++nt) {
         const double *tm = a.tm + (size_t)(n - 1) * a.ntrace * a.pe + (size_t)nt * a.pe;
         const size_t o = t0 + (size_t)nt * a.pe;
-        const double t = tm[q];
         double tc = 0.0, tx = 0.0, ty = 0.0;
         const int type = a.ttype[nt];
         if (type == 1) {                                                   // :1150-1208
             load9(tm, q, a.ld, ph);
-            limited_gradient(ph, mk, mxav, myav, tx, ty);
+            const double t = ph[4];
+            limited_gradient_bits(ph, mbits, mxav, myav, tx, ty);
             tc = t - tx * mxav - ty * myav;
             const int sl = a.slot[nt];
             if (sl >= 0) {                                                 // centre of area * tracer for its dependents
+                unsigned tb = 0;
+#pragma unroll
+                for (int k = 0; k < 9; ++k) tb |= (fabs(ph[k]) > puny ? 1u : 0u) << k;
+                tb &= mbits;
                 double ax = 0.0, ay = 0.0;
-                if (fabs(t) > puny) {                                      // tmask (:977-990), mm > puny holds here
+                if ((tb >> 4) & 1u) {
                     const double w1 = mc * tc, w2 = mc * tx + mx * tc, w3 = mc * ty + my * tc;
                     const double w7 = 1.0 / (m * t);
                     ax = (w1 * xav + w2 * xxav) * w7;
                     ay = (w1 * yav + w3 * yyav) * w7;
                 }
-                mtxav[sl] = ax; mtyav[sl] = ay;
+                mtxav[sl] = ax; mtyav[sl] = ay; tbits[sl] = (unsigned short)tb;
             }
         } else if (type == 2) {                                            // :1210-1229
-            const int p1 = a.parent[nt], sl = a.slot[p1];
-            const double *tp = a.tm + (size_t)(n - 1) * a.ntrace * a.pe + (size_t)p1 * a.pe;
-            double pk[9], tk[9];
-            load9(tp, q, a.ld, pk);
-#pragma unroll
-            for (int k = 0; k < 9; ++k) tk[k] = (mk[k] > puny && fabs(pk[k]) > puny) ? 1.0 : 0.0;   // tmask of the parent
-            if (tk[4] > puny) {
+            const int sl = a.slot[a.parent[nt]];
+            const unsigned tb = tbits[sl];
+            const double ax = mtxav[sl], ay = mtyav[sl];
+            double t;
+            if ((tb >> 4) & 1u) {
                 load9(tm, q, a.ld, ph);
-                limited_gradient(ph, tk, mtxav[sl], mtyav[sl], tx, ty);
+                t = ph[4];
+                limited_gradient_bits(ph, tb, ax, ay, tx, ty);
+            } else {
+                t = tm[q];
             }
-            tc = t - tx * mtxav[sl] - ty * mtyav[sl];
+            tc = t - tx * ax - ty * ay;
         } else if (type == 3) {                                            // :1231-1239
-            tc = t;
+            tc = tm[q];
         }
         a.tc[o] = tc; a.tx[o] = tx; a.ty[o] = ty;
     }

@@ -290,6 +290,9 @@ void emu_tma_load(unsigned dst, const CUtensorMap *map, unsigned bar, int rank, 
     TMap t;
     memcpy(&t, map, sizeof(t));
     if ((int)t.rank != rank) { fprintf(stderr, "cuda_emu: tensor map rank mismatch\n"); abort(); }
+    // the hardware faults ("illegal instruction") on a box that does not start on a 16-byte boundary of the innermost
+    // dimension, or whose shared-memory destination is not 128-byte aligned
+    if (((long long)x * (long long)t.esize) % 16 != 0) { fprintf(stderr, "cuda_emu: TMA box start x = %d is not 16-byte aligned\n", x); abort(); }
     char *d = (char *)emu::from_handle(dst);
     const long long c0[3] = {x, y, z};
     for (uint64_t k = 0; k < t.box[2]; ++k)
