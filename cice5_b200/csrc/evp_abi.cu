@@ -149,7 +149,6 @@ struct evp_handle {
     // tm(ntrace, ncat), mc mx my (0:ncat), tc tx ty (ntrace, ncat) planes of the arena's pitch in one allocation
     double *rc = nullptr;
     ReconArgs rc_args;
-    CUtensorMap rc_map;           // (column, row, plane) over the reconstruction planes, boxes of one tile + its ring
     bool rc_loaded = false;
     cudaEvent_t tev[3] = {nullptr, nullptr, nullptr};     // transport stage: start, kernels done, ghost updates done
     double tr_ms[4] = {0.0, 0.0, 0.0, 0.0};               // departure kernels / halos, reconstruction kernel / halos
@@ -1780,18 +1779,10 @@ void build_reconstruct(evp_handle *h, std::vector<Op> &ops)
     B.sync();
     stage_mark(B, 0);
     B.op([h, l](Launcher &L) {
-        const dim3 grid((h->nxb + 127) / 128, h->nyb, l.ncat + 1);
-        if (h->use_tma) {
-            ReconTmaArgs p;
-            p.a = h->rc_args;
-            p.tiles_x = (h->nxb + kRcTX - 1) / kRcTX; p.tiles_y = (h->nyb + kRcTY - 1) / kRcTY;
-            p.plane_hm = 0; p.plane_mm = (int)l.mm(0); p.plane_tm = (int)l.tm(0);
-            const long long items = (long long)p.tiles_x * p.tiles_y * (l.ncat + 1);
-            const long long slots = (long long)h->sm_count * kRcBlocksPerSM;
-            reconstruct_tma_kernel<<<(unsigned)(items < slots ? items : slots), (kRcTY + 1) * 32, 0, L.s()>>>(h->rc_map, p);
-        } else {
-            reconstruct_kernel<<<grid, 128, 0, L.s()>>>(h->rc_args);
-        }
+        int nparents = 0;
+        for (int nt = 0; nt < l.ntrace; ++nt) if (h->rc_args.slot[nt] >= nparents) nparents = h->rc_args.slot[nt] + 1;
+        const dim3 tiles((h->nxb + kRcDirectW - 1) / kRcDirectW, (h->nyb + kRcDirectH - 1) / kRcDirectH, l.ncat + 1);
+        reconstruct_kernel<<<tiles, dim3(kRcDirectW, kRcDirectH), (size_t)nparents * 128 * 18, L.s()>>>(h->rc_args, nparents);
         ++L.n;
         CK(cudaGetLastError());
         return EVP_OK;
@@ -1874,20 +1865,6 @@ int evp_gpu_set_transport_tracers(evp_handle_t *h, int ncat, int ntrace, const i
     a.tc = pl(l.trc(0, 0)); a.tx = pl(l.trc(1, 0)); a.ty = pl(l.trc(2, 0));
     h->rc_args = a;
     h->rc_loaded = false;
-    if (h->use_tma) {
-        EncodeTiledFn enc = nullptr;
-        TRY(tensor_map_encoder(&enc));
-        const cuuint64_t dims[3] = {(cuuint64_t)h->ld, (cuuint64_t)h->nyb, (cuuint64_t)l.planes()};
-        const cuuint64_t strides[2] = {(cuuint64_t)h->ld * 8, (cuuint64_t)h->plane_elems * 8};
-        const cuuint32_t box[3] = {(cuuint32_t)kRcBoxW, (cuuint32_t)kRcBoxH, 1}, estr[3] = {1, 1, 1};
-        const CUresult r = enc(&h->rc_map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, h->rc, dims, strides, box, estr,
-                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
-                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (r != CUDA_SUCCESS) {
-            snprintf(g_cuda_err, sizeof(g_cuda_err), "cuTensorMapEncodeTiled(reconstruction) failed: %d", (int)r);
-            return EVP_ERR_CUDA;
-        }
-    }
     const double *src[5] = {hm, xav, yav, xxav, yyav};
     for (int k = 0; k < 5; ++k) TRY(h2d_any(h, pl(k), src[k], 0));
     TRY(h2d_flush(h));

@@ -7,7 +7,6 @@
 // vvel straight from the resident EVP state: the velocities never leave the device between evp and this stage.
 #pragma once
 #include "evp_kernels.cuh"
-#include "evp_subcycle_tma.cuh"     // mbarrier / TMA helpers
 
 namespace evp {
 
@@ -149,200 +148,49 @@ __device__ __forceinline__ void limited_gradient_bits(const double (&ph)[9], uns
 {
     double nb[9];
     const double p = ph[4];
+    const double z = 0.0 * p;
+    if (bits == 0x1ffu) {                                                  // every neighbour present (pack ice)
 #pragma unroll
-    for (int k = 0; k < 9; ++k) {
-        const bool on = (bits >> k) & 1u;
-        const double keep = on ? ph[k] : p, drop = on ? p : ph[k];
-        nb[k] = on ? keep + 0.0 * drop : 0.0 * drop + keep;
+        for (int k = 0; k < 9; ++k) nb[k] = ph[k] + z;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) nb[k] = (bits >> k) & 1u ? ph[k] + z : 0.0 * ph[k] + p;
     }
     limit(nb, p, cx, cy, gx, gy);
 }
 }  // namespace recon
 
-// ---- the product kernel: tiles staged by TMA ---------------------------------------------------------------------
-// A work item is one tile of kRcTX x kRcTY cells of one category.  Consumer warp w owns tile row w (one cell per
-// thread); a producer warp walks the same item / plane sequence and brings the (kRcTX + 4) x (kRcTY + 2) box of each plane
-// -- mm of the category, hm, then the tracer planes in table order -- into a ring of kRcStages shared-memory stages with
-// cp.async.bulk.tensor, so that no consumer ever waits on a global load: it copies its 3 x 3 neighbourhood from the
-// stage to registers, hands the stage back and does the FP64 work.  Boxes that stick out of the block are zero-filled
-// by the TMA unit (those values are never used: only physical cells read their neighbours).  Persistent CTAs, items dealt
-// round-robin with the category as the fastest index (CTAs that run side by side share hm and the halo rows in L2).
-#ifndef EVP_RC_TY
-#define EVP_RC_TY 8
+// ---- the kernel: one thread per cell and category ------------------------------------------------------------------
+// grid: (ceil(nxb / 32), ceil(nyb / 4), ncat + 1), block 32 x 4: a warp is 32 consecutive cells of a row (256-byte
+// coalesced loads and stores), the four rows of a block share their neighbour rows in L1; blockIdx.z = category.
+// Measured on the 0.1-degree grid, 5 categories x 11 tracers (profiles/r02_reconstruct.md): the work is ~3000 issued
+// instructions per cell and category (no FMA contraction, FP64 min / max as compare + select), a warp brings only 256
+// new bytes per tracer plane and then waits for them, so the planes ahead are requested from L2 early
+// (prefetch.global.L2); staging the tiles with TMA into a shared-memory ring was built and measured slower (8.4 ms
+// against 6.5 ms: the producer / consumer lockstep per plane and 24 instead of 32 resident warps cost more than the
+// exposed loads).
+#ifndef EVP_RC_DIRECT_BLOCKS
+#define EVP_RC_DIRECT_BLOCKS 8
 #endif
-#ifndef EVP_RC_STAGES
-#define EVP_RC_STAGES 6
+#ifndef EVP_RC_DIRECT_H
+#define EVP_RC_DIRECT_H 4
 #endif
-#ifndef EVP_RC_BLOCKS
-#define EVP_RC_BLOCKS 3
+#ifndef EVP_RC_L2_AHEAD
+#define EVP_RC_L2_AHEAD 4
 #endif
-constexpr int kRcTX = 32, kRcTY = EVP_RC_TY, kRcStages = EVP_RC_STAGES, kRcBlocksPerSM = EVP_RC_BLOCKS;
-constexpr int kRcBoxW = kRcTX + 4, kRcBoxH = kRcTY + 2;      // box starts must be 16-byte aligned: two columns each side
-constexpr int kRcBoxBytes = kRcBoxW * kRcBoxH * 8;                         // 2880
-constexpr int kRcStageBytes = (kRcBoxBytes + 127) / 128 * 128;             // 2944
-
-struct ReconTmaArgs {
-    ReconArgs a;
-    int tiles_x, tiles_y;
-    int plane_hm, plane_mm, plane_tm;          // plane numbers (z coordinate of the tensor map) of hm, mm(0), tm(1,1)
-};
-
-__global__ void __launch_bounds__((kRcTY + 1) * 32, kRcBlocksPerSM)
-reconstruct_tma_kernel(const __grid_constant__ CUtensorMap map, const __grid_constant__ ReconTmaArgs p)
+constexpr int kRcDirectH = EVP_RC_DIRECT_H, kRcDirectW = 128 / kRcDirectH;
+// dynamic shared memory: per tracer with dependents (slot) and thread, the centre of area * tracer (x, y) and the tmask
+// bits of the neighbourhood (:977-990), kept for the type-2 tracers that follow: 18 bytes x 128 x slots
+__global__ void __launch_bounds__(128, EVP_RC_DIRECT_BLOCKS) reconstruct_kernel(const __grid_constant__ ReconArgs a, int nparents)
 {
     using namespace recon;
-    __shared__ __align__(128) unsigned char ring[kRcStages * kRcStageBytes];
-    __shared__ unsigned long long full_bar[kRcStages], empty_bar[kRcStages];
-    const ReconArgs &a = p.a;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (threadIdx.x == 0) {
-#pragma unroll
-        for (int s = 0; s < kRcStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], kRcTY); }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    }
-    __syncthreads();
-    const int ncat1 = a.ncat + 1;
-    const long long nitems = (long long)p.tiles_x * p.tiles_y * ncat1;
-    int stage = 0;
-    unsigned phase = 0;
-
-    if (warp == kRcTY) {
-        // ------------------------------ producer ------------------------------
-        if (lane != 0) return;
-        for (long long it = blockIdx.x; it < nitems; it += gridDim.x) {
-            const int n = (int)(it % ncat1);
-            const long long tile = it / ncat1;
-            const int x0 = (int)(tile % p.tiles_x) * kRcTX - 2, y0 = (int)(tile / p.tiles_x) * kRcTY - 1;
-            const int nplanes = 2 + (n > 0 ? a.ntrace : 0);
-            for (int k = 0; k < nplanes; ++k) {
-                const int z = k == 0 ? p.plane_mm + n : k == 1 ? p.plane_hm : p.plane_tm + (n - 1) * a.ntrace + (k - 2);
-                mbar_wait(&empty_bar[stage], phase ^ 1u);
-                mbar_expect_tx(&full_bar[stage], kRcBoxBytes);
-                tma_load_3d(ring + (size_t)stage * kRcStageBytes, &map, &full_bar[stage], x0, y0, z);
-                if (++stage == kRcStages) { stage = 0; phase ^= 1u; }
-            }
-        }
-        return;
-    }
-
-    // ------------------------------ consumers ------------------------------
-    // stage -> registers: the 3 x 3 neighbourhood of this thread's cell (or only its centre), then the stage goes back
-    auto take = [&](double (&v)[9], bool all) {
-        mbar_wait(&full_bar[stage], phase);
-        const double *b = reinterpret_cast<const double *>(ring + (size_t)stage * kRcStageBytes) + (warp + 1) * kRcBoxW + lane + 2;
-        if (all) {
-#pragma unroll
-            for (int dj = -1; dj <= 1; ++dj)
-#pragma unroll
-                for (int di = -1; di <= 1; ++di) v[(dj + 1) * 3 + di + 1] = b[dj * kRcBoxW + di];
-        } else {
-            v[4] = b[0];
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty_bar[stage]);
-        if (++stage == kRcStages) { stage = 0; phase ^= 1u; }
-    };
-
-    for (long long it = blockIdx.x; it < nitems; it += gridDim.x) {
-        const int n = (int)(it % ncat1);
-        const long long tile = it / ncat1;
-        const int c = (int)(tile % p.tiles_x) * kRcTX + lane, r = (int)(tile / p.tiles_x) * kRcTY + warp;
-        const bool valid = c < a.nxb && r < a.nyb;
-        const bool interior = c >= 1 && c <= a.nxb - 2 && r >= 1 && r <= a.nyb - 2;
-        const size_t q = (size_t)r * a.ld + c;
-        double xav = 0.0, yav = 0.0, xxav = 0.0, yyav = 0.0;
-        if (interior) { xav = a.xav[q]; yav = a.yav[q]; if (n > 0) { xxav = a.xxav[q]; yyav = a.yyav[q]; } }
-
-        double ph[9];
-        take(ph, interior);                                                // mm of this category
-        const double m = ph[4];
-        // icells list of this category: every cell of the block for open water (:930-943), the physical cells for ice
-        // (:999-1010)
-        const bool incell = valid && (n == 0 || interior) && m > puny;
-        const double mc = incell ? m : 0.0;
-        double mx = 0.0, my = 0.0;
-        unsigned mbits = 0;                                                // mmask of the neighbourhood (:958-971)
-        if (interior) {
-#pragma unroll
-            for (int k = 0; k < 9; ++k) mbits |= (ph[k] > puny ? 1u : 0u) << k;
-        }
-        {
-            double mk[9];
-            take(mk, interior);                                            // hm
-            if (interior && mk[4] > puny) limited_gradient(ph, mk, xav, yav, mx, my);     // limited over the land mask
-        }
-        if (valid) {
-            a.mc[(size_t)n * a.pe + q] = mc;
-            a.mx[(size_t)n * a.pe + q] = mx;
-            a.my[(size_t)n * a.pe + q] = my;
-        }
-        if (n == 0 || a.ntrace == 0) continue;
-
-        const size_t t0 = (size_t)(n - 1) * a.ntrace * a.pe + q;           // this cell in tracer plane 0 of category n
-        double mxav = 0.0, myav = 0.0;
-        if (incell) {                                                      // :1139-1146
-            const double nx = mx * xxav + mc * xav, ny = my * yyav + mc * yav;
-            mxav = nx == 0.0 ? nx : nx / m;                                // m > 0: a zero keeps its sign; no slow path
-            myav = ny == 0.0 ? ny : ny / m;
-        }
-        // per tracer with dependents: centre of area * tracer and its tmask over the neighbourhood (:977-990), kept for
-        // the type-2 tracers that follow
-        double mtxav[kRemapMaxParents], mtyav[kRemapMaxParents];
-        unsigned short tbits[kRemapMaxParents];
-
-        for (int nt = 0; nt < a.ntrace; ++nt) {
-            const size_t o = t0 + (size_t)nt * a.pe;
-            double tc = 0.0, tx = 0.0, ty = 0.0;
-            const int type = a.ttype[nt];
-            if (type == 1) {                                               // :1150-1208
-                take(ph, incell);
-                if (incell) {
-                    const double t = ph[4];
-                    limited_gradient_bits(ph, mbits, mxav, myav, tx, ty);
-                    tc = t - tx * mxav - ty * myav;
-                    const int sl = a.slot[nt];
-                    if (sl >= 0) {                                         // centre of area * tracer for its dependents
-                        unsigned tb = 0;
-#pragma unroll
-                        for (int k = 0; k < 9; ++k) tb |= (fabs(ph[k]) > puny ? 1u : 0u) << k;
-                        tb &= mbits;
-                        double ax = 0.0, ay = 0.0;
-                        if ((tb >> 4) & 1u) {
-                            const double w1 = mc * tc, w2 = mc * tx + mx * tc, w3 = mc * ty + my * tc;
-                            const double w7 = 1.0 / (m * t);
-                            ax = (w1 * xav + w2 * xxav) * w7;
-                            ay = (w1 * yav + w3 * yyav) * w7;
-                        }
-                        mtxav[sl] = ax; mtyav[sl] = ay; tbits[sl] = (unsigned short)tb;
-                    }
-                }
-            } else if (type == 2) {                                        // :1210-1229
-                const int sl = a.slot[a.parent[nt]];
-                const unsigned tb = incell ? tbits[sl] : 0u;
-                const bool grad = (tb >> 4) & 1u;
-                take(ph, grad);
-                if (incell) {
-                    const double ax = mtxav[sl], ay = mtyav[sl];
-                    if (grad) limited_gradient_bits(ph, tb, ax, ay, tx, ty);
-                    tc = ph[4] - tx * ax - ty * ay;
-                }
-            } else {                                                       // :1231-1239
-                take(ph, false);
-                if (incell) tc = ph[4];
-            }
-            if (valid) { a.tc[o] = tc; a.tx[o] = tx; a.ty[o] = ty; }
-        }
-    }
-}
-
-// ---- the same work, one thread per cell and category straight from global memory (EVP_B200_KERNEL=sweep: the build without TMA) ---------
-// grid: (ceil(nxb / 128), nyb, ncat + 1); blockIdx.z = category
-__global__ void __launch_bounds__(128, 8) reconstruct_kernel(const __grid_constant__ ReconArgs a)
-{
-    using namespace recon;
-    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y, n = blockIdx.z;
-    if (c >= a.nxb) return;
+    extern __shared__ double par[];
+    const int tid = threadIdx.y * blockDim.x + threadIdx.x;
+    double *mtxav = par + tid, *mtyav = par + (size_t)nparents * 128 + tid;
+    unsigned short *tbits = reinterpret_cast<unsigned short *>(par + (size_t)2 * nparents * 128) + tid;
+    // a block is a tile of kRcDirectW x kRcDirectH cells: the rows of a tile share their neighbour rows in L1
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y * blockDim.y + threadIdx.y, n = blockIdx.z;
+    if (c >= a.nxb || r >= a.nyb) return;
     const size_t q = (size_t)r * a.ld + c;
     const bool interior = c >= 1 && c <= a.nxb - 2 && r >= 1 && r <= a.nyb - 2;
     const double *mm = a.mm + (size_t)n * a.pe;
@@ -380,23 +228,37 @@ __global__ void __launch_bounds__(128, 8) reconstruct_kernel(const __grid_consta
     const double xav = a.xav[q], yav = a.yav[q], xxav = a.xxav[q], yyav = a.yyav[q];
     const double nx = mx * xxav + mc * xav, ny = my * yyav + mc * yav;                     // :1139-1146
     const double mxav = nx == 0.0 ? nx : nx / m, myav = ny == 0.0 ? ny : ny / m;           // m > 0: a zero keeps its sign
-    // per tracer with dependents: centre of area * tracer and its tmask over the neighbourhood (:977-990), kept for the
-    // type-2 tracers that follow
-    double mtxav[kRemapMaxParents], mtyav[kRemapMaxParents];
-    unsigned short tbits[kRemapMaxParents];
-
+    const double *tm0 = a.tm + t0;
+#if EVP_RC_L2_AHEAD
+    // A warp brings 256 new bytes per tracer plane and waits for them: too little in flight to keep HBM busy.  Ask L2
+    // for this cell's line of the planes ahead now (the neighbour rows are the neighbour warps' lines)
+#pragma unroll 1
+    for (int nt = 1; nt < a.ntrace && nt <= EVP_RC_L2_AHEAD; ++nt)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(tm0 + (size_t)nt * a.pe));
+#endif
     for (int nt = 0; nt < a.ntrace; ++nt) {
-        const double *tm = a.tm + (size_t)(n - 1) * a.ntrace * a.pe + (size_t)nt * a.pe;
         const size_t o = t0 + (size_t)nt * a.pe;
-        double tc = 0.0, tx = 0.0, ty = 0.0;
+        load9(tm0 + (size_t)nt * a.pe, 0, a.ld, ph);
+#if EVP_RC_L2_AHEAD
+        if (nt + EVP_RC_L2_AHEAD + 1 < a.ntrace)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(tm0 + (size_t)(nt + EVP_RC_L2_AHEAD + 1) * a.pe));
+#endif
+        const double t = ph[4];
         const int type = a.ttype[nt];
-        if (type == 1) {                                                   // :1150-1208
-            load9(tm, q, a.ld, ph);
-            const double t = ph[4];
-            limited_gradient_bits(ph, mbits, mxav, myav, tx, ty);
-            tc = t - tx * mxav - ty * myav;
+        double tc, tx = 0.0, ty = 0.0;
+        if (type == 3) {                                                   // :1231-1239
+            tc = t;
+        } else {
+            unsigned bits = mbits;                                         // type 1 (:1150-1208): mmask, centre of mass
+            double cx = mxav, cy = myav;
+            if (type == 2) {                                               // :1210-1229: the parent's tmask and centre
+                const int sl = a.slot[a.parent[nt]] * 128;
+                bits = tbits[sl]; cx = mtxav[sl]; cy = mtyav[sl];
+            }
+            if ((bits >> 4) & 1u) limited_gradient_bits(ph, bits, cx, cy, tx, ty);
+            tc = t - tx * cx - ty * cy;
             const int sl = a.slot[nt];
-            if (sl >= 0) {                                                 // centre of area * tracer for its dependents
+            if (type == 1 && sl >= 0) {                                    // centre of area * tracer for its dependents
                 unsigned tb = 0;
 #pragma unroll
                 for (int k = 0; k < 9; ++k) tb |= (fabs(ph[k]) > puny ? 1u : 0u) << k;
@@ -408,23 +270,8 @@ __global__ void __launch_bounds__(128, 8) reconstruct_kernel(const __grid_consta
                     ax = (w1 * xav + w2 * xxav) * w7;
                     ay = (w1 * yav + w3 * yyav) * w7;
                 }
-                mtxav[sl] = ax; mtyav[sl] = ay; tbits[sl] = (unsigned short)tb;
+                mtxav[sl * 128] = ax; mtyav[sl * 128] = ay; tbits[sl * 128] = (unsigned short)tb;
             }
-        } else if (type == 2) {                                            // :1210-1229
-            const int sl = a.slot[a.parent[nt]];
-            const unsigned tb = tbits[sl];
-            const double ax = mtxav[sl], ay = mtyav[sl];
-            double t;
-            if ((tb >> 4) & 1u) {
-                load9(tm, q, a.ld, ph);
-                t = ph[4];
-                limited_gradient_bits(ph, tb, ax, ay, tx, ty);
-            } else {
-                t = tm[q];
-            }
-            tc = t - tx * ax - ty * ay;
-        } else if (type == 3) {                                            // :1231-1239
-            tc = tm[q];
         }
         a.tc[o] = tc; a.tx[o] = tx; a.ty[o] = ty;
     }

@@ -135,6 +135,8 @@ def _rewrite_asm(text: str) -> str:
             rep = f"emu_bar_arrive({template.split()[1].rstrip(',')}, {ins[0]});"
         elif template.startswith("bar.sync"):
             rep = f"emu_bar_sync({template.split()[1].rstrip(',')}, {ins[0]});"
+        elif template.startswith("prefetch."):
+            rep = f"(void)({ins[0]});"                  # a hint: no architectural effect
         elif template.startswith("fence."):
             rep = "std::atomic_thread_fence(std::memory_order_seq_cst);"
         else:
