@@ -236,6 +236,75 @@ def construct_fields(dom, tracer_type, depend, has_dependents, hm, xav, yav, xxa
     return o
 
 
+def triangles(north, dpx, dpy, dxu, dyu, coords=True):
+    """locate_triangles (+ triangle_coordinates, integral_order 3) of source/ice_transport_remap.F90:1680-3187 for one
+    edge orientation on one block (ny_block, nx_block).  Returns a dict xp, yp (6, 4, ny, nx), iflux, jflux (Fortran
+    indices), triarea (6, ny, nx), icells (6), edgearea."""
+    nyb, nxb = dpx.shape
+    o = {"xp": np.full((6, 4, nyb, nxb), np.nan), "yp": np.full((6, 4, nyb, nxb), np.nan),
+         "iflux": np.zeros((6, nyb, nxb), dtype=np.int32), "jflux": np.zeros((6, nyb, nxb), dtype=np.int32),
+         "triarea": np.full((6, nyb, nxb), np.nan), "icells": np.zeros(6, dtype=np.int32), "edgearea": np.zeros((nyb, nxb))}
+    rc = lib().remap_oracle_triangles(C.c_int(nxb), C.c_int(nyb), C.c_int(int(north)), C.c_int(int(coords)), _dp(dpx), _dp(dpy),
+                                      _dp(dxu), _dp(dyu), _dp(o["xp"]), _dp(o["yp"]), _ip(o["iflux"]), _ip(o["jflux"]),
+                                      _dp(o["triarea"]), _ip(o["icells"]), _dp(o["edgearea"]))
+    if rc != 0:
+        raise RuntimeError(f"remap_oracle_triangles failed with status {rc}")
+    return o
+
+
+def transport_integrals(tracer_type, depend, tri, mc, mx, my, tc=None, tx=None, ty=None):
+    """transport_integrals (:3199-3509, integral_order 3) of one category from the arrays of :func:`triangles`.
+    Returns mflx (ny, nx) and, with tracers, mtflx (ntrace, ny, nx)."""
+    nyb, nxb = mc.shape
+    ia = lambda v: np.ascontiguousarray(v, dtype=np.int32)
+    tt, dp = ia(tracer_type), ia(depend)
+    mflx = np.full((nyb, nxb), np.nan)
+    mtflx = np.full(tc.shape, np.nan) if tc is not None else None
+    rc = lib().remap_oracle_transport_integrals(
+        C.c_int(nxb), C.c_int(nyb), C.c_int(tt.size), _ip(tt), _ip(dp), _dp(tri["xp"]), _dp(tri["yp"]), _ip(tri["iflux"]),
+        _ip(tri["jflux"]), _dp(tri["triarea"]), _dp(mc), _dp(mx), _dp(my), _dp(mflx),
+        _dp(np.ascontiguousarray(tc)) if tc is not None else None, _dp(np.ascontiguousarray(tx)) if tc is not None else None,
+        _dp(np.ascontiguousarray(ty)) if tc is not None else None, _dp(mtflx) if tc is not None else None)
+    if rc != 0:
+        raise RuntimeError(f"remap_oracle_transport_integrals failed with status {rc}")
+    return mflx, mtflx
+
+
+def update_fields(tracer_type, depend, tarear, mflxe, mflxn, mm, mtflxe=None, mtflxn=None, tm=None):
+    """update_fields (:3517-3729) of one category; mm (and tm) are updated in place.  Returns (l_stop, istop, jstop)."""
+    nyb, nxb = mm.shape
+    ia = lambda v: np.ascontiguousarray(v, dtype=np.int32)
+    tt, dp = ia(tracer_type), ia(depend)
+    ls, i_s, j_s = C.c_int(0), C.c_int(0), C.c_int(0)
+    rc = lib().remap_oracle_update_fields(C.c_int(nxb), C.c_int(nyb), C.c_int(tt.size), _ip(tt), _ip(dp), _dp(tarear), _dp(mflxe),
+                                          _dp(mflxn), _dp(mm), _dp(mtflxe) if tm is not None else None,
+                                          _dp(mtflxn) if tm is not None else None, _dp(tm) if tm is not None else None,
+                                          C.byref(ls), C.byref(i_s), C.byref(j_s))
+    if rc != 0:
+        raise RuntimeError(f"remap_oracle_update_fields failed with status {rc}")
+    return bool(ls.value), i_s.value, j_s.value
+
+
+def horizontal_remap(dom, dt, tracer_type, depend, has_dependents, g, uvel, vvel, mm, tm, no_halo=False, nslabs=1):
+    """All of horizontal_remap (source/ice_transport_remap.F90:309-850; l_fixed_area = F, integral_order = 3, l_dp_midpt = T)
+    on global-with-ghost planes.  g: dict hm, xav, yav, xxav, yyav, dxu, dyu, HTN, HTE, tarear.  mm (ncat+1, ny+2, nx+2)
+    and tm (ncat, ntrace, ny+2, nx+2) are updated in place on the physical cells.  Returns (stop, category, istop, jstop):
+    stop 0 = completed, 1 = bad departure points, 2 / 3 = negative open-water / ice area (the reference aborts)."""
+    cfg = make_cfg(dom, 1, 1.0, nslabs)
+    ncat, ntrace = tm.shape[0], tm.shape[1]
+    ia = lambda v: np.ascontiguousarray(v, dtype=np.int32)
+    tt, dp, hd = ia(tracer_type), ia(depend), ia(has_dependents)
+    st, sc, i_s, j_s = C.c_int(0), C.c_int(0), C.c_int(0), C.c_int(0)
+    rc = lib().remap_oracle_horizontal_remap(
+        C.byref(cfg), C.c_double(dt), C.c_int(ncat), C.c_int(ntrace), _ip(tt), _ip(dp), _ip(hd), C.c_int(int(no_halo)),
+        *[_dp(np.ascontiguousarray(g[k], dtype=np.float64)) for k in ("hm", "xav", "yav", "xxav", "yyav", "dxu", "dyu", "HTN",
+                                                                      "HTE", "tarear")],
+        _dp(uvel), _dp(vvel), _dp(mm), _dp(tm), C.byref(st), C.byref(sc), C.byref(i_s), C.byref(j_s))
+    if rc != 0:
+        raise RuntimeError(f"remap_oracle_horizontal_remap failed with status {rc}")
+    return st.value, sc.value, i_s.value, j_s.value
+
+
 def departure_points(dom, dt, uvel, vvel, dxu, dyu, HTN, HTE, l_dp_midpt=True, no_halo=False, nslabs=1):
     """departure_points (source/ice_transport_remap.F90:1493-1670) + the ghost update of dpx, dpy that
     horizontal_remap issues (:574-578), on global-with-ghost planes.  Returns (dpx, dpy, l_stop, istop, jstop)."""

@@ -30,6 +30,31 @@ int remap_oracle_construct_fields(const evp_oracle_cfg *cfg, int ncat, int ntrac
                                   const double *mm, const double *tm, double *mc, double *mx, double *my, double *tc,
                                   double *tx, double *ty, double *mmask_out, double *tmask_out, int *icells_out);
 
+/* Third stage, the reference's compile-time settings l_fixed_area = .false., integral_order = 3
+ * (source/ice_transport_driver.F90:31,47).  One block nxb x nyb incl. the ghost ring (ilo = jlo = 2, nghost = 1).
+ * Arrays: xp, yp [6 groups][4 vertices 0..3][nyb][nxb]; iflux, jflux (Fortran indices), triarea [6][nyb][nxb].
+ *   triangles:           locate_triangles (:1680-3047) for the north (north != 0) or east edges, then, if coords != 0,
+ *                        triangle_coordinates (:3078-3187); icells[6] = cells per group; edgearea (may be NULL) as left
+ *   transport_integrals: (:3199-3509) from those arrays; tc == NULL: mass only (the open-water call)
+ *   update_fields:       (:3517-3729); tm == NULL: mass only
+ *   horizontal_remap:    all of :309-850 on a global-with-ghost block (see remap_oracle.c) */
+int remap_oracle_triangles(int nxb, int nyb, int north, int coords, const double *dpx, const double *dpy,
+                           const double *dxu, const double *dyu, double *xp, double *yp, int *iflux, int *jflux,
+                           double *triarea, int *icells, double *edgearea);
+int remap_oracle_transport_integrals(int nxb, int nyb, int ntrace, const int *tracer_type, const int *depend,
+                                     const double *xp, const double *yp, const int *iflux, const int *jflux,
+                                     const double *triarea, const double *mc, const double *mx, const double *my,
+                                     double *mflx, const double *tc, const double *tx, const double *ty, double *mtflx);
+int remap_oracle_update_fields(int nxb, int nyb, int ntrace, const int *tracer_type, const int *depend,
+                               const double *tarear, const double *mflxe, const double *mflxn, double *mm,
+                               const double *mtflxe, const double *mtflxn, double *tm, int *l_stop, int *istop, int *jstop);
+int remap_oracle_horizontal_remap(const evp_oracle_cfg *cfg, double dt, int ncat, int ntrace, const int *tracer_type,
+                                  const int *depend, const int *has_dependents, int no_halo, const double *hm,
+                                  const double *xav, const double *yav, const double *xxav, const double *yyav,
+                                  const double *dxu, const double *dyu, const double *HTN, const double *HTE,
+                                  const double *tarear, const double *uvel, const double *vvel, double *mm, double *tm,
+                                  int *stop, int *stop_cat, int *istop, int *jstop);
+
 #ifdef __cplusplus
 }
 #endif

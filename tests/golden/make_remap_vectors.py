@@ -139,6 +139,112 @@ def run(m, d, dt, midpt):
             "jstop": int(r["jstop"])}
 
 
+# ---- third stage: locate_triangles, triangle_coordinates, transport_integrals, update_fields (:1680-3729) -----------
+NG, NV = 6, 3
+
+
+def load_fluxes():
+    def lines(rel):
+        return fe.preprocess(open(os.path.join(REF, rel)).read(), ())
+    ns = {}
+    fe.parse_parameters(lines("drivers/cice/ice_constants.F90"), ns)
+    ns.update(nu_diag=6, my_task=0, ncat=NCAT, ngroups=NG, nvert=NV, char_len=80, bugcheck=False,
+              p5625m=-9.0 / 16.0, p52083=25.0 / 48.0)
+    m = fe.Module(ns)
+    m.load(lines("source/ice_transport_remap.F90"),
+           ["make_masks", "construct_fields", "limited_gradient", "departure_points", "locate_triangles",
+            "triangle_coordinates", "transport_integrals", "update_fields"])
+    return m
+
+
+def run_triangles(m, edge, dpx, dpy, dxu, dyu):
+    """locate_triangles + triangle_coordinates (integral_order = 3) for one edge, as horizontal_remap calls them
+    (:668-690, :719-741).  Returns the arrays in this repository's order: xp, yp (6, 4, NYB, NXB), ..."""
+    xp, yp = (fe.FArr.from_numpy(np.full((NG, NV + 1, NYB, NXB), -7.0), los=[1, 1, 0, 1]) for _ in range(2))
+    iflux, jflux = (fe.FArr.from_numpy(np.zeros((NG, NYB, NXB), dtype=np.int64)) for _ in range(2))
+    triarea = fe.FArr.from_numpy(np.full((NG, NYB, NXB), -7.0))
+    icells = fe.FArr.from_numpy(np.zeros(NG, dtype=np.int64))
+    indxi, indxj = (fe.FArr.from_numpy(np.zeros((NG, NXB * NYB), dtype=np.int64)) for _ in range(2))
+    edgearea = fe.FArr.from_numpy(np.zeros((NYB, NXB)))
+    geo = dict(nx_block=NXB, ny_block=NYB)
+    m.call("locate_triangles", ilo=2, ihi=NXB - 1, jlo=2, jhi=NYB - 1, nghost=1, edge=edge, icells=icells, indxi=indxi,
+           indxj=indxj, dpx=fe.FArr.from_numpy(dpx), dpy=fe.FArr.from_numpy(dpy), dxu=fe.FArr.from_numpy(dxu),
+           dyu=fe.FArr.from_numpy(dyu), xp=xp, yp=yp, iflux=iflux, jflux=jflux, triarea=triarea, l_fixed_area=False,
+           edgearea=edgearea, **geo)
+    m.call("triangle_coordinates", integral_order=3, icells=icells, indxi=indxi, indxj=indxj, xp=xp, yp=yp, **geo)
+    handles = dict(xp=xp, yp=yp, iflux=iflux, jflux=jflux, triarea=triarea, icells=icells, indxi=indxi, indxj=indxj)
+    out = {"xp": xp.to_numpy(), "yp": yp.to_numpy(), "iflux": iflux.to_numpy().astype(np.int32),
+           "jflux": jflux.to_numpy().astype(np.int32), "triarea": triarea.to_numpy(),
+           "icells": icells.to_numpy().astype(np.int32), "edgearea": edgearea.to_numpy()}
+    return handles, out
+
+
+def triangle_block(seed, amp, shear):
+    """Corner displacements up to `amp` cells in every direction; `shear` adds a gradient along the edges so that the
+    two ends of an edge leave on opposite sides (the xic branches); a fifth of the corners at rest."""
+    r = np.random.default_rng(seed)
+    sh = (NYB, NXB)
+    dxu, dyu = r.uniform(2.0e4, 3.0e4, sh), r.uniform(2.0e4, 3.0e4, sh)
+    ii = np.arange(NXB)[None, :] + np.arange(NYB)[:, None]
+    sx = r.uniform(-amp, amp, sh) + shear * np.where(ii % 2 == 0, 1.0, -1.0) * r.uniform(0.0, amp, sh)
+    sy = r.uniform(-amp, amp, sh) + shear * np.where(ii % 2 == 0, -1.0, 1.0) * r.uniform(0.0, amp, sh)
+    rest = r.uniform(0, 1, sh) < 0.2
+    sx[rest] = 0.0
+    sy[rest] = 0.0
+    sy[r.uniform(0, 1, sh) < 0.05] = 0.0                    # motion along the edge only
+    return {"dpx": sx * dxu, "dpy": sy * dyu, "dxu": dxu, "dyu": dyu}
+
+
+def run_pipeline(m, d, vel, dt, tarear):
+    """horizontal_remap (:452-850) for one block without its ghost-cell updates: the reference's routines in the
+    reference's order, on the inputs of a construct_fields case + velocities."""
+    nt = len(TRACER_TYPE)
+    hd = has_dependents(DEPEND)
+    geo = dict(nx_block=NXB, ny_block=NYB)
+    blk = dict(ilo=2, ihi=NXB - 1, jlo=2, jhi=NYB - 1, **geo)
+    rec = run_fields(m, d)
+    F = fe.FArr.from_numpy
+    dpx, dpy = F(np.zeros((NYB, NXB))), F(np.zeros((NYB, NXB)))
+    r = m.call("departure_points", nghost=1, dt=dt, dpx=dpx, dpy=dpy, l_dp_midpt=True, l_stop=False, istop=0, jstop=0,
+               uvel=F(vel["uvel"]), vvel=F(vel["vvel"]), dxu=F(vel["dxu"]), dyu=F(vel["dyu"]), htn=F(vel["HTN"]),
+               hte=F(vel["HTE"]), **blk)
+    assert not r["l_stop"]
+    tt, dep = F(np.array(TRACER_TYPE)), F(np.array(DEPEND))
+    mc, mx, my = (F(rec[k], los=[1, 1, 0]) for k in ("mc", "mx", "my"))
+    tc, tx, ty = (F(rec[k]) for k in ("tc", "tx", "ty"))
+    S = slice(None)
+    out = {"dpx": dpx.to_numpy(), "dpy": dpy.to_numpy()}
+    flux = {}
+    for edge in ("east", "north"):
+        h, tri = run_triangles(m, edge, dpx.to_numpy(), dpy.to_numpy(), vel["dxu"], vel["dyu"])
+        for k, v in tri.items():
+            out[f"{edge}/{k}"] = v
+        mflx = F(np.full((NCAT + 1, NYB, NXB), -7.0), los=[1, 1, 0])
+        mtflx = F(np.full((NCAT, nt, NYB, NXB), -7.0))
+        common = dict(ntrace=nt, icells=h["icells"], indxi=h["indxi"], indxj=h["indxj"], tracer_type=tt, depend=dep,
+                      integral_order=3, triarea=h["triarea"], iflux=h["iflux"], jflux=h["jflux"], xp=h["xp"], yp=h["yp"], **geo)
+        m.call("transport_integrals", mc=mc(S, S, 0), mx=mx(S, S, 0), my=my(S, S, 0), mflx=mflx(S, S, 0), **common)
+        for n in range(1, NCAT + 1):
+            m.call("transport_integrals", mc=mc(S, S, n), mx=mx(S, S, n), my=my(S, S, n), mflx=mflx(S, S, n),
+                   tc=tc(S, S, S, n), tx=tx(S, S, S, n), ty=ty(S, S, S, n), mtflx=mtflx(S, S, S, n), **common)
+        flux[edge] = (mflx, mtflx)
+        out[f"{edge}/mflx"], out[f"{edge}/mtflx"] = mflx.to_numpy(), mtflx.to_numpy()
+    mm, tm = F(d["mm"], los=[1, 1, 0]), F(d["tm"])
+    stops = []
+    common = dict(ntrace=nt, tracer_type=tt, depend=dep, tarear=F(tarear), **blk)
+    r = m.call("update_fields", l_stop=False, istop=0, jstop=0, mflxe=flux["east"][0](S, S, 0), mflxn=flux["north"][0](S, S, 0),
+               mm=mm(S, S, 0), **common)
+    stops.append((bool(r["l_stop"]), int(r["istop"]), int(r["jstop"])))
+    for n in range(1, NCAT + 1):
+        r = m.call("update_fields", l_stop=False, istop=0, jstop=0, mflxe=flux["east"][0](S, S, n),
+                   mflxn=flux["north"][0](S, S, n), mm=mm(S, S, n), mtflxe=flux["east"][1](S, S, S, n),
+                   mtflxn=flux["north"][1](S, S, S, n), tm=tm(S, S, S, n), **common)
+        stops.append((bool(r["l_stop"]), int(r["istop"]), int(r["jstop"])))
+    out["mm_new"], out["tm_new"] = mm.to_numpy(), tm.to_numpy()
+    out["stops"] = np.array([[int(a), b, c] for a, b, c in stops], dtype=np.int32)
+    return out
+
+
 def main():
     m = load()
     out = {"nxb": NXB, "nyb": NYB}
@@ -168,6 +274,31 @@ def main():
         print(name, "icells", res["icells"], "max |mx|", float(np.abs(res["mx"]).max()), "max |tx|",
               float(np.abs(res["tx"]).max()), "limited cells",
               int(np.count_nonzero(res["tx"])))
+    mx3 = load_fluxes()
+    for name, seed, amp, shear in [("tri_small", 31, 0.25, 0.0), ("tri_large", 32, 0.9, 0.0), ("tri_shear", 33, 0.45, 1.0)]:
+        d = triangle_block(seed, amp, shear)
+        for k, v in d.items():
+            out[f"{name}/{k}"] = v
+        for edge in ("east", "north"):
+            _, tri = run_triangles(mx3, edge, d["dpx"], d["dpy"], d["dxu"], d["dyu"])
+            for k, v in tri.items():
+                out[f"{name}/{edge}/{k}"] = v
+            print(name, edge, "cells per group", tri["icells"])
+    for name, cf_seed, vel_seed, speed, open_frac in [("pipe_a", 21, 41, 1.5, 0.1), ("pipe_b", 22, 42, 3.0, 0.45)]:
+        d = fields_block(cf_seed, open_frac)
+        vel = block(vel_seed, speed)
+        r = np.random.default_rng(vel_seed + 100)
+        tarear = 1.0 / (vel["dxu"] * vel["dyu"] * r.uniform(0.95, 1.05, (NYB, NXB)))
+        res = run_pipeline(mx3, d, vel, 3600.0, tarear)
+        for k, v in d.items():
+            out[f"{name}/{k}"] = v
+        for k, v in vel.items():
+            out[f"{name}/{k}"] = v
+        out[f"{name}/tarear"], out[f"{name}/dt"] = tarear, 3600.0
+        for k, v in res.items():
+            out[f"{name}/out/{k}"] = v
+        print(name, "stops", res["stops"].tolist(), "max |dmm|", float(np.abs(res["mm_new"] - d["mm"]).max()),
+              "cells per group east", res["east/icells"], "north", res["north/icells"])
     np.savez_compressed(OUT, **out)
     print("wrote", OUT)
 

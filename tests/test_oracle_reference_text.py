@@ -423,3 +423,78 @@ def test_construct_fields_oracle_reproduces_reference_text_bitwise(name):
     assert np.count_nonzero(o["tx"]) > 100 and np.count_nonzero(o["mx"]) > 30
     lim = np.abs(o["tx"][:, 0]) > 0                        # the limiter bites somewhere and is idle somewhere
     assert lim.any()
+
+
+def _remap_vectors():
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_remap_vectors.npz"))
+
+
+@pytest.mark.parametrize("name", ["tri_small", "tri_large", "tri_shear"])
+@pytest.mark.parametrize("edge", ["east", "north"])
+def test_triangles_oracle_reproduces_reference_text_bitwise(name, edge):
+    """oracle/remap_oracle.c == locate_triangles + triangle_coordinates (source/ice_transport_remap.F90:1680-3187, l_fixed_area
+    = F, integral_order = 3) executed mechanically: vertices / integration points, source cells, areas, cells per group,
+    edge areas -- small and nearly one-cell displacements, sheared edges (the x-axis intersection branches), corners at rest."""
+    z = _remap_vectors()
+    get = lambda k: np.ascontiguousarray(z[f"{name}/{k}"])
+    o = orc.triangles(edge == "north", get("dpx"), get("dpy"), get("dxu"), get("dyu"))
+    for k in ("icells", "iflux", "jflux", "triarea", "xp", "yp", "edgearea"):
+        want = get(f"{edge}/{k}")
+        assert o[k].shape == want.shape and np.array_equal(o[k], want), k
+        if o[k].dtype == np.float64:
+            assert np.array_equal(np.signbit(o[k]), np.signbit(want)), k
+    assert o["icells"][:2].min() > 20 and o["icells"][3] > 80
+
+
+@pytest.mark.parametrize("name", ["pipe_a", "pipe_b"])
+def test_flux_integrals_and_update_oracle_reproduce_reference_text_bitwise(name):
+    """transport_integrals (:3199-3509) and update_fields (:3517-3729) of the oracle against the reference text, fed with the
+    reference's own intermediate arrays (triangles, reconstructed fields, fluxes) of a whole block."""
+    z = _remap_vectors()
+    get = lambda k: np.ascontiguousarray(z[f"{name}/{k}"])
+    tt, dep = z["tracer_type"], z["depend"]
+    ncat = int(z["ncat"])
+    from cice5_b200 import fixtures as fx
+    dom = fx.Domain(nx=int(z["nxb"]) - 2, ny=int(z["nyb"]) - 2, ew_cyclic=False, ns_open=True, name="block")
+    rec = orc.construct_fields(dom, tt, dep, z["has_dependents"], get("hm"), get("xav"), get("yav"), get("xxav"), get("yyav"),
+                               get("mm"), get("tm"), no_halo=True)
+    flux = {}
+    for edge in ("east", "north"):
+        tri = {k: get(f"out/{edge}/{k}") for k in ("xp", "yp", "iflux", "jflux", "triarea")}
+        mflx = np.zeros((ncat + 1,) + rec["mc"].shape[1:])
+        mtflx = np.zeros(rec["tc"].shape)
+        mflx[0], _ = orc.transport_integrals(tt, dep, tri, rec["mc"][0], rec["mx"][0], rec["my"][0])
+        for n in range(1, ncat + 1):
+            mflx[n], mtflx[n - 1] = orc.transport_integrals(tt, dep, tri, rec["mc"][n], rec["mx"][n], rec["my"][n],
+                                                            rec["tc"][n - 1], rec["tx"][n - 1], rec["ty"][n - 1])
+        assert np.array_equal(mflx, get(f"out/{edge}/mflx")) and np.array_equal(mtflx, get(f"out/{edge}/mtflx")), edge
+        assert np.array_equal(np.signbit(mtflx), np.signbit(get(f"out/{edge}/mtflx")))
+        flux[edge] = (mflx, mtflx)
+        assert np.count_nonzero(mtflx) > 500
+    mm, tm = get("mm"), get("tm")
+    stops = [orc.update_fields(tt, dep, get("tarear"), flux["east"][0][0], flux["north"][0][0], mm[0])]
+    for n in range(1, ncat + 1):
+        stops.append(orc.update_fields(tt, dep, get("tarear"), flux["east"][0][n], flux["north"][0][n], mm[n],
+                                       flux["east"][1][n - 1], flux["north"][1][n - 1], tm[n - 1]))
+    assert np.array_equal(mm, get("out/mm_new")) and np.array_equal(tm, get("out/tm_new"))
+    assert np.array_equal(np.signbit(tm), np.signbit(get("out/tm_new")))
+    assert [list(map(int, s)) for s in stops] == get("out/stops").tolist()
+    assert np.abs(mm - get("mm")).max() > 0.05
+
+
+@pytest.mark.parametrize("name", ["pipe_a", "pipe_b"])
+def test_horizontal_remap_oracle_reproduces_reference_text_bitwise(name):
+    """The oracle's whole horizontal_remap (no ghost-cell updates: one block) == the reference's routines run in the
+    reference's order: make_masks, construct_fields, departure_points, then per edge locate_triangles, triangle_coordinates,
+    transport_integrals of every category, then update_fields of every category."""
+    z = _remap_vectors()
+    get = lambda k: np.ascontiguousarray(z[f"{name}/{k}"])
+    from cice5_b200 import fixtures as fx
+    dom = fx.Domain(nx=int(z["nxb"]) - 2, ny=int(z["nyb"]) - 2, ew_cyclic=False, ns_open=True, name="block")
+    g = {k: get(k) for k in ("hm", "xav", "yav", "xxav", "yyav", "dxu", "dyu", "HTN", "HTE", "tarear")}
+    mm, tm = get("mm"), get("tm")
+    stop = orc.horizontal_remap(dom, float(z[f"{name}/dt"]), z["tracer_type"], z["depend"], z["has_dependents"], g, get("uvel"),
+                                get("vvel"), mm, tm, no_halo=True)
+    assert stop == (0, 0, 0, 0)
+    assert np.array_equal(mm, get("out/mm_new")) and np.array_equal(tm, get("out/tm_new"))
+    assert np.array_equal(np.signbit(tm), np.signbit(get("out/tm_new")))
