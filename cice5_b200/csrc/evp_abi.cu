@@ -149,9 +149,12 @@ struct evp_handle {
     // tm(ntrace, ncat), mc mx my (0:ncat), tc tx ty (ntrace, ncat) planes of the arena's pitch in one allocation
     double *rc = nullptr;
     ReconArgs rc_args;
-    bool rc_loaded = false;
-    cudaEvent_t tev[3] = {nullptr, nullptr, nullptr};     // transport stage: start, kernels done, ghost updates done
-    double tr_ms[4] = {0.0, 0.0, 0.0, 0.0};               // departure kernels / halos, reconstruction kernel / halos
+    int *rc_stop = nullptr;       // update_fields: per category 0 or 1 + r * nxb + c of the last cell with a negative new area
+    int h_rc_stop[256];
+    bool rc_loaded = false, rc_remapped = false;
+    cudaEvent_t tev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // transport stage: start, kernels done, ghost updates
+                                                          // done; whole remap: start, end
+    double tr_ms[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};     // departure kernels / halos, reconstruction kernel / halos, fluxes + update, whole remap
     bool have_ht = false;         // HTE / HTN were given: compact metric rows are possible
     evp_stats_t stats;
     unsigned long long h_counts[2];
@@ -1766,7 +1769,9 @@ struct RcLayout {
     size_t tm(int k) const { return 5 + (size_t)(ncat + 1) + k; }                       // k = (n-1)*ntrace + nt
     size_t mass(int f, int n) const { return tm(ncat * ntrace) + (size_t)f * (ncat + 1) + n; }           // f: mc mx my
     size_t trc(int f, int k) const { return mass(3, 0) + (size_t)f * ncat * ntrace + k; }                // f: tc tx ty
-    size_t planes() const { return trc(3, 0); }
+    size_t mflx(int e) const { return trc(3, 0) + (size_t)e * (ncat + 1 + (size_t)ncat * ntrace); }      // e: east north
+    size_t mtflx(int e) const { return mflx(e) + (ncat + 1); }
+    size_t planes() const { return mflx(2); }
 };
 RcLayout rc_layout(const evp_handle *h) { return RcLayout{h->rc_args.ncat, h->rc_args.ntrace}; }
 
@@ -1811,10 +1816,10 @@ int finish_ops(evp_handle *h)
 }  // namespace
 extern "C" {
 
-int evp_gpu_get_transport_timing(evp_handle_t *h, double ms[4])
+int evp_gpu_get_transport_timing(evp_handle_t *h, double ms[6])
 {
     if (!h || !ms) return EVP_ERR_ARG;
-    for (int k = 0; k < 4; ++k) ms[k] = h->tr_ms[k];
+    for (int k = 0; k < 6; ++k) ms[k] = h->tr_ms[k];
     return EVP_OK;
 }
 
@@ -1822,7 +1827,7 @@ int evp_gpu_set_transport_tracers(evp_handle_t *h, int ncat, int ntrace, const i
                                   const int *has_dependents, const double *hm, const double *xav, const double *yav,
                                   const double *xxav, const double *yyav)
 {
-    if (!h || ncat < 1 || ntrace < 0 || !hm || !xav || !yav || !xxav || !yyav) return EVP_ERR_ARG;
+    if (!h || ncat < 1 || ncat > 255 || ntrace < 0 || !hm || !xav || !yav || !xxav || !yyav) return EVP_ERR_ARG;
     if (ntrace > 0 && (!tracer_type || !depend || !has_dependents)) return EVP_ERR_ARG;
     if (ntrace > kRemapMaxTrace) return EVP_ERR_TOO_LARGE;
     ReconArgs a;
@@ -1833,17 +1838,17 @@ int evp_gpu_set_transport_tracers(evp_handle_t *h, int ncat, int ntrace, const i
         if (ty < 1 || ty > 3) return EVP_ERR_ARG;
         a.ttype[nt] = (signed char)ty;
         a.slot[nt] = -1;
-        if (ty == 1) {
-            if (has_dependents[nt]) {
-                if (parents == kRemapMaxParents) return EVP_ERR_TOO_LARGE;
-                a.slot[nt] = (signed char)parents++;
-            }
-        } else {
-            // the reference reads mtxav(:,:,depend(nt)) when it reaches tracer nt: the parent of a type-2 tracer is
-            // an earlier type-1 tracer flagged has_dependents (init_transport, ice_transport_driver.F90:90-118)
-            if (d < 1 || d > ntrace) return EVP_ERR_ARG;
-            if (ty == 2 && (d > nt || tracer_type[d - 1] != 1 || !has_dependents[d - 1])) return EVP_ERR_ARG;
+        if (ty != 1) {
+            // the reference reads the sums of tracer depend(nt) when it reaches tracer nt: the parent of a type-2 tracer
+            // is an earlier type-1 tracer, that of a type-3 tracer an earlier type-2 tracer, both flagged has_dependents
+            // (init_transport, ice_transport_driver.F90:90-118)
+            if (d < 1 || d > nt || tracer_type[d - 1] != ty - 1 || !has_dependents[d - 1]) return EVP_ERR_ARG;
             a.parent[nt] = (unsigned char)(d - 1);
+        }
+        if (has_dependents[nt]) {
+            if (ty == 3) return EVP_ERR_ARG;
+            if (parents == kRemapMaxParents) return EVP_ERR_TOO_LARGE;
+            a.slot[nt] = (signed char)parents++;
         }
     }
     CK(cudaSetDevice(h->cfg.device));
@@ -1854,8 +1859,9 @@ int evp_gpu_set_transport_tracers(evp_handle_t *h, int ncat, int ntrace, const i
         h->rc = nullptr;
     }
     if (!h->rc) {
-        CK(cudaMalloc(&h->rc, l.planes() * h->plane_elems * sizeof(double)));
-        CK(cudaMemset(h->rc, 0, l.planes() * h->plane_elems * sizeof(double)));
+        CK(cudaMalloc(&h->rc, l.planes() * h->plane_elems * sizeof(double) + 1024));
+        CK(cudaMemset(h->rc, 0, l.planes() * h->plane_elems * sizeof(double) + 1024));
+        h->rc_stop = reinterpret_cast<int *>(h->rc + l.planes() * h->plane_elems);        // [ncat + 1] <= 256 words
     }
     auto pl = [h](size_t k) { return h->rc + k * h->plane_elems; };
     a.nxb = h->nxb; a.nyb = h->nyb; a.ld = h->ld; a.pe = h->plane_elems; a.ncat = ncat; a.ntrace = ntrace;
@@ -1966,6 +1972,159 @@ int evp_gpu_construct_fields(evp_handle_t *h, const double *mm, const double *tm
     TRY(evp_gpu_construct_fields_upload(h, mm, tm));
     TRY(evp_gpu_construct_fields_compute(h));
     return evp_gpu_construct_fields_fetch(h, mc, mx, my, tc, tx, ty);
+}
+
+// ---- all of horizontal_remap on the device ----------------------------------------------------------------------
+}  // extern "C"
+namespace {
+int rc_slots(const evp_handle *h)
+{
+    int n = 0;
+    for (int nt = 0; nt < h->rc_args.ntrace; ++nt) if (h->rc_args.slot[nt] >= n) n = h->rc_args.slot[nt] + 1;
+    return n;
+}
+// horizontal_remap (source/ice_transport_remap.F90:309-850): reconstruction and departure points with their ghost-cell
+// updates (the two programs above), then the fluxes through the east and north edges and update_fields of every category
+void build_remap(evp_handle *h, double dt, std::vector<Op> &ops)
+{
+    { Builder B0{h, ops}; stage_mark(B0, 3); }
+    build_reconstruct(h, ops);
+    build_departure(h, dt, 1, ops);
+    Builder B{h, ops};
+    const RcLayout l = rc_layout(h);
+    B.op([h, l](Launcher &L) {
+        auto pl = [h](size_t k) { return h->rc + k * h->plane_elems; };
+        const int nslots = rc_slots(h);
+        FluxArgs f;
+        f.a = h->rc_args;
+        f.dpx = h->plane(W_1); f.dpy = h->plane(W_2);
+        f.dxu = h->tr; f.dyu = h->tr + h->plane_elems;
+        for (int e = 0; e < 2; ++e) { f.mflx[e] = pl(l.mflx(e)); f.mtflx[e] = pl(l.mtflx(e)); }
+        edge_flux_kernel<<<dim3((h->nxb + 127) / 128, h->nyb, 2), 128, (size_t)nslots * 128 * 24, L.s()>>>(f, nslots);
+        CK(cudaGetLastError());
+        UpdateArgs u;
+        u.a = h->rc_args;
+        u.tarear = h->plane(G_TAREAR);
+        for (int e = 0; e < 2; ++e) { u.mflx[e] = pl(l.mflx(e)); u.mtflx[e] = pl(l.mtflx(e)); }
+        u.mm = pl(l.mm(0)); u.tm = pl(l.tm(0)); u.stop = h->rc_stop;
+        CK(cudaMemsetAsync(h->rc_stop, 0, (l.ncat + 1) * sizeof(int), L.s()));
+        update_fields_kernel<<<dim3((h->nxb + 127) / 128, h->nyb, l.ncat + 1), 128, (size_t)nslots * 128 * 16, L.s()>>>(u, nslots);
+        CK(cudaGetLastError());
+        L.n += 2;
+        return EVP_OK;
+    });
+    stage_mark(B, 4);
+}
+int finish_remap(evp_handle *h)
+{
+    const int ncat = h->rc_args.ncat;
+    CK(cudaMemcpyAsync(&h->h_tr_stop, h->tr_stop, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(h->h_rc_stop, h->rc_stop, (ncat + 1) * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(&h->h_error, h->dev_error(), sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (h->h_error) {
+        snprintf(g_cuda_err, sizeof(g_cuda_err), "halo wait timed out: a peer rank did not arrive");
+        return EVP_ERR_PEER;
+    }
+    h->rc_loaded = false;                                        // mm, tm now hold the transported state
+    h->rc_remapped = true;
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, h->tev[2], h->tev[4])); h->tr_ms[4] = ms;
+    CK(cudaEventElapsedTime(&ms, h->tev[3], h->tev[4])); h->tr_ms[5] = ms;
+    return EVP_OK;
+}
+int remap_ready(const evp_handle *h)
+{
+    if (!h->tr || !h->rc || !h->rc_loaded || !h->uploaded || !h->peers_set || !h->grid_set) return EVP_ERR_STATE;
+    return EVP_OK;
+}
+}  // namespace
+extern "C" {
+
+int evp_gpu_horizontal_remap_compute(evp_handle_t *h, double dt)
+{
+    if (!h || !(dt > 0.0)) return EVP_ERR_ARG;
+    TRY(remap_ready(h));
+    CK(cudaSetDevice(h->cfg.device));
+    std::vector<Op> ops;
+    build_remap(h, dt, ops);
+    Launcher L{h};
+    for (const Op &op : ops) {
+        if (op.sync) { TRY(launch_signal(L)); TRY(launch_wait(L)); }
+        else TRY(op.fn(L));
+    }
+    return finish_remap(h);
+}
+
+// all ranks of a one-device group on one stream, steps interleaved (see evp_gpu_compute_group)
+int evp_gpu_horizontal_remap_group(evp_handle_t **hs, int n, double dt)
+{
+    if (!hs || n < 1 || n > kMaxRanks || !(dt > 0.0)) return EVP_ERR_ARG;
+    for (int r = 0; r < n; ++r) {
+        if (!hs[r] || hs[r]->cfg.nranks != n || hs[r]->cfg.rank != r) return EVP_ERR_ARG;
+        TRY(remap_ready(hs[r]));
+        if (hs[r]->cfg.device != hs[0]->cfg.device) return EVP_ERR_UNSUPPORTED;
+        if (hs[r]->rc_args.ncat != hs[0]->rc_args.ncat || hs[r]->rc_args.ntrace != hs[0]->rc_args.ntrace) return EVP_ERR_ARG;
+    }
+    CK(cudaSetDevice(hs[0]->cfg.device));
+    std::vector<std::vector<Op>> P(n);
+    std::vector<Launcher> L;
+    for (int r = 0; r < n; ++r) {
+        CK(cudaStreamSynchronize(hs[r]->stream));
+        hs[r]->stream = hs[0]->own_stream;
+        build_remap(hs[r], dt, P[r]);
+        L.push_back(Launcher{hs[r]});
+    }
+    int rc = EVP_OK;
+    for (size_t i = 0; i < P[0].size() && rc == EVP_OK; ++i) {
+        if (P[0][i].sync) {
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = launch_signal(L[r]);
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = launch_wait(L[r]);
+        } else {
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = P[r][i].fn(L[r]);
+        }
+    }
+    for (int r = 0; r < n; ++r) {
+        const int rc2 = rc == EVP_OK ? finish_remap(hs[r]) : rc;
+        hs[r]->stream = hs[r]->own_stream;
+        if (rc2 != EVP_OK) rc = rc2;
+    }
+    return rc;
+}
+
+int evp_gpu_horizontal_remap_fetch(evp_handle_t *h, double *mm, double *tm, int *stop, int *stop_cat, int *istop, int *jstop)
+{
+    if (!h) return EVP_ERR_ARG;
+    if (!h->rc || !h->rc_remapped) return EVP_ERR_STATE;
+    CK(cudaSetDevice(h->cfg.device));
+    const RcLayout l = rc_layout(h);
+    const size_t cells = (size_t)h->nxb * h->nyb;
+    auto pl = [h](size_t k) { return h->rc + k * h->plane_elems; };
+    D2HBatch B{h, {}};
+    h->batch_dst.clear();
+    if (mm) for (int n = 0; n <= l.ncat; ++n) TRY(B.add(pl(l.mm(n)), mm + (size_t)n * cells, 0));
+    if (tm) for (int k = 0; k < l.ncat * l.ntrace; ++k) TRY(B.add(pl(l.tm(k)), tm + (size_t)k * cells, 0));
+    TRY(B.flush());
+    CK(cudaStreamSynchronize(h->stream));
+    // what the reference would report before abort_ice: bad departure points (:552-563), then the first category (open
+    // water first) whose new area is negative (:783-825)
+    int kind = 0, cat = 0, code = 0;
+    if (h->h_tr_stop) { kind = 1; code = h->h_tr_stop; }
+    else
+        for (int n = 0; n <= l.ncat; ++n)
+            if (h->h_rc_stop[n]) { kind = n == 0 ? 2 : 3; cat = n; code = h->h_rc_stop[n]; break; }
+    if (stop) *stop = kind;
+    if (stop_cat) *stop_cat = cat;
+    if (istop) *istop = code ? (code - 1) % h->nxb + 1 : 0;
+    if (jstop) *jstop = code ? (code - 1) / h->nxb + 1 : 0;
+    return EVP_OK;
+}
+
+int evp_gpu_horizontal_remap(evp_handle_t *h, double dt, double *mm, double *tm, int *stop, int *stop_cat, int *istop, int *jstop)
+{
+    TRY(evp_gpu_construct_fields_upload(h, mm, tm));
+    TRY(evp_gpu_horizontal_remap_compute(h, dt));
+    return evp_gpu_horizontal_remap_fetch(h, mm, tm, stop, stop_cat, istop, jstop);
 }
 
 int evp_gpu_principal_stress(evp_handle_t *h, double *sig1, double *sig2)

@@ -277,4 +277,272 @@ __global__ void __launch_bounds__(128, EVP_RC_DIRECT_BLOCKS) reconstruct_kernel(
     }
 }
 
+// ---- third stage: locate_triangles + triangle_coordinates + transport_integrals, then update_fields ----------------
+// reference: source/ice_transport_remap.F90:1680-3047 (locate_triangles), :3078-3187 (triangle_coordinates), :3199-3509
+// (transport_integrals), :3517-3729 (update_fields), called by horizontal_remap :640-850 with the compile-time settings
+// l_fixed_area = .false., integral_order = 3 (source/ice_transport_driver.F90:31,47); other settings are not built.
+//
+// The reference writes the triangles of a whole block to memory (vertices, areas, source cells, six index lists) and
+// then sweeps the lists once per category and tracer.  Here one thread owns one cell edge: it works out the edge's six
+// triangles, keeps the ten points they are made of, and per triangle that survives the area threshold integrates every
+// category and tracer over it straight away; triangles never reach memory.  The flux of a (category, tracer) at an edge
+// is the reference's sum over the groups in ascending order, accumulated in its output cell (which this thread alone
+// touches).  The case analysis of locate_triangles is data here: one table row per triangle the reference assigns.
+namespace flux {
+// points: 0 CL  1 CR  2 DL  3 DR  4 IL  5 IR  6 IC (= ICL = ICR without l_fixed_area)  7 DM  8, 9 DL, DR after the
+// departure points in the side cells have been moved to the cell boundary (:2238-2255)
+enum { CL, CR, DL, DR, IL, IR, IC, DM, DL2, DR2 };
+enum { TL, BL, TR, BR, TC, BC };                       // source cell: ishift_* / jshift_* (:1820-1898)
+enum { PL, ML, PR, MR, PC, MC };                       // areafact: +/- areafac_l, _r, _c
+struct Row { unsigned char ng, p1, p2, p3, sh, fac; };  // ng = 0: no triangle
+// TL / BL triangles (:2034-2108), in the order of the if / elseif chain; the rows of a case in assignment order
+__device__ const Row kLeft[4][2] = {
+    {{1, CL, IL, DL, TL, ML}, {0, 0, 0, 0, 0, 0}},
+    {{1, CL, DL, IL, BL, PL}, {0, 0, 0, 0, 0, 0}},
+    {{1, CL, DL, IC, TL, PL}, {3, CL, IC, IL, BL, PL}},
+    {{3, CL, IL, IC, TL, ML}, {1, CL, IC, DL, BL, ML}}};
+// TR / BR triangles (:2114-2190)
+__device__ const Row kRight[4][2] = {
+    {{2, CR, DR, IR, TR, MR}, {0, 0, 0, 0, 0, 0}},
+    {{2, CR, IR, DR, BR, PR}, {0, 0, 0, 0, 0, 0}},
+    {{2, CR, IC, DR, TR, PR}, {3, CR, IR, IC, BR, PR}},
+    {{3, CR, IC, IR, TR, MR}, {2, CR, DR, IC, BR, MR}}};
+// TC / BC triangles (:2394-2923), groups 4, 5, 6
+__device__ const Row kCentre[12][3] = {
+    {{4, CL, CR, DL2, TC, MC}, {5, CR, DR2, DL2, TC, MC}, {6, DL2, DR2, DM, TC, MC}},
+    {{4, CL, IC, DL2, TC, MC}, {5, CR, DR2, IC, TC, MC}, {6, IC, IC, DM, BC, PC}},
+    {{4, CL, DL2, CR, BC, PC}, {5, CR, DL2, DR2, BC, PC}, {6, DL2, DM, DR2, BC, PC}},
+    {{4, CL, DL2, IC, BC, PC}, {5, CR, IC, DR2, BC, PC}, {6, IC, IC, DM, TC, MC}},
+    {{4, CL, IC, DL2, TC, MC}, {5, CR, IC, DR2, BC, PR}, {6, DL2, IC, DM, TC, MC}},
+    {{4, CL, IC, DL2, TC, MC}, {5, CR, IC, DR2, BC, PR}, {6, IC, IC, DM, BC, PC}},
+    {{4, CL, IC, DL2, TC, ML}, {5, CR, IC, DR2, BC, PC}, {6, DR2, IC, DM, BC, PC}},
+    {{4, CL, IC, DL2, TC, ML}, {5, CR, IC, DR2, BC, PC}, {6, IC, IC, DM, TC, MC}},
+    {{4, CL, DL2, IC, BC, PL}, {5, CR, DR2, IC, TC, MC}, {6, IC, DR2, DM, TC, MC}},
+    {{4, CL, DL2, IC, BC, PL}, {5, CR, DR2, IC, TC, MC}, {6, IC, IC, DM, BC, PC}},
+    {{4, CL, DL2, IC, BC, PC}, {5, CR, DR2, IC, TC, MR}, {6, IC, DL2, DM, BC, PC}},
+    {{4, CL, DL2, IC, BC, PC}, {5, CR, DR2, IC, TC, MR}, {6, IC, IC, DM, TC, MC}}};
+// (ishift, jshift) of TL BL TR BR TC BC for the east edge (row 0) and the north edge (row 1)
+__device__ const signed char kShift[2][6][2] = {{{1, 1}, {0, 1}, {1, -1}, {0, -1}, {1, 0}, {0, 0}},
+                                                {{-1, 1}, {-1, 0}, {1, 1}, {1, 0}, {0, 1}, {0, 0}}};
+constexpr double puny = 1.0e-11, eps16 = 1.0e-16;
+}  // namespace flux
+
+struct FluxArgs {
+    ReconArgs a;                       // sizes, tracer tables, the reconstructed fields mc mx my tc tx ty
+    const double *dpx, *dpy, *dxu, *dyu;
+    double *mflx[2], *mtflx[2];        // [east, north]: ncat+1 planes; ncat * ntrace planes
+};
+
+// grid: (ceil(nxb / 128), nyb, 2); blockIdx.z = 0 east edges, 1 north edges.  Dynamic shared memory: per tracer with
+// dependents and thread mtsum, mtxsum, mtysum of the current triangle (3 x 8 bytes x 128 x slots)
+__global__ void __launch_bounds__(128) edge_flux_kernel(const __grid_constant__ FluxArgs f, int nslots)
+{
+    using namespace flux;
+    extern __shared__ double par[];
+    const ReconArgs &a = f.a;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y, north = blockIdx.z;
+    if (c >= a.nxb) return;
+    const size_t q = (size_t)r * a.ld + c;
+    double *mflx = f.mflx[north], *mtflx = f.mtflx[north];
+    const int nplanes_t = a.ncat * a.ntrace;
+    // edges of the block that carry a flux (:1820-1826, :1860-1866); every other cell of the flux planes is zero
+    const bool edge = north ? (c >= 1 && c <= a.nxb - 2 && r <= a.nyb - 2) : (c <= a.nxb - 2 && r >= 1 && r <= a.nyb - 2);
+    const size_t ql = north ? q - 1 : q, qr = north ? q : q - a.ld;       // corners: left (i-1,j | i,j), right (i,j | i,j-1)
+    bool moving = false;
+    if (edge) moving = f.dpx[ql] != 0.0 || f.dpy[ql] != 0.0 || f.dpx[qr] != 0.0 || f.dpy[qr] != 0.0;        // :1956-1980
+    bool first = true;                 // nothing accumulated in this thread's flux cells yet
+    if (moving) {
+        const double fl = f.dxu[ql] * f.dyu[ql], fr = f.dxu[qr] * f.dyu[qr], fc = 0.5 * (fl + fr);           // areafac
+        const double dxl = f.dpx[ql] / f.dxu[ql], dyl = f.dpy[ql] / f.dyu[ql];                               // :1986-1991
+        const double dxr = f.dpx[qr] / f.dxu[qr], dyr = f.dpy[qr] / f.dyu[qr];
+        double px[10], py[10];
+        px[CL] = -0.5; py[CL] = 0.0; px[CR] = 0.5; py[CR] = 0.0;
+        double xdl, ydl, xdr, ydr;
+        if (north) { xdl = px[CL] + dxl; ydl = py[CL] + dyl; xdr = px[CR] + dxr; ydr = py[CR] + dyr; }
+        else { xdl = px[CL] - dyl; ydl = py[CL] + dxl; xdr = px[CR] - dyr; ydr = py[CR] + dxr; }           // rotated by pi/2
+        const double xdm = 0.5 * (xdr + xdl), ydm = 0.5 * (ydr + ydl);
+        const double yil = (px[CL] * (ydm - ydl) + xdm * ydl - xdl * ydm) / (xdm - xdl);
+        const double yir = (px[CR] * (ydr - ydm) - xdm * ydr + xdr * ydm) / (xdr - xdm);
+        const double md = (ydr - ydl) / (xdr - xdl);
+        const double xic = fabs(md) > puny ? xdl - ydl / md : 0.0;
+        px[DL] = xdl; py[DL] = ydl; px[DR] = xdr; py[DR] = ydr; px[IL] = px[CL]; py[IL] = yil; px[IR] = px[CR]; py[IR] = yir;
+        px[IC] = xic; py[IC] = 0.0; px[DM] = xdm; py[DM] = ydm;
+        const Row *rows[3] = {nullptr, nullptr, nullptr};
+        int nrows[3] = {0, 0, 0};
+        {
+            int k = -1;
+            if (yil > 0.0 && xdl < px[CL] && ydl >= 0.0) k = 0;
+            else if (yil < 0.0 && xdl < px[CL] && ydl < 0.0) k = 1;
+            else if (yil < 0.0 && xdl < px[CL] && ydl >= 0.0) k = 2;
+            else if (yil > 0.0 && xdl < px[CL] && ydl < 0.0) k = 3;
+            if (k >= 0) { rows[0] = kLeft[k]; nrows[0] = 2; }
+            k = -1;
+            if (yir > 0.0 && xdr >= px[CR] && ydr >= 0.0) k = 0;
+            else if (yir < 0.0 && xdr >= px[CR] && ydr < 0.0) k = 1;
+            else if (yir < 0.0 && xdr >= px[CR] && ydr >= 0.0) k = 2;
+            else if (yir > 0.0 && xdr >= px[CR] && ydr < 0.0) k = 3;
+            if (k >= 0) { rows[1] = kRight[k]; nrows[1] = 2; }
+            if (xdl < px[CL]) { xdl = px[IL]; ydl = yil; }
+            if (xdr > px[CR]) { xdr = px[IR]; ydr = yir; }
+            px[DL2] = xdl; py[DL2] = ydl; px[DR2] = xdr; py[DR2] = ydr;
+            k = -1;
+            if (ydl >= 0.0 && ydr >= 0.0 && ydm >= 0.0) k = 0;
+            else if (ydl >= 0.0 && ydr >= 0.0 && ydm < 0.0) k = 1;
+            else if (ydl < 0.0 && ydr < 0.0 && ydm < 0.0) k = 2;
+            else if (ydl < 0.0 && ydr < 0.0 && ydm >= 0.0) k = 3;
+            else if (ydl >= 0.0 && ydr < 0.0 && xic >= 0.0 && ydm >= 0.0) k = 4;
+            else if (ydl >= 0.0 && ydr < 0.0 && xic >= 0.0 && ydm < 0.0) k = 5;
+            else if (ydl >= 0.0 && ydr < 0.0 && xic < 0.0 && ydm < 0.0) k = 6;
+            else if (ydl >= 0.0 && ydr < 0.0 && xic < 0.0 && ydm >= 0.0) k = 7;
+            else if (ydl < 0.0 && ydr >= 0.0 && xic < 0.0 && ydm >= 0.0) k = 8;
+            else if (ydl < 0.0 && ydr >= 0.0 && xic < 0.0 && ydm < 0.0) k = 9;
+            else if (ydl < 0.0 && ydr >= 0.0 && xic >= 0.0 && ydm < 0.0) k = 10;
+            else if (ydl < 0.0 && ydr >= 0.0 && xic >= 0.0 && ydm >= 0.0) k = 11;
+            if (k >= 0) { rows[2] = kCentre[k]; nrows[2] = 3; }
+        }
+        // the triangle of each group: the LAST row that names the group (a right-hand case overwrites group 3 of a
+        // left-hand one, as the reference's assignments do)
+        Row tri[6];
+#pragma unroll
+        for (int g = 0; g < 6; ++g) tri[g].ng = 0;
+        for (int s3 = 0; s3 < 3; ++s3)
+            for (int k = 0; k < nrows[s3]; ++k) {
+                const Row w = rows[s3][k];
+                if (w.ng) tri[w.ng - 1] = w;
+            }
+        double *mtsum = par + threadIdx.x, *mtxsum = par + (size_t)nslots * 128 + threadIdx.x,
+               *mtysum = par + (size_t)2 * nslots * 128 + threadIdx.x;
+        for (int g = 0; g < 6; ++g) {                                      // groups in ascending order (:3235)
+            const Row w = tri[g];
+            if (!w.ng) continue;
+            double x1 = px[w.p1], y1 = py[w.p1], x2 = px[w.p2], y2 = py[w.p2], x3 = px[w.p3], y3 = py[w.p3];
+            const double fa = w.fac == PL ? fl : w.fac == ML ? -fl : w.fac == PR ? fr : w.fac == MR ? -fr : w.fac == PC ? fc : -fc;
+            const double area = 0.5 * ((x2 - x1) * (y3 - y1) - (y2 - y1) * (x3 - x1)) * fa;                  // :2932-2937
+            if (fabs(area) < eps16 * fc) continue;                          // not in the list of this group (:2939-2946)
+            const int is = kShift[north][w.sh][0], js = kShift[north][w.sh][1];
+            // vertices in the coordinates of the source cell (:2989-3021), then the four integration points (:3160-3183)
+            if (north) {
+                x1 = x1 - 1.0 * is; y1 = y1 + 0.5 - 1.0 * js; x2 = x2 - 1.0 * is; y2 = y2 + 0.5 - 1.0 * js;
+                x3 = x3 - 1.0 * is; y3 = y3 + 0.5 - 1.0 * js;
+            } else {
+                double t;
+                t = x1; x1 = y1 + 0.5 - 1.0 * is; y1 = -t - 1.0 * js;
+                t = x2; x2 = y2 + 0.5 - 1.0 * is; y2 = -t - 1.0 * js;
+                t = x3; x3 = y3 + 0.5 - 1.0 * is; y3 = -t - 1.0 * js;
+            }
+            const double p333 = 1.0 / 3.0;
+            const double x0 = p333 * (x1 + x2 + x3), y0 = p333 * (y1 + y2 + y3);
+            x1 = 0.4 * x1 + 0.6 * x0; y1 = 0.4 * y1 + 0.6 * y0;
+            x2 = 0.4 * x2 + 0.6 * x0; y2 = 0.4 * y2 + 0.6 * y0;
+            x3 = 0.4 * x3 + 0.6 * x0; y3 = 0.4 * y3 + 0.6 * y0;
+            const size_t qs = q + (ptrdiff_t)js * a.ld + is;                // source cell (iflux, jflux)
+            for (int n = 0; n <= a.ncat; ++n) {                            // :3380-3420, cubic (4-point) formula
+                const double mc = a.mc[(size_t)n * a.pe + qs], mx = a.mx[(size_t)n * a.pe + qs], my = a.my[(size_t)n * a.pe + qs];
+                const double m0 = (-9.0 / 16.0) * (mc + x0 * mx + y0 * my);
+                const double m1 = (25.0 / 48.0) * (mc + x1 * mx + y1 * my);
+                const double m2 = (25.0 / 48.0) * (mc + x2 * mx + y2 * my);
+                const double m3 = (25.0 / 48.0) * (mc + x3 * mx + y3 * my);
+                const double msum = m0 + m1 + m2 + m3;
+                double *o = mflx + (size_t)n * a.pe + q;
+                *o = (first ? 0.0 : *o) + area * msum;
+                if (n == 0 || a.ntrace == 0) continue;
+                double w0 = m0 * x0, w1 = m1 * x1, w2 = m2 * x2, w3 = m3 * x3;
+                const double mxsum = w0 + w1 + w2 + w3;
+                const double mxxsum = w0 * x0 + w1 * x1 + w2 * x2 + w3 * x3;
+                const double mxysum = w0 * y0 + w1 * y1 + w2 * y2 + w3 * y3;
+                w0 = m0 * y0; w1 = m1 * y1; w2 = m2 * y2; w3 = m3 * y3;
+                const double mysum = w0 + w1 + w2 + w3;
+                const double myysum = w0 * y0 + w1 * y1 + w2 * y2 + w3 * y3;
+                const size_t t0 = (size_t)(n - 1) * a.ntrace * a.pe;
+                for (int nt = 0; nt < a.ntrace; ++nt) {                    // :3423-3500
+                    const size_t pl = t0 + (size_t)nt * a.pe;
+                    const int type = a.ttype[nt], sl = a.slot[nt] * 128;
+                    const double tc = a.tc[pl + qs];
+                    double ms;
+                    if (type == 1) {
+                        const double tx = a.tx[pl + qs], ty = a.ty[pl + qs];
+                        ms = msum * tc + mxsum * tx + mysum * ty;
+                        if (sl >= 0) {
+                            mtsum[sl] = ms;
+                            mtxsum[sl] = mxsum * tc + mxxsum * tx + mxysum * ty;
+                            mtysum[sl] = mysum * tc + mxysum * tx + myysum * ty;
+                        }
+                    } else {
+                        const int s1 = a.slot[a.parent[nt]] * 128;
+                        if (type == 2) ms = mtsum[s1] * tc + mtxsum[s1] * a.tx[pl + qs] + mtysum[s1] * a.ty[pl + qs];
+                        else ms = mtsum[s1] * tc;
+                        if (sl >= 0) mtsum[sl] = ms;
+                    }
+                    double *ot = mtflx + pl + q;
+                    *ot = (first ? 0.0 : *ot) + area * ms;
+                }
+            }
+            first = false;
+        }
+    }
+    if (first) {                                                           // no triangle: the fluxes are zero (:3224-3230)
+        for (int n = 0; n <= a.ncat; ++n) mflx[(size_t)n * a.pe + q] = 0.0;
+        for (int k = 0; k < nplanes_t; ++k) mtflx[(size_t)k * a.pe + q] = 0.0;
+    }
+}
+
+struct UpdateArgs {
+    ReconArgs a;
+    const double *tarear;
+    const double *mflx[2], *mtflx[2];
+    double *mm, *tm;                   // updated in place on the physical cells (the reconstruction's input planes)
+    int *stop;                         // [ncat+1]: 0 or 1 + r * nxb + c of the LAST cell (loop order) whose new area < -puny
+};
+
+// grid: (ceil(nxb / 128), nyb, ncat + 1).  Dynamic shared memory: per tracer with dependents and thread its old and its
+// new value (2 x 8 bytes x 128 x slots)
+__global__ void __launch_bounds__(128) update_fields_kernel(const __grid_constant__ UpdateArgs u, int nslots)
+{
+    extern __shared__ double par[];
+    const ReconArgs &a = u.a;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y, n = blockIdx.z;
+    if (c < 1 || c > a.nxb - 2 || r < 1 || r > a.nyb - 2) return;
+    const size_t q = (size_t)r * a.ld + c;
+    double *told = par + threadIdx.x, *tnew = par + (size_t)nslots * 128 + threadIdx.x;
+    const double *fe = u.mflx[0] + (size_t)n * a.pe, *fn = u.mflx[1] + (size_t)n * a.pe;
+    const double tarear = u.tarear[q];
+    const double mold = u.mm[(size_t)n * a.pe + q];
+    double w1 = fe[q] - fe[q - 1] + fn[q] - fn[q - a.ld];                  // :3605-3609
+    double m = mold - w1 * tarear;
+    if (m < -1.0e-11) atomicMax(u.stop + n, 1 + r * a.nxb + c);            // the reference aborts (:3611-3630)
+    else if (m < 0.0) m = 0.0;
+    u.mm[(size_t)n * a.pe + q] = m;
+    if (n == 0 || a.ntrace == 0) return;
+    const size_t t0 = (size_t)(n - 1) * a.ntrace * a.pe;
+    for (int nt = 0; nt < a.ntrace; ++nt) {
+        const size_t pl = t0 + (size_t)nt * a.pe;
+        const int type = a.ttype[nt], sl = a.slot[nt] * 128;
+        const double t = u.tm[pl + q];
+        double mtold, den = m, tn = 0.0;                                   // :3560-3590, :3645-3700
+        bool on = m > 0.0;
+        if (type == 1) {
+            mtold = mold * t;
+        } else {
+            const int s1 = a.slot[a.parent[nt]] * 128;
+            if (type == 2) {
+                mtold = mold * told[s1] * t;
+                on = on && fabs(tnew[s1]) > 0.0;
+                den = m * tnew[s1];
+            } else {
+                const int s2 = a.slot[a.parent[a.parent[nt]]] * 128;
+                mtold = mold * told[s2] * told[s1] * t;
+                on = on && fabs(tnew[s1]) > 0.0 && fabs(tnew[s2]) > 0.0;
+                den = m * tnew[s2] * tnew[s1];
+            }
+        }
+        if (on) {
+            const double *te = u.mtflx[0] + pl, *tn_ = u.mtflx[1] + pl;
+            w1 = te[q] - te[q - 1] + tn_[q] - tn_[q - a.ld];
+            tn = (mtold - w1 * tarear) / den;
+        }
+        if (sl >= 0) { told[sl] = t; tnew[sl] = tn; }
+        u.tm[pl + q] = tn;
+    }
+}
+
 }  // namespace evp

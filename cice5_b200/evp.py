@@ -80,7 +80,8 @@ EXPORTS = ("evp_gpu_init", "evp_gpu_set_grid", "evp_gpu_run", "evp_gpu_upload", 
            "evp_gpu_departure_points_group", "evp_gpu_departure_points_fetch", "evp_gpu_departure_points",
            "evp_gpu_set_transport_tracers", "evp_gpu_construct_fields_upload", "evp_gpu_construct_fields_compute",
            "evp_gpu_construct_fields_group", "evp_gpu_construct_fields_fetch", "evp_gpu_construct_fields",
-           "evp_gpu_get_transport_timing")
+           "evp_gpu_get_transport_timing", "evp_gpu_horizontal_remap_compute", "evp_gpu_horizontal_remap_group",
+           "evp_gpu_horizontal_remap_fetch", "evp_gpu_horizontal_remap")
 REMAP_MAX_TRACE, REMAP_MAX_PARENTS = 128, 16     # EVP_REMAP_MAX_TRACE, EVP_REMAP_MAX_PARENTS of include/evp_b200.h
 STATIC_MAX_CELLS = 131072       # EVP_STATIC_MAX_CELLS of include/evp_b200.h
 
@@ -327,9 +328,30 @@ class EvpGpu:
 
     def transport_timing(self):
         """Device ms of the last departure_points (kernels, ghost updates) and construct_fields (kernel, ghost updates)."""
-        ms = (C.c_double * 4)()
+        ms = (C.c_double * 6)()
         self._check(self.lib.evp_gpu_get_transport_timing(self._h, ms))
-        return {"departure_ms": ms[0], "departure_halo_ms": ms[1], "reconstruct_ms": ms[2], "reconstruct_halo_ms": ms[3]}
+        return {"departure_ms": ms[0], "departure_halo_ms": ms[1], "reconstruct_ms": ms[2], "reconstruct_halo_ms": ms[3],
+                "flux_update_ms": ms[4], "remap_ms": ms[5]}
+
+    def horizontal_remap_compute(self, dt):
+        self._check(self.lib.evp_gpu_horizontal_remap_compute(self._h, C.c_double(dt)))
+
+    def horizontal_remap_fetch(self):
+        """Returns (mm, tm, (stop, category, istop, jstop)) of the last horizontal_remap."""
+        ncat, nt = self._rc_shape
+        mm, tm = np.zeros((ncat + 1,) + self.shape), np.zeros((ncat, nt) + self.shape)
+        st, sc, i_s, j_s = C.c_int(0), C.c_int(0), C.c_int(0), C.c_int(0)
+        self._check(self.lib.evp_gpu_horizontal_remap_fetch(self._h, _dp(mm), _dp(tm) if nt else None, C.byref(st), C.byref(sc),
+                                                            C.byref(i_s), C.byref(j_s)))
+        return mm, tm, (st.value, sc.value, i_s.value, j_s.value)
+
+    def horizontal_remap(self, dt, mm, tm):
+        """horizontal_remap (source/ice_transport_remap.F90:309-850) of this block from the resident velocities: mm
+        (ncat+1, ny_block, nx_block), tm (ncat, ntrace, ny_block, nx_block) with ghost cells.  Returns the new (mm, tm,
+        (stop, category, istop, jstop)); ghost cells of the results are not updated (the caller's halo update follows)."""
+        self.construct_fields_upload(mm, tm)
+        self.horizontal_remap_compute(dt)
+        return self.horizontal_remap_fetch()
 
     def construct_fields_compute(self):
         self._check(self.lib.evp_gpu_construct_fields_compute(self._h))
@@ -514,6 +536,15 @@ class EvpGroup:
         for r, e in enumerate(self.ranks):
             e.set_transport_tracers(ncat, tracer_type, depend, has_dependents,
                                     self._slabs({k: f[k] for k in ("hm", "xav", "yav", "xxav", "yyav")}, r))
+
+    def horizontal_remap(self, dt, mm, tm):
+        """All ranks; returns the global new mm, tm and the per-rank (stop, category, istop, jstop)."""
+        for r, e in enumerate(self.ranks):
+            e.construct_fields_upload(self._fx.slab(mm, r, self.n, self.starts), self._fx.slab(tm, r, self.n, self.starts))
+        arr = (C.c_void_p * self.n)(*[e._h for e in self.ranks])
+        self.ranks[0]._check(self.ranks[0].lib.evp_gpu_horizontal_remap_group(arr, self.n, C.c_double(dt)))
+        parts = [e.horizontal_remap_fetch() for e in self.ranks]
+        return (self._fx.unslab([p[0] for p in parts]), self._fx.unslab([p[1] for p in parts]), [p[2] for p in parts])
 
     def construct_fields(self, mm, tm):
         """All ranks; returns the global mc, mx, my, tc, tx, ty."""

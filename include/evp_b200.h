@@ -227,10 +227,29 @@ int evp_gpu_construct_fields_group(evp_handle_t **handles, int n);
 int evp_gpu_construct_fields_fetch(evp_handle_t *h, double *mc, double *mx, double *my, double *tc, double *tx, double *ty);
 int evp_gpu_construct_fields(evp_handle_t *h, const double *mm, const double *tm, double *mc, double *mx, double *my,
                              double *tc, double *tx, double *ty);
+/* All of horizontal_remap (source/ice_transport_remap.F90:309-850) with the reference's compile-time settings l_fixed_area
+ * = .false., integral_order = 3, l_dp_midpt = .true. (source/ice_transport_driver.F90:31,47,51): the reconstruction and the
+ * departure points above with their ghost-cell updates, then per edge (east, north) locate_triangles (:1680-3047),
+ * triangle_coordinates (:3078-3187) and transport_integrals (:3199-3509) of every category, and update_fields (:3517-3729)
+ * of open water and of every ice category.  Needs set_grid (tarear), set_transport_grid, set_transport_tracers, the
+ * velocities of the last evp resident, and mm / tm uploaded (construct_fields_upload).
+ *   compute / group: every rank of the run calls it.
+ *   fetch:   mm (nx_block, ny_block, 0:ncat), tm (nx_block, ny_block, ntrace, ncat) after the remap (physical cells; the
+ *            caller's ice_HaloUpdate of the state follows as in transport_remap, ice_transport_driver.F90:490-520), and
+ *            what the reference would print before abort_ice: *stop = 0 completed, 1 bad departure points (:552-563),
+ *            2 negative open-water area (:783-795), 3 negative ice area of category *stop_cat (:797-825); istop, jstop the
+ *            block indices it reports.  After a stop the arrays are not meaningful (the reference aborts).
+ *   evp_gpu_horizontal_remap = construct_fields_upload + compute + fetch, mm and tm in place. */
+int evp_gpu_horizontal_remap_compute(evp_handle_t *h, double dt);
+int evp_gpu_horizontal_remap_group(evp_handle_t **handles, int n, double dt);
+int evp_gpu_horizontal_remap_fetch(evp_handle_t *h, double *mm, double *tm, int *stop, int *stop_cat, int *istop, int *jstop);
+int evp_gpu_horizontal_remap(evp_handle_t *h, double dt, double *mm, double *tm, int *stop, int *stop_cat, int *istop,
+                             int *jstop);
 /* Device time (CUDA events, ms) of the last call of each transport stage on this handle: ms[0] departure_points kernels,
- * ms[1] their two ghost updates, ms[2] the reconstruction kernel, ms[3] its ghost updates.  What the reference's
- * timer_advect / timer_bound would show for these stages (source/ice_timers.F90); bench.py reads it. */
-int evp_gpu_get_transport_timing(evp_handle_t *h, double ms[4]);
+ * ms[1] their two ghost updates, ms[2] the reconstruction kernel, ms[3] its ghost updates, ms[4] the edge fluxes and
+ * update_fields of the last horizontal_remap, ms[5] that whole horizontal_remap.  What the reference's timer_advect /
+ * timer_bound would show for these stages (source/ice_timers.F90); bench.py reads it. */
+int evp_gpu_get_transport_timing(evp_handle_t *h, double ms[6]);
 
 /* Several ranks driven by one host thread (handles of ranks 0..n-1 on ONE device, e.g. tests with
  * fewer GPUs than ranks): steps are interleaved on one stream so that no kernel ever waits. */

@@ -647,3 +647,72 @@ def test_construct_fields_gx3_and_argument_errors(dev):
             e.set_transport_tracers(5, many, 0 * many, 0 * many, d)
     finally:
         e.close()
+
+
+# ---- all of horizontal_remap ---------------------------------------------------------------------
+def _remap_case(dev, grid, scenario, nranks, dt_scale, geometry="cice", seed=7, ndte=6, tarear_scale=1.0):
+    """evp(dt), then horizontal_remap on the device from the resident velocities against the oracle's (pinned to the
+    reference text routine by routine and as a whole), every cell of mm and tm."""
+    case = fx.make_case(grid, scenario, ndte=ndte, dt=3600.0)
+    got = clone_case(case)
+    d = fx.transport_tracers(grid, case.inp, seed, geometry)
+    ncat = d["tm"].shape[0]
+    f = dict(grid.f)
+    f["tarear"] = grid.f["tarear"] * tarear_scale           # > 1: exaggerated flux divergence, areas go negative
+    dt = case.dt * dt_scale
+    if nranks == 1:
+        e = dev.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True)
+        try:
+            e.set_grid(f)
+            e.set_transport_grid(f)
+            e.set_transport_tracers(ncat, d["tracer_type"], d["depend"], d["has_dependents"], d)
+            e.evp(case.dt, got.inp, got.io, got.out)
+            mm, tm, stop = e.horizontal_remap(dt, d["mm"], d["tm"])
+            stops = [stop]
+        finally:
+            e.close()
+    else:
+        g = dev.EvpGroup(case.dom, case.ndte, case.dt, nranks, strict=True)
+        try:
+            g.set_grid(f)
+            g.set_transport_grid(f)
+            g.set_transport_tracers(ncat, d["tracer_type"], d["depend"], d["has_dependents"], d)
+            g.evp(case.dt, got.inp, got.io, got.out)
+            mm, tm, stops = g.horizontal_remap(dt, d["mm"], d["tm"])
+        finally:
+            g.close()
+    geo = dict(d)
+    geo.update({k: f[k] for k in ("dxu", "dyu", "HTN", "HTE", "tarear")})
+    rmm, rtm = d["mm"].copy(), d["tm"].copy()
+    rstop = orc.horizontal_remap(case.dom, dt, d["tracer_type"], d["depend"], d["has_dependents"], geo, got.io["uvel"],
+                                 got.io["vvel"], rmm, rtm)
+    return mm, tm, stops, rmm, rtm, rstop, d
+
+
+@pytest.mark.parametrize("nranks,geometry,dt_scale", [(1, "cice", 40.0), (1, "random", 150.0), (2, "cice", 150.0), (4, "random", 40.0)])
+def test_horizontal_remap_bitwise(dev, nranks, geometry, dt_scale):
+    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
+    mm, tm, stops, rmm, rtm, rstop, d = _remap_case(dev, grid, "caps", nranks, dt_scale, geometry)
+    assert rstop == (0, 0, 0, 0) and all(s == (0, 0, 0, 0) for s in stops)
+    assert np.array_equal(mm, rmm) and np.array_equal(tm, rtm)
+    assert np.array_equal(np.signbit(tm), np.signbit(rtm))
+    moved = np.abs(rmm - d["mm"])[:, 1:-1, 1:-1]
+    assert moved.max() > 1e-3 and np.count_nonzero(moved) > 1000         # ice was transported
+    assert np.abs(rtm - d["tm"])[:, 3:, 1:-1, 1:-1].max() > 1e-6           # the type-2 / type-3 tracers too
+    tot0 = (d["mm"][:, 1:-1, 1:-1] * grid.f["tarea"][1:-1, 1:-1]).sum()    # area is conserved up to the clipping of
+    tot1 = (rmm[:, 1:-1, 1:-1] * grid.f["tarea"][1:-1, 1:-1]).sum()        # negative areas and the open boundaries
+    assert abs(tot1 - tot0) < 1e-3 * tot0
+
+
+def test_horizontal_remap_gx3_and_stops(dev):
+    """Displaced-pole grid; then a time step so long that the remap must stop: bad departure points, reported as the
+    reference reports them."""
+    grid = fx.make_grid("gx3")
+    mm, tm, stops, rmm, rtm, rstop, d = _remap_case(dev, grid, "full", 1, 20.0, "random")
+    assert rstop == (0, 0, 0, 0) and stops == [rstop]
+    assert np.array_equal(mm, rmm) and np.array_equal(tm, rtm)
+    mm, tm, stops, rmm, rtm, rstop, d = _remap_case(dev, grid, "full", 1, 4.0e3, "random")
+    assert rstop[0] == 1 and stops == [rstop]
+    # negative new areas: open water first, then (open water made thick enough) an ice category
+    mm, tm, stops, rmm, rtm, rstop, d = _remap_case(dev, grid, "full", 1, 20.0, "random", tarear_scale=40.0)
+    assert rstop[0] in (2, 3) and rstop[2] > 1 and stops == [rstop]

@@ -1,7 +1,8 @@
 """Horizontal transport, first stages on the device, bit for bit against the oracle
 (oracle/remap_oracle.c, itself pinned to the reference text): departure_points (source/ice_transport_remap.F90:1493-1670)
 + the ghost update of dpx, dpy (:574-578) from the resident velocities of the last evp; make_masks + construct_fields +
-limited_gradient (:867-1484) + the ghost updates of mc, mx, my, tc, tx, ty (:579-584, :616-621).  The test bodies are the
+limited_gradient (:867-1484) + the ghost updates of mc, mx, my, tc, tx, ty (:579-584, :616-621); and all of horizontal_remap (:309-850: the two stages
+above, then locate_triangles, triangle_coordinates, transport_integrals per edge and update_fields).  The test bodies are the
 ones the CPU tier runs on the host build of the device sources."""
 import pytest
 
@@ -47,3 +48,23 @@ def test_construct_fields_one_degree_tripole_on_device():
         assert np.array_equal(got[k], want[k]), k
         assert np.array_equal(np.signbit(got[k]), np.signbit(want[k])), k
     assert np.count_nonzero(want["tx"]) > 10000
+
+
+@pytest.mark.parametrize("nranks,geometry,dt_scale", [(1, "cice", 40.0), (1, "random", 150.0), (2, "cice", 150.0), (4, "random", 40.0)])
+def test_horizontal_remap_bitwise_on_device(nranks, geometry, dt_scale):
+    shared.test_horizontal_remap_bitwise(evp, nranks, geometry, dt_scale)
+
+
+def test_horizontal_remap_gx3_and_stops_on_device():
+    shared.test_horizontal_remap_gx3_and_stops(evp)
+
+
+def test_horizontal_remap_one_degree_tripole_on_device():
+    """The 1-degree tripole after a full evp (ndte = 120), a transport step of six hours."""
+    from cice5_b200 import fixtures as fx
+    import numpy as np
+    grid = fx.make_grid("tp1")
+    mm, tm, stops, rmm, rtm, rstop, d = shared._remap_case(evp, grid, "caps", 1, 6.0, "cice", ndte=120)
+    assert rstop == (0, 0, 0, 0) and stops == [rstop]
+    assert np.array_equal(mm, rmm) and np.array_equal(tm, rtm) and np.array_equal(np.signbit(tm), np.signbit(rtm))
+    assert np.abs(rmm - d["mm"]).max() > 1e-4
