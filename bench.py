@@ -535,6 +535,16 @@ def transport_block(e, args, grid, case, dt, steps=5, warmup=2):
         e.construct_fields_compute()
         if k >= warmup:
             rec.append(e.transport_timing())
+    # all of horizontal_remap (reconstruction + departure points + their ghost updates + edge fluxes + update_fields);
+    # mm / tm are updated in place, so every call starts from a fresh upload (not timed)
+    rem = []
+    stop = None
+    for k in range(1 + 3):
+        e.construct_fields_upload(d["mm"], d["tm"])
+        e.horizontal_remap_compute(dt)
+        if k >= 1:
+            rem.append(e.transport_timing())
+    mm_new, _, stop = e.horizontal_remap_fetch()
     med = lambda rows, key: float(np.median([r[key] for r in rows]))
     # algorithmic bytes per cell: departure reads u, v, dxu, dyu, HTN, HTE and writes dpx, dpy twice (first-order,
     # midpoint) -> 10 doubles; reconstruction, per ice category, reads mm + ntrace tracers + hm xav yav xxav yyav and
@@ -548,6 +558,16 @@ def transport_block(e, args, grid, case, dt, steps=5, warmup=2):
             "construct_fields": {"kernel_ms": rms, "halo_ms": med(rec, "reconstruct_halo_ms"), "alg_bytes": rec_bytes,
                                  "achieved_GBps": rec_bytes / (rms * 1e-3) / 1e9, "frac": rec_bytes / (rms * 1e-3) / 1e9 / peak,
                                  "halo_updates": 3 * (ncat + 1) + 3 * ncat * nt},
+            # per cell: the two edge sweeps gather dpx dpy dxu dyu + (mc mx my) x (ncat+1) + (tc tx ty) x ncat x ntrace and
+            # write (ncat+1) + ncat x ntrace flux planes each; update_fields reads both flux sets, mm, tm, tarear and
+            # writes mm, tm
+            "horizontal_remap": (lambda fb, ms, fms: {"remap_ms": ms, "fluxes_and_update_ms": fms, "fluxes_and_update_alg_bytes": fb,
+                                                      "fluxes_and_update_GBps": fb / (fms * 1e-3) / 1e9,
+                                                      "fluxes_and_update_frac": fb / (fms * 1e-3) / 1e9 / peak,
+                                                      "stop": list(stop), "max_abs_area_change": float(np.abs(mm_new - d["mm"])[:, 1:-1, 1:-1].max())})(
+                8 * cells * (2 * (4 + 3 * (ncat + 1) + 3 * ncat * nt) + 2 * ((ncat + 1) + ncat * nt)        # edge sweeps
+                             + 2 * ((ncat + 1) + ncat * nt) + 2 * ((ncat + 1) + ncat * nt) + 1),             # update_fields
+                med(rem, "remap_ms"), med(rem, "flux_update_ms")),
             "peak_GBps": peak, "peak_source": peak_src,
             "parity": "tests/test_gpu_zt_transport.py: bitwise against oracle/remap_oracle.c (pinned to the reference text)"}
 

@@ -2000,7 +2000,10 @@ void build_remap(evp_handle *h, double dt, std::vector<Op> &ops)
         f.dpx = h->plane(W_1); f.dpy = h->plane(W_2);
         f.dxu = h->tr; f.dyu = h->tr + h->plane_elems;
         for (int e = 0; e < 2; ++e) { f.mflx[e] = pl(l.mflx(e)); f.mtflx[e] = pl(l.mtflx(e)); }
-        edge_flux_kernel<<<dim3((h->nxb + 127) / 128, h->nyb, 2), 128, (size_t)nslots * 128 * 24, L.s()>>>(f, nslots);
+        // shared memory per block: (1 + ntrace + 3 slots) doubles x 128 threads (at most (1 + 128 + 48) KB: opt in)
+        const size_t fsm = (size_t)(1 + l.ntrace + 3 * nslots) * 128 * sizeof(double);
+        if (fsm > 48 * 1024) CK(cudaFuncSetAttribute(edge_flux_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm));
+        edge_flux_kernel<<<dim3((h->nxb + 127) / 128, h->nyb, 2 * (l.ncat + 1)), 128, fsm, L.s()>>>(f, nslots);
         CK(cudaGetLastError());
         UpdateArgs u;
         u.a = h->rc_args;

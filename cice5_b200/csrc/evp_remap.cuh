@@ -326,6 +326,10 @@ __device__ const signed char kShift[2][6][2] = {{{1, 1}, {0, 1}, {1, -1}, {0, -1
                                                 {{-1, 1}, {-1, 0}, {1, 1}, {1, 0}, {0, 1}, {0, 0}}};
 constexpr double puny = 1.0e-11, eps16 = 1.0e-16;
 }  // namespace flux
+#ifndef EVP_FLUX_CHUNK
+#define EVP_FLUX_CHUNK 4
+#endif
+constexpr int kFluxChunk = EVP_FLUX_CHUNK;
 
 struct FluxArgs {
     ReconArgs a;                       // sizes, tracer tables, the reconstructed fields mc mx my tc tx ty
@@ -333,24 +337,30 @@ struct FluxArgs {
     double *mflx[2], *mtflx[2];        // [east, north]: ncat+1 planes; ncat * ntrace planes
 };
 
-// grid: (ceil(nxb / 128), nyb, 2); blockIdx.z = 0 east edges, 1 north edges.  Dynamic shared memory: per tracer with
-// dependents and thread mtsum, mtxsum, mtysum of the current triangle (3 x 8 bytes x 128 x slots)
+// grid: (ceil(nxb / 128), nyb, 2 * (ncat + 1)); blockIdx.z = edge * (ncat + 1) + category, edge 0 = east, 1 = north: a
+// thread integrates one category (its mass and every tracer) over the triangles of one cell edge; the triangles are
+// worked out again per category (a few hundred operations against the ~100 gathers of a category).
+// Dynamic shared memory, per thread: the flux accumulators of the category (1 + ntrace doubles) and, per tracer with
+// dependents, mtsum, mtxsum, mtysum of the current triangle (3 doubles x slots)
 __global__ void __launch_bounds__(128) edge_flux_kernel(const __grid_constant__ FluxArgs f, int nslots)
 {
     using namespace flux;
     extern __shared__ double par[];
     const ReconArgs &a = f.a;
-    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y, north = blockIdx.z;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+    const int north = blockIdx.z / (a.ncat + 1), n = blockIdx.z % (a.ncat + 1);
     if (c >= a.nxb) return;
     const size_t q = (size_t)r * a.ld + c;
-    double *mflx = f.mflx[north], *mtflx = f.mtflx[north];
-    const int nplanes_t = a.ncat * a.ntrace;
+    const int ntr = n > 0 ? a.ntrace : 0;
+    double *acc = par + threadIdx.x;                                        // acc[k * 128]: k = 0 mass, 1 + nt tracers
+    double *mtsum = par + (size_t)(1 + a.ntrace) * 128 + threadIdx.x, *mtxsum = mtsum + (size_t)nslots * 128,
+           *mtysum = mtxsum + (size_t)nslots * 128;
+    for (int k = 0; k <= ntr; ++k) acc[k * 128] = 0.0;                      // mflx = c0, mtflx = c0 (:3224-3230)
     // edges of the block that carry a flux (:1820-1826, :1860-1866); every other cell of the flux planes is zero
     const bool edge = north ? (c >= 1 && c <= a.nxb - 2 && r <= a.nyb - 2) : (c <= a.nxb - 2 && r >= 1 && r <= a.nyb - 2);
     const size_t ql = north ? q - 1 : q, qr = north ? q : q - a.ld;       // corners: left (i-1,j | i,j), right (i,j | i,j-1)
     bool moving = false;
     if (edge) moving = f.dpx[ql] != 0.0 || f.dpy[ql] != 0.0 || f.dpx[qr] != 0.0 || f.dpy[qr] != 0.0;        // :1956-1980
-    bool first = true;                 // nothing accumulated in this thread's flux cells yet
     if (moving) {
         const double fl = f.dxu[ql] * f.dyu[ql], fr = f.dxu[qr] * f.dyu[qr], fc = 0.5 * (fl + fr);           // areafac
         const double dxl = f.dpx[ql] / f.dxu[ql], dyl = f.dpy[ql] / f.dyu[ql];                               // :1986-1991
@@ -410,8 +420,8 @@ __global__ void __launch_bounds__(128) edge_flux_kernel(const __grid_constant__ 
                 const Row w = rows[s3][k];
                 if (w.ng) tri[w.ng - 1] = w;
             }
-        double *mtsum = par + threadIdx.x, *mtxsum = par + (size_t)nslots * 128 + threadIdx.x,
-               *mtysum = par + (size_t)2 * nslots * 128 + threadIdx.x;
+        const double *mcp = a.mc + (size_t)n * a.pe, *mxp = a.mx + (size_t)n * a.pe, *myp = a.my + (size_t)n * a.pe;
+        const size_t t0 = (size_t)(n > 0 ? n - 1 : 0) * a.ntrace * a.pe;
         for (int g = 0; g < 6; ++g) {                                      // groups in ascending order (:3235)
             const Row w = tri[g];
             if (!w.ng) continue;
@@ -436,31 +446,39 @@ __global__ void __launch_bounds__(128) edge_flux_kernel(const __grid_constant__ 
             x2 = 0.4 * x2 + 0.6 * x0; y2 = 0.4 * y2 + 0.6 * y0;
             x3 = 0.4 * x3 + 0.6 * x0; y3 = 0.4 * y3 + 0.6 * y0;
             const size_t qs = q + (ptrdiff_t)js * a.ld + is;                // source cell (iflux, jflux)
-            for (int n = 0; n <= a.ncat; ++n) {                            // :3380-3420, cubic (4-point) formula
-                const double mc = a.mc[(size_t)n * a.pe + qs], mx = a.mx[(size_t)n * a.pe + qs], my = a.my[(size_t)n * a.pe + qs];
-                const double m0 = (-9.0 / 16.0) * (mc + x0 * mx + y0 * my);
-                const double m1 = (25.0 / 48.0) * (mc + x1 * mx + y1 * my);
-                const double m2 = (25.0 / 48.0) * (mc + x2 * mx + y2 * my);
-                const double m3 = (25.0 / 48.0) * (mc + x3 * mx + y3 * my);
-                const double msum = m0 + m1 + m2 + m3;
-                double *o = mflx + (size_t)n * a.pe + q;
-                *o = (first ? 0.0 : *o) + area * msum;
-                if (n == 0 || a.ntrace == 0) continue;
-                double w0 = m0 * x0, w1 = m1 * x1, w2 = m2 * x2, w3 = m3 * x3;
-                const double mxsum = w0 + w1 + w2 + w3;
-                const double mxxsum = w0 * x0 + w1 * x1 + w2 * x2 + w3 * x3;
-                const double mxysum = w0 * y0 + w1 * y1 + w2 * y2 + w3 * y3;
-                w0 = m0 * y0; w1 = m1 * y1; w2 = m2 * y2; w3 = m3 * y3;
-                const double mysum = w0 + w1 + w2 + w3;
-                const double myysum = w0 * y0 + w1 * y1 + w2 * y2 + w3 * y3;
-                const size_t t0 = (size_t)(n - 1) * a.ntrace * a.pe;
-                for (int nt = 0; nt < a.ntrace; ++nt) {                    // :3423-3500
-                    const size_t pl = t0 + (size_t)nt * a.pe;
+            // :3380-3420, cubic (4-point) formula
+            const double mc = mcp[qs], mx = mxp[qs], my = myp[qs];
+            const double m0 = (-9.0 / 16.0) * (mc + x0 * mx + y0 * my);
+            const double m1 = (25.0 / 48.0) * (mc + x1 * mx + y1 * my);
+            const double m2 = (25.0 / 48.0) * (mc + x2 * mx + y2 * my);
+            const double m3 = (25.0 / 48.0) * (mc + x3 * mx + y3 * my);
+            const double msum = m0 + m1 + m2 + m3;
+            acc[0] = acc[0] + area * msum;
+            if (ntr == 0) continue;
+            double w0 = m0 * x0, w1 = m1 * x1, w2 = m2 * x2, w3 = m3 * x3;
+            const double mxsum = w0 + w1 + w2 + w3;
+            const double mxxsum = w0 * x0 + w1 * x1 + w2 * x2 + w3 * x3;
+            const double mxysum = w0 * y0 + w1 * y1 + w2 * y2 + w3 * y3;
+            w0 = m0 * y0; w1 = m1 * y1; w2 = m2 * y2; w3 = m3 * y3;
+            const double mysum = w0 + w1 + w2 + w3;
+            const double myysum = w0 * y0 + w1 * y1 + w2 * y2 + w3 * y3;
+            // :3423-3500.  A thread's loads are its latency: the fields of kFluxChunk tracers are requested together
+            // before the first is used (tx, ty of a type-3 tracer are loaded and ignored)
+            for (int nb = 0; nb < ntr; nb += kFluxChunk) {
+                double tcv[kFluxChunk], txv[kFluxChunk], tyv[kFluxChunk];
+#pragma unroll
+                for (int k = 0; k < kFluxChunk; ++k) {
+                    const size_t pl = t0 + (size_t)(nb + k < ntr ? nb + k : nb) * a.pe + qs;
+                    tcv[k] = a.tc[pl]; txv[k] = a.tx[pl]; tyv[k] = a.ty[pl];
+                }
+#pragma unroll
+                for (int k = 0; k < kFluxChunk; ++k) {
+                    const int nt = nb + k;
+                    if (nt >= ntr) break;
                     const int type = a.ttype[nt], sl = a.slot[nt] * 128;
-                    const double tc = a.tc[pl + qs];
+                    const double tc = tcv[k], tx = txv[k], ty = tyv[k];
                     double ms;
                     if (type == 1) {
-                        const double tx = a.tx[pl + qs], ty = a.ty[pl + qs];
                         ms = msum * tc + mxsum * tx + mysum * ty;
                         if (sl >= 0) {
                             mtsum[sl] = ms;
@@ -469,21 +487,18 @@ __global__ void __launch_bounds__(128) edge_flux_kernel(const __grid_constant__ 
                         }
                     } else {
                         const int s1 = a.slot[a.parent[nt]] * 128;
-                        if (type == 2) ms = mtsum[s1] * tc + mtxsum[s1] * a.tx[pl + qs] + mtysum[s1] * a.ty[pl + qs];
+                        if (type == 2) ms = mtsum[s1] * tc + mtxsum[s1] * tx + mtysum[s1] * ty;
                         else ms = mtsum[s1] * tc;
                         if (sl >= 0) mtsum[sl] = ms;
                     }
-                    double *ot = mtflx + pl + q;
-                    *ot = (first ? 0.0 : *ot) + area * ms;
+                    acc[(1 + nt) * 128] = acc[(1 + nt) * 128] + area * ms;
                 }
             }
-            first = false;
         }
     }
-    if (first) {                                                           // no triangle: the fluxes are zero (:3224-3230)
-        for (int n = 0; n <= a.ncat; ++n) mflx[(size_t)n * a.pe + q] = 0.0;
-        for (int k = 0; k < nplanes_t; ++k) mtflx[(size_t)k * a.pe + q] = 0.0;
-    }
+    f.mflx[north][(size_t)n * a.pe + q] = acc[0];
+    const size_t t0 = (size_t)(n > 0 ? n - 1 : 0) * a.ntrace * a.pe;
+    for (int nt = 0; nt < ntr; ++nt) f.mtflx[north][t0 + (size_t)nt * a.pe + q] = acc[(1 + nt) * 128];
 }
 
 struct UpdateArgs {
@@ -514,34 +529,43 @@ __global__ void __launch_bounds__(128) update_fields_kernel(const __grid_constan
     u.mm[(size_t)n * a.pe + q] = m;
     if (n == 0 || a.ntrace == 0) return;
     const size_t t0 = (size_t)(n - 1) * a.ntrace * a.pe;
-    for (int nt = 0; nt < a.ntrace; ++nt) {
-        const size_t pl = t0 + (size_t)nt * a.pe;
-        const int type = a.ttype[nt], sl = a.slot[nt] * 128;
-        const double t = u.tm[pl + q];
-        double mtold, den = m, tn = 0.0;                                   // :3560-3590, :3645-3700
-        bool on = m > 0.0;
-        if (type == 1) {
-            mtold = mold * t;
-        } else {
-            const int s1 = a.slot[a.parent[nt]] * 128;
-            if (type == 2) {
-                mtold = mold * told[s1] * t;
-                on = on && fabs(tnew[s1]) > 0.0;
-                den = m * tnew[s1];
-            } else {
-                const int s2 = a.slot[a.parent[a.parent[nt]]] * 128;
-                mtold = mold * told[s2] * told[s1] * t;
-                on = on && fabs(tnew[s1]) > 0.0 && fabs(tnew[s2]) > 0.0;
-                den = m * tnew[s2] * tnew[s1];
-            }
-        }
-        if (on) {
+    for (int nb = 0; nb < a.ntrace; nb += kFluxChunk) {                    // loads of kFluxChunk tracers in flight together
+        double tv[kFluxChunk], wv[kFluxChunk];
+#pragma unroll
+        for (int k = 0; k < kFluxChunk; ++k) {
+            const size_t pl = t0 + (size_t)(nb + k < a.ntrace ? nb + k : nb) * a.pe;
             const double *te = u.mtflx[0] + pl, *tn_ = u.mtflx[1] + pl;
-            w1 = te[q] - te[q - 1] + tn_[q] - tn_[q - a.ld];
-            tn = (mtold - w1 * tarear) / den;
+            tv[k] = u.tm[pl + q];
+            wv[k] = te[q] - te[q - 1] + tn_[q] - tn_[q - a.ld];            // used only where the reference evaluates it
         }
-        if (sl >= 0) { told[sl] = t; tnew[sl] = tn; }
-        u.tm[pl + q] = tn;
+#pragma unroll
+        for (int k = 0; k < kFluxChunk; ++k) {
+            const int nt = nb + k;
+            if (nt >= a.ntrace) break;
+            const size_t pl = t0 + (size_t)nt * a.pe;
+            const int type = a.ttype[nt], sl = a.slot[nt] * 128;
+            const double t = tv[k];
+            double mtold, den = m, tn = 0.0;                               // :3560-3590, :3645-3700
+            bool on = m > 0.0;
+            if (type == 1) {
+                mtold = mold * t;
+            } else {
+                const int s1 = a.slot[a.parent[nt]] * 128;
+                if (type == 2) {
+                    mtold = mold * told[s1] * t;
+                    on = on && fabs(tnew[s1]) > 0.0;
+                    den = m * tnew[s1];
+                } else {
+                    const int s2 = a.slot[a.parent[a.parent[nt]]] * 128;
+                    mtold = mold * told[s2] * told[s1] * t;
+                    on = on && fabs(tnew[s1]) > 0.0 && fabs(tnew[s2]) > 0.0;
+                    den = m * tnew[s2] * tnew[s1];
+                }
+            }
+            if (on) tn = (mtold - wv[k] * tarear) / den;
+            if (sl >= 0) { told[sl] = t; tnew[sl] = tn; }
+            u.tm[pl + q] = tn;
+        }
     }
 }
 

@@ -53,6 +53,8 @@ def test_measure_reports_parity_value_checks_and_e2e(tiny):
     for k in ("departure_points", "construct_fields"):
         assert t[k]["kernel_ms"] > 0 and t[k]["achieved_GBps"] > 0 and t[k]["alg_bytes"] > 0
     assert t["construct_fields"]["halo_updates"] == 183
+    assert t["horizontal_remap"]["remap_ms"] > 0 and t["horizontal_remap"]["stop"] == [0, 0, 0, 0]
+    assert t["horizontal_remap"]["max_abs_area_change"] > 0
 
 
 def test_parity_leg_detects_a_wrong_result(tiny, monkeypatch):
