@@ -152,6 +152,9 @@ struct evp_handle {
     int *rc_stop = nullptr;       // update_fields: per category 0 or 1 + r * nxb + c of the last cell with a negative new area
     int h_rc_stop[256];
     bool rc_loaded = false, rc_remapped = false;
+    // transport_remap: the ice state aice0, aicen, vicen, vsnon (ncat each), trcrn (ncat * ntrcr) as planes
+    double *st = nullptr;
+    bool st_loaded = false, st_done = false;
     cudaEvent_t tev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // transport stage: start, kernels done, ghost updates
                                                           // done; whole remap: start, end
     double tr_ms[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};     // departure kernels / halos, reconstruction kernel / halos, fluxes + update, whole remap
@@ -503,6 +506,7 @@ int evp_gpu_finalize(evp_handle_t *h)
     if (h->itd) cudaFree(h->itd);
     if (h->tr) cudaFree(h->tr);
     if (h->rc) cudaFree(h->rc);
+    if (h->st) cudaFree(h->st);
     for (auto &ev : h->tev) if (ev) cudaEventDestroy(ev);
     if (h->stage) cudaFree(h->stage);
     if (h->arena) cudaFree(h->arena);
@@ -1857,6 +1861,8 @@ int evp_gpu_set_transport_tracers(evp_handle_t *h, int ncat, int ntrace, const i
         CK(cudaStreamSynchronize(h->stream));
         CK(cudaFree(h->rc));
         h->rc = nullptr;
+        if (h->st) { CK(cudaFree(h->st)); h->st = nullptr; }
+        h->st_loaded = h->st_done = h->rc_remapped = false;
     }
     if (!h->rc) {
         CK(cudaMalloc(&h->rc, l.planes() * h->plane_elems * sizeof(double) + 1024));
@@ -2000,10 +2006,12 @@ void build_remap(evp_handle *h, double dt, std::vector<Op> &ops)
         f.dpx = h->plane(W_1); f.dpy = h->plane(W_2);
         f.dxu = h->tr; f.dyu = h->tr + h->plane_elems;
         for (int e = 0; e < 2; ++e) { f.mflx[e] = pl(l.mflx(e)); f.mtflx[e] = pl(l.mtflx(e)); }
-        // shared memory per block: (1 + ntrace + 3 slots) doubles x 128 threads (at most (1 + 128 + 48) KB: opt in)
-        const size_t fsm = (size_t)(1 + l.ntrace + 3 * nslots) * 128 * sizeof(double);
+        // shared memory per block: (1 + ntrace + 3 slots [+ 20]) doubles x 128 threads (above 48 KB: opt in)
+        const size_t fsm = (size_t)(1 + l.ntrace + 3 * nslots + (EVP_FLUX_PTS_SMEM ? 20 : 0)) * 128 * sizeof(double);
         if (fsm > 48 * 1024) CK(cudaFuncSetAttribute(edge_flux_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm));
-        edge_flux_kernel<<<dim3((h->nxb + 127) / 128, h->nyb, 2 * (l.ncat + 1)), 128, fsm, L.s()>>>(f, nslots);
+        const int xb = (h->nxb + 127) / 128;
+        const dim3 fgrid = EVP_FLUX_EDGE_X ? dim3(2 * xb, h->nyb, l.ncat + 1) : dim3(xb, h->nyb, 2 * (l.ncat + 1));
+        edge_flux_kernel<<<fgrid, 128, fsm, L.s()>>>(f, nslots);
         CK(cudaGetLastError());
         UpdateArgs u;
         u.a = h->rc_args;
@@ -2128,6 +2136,188 @@ int evp_gpu_horizontal_remap(evp_handle_t *h, double dt, double *mm, double *tm,
     TRY(evp_gpu_construct_fields_upload(h, mm, tm));
     TRY(evp_gpu_horizontal_remap_compute(h, dt));
     return evp_gpu_horizontal_remap_fetch(h, mm, tm, stop, stop_cat, istop, jstop);
+}
+
+// ---- transport_remap: the caller of horizontal_remap, from and to the ice state -------------------------------------
+}  // extern "C"
+namespace {
+struct StLayout {
+    int ncat, ntrcr;
+    size_t aice0() const { return 0; }
+    size_t aicen(int n) const { return 1 + (size_t)n; }                                // n = 0 .. ncat-1
+    size_t vicen(int n) const { return 1 + (size_t)ncat + n; }
+    size_t vsnon(int n) const { return 1 + 2 * (size_t)ncat + n; }
+    size_t trcrn(int k) const { return 1 + 3 * (size_t)ncat + k; }                      // k = (n-1)*ntrcr + it-1
+    size_t planes() const { return trcrn(ncat * ntrcr); }
+};
+StLayout st_layout(const evp_handle *h) { return StLayout{h->rc_args.ncat, h->rc_args.ntrace - 2}; }
+
+// transport_remap (source/ice_transport_driver.F90:198-627; l_conservation_check = l_monotonicity_check = .false.):
+// state_to_tracers, horizontal_remap, tracers_to_state, bound_state (source/ice_state.F90:173-238)
+void build_transport(evp_handle *h, double dt, int nt_qsno, int nslyr, double rhos, double Lfresh, std::vector<Op> &ops)
+{
+    const RcLayout l = rc_layout(h);
+    const StLayout sl = st_layout(h);
+    auto args = [h, l, sl, nt_qsno, nslyr, rhos, Lfresh]() {
+        StateArgs s;
+        auto sp = [h](size_t k) { return h->st + k * h->plane_elems; };
+        s.nxb = h->nxb; s.nyb = h->nyb; s.ld = h->ld; s.pe = h->plane_elems;
+        s.ncat = sl.ncat; s.ntrcr = sl.ntrcr; s.nt_qsno = nt_qsno; s.nslyr = nslyr; s.rhosLf = rhos * Lfresh;
+        s.aice0 = sp(sl.aice0()); s.aicen = sp(sl.aicen(0)); s.vicen = sp(sl.vicen(0)); s.vsnon = sp(sl.vsnon(0));
+        s.trcrn = sp(sl.trcrn(0));
+        s.aim = h->rc + l.mm(0) * h->plane_elems; s.trm = h->rc + l.tm(0) * h->plane_elems;
+        return s;
+    };
+    {
+        Builder B{h, ops};
+        B.op([h, l, args](Launcher &L) {
+            state_to_tracers_kernel<<<dim3((h->nxb + 127) / 128, h->nyb, l.ncat + 1), 128, 0, L.s()>>>(args());
+            ++L.n;
+            CK(cudaGetLastError());
+            return EVP_OK;
+        });
+    }
+    build_remap(h, dt, ops);
+    Builder B{h, ops};
+    B.op([h, l, args](Launcher &L) {
+        tracers_to_state_kernel<<<dim3((h->nxb + 127) / 128, h->nyb, l.ncat + 1), 128, 0, L.s()>>>(args());
+        ++L.n;
+        CK(cudaGetLastError());
+        return EVP_OK;
+    });
+    auto sp = [h](size_t k) { return h->st + k * h->plane_elems; };
+    B.sync();
+    B.halo_multi(sp(sl.aicen(0)), sl.ncat, h->plane_elems, 1.0, 0.0);                    // bound_state: center, scalar
+    if (sl.ntrcr > 0) B.halo_multi(sp(sl.trcrn(0)), sl.ncat * sl.ntrcr, h->plane_elems, 1.0, 0.0);
+    B.halo_multi(sp(sl.vicen(0)), 2 * sl.ncat, h->plane_elems, 1.0, 0.0);                // vicen, vsnon
+    B.sync();
+    stage_mark(B, 4);
+}
+int transport_ready(const evp_handle *h)
+{
+    if (!h->tr || !h->rc || !h->st || !h->st_loaded || !h->uploaded || !h->peers_set || !h->grid_set) return EVP_ERR_STATE;
+    if (h->rc_args.ntrace < 2) return EVP_ERR_STATE;             // hice, hsno lead the tracer table
+    return EVP_OK;
+}
+int finish_transport(evp_handle *h)
+{
+    h->rc_loaded = true;                                         // state_to_tracers filled mm, tm
+    TRY(finish_remap(h));
+    h->st_loaded = false;
+    h->st_done = true;
+    return EVP_OK;
+}
+}  // namespace
+extern "C" {
+
+int evp_gpu_transport_remap_upload(evp_handle_t *h, const double *aice0, const double *aicen, const double *trcrn,
+                                   const double *vicen, const double *vsnon)
+{
+    if (!h || !aice0 || !aicen || !vicen || !vsnon) return EVP_ERR_ARG;
+    if (!h->rc || h->rc_args.ntrace < 2) return EVP_ERR_STATE;
+    const StLayout sl = st_layout(h);
+    if (sl.ntrcr > 0 && !trcrn) return EVP_ERR_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    if (!h->st) {
+        CK(cudaMalloc(&h->st, sl.planes() * h->plane_elems * sizeof(double)));
+        CK(cudaMemset(h->st, 0, sl.planes() * h->plane_elems * sizeof(double)));
+    }
+    const size_t cells = (size_t)h->nxb * h->nyb;
+    auto sp = [h](size_t k) { return h->st + k * h->plane_elems; };
+    TRY(h2d_any(h, sp(sl.aice0()), aice0, 0));
+    for (int n = 0; n < sl.ncat; ++n) {
+        TRY(h2d_any(h, sp(sl.aicen(n)), aicen + (size_t)n * cells, 0));
+        TRY(h2d_any(h, sp(sl.vicen(n)), vicen + (size_t)n * cells, 0));
+        TRY(h2d_any(h, sp(sl.vsnon(n)), vsnon + (size_t)n * cells, 0));
+    }
+    for (int k = 0; k < sl.ncat * sl.ntrcr; ++k) TRY(h2d_any(h, sp(sl.trcrn(k)), trcrn + (size_t)k * cells, 0));
+    TRY(h2d_flush(h));
+    CK(cudaStreamSynchronize(h->stream));
+    h->st_loaded = true;
+    return EVP_OK;
+}
+
+int evp_gpu_transport_remap_compute(evp_handle_t *h, double dt, int nt_qsno, int nslyr, double rhos, double Lfresh)
+{
+    if (!h || !(dt > 0.0) || nslyr < 0) return EVP_ERR_ARG;
+    TRY(transport_ready(h));
+    CK(cudaSetDevice(h->cfg.device));
+    std::vector<Op> ops;
+    build_transport(h, dt, nt_qsno, nslyr, rhos, Lfresh, ops);
+    Launcher L{h};
+    for (const Op &op : ops) {
+        if (op.sync) { TRY(launch_signal(L)); TRY(launch_wait(L)); }
+        else TRY(op.fn(L));
+    }
+    return finish_transport(h);
+}
+
+// all ranks of a one-device group on one stream, steps interleaved (see evp_gpu_compute_group)
+int evp_gpu_transport_remap_group(evp_handle_t **hs, int n, double dt, int nt_qsno, int nslyr, double rhos, double Lfresh)
+{
+    if (!hs || n < 1 || n > kMaxRanks || !(dt > 0.0) || nslyr < 0) return EVP_ERR_ARG;
+    for (int r = 0; r < n; ++r) {
+        if (!hs[r] || hs[r]->cfg.nranks != n || hs[r]->cfg.rank != r) return EVP_ERR_ARG;
+        TRY(transport_ready(hs[r]));
+        if (hs[r]->cfg.device != hs[0]->cfg.device) return EVP_ERR_UNSUPPORTED;
+        if (hs[r]->rc_args.ncat != hs[0]->rc_args.ncat || hs[r]->rc_args.ntrace != hs[0]->rc_args.ntrace) return EVP_ERR_ARG;
+    }
+    CK(cudaSetDevice(hs[0]->cfg.device));
+    std::vector<std::vector<Op>> P(n);
+    std::vector<Launcher> L;
+    for (int r = 0; r < n; ++r) {
+        CK(cudaStreamSynchronize(hs[r]->stream));
+        hs[r]->stream = hs[0]->own_stream;
+        build_transport(hs[r], dt, nt_qsno, nslyr, rhos, Lfresh, P[r]);
+        L.push_back(Launcher{hs[r]});
+    }
+    int rc = EVP_OK;
+    for (size_t i = 0; i < P[0].size() && rc == EVP_OK; ++i) {
+        if (P[0][i].sync) {
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = launch_signal(L[r]);
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = launch_wait(L[r]);
+        } else {
+            for (int r = 0; r < n && rc == EVP_OK; ++r) rc = P[r][i].fn(L[r]);
+        }
+    }
+    for (int r = 0; r < n; ++r) {
+        const int rc2 = rc == EVP_OK ? finish_transport(hs[r]) : rc;
+        hs[r]->stream = hs[r]->own_stream;
+        if (rc2 != EVP_OK) rc = rc2;
+    }
+    return rc;
+}
+
+int evp_gpu_transport_remap_fetch(evp_handle_t *h, double *aice0, double *aicen, double *trcrn, double *vicen, double *vsnon,
+                                  int *stop, int *stop_cat, int *istop, int *jstop)
+{
+    if (!h) return EVP_ERR_ARG;
+    if (!h->st || !h->st_done) return EVP_ERR_STATE;
+    CK(cudaSetDevice(h->cfg.device));
+    const StLayout sl = st_layout(h);
+    const size_t cells = (size_t)h->nxb * h->nyb;
+    auto sp = [h](size_t k) { return h->st + k * h->plane_elems; };
+    D2HBatch B{h, {}};
+    h->batch_dst.clear();
+    if (aice0) TRY(B.add(sp(sl.aice0()), aice0, 0));
+    for (int n = 0; n < sl.ncat; ++n) {
+        if (aicen) TRY(B.add(sp(sl.aicen(n)), aicen + (size_t)n * cells, 0));
+        if (vicen) TRY(B.add(sp(sl.vicen(n)), vicen + (size_t)n * cells, 0));
+        if (vsnon) TRY(B.add(sp(sl.vsnon(n)), vsnon + (size_t)n * cells, 0));
+    }
+    if (trcrn) for (int k = 0; k < sl.ncat * sl.ntrcr; ++k) TRY(B.add(sp(sl.trcrn(k)), trcrn + (size_t)k * cells, 0));
+    TRY(B.flush());
+    CK(cudaStreamSynchronize(h->stream));
+    return evp_gpu_horizontal_remap_fetch(h, nullptr, nullptr, stop, stop_cat, istop, jstop);
+}
+
+int evp_gpu_transport_remap(evp_handle_t *h, double dt, int nt_qsno, int nslyr, double rhos, double Lfresh, double *aice0,
+                            double *aicen, double *trcrn, double *vicen, double *vsnon, int *stop, int *stop_cat, int *istop,
+                            int *jstop)
+{
+    TRY(evp_gpu_transport_remap_upload(h, aice0, aicen, trcrn, vicen, vsnon));
+    TRY(evp_gpu_transport_remap_compute(h, dt, nt_qsno, nslyr, rhos, Lfresh));
+    return evp_gpu_transport_remap_fetch(h, aice0, aicen, trcrn, vicen, vsnon, stop, stop_cat, istop, jstop);
 }
 
 int evp_gpu_principal_stress(evp_handle_t *h, double *sig1, double *sig2)

@@ -330,6 +330,12 @@ constexpr double puny = 1.0e-11, eps16 = 1.0e-16;
 #define EVP_FLUX_CHUNK 4
 #endif
 constexpr int kFluxChunk = EVP_FLUX_CHUNK;
+#ifndef EVP_FLUX_PTS_SMEM
+#define EVP_FLUX_PTS_SMEM 0
+#endif
+#ifndef EVP_FLUX_EDGE_X
+#define EVP_FLUX_EDGE_X 1
+#endif
 
 struct FluxArgs {
     ReconArgs a;                       // sizes, tracer tables, the reconstructed fields mc mx my tc tx ty
@@ -337,24 +343,38 @@ struct FluxArgs {
     double *mflx[2], *mtflx[2];        // [east, north]: ncat+1 planes; ncat * ntrace planes
 };
 
-// grid: (ceil(nxb / 128), nyb, 2 * (ncat + 1)); blockIdx.z = edge * (ncat + 1) + category, edge 0 = east, 1 = north: a
-// thread integrates one category (its mass and every tracer) over the triangles of one cell edge; the triangles are
-// worked out again per category (a few hundred operations against the ~100 gathers of a category).
-// Dynamic shared memory, per thread: the flux accumulators of the category (1 + ntrace doubles) and, per tracer with
-// dependents, mtsum, mtxsum, mtysum of the current triangle (3 doubles x slots)
+// grid: (2 * ceil(nxb / 128), nyb, ncat + 1); blockIdx.x = 2 * (column block) + edge (0 = east, 1 = north), blockIdx.z
+// = category: a thread integrates one category (its mass and every tracer) over the triangles of one cell edge; the
+// triangles are worked out again per category (a few hundred operations against the ~100 gathers of a category).  The
+// east and the north edges of the same cells run side by side: they gather from the same 3 x 3 cells, once from HBM.
+// Dynamic shared memory, per thread: the flux accumulators of the category (1 + ntrace doubles), per tracer with
+// dependents mtsum, mtxsum, mtysum of the current triangle (3 doubles x slots), and the ten points of the triangles
+// (20 doubles; they are picked by table index, which would put a per-thread array into local memory)
 __global__ void __launch_bounds__(128) edge_flux_kernel(const __grid_constant__ FluxArgs f, int nslots)
 {
     using namespace flux;
     extern __shared__ double par[];
     const ReconArgs &a = f.a;
+#if EVP_FLUX_EDGE_X
+    const int c = (blockIdx.x >> 1) * blockDim.x + threadIdx.x, r = blockIdx.y;
+    const int north = blockIdx.x & 1, n = blockIdx.z;
+#else
     const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
     const int north = blockIdx.z / (a.ncat + 1), n = blockIdx.z % (a.ncat + 1);
+#endif
     if (c >= a.nxb) return;
     const size_t q = (size_t)r * a.ld + c;
     const int ntr = n > 0 ? a.ntrace : 0;
     double *acc = par + threadIdx.x;                                        // acc[k * 128]: k = 0 mass, 1 + nt tracers
     double *mtsum = par + (size_t)(1 + a.ntrace) * 128 + threadIdx.x, *mtxsum = mtsum + (size_t)nslots * 128,
            *mtysum = mtxsum + (size_t)nslots * 128;
+#if EVP_FLUX_PTS_SMEM
+    constexpr int kPS = 128;
+    double *pxs = mtysum + (size_t)nslots * 128, *pys = pxs + 10 * 128;     // point k: pxs[k * 128], pys[k * 128]
+#else
+    constexpr int kPS = 1;
+    double pxs[10], pys[10];                                                // picked by table index: local memory
+#endif
     for (int k = 0; k <= ntr; ++k) acc[k * 128] = 0.0;                      // mflx = c0, mtflx = c0 (:3224-3230)
     // edges of the block that carry a flux (:1820-1826, :1860-1866); every other cell of the flux planes is zero
     const bool edge = north ? (c >= 1 && c <= a.nxb - 2 && r <= a.nyb - 2) : (c <= a.nxb - 2 && r >= 1 && r <= a.nyb - 2);
@@ -365,36 +385,35 @@ __global__ void __launch_bounds__(128) edge_flux_kernel(const __grid_constant__ 
         const double fl = f.dxu[ql] * f.dyu[ql], fr = f.dxu[qr] * f.dyu[qr], fc = 0.5 * (fl + fr);           // areafac
         const double dxl = f.dpx[ql] / f.dxu[ql], dyl = f.dpy[ql] / f.dyu[ql];                               // :1986-1991
         const double dxr = f.dpx[qr] / f.dxu[qr], dyr = f.dpy[qr] / f.dyu[qr];
-        double px[10], py[10];
-        px[CL] = -0.5; py[CL] = 0.0; px[CR] = 0.5; py[CR] = 0.0;
+        pxs[CL * kPS] = -0.5; pys[CL * kPS] = 0.0; pxs[CR * kPS] = 0.5; pys[CR * kPS] = 0.0;
         double xdl, ydl, xdr, ydr;
-        if (north) { xdl = px[CL] + dxl; ydl = py[CL] + dyl; xdr = px[CR] + dxr; ydr = py[CR] + dyr; }
-        else { xdl = px[CL] - dyl; ydl = py[CL] + dxl; xdr = px[CR] - dyr; ydr = py[CR] + dxr; }           // rotated by pi/2
+        if (north) { xdl = pxs[CL * kPS] + dxl; ydl = pys[CL * kPS] + dyl; xdr = pxs[CR * kPS] + dxr; ydr = pys[CR * kPS] + dyr; }
+        else { xdl = pxs[CL * kPS] - dyl; ydl = pys[CL * kPS] + dxl; xdr = pxs[CR * kPS] - dyr; ydr = pys[CR * kPS] + dxr; }           // rotated by pi/2
         const double xdm = 0.5 * (xdr + xdl), ydm = 0.5 * (ydr + ydl);
-        const double yil = (px[CL] * (ydm - ydl) + xdm * ydl - xdl * ydm) / (xdm - xdl);
-        const double yir = (px[CR] * (ydr - ydm) - xdm * ydr + xdr * ydm) / (xdr - xdm);
+        const double yil = (pxs[CL * kPS] * (ydm - ydl) + xdm * ydl - xdl * ydm) / (xdm - xdl);
+        const double yir = (pxs[CR * kPS] * (ydr - ydm) - xdm * ydr + xdr * ydm) / (xdr - xdm);
         const double md = (ydr - ydl) / (xdr - xdl);
         const double xic = fabs(md) > puny ? xdl - ydl / md : 0.0;
-        px[DL] = xdl; py[DL] = ydl; px[DR] = xdr; py[DR] = ydr; px[IL] = px[CL]; py[IL] = yil; px[IR] = px[CR]; py[IR] = yir;
-        px[IC] = xic; py[IC] = 0.0; px[DM] = xdm; py[DM] = ydm;
+        pxs[DL * kPS] = xdl; pys[DL * kPS] = ydl; pxs[DR * kPS] = xdr; pys[DR * kPS] = ydr; pxs[IL * kPS] = pxs[CL * kPS]; pys[IL * kPS] = yil; pxs[IR * kPS] = pxs[CR * kPS]; pys[IR * kPS] = yir;
+        pxs[IC * kPS] = xic; pys[IC * kPS] = 0.0; pxs[DM * kPS] = xdm; pys[DM * kPS] = ydm;
         const Row *rows[3] = {nullptr, nullptr, nullptr};
         int nrows[3] = {0, 0, 0};
         {
             int k = -1;
-            if (yil > 0.0 && xdl < px[CL] && ydl >= 0.0) k = 0;
-            else if (yil < 0.0 && xdl < px[CL] && ydl < 0.0) k = 1;
-            else if (yil < 0.0 && xdl < px[CL] && ydl >= 0.0) k = 2;
-            else if (yil > 0.0 && xdl < px[CL] && ydl < 0.0) k = 3;
+            if (yil > 0.0 && xdl < pxs[CL * kPS] && ydl >= 0.0) k = 0;
+            else if (yil < 0.0 && xdl < pxs[CL * kPS] && ydl < 0.0) k = 1;
+            else if (yil < 0.0 && xdl < pxs[CL * kPS] && ydl >= 0.0) k = 2;
+            else if (yil > 0.0 && xdl < pxs[CL * kPS] && ydl < 0.0) k = 3;
             if (k >= 0) { rows[0] = kLeft[k]; nrows[0] = 2; }
             k = -1;
-            if (yir > 0.0 && xdr >= px[CR] && ydr >= 0.0) k = 0;
-            else if (yir < 0.0 && xdr >= px[CR] && ydr < 0.0) k = 1;
-            else if (yir < 0.0 && xdr >= px[CR] && ydr >= 0.0) k = 2;
-            else if (yir > 0.0 && xdr >= px[CR] && ydr < 0.0) k = 3;
+            if (yir > 0.0 && xdr >= pxs[CR * kPS] && ydr >= 0.0) k = 0;
+            else if (yir < 0.0 && xdr >= pxs[CR * kPS] && ydr < 0.0) k = 1;
+            else if (yir < 0.0 && xdr >= pxs[CR * kPS] && ydr >= 0.0) k = 2;
+            else if (yir > 0.0 && xdr >= pxs[CR * kPS] && ydr < 0.0) k = 3;
             if (k >= 0) { rows[1] = kRight[k]; nrows[1] = 2; }
-            if (xdl < px[CL]) { xdl = px[IL]; ydl = yil; }
-            if (xdr > px[CR]) { xdr = px[IR]; ydr = yir; }
-            px[DL2] = xdl; py[DL2] = ydl; px[DR2] = xdr; py[DR2] = ydr;
+            if (xdl < pxs[CL * kPS]) { xdl = pxs[IL * kPS]; ydl = yil; }
+            if (xdr > pxs[CR * kPS]) { xdr = pxs[IR * kPS]; ydr = yir; }
+            pxs[DL2 * kPS] = xdl; pys[DL2 * kPS] = ydl; pxs[DR2 * kPS] = xdr; pys[DR2 * kPS] = ydr;
             k = -1;
             if (ydl >= 0.0 && ydr >= 0.0 && ydm >= 0.0) k = 0;
             else if (ydl >= 0.0 && ydr >= 0.0 && ydm < 0.0) k = 1;
@@ -425,7 +444,7 @@ __global__ void __launch_bounds__(128) edge_flux_kernel(const __grid_constant__ 
         for (int g = 0; g < 6; ++g) {                                      // groups in ascending order (:3235)
             const Row w = tri[g];
             if (!w.ng) continue;
-            double x1 = px[w.p1], y1 = py[w.p1], x2 = px[w.p2], y2 = py[w.p2], x3 = px[w.p3], y3 = py[w.p3];
+            double x1 = pxs[w.p1 * kPS], y1 = pys[w.p1 * kPS], x2 = pxs[w.p2 * kPS], y2 = pys[w.p2 * kPS], x3 = pxs[w.p3 * kPS], y3 = pys[w.p3 * kPS];
             const double fa = w.fac == PL ? fl : w.fac == ML ? -fl : w.fac == PR ? fr : w.fac == MR ? -fr : w.fac == PC ? fc : -fc;
             const double area = 0.5 * ((x2 - x1) * (y3 - y1) - (y2 - y1) * (x3 - x1)) * fa;                  // :2932-2937
             if (fabs(area) < eps16 * fc) continue;                          // not in the list of this group (:2939-2946)
@@ -566,6 +585,65 @@ __global__ void __launch_bounds__(128) update_fields_kernel(const __grid_constan
             if (sl >= 0) { told[sl] = t; tnew[sl] = tn; }
             u.tm[pl + q] = tn;
         }
+    }
+}
+
+// ---- the caller's conversions: state_to_tracers (source/ice_transport_driver.F90:789-900) and tracers_to_state
+// (:908-1002) of transport_remap ------------------------------------------------------------------------------------------
+struct StateArgs {
+    int nxb, nyb, ld;
+    size_t pe;
+    int ncat, ntrcr, nt_qsno, nslyr;   // nt_qsno 1-based (ice_state)
+    double rhosLf;                     // rhos * Lfresh
+    double *aice0, *aicen, *vicen, *vsnon, *trcrn;     // 1, ncat, ncat, ncat, ncat * ntrcr planes ([n-1][it-1])
+    double *aim, *trm;                 // ncat + 1, ncat * (2 + ntrcr) planes: mm, tm of the reconstruction
+};
+
+// grid: (ceil(nxb / 128), nyb, ncat + 1): every cell of the block, ghost cells included
+__global__ void state_to_tracers_kernel(const __grid_constant__ StateArgs s)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y, n = blockIdx.z;
+    if (c >= s.nxb) return;
+    const size_t q = (size_t)r * s.ld + c;
+    if (n == 0) { s.aim[q] = s.aice0[q]; return; }
+    const int ntrace = 2 + s.ntrcr;
+    const double am = s.aicen[(size_t)(n - 1) * s.pe + q];
+    s.aim[(size_t)n * s.pe + q] = am;
+    double *tr = s.trm + (size_t)(n - 1) * ntrace * s.pe + q;
+    const double *tn = s.trcrn + (size_t)(n - 1) * s.ntrcr * s.pe + q;
+    if (am > 1.0e-11) {
+        const double w1 = 1.0 / am;
+        tr[0] = s.vicen[(size_t)(n - 1) * s.pe + q] * w1;                  // hice
+        tr[s.pe] = s.vsnon[(size_t)(n - 1) * s.pe + q] * w1;               // hsno
+        for (int it = 1; it <= s.ntrcr; ++it) {
+            const bool snow = it >= s.nt_qsno && it < s.nt_qsno + s.nslyr; // snow enthalpy, shifted (:880-886)
+            const double v = tn[(size_t)(it - 1) * s.pe];
+            tr[(size_t)(1 + it) * s.pe] = snow ? v + s.rhosLf : v;
+        }
+    } else {
+        for (int k = 0; k < ntrace; ++k) tr[(size_t)k * s.pe] = 0.0;
+    }
+}
+
+// cells whose new area is not positive keep their old state (:963-975)
+__global__ void tracers_to_state_kernel(const __grid_constant__ StateArgs s)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y, n = blockIdx.z;
+    if (c >= s.nxb) return;
+    const size_t q = (size_t)r * s.ld + c;
+    if (n == 0) { s.aice0[q] = s.aim[q]; return; }
+    const int ntrace = 2 + s.ntrcr;
+    const double am = s.aim[(size_t)n * s.pe + q];
+    if (!(am > 0.0)) return;
+    const double *tr = s.trm + (size_t)(n - 1) * ntrace * s.pe + q;
+    double *tn = s.trcrn + (size_t)(n - 1) * s.ntrcr * s.pe + q;
+    s.aicen[(size_t)(n - 1) * s.pe + q] = am;
+    s.vicen[(size_t)(n - 1) * s.pe + q] = am * tr[0];
+    s.vsnon[(size_t)(n - 1) * s.pe + q] = am * tr[s.pe];
+    for (int it = 1; it <= s.ntrcr; ++it) {
+        const bool snow = it >= s.nt_qsno && it < s.nt_qsno + s.nslyr;
+        const double v = tr[(size_t)(1 + it) * s.pe];
+        tn[(size_t)(it - 1) * s.pe] = snow ? v - s.rhosLf : v;
     }
 }
 

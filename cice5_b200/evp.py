@@ -81,7 +81,9 @@ EXPORTS = ("evp_gpu_init", "evp_gpu_set_grid", "evp_gpu_run", "evp_gpu_upload", 
            "evp_gpu_set_transport_tracers", "evp_gpu_construct_fields_upload", "evp_gpu_construct_fields_compute",
            "evp_gpu_construct_fields_group", "evp_gpu_construct_fields_fetch", "evp_gpu_construct_fields",
            "evp_gpu_get_transport_timing", "evp_gpu_horizontal_remap_compute", "evp_gpu_horizontal_remap_group",
-           "evp_gpu_horizontal_remap_fetch", "evp_gpu_horizontal_remap")
+           "evp_gpu_horizontal_remap_fetch", "evp_gpu_horizontal_remap", "evp_gpu_transport_remap_upload",
+           "evp_gpu_transport_remap_compute", "evp_gpu_transport_remap_group", "evp_gpu_transport_remap_fetch",
+           "evp_gpu_transport_remap")
 REMAP_MAX_TRACE, REMAP_MAX_PARENTS = 128, 16     # EVP_REMAP_MAX_TRACE, EVP_REMAP_MAX_PARENTS of include/evp_b200.h
 STATIC_MAX_CELLS = 131072       # EVP_STATIC_MAX_CELLS of include/evp_b200.h
 
@@ -353,6 +355,37 @@ class EvpGpu:
         self.horizontal_remap_compute(dt)
         return self.horizontal_remap_fetch()
 
+    # ---- transport_remap: from and to the ice state (aice0, aicen, trcrn, vicen, vsnon) ----
+    def transport_remap_upload(self, st):
+        ncat, nt = self._rc_shape
+        a = {k: np.ascontiguousarray(st[k], dtype=np.float64) for k in ("aice0", "aicen", "trcrn", "vicen", "vsnon")}
+        if a["aice0"].shape != self.shape or a["aicen"].shape != (ncat,) + self.shape or \
+                a["trcrn"].shape != (ncat, nt - 2) + self.shape:
+            raise ValueError("state arrays do not match ncat, ntrace - 2 and the block")
+        self._check(self.lib.evp_gpu_transport_remap_upload(self._h, _dp(a["aice0"]), _dp(a["aicen"]),
+                                                            _dp(a["trcrn"]) if nt > 2 else None, _dp(a["vicen"]), _dp(a["vsnon"])))
+
+    def transport_remap_compute(self, dt, nt_qsno, nslyr, rhos, Lfresh):
+        self._check(self.lib.evp_gpu_transport_remap_compute(self._h, C.c_double(dt), C.c_int(int(nt_qsno)), C.c_int(int(nslyr)),
+                                                             C.c_double(rhos), C.c_double(Lfresh)))
+
+    def transport_remap_fetch(self):
+        ncat, nt = self._rc_shape
+        o = {"aice0": np.zeros(self.shape), "aicen": np.zeros((ncat,) + self.shape), "trcrn": np.zeros((ncat, nt - 2) + self.shape),
+             "vicen": np.zeros((ncat,) + self.shape), "vsnon": np.zeros((ncat,) + self.shape)}
+        st, sc, i_s, j_s = C.c_int(0), C.c_int(0), C.c_int(0), C.c_int(0)
+        self._check(self.lib.evp_gpu_transport_remap_fetch(self._h, _dp(o["aice0"]), _dp(o["aicen"]),
+                                                           _dp(o["trcrn"]) if nt > 2 else None, _dp(o["vicen"]), _dp(o["vsnon"]),
+                                                           C.byref(st), C.byref(sc), C.byref(i_s), C.byref(j_s)))
+        return o, (st.value, sc.value, i_s.value, j_s.value)
+
+    def transport_remap(self, dt, st, nt_qsno, nslyr, rhos, Lfresh):
+        """transport_remap (source/ice_transport_driver.F90:198-627) of this block from the resident velocities.  st: dict
+        aice0, aicen, trcrn, vicen, vsnon.  Returns (new state dict, (stop, category, istop, jstop))."""
+        self.transport_remap_upload(st)
+        self.transport_remap_compute(dt, nt_qsno, nslyr, rhos, Lfresh)
+        return self.transport_remap_fetch()
+
     def construct_fields_compute(self):
         self._check(self.lib.evp_gpu_construct_fields_compute(self._h))
 
@@ -536,6 +569,17 @@ class EvpGroup:
         for r, e in enumerate(self.ranks):
             e.set_transport_tracers(ncat, tracer_type, depend, has_dependents,
                                     self._slabs({k: f[k] for k in ("hm", "xav", "yav", "xxav", "yyav")}, r))
+
+    def transport_remap(self, dt, st, nt_qsno, nslyr, rhos, Lfresh):
+        """All ranks; returns the global new state dict and the per-rank (stop, category, istop, jstop)."""
+        for r, e in enumerate(self.ranks):
+            e.transport_remap_upload({k: self._fx.slab(np.ascontiguousarray(v), r, self.n, self.starts) for k, v in st.items()})
+        arr = (C.c_void_p * self.n)(*[e._h for e in self.ranks])
+        self.ranks[0]._check(self.ranks[0].lib.evp_gpu_transport_remap_group(arr, self.n, C.c_double(dt), C.c_int(int(nt_qsno)),
+                                                                             C.c_int(int(nslyr)), C.c_double(rhos),
+                                                                             C.c_double(Lfresh)))
+        parts = [e.transport_remap_fetch() for e in self.ranks]
+        return {k: self._fx.unslab([p[0][k] for p in parts]) for k in parts[0][0]}, [p[1] for p in parts]
 
     def horizontal_remap(self, dt, mm, tm):
         """All ranks; returns the global new mm, tm and the per-rank (stop, category, istop, jstop)."""

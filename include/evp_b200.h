@@ -245,6 +245,27 @@ int evp_gpu_horizontal_remap_group(evp_handle_t **handles, int n, double dt);
 int evp_gpu_horizontal_remap_fetch(evp_handle_t *h, double *mm, double *tm, int *stop, int *stop_cat, int *istop, int *jstop);
 int evp_gpu_horizontal_remap(evp_handle_t *h, double dt, double *mm, double *tm, int *stop, int *stop_cat, int *istop,
                              int *jstop);
+/* The caller of horizontal_remap, transport_remap (source/ice_transport_driver.F90:198-627) with its compile-time settings
+ * l_conservation_check = l_monotonicity_check = .false. (:249-251): state_to_tracers (:789-900), horizontal_remap,
+ * tracers_to_state (:908-1002) and bound_state (source/ice_state.F90:173-238, maskhalo_bound = .false.) -- what
+ * step_dynamics calls after evp (source/ice_step_mod.F90:1126-1130).  The tracer table given to set_transport_tracers
+ * starts with hice, hsno (ntrace = 2 + ntrcr, init_transport :90-110).
+ *   upload:  aice0 (nx_block, ny_block), aicen / vicen / vsnon (nx_block, ny_block, ncat), trcrn (nx_block, ny_block,
+ *            ntrcr, ncat) of this block, ghost cells filled.
+ *   compute / group: nt_qsno (1-based), nslyr, rhos, Lfresh: ice_state's / ice_constants' values (snow enthalpy is
+ *            transported as trcrn + rhos * Lfresh, :880-886).  Every rank of the run calls it.
+ *   fetch:   the transported state, ghost cells updated by bound_state; cells whose new area is not positive keep their
+ *            old aicen, vicen, vsnon, trcrn as in the reference (:963-975).  stop etc. as evp_gpu_horizontal_remap_fetch.
+ *   evp_gpu_transport_remap = upload + compute + fetch, in place. */
+int evp_gpu_transport_remap_upload(evp_handle_t *h, const double *aice0, const double *aicen, const double *trcrn,
+                                   const double *vicen, const double *vsnon);
+int evp_gpu_transport_remap_compute(evp_handle_t *h, double dt, int nt_qsno, int nslyr, double rhos, double Lfresh);
+int evp_gpu_transport_remap_group(evp_handle_t **handles, int n, double dt, int nt_qsno, int nslyr, double rhos, double Lfresh);
+int evp_gpu_transport_remap_fetch(evp_handle_t *h, double *aice0, double *aicen, double *trcrn, double *vicen, double *vsnon,
+                                  int *stop, int *stop_cat, int *istop, int *jstop);
+int evp_gpu_transport_remap(evp_handle_t *h, double dt, int nt_qsno, int nslyr, double rhos, double Lfresh, double *aice0,
+                            double *aicen, double *trcrn, double *vicen, double *vsnon, int *stop, int *stop_cat, int *istop,
+                            int *jstop);
 /* Device time (CUDA events, ms) of the last call of each transport stage on this handle: ms[0] departure_points kernels,
  * ms[1] their two ghost updates, ms[2] the reconstruction kernel, ms[3] its ghost updates, ms[4] the edge fluxes and
  * update_fields of the last horizontal_remap, ms[5] that whole horizontal_remap.  What the reference's timer_advect /

@@ -305,6 +305,54 @@ def horizontal_remap(dom, dt, tracer_type, depend, has_dependents, g, uvel, vvel
     return st.value, sc.value, i_s.value, j_s.value
 
 
+def state_to_tracers(st, nt_qsno, nslyr, rhos, Lfresh):
+    """state_to_tracers (source/ice_transport_driver.F90:789-900) of one block.  st: dict aice0 (ny, nx), aicen / vicen /
+    vsnon (ncat, ny, nx), trcrn (ncat, ntrcr, ny, nx).  Returns aim (ncat+1, ny, nx), trm (ncat, 2+ntrcr, ny, nx)."""
+    a = {k: np.ascontiguousarray(st[k], dtype=np.float64) for k in ("aice0", "aicen", "trcrn", "vicen", "vsnon")}
+    ncat, ntrcr = a["trcrn"].shape[0], a["trcrn"].shape[1]
+    nyb, nxb = a["aice0"].shape
+    aim, trm = np.full((ncat + 1, nyb, nxb), np.nan), np.full((ncat, 2 + ntrcr, nyb, nxb), np.nan)
+    rc = lib().remap_oracle_state_to_tracers(C.c_int(nxb), C.c_int(nyb), C.c_int(ncat), C.c_int(ntrcr), C.c_int(nt_qsno),
+                                             C.c_int(nslyr), C.c_double(rhos), C.c_double(Lfresh), _dp(a["aice0"]), _dp(a["aicen"]),
+                                             _dp(a["trcrn"]), _dp(a["vicen"]), _dp(a["vsnon"]), _dp(aim), _dp(trm))
+    assert rc == 0
+    return aim, trm
+
+
+def tracers_to_state(aim, trm, st, nt_qsno, nslyr, rhos, Lfresh):
+    """tracers_to_state (:908-1002): the state dict `st` (as for state_to_tracers, C-contiguous float64) is updated in place."""
+    ncat, ntrcr = st["trcrn"].shape[0], st["trcrn"].shape[1]
+    nyb, nxb = st["aice0"].shape
+    rc = lib().remap_oracle_tracers_to_state(C.c_int(nxb), C.c_int(nyb), C.c_int(ncat), C.c_int(ntrcr), C.c_int(nt_qsno),
+                                             C.c_int(nslyr), C.c_double(rhos), C.c_double(Lfresh), _dp(aim), _dp(trm),
+                                             _dp(st["aice0"]), _dp(st["aicen"]), _dp(st["trcrn"]), _dp(st["vicen"]), _dp(st["vsnon"]))
+    assert rc == 0
+    return st
+
+
+def transport_remap(dom, dt, tracer_type, depend, has_dependents, g, uvel, vvel, st, nt_qsno, nslyr, rhos, Lfresh,
+                    no_halo=False, nslabs=1):
+    """transport_remap (source/ice_transport_driver.F90:198-627, checks off) on global-with-ghost planes: the state dict `st`
+    (aice0, aicen, trcrn, vicen, vsnon; C-contiguous float64) is updated in place, ghost cells by bound_state.  Returns
+    (stop, category, istop, jstop) as :func:`horizontal_remap`."""
+    cfg = make_cfg(dom, 1, 1.0, nslabs)
+    ncat, ntrcr = st["trcrn"].shape[0], st["trcrn"].shape[1]
+    ia = lambda v: np.ascontiguousarray(v, dtype=np.int32)
+    tt, dp, hd = ia(tracer_type), ia(depend), ia(has_dependents)
+    assert tt.size == 2 + ntrcr
+    sv, sc, i_s, j_s = C.c_int(0), C.c_int(0), C.c_int(0), C.c_int(0)
+    rc = lib().remap_oracle_transport_remap(
+        C.byref(cfg), C.c_double(dt), C.c_int(ncat), C.c_int(ntrcr), C.c_int(nt_qsno), C.c_int(nslyr), C.c_double(rhos),
+        C.c_double(Lfresh), _ip(tt), _ip(dp), _ip(hd), C.c_int(int(no_halo)),
+        *[_dp(np.ascontiguousarray(g[k], dtype=np.float64)) for k in ("hm", "xav", "yav", "xxav", "yyav", "dxu", "dyu", "HTN",
+                                                                      "HTE", "tarear")],
+        _dp(uvel), _dp(vvel), _dp(st["aice0"]), _dp(st["aicen"]), _dp(st["trcrn"]), _dp(st["vicen"]), _dp(st["vsnon"]),
+        C.byref(sv), C.byref(sc), C.byref(i_s), C.byref(j_s))
+    if rc != 0:
+        raise RuntimeError(f"remap_oracle_transport_remap failed with status {rc}")
+    return sv.value, sc.value, i_s.value, j_s.value
+
+
 def departure_points(dom, dt, uvel, vvel, dxu, dyu, HTN, HTE, l_dp_midpt=True, no_halo=False, nslabs=1):
     """departure_points (source/ice_transport_remap.F90:1493-1670) + the ghost update of dpx, dpy that
     horizontal_remap issues (:574-578), on global-with-ghost planes.  Returns (dpx, dpy, l_stop, istop, jstop)."""

@@ -765,3 +765,118 @@ done:
     free(mc); free(tc); free(dp); free(mflx); free(mtflx); free(xp); free(tri); free(ifl);
     return 0;
 }
+
+/* ---- the caller: transport_remap (source/ice_transport_driver.F90:198-627) with its compile-time settings
+ * l_conservation_check = l_monotonicity_check = .false. (:249-251): state_to_tracers (:789-900), horizontal_remap,
+ * tracers_to_state (:908-1002), bound_state (source/ice_state.F90:173-238, maskhalo_bound = .false.) ------------------ */
+/* arrays: aicen, vicen, vsnon [ncat][nyb][nxb]; trcrn [ncat][ntrcr][nyb][nxb]; aim [ncat+1]...; trm [ncat][ntrace]... */
+static void state_to_tracers(const blk *b, int ncat, int ntrcr, int nt_qsno, int nslyr, double rhos, double Lfresh,
+                             const double *aice0, const double *aicen, const double *trcrn, const double *vicen,
+                             const double *vsnon, double *aim, double *trm)
+{
+    const size_t pe = (size_t)b->nxb * b->nyb;
+    const int ntrace = 2 + ntrcr;
+    int *xi = malloc(pe * sizeof(int)), *xj = malloc(pe * sizeof(int));
+    for (size_t q = 0; q < pe; ++q) aim[q] = aice0[q];
+    for (int n = 1; n <= ncat; ++n) {
+        double *am = aim + (size_t)n * pe, *tr = trm + (size_t)(n - 1) * ntrace * pe;
+        const double *an = aicen + (size_t)(n - 1) * pe, *vi = vicen + (size_t)(n - 1) * pe, *vs = vsnon + (size_t)(n - 1) * pe;
+        const double *tn = trcrn + (size_t)(n - 1) * ntrcr * pe;
+        int icells = 0;
+        for (size_t q = 0; q < (size_t)ntrace * pe; ++q) tr[q] = c0;
+        for (int j = 1; j <= b->nyb; ++j)
+            for (int i = 1; i <= b->nxb; ++i) {
+                B2(am, i, j) = B2(an, i, j);
+                if (B2(am, i, j) > puny) { xi[icells] = i; xj[icells] = j; ++icells; }
+            }
+        for (int ij = 0; ij < icells; ++ij) {
+            const int i = xi[ij], j = xj[ij];
+            const double w1 = c1 / B2(am, i, j);
+            T3(tr, i, j, 1) = B2(vi, i, j) * w1;                           /* hice */
+            T3(tr, i, j, 2) = B2(vs, i, j) * w1;                           /* hsno */
+        }
+        for (int it = 1; it <= ntrcr; ++it) {
+            const int snow = it >= nt_qsno && it < nt_qsno + nslyr;        /* snow enthalpy, shifted to be positive */
+            for (int ij = 0; ij < icells; ++ij) {
+                const int i = xi[ij], j = xj[ij];
+                T3(tr, i, j, 2 + it) = snow ? T3(tn, i, j, it) + rhos * Lfresh : T3(tn, i, j, it);
+            }
+        }
+    }
+    free(xi); free(xj);
+}
+
+static void tracers_to_state(const blk *b, int ncat, int ntrcr, int nt_qsno, int nslyr, double rhos, double Lfresh,
+                             const double *aim, const double *trm, double *aice0, double *aicen, double *trcrn,
+                             double *vicen, double *vsnon)
+{
+    const size_t pe = (size_t)b->nxb * b->nyb;
+    const int ntrace = 2 + ntrcr;
+    for (size_t q = 0; q < pe; ++q) aice0[q] = aim[q];
+    for (int n = 1; n <= ncat; ++n) {
+        const double *am = aim + (size_t)n * pe, *tr = trm + (size_t)(n - 1) * ntrace * pe;
+        double *an = aicen + (size_t)(n - 1) * pe, *vi = vicen + (size_t)(n - 1) * pe, *vs = vsnon + (size_t)(n - 1) * pe;
+        double *tn = trcrn + (size_t)(n - 1) * ntrcr * pe;
+        for (int j = 1; j <= b->nyb; ++j)                                  /* cells with aim > 0 only: the others keep */
+            for (int i = 1; i <= b->nxb; ++i) {                            /* their old state (:963-975)               */
+                if (!(B2(am, i, j) > c0)) continue;
+                B2(an, i, j) = B2(am, i, j);
+                B2(vi, i, j) = B2(am, i, j) * T3(tr, i, j, 1);
+                B2(vs, i, j) = B2(am, i, j) * T3(tr, i, j, 2);
+                for (int it = 1; it <= ntrcr; ++it) {
+                    const int snow = it >= nt_qsno && it < nt_qsno + nslyr;
+                    T3(tn, i, j, it) = snow ? T3(tr, i, j, 2 + it) - rhos * Lfresh : T3(tr, i, j, 2 + it);
+                }
+            }
+    }
+}
+
+int remap_oracle_state_to_tracers(int nxb, int nyb, int ncat, int ntrcr, int nt_qsno, int nslyr, double rhos, double Lfresh,
+                                  const double *aice0, const double *aicen, const double *trcrn, const double *vicen,
+                                  const double *vsnon, double *aim, double *trm)
+{
+    blk bb = {nxb, nyb, 2, nxb - 1, 2, nyb - 1};
+    state_to_tracers(&bb, ncat, ntrcr, nt_qsno, nslyr, rhos, Lfresh, aice0, aicen, trcrn, vicen, vsnon, aim, trm);
+    return 0;
+}
+
+int remap_oracle_tracers_to_state(int nxb, int nyb, int ncat, int ntrcr, int nt_qsno, int nslyr, double rhos, double Lfresh,
+                                  const double *aim, const double *trm, double *aice0, double *aicen, double *trcrn,
+                                  double *vicen, double *vsnon)
+{
+    blk bb = {nxb, nyb, 2, nxb - 1, 2, nyb - 1};
+    tracers_to_state(&bb, ncat, ntrcr, nt_qsno, nslyr, rhos, Lfresh, aim, trm, aice0, aicen, trcrn, vicen, vsnon);
+    return 0;
+}
+
+/* transport_remap on one global-with-ghost block; the state arrays are updated in place, ghost cells by bound_state
+ * (unless no_halo).  stop etc. as remap_oracle_horizontal_remap (the reference aborts; the state is then left as read) */
+int remap_oracle_transport_remap(const evp_oracle_cfg *cfg, double dt, int ncat, int ntrcr, int nt_qsno, int nslyr,
+                                 double rhos, double Lfresh, const int *tracer_type, const int *depend,
+                                 const int *has_dependents, int no_halo, const double *hm, const double *xav,
+                                 const double *yav, const double *xxav, const double *yyav, const double *dxu,
+                                 const double *dyu, const double *HTN, const double *HTE, const double *tarear,
+                                 const double *uvel, const double *vvel, double *aice0, double *aicen, double *trcrn,
+                                 double *vicen, double *vsnon, int *stop, int *stop_cat, int *istop, int *jstop)
+{
+    blk bb = {cfg->nx_global + 2, cfg->ny_global + 2, 2, cfg->nx_global + 1, 2, cfg->ny_global + 1};
+    const size_t pe = (size_t)bb.nxb * bb.nyb;
+    const int ntrace = 2 + ntrcr;
+    double *aim = malloc((size_t)(ncat + 1) * pe * sizeof(double)), *trm = malloc((size_t)ncat * ntrace * pe * sizeof(double));
+    if (!aim || !trm) return 2;
+    state_to_tracers(&bb, ncat, ntrcr, nt_qsno, nslyr, rhos, Lfresh, aice0, aicen, trcrn, vicen, vsnon, aim, trm);
+    int rc = remap_oracle_horizontal_remap(cfg, dt, ncat, ntrace, tracer_type, depend, has_dependents, no_halo, hm, xav, yav,
+                                           xxav, yyav, dxu, dyu, HTN, HTE, tarear, uvel, vvel, aim, trm, stop, stop_cat, istop,
+                                           jstop);
+    if (rc == 0 && *stop == 0) {
+        tracers_to_state(&bb, ncat, ntrcr, nt_qsno, nslyr, rhos, Lfresh, aim, trm, aice0, aicen, trcrn, vicen, vsnon);
+        if (!no_halo) {                                                    /* bound_state */
+            for (int n = 0; n < ncat && !rc; ++n) rc = evp_oracle_halo_r8(cfg, aicen + (size_t)n * pe, 0, 0, 0.0);
+            for (int k = 0; k < ncat * ntrcr && !rc; ++k) rc = evp_oracle_halo_r8(cfg, trcrn + (size_t)k * pe, 0, 0, 0.0);
+            for (int n = 0; n < ncat && !rc; ++n) rc = evp_oracle_halo_r8(cfg, vicen + (size_t)n * pe, 0, 0, 0.0);
+            for (int n = 0; n < ncat && !rc; ++n) rc = evp_oracle_halo_r8(cfg, vsnon + (size_t)n * pe, 0, 0, 0.0);
+        }
+    }
+    free(aim); free(trm);
+    return rc;
+}

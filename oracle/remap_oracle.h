@@ -55,6 +55,24 @@ int remap_oracle_horizontal_remap(const evp_oracle_cfg *cfg, double dt, int ncat
                                   const double *tarear, const double *uvel, const double *vvel, double *mm, double *tm,
                                   int *stop, int *stop_cat, int *istop, int *jstop);
 
+/* The caller, transport_remap (source/ice_transport_driver.F90:198-627) with l_conservation_check = l_monotonicity_check
+ * = .false.: state_to_tracers (:789-900), horizontal_remap, tracers_to_state (:908-1002), bound_state
+ * (source/ice_state.F90:173-238).  aicen, vicen, vsnon: ncat planes; trcrn: planes [n-1][it-1] = the reference's
+ * (nx_block, ny_block, ntrcr, ncat); ntrace = 2 + ntrcr; nt_qsno 1-based; tracer tables as for construct_fields. */
+int remap_oracle_state_to_tracers(int nxb, int nyb, int ncat, int ntrcr, int nt_qsno, int nslyr, double rhos, double Lfresh,
+                                  const double *aice0, const double *aicen, const double *trcrn, const double *vicen,
+                                  const double *vsnon, double *aim, double *trm);
+int remap_oracle_tracers_to_state(int nxb, int nyb, int ncat, int ntrcr, int nt_qsno, int nslyr, double rhos, double Lfresh,
+                                  const double *aim, const double *trm, double *aice0, double *aicen, double *trcrn,
+                                  double *vicen, double *vsnon);
+int remap_oracle_transport_remap(const evp_oracle_cfg *cfg, double dt, int ncat, int ntrcr, int nt_qsno, int nslyr,
+                                 double rhos, double Lfresh, const int *tracer_type, const int *depend,
+                                 const int *has_dependents, int no_halo, const double *hm, const double *xav,
+                                 const double *yav, const double *xxav, const double *yyav, const double *dxu,
+                                 const double *dyu, const double *HTN, const double *HTE, const double *tarear,
+                                 const double *uvel, const double *vvel, double *aice0, double *aicen, double *trcrn,
+                                 double *vicen, double *vsnon, int *stop, int *stop_cat, int *istop, int *jstop);
+
 #ifdef __cplusplus
 }
 #endif

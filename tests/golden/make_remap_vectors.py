@@ -245,6 +245,53 @@ def run_pipeline(m, d, vel, dt, tarear):
     return out
 
 
+# ---- the caller's conversions: state_to_tracers / tracers_to_state (source/ice_transport_driver.F90:789-1002) ---------
+NTRCR, NT_QSNO, NSLYR = 7, 6, 1          # Tsfc, 4 x qice, qsno, one more; nt_qsno 1-based
+
+
+def load_driver():
+    def lines(rel):
+        return fe.preprocess(open(os.path.join(REF, rel)).read(), ())
+    ns = {}
+    fe.parse_parameters(lines("drivers/cice/ice_constants.F90"), ns)
+    ns.update(nu_diag=6, my_task=0, ncat=NCAT, nslyr=NSLYR, nt_qsno=NT_QSNO)
+    m = fe.Module(ns)
+    m.load(lines("source/ice_transport_driver.F90"), ["state_to_tracers", "tracers_to_state"])
+    return m, ns
+
+
+def state_block(seed):
+    r = np.random.default_rng(seed)
+    sh = (NYB, NXB)
+    aicen = r.uniform(0.02, 0.4, (NCAT,) + sh)
+    aicen[r.uniform(0, 1, aicen.shape) < 0.3] = 0.0
+    aicen[r.uniform(0, 1, aicen.shape) < 0.05] = 4.0e-12
+    st = {"aice0": 1.0 - aicen.sum(axis=0), "aicen": aicen, "vicen": aicen * r.uniform(0.2, 3.0, aicen.shape),
+          "vsnon": aicen * r.uniform(0.0, 0.4, aicen.shape), "trcrn": r.uniform(-3.0e8, 1.0, (NCAT, NTRCR) + sh)}
+    return st
+
+
+def run_state(m, st):
+    F = fe.FArr.from_numpy
+    nt = 2 + NTRCR
+    aim = F(np.full((NCAT + 1, NYB, NXB), -7.0), los=[1, 1, 0])
+    trm = F(np.full((NCAT, nt, NYB, NXB), -7.0))
+    geo = dict(nx_block=NXB, ny_block=NYB, ntrcr=NTRCR, ntrace=nt)
+    m.call("state_to_tracers", aice0=F(st["aice0"]), aicen=F(st["aicen"]), trcrn=F(st["trcrn"]), vicen=F(st["vicen"]),
+           vsnon=F(st["vsnon"]), aim=aim, trm=trm, **geo)
+    out = {"aim": aim.to_numpy(), "trm": trm.to_numpy()}
+    # back, from a perturbed aim / trm (some areas gone to zero: those cells keep their old state)
+    r = np.random.default_rng(99)
+    aim2 = out["aim"] * r.uniform(0.5, 1.5, out["aim"].shape)
+    aim2[r.uniform(0, 1, aim2.shape) < 0.2] = 0.0
+    trm2 = out["trm"] * r.uniform(0.9, 1.1, out["trm"].shape)
+    back = {k: F(st[k]) for k in ("aice0", "aicen", "trcrn", "vicen", "vsnon")}
+    m.call("tracers_to_state", aim=F(aim2, los=[1, 1, 0]), trm=F(trm2), **back, **geo)
+    out.update(aim2=aim2, trm2=trm2)
+    out.update({f"back_{k}": v.to_numpy() for k, v in back.items()})
+    return out
+
+
 def main():
     m = load()
     out = {"nxb": NXB, "nyb": NYB}
@@ -299,6 +346,15 @@ def main():
             out[f"{name}/out/{k}"] = v
         print(name, "stops", res["stops"].tolist(), "max |dmm|", float(np.abs(res["mm_new"] - d["mm"]).max()),
               "cells per group east", res["east/icells"], "north", res["north/icells"])
+    md, cns = load_driver()
+    out.update(ntrcr=NTRCR, nt_qsno=NT_QSNO, nslyr=NSLYR, rhos=cns["rhos"], Lfresh=cns["lfresh"])
+    st = state_block(51)
+    res = run_state(md, st)
+    for k, v in st.items():
+        out[f"state/{k}"] = v
+    for k, v in res.items():
+        out[f"state/out/{k}"] = v
+    print("state", "cells with ice", int((res["aim"][1:] > 1e-11).sum()), "rhos*Lfresh", cns["rhos"] * cns["lfresh"])
     np.savez_compressed(OUT, **out)
     print("wrote", OUT)
 

@@ -716,3 +716,66 @@ def test_horizontal_remap_gx3_and_stops(dev):
     # negative new areas: open water first, then (open water made thick enough) an ice category
     mm, tm, stops, rmm, rtm, rstop, d = _remap_case(dev, grid, "full", 1, 20.0, "random", tarear_scale=40.0)
     assert rstop[0] in (2, 3) and rstop[2] > 1 and stops == [rstop]
+
+
+# ---- transport_remap: the caller of horizontal_remap, from and to the ice state --------------------------------------
+RHOS, LFRESH = 330.0, 2.835e6 - 2.501e6          # ice_constants.F90: rhos, Lfresh = Lsub - Lvap
+
+
+def _transport_state(grid, case, seed):
+    """aice0, aicen, vicen, vsnon, trcrn consistent with fx.transport_tracers (tracers 3.. of the table are trcrn; the
+    snow enthalpy tracer qsno1 = trcrn 6 is stored as the model stores it, without the rhos * Lfresh shift)."""
+    d = fx.transport_tracers(grid, case.inp, seed, "cice")
+    mm, tm = d["mm"], d["tm"]
+    st = {"aice0": mm[0].copy(), "aicen": mm[1:].copy(), "vicen": mm[1:] * tm[:, 0], "vsnon": mm[1:] * tm[:, 1],
+          "trcrn": np.ascontiguousarray(tm[:, 2:])}
+    return d, st
+
+
+def _transport_case(dev, grid, scenario, nranks, dt_scale, seed=9):
+    case = fx.make_case(grid, scenario, ndte=6, dt=3600.0)
+    got = clone_case(case)
+    d, st = _transport_state(grid, case, seed)
+    ncat = st["aicen"].shape[0]
+    f = grid.f
+    dt = case.dt * dt_scale
+    par = (6, 1, RHOS, LFRESH)                                            # nt_qsno, nslyr, rhos, Lfresh
+    if nranks == 1:
+        e = dev.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True)
+        try:
+            e.set_grid(f)
+            e.set_transport_grid(f)
+            e.set_transport_tracers(ncat, d["tracer_type"], d["depend"], d["has_dependents"], d)
+            e.evp(case.dt, got.inp, got.io, got.out)
+            new, stop = e.transport_remap(dt, st, *par)
+            stops = [stop]
+        finally:
+            e.close()
+    else:
+        g = dev.EvpGroup(case.dom, case.ndte, case.dt, nranks, strict=True)
+        try:
+            g.set_grid(f)
+            g.set_transport_grid(f)
+            g.set_transport_tracers(ncat, d["tracer_type"], d["depend"], d["has_dependents"], d)
+            g.evp(case.dt, got.inp, got.io, got.out)
+            new, stops = g.transport_remap(dt, st, *par)
+        finally:
+            g.close()
+    geo = dict(d)
+    geo.update({k: f[k] for k in ("dxu", "dyu", "HTN", "HTE", "tarear")})
+    ref = {k: v.copy() for k, v in st.items()}
+    rstop = orc.transport_remap(case.dom, dt, d["tracer_type"], d["depend"], d["has_dependents"], geo, got.io["uvel"],
+                                got.io["vvel"], ref, *par)
+    return new, stops, ref, rstop, st
+
+
+@pytest.mark.parametrize("nranks", [1, 2, 4])
+def test_transport_remap_bitwise(dev, nranks):
+    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
+    new, stops, ref, rstop, st = _transport_case(dev, grid, "caps", nranks, 100.0)
+    assert rstop == (0, 0, 0, 0) and all(s == rstop for s in stops)
+    for k in ("aice0", "aicen", "vicen", "vsnon", "trcrn"):
+        assert np.array_equal(new[k], ref[k]), k                          # ghost cells too (bound_state), except aice0's
+        assert np.array_equal(np.signbit(new[k]), np.signbit(ref[k])), k
+    assert np.abs(ref["aicen"] - st["aicen"])[:, 1:-1, 1:-1].max() > 1e-3 and np.abs(ref["vicen"] - st["vicen"]).max() > 1e-3
+    assert ref["aicen"][:, -1, 1:-1].any()                                # the fold filled the north ghost row

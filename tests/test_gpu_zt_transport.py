@@ -68,3 +68,10 @@ def test_horizontal_remap_one_degree_tripole_on_device():
     assert rstop == (0, 0, 0, 0) and stops == [rstop]
     assert np.array_equal(mm, rmm) and np.array_equal(tm, rtm) and np.array_equal(np.signbit(tm), np.signbit(rtm))
     assert np.abs(rmm - d["mm"]).max() > 1e-4
+
+
+@pytest.mark.parametrize("nranks", [1, 2, 4])
+def test_transport_remap_bitwise_on_device(nranks):
+    """transport_remap (source/ice_transport_driver.F90:198-627): state_to_tracers, horizontal_remap, tracers_to_state,
+    bound_state, from and to aice0 / aicen / vicen / vsnon / trcrn."""
+    shared.test_transport_remap_bitwise(evp, nranks)

@@ -498,3 +498,21 @@ def test_horizontal_remap_oracle_reproduces_reference_text_bitwise(name):
     assert stop == (0, 0, 0, 0)
     assert np.array_equal(mm, get("out/mm_new")) and np.array_equal(tm, get("out/tm_new"))
     assert np.array_equal(np.signbit(tm), np.signbit(get("out/tm_new")))
+
+
+def test_state_conversions_oracle_reproduce_reference_text_bitwise():
+    """state_to_tracers and tracers_to_state (source/ice_transport_driver.F90:789-1002) of the oracle against the
+    reference text: areas below puny carry no tracers, snow enthalpy is shifted by rhos * Lfresh and back, cells whose new
+    area is zero keep their old state."""
+    z = _remap_vectors()
+    st = {k: np.ascontiguousarray(z[f"state/{k}"]) for k in ("aice0", "aicen", "trcrn", "vicen", "vsnon")}
+    par = (int(z["nt_qsno"]), int(z["nslyr"]), float(z["rhos"]), float(z["Lfresh"]))
+    aim, trm = orc.state_to_tracers(st, *par)
+    assert np.array_equal(aim, z["state/out/aim"]) and np.array_equal(trm, z["state/out/trm"])
+    assert np.array_equal(np.signbit(trm), np.signbit(z["state/out/trm"]))
+    back = {k: v.copy() for k, v in st.items()}
+    orc.tracers_to_state(np.ascontiguousarray(z["state/out/aim2"]), np.ascontiguousarray(z["state/out/trm2"]), back, *par)
+    for k in back:
+        assert np.array_equal(back[k], z[f"state/out/back_{k}"]), k
+    kept = (z["state/out/aim2"][1:] == 0.0) & (st["aicen"] > 0.0)
+    assert kept.any() and np.array_equal(back["aicen"][kept], st["aicen"][kept])
