@@ -137,6 +137,30 @@
             import :: c_int, c_ptr
             integer(c_int), value :: rc
          end function
+         ! ---- transport_remap on the device (include/evp_b200.h, "Horizontal transport") ----
+         integer(c_int) function evp_gpu_set_transport_grid(h, g) bind(C, name='evp_gpu_set_transport_grid')
+            import :: c_int, c_ptr
+            type(c_ptr), value :: h
+            type(c_ptr), intent(in) :: g(4)                 ! dxu, dyu, HTN, HTE
+         end function
+         integer(c_int) function evp_gpu_set_transport_tracers(h, ncat, ntrace, tracer_type, depend, has_dependents, &
+                                                               hm, xav, yav, xxav, yyav) &
+                                                               bind(C, name='evp_gpu_set_transport_tracers')
+            import :: c_int, c_ptr
+            type(c_ptr), value :: h
+            integer(c_int), value :: ncat, ntrace
+            integer(c_int), intent(in) :: tracer_type(*), depend(*), has_dependents(*)
+            type(c_ptr), value :: hm, xav, yav, xxav, yyav
+         end function
+         integer(c_int) function evp_gpu_transport_remap(h, dt, nt_qsno, nslyr, rhos, Lfresh, aice0, aicen, trcrn, vicen, vsnon, &
+                                                         stop, stop_cat, istop, jstop) bind(C, name='evp_gpu_transport_remap')
+            import :: c_int, c_ptr, c_double
+            type(c_ptr), value :: h
+            real(c_double), value :: dt, rhos, Lfresh
+            integer(c_int), value :: nt_qsno, nslyr
+            type(c_ptr), value :: aice0, aicen, trcrn, vicen, vsnon
+            integer(c_int), intent(out) :: stop, stop_cat, istop, jstop
+         end function
       end interface
 
       type(c_ptr) :: handle = c_null_ptr
@@ -423,5 +447,45 @@
       if (.not. ready) return
       call check(evp_gpu_invalidate_state(handle), 'invalidate_state')
       end subroutine evp_gpu_state_changed
+
+!=======================================================================
+! == subroutine transport_remap(dt) of the reference (source/ice_transport_driver.F90:198-627, its checks off as
+! compiled), called by step_dynamics right after evp (source/ice_step_mod.F90:1126-1130): the velocities of the evp
+! call above are still on the device.  One block per task (max_blocks = 1), as for evp.  trcrn is passed as
+! trcrn(:,:,1:ntrcr,:,1): contiguous when ntrcr == max_ntrcr, otherwise copied to a work array by the caller.
+      subroutine transport_remap_gpu (dt)
+      use ice_kinds_mod
+      use ice_constants, only: rhos, Lfresh
+      use ice_domain_size, only: ncat, nslyr, max_ntrcr
+      use ice_state, only: aice0, aicen, vicen, vsnon, trcrn, ntrcr, nt_qsno
+      use ice_grid, only: dxu, dyu, HTN, HTE, hm, xav, yav, xxav, yyav
+      use ice_transport_driver, only: ntrace, tracer_type, depend, has_dependents     ! made public by the patch
+      use ice_exit, only: abort_ice
+      use ice_fileunits, only: nu_diag
+      real (kind=dbl_kind), intent(in) :: dt
+      logical, save :: first = .true.
+      integer(c_int) :: stop, stop_cat, istop, jstop
+      integer(c_int), allocatable :: hd(:)
+      type(c_ptr) :: g(4)
+      if (first) then
+         g = [r8loc(dxu), r8loc(dyu), r8loc(HTN), r8loc(HTE)]
+         call check(evp_gpu_set_transport_grid(handle, g), 'set_transport_grid')
+         allocate(hd(ntrace))
+         hd = merge(1_c_int, 0_c_int, has_dependents(1:ntrace))
+         call check(evp_gpu_set_transport_tracers(handle, int(ncat, c_int), int(ntrace, c_int), tracer_type, depend, hd, &
+                    r8loc(hm), r8loc(xav), r8loc(yav), r8loc(xxav), r8loc(yyav)), 'set_transport_tracers')
+         first = .false.
+      endif
+      if (ntrcr /= max_ntrcr) call abort_ice('transport_remap (B200): pass a contiguous copy of trcrn(:,:,1:ntrcr,:,1)')
+      call check(evp_gpu_transport_remap(handle, dt, int(nt_qsno, c_int), int(nslyr, c_int), rhos, Lfresh, &
+                 r8loc(aice0), r8loc(aicen), r8loc(trcrn), r8loc(vicen), r8loc(vsnon), stop, stop_cat, istop, jstop), &
+                 'transport_remap')
+      if (stop /= 0) then        ! what horizontal_remap prints before abort_ice (ice_transport_remap.F90:552-563, :783-825)
+         write (nu_diag,*) 'remap transport stop kind, category, block i, j =', stop, stop_cat, istop, jstop
+         if (stop == 1) call abort_ice('remap transport: bad departure points')
+         if (stop == 2) call abort_ice('ice remap_transport: negative area (open water)')
+         call abort_ice('ice remap_transport: negative area (ice)')
+      endif
+      end subroutine transport_remap_gpu
 
       end module ice_dyn_evp
