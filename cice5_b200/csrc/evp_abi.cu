@@ -155,8 +155,9 @@ struct evp_handle {
     // transport_remap: the ice state aice0, aicen, vicen, vsnon (ncat each), trcrn (ncat * ntrcr) as planes
     double *st = nullptr;
     bool st_loaded = false, st_done = false;
-    cudaEvent_t tev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // transport stage: start, kernels done, ghost updates
-                                                          // done; whole remap: start, end
+    cudaEvent_t tev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+                                                          // reconstruction: start, kernel done, ghost updates done [0..2];
+                                                          // whole remap: start, end [3, 4]; departure points [5..7]
     double tr_ms[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};     // departure kernels / halos, reconstruction kernel / halos, fluxes + update, whole remap
     bool have_ht = false;         // HTE / HTN were given: compact metric rows are possible
     evp_stats_t stats;
@@ -1622,11 +1623,11 @@ void stage_mark(Builder &B, int k)
         return EVP_OK;
     });
 }
-int stage_times(evp_handle *h, int slot)
+int stage_times(evp_handle *h, int slot, int ev)
 {
     float ms = 0.f;
-    CK(cudaEventElapsedTime(&ms, h->tev[0], h->tev[1])); h->tr_ms[slot] = ms;
-    CK(cudaEventElapsedTime(&ms, h->tev[1], h->tev[2])); h->tr_ms[slot + 1] = ms;
+    CK(cudaEventElapsedTime(&ms, h->tev[ev], h->tev[ev + 1])); h->tr_ms[slot] = ms;
+    CK(cudaEventElapsedTime(&ms, h->tev[ev + 1], h->tev[ev + 2])); h->tr_ms[slot + 1] = ms;
     return EVP_OK;
 }
 
@@ -1636,7 +1637,7 @@ void build_departure(evp_handle *h, double dt, int midpt, std::vector<Op> &ops)
 {
     Builder B{h, ops};
     B.sync();                                                    // every rank has left its previous operation
-    stage_mark(B, 0);
+    stage_mark(B, 5);
     B.op([h, dt, midpt](Launcher &L) {
         DepartArgs a;
         a.nxb = h->nxb; a.nyb = h->nyb; a.ld = h->ld; a.dt = dt; a.midpt = midpt;
@@ -1650,11 +1651,11 @@ void build_departure(evp_handle *h, double dt, int midpt, std::vector<Op> &ops)
         CK(cudaGetLastError());
         return EVP_OK;
     });
-    stage_mark(B, 1);
+    stage_mark(B, 6);
     B.halo(W_1, 1, -1.0, 0.0);                                   // ice_HaloUpdate(dpx, NEcorner, vector)
     B.halo(W_2, 1, -1.0, 0.0);
     B.sync();                                                    // inbox buffers are free again
-    stage_mark(B, 2);
+    stage_mark(B, 7);
 }
 int finish_departure(evp_handle *h)
 {
@@ -1665,7 +1666,7 @@ int finish_departure(evp_handle *h)
         snprintf(g_cuda_err, sizeof(g_cuda_err), "halo wait timed out: a peer rank did not arrive");
         return EVP_ERR_PEER;
     }
-    return stage_times(h, 0);
+    return stage_times(h, 0, 5);
 }
 }  // namespace
 
@@ -1815,7 +1816,7 @@ int finish_ops(evp_handle *h)
         snprintf(g_cuda_err, sizeof(g_cuda_err), "halo wait timed out: a peer rank did not arrive");
         return EVP_ERR_PEER;
     }
-    return stage_times(h, 2);
+    return stage_times(h, 2, 0);
 }
 }  // namespace
 extern "C" {
@@ -1853,6 +1854,14 @@ int evp_gpu_set_transport_tracers(evp_handle_t *h, int ncat, int ntrace, const i
             if (ty == 3) return EVP_ERR_ARG;
             if (parents == kRemapMaxParents) return EVP_ERR_TOO_LARGE;
             a.slot[nt] = (signed char)parents++;
+        }
+    }
+    {   // tracer numbers type by type
+        int k = 0;
+        for (int ty = 1; ty <= 3; ++ty) {
+            for (int nt = 0; nt < ntrace; ++nt) if (tracer_type[nt] == ty) a.order[k++] = (unsigned char)nt;
+            if (ty == 1) a.n1 = (short)k;
+            if (ty == 2) a.n2 = (short)(k - a.n1);
         }
     }
     CK(cudaSetDevice(h->cfg.device));
@@ -2040,7 +2049,9 @@ int finish_remap(evp_handle *h)
     h->rc_loaded = false;                                        // mm, tm now hold the transported state
     h->rc_remapped = true;
     float ms = 0.f;
-    CK(cudaEventElapsedTime(&ms, h->tev[2], h->tev[4])); h->tr_ms[4] = ms;
+    TRY(stage_times(h, 2, 0));
+    TRY(stage_times(h, 0, 5));
+    CK(cudaEventElapsedTime(&ms, h->tev[7], h->tev[4])); h->tr_ms[4] = ms;
     CK(cudaEventElapsedTime(&ms, h->tev[3], h->tev[4])); h->tr_ms[5] = ms;
     return EVP_OK;
 }

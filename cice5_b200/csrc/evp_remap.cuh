@@ -84,7 +84,9 @@ struct ReconArgs {
     double *tc, *tx, *ty;              // as tm
     signed char ttype[kRemapMaxTrace];          // tracer_type
     unsigned char parent[kRemapMaxTrace];       // depend - 1 (types 2, 3)
-    signed char slot[kRemapMaxTrace];           // type 1 with dependents: index into the thread's mtxav / mtyav; else -1
+    signed char slot[kRemapMaxTrace];           // tracer with dependents: its slot in the per-thread parent storage; else -1
+    unsigned char order[kRemapMaxTrace];        // tracer numbers sorted by type (stable): parents come before children
+    short n1, n2;                               // number of type-1, type-2 tracers (the rest is type 3)
 };
 
 namespace recon {
@@ -350,7 +352,10 @@ struct FluxArgs {
 // Dynamic shared memory, per thread: the flux accumulators of the category (1 + ntrace doubles), per tracer with
 // dependents mtsum, mtxsum, mtysum of the current triangle (3 doubles x slots), and the ten points of the triangles
 // (20 doubles; they are picked by table index, which would put a per-thread array into local memory)
-__global__ void __launch_bounds__(128) edge_flux_kernel(const __grid_constant__ FluxArgs f, int nslots)
+#ifndef EVP_FLUX_BLOCKS
+#define EVP_FLUX_BLOCKS 8
+#endif
+__global__ void __launch_bounds__(128, EVP_FLUX_BLOCKS) edge_flux_kernel(const __grid_constant__ FluxArgs f, int nslots)
 {
     using namespace flux;
     extern __shared__ double par[];
@@ -481,37 +486,55 @@ __global__ void __launch_bounds__(128) edge_flux_kernel(const __grid_constant__ 
             w0 = m0 * y0; w1 = m1 * y1; w2 = m2 * y2; w3 = m3 * y3;
             const double mysum = w0 + w1 + w2 + w3;
             const double myysum = w0 * y0 + w1 * y1 + w2 * y2 + w3 * y3;
-            // :3423-3500.  A thread's loads are its latency: the fields of kFluxChunk tracers are requested together
-            // before the first is used (tx, ty of a type-3 tracer are loaded and ignored)
-            for (int nb = 0; nb < ntr; nb += kFluxChunk) {
+            // :3423-3500, the tracers type by type (a tracer's flux depends on its parent's sums only, and parents are of
+            // the type before).  A thread's loads are its latency: the fields of kFluxChunk tracers are requested
+            // together before the first is used
+            for (int nb = 0; nb < a.n1; nb += kFluxChunk) {                // type 1: mass * tracer
                 double tcv[kFluxChunk], txv[kFluxChunk], tyv[kFluxChunk];
+                int ntv[kFluxChunk];
 #pragma unroll
                 for (int k = 0; k < kFluxChunk; ++k) {
-                    const size_t pl = t0 + (size_t)(nb + k < ntr ? nb + k : nb) * a.pe + qs;
+                    ntv[k] = a.order[nb + k < a.n1 ? nb + k : nb];
+                    const size_t pl = t0 + (size_t)ntv[k] * a.pe + qs;
                     tcv[k] = a.tc[pl]; txv[k] = a.tx[pl]; tyv[k] = a.ty[pl];
                 }
 #pragma unroll
                 for (int k = 0; k < kFluxChunk; ++k) {
-                    const int nt = nb + k;
-                    if (nt >= ntr) break;
-                    const int type = a.ttype[nt], sl = a.slot[nt] * 128;
+                    if (nb + k >= a.n1) break;
+                    const int nt = ntv[k], sl = a.slot[nt] * 128;
                     const double tc = tcv[k], tx = txv[k], ty = tyv[k];
-                    double ms;
-                    if (type == 1) {
-                        ms = msum * tc + mxsum * tx + mysum * ty;
-                        if (sl >= 0) {
-                            mtsum[sl] = ms;
-                            mtxsum[sl] = mxsum * tc + mxxsum * tx + mxysum * ty;
-                            mtysum[sl] = mysum * tc + mxysum * tx + myysum * ty;
-                        }
-                    } else {
-                        const int s1 = a.slot[a.parent[nt]] * 128;
-                        if (type == 2) ms = mtsum[s1] * tc + mtxsum[s1] * tx + mtysum[s1] * ty;
-                        else ms = mtsum[s1] * tc;
-                        if (sl >= 0) mtsum[sl] = ms;
+                    const double ms = msum * tc + mxsum * tx + mysum * ty;
+                    if (sl >= 0) {
+                        mtsum[sl] = ms;
+                        mtxsum[sl] = mxsum * tc + mxxsum * tx + mxysum * ty;
+                        mtysum[sl] = mysum * tc + mxysum * tx + myysum * ty;
                     }
                     acc[(1 + nt) * 128] = acc[(1 + nt) * 128] + area * ms;
                 }
+            }
+            const int e2 = a.n1 + a.n2;
+            for (int nb = a.n1; nb < e2; nb += kFluxChunk) {               // type 2: mass * parent * tracer
+                double tcv[kFluxChunk], txv[kFluxChunk], tyv[kFluxChunk];
+                int ntv[kFluxChunk];
+#pragma unroll
+                for (int k = 0; k < kFluxChunk; ++k) {
+                    ntv[k] = a.order[nb + k < e2 ? nb + k : nb];
+                    const size_t pl = t0 + (size_t)ntv[k] * a.pe + qs;
+                    tcv[k] = a.tc[pl]; txv[k] = a.tx[pl]; tyv[k] = a.ty[pl];
+                }
+#pragma unroll
+                for (int k = 0; k < kFluxChunk; ++k) {
+                    if (nb + k >= e2) break;
+                    const int nt = ntv[k], sl = a.slot[nt] * 128, s1 = a.slot[a.parent[nt]] * 128;
+                    const double ms = mtsum[s1] * tcv[k] + mtxsum[s1] * txv[k] + mtysum[s1] * tyv[k];
+                    if (sl >= 0) mtsum[sl] = ms;
+                    acc[(1 + nt) * 128] = acc[(1 + nt) * 128] + area * ms;
+                }
+            }
+            for (int nb = e2; nb < ntr; ++nb) {                            // type 3: mass * grandparent * parent * tracer
+                const int nt = a.order[nb], s1 = a.slot[a.parent[nt]] * 128;
+                const double ms = mtsum[s1] * a.tc[t0 + (size_t)nt * a.pe + qs];
+                acc[(1 + nt) * 128] = acc[(1 + nt) * 128] + area * ms;
             }
         }
     }

@@ -90,6 +90,10 @@ def main():
     ap.add_argument("--evolve", type=int, default=0,
                     help="1: the forcing evolves from call to call (the 10-day run of SURVEY 8d: 240 calls) and EVERY "
                          "call is compared; prints max / final err_inf and err_rms per field group")
+    ap.add_argument("--transport", type=int, default=0,
+                    help="1: after the evp calls, transport_remap on every rank's slab from the resident velocities "
+                         "(peer-memory halos of the transport stages), compared bitwise with the oracle's")
+    ap.add_argument("--dt-scale", type=float, default=6.0, help="transport time step = dt * this")
     ap.add_argument("--out", default=None, help="JSON report (rank 0)")
     args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -123,6 +127,19 @@ def main():
     gathered = [None] * world
     dist.gather_object((io, out), gathered if rank == 0 else None, dst=0)
     ok = True
+    tgath = None
+    if args.transport:
+        from tests.test_emu_device_sources import RHOS, LFRESH, _transport_state
+        d, state = _transport_state(grid, case, 9)
+        slab = lambda a: fx.slab(np.ascontiguousarray(a), rank, world, starts)
+        e.set_transport_grid(sl({k: grid.f[k] for k in ("dxu", "dyu", "HTN", "HTE")}))
+        e.set_transport_tracers(state["aicen"].shape[0], d["tracer_type"], d["depend"], d["has_dependents"],
+                                sl({k: d[k] for k in ("hm", "xav", "yav", "xxav", "yyav")}))
+        dist.barrier()
+        new, stop = e.transport_remap(case.dt * args.dt_scale, {k: slab(v) for k, v in state.items()}, 6, 1, RHOS, LFRESH)
+        tms = e.transport_timing()
+        tgath = [None] * world
+        dist.gather_object((new, stop, tms), tgath if rank == 0 else None, dst=0)
     if rank == 0:
         from oracle import oracle as orc
         from tests.util import clone_case, compare_cases
@@ -141,6 +158,20 @@ def main():
         except AssertionError as ex:
             ok = False
             print("MULTIGPU PARITY FAILED:", str(ex)[:2000], flush=True)
+    if rank == 0 and args.transport:
+        geo = dict(d)
+        geo.update({k: grid.f[k] for k in ("dxu", "dyu", "HTN", "HTE", "tarear")})
+        rs = {k: v.copy() for k, v in state.items()}
+        rstop = orc.transport_remap(dom, case.dt * args.dt_scale, d["tracer_type"], d["depend"], d["has_dependents"], geo,
+                                    ref.io["uvel"], ref.io["vvel"], rs, 6, 1, RHOS, LFRESH)
+        bad = [k for k in rs if not np.array_equal(fx.unslab([g[0][k] for g in tgath]), rs[k])]
+        stops = [tuple(g[1]) for g in tgath]
+        tok = not bad and all(s == tuple(rstop) for s in stops)
+        moved = float(np.abs(rs["aicen"] - state["aicen"])[:, 1:-1, 1:-1].max())
+        print(f"MULTIGPU TRANSPORT {'OK' if tok else 'FAILED'}: {args.grid} N={world} transport_remap bitwise == oracle "
+              f"(ghost cells included), stops {stops} oracle {rstop}, mismatching arrays {bad}, max |d aicen| {moved:.3e}, "
+              f"remap {max(g[2]['remap_ms'] for g in tgath):.3f} ms (slowest rank)", flush=True)
+        ok = ok and tok
     e.close()
     dist.barrier()
     dist.destroy_process_group()
