@@ -500,16 +500,18 @@ def measure(ctx, args, gridname, scenario, steps, warmup, do_e2e, do_parity, ref
                "roofline": roof, "clocks": clocks, "value_check": check_value, "parity": parity, "e2e": e2e,
                "e2e_full": e2e_full,
                "gpu_launches": int(launches), "loop_kernel_launches_per_step": int(loop_launches)}
-    if N == 1 and do_e2e and not args.no_transport and res is not None:
+    # the bench workload: timing only (its oracle twin would hold 370 planes of 78 MB on the host); the 1-degree tripole
+    # among the other configurations: timing + the oracle port beside it (parity of every cell, CPU baseline)
+    if N == 1 and (do_e2e or gridname == "tp1") and not getattr(args, "no_transport", False) and res is not None:
         try:
-            res["transport"] = transport_block(e, args, grid, case, dt)
+            res["transport"] = transport_block(e, args, grid, case, dt, cpu=not do_e2e)
         except Exception as ex:                   # noqa: BLE001 -- a side block must not cost the headline line
             res["transport"] = {"error": str(ex)[:300]}
     e.close()
     return res
 
 
-def transport_block(e, args, grid, case, dt, steps=5, warmup=2):
+def transport_block(e, args, grid, case, dt, steps=5, warmup=2, cpu=False):
     """SURVEY.md 8f row 2, the stages of horizontal_remap that run on the device so far, on the bench workload's grid
     (N = 1): departure_points from the velocities the timed evp calls left resident, and the field reconstruction
     (make_masks + construct_fields + limited_gradient) of 5 ice categories x 11 tracers + open water.  Device time by
@@ -544,7 +546,25 @@ def transport_block(e, args, grid, case, dt, steps=5, warmup=2):
         e.horizontal_remap_compute(dt)
         if k >= 1:
             rem.append(e.transport_timing())
-    mm_new, _, stop = e.horizontal_remap_fetch()
+    mm_new, tm_new, stop = e.horizontal_remap_fetch()
+    check = None
+    if cpu:
+        # the same horizontal_remap on one host core by the oracle port, from the velocities on the device: a parity leg
+        # (every cell of mm, tm bitwise) and the CPU baseline of this stage
+        from oracle import oracle as orc
+        pio = {k: np.zeros_like(v) for k, v in case.io.items()}
+        pout = {k: np.zeros_like(v) for k, v in case.out.items()}
+        e.download(pio, pout)
+        geo = dict(d)
+        geo.update({k: grid.f[k] for k in ("dxu", "dyu", "HTN", "HTE", "tarear")})
+        rmm, rtm = d["mm"].copy(), d["tm"].copy()
+        t0 = time.perf_counter()
+        rstop = orc.horizontal_remap(grid.dom, dt, d["tracer_type"], d["depend"], d["has_dependents"], geo, pio["uvel"],
+                                     pio["vvel"], rmm, rtm)
+        cpu_ms = 1e3 * (time.perf_counter() - t0)
+        check = {"bitwise": bool(np.array_equal(mm_new, rmm) and np.array_equal(tm_new, rtm) and tuple(stop) == tuple(rstop)),
+                 "arrays": "mm (ncat+1 planes), tm (ncat x ntrace planes), every cell; the stop report",
+                 "cpu_port_ms": cpu_ms, "cpu_cores": 1, "cpu_kind": "port (oracle/remap_oracle.c, serial)"}
     med = lambda rows, key: float(np.median([r[key] for r in rows]))
     # algorithmic bytes per cell: departure reads u, v, dxu, dyu, HTN, HTE and writes dpx, dpy twice (first-order,
     # midpoint) -> 10 doubles; reconstruction, per ice category, reads mm + ntrace tracers + hm xav yav xxav yyav and
@@ -564,7 +584,8 @@ def transport_block(e, args, grid, case, dt, steps=5, warmup=2):
             "horizontal_remap": (lambda fb, ms, fms: {"remap_ms": ms, "fluxes_and_update_ms": fms, "fluxes_and_update_alg_bytes": fb,
                                                       "fluxes_and_update_GBps": fb / (fms * 1e-3) / 1e9,
                                                       "fluxes_and_update_frac": fb / (fms * 1e-3) / 1e9 / peak,
-                                                      "stop": list(stop), "max_abs_area_change": float(np.abs(mm_new - d["mm"])[:, 1:-1, 1:-1].max())})(
+                                                      "stop": list(stop), "max_abs_area_change": float(np.abs(mm_new - d["mm"])[:, 1:-1, 1:-1].max()),
+                                                      "oracle_check": check})(
                 8 * cells * (2 * (4 + 3 * (ncat + 1) + 3 * ncat * nt) + 2 * ((ncat + 1) + ncat * nt)        # edge sweeps
                              + 2 * ((ncat + 1) + ncat * nt) + 2 * ((ncat + 1) + ncat * nt) + 1),             # update_fields
                 med(rem, "remap_ms"), med(rem, "flux_update_ms")),
@@ -620,6 +641,8 @@ def main():
                     "regime": "HBM" if ALG_BYTES * r["roofline"]["active_cells_per_launch"] > L2_BYTES else "L2-resident",
                     "parity": r["parity"], "value_check": r["value_check"],
                     "loop_kernel_launches_per_step": r["loop_kernel_launches_per_step"]}
+                if r.get("transport"):
+                    others[g]["transport"] = r["transport"]
     if rank == 0:
         if cpu is not None:
             res["cpu_baseline"] = cpu

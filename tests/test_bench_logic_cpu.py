@@ -54,7 +54,7 @@ def test_measure_reports_parity_value_checks_and_e2e(tiny):
         assert t[k]["kernel_ms"] > 0 and t[k]["achieved_GBps"] > 0 and t[k]["alg_bytes"] > 0
     assert t["construct_fields"]["halo_updates"] == 183
     assert t["horizontal_remap"]["remap_ms"] > 0 and t["horizontal_remap"]["stop"] == [0, 0, 0, 0]
-    assert t["horizontal_remap"]["max_abs_area_change"] > 0
+    assert t["horizontal_remap"]["max_abs_area_change"] > 0 and t["horizontal_remap"]["oracle_check"] is None
 
 
 def test_parity_leg_detects_a_wrong_result(tiny, monkeypatch):
@@ -74,3 +74,21 @@ def test_parity_leg_detects_a_wrong_result(tiny, monkeypatch):
         r = bench.measure(_Ctx(), tiny, "tiny", "full", steps=1, warmup=0, do_e2e=False, do_parity=True)
     assert r["parity"]["bitwise"] is False and (0, "uvel") in [tuple(m) for m in r["parity"]["mismatches"]]
     assert 0.0 < r["parity"]["max_rel"] < 1e-12
+
+
+def test_transport_block_oracle_leg(tiny):
+    """The transport block with the oracle port beside it (what bench.py attaches to the 1-degree configuration): parity
+    of every cell and a CPU time."""
+    from cice5_b200 import fixtures
+    with emu.patched(kernel="tma") as evp:
+        grid = fixtures.make_grid("tiny")
+        case = fixtures.make_case(grid, "full", ndte=5, dt=3600.0)
+        e = evp.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True)
+        try:
+            e.set_grid(grid.f)
+            e.evp(case.dt, case.inp, case.io, case.out)
+            t = bench.transport_block(e, tiny, grid, case, 40 * case.dt, steps=1, warmup=1, cpu=True)
+        finally:
+            e.close()
+    c = t["horizontal_remap"]["oracle_check"]
+    assert c["bitwise"] is True and c["cpu_port_ms"] > 0 and t["horizontal_remap"]["max_abs_area_change"] > 1e-4
