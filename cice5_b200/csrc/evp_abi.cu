@@ -2015,12 +2015,10 @@ void build_remap(evp_handle *h, double dt, std::vector<Op> &ops)
         f.dpx = h->plane(W_1); f.dpy = h->plane(W_2);
         f.dxu = h->tr; f.dyu = h->tr + h->plane_elems;
         for (int e = 0; e < 2; ++e) { f.mflx[e] = pl(l.mflx(e)); f.mtflx[e] = pl(l.mtflx(e)); }
-        // shared memory per block: (1 + ntrace + 3 slots [+ 20]) doubles x 128 threads (above 48 KB: opt in)
-        const size_t fsm = (size_t)(1 + l.ntrace + 3 * nslots + (EVP_FLUX_PTS_SMEM ? 20 : 0)) * 128 * sizeof(double);
+        // shared memory per block: (1 + ntrace + 3 slots) doubles x 128 threads (above 48 KB: opt in; at most 177 KB)
+        const size_t fsm = (size_t)(1 + l.ntrace + 3 * nslots) * 128 * sizeof(double);
         if (fsm > 48 * 1024) CK(cudaFuncSetAttribute(edge_flux_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm));
-        const int xb = (h->nxb + 127) / 128;
-        const dim3 fgrid = EVP_FLUX_EDGE_X ? dim3(2 * xb, h->nyb, l.ncat + 1) : dim3(xb, h->nyb, 2 * (l.ncat + 1));
-        edge_flux_kernel<<<fgrid, 128, fsm, L.s()>>>(f, nslots);
+        edge_flux_kernel<<<dim3(2 * ((h->nxb + 127) / 128), h->nyb, l.ncat + 1), 128, fsm, L.s()>>>(f, nslots);
         CK(cudaGetLastError());
         UpdateArgs u;
         u.a = h->rc_args;

@@ -332,12 +332,7 @@ constexpr double puny = 1.0e-11, eps16 = 1.0e-16;
 #define EVP_FLUX_CHUNK 4
 #endif
 constexpr int kFluxChunk = EVP_FLUX_CHUNK;
-#ifndef EVP_FLUX_PTS_SMEM
-#define EVP_FLUX_PTS_SMEM 0
-#endif
-#ifndef EVP_FLUX_EDGE_X
-#define EVP_FLUX_EDGE_X 1
-#endif
+
 
 struct FluxArgs {
     ReconArgs a;                       // sizes, tracer tables, the reconstructed fields mc mx my tc tx ty
@@ -349,9 +344,8 @@ struct FluxArgs {
 // = category: a thread integrates one category (its mass and every tracer) over the triangles of one cell edge; the
 // triangles are worked out again per category (a few hundred operations against the ~100 gathers of a category).  The
 // east and the north edges of the same cells run side by side: they gather from the same 3 x 3 cells, once from HBM.
-// Dynamic shared memory, per thread: the flux accumulators of the category (1 + ntrace doubles), per tracer with
-// dependents mtsum, mtxsum, mtysum of the current triangle (3 doubles x slots), and the ten points of the triangles
-// (20 doubles; they are picked by table index, which would put a per-thread array into local memory)
+// Dynamic shared memory, per thread: the flux accumulators of the category (1 + ntrace doubles) and, per tracer with
+// dependents, mtsum, mtxsum, mtysum of the current triangle (3 doubles x slots)
 #ifndef EVP_FLUX_BLOCKS
 #define EVP_FLUX_BLOCKS 8
 #endif
@@ -360,26 +354,18 @@ __global__ void __launch_bounds__(128, EVP_FLUX_BLOCKS) edge_flux_kernel(const _
     using namespace flux;
     extern __shared__ double par[];
     const ReconArgs &a = f.a;
-#if EVP_FLUX_EDGE_X
     const int c = (blockIdx.x >> 1) * blockDim.x + threadIdx.x, r = blockIdx.y;
     const int north = blockIdx.x & 1, n = blockIdx.z;
-#else
-    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
-    const int north = blockIdx.z / (a.ncat + 1), n = blockIdx.z % (a.ncat + 1);
-#endif
     if (c >= a.nxb) return;
     const size_t q = (size_t)r * a.ld + c;
     const int ntr = n > 0 ? a.ntrace : 0;
     double *acc = par + threadIdx.x;                                        // acc[k * 128]: k = 0 mass, 1 + nt tracers
     double *mtsum = par + (size_t)(1 + a.ntrace) * 128 + threadIdx.x, *mtxsum = mtsum + (size_t)nslots * 128,
            *mtysum = mtxsum + (size_t)nslots * 128;
-#if EVP_FLUX_PTS_SMEM
-    constexpr int kPS = 128;
-    double *pxs = mtysum + (size_t)nslots * 128, *pys = pxs + 10 * 128;     // point k: pxs[k * 128], pys[k * 128]
-#else
+    // the ten points, picked by table index: a per-thread array in local memory (in shared memory they cost occupancy:
+    // measured slower, profiles/r02_remap.md)
     constexpr int kPS = 1;
-    double pxs[10], pys[10];                                                // picked by table index: local memory
-#endif
+    double pxs[10], pys[10];
     for (int k = 0; k <= ntr; ++k) acc[k * 128] = 0.0;                      // mflx = c0, mtflx = c0 (:3224-3230)
     // edges of the block that carry a flux (:1820-1826, :1860-1866); every other cell of the flux planes is zero
     const bool edge = north ? (c >= 1 && c <= a.nxb - 2 && r <= a.nyb - 2) : (c <= a.nxb - 2 && r >= 1 && r <= a.nyb - 2);
