@@ -660,12 +660,14 @@ def test_construct_fields_gx3_and_argument_errors(dev):
 
 
 # ---- all of horizontal_remap ---------------------------------------------------------------------
-def _remap_case(dev, grid, scenario, nranks, dt_scale, geometry="cice", seed=7, ndte=6, tarear_scale=1.0):
+def _remap_case(dev, grid, scenario, nranks, dt_scale, geometry="cice", seed=7, ndte=6, tarear_scale=1.0, open_water=True):
     """evp(dt), then horizontal_remap on the device from the resident velocities against the oracle's (pinned to the
     reference text routine by routine and as a whole), every cell of mm and tm."""
     case = fx.make_case(grid, scenario, ndte=ndte, dt=3600.0)
     got = clone_case(case)
     d = fx.transport_tracers(grid, case.inp, seed, geometry)
+    if not open_water:
+        d["mm"][0] = 0.0                                    # no open water to run out of: an ice category does first
     ncat = d["tm"].shape[0]
     f = dict(grid.f)
     f["tarear"] = grid.f["tarear"] * tarear_scale           # > 1: exaggerated flux divergence, areas go negative
@@ -728,7 +730,9 @@ def test_horizontal_remap_gx3_and_stops(dev):
     assert rstop[0] == 1 and stops == [rstop]
     # negative new areas: open water first, then (open water made thick enough) an ice category
     mm, tm, stops, rmm, rtm, rstop, d = _remap_case(dev, grid, "full", 1, 20.0, "random", tarear_scale=400.0)
-    assert rstop[0] in (2, 3) and rstop[2] > 1 and stops == [rstop]
+    assert rstop[0] == 2 and rstop[2] > 1 and stops == [rstop]
+    mm, tm, stops, rmm, rtm, rstop, d = _remap_case(dev, grid, "full", 1, 20.0, "random", tarear_scale=400.0, open_water=False)
+    assert rstop[0] == 3 and rstop[1] >= 1 and rstop[2] > 1 and stops == [rstop]
 
 
 # ---- transport_remap: the caller of horizontal_remap, from and to the ice state --------------------------------------
