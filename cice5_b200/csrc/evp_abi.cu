@@ -939,7 +939,7 @@ struct Builder {
 
     // ice_HaloUpdate (center) of `nplanes` planes `stride` elements apart, 2 * kWideSlots planes per operation
     int wide_seq = 0;
-    void halo_multi(double *plane0, int nplanes, size_t stride, double sgn, double fill)
+    void halo_multi(double *plane0, int nplanes, size_t stride, NegRanges neg, double fill)
     {
         evp_handle *hh = h;
         for (int first = 0; first < nplanes; first += 2 * kWideSlots) {
@@ -961,11 +961,11 @@ struct Builder {
                 return EVP_OK;
             });
             sync();
-            op([hh, plane, np, stride, sgn, fill, buf](Launcher &L) {
+            op([hh, plane, np, stride, first, neg, fill, buf](Launcher &L) {
                 const Geom &g = hh->g;
                 const int na = g.nxl + 2 + g.ny;
                 halo_apply_multi_kernel<<<dim3((na + 255) / 256, np), 256, 0, L.s()>>>(
-                    plane, stride, g, hh->ib, hh->inbox_wide(buf), sgn, fill, hh->west_closed(), hh->east_closed());
+                    plane, stride, g, hh->ib, hh->inbox_wide(buf), first, neg, fill, hh->west_closed(), hh->east_closed());
                 ++L.n;
                 CK(cudaGetLastError());
                 return EVP_OK;
@@ -1799,11 +1799,10 @@ void build_reconstruct(evp_handle *h, std::vector<Op> &ops)
     });
     stage_mark(B, 1);
     auto pl = [h](size_t k) { return h->rc + k * h->plane_elems; };
-    B.halo_multi(pl(l.mass(0, 0)), l.ncat + 1, h->plane_elems, 1.0, 0.0);                  // mc: center, scalar
-    B.halo_multi(pl(l.mass(1, 0)), 2 * (l.ncat + 1), h->plane_elems, -1.0, 0.0);           // mx, my: center, vector
-    if (l.ntrace > 0) {
-        B.halo_multi(pl(l.trc(0, 0)), l.ncat * l.ntrace, h->plane_elems, 1.0, 0.0);        // tc
-        B.halo_multi(pl(l.trc(1, 0)), 2 * l.ncat * l.ntrace, h->plane_elems, -1.0, 0.0);   // tx, ty
+    {   // mc | mx my | tc | tx ty are consecutive planes: one stack, the gradients change sign across the fold
+        const int nm = l.ncat + 1, nt = l.ncat * l.ntrace;
+        const NegRanges neg{{nm, 3 * nm + nt}, {3 * nm, 3 * nm + 3 * nt}};
+        B.halo_multi(pl(l.mass(0, 0)), 3 * nm + 3 * nt, h->plane_elems, neg, 0.0);
     }
     B.sync();
     stage_mark(B, 2);
@@ -2196,9 +2195,8 @@ void build_transport(evp_handle *h, double dt, int nt_qsno, int nslyr, double rh
     });
     auto sp = [h](size_t k) { return h->st + k * h->plane_elems; };
     B.sync();
-    B.halo_multi(sp(sl.aicen(0)), sl.ncat, h->plane_elems, 1.0, 0.0);                    // bound_state: center, scalar
-    if (sl.ntrcr > 0) B.halo_multi(sp(sl.trcrn(0)), sl.ncat * sl.ntrcr, h->plane_elems, 1.0, 0.0);
-    B.halo_multi(sp(sl.vicen(0)), 2 * sl.ncat, h->plane_elems, 1.0, 0.0);                // vicen, vsnon
+    // bound_state: aicen | vicen | vsnon | trcrn are consecutive planes, all center / scalar
+    B.halo_multi(sp(sl.aicen(0)), 3 * sl.ncat + sl.ncat * sl.ntrcr, h->plane_elems, NegRanges{{0, 0}, {0, 0}}, 0.0);
     B.sync();
     stage_mark(B, 4);
 }

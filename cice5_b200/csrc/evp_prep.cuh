@@ -132,7 +132,9 @@ __global__ void halo_apply_kernel(double *plane, Geom g, InboxGeom ib, double *i
 // Plane p of the stack (blockIdx.y) uses field (p & 1) of slot (p >> 1) of a wide inbox -- kWideSlots slots with the
 // layout above, two buffers alternated per operation like the narrow ones.  Same values into the same ghost cells as
 // nplanes calls of halo_push_kernel / halo_apply_kernel; one launch each and, between ranks, one sync instead of nplanes.
-constexpr int kWideSlots = 32;
+// Scalar and vector fields share an operation: planes [neg_lo[0], neg_hi[0]) and [neg_lo[1], neg_hi[1]) of the stack change sign
+// across the tripole fold (field_type_vector), the others do not.
+constexpr int kWideSlots = 96;
 
 __global__ void halo_push_multi_kernel(const __grid_constant__ PushArgs a, size_t plane_stride)
 {
@@ -166,10 +168,13 @@ __global__ void halo_push_multi_kernel(const __grid_constant__ PushArgs a, size_
 }
 
 // center fields only (loc 0): ghost row = sgn * mirrored top row, E-W ghosts, fill on closed edges
+struct NegRanges { int lo[2], hi[2]; };
 __global__ void halo_apply_multi_kernel(double *plane0, size_t plane_stride, Geom g, InboxGeom ib, double *inbox0,
-                                        double sgn, double fill, int west_closed, int east_closed)
+                                        int first, NegRanges neg, double fill, int west_closed, int east_closed)
 {
     const int t = blockIdx.x * blockDim.x + threadIdx.x, p = blockIdx.y;
+    const int pa = first + p;                                      // plane number in the whole stack
+    const double sgn = ((pa >= neg.lo[0] && pa < neg.hi[0]) || (pa >= neg.lo[1] && pa < neg.hi[1])) ? -1.0 : 1.0;
     double *plane = plane0 + (size_t)p * plane_stride;
     double *inbox = inbox0 + (size_t)(p >> 1) * inbox_doubles(ib);
     const int fo = (p & 1) * 2;
