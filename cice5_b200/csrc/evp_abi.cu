@@ -1586,8 +1586,8 @@ int evp_gpu_restart_fixup_group(evp_handle_t **hs, int n)
     CK(cudaSetDevice(hs[0]->cfg.device));
     std::vector<std::vector<Op>> P(n);
     std::vector<Launcher> L;
-    for (int r = 0; r < n; ++r) {
-        CK(cudaStreamSynchronize(hs[r]->stream));
+    for (int r = 0; r < n; ++r) CK(cudaStreamSynchronize(hs[r]->stream));      // (before any stream is switched: an early
+    for (int r = 0; r < n; ++r) {                                                // return leaves every handle as it was)
         hs[r]->stream = hs[0]->own_stream;
         build_restart_fixup(hs[r], P[r]);
         L.push_back(Launcher{hs[r]});
@@ -1715,8 +1715,8 @@ int evp_gpu_departure_points_group(evp_handle_t **hs, int n, double dt, int l_dp
     CK(cudaSetDevice(hs[0]->cfg.device));
     std::vector<std::vector<Op>> P(n);
     std::vector<Launcher> L;
-    for (int r = 0; r < n; ++r) {
-        CK(cudaStreamSynchronize(hs[r]->stream));
+    for (int r = 0; r < n; ++r) CK(cudaStreamSynchronize(hs[r]->stream));      // (before any stream is switched: an early
+    for (int r = 0; r < n; ++r) {                                                // return leaves every handle as it was)
         hs[r]->stream = hs[0]->own_stream;
         build_departure(hs[r], dt, l_dp_midpt ? 1 : 0, P[r]);
         L.push_back(Launcher{hs[r]});
@@ -1937,8 +1937,8 @@ int evp_gpu_construct_fields_group(evp_handle_t **hs, int n)
     CK(cudaSetDevice(hs[0]->cfg.device));
     std::vector<std::vector<Op>> P(n);
     std::vector<Launcher> L;
-    for (int r = 0; r < n; ++r) {
-        CK(cudaStreamSynchronize(hs[r]->stream));
+    for (int r = 0; r < n; ++r) CK(cudaStreamSynchronize(hs[r]->stream));      // (before any stream is switched: an early
+    for (int r = 0; r < n; ++r) {                                                // return leaves every handle as it was)
         hs[r]->stream = hs[0]->own_stream;
         build_reconstruct(hs[r], P[r]);
         L.push_back(Launcher{hs[r]});
@@ -2088,8 +2088,8 @@ int evp_gpu_horizontal_remap_group(evp_handle_t **hs, int n, double dt)
     CK(cudaSetDevice(hs[0]->cfg.device));
     std::vector<std::vector<Op>> P(n);
     std::vector<Launcher> L;
-    for (int r = 0; r < n; ++r) {
-        CK(cudaStreamSynchronize(hs[r]->stream));
+    for (int r = 0; r < n; ++r) CK(cudaStreamSynchronize(hs[r]->stream));      // (before any stream is switched: an early
+    for (int r = 0; r < n; ++r) {                                                // return leaves every handle as it was)
         hs[r]->stream = hs[0]->own_stream;
         build_remap(hs[r], dt, P[r]);
         L.push_back(Launcher{hs[r]});
@@ -2272,8 +2272,8 @@ int evp_gpu_transport_remap_group(evp_handle_t **hs, int n, double dt, int nt_qs
     CK(cudaSetDevice(hs[0]->cfg.device));
     std::vector<std::vector<Op>> P(n);
     std::vector<Launcher> L;
-    for (int r = 0; r < n; ++r) {
-        CK(cudaStreamSynchronize(hs[r]->stream));
+    for (int r = 0; r < n; ++r) CK(cudaStreamSynchronize(hs[r]->stream));      // (before any stream is switched: an early
+    for (int r = 0; r < n; ++r) {                                                // return leaves every handle as it was)
         hs[r]->stream = hs[0]->own_stream;
         build_transport(hs[r], dt, nt_qsno, nslyr, rhos, Lfresh, P[r]);
         L.push_back(Launcher{hs[r]});
