@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """One evp call, then horizontal_remap (evp_gpu_horizontal_remap_compute) on a bench grid, for timing / ncu runs:
-    python tools/profile_remap.py [grid] [calls] [dt_scale]
+    python tools/profile_remap.py [grid] [calls] [dt_scale] [scenario]
 Prints the device time of each stage (evp_gpu_get_transport_timing)."""
 import os
 import sys
@@ -15,9 +15,10 @@ def main():
     gridname = sys.argv[1] if len(sys.argv) > 1 else "tp01"
     calls = int(sys.argv[2]) if len(sys.argv) > 2 else 3
     dt_scale = float(sys.argv[3]) if len(sys.argv) > 3 else 1.0
+    scenario = sys.argv[4] if len(sys.argv) > 4 else "full"
     grid = fx.make_grid(gridname)
     dt = fx.GRID_DT.get(gridname, 3600.0)
-    case = fx.make_case(grid, "full", ndte=120, dt=dt)
+    case = fx.make_case(grid, scenario, ndte=120, dt=dt)
     d = fx.transport_tracers(grid, case.inp, 1, "cice")
     e = evp.EvpGpu.for_domain(grid.dom, 120, dt, strict=True)
     try:
