@@ -797,3 +797,64 @@ def test_transport_remap_bitwise(dev, nranks):
         assert np.array_equal(np.signbit(new[k]), np.signbit(ref[k])), k
     assert np.abs(ref["aicen"] - st["aicen"])[:, 1:-1, 1:-1].max() > 1e-3 and np.abs(ref["vicen"] - st["vicen"]).max() > 1e-3
     assert ref["aicen"][:, -1, 1:-1].any()                                # the fold filled the north ghost row
+
+
+# ---- dynamics + advection as one resident phase: evp and transport_remap step after step -------------------------------
+def _dynamics_steps(dev, grid, nsteps, nranks, scenario="caps", ndte=4, dt_scale=20.0, seed=11):
+    """step_dynamics' two device calls, `nsteps` times (source/ice_step_mod.F90:1113-1130): evp from the aggregated ice
+    state, transport_remap of the state from the velocities evp left on the device.  The oracle does the same with its
+    own state; after every step the dynamic state of evp and the whole ice state are compared bit for bit."""
+    case = fx.make_case(grid, scenario, ndte=ndte, dt=3600.0)
+    d, st0 = _transport_state(grid, case, seed)
+    ncat = st0["aicen"].shape[0]
+    f = grid.f
+    par = (6, 1, RHOS, LFRESH)
+    geo = dict(d)
+    geo.update({k: f[k] for k in ("dxu", "dyu", "HTN", "HTE", "tarear")})
+
+    def evp_inputs(st, step):
+        s = {"aice": st["aicen"].sum(axis=0), "vice": st["vicen"].sum(axis=0), "vsno": st["vsnon"].sum(axis=0)}
+        s["aice_init"] = s["aice"].copy()
+        s["strength"] = fx.PSTAR * s["vice"] * np.exp(-fx.CSTAR * (1.0 - s["aice"]))     # Hibler (ice_mechred.F90:2263)
+        inp = dict(s)
+        inp.update(fx.forcing(grid, s, step, steps_per_cycle=24))
+        return inp
+
+    dev_st = {k: v.copy() for k, v in st0.items()}
+    ref_st = {k: v.copy() for k, v in st0.items()}
+    got, ref = clone_case(case), clone_case(case)
+    single = nranks == 1
+    h = dev.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True) if single else \
+        dev.EvpGroup(case.dom, case.ndte, case.dt, nranks, strict=True)
+    moved = 0.0
+    try:
+        h.set_grid(f)
+        h.set_transport_grid(f)
+        h.set_transport_tracers(ncat, d["tracer_type"], d["depend"], d["has_dependents"], d)
+        for step in range(nsteps):
+            got.inp, ref.inp = evp_inputs(dev_st, step), evp_inputs(ref_st, step)
+            got.out, ref.out = fx.zeroed_outputs(case.dom), fx.zeroed_outputs(case.dom)
+            h.evp(case.dt, got.inp, got.io, got.out)
+            orc.run_case(ref)
+            new, stop = h.transport_remap(case.dt * dt_scale, dev_st, *par)
+            rstop = orc.transport_remap(case.dom, case.dt * dt_scale, d["tracer_type"], d["depend"], d["has_dependents"], geo,
+                                        ref.io["uvel"], ref.io["vvel"], ref_st, *par)
+            stops = [stop] if single else stop
+            assert rstop == (0, 0, 0, 0) and all(s == rstop for s in stops), (step, stops, rstop)
+            for k in ("uvel", "vvel") + fx.STRESS_FIELDS:
+                assert np.array_equal(phys(got.io[k]), phys(ref.io[k])), (step, k)
+            for k in ref_st:
+                assert np.array_equal(new[k], ref_st[k]), (step, k)
+            moved = max(moved, float(np.abs(new["aicen"] - dev_st["aicen"])[:, 1:-1, 1:-1].max()))
+            dev_st = new
+    finally:
+        h.close()
+    return moved, float(np.abs(ref_st["aicen"] - st0["aicen"])[:, 1:-1, 1:-1].max())
+
+
+@pytest.mark.parametrize("nranks", [1, 2])
+def test_dynamics_and_advection_steps_bitwise(dev, nranks):
+    _once(dev)
+    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
+    moved, total = _dynamics_steps(dev, grid, 6, nranks)
+    assert moved > 1e-4 and total > 1e-3

@@ -75,3 +75,17 @@ def test_transport_remap_bitwise_on_device(nranks):
     """transport_remap (source/ice_transport_driver.F90:198-627): state_to_tracers, horizontal_remap, tracers_to_state,
     bound_state, from and to aice0 / aicen / vicen / vsnon / trcrn."""
     shared.test_transport_remap_bitwise(evp, nranks)
+
+
+@pytest.mark.parametrize("nranks", [1, 2])
+def test_dynamics_and_advection_steps_bitwise_on_device(nranks):
+    """evp + transport_remap, six steps in a row on the device-resident state."""
+    shared.test_dynamics_and_advection_steps_bitwise(evp, nranks)
+
+
+def test_dynamics_and_advection_one_degree_tripole_on_device():
+    """The 1-degree tripole: 12 steps of evp (ndte = 120) + transport_remap, every step bit for bit against the oracle."""
+    from cice5_b200 import fixtures as fx
+    grid = fx.make_grid("tp1")
+    moved, total = shared._dynamics_steps(evp, grid, 12, 1, scenario="caps", ndte=120, dt_scale=2.0)
+    assert total > 1e-4
