@@ -701,6 +701,8 @@ static void evp_finish(const Dom *d, const evp_oracle_cfg *cfg, const Lists *L,
     }
 }
 
+#include "eap_oracle.inc"
+
 /* ------------------------------------------------------------------ */
 static double now_s(void)
 {
@@ -712,9 +714,10 @@ static double now_s(void)
 #define NB (d->nslabs)
 #define FOR_BLOCKS for (int b = 0; b < d->nslabs; ++b)
 
-/* evp(dt), ice_dyn_evp.F90:68-510 */
-int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
-                   evp_oracle_state *s, double dt, evp_oracle_stats *stats)
+/* evp(dt), ice_dyn_evp.F90:68-510; with E != NULL eap(dt), ice_dyn_eap.F90:66-486 (the same driver around
+ * stress_eap + stepa, no ice_HaloUpdate_stress) */
+static int run_impl(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
+                    evp_oracle_state *s, double dt, evp_oracle_stats *stats, evp_oracle_eap *E)
 {
     Dom dom, *d = &dom;
     Consts K;
@@ -778,6 +781,15 @@ int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
     }
     int **iceumask = split_i4(d, s->iceumask);
     double **fm = split_r8(d, s->fm);
+    /* eap: structure tensor (inout), its cell averages (inout), strain / stress / yield diagnostics (out) */
+    double **a11c[4] = {0, 0, 0, 0}, **a12c[4] = {0, 0, 0, 0}, **ea[11] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    if (E) {
+        double *src[11] = {E->a11, E->a12, E->e11, E->e12, E->e22, E->s11, E->s12, E->s22,
+                           E->yieldstress11, E->yieldstress12, E->yieldstress22};
+        if (cfg->revised_evp) return 7;
+        for (int c = 0; c < 4; ++c) { a11c[c] = split_r8(d, E->a11_c[c]); a12c[c] = split_r8(d, E->a12_c[c]); }
+        for (int f = 0; f < 11; ++f) ea[f] = split_r8(d, src[f]);
+    }
 
     /* outputs that the caller pre-zeroed via init_history_dyn (ice_flux.F90:639-673) are
      * taken as given so that values outside the ice lists pass through unchanged */
@@ -813,6 +825,7 @@ int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
         memset(divu[b], 0, sizeof(double) * n);
         memset(shear[b], 0, sizeof(double) * n);
         memset(prs_sig[b], 0, sizeof(double) * n);
+        if (E) for (int f = 2; f < 11; ++f) memset(ea[f][b], 0, sizeof(double) * n);   /* ice_dyn_eap.F90:174-182 */
         evp_prep1(d, cfg, aice[b], vice[b], vsno[b], tmask[b], strairxT[b], strairyT[b],
                   strairx[b], strairy[b], tmass[b], icetmask[b]);
     }
@@ -850,6 +863,11 @@ int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
                   strocnx[b], strocny[b], strintx[b], strinty[b], waterx[b], watery[b],
                   forcex[b], forcey[b], spb, smb, s12b, uvel_init[b], vvel_init[b],
                   uvel[b], vvel[b]);
+        if (E) {                                        /* ice_dyn_eap.F90:274-289: every cell of the block */
+            for (size_t q = 0; q < n; ++q)
+                if (icetmask[b][q] == 0)
+                    for (int c = 0; c < 4; ++c) { a11c[c][b][q] = p5; a12c[c][b][q] = c0; }
+        }
         /* ice_strength (:291): host-supplied values; 0 outside the block interior / list */
         memset(strength[b], 0, sizeof(double) * n);
         if (cfg->strength_masked) {
@@ -874,6 +892,14 @@ int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
         FOR_BLOCKS {
             double *spb[4], *smb[4], *s12b[4];
             for (int c = 0; c < 4; ++c) { spb[c] = sp[c][b]; smb[c] = sm[c][b]; s12b[c] = s12[c][b]; }
+            double *a11b[4] = {0, 0, 0, 0}, *a12b[4] = {0, 0, 0, 0};
+            if (E) {
+                for (int c = 0; c < 4; ++c) { a11b[c] = a11c[c][b]; a12b[c] = a12c[c][b]; }
+                stress_eap(d, &K, ksub, cfg->ndte, &L[b], E, uvel[b], vvel[b], dxt[b], dyt[b], dxhy[b], dyhx[b],
+                           cxp[b], cyp[b], cxm[b], cym[b], tarear[b], strength[b], a11b, a12b, spb, smb, s12b,
+                           shear[b], divu[b], ea[2][b], ea[3][b], ea[4][b], ea[5][b], ea[6][b], ea[7][b],
+                           ea[8][b], ea[9][b], ea[10][b], prs_sig[b], rdg_conv[b], str);
+            } else
             stress(d, &K, ksub, cfg->ndte, &L[b], uvel[b], vvel[b], dxt[b], dyt[b], dxhy[b],
                    dyhx[b], cxp[b], cyp[b], cxm[b], cym[b], tarear[b], tinyarea[b],
                    strength[b], spb, smb, s12b, shear[b], divu[b], prs_sig[b],
@@ -882,6 +908,8 @@ int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
                   watery[b], forcex[b], forcey[b], umassdti[b], fm[b], uarear[b],
                   strocnx[b], strocny[b], strintx[b], strinty[b], uvel_init[b],
                   vvel_init[b], uvel[b], vvel[b]);
+            if (E && ksub % 10 == 1)                    /* ice_dyn_eap.F90:408-421: only every 10th subcycle */
+                stepa(d, E->trig_mode, K.dtei, &L[b], ea[0][b], ea[1][b], a11b, a12b, spb, smb, s12b);
         }
         halo_r8_fld2(d, uvel, LOC_NECORNER, KIND_VECTOR, 0.0);            /* :397 */
         halo_r8_fld2(d, vvel, LOC_NECORNER, KIND_VECTOR, 0.0);
@@ -889,7 +917,7 @@ int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
     t_loop1 = now_s();
 
     /* ---- tripole stress symmetrisation :416-481 ---- */
-    if (cfg->grid_tripole) {
+    if (cfg->grid_tripole && !E) {                      /* eap has no stress halo */
         halo_stress(d, sp[0], sp[2]);  halo_stress(d, sp[2], sp[0]);
         halo_stress(d, sp[1], sp[3]);  halo_stress(d, sp[3], sp[1]);
         halo_stress(d, sm[0], sm[2]);  halo_stress(d, sm[2], sm[0]);
@@ -934,6 +962,15 @@ int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
     merge_r8(d, uvel_init, s->uvel_init); merge_r8(d, vvel_init, s->vvel_init);
     merge_r8(d, tmass, s->tmass); merge_r8(d, strength, s->strength);
     merge_i4(d, icetmask, s->icetmask);
+    if (E) {
+        double *dst[11] = {E->a11, E->a12, E->e11, E->e12, E->e22, E->s11, E->s12, E->s22,
+                           E->yieldstress11, E->yieldstress12, E->yieldstress22};
+        for (int c = 0; c < 4; ++c) {
+            merge_r8(d, a11c[c], E->a11_c[c]); merge_r8(d, a12c[c], E->a12_c[c]);
+            free_slabs(d, (void **)a11c[c]); free_slabs(d, (void **)a12c[c]);
+        }
+        for (int f = 0; f < 11; ++f) { merge_r8(d, ea[f], dst[f]); free_slabs(d, (void **)ea[f]); }
+    }
 
     /* ---- free ---- */
     {
@@ -952,6 +989,19 @@ int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
     }
     if (stats) stats->total_seconds = now_s() - t_start;
     return 0;
+}
+
+int evp_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g,
+                   evp_oracle_state *s, double dt, evp_oracle_stats *stats)
+{
+    return run_impl(cfg, g, s, dt, stats, NULL);
+}
+
+int eap_oracle_run(const evp_oracle_cfg *cfg, const evp_oracle_grid *g, evp_oracle_state *s, evp_oracle_eap *e,
+                   double dt, evp_oracle_stats *stats)
+{
+    if (!e) return 1;
+    return run_impl(cfg, g, s, dt, stats, e);
 }
 
 /* ------------------------------------------------------------------ */

@@ -60,7 +60,8 @@ def build(force: bool = False) -> str:
     if force or not os.path.exists(_SO) or \
             os.path.getmtime(_SO) < max(os.path.getmtime(os.path.join(_HERE, f))
                                         for f in ("evp_oracle.c", "strength_oracle.c", "strength_oracle.h", "remap_oracle.c", "remap_oracle.h",
-                                                  "../cice5_b200/csrc/evp_exp.h")):
+                                                  "eap_oracle.inc", "eap_oracle.h", "../cice5_b200/csrc/evp_exp.h",
+                                                  "../cice5_b200/csrc/evp_trig.h")):
         subprocess.run(["make", "-C", _HERE] + (["-B"] if force else []), check=True,
                        stdout=subprocess.DEVNULL)
     return _SO
@@ -365,3 +366,94 @@ def departure_points(dom, dt, uvel, vvel, dxu, dyu, HTN, HTE, l_dp_midpt=True, n
     if rc != 0:
         raise RuntimeError(f"remap_oracle_departure_points failed with status {rc}")
     return dpx, dpy, bool(ls.value), i_s.value, j_s.value
+
+
+# ---- EAP (kdyn = 2): oracle/eap_oracle.h ------------------------------------------------------------------------
+EAP_TABLE_SHAPE = (21, 41, 41)          # (na_yield, ny_yield, nx_yield): C order of Fortran (nx_yield, ny_yield, na_yield)
+EAP_TABLES = ("s11r", "s12r", "s22r", "s11s", "s12s", "s22s")
+EAP_CORNER = tuple(f"a11_{c}" for c in (1, 2, 3, 4)) + tuple(f"a12_{c}" for c in (1, 2, 3, 4))
+EAP_AVG = ("a11", "a12")
+EAP_OUT = ("e11", "e12", "e22", "s11", "s12", "s22", "yieldstress11", "yieldstress12", "yieldstress22")
+
+
+class EapS(C.Structure):
+    _fields_ = [(n, _DP) for n in EAP_TABLES] + [("a11_c", _DP * 4), ("a12_c", _DP * 4)] + \
+               [(n, _DP) for n in EAP_AVG + EAP_OUT] + [("trig_mode", C.c_int)]
+
+
+_eap_tables = None
+
+
+def eap_tables(ia=(1, 21), ix=(1, 41), iy=(1, 41)):
+    """init_eap's lookup tables (source/ice_dyn_eap.F90:557-618) as a dict of (21, 41, 41) arrays; the full tables
+    are computed once per process."""
+    global _eap_tables
+    full = ia == (1, 21) and ix == (1, 41) and iy == (1, 41)
+    if full and _eap_tables is not None:
+        return _eap_tables
+    t = {n: np.zeros(EAP_TABLE_SHAPE) for n in EAP_TABLES}
+    f = lib().eap_oracle_init_tables
+    f.restype = None
+    f(*[_dp(t[n]) for n in EAP_TABLES], *[C.c_int(v) for v in (*ia, *ix, *iy)])
+    if full:
+        _eap_tables = t
+    return t
+
+
+def eap_state(dom):
+    """Fresh EAP state as init_eap leaves it (:531-548): a11_k = 0.5, a12_k = 0, everything else 0."""
+    sh = (dom.ny + 2, dom.nx + 2)
+    e = {n: np.zeros(sh) for n in EAP_CORNER + EAP_AVG + EAP_OUT}
+    for c in (1, 2, 3, 4):
+        e[f"a11_{c}"][...] = 0.5
+    return e
+
+
+def _eap_struct(tables, eap, trig_mode):
+    E = EapS(trig_mode=trig_mode)
+    for n in EAP_TABLES:
+        setattr(E, n, _dp(tables[n]))
+    for c in range(4):
+        E.a11_c[c] = _dp(eap[f"a11_{c + 1}"])
+        E.a12_c[c] = _dp(eap[f"a12_{c + 1}"])
+    for n in EAP_AVG + EAP_OUT:
+        setattr(E, n, _dp(eap[n]))
+    return E
+
+
+def run_case_eap(case, eap, tables=None, nslabs=1, nthreads=0, dt_init=None, trig_mode=1, **cfg_kw):
+    """One eap(dt) call on a fixtures.Case + an EAP state dict (eap_state); updates case.io / case.out / eap in place."""
+    dom = case.dom
+    tables = eap_tables() if tables is None else tables
+    cfg = make_cfg(dom, case.ndte, case.dt if dt_init is None else dt_init, nslabs, nthreads, **cfg_kw)
+    gf = case.grid.f
+    g = GridS(**{n: _dp(gf[n]) for n in _GRID_R8}, tmask=_ip(gf["tmask"]), umask=_ip(gf["umask"]))
+    inp, io, out = case.inp, case.io, case.out
+    s = StateS()
+    for n in _STATE_IN:
+        setattr(s, n, _dp(inp["strength" if n == "strength_in" else n]))
+    s.uvel, s.vvel, s.fm = _dp(io["uvel"]), _dp(io["vvel"]), _dp(io["fm"])
+    for c in range(4):
+        s.stressp[c] = _dp(io[f"stressp_{c + 1}"])
+        s.stressm[c] = _dp(io[f"stressm_{c + 1}"])
+        s.stress12[c] = _dp(io[f"stress12_{c + 1}"])
+    s.iceumask = _ip(io["iceumask"])
+    for n in _STATE_OUT:
+        setattr(s, n, _dp(out["strength_out" if n == "strength" else n]))
+    s.icetmask = _ip(out["icetmask"])
+    E = _eap_struct(tables, eap, trig_mode)
+    st = Stats()
+    f = lib().eap_oracle_run
+    f.restype = C.c_int
+    rc = f(C.byref(cfg), C.byref(g), C.byref(s), C.byref(E), C.c_double(case.dt), C.byref(st))
+    if rc != 0:
+        raise RuntimeError(f"eap_oracle_run failed with status {rc}")
+    return st
+
+
+def trig(name):
+    """evp_trig.h's sin / cos / atan2 as Python callables."""
+    f = getattr(lib(), f"evp_oracle_{name}")
+    f.restype = C.c_double
+    f.argtypes = [C.c_double] * (2 if name == "atan2" else 1)
+    return f

@@ -282,7 +282,7 @@ def find_subroutine(lines: list, name: str) -> list:
     return lines[start:end]
 
 
-_DECL = re.compile(r"^(integer|real|logical|character|type\s*\()")
+_DECL = re.compile(r"^(integer|real|double precision|logical|character|type\s*\()")
 
 
 def split_top(s: str, sep=",") -> list:
