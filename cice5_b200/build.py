@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIBDIR = os.path.join(_HERE, "lib")
 SOURCES = ["evp_abi.cu"]
-HEADERS = ["evp_kernels.cuh", "evp_prep.cuh", "evp_subcycle_tma.cuh", "evp_loop_tma.cuh", "evp_strength.cuh", "evp_remap.cuh", "evp_exp.h"]
+HEADERS = ["evp_kernels.cuh", "evp_prep.cuh", "evp_subcycle_tma.cuh", "evp_loop_tma.cuh", "evp_strength.cuh", "evp_remap.cuh", "evp_eap.cuh", "evp_exp.h", "evp_trig.h"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 VARIANTS = {

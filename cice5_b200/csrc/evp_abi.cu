@@ -20,6 +20,7 @@
 #include "evp_loop_tma.cuh"
 #include "evp_strength.cuh"
 #include "evp_remap.cuh"
+#include "evp_eap.cuh"
 
 using namespace evp;
 
@@ -75,6 +76,9 @@ enum Plane {
     NPLANES
 };
 constexpr int kTGroup = G_HTE, kUGroup = W_VRELC;
+
+constexpr int kEapTablePitch = (kEapTableElems + 31) / 32 * 32;
+constexpr int kEapPlanes = 19;
 
 struct PeerBlob {                 // exchanged between the tasks of one node
     cudaIpcMemHandle_t arena;
@@ -160,6 +164,11 @@ struct evp_handle {
                                                           // whole remap: start, end [3, 4]; departure points [5..7]
     double tr_ms[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};     // departure kernels / halos, reconstruction kernel / halos, fluxes + update, whole remap
     bool have_ht = false;         // HTE / HTN were given: compact metric rows are possible
+    // EAP (kdyn = 2, evp_gpu_set_eap_tables): 6 lookup tables of kEapTableElems doubles (padded to kEapTablePitch), then 19
+    // planes of the arena's pitch: a11_1..4, a12_1..4, a11, a12, e11 e12 e22 s11 s12 s22 yieldstress11 / 12 / 22
+    double *eap = nullptr;
+    bool eap_tables_set = false;
+    double *eap_plane(int p) const { return eap + 6 * (size_t)kEapTablePitch + (size_t)p * plane_elems; }
     evp_stats_t stats;
     unsigned long long h_counts[2];
 
@@ -334,7 +343,7 @@ const char *evp_gpu_strerror(int status)
         case EVP_OK: return "ok";
         case EVP_ERR_ARG: return "evp_gpu: invalid argument (null pointer or inconsistent block sizes)";
         case EVP_ERR_UNSUPPORTED:
-            return "evp_gpu: unsupported configuration (needs kdyn=1 (EVP), "
+            return "evp_gpu: unsupported configuration (needs kdyn=1 (EVP) or 2 (EAP, classic relaxation), "
                    "tripole only with cyclic E-W, nranks <= 8, slabs >= 2 columns)";
         case EVP_ERR_CUDA: return "evp_gpu: CUDA runtime error (see evp_gpu_last_cuda_error)";
         case EVP_ERR_STATE: return "evp_gpu: call order violated (init -> set_grid -> [set_peers] -> run)";
@@ -360,7 +369,8 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
 {
     if (!cfg || !out) return EVP_ERR_ARG;
     *out = nullptr;
-    if (cfg->kdyn != 1 || cfg->revised_evp < 0 || cfg->revised_evp > 1) return EVP_ERR_UNSUPPORTED;
+    if ((cfg->kdyn != 1 && cfg->kdyn != 2) || cfg->revised_evp < 0 || cfg->revised_evp > 1) return EVP_ERR_UNSUPPORTED;
+    if (cfg->kdyn == 2 && cfg->revised_evp) return EVP_ERR_UNSUPPORTED;
     if (cfg->revised_evp && cfg->nranks > 1 && !(cfg->xmin > 0.0)) return EVP_ERR_ARG;   // needs the GLOBAL xmin
     if (cfg->nranks < 1 || cfg->nranks > kMaxRanks || cfg->rank < 0 || cfg->rank >= cfg->nranks)
         return EVP_ERR_UNSUPPORTED;
@@ -408,6 +418,8 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
         h->use_tma = !(kv && strcmp(kv, "sweep") == 0);
         const char *lv = getenv("EVP_B200_LOOP");            // "1" (default) | "0": one launch per subcycle
         h->use_loop = h->use_tma && !(lv && strcmp(lv, "0") == 0);
+        // EAP: the register-sweep kernel with stress_eap as its cell function (evp_eap.cuh), one launch per subcycle
+        if (cfg->kdyn == 2) h->use_tma = h->use_loop = false;
     }
     set_evp_parameters(*cfg, h->k);
     h->nxb = cfg->nx_block; h->nyb = cfg->ny_block;
@@ -508,6 +520,7 @@ int evp_gpu_finalize(evp_handle_t *h)
     if (h->tr) cudaFree(h->tr);
     if (h->rc) cudaFree(h->rc);
     if (h->st) cudaFree(h->st);
+    if (h->eap) cudaFree(h->eap);
     for (auto &ev : h->tev) if (ev) cudaEventDestroy(ev);
     if (h->stage) cudaFree(h->stage);
     if (h->arena) cudaFree(h->arena);
@@ -1047,6 +1060,17 @@ void fill_loop_args(const evp_handle *h, int from_parity, int inbox_buf, LoopArg
     a.k = h->k;
 }
 
+void fill_eap_args(const evp_handle *h, EapArgs &e)
+{
+    memset(&e, 0, sizeof(e));
+    for (int t = 0; t < 6; ++t) e.tab[t] = h->eap + (size_t)t * kEapTablePitch;
+    for (int q = 0; q < 4; ++q) { e.a11c[q] = h->eap_plane(q); e.a12c[q] = h->eap_plane(4 + q); }
+    e.a11 = h->eap_plane(8); e.a12 = h->eap_plane(9);
+    for (int q = 0; q < 9; ++q) e.out[q] = h->eap_plane(10 + q);
+    // dtei = c1 / dte, dte = dt / ndte with the dt of init_evp (ice_dyn_shared.F90:209-210)
+    e.dtei = 1.0 / (h->cfg.dt_init / (double)h->cfg.ndte);
+}
+
 // all ndte subcycles as one persistent kernel (evp_loop_tma.cuh): work items ordered by (subcycle, item),
 // per-tile dependency counters instead of launch boundaries and cross-rank barriers
 void add_loop(Builder &B, int from_parity, int nsteps)
@@ -1165,6 +1189,23 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
         }
         const int strips = (g.nxl + kUColsPerWarp - 1) / kUColsPerWarp;
         dim3 grid((strips + kWarpsPerBlock - 1) / kWarpsPerBlock, (g.ny + a.rows_per_chunk - 1) / a.rows_per_chunk);
+        if (h->cfg.kdyn == 2) {
+            // eap (source/ice_dyn_eap.F90:340-421): stress_eap + stepu fused, then stepa on every 10th subcycle (:408)
+            // from the stresses this subcycle wrote
+            EapArgs e;
+            fill_eap_args(h, e);
+            auto kern2 = last ? eap_subcycle_kernel<true> : eap_subcycle_kernel<false>;
+            kern2<<<grid, kWarpsPerBlock * 32, 0, L.s()>>>(a, e);
+            ++L.n;
+            if (ksub % 10 == 1) {
+                dim3 g2((g.nxl + 1 + 127) / 128, g.ny + 1);
+                eap_stepa_kernel<<<g2, 128, 0, L.s()>>>(e, g.nxl, g.ny, g.ld, h->ldm, h->mask(),
+                                                        h->plane(from_parity ? S_STRA : S_STRB), h->plane_elems);
+                ++L.n;
+            }
+            CK(cudaGetLastError());
+            return EVP_OK;
+        }
         auto kern1 = h->cfg.revised_evp ? (last ? evp_subcycle_kernel<true, true> : evp_subcycle_kernel<false, true>)
                                         : (last ? evp_subcycle_kernel<true, false> : evp_subcycle_kernel<false, false>);
         kern1<<<grid, kWarpsPerBlock * 32, 0, L.s()>>>(a);
@@ -1209,6 +1250,8 @@ void build_program(evp_handle *h, double dt, Program &P)
         CK(cudaMemsetAsync(h->plane(O_STRAIRX), 0, pb * 17, s));   // all output planes
         CK(cudaMemsetAsync(h->plane(S_FM), 0, pb, s));
         CK(cudaMemsetAsync(h->counts(), 0, 16, s));
+        // eap zeroes its strain / stress / yield diagnostics too (source/ice_dyn_eap.F90:166-182)
+        if (h->cfg.kdyn == 2) CK(cudaMemsetAsync(h->eap_plane(10), 0, pb * 9, s));
         // ghost mailbox of the loop kernel: its flags count subcycles from 1 in every call (the neighbours write it only
         // inside their loop kernels, several cross-rank barriers after this point)
         if (h->cfg.nranks > 1 && loop_mode(h)) CK(cudaMemsetAsync(h->ll_box(), 0, h->ll_bytes(), s));
@@ -1287,6 +1330,12 @@ void build_program(evp_handle *h, double dt, Program &P)
             prep2_kernel<<<grid2d(h), 128, 0, s>>>(a);
             ++L.n;
         }
+        if (cfg.kdyn == 2) {   // structure tensor back to isotropic where there is no ice (ice_dyn_eap.F90:274-289)
+            EapArgs e;
+            fill_eap_args(h, e);
+            eap_reset_kernel<<<grid2d(h), 128, 0, s>>>(e, h->nxb, h->nyb, h->ld, h->plane(W_ICETMASK));
+            ++L.n;
+        }
         if (h->use_tma) {   // per-strip row activity for the TMA producer
             dim3 grid(h->tstrips, (h->g.ny + 4 + 3) / 4);
             tile_flags_kernel<<<grid, 128, 0, s>>>(h->mask(), h->ldm, h->g.nxl, h->g.ny, h->tstrips, h->tflags(),
@@ -1347,7 +1396,7 @@ void build_program(evp_handle *h, double dt, Program &P)
     B.op([h](Launcher &L) { CK(cudaEventRecord(h->ev[2], L.s())); return EVP_OK; });
 
     // ---- tripole stress symmetrisation (:416-481) ----
-    if (cfg.grid_tripole) {
+    if (cfg.grid_tripole && cfg.kdyn != 2) {      // eap has no ice_HaloUpdate_stress
         const int S = par ? S_STRB : S_STRA;
         for (int f = 0; f < 3; ++f) {
             const int b = S + 4 * f;
@@ -1452,6 +1501,7 @@ int evp_gpu_compute(evp_handle_t *h, double dt)
 {
     if (!h) return EVP_ERR_ARG;
     if (!h->grid_set || !h->uploaded || !h->peers_set) return EVP_ERR_STATE;
+    if (h->cfg.kdyn == 2 && !h->eap_tables_set) return EVP_ERR_STATE;
     if (!(dt > 0.0)) return EVP_ERR_ARG;
     CK(cudaSetDevice(h->cfg.device));
     Program P;
@@ -1474,6 +1524,7 @@ int evp_gpu_compute_group(evp_handle_t **hs, int n, double dt)
     for (int r = 0; r < n; ++r) {
         if (!hs[r] || hs[r]->cfg.nranks != n || hs[r]->cfg.rank != r) return EVP_ERR_ARG;
         if (!hs[r]->grid_set || !hs[r]->uploaded || !hs[r]->peers_set) return EVP_ERR_STATE;
+        if (hs[r]->cfg.kdyn == 2 && !hs[r]->eap_tables_set) return EVP_ERR_STATE;
         if (hs[r]->cfg.device != hs[0]->cfg.device) return EVP_ERR_UNSUPPORTED;
     }
     if (!(dt > 0.0)) return EVP_ERR_ARG;
@@ -2341,6 +2392,71 @@ int evp_gpu_principal_stress(evp_handle_t *h, double *sig1, double *sig2)
     h->batch_dst.clear();
     TRY(B.r8(W_1, sig1));
     TRY(B.r8(W_2, sig2));
+    TRY(B.flush());
+    CK(cudaStreamSynchronize(h->stream));
+    return EVP_OK;
+}
+
+// ---- EAP (kdyn = 2): lookup tables, structure tensor, diagnostics ---------------------------------------------------
+int evp_gpu_set_eap_tables(evp_handle_t *h, const evp_eap_tables_t *t)
+{
+    if (!h || !t || !t->s11r || !t->s12r || !t->s22r || !t->s11s || !t->s12s || !t->s22s) return EVP_ERR_ARG;
+    if (h->cfg.kdyn != 2) return EVP_ERR_STATE;
+    CK(cudaSetDevice(h->cfg.device));
+    if (!h->eap) {
+        const size_t elems = 6 * (size_t)kEapTablePitch + (size_t)kEapPlanes * h->plane_elems;
+        CK(cudaMalloc(&h->eap, elems * sizeof(double)));
+        CK(cudaMemsetAsync(h->eap, 0, elems * sizeof(double), h->stream));
+        // init_eap's state (source/ice_dyn_eap.F90:531-548): a11_k = p5, a12_k = c0, the diagnostics zero
+        fill_plane_kernel<<<(unsigned)((4 * h->plane_elems + 255) / 256), 256, 0, h->stream>>>(h->eap_plane(0), 0.5,
+                                                                                            4 * h->plane_elems);
+        CK(cudaGetLastError());
+    }
+    const double *src[6] = {t->s11r, t->s12r, t->s22r, t->s11s, t->s12s, t->s22s};
+    for (int q = 0; q < 6; ++q)
+        CK(cudaMemcpyAsync(h->eap + (size_t)q * kEapTablePitch, src[q], kEapTableElems * sizeof(double),
+                           cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    h->eap_tables_set = true;
+    return EVP_OK;
+}
+
+int evp_gpu_upload_eap(evp_handle_t *h, const evp_eap_state_t *st)
+{
+    if (!h || !st) return EVP_ERR_ARG;
+    if (h->cfg.kdyn != 2 || !h->eap) return EVP_ERR_STATE;
+    CK(cudaSetDevice(h->cfg.device));
+    for (int q = 0; q < 4; ++q) {
+        if (st->a11[q]) TRY(h2d_any(h, h->eap_plane(q), st->a11[q], 0));
+        if (st->a12[q]) TRY(h2d_any(h, h->eap_plane(4 + q), st->a12[q], 0));
+    }
+    if (st->a11_avg) TRY(h2d_any(h, h->eap_plane(8), st->a11_avg, 0));
+    if (st->a12_avg) TRY(h2d_any(h, h->eap_plane(9), st->a12_avg, 0));
+    TRY(h2d_flush(h));
+    CK(cudaStreamSynchronize(h->stream));
+    return EVP_OK;
+}
+
+int evp_gpu_download_eap(evp_handle_t *h, evp_eap_state_t *st, evp_eap_out_t *out)
+{
+    if (!h) return EVP_ERR_ARG;
+    if (h->cfg.kdyn != 2 || !h->eap) return EVP_ERR_STATE;
+    CK(cudaSetDevice(h->cfg.device));
+    D2HBatch B{h, {}};
+    h->batch_dst.clear();
+    if (st) {
+        for (int q = 0; q < 4; ++q) {
+            TRY(B.add(h->eap_plane(q), st->a11[q], 0));
+            TRY(B.add(h->eap_plane(4 + q), st->a12[q], 0));
+        }
+        TRY(B.add(h->eap_plane(8), st->a11_avg, 0));
+        TRY(B.add(h->eap_plane(9), st->a12_avg, 0));
+    }
+    if (out) {
+        double *dst[9] = {out->e11, out->e12, out->e22, out->s11, out->s12, out->s22, out->yieldstress11,
+                          out->yieldstress12, out->yieldstress22};
+        for (int q = 0; q < 9; ++q) TRY(B.add(h->eap_plane(10 + q), dst[q], 0));
+    }
     TRY(B.flush());
     CK(cudaStreamSynchronize(h->stream));
     return EVP_OK;

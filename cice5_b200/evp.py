@@ -63,6 +63,26 @@ class OutS(C.Structure):
     _fields_ = [(n, _DP) for n in OUT_R8] + [("icetmask", _IP)]
 
 
+# EAP (kdyn = 2): the module variables of source/ice_dyn_eap.F90:31-57
+EAP_TABLES = ("s11r", "s12r", "s22r", "s11s", "s12s", "s22s")
+EAP_TABLE_SHAPE = (21, 41, 41)      # C order of Fortran (nx_yield, ny_yield, na_yield)
+EAP_CORNER = tuple(f"a11_{c}" for c in (1, 2, 3, 4)) + tuple(f"a12_{c}" for c in (1, 2, 3, 4))
+EAP_AVG = ("a11", "a12")
+EAP_OUT = ("e11", "e12", "e22", "s11", "s12", "s22", "yieldstress11", "yieldstress12", "yieldstress22")
+
+
+class EapTablesS(C.Structure):
+    _fields_ = [(n, _DP) for n in EAP_TABLES]
+
+
+class EapStateS(C.Structure):
+    _fields_ = [("a11", _DP * 4), ("a12", _DP * 4), ("a11_avg", _DP), ("a12_avg", _DP)]
+
+
+class EapOutS(C.Structure):
+    _fields_ = [(n, _DP) for n in EAP_OUT]
+
+
 class Stats(C.Structure):
     _fields_ = [("prep_ms", C.c_double), ("loop_ms", C.c_double), ("finish_ms", C.c_double),
                 ("total_ms", C.c_double), ("active_t_cells", C.c_longlong),
@@ -83,7 +103,7 @@ EXPORTS = ("evp_gpu_init", "evp_gpu_set_grid", "evp_gpu_run", "evp_gpu_upload", 
            "evp_gpu_get_transport_timing", "evp_gpu_horizontal_remap_compute", "evp_gpu_horizontal_remap_group",
            "evp_gpu_horizontal_remap_fetch", "evp_gpu_horizontal_remap", "evp_gpu_transport_remap_upload",
            "evp_gpu_transport_remap_compute", "evp_gpu_transport_remap_group", "evp_gpu_transport_remap_fetch",
-           "evp_gpu_transport_remap")
+           "evp_gpu_transport_remap", "evp_gpu_set_eap_tables", "evp_gpu_upload_eap", "evp_gpu_download_eap")
 REMAP_MAX_TRACE, REMAP_MAX_PARENTS = 128, 16     # EVP_REMAP_MAX_TRACE, EVP_REMAP_MAX_PARENTS of include/evp_b200.h
 STATIC_MAX_CELLS = 131072       # EVP_STATIC_MAX_CELLS of include/evp_b200.h
 
@@ -412,6 +432,40 @@ class EvpGpu:
         self._check(self.lib.evp_gpu_construct_fields_compute(self._h))
         return self.construct_fields_fetch()
 
+    # -- EAP (kdyn = 2)
+    def set_eap_tables(self, tables: dict):
+        """init_eap's lookup tables s11r ... s22s, each (21, 41, 41) = Fortran (nx_yield, ny_yield, na_yield)."""
+        for n in EAP_TABLES:
+            if tables[n].shape != EAP_TABLE_SHAPE:
+                raise EvpError(f"table {n} has shape {tables[n].shape}, expected {EAP_TABLE_SHAPE}")
+        t = EapTablesS(**{n: _dp(tables[n]) for n in EAP_TABLES})
+        self._check(self.lib.evp_gpu_set_eap_tables(self._h, C.byref(t)))
+
+    @staticmethod
+    def _eap_state_struct(eap):
+        st = EapStateS()
+        for c in range(4):
+            if eap.get(f"a11_{c + 1}") is not None:
+                st.a11[c] = _dp(eap[f"a11_{c + 1}"])
+            if eap.get(f"a12_{c + 1}") is not None:
+                st.a12[c] = _dp(eap[f"a12_{c + 1}"])
+        if eap.get("a11") is not None:
+            st.a11_avg = _dp(eap["a11"])
+        if eap.get("a12") is not None:
+            st.a12_avg = _dp(eap["a12"])
+        return st
+
+    def upload_eap(self, eap: dict):
+        """The structure tensor a11_1..4, a12_1..4 (and the averages a11, a12) of this block; missing keys stay."""
+        st = self._eap_state_struct(eap)
+        self._check(self.lib.evp_gpu_upload_eap(self._h, C.byref(st)))
+
+    def download_eap(self, eap: dict):
+        """Fills the arrays of `eap` that are present: structure tensor, averages and the EAP_OUT diagnostics."""
+        st = self._eap_state_struct(eap)
+        out = EapOutS(**{n: _dp(eap[n]) for n in EAP_OUT if eap.get(n) is not None})
+        self._check(self.lib.evp_gpu_download_eap(self._h, C.byref(st), C.byref(out)))
+
     def stats(self) -> Stats:
         st = Stats()
         self._check(self.lib.evp_gpu_get_stats(self._h, C.byref(st)))
@@ -492,6 +546,20 @@ def run_case(case, strict=True, **kw):
         e.close()
 
 
+def run_case_eap(case, eap, tables, strict=True, **kw):
+    """One eap(dt) call (kdyn = 2) on a fixtures.Case and an EAP state dict (structure tensor in, every EAP field out)."""
+    e = EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=strict, kdyn=2, **kw)
+    try:
+        e.set_grid(case.grid.f)
+        e.set_eap_tables(tables)
+        e.upload_eap(eap)
+        e.evp(case.dt, case.inp, case.io, case.out)
+        e.download_eap(eap)
+        return e.stats()
+    finally:
+        e.close()
+
+
 class EvpGroup:
     """All x-slabs of one decomposition driven from one process (one device): the host-side mirror
     of `nranks` tasks each calling evp(dt) on its own block.  Global-with-ghost arrays in and out."""
@@ -547,6 +615,23 @@ class EvpGroup:
         for k in out:
             if out[k] is not None:
                 out[k][...] = self._fx.unslab([p[1][k] for p in parts])
+
+    def set_eap_tables(self, tables):
+        for e in self.ranks:
+            e.set_eap_tables(tables)
+
+    def upload_eap(self, eap):
+        for r, e in enumerate(self.ranks):
+            e.upload_eap(self._slabs(eap, r))
+
+    def download_eap(self, eap):
+        parts = []
+        for r, e in enumerate(self.ranks):
+            se = self._slabs(eap, r)
+            e.download_eap(se)
+            parts.append(se)
+        for k in eap:
+            eap[k][...] = self._fx.unslab([p[k] for p in parts])
 
     def set_transport_grid(self, f):
         for r, e in enumerate(self.ranks):

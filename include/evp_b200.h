@@ -29,7 +29,7 @@ typedef struct evp_handle evp_handle_t;
 enum {
     EVP_OK = 0,
     EVP_ERR_ARG = 1,          /* null pointer / inconsistent sizes                      */
-    EVP_ERR_UNSUPPORTED = 2,  /* kdyn != 1, unsupported boundary type / decomposition   */
+    EVP_ERR_UNSUPPORTED = 2,  /* kdyn not 1 / 2, unsupported boundary type / decomposition */
     EVP_ERR_CUDA = 3,         /* a CUDA runtime call failed (see evp_gpu_last_cuda_error) */
     EVP_ERR_STATE = 4,        /* call order violated (e.g. run before set_grid)         */
     EVP_ERR_NO_DEVICE = 5,    /* no usable CUDA device: there is NO CPU fallback        */
@@ -47,7 +47,8 @@ typedef struct {
     int rank, nranks;           /* x-slab index / count (slenderX1-style decomposition)        */
     int device;                 /* CUDA device ordinal for this task                           */
     int ndte;                   /* dynamics_nml ndte (ice_dyn_shared.F90:33)                   */
-    int kdyn;                   /* must be 1 (EVP)                                             */
+    int kdyn;                   /* 1: EVP; 2: EAP (ice_dyn_eap.F90, classic relaxation only; needs
+                                   evp_gpu_set_eap_tables before the first call)                */
     int revised_evp;            /* 0: classic EVP (ice_dyn_shared.F90:239-242); 1: revised EVP
                                    (Bouillon et al. 2013, :230-233,492-504,715,732-734)         */
     int ew_boundary;            /* EVP_EW_*   (ice_domain.F90 ew_boundary_type)                 */
@@ -285,6 +286,36 @@ int evp_gpu_synchronize(evp_handle_t *h);
  * source/ice_history.F90:1921) from the device-resident stressp_1, stressm_1, stress12_1, prs_sig of
  * the last evp: sig1, sig2 over the whole block, spval_dbl = 1e30 where prs_sig <= puny. */
 int evp_gpu_principal_stress(evp_handle_t *h, double *sig1, double *sig2);
+
+/* EAP, the elastic-anisotropic-plastic rheology (kdyn = 2): `eap(dt)`, source/ice_dyn_eap.F90:66-486,
+ * called by step_dynamics in place of evp (source/ice_step_mod.F90:1119-1124).  It shares evp_prep1 / evp_prep2 / stepu /
+ * evp_finish and the halo pattern with evp, so a handle initialised with kdyn = 2 is driven by the same evp_gpu_run /
+ * upload / compute / download calls with the same arrays; stress_eap (:1052-1467, update_stress_rdg :1474-1658) replaces
+ * stress, stepa (:1664-1787, calc_ffrac :1795-1864) runs on every 10th subcycle (:408), and there is no
+ * ice_HaloUpdate_stress.  What is new at the boundary are the module variables of ice_dyn_eap (:31-57):
+ *   tables   s11r ... s22s (nx_yield, ny_yield, na_yield) = (41, 41, 21), Fortran order, as init_eap computed them on the
+ *            host (:557-618).  Once, before the first call; they are an input, the device does not recompute them.
+ *   state    a11_1..4, a12_1..4 (restart fields, read_restart_eap :1908) and the cell averages a11, a12 (history): device
+ *            resident, initialised as init_eap does (a11_k = 0.5, everything else 0, :531-548).  upload after a restart
+ *            was read, download when a restart / history file is written; NULL pointers are skipped.
+ *   out      e11, e12, e22, s11, s12, s22, yieldstress11 / 12 / 22 (history), zeroed at the start of every call
+ *            (:166-182).  rdg_shear stays 0 under EAP (its statement is commented out, :1283-1285), prs_sig = strength.
+ * The intrinsics atan2 / sin / cos of update_stress_rdg and calc_ffrac are cice5_b200/csrc/evp_trig.h (error < 1.5 ulp): a
+ * Fortran processor is free in their last bit, and the table look-up (`int((x-piq-pi)*invdx)`, :1599-1601) can turn a
+ * last-bit difference into the neighbouring table entry.  Every entry point returns EVP_ERR_STATE on a kdyn = 1 handle. */
+typedef struct {
+    const double *s11r, *s12r, *s22r, *s11s, *s12s, *s22s;
+} evp_eap_tables_t;
+typedef struct {
+    double *a11[4], *a12[4];      /* a11_1..4, a12_1..4: corners ne, nw, sw, se                    */
+    double *a11_avg, *a12_avg;    /* a11, a12                                                       */
+} evp_eap_state_t;
+typedef struct {
+    double *e11, *e12, *e22, *s11, *s12, *s22, *yieldstress11, *yieldstress12, *yieldstress22;
+} evp_eap_out_t;
+int evp_gpu_set_eap_tables(evp_handle_t *h, const evp_eap_tables_t *t);
+int evp_gpu_upload_eap(evp_handle_t *h, const evp_eap_state_t *st);
+int evp_gpu_download_eap(evp_handle_t *h, evp_eap_state_t *st, evp_eap_out_t *out);
 
 /* No counterpart in the reference.  principal_stress (the same kernel
  * as evp_gpu_principal_stress) for callers that must not allocate -- code under CUDA graph capture, tight serving
