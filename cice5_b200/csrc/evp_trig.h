@@ -91,6 +91,11 @@ EVP_EXP_FN void evp_sincos(double x, double *s, double *c)
         *c = cos(x);
         return;
     }
+    if (x == 0.0) {                    /* sin(+-0) = +-0 */
+        *s = x;
+        *c = 1.0;
+        return;
+    }
     n = evp_rem_pio2(x, &r, &rl);
     sk = evp_sin_k(r, rl);
     ck = evp_cos_k(r, rl);

@@ -35,7 +35,7 @@
 
       implicit none
       private
-      public :: evp, evp_gpu_fetch_all, evp_gpu_state_changed
+      public :: evp, evp_gpu_fetch_all, evp_gpu_state_changed, evp_gpu_get_handle
       save
 
       type, bind(C) :: evp_config_t
@@ -310,6 +310,16 @@
 #endif
       ready = .true.
       end subroutine evp_gpu_setup
+
+!=======================================================================
+! The handle, set up on first use: for the EAP shim (ice_dyn_eap_gpu.F90), which hands the lookup tables and the
+! structure tensor to the same handle (cfg%kdyn = 2) before its first call of evp.
+      function evp_gpu_get_handle(dt) result(h)
+      real (kind=dbl_kind), intent(in) :: dt
+      type(c_ptr) :: h
+      if (.not. ready) call evp_gpu_setup(dt)
+      h = handle
+      end function evp_gpu_get_handle
 
 !=======================================================================
 ! == subroutine evp(dt) of the reference (source/ice_dyn_evp.F90:68)

@@ -65,7 +65,9 @@ def test_no_gpu_means_loud_failure(have_gpu):
 
 def test_argument_validation_precedes_device_probe():
     with pytest.raises(evp.EvpError, match="unsupported"):
-        evp.EvpGpu(100, 116, 120, 3600.0, kdyn=2)
+        evp.EvpGpu(100, 116, 120, 3600.0, kdyn=3)
+    with pytest.raises(evp.EvpError, match="unsupported"):
+        evp.EvpGpu(100, 116, 120, 3600.0, kdyn=2, revised_evp=True)      # not a configuration of the reference's eap
     with pytest.raises(evp.EvpError, match="invalid argument"):
         # revised EVP split over tasks needs the global xmin (ice_dyn_shared.F90:220-223)
         evp.EvpGpu(100, 116, 120, 3600.0, revised_evp=True, nranks=2, rank=0)

@@ -296,3 +296,65 @@ def test_wet_pole_tripole_velocity_fold_skips_the_pole_pair():
         i = np.arange(2, nx // 2)
         assert np.array_equal(top[i - 1], -top[nx - i - 1])
         assert top[0] != 0.0 and top[0] != -top[nx - 2]
+
+
+def test_shared_trig_accuracy_against_multiprecision():
+    """evp_trig.h (the sin / cos / atan2 the EAP kernels and the oracle share) against 200-bit arithmetic:
+    sin, cos < 1 ulp for |x| <= 1e5, atan2 < 1.5 ulp; C's conventions for signed zeros and the axes."""
+    import math
+    mp = pytest.importorskip("mpmath")
+    mp.mp.prec = 200
+    fsin, fcos, fatan2 = orc.trig("sin"), orc.trig("cos"), orc.trig("atan2")
+
+    def ulps(got, exact):
+        return float(abs(mp.mpf(got) - exact) / math.ulp(float(exact)))
+
+    r = np.random.default_rng(7)
+    xs = np.concatenate([r.uniform(-4, 4, 4000), r.uniform(-1e5, 1e5, 1500), r.uniform(-1e-3, 1e-3, 500),
+                         [k * math.pi / 4 for k in range(-16, 17)]])
+    worst_s = max(ulps(fsin(float(x)), mp.sin(float(x))) for x in xs)
+    worst_c = max(ulps(fcos(float(x)), mp.cos(float(x))) for x in xs)
+    assert worst_s < 1.0 and worst_c < 1.0, (worst_s, worst_c)
+    worst_a = 0.0
+    for _ in range(6000):
+        y, x = float(r.normal() * 10 ** r.uniform(-6, 6)), float(r.normal() * 10 ** r.uniform(-6, 6))
+        worst_a = max(worst_a, ulps(fatan2(y, x), mp.atan2(y, x)))
+    for _ in range(6000):
+        y, x = float(r.uniform(-1, 1)), float(r.uniform(-1, 1))
+        worst_a = max(worst_a, ulps(fatan2(y, x), mp.atan2(y, x)))
+    assert worst_a < 1.5, worst_a
+    for y, x in ((0.0, 1.0), (-0.0, 1.0), (0.0, -1.0), (-0.0, -1.0), (0.0, 0.0), (-0.0, 0.0), (0.0, -0.0), (-0.0, -0.0),
+                 (1.0, 0.0), (-1.0, 0.0), (1.0, -0.0), (1.0, 1.0), (1.0, -1.0), (-1.0, -1.0), (-1.0, 1.0)):
+        g, e = fatan2(y, x), math.atan2(y, x)
+        assert g == e and math.copysign(1.0, g) == math.copysign(1.0, e), (y, x, g, e)
+    assert fsin(0.0) == 0.0 and fcos(0.0) == 1.0 and math.copysign(1.0, fsin(-0.0)) == -1.0
+    # the one constant of update_stress_rdg that goes through sin: sin(pi2/c12) (ice_dyn_eap.F90:1525)
+    assert fsin(2.0 * 3.14159265358979323846 / 12.0) == math.sin(2.0 * 3.14159265358979323846 / 12.0)
+
+
+@pytest.mark.parametrize("slabs", [2, 4])
+def test_eap_decomposition_independence_and_invariants(slabs):
+    """eap(dt) of the oracle: x-slabs give the bits of one block; the structure tensor stays a valid one
+    (eigenvalues of [[a11, a12], [a12, 1 - a11]] in [0, 1]) and isotropic where there is no ice."""
+    grid = fx.synthetic_tripole(96, 40, wet_poles=True)
+    case = fx.make_case(grid, "full", ndte=21, dt=3600.0)
+    tables = orc.eap_tables()
+    res = []
+    for ns in (1, slabs):
+        c = clone_case(case)
+        e = orc.eap_state(case.dom)
+        orc.run_case_eap(c, e, tables, nslabs=ns)
+        res.append((c, e))
+    (c1, e1), (c2, e2) = res
+    for n in ("uvel", "vvel", "stressp_1", "stress12_3"):
+        assert np.array_equal(phys(c1.io[n]), phys(c2.io[n])), n
+    for n in orc.EAP_CORNER + orc.EAP_AVG + orc.EAP_OUT:
+        assert np.array_equal(phys(e1[n]), phys(e2[n])), n
+    ice = phys(c1.out["icetmask"]) == 1
+    assert ice.any() and (~ice).any()
+    for c in (1, 2, 3, 4):
+        a11, a12 = phys(e1[f"a11_{c}"]), phys(e1[f"a12_{c}"])
+        lam = 0.5 + np.sqrt((a11 - 0.5) ** 2 + a12 ** 2)
+        assert (lam <= 1.0 + 1e-12).all() and (a11[~ice] == 0.5).all() and (a12[~ice] == 0.0).all()
+        assert (a11[ice] != 0.5).any()            # stepa moved it (subcycles 1, 11, 21)
+    assert np.abs(phys(c1.io["uvel"])).max() < 5.0
