@@ -78,7 +78,7 @@ enum Plane {
 constexpr int kTGroup = G_HTE, kUGroup = W_VRELC;
 
 constexpr int kEapTablePitch = (kEapTableElems + 31) / 32 * 32;
-constexpr int kEapPlanes = 19;
+constexpr int kEapPlanes = 51;   // 8 tensor + 2 averages + 9 diagnostics + 16 rotation + 12 yield stresses + 4 alphar
 
 struct PeerBlob {                 // exchanged between the tasks of one node
     cudaIpcMemHandle_t arena;
@@ -164,8 +164,9 @@ struct evp_handle {
                                                           // whole remap: start, end [3, 4]; departure points [5..7]
     double tr_ms[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};     // departure kernels / halos, reconstruction kernel / halos, fluxes + update, whole remap
     bool have_ht = false;         // HTE / HTN were given: compact metric rows are possible
-    // EAP (kdyn = 2, evp_gpu_set_eap_tables): 6 lookup tables of kEapTableElems doubles (padded to kEapTablePitch), then 19
-    // planes of the arena's pitch: a11_1..4, a12_1..4, a11, a12, e11 e12 e22 s11 s12 s22 yieldstress11 / 12 / 22
+    // EAP (kdyn = 2, evp_gpu_set_eap_tables): 6 lookup tables of kEapTableElems doubles (padded to kEapTablePitch), then
+    // kEapPlanes planes of the arena's pitch: a11_1..4, a12_1..4, a11, a12, e11 e12 e22 s11 s12 s22 yieldstress11 / 12 / 22,
+    // and the work planes of the two-stage subcycle (rotation of the tensor, yield stresses, alphar; evp_eap.cuh)
     double *eap = nullptr;
     bool eap_tables_set = false;
     double *eap_plane(int p) const { return eap + 6 * (size_t)kEapTablePitch + (size_t)p * plane_elems; }
@@ -1067,6 +1068,9 @@ void fill_eap_args(const evp_handle *h, EapArgs &e)
     for (int q = 0; q < 4; ++q) { e.a11c[q] = h->eap_plane(q); e.a12c[q] = h->eap_plane(4 + q); }
     e.a11 = h->eap_plane(8); e.a12 = h->eap_plane(9);
     for (int q = 0; q < 9; ++q) e.out[q] = h->eap_plane(10 + q);
+    for (int q = 0; q < 16; ++q) e.rot[q] = h->eap_plane(19 + q);
+    for (int q = 0; q < 12; ++q) e.yld[q] = h->eap_plane(35 + q);
+    for (int q = 0; q < 4; ++q) e.alphar[q] = h->eap_plane(47 + q);
     // dtei = c1 / dte, dte = dt / ndte with the dt of init_evp (ice_dyn_shared.F90:209-210)
     e.dtei = 1.0 / (h->cfg.dt_init / (double)h->cfg.ndte);
 }
@@ -1190,15 +1194,19 @@ void add_subcycle(Builder &B, int from_parity, bool last, int ksub)
         const int strips = (g.nxl + kUColsPerWarp - 1) / kUColsPerWarp;
         dim3 grid((strips + kWarpsPerBlock - 1) / kWarpsPerBlock, (g.ny + a.rows_per_chunk - 1) / a.rows_per_chunk);
         if (h->cfg.kdyn == 2) {
-            // eap (source/ice_dyn_eap.F90:340-421): stress_eap + stepu fused, then stepa on every 10th subcycle (:408)
-            // from the stresses this subcycle wrote
+            // eap (source/ice_dyn_eap.F90:340-421) in two stages: the yield stresses of stress_eap, one thread per (cell,
+            // corner); then relaxation + combinations + stepu in the row sweep; stepa on every 10th subcycle (:408) from the
+            // stresses this subcycle wrote
             EapArgs e;
             fill_eap_args(h, e);
+            dim3 g2((g.nxl + 1 + 31) / 32, g.ny + 1);
+            auto kern0 = last ? eap_yield_kernel<true> : eap_yield_kernel<false>;
+            kern0<<<g2, 128, 0, L.s()>>>(a, e);
+            ++L.n;
             auto kern2 = last ? eap_subcycle_kernel<true> : eap_subcycle_kernel<false>;
             kern2<<<grid, kWarpsPerBlock * 32, 0, L.s()>>>(a, e);
             ++L.n;
             if (ksub % 10 == 1) {
-                dim3 g2((g.nxl + 1 + 127) / 128, g.ny + 1);
                 eap_stepa_kernel<<<g2, 128, 0, L.s()>>>(e, g.nxl, g.ny, g.ld, h->ldm, h->mask(),
                                                         h->plane(from_parity ? S_STRA : S_STRB), h->plane_elems);
                 ++L.n;
@@ -1333,7 +1341,8 @@ void build_program(evp_handle *h, double dt, Program &P)
         if (cfg.kdyn == 2) {   // structure tensor back to isotropic where there is no ice (ice_dyn_eap.F90:274-289)
             EapArgs e;
             fill_eap_args(h, e);
-            eap_reset_kernel<<<grid2d(h), 128, 0, s>>>(e, h->nxb, h->nyb, h->ld, h->plane(W_ICETMASK));
+            eap_reset_kernel<<<dim3((h->nxb + 31) / 32, h->nyb), 128, 0, s>>>(e, h->nxb, h->nyb, h->ld, h->ldm,
+                                                                             h->plane(W_ICETMASK), h->mask());
             ++L.n;
         }
         if (h->use_tma) {   // per-strip row activity for the TMA producer

@@ -27,31 +27,44 @@ struct EapArgs {
     double *a11c[4], *a12c[4];         // structure tensor at the corners ne nw sw se (planes of the arena's pitch)
     double *a11, *a12;                 // cell averages (stepa)
     double *out[9];                    // e11 e12 e22 s11 s12 s22 yieldstress11 yieldstress12 yieldstress22
+    double *rot[16];                   // per corner q: rot[4q] gamma, [4q+1] Q11, [4q+2] Q12, [4q+3] ka (as a double)
+    double *yld[12];                   // per corner q: yld[3q] stressptmp, [3q+1] stressmtmp, [3q+2] stress12tmp
+    double *alphar[4];                 // per corner: ridging function of the last subcycle
     double dtei;                       // 1 / dte (stepa)
 };
+
+// First part of update_stress_rdg (:1527-1548 and ka of :1601): what depends on the structure tensor alone -- the angle
+// gamma of its principal axis, the rotation (Q11, Q12) and the table index ka.  a11, a12 change only in stepa (every
+// 10th subcycle) and in the reset at the start of a call, so these four values are computed there and stored; the
+// statements and their operands are the reference's, only the moment of evaluation differs.
+__device__ __forceinline__ void eap_rotation(double a11, double a12, double &gamma, double &Q11, double &Q12, double &kaf)
+{
+    const double a22 = 1.0 - a11;
+    gamma = 0.5 * evp_atan2((2.0 * a12), (a11 - a22));
+    evp_sincos(gamma, &Q12, &Q11);
+    const double Q11Q11 = Q11 * Q11, Q11Q12 = Q11 * Q12, Q12Q12 = Q12 * Q12;
+    double atempprime = Q11Q11 * a11 + 2.0 * Q11Q12 * a12 + Q12Q12 * a22;
+    atempprime = fmax(atempprime, 1.0 - atempprime);
+    const double da = 0.5 / (double)(kEapNa - 1), invda = 1.0 / da;
+    kaf = (double)((int)((atempprime - 0.5) * invda) + 1);
+}
 
 struct EapCorner {
     double sp, sm, s12;                // the yield stresses stressptmp, stressmtmp, stress12tmp
     double alphar;                     // ridging function (last subcycle only)
 };
 
-// update_stress_rdg (:1474-1658), every statement the reference's; alphas is not computed (its only use, rdg_shear,
-// is commented out at :1283-1285).  invsin = c1/sin(pi2/c12) * invstressconviso is passed in (computed once per thread).
+// The rest of update_stress_rdg (:1550-1656), every statement the reference's; alphas is not computed (its only use,
+// rdg_shear, is commented out at :1283-1285).  invsin = c1/sin(pi2/c12) * invstressconviso (:1523-1525).
 template <bool LAST>
-__device__ __forceinline__ EapCorner eap_update_stress_rdg(const EapArgs &e, double invsin, double divu, double tension,
-                                                           double shear, double a11, double a12, double strength)
+__device__ __forceinline__ EapCorner eap_yield(const EapArgs &e, double invsin, double divu, double tension, double shear,
+                                               double gamma, double Q11, double Q12, int ka, double strength)
 {
     const double pi = 3.14159265358979323846, pi2 = 2.0 * pi, piq = 0.5 * (0.5 * pi);
     const double kfriction = 0.45, puny = 1.0e-11;
     EapCorner o;
-    double Q11, Q12, Qd11, Qd12;
-
-    const double a22 = 1.0 - a11;
-    const double gamma = 0.5 * evp_atan2((2.0 * a12), (a11 - a22));
-    evp_sincos(gamma, &Q12, &Q11);
+    double Qd11, Qd12;
     const double Q11Q11 = Q11 * Q11, Q11Q12 = Q11 * Q12, Q12Q12 = Q12 * Q12;
-    double atempprime = Q11Q11 * a11 + 2.0 * Q11Q12 * a12 + Q12Q12 * a22;
-    atempprime = fmax(atempprime, 1.0 - atempprime);
 
     const double dtemp11 = 0.5 * (divu + tension), dtemp12 = shear * 0.5, dtemp22 = 0.5 * (divu - tension);
     double alpha = 0.5 * evp_atan2((2.0 * dtemp12), (dtemp11 - dtemp22));
@@ -71,11 +84,10 @@ __device__ __forceinline__ EapCorner eap_update_stress_rdg(const EapArgs &e, dou
     }
     if (x < piq) x = x + pi2;
 
-    const double dx = pi / (double)(kEapNx - 1), dy = pi / (double)(kEapNy - 1), da = 0.5 / (double)(kEapNa - 1);
-    const double invdx = 1.0 / dx, invdy = 1.0 / dy, invda = 1.0 / da;
+    const double dx = pi / (double)(kEapNx - 1), dy = pi / (double)(kEapNy - 1);
+    const double invdx = 1.0 / dx, invdy = 1.0 / dy;
     const int kx = (int)((x - piq - pi) * invdx) + 1;
     const int ky = (int)(y * invdy) + 1;
-    const int ka = (int)((atempprime - 0.5) * invda) + 1;
     const int q = ((ka - 1) * kEapNy + (ky - 1)) * kEapNx + (kx - 1);
     const double stemp11r = e.tab[0][q], stemp12r = e.tab[1][q], stemp22r = e.tab[2][q];
     const double stemp11s = e.tab[3][q], stemp12s = e.tab[4][q], stemp22s = e.tab[5][q];
@@ -152,57 +164,103 @@ __device__ __forceinline__ void stress_combine(const Consts &k, const double (&s
     str[7] = strp_tmp - strm_tmp + str12sn - dyhx * (csigpsw + csigmsw) + dxhy * csig12sw;
 }
 
-// One T cell of stress_eap (:1186-1463).  s[12] in/out; str[8] out; on the last subcycle the diagnostics too.
+// ---- stage 1 of a subcycle: the yield stresses, one thread per (T cell, corner) ---------------------------------------
+// stress_eap's strain rates of ONE corner (:1194-1232) and update_stress_rdg for it (:1239-1262).  A warp works on one
+// corner of 32 consecutive cells of a row (the corner is warp-uniform: no divergence in the choice of coefficients; loads
+// and stores are 256-byte rows), a CTA of 4 warps on the four corners of the same 32 cells (the metric terms and
+// velocities the corners share come out of L1).  About 70 registers per thread: 6 and more CTAs per SM, where the same
+// arithmetic inside the row sweep (140 registers) kept 2.7 warps per scheduler in flight (profiles/r02_eap.md).
+template <bool LAST>
+__global__ void __launch_bounds__(128)
+eap_yield_kernel(const __grid_constant__ LoopArgs a, const __grid_constant__ EapArgs e)
+{
+    const int q = threadIdx.x >> 5;                        // corner: 0 ne, 1 nw, 2 sw, 3 se
+    const int c = 1 + blockIdx.x * 32 + (threadIdx.x & 31), r = 1 + blockIdx.y;
+    if (c > a.nxl + 1) return;
+    if (!(a.mask[(size_t)r * a.ldm + c] & 1u)) return;
+    const size_t idx = (size_t)r * a.ld + c;
+    const double u_ij = a.u0[idx], u_wj = a.u0[idx - 1], u_is = a.u0[idx - a.ld], u_ws = a.u0[idx - a.ld - 1];
+    const double v_ij = a.v0[idx], v_wj = a.v0[idx - 1], v_is = a.v0[idx - a.ld], v_ws = a.v0[idx - a.ld - 1];
+    const double dxt = a.dxt[idx], dyt = a.dyt[idx], cxp = a.cxp[idx], cyp = a.cyp[idx], cxm = a.cxm[idx], cym = a.cym[idx];
+    double divu, tension, shear;
+    if (q == 0) {
+        divu = cyp * u_ij - dyt * u_wj + cxp * v_ij - dxt * v_is;
+        tension = -cym * u_ij - dyt * u_wj + cxm * v_ij + dxt * v_is;
+        shear = -cym * v_ij - dyt * v_wj - cxm * u_ij - dxt * u_is;
+    } else if (q == 1) {
+        divu = cym * u_wj + dyt * u_ij + cxp * v_wj - dxt * v_ws;
+        tension = -cyp * u_wj + dyt * u_ij + cxm * v_wj + dxt * v_ws;
+        shear = -cyp * v_wj + dyt * v_ij - cxm * u_wj - dxt * u_ws;
+    } else if (q == 2) {
+        divu = cym * u_ws + dyt * u_is + cxm * v_ws + dxt * v_wj;
+        tension = -cyp * u_ws + dyt * u_is + cxp * v_ws - dxt * v_wj;
+        shear = -cyp * v_ws + dyt * v_is - cxp * u_ws + dxt * u_wj;
+    } else {
+        divu = cyp * u_is - dyt * u_ws + cxm * v_is + dxt * v_ij;
+        tension = -cym * u_is - dyt * u_ws + cxp * v_is - dxt * v_ij;
+        shear = -cym * v_is - dyt * v_ws - cxp * u_is + dxt * u_ij;
+    }
+    // invsin = c1/sin(pi2/c12) * invstressconviso (:1523-1525)
+    const double invsin = 1.0 / evp_sin((2.0 * 3.14159265358979323846) / 12.0) * (1.0 / (1.0 + 0.45 * 0.45));
+    const EapCorner o = eap_yield<LAST>(e, invsin, divu, tension, shear, e.rot[4 * q][idx], e.rot[4 * q + 1][idx],
+                                        e.rot[4 * q + 2][idx], (int)e.rot[4 * q + 3][idx], a.strength[idx]);
+    e.yld[3 * q][idx] = o.sp;
+    e.yld[3 * q + 1][idx] = o.sm;
+    e.yld[3 * q + 2][idx] = o.s12;
+    if (LAST) e.alphar[q][idx] = o.alphar;
+}
+
+// ---- stage 2: relaxation + combinations + stepu --------------------------------------------------------------------
+// One T cell of the rest of stress_eap (:1264-1463): s[12] in/out, the yield stresses from stage 1; str[8] out; on the
+// last subcycle the diagnostics (which need the strain rates again: 12 cheap expressions).
 struct EapDiag {
     double divu, shear, rdg_conv, e11, e12, e22, s11, s12, s22, ys11, ys12, ys22;
 };
 template <bool LAST>
 __device__ __forceinline__ void stress_eap_cell(
-    const Consts &k, const EapArgs &e, double invsin, size_t idx, double u_ij, double u_wj, double u_is, double u_ws,
-    double v_ij, double v_wj, double v_is, double v_ws, double dxt, double dyt, double dxhy, double dyhx, double cxp,
-    double cyp, double cxm, double cym, double strength, double tarear, double (&s)[12], double (&str)[8], EapDiag &dg)
+    const Consts &k, const EapArgs &e, const LoopArgs &a, size_t idx, double u_ij, double u_wj, double u_is, double u_ws,
+    double v_ij, double v_wj, double v_is, double v_ws, double (&s)[12], double (&str)[8], EapDiag &dg)
 {
-    // strain rates * area (:1194-1232)
-    const double divune = cyp * u_ij - dyt * u_wj + cxp * v_ij - dxt * v_is;
-    const double divunw = cym * u_wj + dyt * u_ij + cxp * v_wj - dxt * v_ws;
-    const double divusw = cym * u_ws + dyt * u_is + cxm * v_ws + dxt * v_wj;
-    const double divuse = cyp * u_is - dyt * u_ws + cxm * v_is + dxt * v_ij;
-    const double tensionne = -cym * u_ij - dyt * u_wj + cxm * v_ij + dxt * v_is;
-    const double tensionnw = -cyp * u_wj + dyt * u_ij + cxm * v_wj + dxt * v_ws;
-    const double tensionsw = -cyp * u_ws + dyt * u_is + cxp * v_ws - dxt * v_wj;
-    const double tensionse = -cym * u_is - dyt * u_ws + cxp * v_is - dxt * v_ij;
-    const double shearne = -cym * v_ij - dyt * v_wj - cxm * u_ij - dxt * u_is;
-    const double shearnw = -cyp * v_wj + dyt * v_ij - cxm * u_wj - dxt * u_ws;
-    const double shearsw = -cyp * v_ws + dyt * v_is - cxp * u_ws + dxt * u_wj;
-    const double shearse = -cym * v_is - dyt * v_ws - cxp * u_is + dxt * u_ij;
-
-    // :1239-1262
-    const EapCorner ne = eap_update_stress_rdg<LAST>(e, invsin, divune, tensionne, shearne, e.a11c[0][idx], e.a12c[0][idx], strength);
-    const EapCorner nw = eap_update_stress_rdg<LAST>(e, invsin, divunw, tensionnw, shearnw, e.a11c[1][idx], e.a12c[1][idx], strength);
-    const EapCorner sw = eap_update_stress_rdg<LAST>(e, invsin, divusw, tensionsw, shearsw, e.a11c[2][idx], e.a12c[2][idx], strength);
-    const EapCorner se = eap_update_stress_rdg<LAST>(e, invsin, divuse, tensionse, shearse, e.a11c[3][idx], e.a12c[3][idx], strength);
+    double y[12];                                          // ne.sp ne.sm ne.s12 nw.sp ...
+#pragma unroll
+    for (int t = 0; t < 12; ++t) y[t] = e.yld[t][idx];
+    const double dxt = a.dxt[idx], dyt = a.dyt[idx];
 
     // elastic relaxation (:1303-1331)
-    s[0] = (s[0] + ne.sp * k.arlx1i) * k.denom1;
-    s[1] = (s[1] + nw.sp * k.arlx1i) * k.denom1;
-    s[2] = (s[2] + sw.sp * k.arlx1i) * k.denom1;
-    s[3] = (s[3] + se.sp * k.arlx1i) * k.denom1;
-    s[4] = (s[4] + ne.sm * k.arlx1i) * k.denom1;
-    s[5] = (s[5] + nw.sm * k.arlx1i) * k.denom1;
-    s[6] = (s[6] + sw.sm * k.arlx1i) * k.denom1;
-    s[7] = (s[7] + se.sm * k.arlx1i) * k.denom1;
-    s[8] = (s[8] + ne.s12 * k.arlx1i) * k.denom1;
-    s[9] = (s[9] + nw.s12 * k.arlx1i) * k.denom1;
-    s[10] = (s[10] + sw.s12 * k.arlx1i) * k.denom1;
-    s[11] = (s[11] + se.s12 * k.arlx1i) * k.denom1;
+    s[0] = (s[0] + y[0] * k.arlx1i) * k.denom1;
+    s[1] = (s[1] + y[3] * k.arlx1i) * k.denom1;
+    s[2] = (s[2] + y[6] * k.arlx1i) * k.denom1;
+    s[3] = (s[3] + y[9] * k.arlx1i) * k.denom1;
+    s[4] = (s[4] + y[1] * k.arlx1i) * k.denom1;
+    s[5] = (s[5] + y[4] * k.arlx1i) * k.denom1;
+    s[6] = (s[6] + y[7] * k.arlx1i) * k.denom1;
+    s[7] = (s[7] + y[10] * k.arlx1i) * k.denom1;
+    s[8] = (s[8] + y[2] * k.arlx1i) * k.denom1;
+    s[9] = (s[9] + y[5] * k.arlx1i) * k.denom1;
+    s[10] = (s[10] + y[8] * k.arlx1i) * k.denom1;
+    s[11] = (s[11] + y[11] * k.arlx1i) * k.denom1;
 
     if (LAST) {
+        const double cxp = a.cxp[idx], cyp = a.cyp[idx], cxm = a.cxm[idx], cym = a.cym[idx], tarear = a.tarear[idx];
+        // strain rates * area (:1194-1232)
+        const double divune = cyp * u_ij - dyt * u_wj + cxp * v_ij - dxt * v_is;
+        const double divunw = cym * u_wj + dyt * u_ij + cxp * v_wj - dxt * v_ws;
+        const double divusw = cym * u_ws + dyt * u_is + cxm * v_ws + dxt * v_wj;
+        const double divuse = cyp * u_is - dyt * u_ws + cxm * v_is + dxt * v_ij;
+        const double tensionne = -cym * u_ij - dyt * u_wj + cxm * v_ij + dxt * v_is;
+        const double tensionnw = -cyp * u_wj + dyt * u_ij + cxm * v_wj + dxt * v_ws;
+        const double tensionsw = -cyp * u_ws + dyt * u_is + cxp * v_ws - dxt * v_wj;
+        const double tensionse = -cym * u_is - dyt * u_ws + cxp * v_is - dxt * v_ij;
+        const double shearne = -cym * v_ij - dyt * v_wj - cxm * u_ij - dxt * u_is;
+        const double shearnw = -cyp * v_wj + dyt * v_ij - cxm * u_wj - dxt * u_ws;
+        const double shearsw = -cyp * v_ws + dyt * v_is - cxp * u_ws + dxt * u_wj;
+        const double shearse = -cym * v_is - dyt * v_ws - cxp * u_is + dxt * u_ij;
         // :1268-1286
         const double ts = tensionne + tensionnw + tensionse + tensionsw;
         const double ss = shearne + shearnw + shearse + shearsw;
         dg.shear = 0.25 * tarear * sqrt(ts * ts + ss * ss);
         dg.divu = 0.25 * (divune + divunw + divuse + divusw) * tarear;
-        dg.rdg_conv = -fmin(0.25 * (ne.alphar + nw.alphar + sw.alphar + se.alphar), 0.0) * tarear;
+        dg.rdg_conv = -fmin(0.25 * (e.alphar[0][idx] + e.alphar[1][idx] + e.alphar[2][idx] + e.alphar[3][idx]), 0.0) * tarear;
         // :1288-1295 (written on every subcycle by the reference; the last one's values survive the call)
         dg.e11 = 0.5 * 0.25 * (divune + divunw + divuse + divusw + tensionne + tensionnw + tensionse + tensionsw) * tarear;
         dg.e12 = 0.5 * 0.25 * (shearne + shearnw + shearse + shearsw) * tarear;
@@ -211,16 +269,15 @@ __device__ __forceinline__ void stress_eap_cell(
         dg.s11 = 0.5 * 0.25 * (s[0] + s[1] + s[2] + s[3] + s[4] + s[5] + s[6] + s[7]);
         dg.s22 = 0.5 * 0.25 * (s[0] + s[1] + s[2] + s[3] - s[4] - s[5] - s[6] - s[7]);
         dg.s12 = 0.25 * (s[8] + s[9] + s[10] + s[11]);
-        dg.ys11 = 0.5 * 0.25 * (ne.sp + nw.sp + sw.sp + se.sp + ne.sm + nw.sm + sw.sm + se.sm);
-        dg.ys22 = 0.5 * 0.25 * (ne.sp + nw.sp + sw.sp + se.sp - ne.sm - nw.sm - sw.sm - se.sm);
-        dg.ys12 = 0.25 * (ne.s12 + nw.s12 + sw.s12 + se.s12);
+        dg.ys11 = 0.5 * 0.25 * (y[0] + y[3] + y[6] + y[9] + y[1] + y[4] + y[7] + y[10]);
+        dg.ys22 = 0.5 * 0.25 * (y[0] + y[3] + y[6] + y[9] - y[1] - y[4] - y[7] - y[10]);
+        dg.ys12 = 0.25 * (y[2] + y[5] + y[8] + y[11]);
     }
-    stress_combine(k, s, dxt, dyt, dxhy, dyhx, str);
+    stress_combine(k, s, dxt, dyt, a.dxhy[idx], a.dyhx[idx], str);
 }
 
-// stress_eap + stepu + E-W ghost stores + tripole inbox stores: the register sweep of evp_subcycle_kernel
-// (evp_kernels.cuh) around stress_eap_cell.  Classic relaxation only (the reference's eap ignores revised_evp's stepu
-// terms in the same way the EVP kernel handles revp = 0).
+// relaxation + combinations + stepu + E-W ghost stores + tripole inbox stores: the register sweep of evp_subcycle_kernel
+// (evp_kernels.cuh) around stress_eap_cell.  Classic relaxation only (kdyn = 2 with revised_evp is rejected at init).
 template <bool LAST>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 eap_subcycle_kernel(const __grid_constant__ LoopArgs a, const __grid_constant__ EapArgs e)
@@ -237,8 +294,6 @@ eap_subcycle_kernel(const __grid_constant__ LoopArgs a, const __grid_constant__ 
     const bool tstore_col = tcol && (lane < kUColsPerWarp || c == a.nxl + 1);
     const Consts &k = a.k;
     const int ld = a.ld;
-    // invsin = c1/sin(pi2/c12) * invstressconviso (:1523-1525)
-    const double invsin = 1.0 / evp_sin((2.0 * 3.14159265358979323846) / 12.0) * (1.0 / (1.0 + 0.45 * 0.45));
 
     size_t idx = (size_t)(r0 - 1) * ld + c;
     double u_s = tcol ? a.u0[idx] : 0.0, v_s = tcol ? a.v0[idx] : 0.0;
@@ -261,16 +316,13 @@ eap_subcycle_kernel(const __grid_constant__ LoopArgs a, const __grid_constant__ 
 #pragma unroll
             for (int q = 0; q < 12; ++q) s[q] = a.s0[q][idx];
             EapDiag dg;
-            const double strength = a.strength[idx];
-            stress_eap_cell<LAST>(k, e, invsin, idx, u_c, uw_c, u_s, uw_s, v_c, vw_c, v_s, vw_s, a.dxt[idx], a.dyt[idx],
-                                  a.dxhy[idx], a.dyhx[idx], a.cxp[idx], a.cyp[idx], a.cxm[idx], a.cym[idx], strength,
-                                  LAST ? a.tarear[idx] : 0.0, s, str, dg);
+            stress_eap_cell<LAST>(k, e, a, idx, u_c, uw_c, u_s, uw_s, v_c, vw_c, v_s, vw_s, s, str, dg);
             if (tstore_col && (r < rend || r == a.ny + 1)) {
 #pragma unroll
                 for (int q = 0; q < 12; ++q) a.s1[q][idx] = s[q];
                 if (LAST) {
                     a.divu[idx] = dg.divu; a.shear[idx] = dg.shear; a.rdg_conv[idx] = dg.rdg_conv;
-                    a.prs_sig[idx] = strength;                                             // :1297
+                    a.prs_sig[idx] = a.strength[idx];                                      // :1297
                     e.out[0][idx] = dg.e11; e.out[1][idx] = dg.e12; e.out[2][idx] = dg.e22;
                     e.out[3][idx] = dg.s11; e.out[4][idx] = dg.s12; e.out[5][idx] = dg.s22;
                     e.out[6][idx] = dg.ys11; e.out[7][idx] = dg.ys12; e.out[8][idx] = dg.ys22;
@@ -343,32 +395,43 @@ __device__ __forceinline__ void eap_calc_ffrac(double stressp, double stressm, d
     mresult12 = diffuse ? kfrac * (a12 + Q11Q12) : 0.0;
 }
 
-// stepa (:1664-1787) on the T cells of the list (mask bit 0), ghost ring north / east included as in the reference's list
-__global__ void eap_stepa_kernel(EapArgs e, int nxl, int ny, int ld, int ldm, const unsigned char *mask, const double *sp0,
-                                 size_t plane_elems)
+// stepa (:1664-1787), one thread per (T cell of the list, corner) -- mask bit 0; the list includes the north / east ghost
+// cells -- followed by the rotation of the new tensor (eap_rotation) for the subcycles to come; the cell averages
+// (:1780-1781) through shared memory, summed in the reference's order.
+__global__ void __launch_bounds__(128)
+eap_stepa_kernel(const __grid_constant__ EapArgs e, int nxl, int ny, int ld, int ldm, const unsigned char *mask, const double *sp0,
+                 size_t plane_elems)
 {
-    const int c = 1 + blockIdx.x * blockDim.x + threadIdx.x, r = 1 + blockIdx.y;
-    if (c > nxl + 1 || r > ny + 1) return;
-    if (!(mask[(size_t)r * ldm + c] & 1u)) return;
+    __shared__ double sh11[4][32], sh12[4][32];
+    const int q = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int c = 1 + blockIdx.x * 32 + lane, r = 1 + blockIdx.y;
+    const bool act = c <= nxl + 1 && (mask[(size_t)r * ldm + min(c, nxl + 1)] & 1u);
     const size_t idx = (size_t)r * ld + c;
-    const double kth = 0.2 * 0.001;
-    const double dteikth = 1.0 / (e.dtei + kth), p5kth = 0.5 * kth;
-    double a11n[4], a12n[4];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {                        // ne nw sw se; stresses: 12 consecutive planes p1..4 m1..4 12_1..4
+    if (act) {
+        const double kth = 0.2 * 0.001;
+        const double dteikth = 1.0 / (e.dtei + kth), p5kth = 0.5 * kth;
+        // stresses: 12 consecutive planes p1..4 m1..4 12_1..4
         const double stressp = sp0[(size_t)q * plane_elems + idx];
         const double stressm = sp0[(size_t)(4 + q) * plane_elems + idx];
         const double stress12 = sp0[(size_t)(8 + q) * plane_elems + idx];
         const double a11 = e.a11c[q][idx], a12 = e.a12c[q][idx];
         double m11, m12;
         eap_calc_ffrac(stressp, stressm, stress12, a11, a12, m11, m12);
-        a11n[q] = (a11 * e.dtei + p5kth - m11) * dteikth;
-        a12n[q] = (a12 * e.dtei - m12) * dteikth;
-        e.a11c[q][idx] = a11n[q];
-        e.a12c[q][idx] = a12n[q];
+        const double a11n = (a11 * e.dtei + p5kth - m11) * dteikth;
+        const double a12n = (a12 * e.dtei - m12) * dteikth;
+        e.a11c[q][idx] = a11n;
+        e.a12c[q][idx] = a12n;
+        sh11[q][lane] = a11n;
+        sh12[q][lane] = a12n;
+        double gamma, Q11, Q12, kaf;
+        eap_rotation(a11n, a12n, gamma, Q11, Q12, kaf);
+        e.rot[4 * q][idx] = gamma; e.rot[4 * q + 1][idx] = Q11; e.rot[4 * q + 2][idx] = Q12; e.rot[4 * q + 3][idx] = kaf;
     }
-    e.a11[idx] = 0.25 * (a11n[0] + a11n[1] + a11n[2] + a11n[3]);
-    e.a12[idx] = 0.25 * (a12n[0] + a12n[1] + a12n[2] + a12n[3]);
+    __syncthreads();
+    if (act && q == 0) {
+        e.a11[idx] = 0.25 * (sh11[0][lane] + sh11[1][lane] + sh11[2][lane] + sh11[3][lane]);
+        e.a12[idx] = 0.25 * (sh12[0][lane] + sh12[1][lane] + sh12[2][lane] + sh12[3][lane]);
+    }
 }
 
 __global__ void fill_plane_kernel(double *p, double v, size_t n)
@@ -377,15 +440,25 @@ __global__ void fill_plane_kernel(double *p, double v, size_t n)
     if (i < n) p[i] = v;
 }
 
-// the structure-tensor reset of the driver (:274-289): every cell of the block, ghost ring included
-__global__ void eap_reset_kernel(EapArgs e, int nxb, int nyb, int ld, const double *icetmask)
+// the structure-tensor reset of the driver (:274-289) on every cell of the block, ghost ring included, then the rotation
+// of the tensor on the T cells of the list (mask bit 0: set by prep2_kernel, launched before this kernel)
+__global__ void __launch_bounds__(128)
+eap_reset_kernel(const __grid_constant__ EapArgs e, int nxb, int nyb, int ld, int ldm, const double *icetmask,
+                 const unsigned char *mask)
 {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+    const int q = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + (threadIdx.x & 31), r = blockIdx.y;
     if (c >= nxb || r >= nyb) return;
     const size_t idx = (size_t)r * ld + c;
+    double a11 = e.a11c[q][idx], a12 = e.a12c[q][idx];
     if (icetmask[idx] == 0.0) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q) { e.a11c[q][idx] = 0.5; e.a12c[q][idx] = 0.0; }
+        a11 = 0.5; a12 = 0.0;
+        e.a11c[q][idx] = a11; e.a12c[q][idx] = a12;
+    }
+    if (mask[(size_t)r * ldm + c] & 1u) {
+        double gamma, Q11, Q12, kaf;
+        eap_rotation(a11, a12, gamma, Q11, Q12, kaf);
+        e.rot[4 * q][idx] = gamma; e.rot[4 * q + 1][idx] = Q11; e.rot[4 * q + 2][idx] = Q12; e.rot[4 * q + 3][idx] = kaf;
     }
 }
 

@@ -86,9 +86,8 @@ EVP_EXP_FN void evp_sincos(double x, double *s, double *c)
 {
     double r, rl, sk, ck;
     int n;
-    if (x != x || fabs(x) > 1.0e5) {   /* outside the claim: NaN stays NaN, huge arguments take the library's values */
-        *s = sin(x);
-        *c = cos(x);
+    if (!(fabs(x) <= 1.0e5)) {         /* outside the claim (NaN, infinities, huge arguments): NaN, on every side alike */
+        *s = *c = EVP_X_DIV(EVP_X_SUB(x, x), EVP_X_SUB(x, x));
         return;
     }
     if (x == 0.0) {                    /* sin(+-0) = +-0 */
