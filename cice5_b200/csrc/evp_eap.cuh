@@ -7,12 +7,17 @@
 //
 // EAP shares evp_prep1 / evp_prep2 / stepu / evp_finish and the halo pattern with EVP; what is new is the stress update
 // (a table look-up per corner instead of the elliptical yield curve), the structure tensor (a11, a12 at the four corners,
-// persistent state) and its evolution.  The subcycle kernel below is the register-sweep kernel of evp_kernels.cuh with
-// stress_eap as its cell function: a warp marches a strip of 31 U columns north, `str` never reaches memory.  The kernel
-// is FP64-arithmetic heavy (three atan2 and two sin / cos pairs per corner, cice5_b200/csrc/evp_trig.h: the one definition
-// shared with the CPU oracle) and gathers 6 table values per corner from 1.7 MB of L2-resident tables.
-// The structure tensor is read-only inside the subcycle kernel (the redundant ring cells of the sweep read the same
-// values as their owners); stepa runs as its own element-wise kernel on the subcycles the reference calls it.
+// persistent state) and its evolution.  A subcycle runs in two stages:
+//   1. eap_yield_kernel: one thread per (T cell, corner) evaluates update_stress_rdg -- two atan2, one sin / cos pair
+//      (cice5_b200/csrc/evp_trig.h: the one definition shared with the CPU oracle), 6 gathers from 1.7 MB of L2-resident
+//      tables -- and stores the three yield stresses of its corner.  FP64-pipe bound; 54 registers keep 36 warps per SM in
+//      flight.  (Measured first with this arithmetic inside the sweep: 140 registers, 2.7 warps per scheduler, the FP64
+//      pipe 38 % active; profiles/r02_eap.md.)
+//   2. eap_subcycle_kernel: the register-sweep kernel of evp_kernels.cuh with the rest of stress_eap as its cell function
+//      (relaxation towards the yield stresses, stress combinations) fused with stepu: `str` never reaches memory.
+// The part of update_stress_rdg that depends on the structure tensor alone (gamma, Q11, Q12, ka) is evaluated where the
+// tensor changes -- eap_stepa_kernel on the subcycles the reference calls stepa, eap_reset_kernel at the start of a call --
+// and stored.  The tensor is read-only inside the subcycle kernels.
 #pragma once
 #include "evp_kernels.cuh"
 #include "evp_trig.h"
