@@ -51,7 +51,9 @@ __device__ __forceinline__ void eap_rotation(double a11, double a12, double &gam
     double atempprime = Q11Q11 * a11 + 2.0 * Q11Q12 * a12 + Q12Q12 * a22;
     atempprime = fmax(atempprime, 1.0 - atempprime);
     const double da = 0.5 / (double)(kEapNa - 1), invda = 1.0 / da;
-    kaf = (double)((int)((atempprime - 0.5) * invda) + 1);
+    // (a tensor with an eigenvalue outside [0, 1] -- possible only outside the model's regime, e.g. dte of the order of
+    // 1 / kfrac -- would index past the tables, which the reference does not check: the nearest entry is taken instead)
+    kaf = (double)min(max((int)((atempprime - 0.5) * invda) + 1, 1), kEapNa);
 }
 
 struct EapCorner {
@@ -91,8 +93,8 @@ __device__ __forceinline__ EapCorner eap_yield(const EapArgs &e, double invsin, 
 
     const double dx = pi / (double)(kEapNx - 1), dy = pi / (double)(kEapNy - 1);
     const double invdx = 1.0 / dx, invdy = 1.0 / dy;
-    const int kx = (int)((x - piq - pi) * invdx) + 1;
-    const int ky = (int)(y * invdy) + 1;
+    const int kx = min(max((int)((x - piq - pi) * invdx) + 1, 1), kEapNx);   // clamped: see eap_rotation
+    const int ky = min(max((int)(y * invdy) + 1, 1), kEapNy);
     const int q = ((ka - 1) * kEapNy + (ky - 1)) * kEapNx + (kx - 1);
     const double stemp11r = e.tab[0][q], stemp12r = e.tab[1][q], stemp22r = e.tab[2][q];
     const double stemp11s = e.tab[3][q], stemp12s = e.tab[4][q], stemp22s = e.tab[5][q];

@@ -49,6 +49,21 @@ def test_one_rank_bitwise(dev, tables, grid, scenario, ndte, fresh):
     assert not np.array_equal(evp_ref.io["uvel"], ref.io["uvel"])
 
 
+def test_outside_the_regime_nearest_table_entry(dev, tables):
+    """ndte = 3 with dt = 3600 s: a subcycle step of the order of 1 / kfrac lets stepa leave the set of valid structure
+    tensors (an eigenvalue above 1), where the reference would index past its tables (it does not check).  Device and
+    oracle take the nearest entry: no fault, and still the same bits."""
+    case = fx.make_case(fx.make_grid("gx3"), "full", ndte=3, dt=3600.0)
+    e0 = eap_state(case.dom)
+    ref, ref_e = clone_case(case), clone_eap(e0)
+    orc.run_case_eap(ref, ref_e, tables)
+    lam = max(float((0.5 + np.sqrt((ref_e[f"a11_{c}"] - 0.5) ** 2 + ref_e[f"a12_{c}"] ** 2)).max()) for c in (1, 2, 3, 4))
+    assert lam > 1.0                                  # the case does leave the valid set
+    got, got_e = clone_case(case), clone_eap(e0)
+    dev.run_case_eap(got, got_e, tables, strict=True)
+    compare_eap(got, ref, got_e, ref_e, case.dom)
+
+
 @pytest.mark.parametrize("nranks,starts", [(2, None), (3, [0, 20, 60])])
 def test_ranks_two_calls_bitwise(dev, tables, nranks, starts):
     """x-slabs, state (velocities, stresses, structure tensor) carried on the device from one call to the next."""

@@ -3,10 +3,8 @@
 reference: set_evp_parameters `revised_evp` branch (source/ice_dyn_shared.F90:225-233), stresses
 restarted from zero in evp_prep2 (:492-504), revp in stepu (:715,732-734).
 
-NOT YET RUN ON HARDWARE: this row was written after the round's GPU budget was spent (DESIGN.md
-section 8); the CPU oracle side is tested in tests/test_oracle_cpu.py.  The tests are marked
-(first hardware run: round 1 end tier, all passed) -- a defect here must not hide behind the
-validated classic-EVP parity suite behind `pytest -x`; an XPASS is the expected outcome."""
+The CPU oracle side is tested in tests/test_oracle_cpu.py.  Validated on hardware since the end of round 1
+(no xfail mark: a failure is a failure)."""
 import numpy as np
 import pytest
 

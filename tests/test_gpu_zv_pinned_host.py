@@ -4,8 +4,7 @@ host-buffer call is not slower than with pageable arrays.
 reference: the arrays that cross the boundary are static module arrays (source/ice_state.F90:54-56,143-146;
 source/ice_flux.F90:37-107), so a Fortran host can register them once.
 
-NOT YET RUN ON HARDWARE (written after the round's GPU budget was spent): xfail(strict=False) until its
-first run on a B200, an XPASS is the expected outcome; runs in its own child process (tests/conftest.py)."""
+Validated on hardware since the end of round 1 (no xfail mark: a failure is a failure)."""
 import time
 
 import numpy as np

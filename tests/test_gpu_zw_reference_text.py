@@ -13,10 +13,8 @@ The strength is handed in from the host (the oracle's ice_strength on every cell
 bit to the reference's ice_strength text) and masked to the icetmask list on the device
 (strength_masked = 1), which is what the in-driver call of the reference does.
 
-NOT YET RUN ON HARDWARE: the vectors were produced after the round's GPU budget was spent; the domains
-are far smaller than anything validated so far (24 x 12).  Marked xfail(strict=False) until the first
-run on a B200 so that a defect here cannot hide the validated parity suite behind `pytest -x`; an
-XPASS is the expected outcome."""
+The domains are far smaller than the other device tests' (24 x 12).  Validated on hardware since the end of
+round 1 (no xfail mark: a failure is a failure)."""
 import os
 
 import numpy as np

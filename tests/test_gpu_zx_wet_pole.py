@@ -8,10 +8,8 @@ reproduced in oracle/evp_oracle.c (halo_r8_ex) and csrc/evp_kernels.cuh (fold_ne
 kFirstPair3D).  On every real grid, and on the other fixtures of this suite, those U points are land
 and hold 0 either way; `synthetic_tripole(..., wet_poles=True)` puts ice on them.
 
-NOT YET RUN ON HARDWARE: the finding came after the round's GPU budget was spent.  The device change is
-two comparisons in fold_necorner_column; the tests are marked xfail(strict=False) until their first run
-on a B200 so that a defect here cannot hide the validated parity suite behind `pytest -x`; an XPASS is
-the expected outcome."""
+The device change is two comparisons in fold_necorner_column.  Validated on hardware since the end of round 1
+(no xfail mark: a failure is a failure)."""
 import numpy as np
 import pytest
 

@@ -4,8 +4,8 @@ CPU part (runs everywhere): the example compiles against include/evp_b200.h, lin
 library and, without a device, fails loudly with EVP_ERR_NO_DEVICE (there is no CPU fallback).
 GPU part: the same binary runs evp(dt) on a closed basin and must reproduce the oracle's numbers
 for that case (computed with oracle.run_case on the same inputs: uvel = 1.154007e-01,
-vvel = -2.511930e-02 at the centre).  Added after the round's GPU budget was spent:
-xfail(strict=False) until its first hardware run."""
+vvel = -2.511930e-02 at the centre).  Validated on hardware since the end of round 1
+(no xfail mark: a failure is a failure)."""
 import os
 import re
 import shutil
