@@ -59,6 +59,7 @@ def parse():
                     help="skip the transport-stage block (departure_points + field reconstruction, N = 1 only)")
     ap.add_argument("--no-other-configs", action="store_true",
                     help="skip the short measurements of the other BASELINE grid shapes")
+    ap.add_argument("--no-eap", action="store_true", help="skip the EAP (kdyn = 2) block (N = 1 only)")
     ap.add_argument("--cpu-ndte", type=int, default=120,
                     help="subcycles of the CPU sample (120 = one whole evp call, about 25 s on 16 cores)")
     return ap.parse_args()
@@ -593,6 +594,79 @@ def transport_block(e, args, grid, case, dt, steps=5, warmup=2, cpu=False):
             "parity": "tests/test_gpu_zt_transport.py: bitwise against oracle/remap_oracle.c (pinned to the reference text)"}
 
 
+def eap_block(args, device=0):
+    """EAP (kdyn = 2) beside the headline, N = 1: `eap(dt)` through the same entry points.
+    (a) the 1-degree tripole, one whole call at ndte = 120: every inout / out field and every EAP field bit for bit against
+        the oracle (outside any timed region), device time of the ndte loop;
+    (b) the bench grid, ndte = 11 (stepa on subcycles 1 and 11), three calls: device time per subcycle (its parity at this
+        size: tools/profile_eap.py, profiles/r02_eap.md).
+    The lookup tables are an input of the path (the host's init_eap): fixtures.eap_tables()."""
+    from cice5_b200 import evp, fixtures as fx
+    tables = fx.eap_tables()
+
+    def state(dom, seed=5):
+        r = np.random.default_rng(seed)
+        sh = (dom.ny + 2, dom.nx + 2)
+        e = {}
+        for c in (1, 2, 3, 4):                    # a valid structure tensor: eigenvalues inside (0, 1)
+            e[f"a11_{c}"] = r.uniform(0.3, 0.9, sh)
+            e[f"a12_{c}"] = r.uniform(-0.9, 0.9, sh) * np.sqrt(e[f"a11_{c}"] * (1.0 - e[f"a11_{c}"]))
+        for n in ("a11", "a12") + evp.EAP_OUT:
+            e[n] = np.zeros(sh)
+        return e
+
+    def run(gridname, ndte, calls, check):
+        grid = fx.make_grid(gridname)
+        dt = fx.GRID_DT.get(gridname, 3600.0)
+        case = fx.make_case(grid, args.scenario, ndte=ndte, dt=dt)
+        e0 = state(case.dom)
+        got_e = {k: v.copy() for k, v in e0.items()}
+        io = {k: v.copy() for k, v in case.io.items()}
+        e = evp.EvpGpu.for_domain(grid.dom, ndte, dt, device=device, strict=True, kdyn=2)
+        try:
+            e.set_grid(grid.f)
+            e.set_eap_tables(tables)
+            e.upload_eap(got_e)
+            ms = []
+            out = None
+            for k in range(calls):
+                out = fx.zeroed_outputs(case.dom)
+                e.evp(dt, case.inp, io, out)
+                st = e.stats()
+                ms.append(st.loop_ms)
+                if k == 0 and check:
+                    e.download_eap(got_e)
+                    first = ({n: v.copy() for n, v in io.items()}, out, {n: v.copy() for n, v in got_e.items()})
+            r = {"workload": workload_name(args, grid.dom, dt, gridname).replace(f"ndte={args.ndte}", f"ndte={ndte}") + " kdyn=2 (EAP)",
+                 "ndte": ndte, "active_t_cells": int(st.active_t_cells), "loop_ms": min(ms),
+                 "us_per_subcycle": 1e3 * min(ms) / ndte, "value": st.active_t_cells * ndte / (min(ms) * 1e-3),
+                 "unit": "cell-subcycles/s", "loop_kernel_launches": int(st.loop_kernel_launches)}
+            if check:
+                from oracle import oracle as orc                     # the checker, outside every timed region
+                ref = fx.make_case(grid, args.scenario, ndte=ndte, dt=dt)
+                ref_e = {k: v.copy() for k, v in e0.items()}
+                t0 = time.perf_counter()
+                ost = orc.run_case_eap(ref, ref_e, tables, nthreads=len(os.sched_getaffinity(0)))
+                cpu_s = time.perf_counter() - t0
+                gio, gout, ge = first
+                ph = lambda a: a[1:-1, 1:-1]
+                bad = [n for n in PARITY_IO if not np.array_equal(ph(gio[n]), ph(ref.io[n]))]
+                bad += [n for n in PARITY_OUT if gout.get(n) is not None and not np.array_equal(ph(gout[n]), ph(ref.out[n]))]
+                bad += [n for n in evp.EAP_CORNER + evp.EAP_AVG + evp.EAP_OUT if not np.array_equal(ph(ge[n]), ph(ref_e[n]))]
+                r["parity"] = {"bitwise": not bad, "fields": len(PARITY_IO) + len(PARITY_OUT) + 19, "differing": bad[:8],
+                               "oracle": "oracle/eap_oracle.inc, pinned to the reference text (its atan2 / sin / cos: csrc/evp_trig.h)"}
+                r["cpu_port"] = {"value": ost.active_t_cells * ndte / ost.loop_seconds, "unit": "cell-subcycles/s",
+                                 "cores": len(os.sched_getaffinity(0)), "call_s": cpu_s}
+            return r
+        finally:
+            e.close()
+
+    blk = {"tp1": run("tp1", 120, 2, True)}
+    if args.grid != "tp1":
+        blk[args.grid] = run(args.grid, 11, 3, False)
+    return blk
+
+
 def main():
     args = parse()
     if args.impl == "reference":
@@ -643,6 +717,11 @@ def main():
                     "loop_kernel_launches_per_step": r["loop_kernel_launches_per_step"]}
                 if r.get("transport"):
                     others[g]["transport"] = r["transport"]
+    if rank == 0 and N == 1 and not args.no_eap:
+        try:
+            res["eap"] = eap_block(args, ctx.local_rank)
+        except Exception as ex:                   # noqa: BLE001 -- a side block must not cost the headline line
+            res["eap"] = {"error": str(ex)[:300]}
     if rank == 0:
         if cpu is not None:
             res["cpu_baseline"] = cpu

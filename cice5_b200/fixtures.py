@@ -626,3 +626,75 @@ def unslab(parts: list) -> np.ndarray:
     cols = [p[..., (0 if r == 0 else 1):(p.shape[-1] if r == n - 1 else p.shape[-1] - 1)]
             for r, p in enumerate(parts)]
     return np.ascontiguousarray(np.concatenate(cols, axis=-1))
+
+
+# ---- EAP (kdyn = 2): the lookup tables a host hands to evp_gpu_set_eap_tables ------------------------------------
+EAP_TABLES = ("s11r", "s12r", "s22r", "s11s", "s12s", "s22s")
+_eap_tables_cache = None
+
+
+def eap_tables():
+    """init_eap's lookup tables (source/ice_dyn_eap.F90:557-618, kernels s11kr ... s22ks :664-1047, weights w1, w2
+    :626-659) as a dict of (21, 41, 41) arrays = Fortran (nx_yield, ny_yield, na_yield) in C order.  In a model run the
+    host's init_eap computes them; the synthetic drivers (bench.py, tools/) use this vectorised restatement.  Values agree
+    with the reference's loop to rounding (numpy's sin / cos, a vectorised sum over z), which is all an INPUT needs: the
+    device and whatever it is compared with are given the same tables."""
+    global _eap_tables_cache
+    if _eap_tables_cache is not None:
+        return _eap_tables_cache
+    nx, ny, na, nz = 41, 41, 21, 100
+    pi = 3.14159265358979323846
+    pih, piq, puny, eps6, phi = 0.5 * pi, 0.25 * pi, 1.0e-11, 1.0e-6, pi / 12.0
+    da, dx, dy, dz = 0.5 / (na - 1), pi / (nx - 1), pi / (ny - 1), pi / nz
+    ainit, xinit, yinit, zinit = 0.5 - da, pi + piq - dx, -dy, -pih
+    x = (xinit + np.arange(1, nx + 1) * dx)[None, :, None]          # (1, nx, 1)
+    y = (yinit + np.arange(1, ny + 1) * dy)[:, None, None]          # (ny, 1, 1)
+
+    def kernels(z):
+        """The six kernels at z (broadcast over the last axis): arrays (ny, nx, len(z))."""
+        p = phi
+        c, s = np.cos, np.sin
+        n1 = (c(z + pih - p) * c(z + p), c(z + pih - p) * s(z + p), s(z + pih - p) * c(z + p), s(z + pih - p) * s(z + p))
+        n2 = (c(z - pih + p) * c(z - p), c(z - pih + p) * s(z - p), s(z - pih + p) * c(z - p), s(z - pih + p) * s(z - p))
+        t1 = (c(z - p) * c(z + p), c(z - p) * s(z + p), s(z - p) * c(z + p), s(z - p) * s(z + p))
+        t2 = (c(z + p) * c(z - p), c(z + p) * s(z - p), s(z + p) * c(z - p), s(z + p) * s(z - p))
+        ty = np.tan(y)
+        d11 = c(y) * c(y) * (c(x) + s(x) * ty * ty)
+        d12 = c(y) * c(y) * ty * (-c(x) + s(x))
+        d22 = c(y) * c(y) * (s(x) + c(x) * ty * ty)
+        II = lambda m: m[0] * d11 + (m[1] + m[2]) * d12 + m[3] * d22
+        H1 = (-II(n1) >= puny).astype(float)
+        H2 = (-II(n2) >= puny).astype(float)
+        sg = np.copysign(1.0, II(t1) + puny)
+        return (-H1 * n1[0] - H2 * n2[0],
+                0.5 * ((-H1 * n1[1] - H2 * n2[1]) + (-H1 * n1[2] - H2 * n2[2])),
+                -H1 * n1[3] - H2 * n2[3],
+                sg * (H1 * t1[0] + H2 * t2[0]),
+                0.5 * (sg * (H1 * t1[1] + H2 * t2[1]) + sg * (H1 * t1[2] + H2 * t2[2])),
+                sg * (H1 * t1[3] + H2 * t2[3]))
+
+    def w1(a):
+        return (-223.87569446 + 2361.2198663 * a - 10606.56079975 * a ** 2 + 26315.50025642 * a ** 3
+                - 38948.30444297 * a ** 4 + 34397.72407466 * a ** 5 - 16789.98003081 * a ** 6 + 3495.82839237 * a ** 7)
+
+    def w2(a):
+        return (-6670.68911883 + 70222.33061536 * a - 314871.71525448 * a ** 2 + 779570.02793492 * a ** 3
+                - 1151098.82436864 * a ** 4 + 1013896.59464498 * a ** 5 - 493379.44906738 * a ** 6 + 102356.551518 * a ** 7)
+
+    z = (zinit + np.arange(1, nz + 1) * dz)[None, None, :]
+    kz = kernels(z)                                                  # 6 x (ny, nx, nz)
+    k0 = kernels(np.zeros((1, 1, 1)))                                # ia = na_yield: z = 0
+    s2p = np.sin(2.0 * phi)
+    tabs = {n: np.zeros((na, ny, nx)) for n in EAP_TABLES}
+    for ia in range(1, na + 1):
+        a = ainit + ia * da
+        for f, n in enumerate(EAP_TABLES):
+            if ia <= na - 1:
+                wz = w1(a) * np.exp(-w2(a) * z * z) * dz / s2p
+                v = (kz[f] * wz).sum(axis=2)
+            else:
+                v = 0.5 * k0[f][:, :, 0] / s2p
+            v = np.where(np.abs(v) < eps6, 0.0, v)
+            tabs[n][ia - 1] = v
+    _eap_tables_cache = tabs
+    return tabs

@@ -358,3 +358,16 @@ def test_eap_decomposition_independence_and_invariants(slabs):
         assert (lam <= 1.0 + 1e-12).all() and (a11[~ice] == 0.5).all() and (a12[~ice] == 0.0).all()
         assert (a11[ice] != 0.5).any()            # stepa moved it (subcycles 1, 11, 21)
     assert np.abs(phys(c1.io["uvel"])).max() < 5.0
+
+
+def test_fixture_eap_tables_agree_with_the_oracles_generator():
+    """fixtures.eap_tables (vectorised numpy, what bench.py and tools/ hand to evp_gpu_set_eap_tables) against the oracle's
+    restatement of init_eap's loop (pinned bit for bit to the reference text on 64 entries): equal to the rounding of the
+    ill-conditioned weight polynomials w1, w2 (coefficients of 1e6 cancelling to order 1)."""
+    T, R = fx.eap_tables(), orc.eap_tables()
+    for n in fx.EAP_TABLES:
+        assert T[n].shape == orc.EAP_TABLE_SHAPE
+        d = np.abs(T[n] - R[n])
+        flipped = (T[n] == 0.0) != (R[n] == 0.0)                  # |value| within rounding of the 1e-6 cut-off
+        assert d[~flipped].max() < 1.0e-9 and flipped.sum() <= 4 and d.max() <= 1.0e-6 + 1.0e-9, (n, d.max(), flipped.sum())
+        assert np.abs(R[n]).max() > 0.1

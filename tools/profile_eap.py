@@ -19,10 +19,10 @@ def main():
     ndte = int(sys.argv[2]) if len(sys.argv) > 2 else 11
     calls = int(sys.argv[3]) if len(sys.argv) > 3 else 2
     check = int(sys.argv[4]) if len(sys.argv) > 4 else 0
-    from oracle import oracle as orc               # tables: init_eap's generator lives in the oracle (host code)
+    from oracle import oracle as orc               # the checker (check = 1); the tables are fixtures' (an input of the path)
     from tests.eap_util import clone_eap, compare_eap, eap_state
     from tests.util import clone_case
-    tables = orc.eap_tables()
+    tables = fx.eap_tables()
     grid = fx.make_grid(gridname)
     dt = fx.GRID_DT.get(gridname, 3600.0)
     case = fx.make_case(grid, "full", ndte=ndte, dt=dt)
