@@ -464,12 +464,16 @@ int evp_gpu_init(const evp_config_t *cfg, evp_handle_t **out)
         if (h->use_loop) {
             rpc = (2 * nstrips * g.ny) / (3 * slots);
             rpc = rpc < 2 ? 2 : (rpc > 48 ? 48 : rpc);
+            // a grid with fewer one-row items than resident CTAs (gx3: 116): one row per item.  On the L2-resident grids a
+            // subcycle takes a fixed chain + about 2 us per row of an item (profiles/r02_small_grids.md); measured on one
+            // B200: gx3 8.86 -> 7.15 us per subcycle, but gx1 (1152 items) 12.0 -> 14.0, so only below the slot count
+            if (cfg->nranks == 1 && nstrips * g.ny <= slots) rpc = 1;
         } else {
             rpc = (wstrips * g.ny + 4 * slots - 1) / (4 * slots);
             rpc = rpc < 4 ? 4 : (rpc > 32 ? 32 : rpc);
         }
         if (const char *ev = getenv("EVP_B200_RPC")) rpc = atoi(ev);      // tuning experiments
-        rpc = rpc < 2 ? 2 : (rpc > 64 ? 64 : rpc);
+        rpc = rpc < 1 ? 1 : (rpc > 64 ? 64 : rpc);
         h->t_rpc = (int)rpc;
         h->t_chunks = (g.ny + h->t_rpc - 1) / h->t_rpc;
         h->t_items = h->tstrips * h->t_chunks;

@@ -333,7 +333,7 @@ def _group_case(evp, monkeypatch, grid, case, nranks, starts=None, threads=True,
 
 
 @pytest.mark.parametrize("nranks,starts,rpc", [(1, None, None), (2, None, None), (4, None, "3"), (3, [0, 20, 60], "5"),
-                                               (8, None, "2")])
+                                               (8, None, "2"), (1, None, "1"), (3, [0, 20, 60], "1")])
 def test_loop_kernel_tripole_ranks_on_threads_bitwise(monkeypatch, nranks, starts, rpc):
     """evp_loop_tma_kernel (all ndte subcycles in one launch, per-tile dependency counters, the fold as an item):
     1 to 8 ranks really overlapping (a thread and a stream per rank), equal and unequal slabs, several chunk
