@@ -115,3 +115,21 @@ def test_cuda_graph_and_call_order(dev, tables):
         e.close()
     with pytest.raises(dev.EvpError):
         dev.EvpGpu.for_domain(case.dom, case.ndte, case.dt, strict=True, kdyn=2, revised_evp=True)
+
+
+def test_bench_eap_block_on_the_host_build(dev, monkeypatch):
+    """bench.py's `eap` block (the 1-degree call compared with the oracle, the bench grid timed) with both grids replaced by
+    a small tripole: the block's host logic, its parity verdict and the shape of what it adds to the JSON line."""
+    import sys
+    import bench
+    small = fx.synthetic_tripole(48, 24, wet_poles=True)
+    monkeypatch.setattr(fx, "make_grid", lambda name: small)
+    monkeypatch.setattr(sys, "argv", ["bench.py"])
+    args = bench.parse()
+    blk = bench.eap_block(args, 0)
+    assert set(blk) == {"tp1", "tp01"}
+    one = blk["tp1"]
+    assert one["parity"]["bitwise"] is True and one["parity"]["fields"] == 55 and not one["parity"]["differing"]
+    assert one["ndte"] == 120 and one["value"] > 0 and one["cpu_port"]["value"] > 0
+    assert blk["tp01"]["ndte"] == 11 and blk["tp01"]["loop_kernel_launches"] == 2 * 11 + 2 + 11   # yield + sweep, stepa x 2, fold
+    assert "kdyn=2 (EAP)" in one["workload"]
