@@ -31,6 +31,22 @@ def test_eap_one_call_bitwise(grid, scenario, ndte):
           f"{st.active_t_cells} T cells")
 
 
+def test_eap_tenth_degree_bitwise():
+    """The bench grid (3600 x 2700, 7.6 M active T cells), ndte = 11: stepa on subcycles 1 and 11.  The oracle needs about
+    13 s for this call on 16 host threads (profiles/r02_eap.md: first run through tools/profile_eap.py, calls 42 / 43)."""
+    from oracle import oracle as orc
+    tables = orc.eap_tables()
+    case = fx.make_case("tp01", "full", ndte=11)
+    e0 = eap_state(case.dom)
+    ref, ref_e = clone_case(case), clone_eap(e0)
+    orc.run_case_eap(ref, ref_e, tables)
+    got, got_e = clone_case(case), clone_eap(e0)
+    st = evp.run_case_eap(got, got_e, tables, strict=True)
+    compare_eap(got, ref, got_e, ref_e, case.dom)
+    assert st.active_t_cells > 7_000_000
+    print(f"EAP tp01 full ndte=11: loop {st.loop_ms:.3f} ms = {1e3 * st.loop_ms / 11:.1f} us per subcycle")
+
+
 def test_eap_two_calls_three_ranks_and_graph_bitwise():
     from oracle import oracle as orc
     tables = orc.eap_tables()
