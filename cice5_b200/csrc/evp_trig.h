@@ -25,6 +25,28 @@
 
 #include "evp_exp.h" /* EVP_EXP_FN, EVP_X_ADD / SUB / MUL */
 
+/* Polynomial coefficients: file-scope tables.  On the device they live in __constant__ memory, so that DADD / DMUL take
+ * them as c[bank][offset] operands; as local constant arrays every use cost two extra instructions that build the 64-bit
+ * immediate (a third of eap_yield_kernel's issue slots, profiles/r02_eap.md).  Same values, same operations on every side. */
+#if defined(__CUDACC__) && !defined(EVP_EMU)
+#define EVP_TRIG_TABLE static __constant__ double
+#else
+#define EVP_TRIG_TABLE static const double
+#endif
+/* sin: (-1)^k / (2k+1)!, k = 1 .. 9;  cos: (-1)^k / (2k)!, k = 2 .. 10;  atan: (-1)^k / (2k+1), k = 1 .. 21 */
+EVP_TRIG_TABLE evp_trig_S[9] = {-0x1.5555555555555p-3, 0x1.1111111111111p-7, -0x1.a01a01a01a01ap-13, 0x1.71de3a556c734p-19,
+                                -0x1.ae64567f544e4p-26, 0x1.6124613a86d09p-33, -0x1.ae7f3e733b81fp-41, 0x1.952c77030ad4ap-49,
+                                -0x1.2f49b46814157p-57};
+EVP_TRIG_TABLE evp_trig_C[9] = {0x1.5555555555555p-5, -0x1.6c16c16c16c17p-10, 0x1.a01a01a01a01ap-16, -0x1.27e4fb7789f5cp-22,
+                                0x1.1eed8eff8d898p-29, -0x1.93974a8c07c9dp-37, 0x1.ae7f3e733b81fp-45, -0x1.6827863b97d97p-53,
+                                0x1.e542ba4020225p-62};
+EVP_TRIG_TABLE evp_trig_A[21] = {-0x1.5555555555555p-2, 0x1.999999999999ap-3, -0x1.2492492492492p-3, 0x1.c71c71c71c71cp-4,
+                                 -0x1.745d1745d1746p-4, 0x1.3b13b13b13b14p-4, -0x1.1111111111111p-4, 0x1.e1e1e1e1e1e1ep-5,
+                                 -0x1.af286bca1af28p-5, 0x1.8618618618618p-5, -0x1.642c8590b2164p-5, 0x1.47ae147ae147bp-5,
+                                 -0x1.2f684bda12f68p-5, 0x1.1a7b9611a7b96p-5, -0x1.0842108421084p-5, 0x1.f07c1f07c1f08p-6,
+                                 -0x1.d41d41d41d41dp-6, 0x1.bacf914c1bad0p-6, -0x1.a41a41a41a41ap-6, 0x1.8f9c18f9c18fap-6,
+                                 -0x1.7d05f417d05f4p-6};
+
 #define EVP_X_DIV(a, b) evp_x_div_((a), (b))
 #if defined(__CUDACC__) || defined(EVP_EMU)
 EVP_EXP_FN double evp_x_div_(double a, double b) { return __ddiv_rn(a, b); }
@@ -51,13 +73,10 @@ EVP_EXP_FN int evp_rem_pio2(double x, double *rh, double *rl)
 /* sin(r + rl), |r| <= pi/4 */
 EVP_EXP_FN double evp_sin_k(double r, double rl)
 {
-    const double S[9] = {-0x1.5555555555555p-3, 0x1.1111111111111p-7, -0x1.a01a01a01a01ap-13, 0x1.71de3a556c734p-19,
-                         -0x1.ae64567f544e4p-26, 0x1.6124613a86d09p-33, -0x1.ae7f3e733b81fp-41, 0x1.952c77030ad4ap-49,
-                         -0x1.2f49b46814157p-57};
     const double z = EVP_X_MUL(r, r);
-    double p = S[8];
+    double p = evp_trig_S[8];
     int i;
-    for (i = 7; i >= 0; --i) p = EVP_X_ADD(EVP_X_MUL(p, z), S[i]);
+    for (i = 7; i >= 0; --i) p = EVP_X_ADD(EVP_X_MUL(p, z), evp_trig_S[i]);
     /* r + (r z p + rl (1 - z/2)) */
     return EVP_X_ADD(r, EVP_X_ADD(EVP_X_MUL(EVP_X_MUL(r, z), p),
                                   EVP_X_MUL(rl, EVP_X_SUB(1.0, EVP_X_MUL(0.5, z)))));
@@ -66,14 +85,11 @@ EVP_EXP_FN double evp_sin_k(double r, double rl)
 /* cos(r + rl), |r| <= pi/4 */
 EVP_EXP_FN double evp_cos_k(double r, double rl)
 {
-    const double Cc[9] = {0x1.5555555555555p-5, -0x1.6c16c16c16c17p-10, 0x1.a01a01a01a01ap-16, -0x1.27e4fb7789f5cp-22,
-                          0x1.1eed8eff8d898p-29, -0x1.93974a8c07c9dp-37, 0x1.ae7f3e733b81fp-45, -0x1.6827863b97d97p-53,
-                          0x1.e542ba4020225p-62};
     const double z = EVP_X_MUL(r, r);
-    double p = Cc[8];
+    double p = evp_trig_C[8];
     double hz, w;
     int i;
-    for (i = 7; i >= 0; --i) p = EVP_X_ADD(EVP_X_MUL(p, z), Cc[i]);
+    for (i = 7; i >= 0; --i) p = EVP_X_ADD(EVP_X_MUL(p, z), evp_trig_C[i]);
     hz = EVP_X_MUL(0.5, z);
     w = EVP_X_SUB(1.0, hz);
     /* w + (((1 - w) - hz) + (z z p - r rl)) */
@@ -110,12 +126,6 @@ EVP_EXP_FN double evp_atan2(double y, double x)
     const double PIO2_H = 0x1.921fb54442d18p+0, PIO2_L = 0x1.1a62633145c07p-54;
     const double PIO4_H = 0x1.921fb54442d18p-1, PIO4_L = 0x1.1a62633145c07p-55;
     const double T0 = 0x1.a827999fcef32p-2;   /* sqrt(2) - 1 */
-    const double A[21] = {-0x1.5555555555555p-2, 0x1.999999999999ap-3, -0x1.2492492492492p-3, 0x1.c71c71c71c71cp-4,
-                          -0x1.745d1745d1746p-4, 0x1.3b13b13b13b14p-4, -0x1.1111111111111p-4, 0x1.e1e1e1e1e1e1ep-5,
-                          -0x1.af286bca1af28p-5, 0x1.8618618618618p-5, -0x1.642c8590b2164p-5, 0x1.47ae147ae147bp-5,
-                          -0x1.2f684bda12f68p-5, 0x1.1a7b9611a7b96p-5, -0x1.0842108421084p-5, 0x1.f07c1f07c1f08p-6,
-                          -0x1.d41d41d41d41dp-6, 0x1.bacf914c1bad0p-6, -0x1.a41a41a41a41ap-6, 0x1.8f9c18f9c18fap-6,
-                          -0x1.7d05f417d05f4p-6};
     double a, b, t, u, ul, z, p, r;
     int swap, shifted, i;
 
@@ -143,8 +153,8 @@ EVP_EXP_FN double evp_atan2(double y, double x)
         ul = EVP_X_DIV(EVP_X_FMA(-t, b, a), b);                               /* a / b = u + ul */
     }
     z = EVP_X_MUL(u, u);
-    p = A[20];
-    for (i = 19; i >= 0; --i) p = EVP_X_ADD(EVP_X_MUL(p, z), A[i]);
+    p = evp_trig_A[20];
+    for (i = 19; i >= 0; --i) p = EVP_X_ADD(EVP_X_MUL(p, z), evp_trig_A[i]);
     /* atan(u + ul) = u + (u z p + ul / (1 + z)) */
     p = EVP_X_ADD(u, EVP_X_ADD(EVP_X_MUL(EVP_X_MUL(u, z), p), EVP_X_DIV(ul, EVP_X_ADD(1.0, z))));
     r = shifted ? EVP_X_ADD(PIO4_H, EVP_X_ADD(p, PIO4_L)) : p;
