@@ -16,7 +16,7 @@
  * |k| < 2^20), kept as head + tail; Taylor polynomials to r^19 / r^20 on |r| <= pi/4 (truncation < 2^-63), evaluated in
  * the fdlibm arrangement (the tail enters to first order).  atan2: t = min(|y|,|x|) / max(|y|,|x|) in [0, 1]; for
  * t > sqrt(2) - 1 the argument (t - 1)/(t + 1) = (a - b)/(a + b) and the offset pi/4, the quotient's rounding error
- * carried to first order (one fma); odd Taylor polynomial to u^43 on |u| <= sqrt(2) - 1
+ * carried to first order (one fma; two divisions per call in all); odd Taylor polynomial to u^43 on |u| <= sqrt(2) - 1
  * (truncation < 2^-58 relative); pi/2 - r and pi - r with two-part constants; signs and zeros as C's atan2
  * (atan2(+-0, x >= +0) = +-0, atan2(+-0, x <= -0) = +-pi, atan2(y, +-0) = +-pi/2).
  */
@@ -126,7 +126,7 @@ EVP_EXP_FN double evp_atan2(double y, double x)
     const double PIO2_H = 0x1.921fb54442d18p+0, PIO2_L = 0x1.1a62633145c07p-54;
     const double PIO4_H = 0x1.921fb54442d18p-1, PIO4_L = 0x1.1a62633145c07p-55;
     const double T0 = 0x1.a827999fcef32p-2;   /* sqrt(2) - 1 */
-    double a, b, t, u, ul, z, p, r;
+    double a, b, u, ul, z, p, r;
     int swap, shifted, i;
 
     if (x != x || y != y) return EVP_X_ADD(x, y);
@@ -141,22 +141,21 @@ EVP_EXP_FN double evp_atan2(double y, double x)
         return copysign(r, y);
     }
     swap = a > b;
-    if (swap) { const double q = a; a = b; b = q; }                          /* a <= b: t = a / b in [0, 1] */
-    t = EVP_X_DIV(a, b);
-    shifted = t > T0;
+    if (swap) { const double q = a; a = b; b = q; }                          /* a <= b: a / b in [0, 1] */
+    shifted = a > EVP_X_MUL(T0, b);                                           /* a / b > sqrt(2) - 1, without dividing */
     if (shifted) {            /* (t - 1)/(t + 1) = (a - b)/(a + b), numerator and denominator as head + tail */
         const evp_dd n = evp_two_sum(a, -b), d = evp_two_sum(a, b);
         u = EVP_X_DIV(n.hi, d.hi);
         ul = EVP_X_DIV(EVP_X_ADD(EVP_X_FMA(-u, d.hi, n.hi), EVP_X_SUB(n.lo, EVP_X_MUL(u, d.lo))), d.hi);
     } else {
-        u = t;
-        ul = EVP_X_DIV(EVP_X_FMA(-t, b, a), b);                               /* a / b = u + ul */
+        u = EVP_X_DIV(a, b);
+        ul = EVP_X_DIV(EVP_X_FMA(-u, b, a), b);                               /* a / b = u + ul */
     }
     z = EVP_X_MUL(u, u);
     p = evp_trig_A[20];
     for (i = 19; i >= 0; --i) p = EVP_X_ADD(EVP_X_MUL(p, z), evp_trig_A[i]);
-    /* atan(u + ul) = u + (u z p + ul / (1 + z)) */
-    p = EVP_X_ADD(u, EVP_X_ADD(EVP_X_MUL(EVP_X_MUL(u, z), p), EVP_X_DIV(ul, EVP_X_ADD(1.0, z))));
+    /* atan(u + ul) = u + (u z p + ul / (1 + z)); 1 / (1 + z) = 1 - z up to z^2 <= 0.03 of a term below 2^-53 u */
+    p = EVP_X_ADD(u, EVP_X_ADD(EVP_X_MUL(EVP_X_MUL(u, z), p), EVP_X_MUL(ul, EVP_X_SUB(1.0, z))));
     r = shifted ? EVP_X_ADD(PIO4_H, EVP_X_ADD(p, PIO4_L)) : p;
     if (swap) r = EVP_X_SUB(PIO2_H, EVP_X_SUB(r, PIO2_L));
     if (x < 0.0) r = EVP_X_SUB(PI_H, EVP_X_SUB(r, PI_L));
